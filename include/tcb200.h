@@ -1,0 +1,111 @@
+/*
+ * tcb200.h — C ABI of libtcb200.so: the B200 (sm_100a) pre/post-processing hot path of
+ * niqbal996/triton_client, rebuilt from scratch.
+ *
+ * Conventions:
+ *   - every entry point returns int: 0 = ok, <0 = one of TCB_ERR_*; the text of the last failure is
+ *     tcb_last_error(ctx). Nothing here throws, aborts or calls exit() (the reference's own native
+ *     code does: OpenPCDet pcdet/ops/iou3d_nms/src/iou3d_nms.cpp:14-38 — deliberately not mirrored).
+ *   - all `*_dev` pointers are CUDA device pointers on the context's device (e.g. torch
+ *     Tensor.data_ptr()); `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *   - inputs are borrowed and never written; outputs are caller-allocated.
+ *   - after tcb_create no entry point allocates: scratch comes out of the context's workspace and a
+ *     call that needs more than the workspace holds fails with TCB_ERR_WORKSPACE.
+ *   - calls on one context are issued in order on the caller's stream; one frame/batch in flight per
+ *     context (the reference keeps one frame in flight per client object, communicator/ros_inference.py:117-175).
+ *
+ * Paths quoted below are relative to the reference repository root; OPCD/ abbreviates
+ * utils/export_models/OpenPCDet/.
+ */
+#ifndef TCB200_H
+#define TCB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct tcb_ctx tcb_ctx;
+
+enum {
+    TCB_OK = 0,
+    TCB_ERR_ARG = -1,       /* invalid argument */
+    TCB_ERR_CUDA = -2,      /* a CUDA runtime call failed; see tcb_last_error */
+    TCB_ERR_WORKSPACE = -3, /* context workspace too small for this call */
+    TCB_ERR_ALLOC = -4,     /* allocation failed in tcb_create */
+    TCB_ERR_LIMIT = -5      /* size beyond a compiled-in limit */
+};
+
+/* ---- context ------------------------------------------------------------------------------- */
+
+/* Creates a context on `device` owning `workspace_bytes` of device scratch (one cudaMalloc, here and
+ * nowhere else). The pre/post objects of the reference are built once per process
+ * (communicator/ros_inference.py:39-41): that is where this is called. */
+int tcb_create(int device, size_t workspace_bytes, tcb_ctx** out);
+int tcb_destroy(tcb_ctx* ctx);
+/* Last error text of `ctx` (or of the calling thread when ctx is NULL, e.g. after a failed tcb_create). */
+const char* tcb_last_error(const tcb_ctx* ctx);
+size_t tcb_workspace_bytes(const tcb_ctx* ctx);
+const char* tcb_version(void);
+/* Number of kernels launched through this context since creation (bench.py's gpu_launches). */
+long long tcb_launch_count(const tcb_ctx* ctx);
+
+/* ---- 2D preprocess -------------------------------------------------------- */
+
+enum { TCB_RESIZE_STRETCH = 0, TCB_RESIZE_LETTERBOX = 1, TCB_RESIZE_PAD = 2 };
+
+/*
+ * Fused u8 HWC -> [resize] -> [channel swap] -> x/div - sub[c] -> f32 NCHW, n frames per launch.
+ * Replaces, in one pass: cv2.resize(img,(W,H)) INTER_LINEAR (communicator/ros_inference.py:140,
+ * bag_inference2d.py:110, evaluate_inference.py:305, utils/preprocess.py:170), the BGR->RGB flip
+ * (ros_inference.py:131, utils/preprocess.py:171), Yolov5preprocess.image_adjust
+ * (clients/preprocess/yolov5_preprocess.py:12-24; div=255), FCOSpreprocess.image_adjust
+ * (clients/preprocess/detectron_preprocess.py:12-24; div=1), the scaling modes of
+ * utils/preprocess.py:127-175 (INCEPTION div=127.5 sub=1; VGG div=1 sub=(123,117,104)) and
+ * image_adjust_ros' bottom padding (utils/preprocess.py:177-183; TCB_RESIZE_PAD, pad 0).
+ *
+ * Resampling is bit-identical to OpenCV's 8-bit INTER_LINEAR (11-bit fixed-point taps, half-pixel
+ * centres, 2x2 averaging when both scale factors are exactly 2).
+ *   mode STRETCH   : src (h,w) resampled to the whole (out_h,out_w) output (what the reference does).
+ *   mode LETTERBOX : YOLOv5 convention (not in the reference): r=min(out_h/h,out_w/w),
+ *                    content round(w r) x round(h r) centred, rest filled with pad_value.
+ *   mode PAD       : no resampling, src placed top-left, rest filled with pad_value.
+ * src_dev: n frames, row pitch src_row_stride bytes, frame pitch src_img_stride bytes, 3 bytes/pixel.
+ * channel_swap: 0 keep order, 1 reverse (BGR<->RGB).
+ * inv_affine_host (may be NULL): float[4] = {gain_x, gain_y, pad_left, pad_top} so that
+ *   x_src = (x_out - pad_left) / gain_x  — the inverse used to map boxes back
+ *   (communicator/ros_inference.py:100-115 is the stretch case).
+ */
+int tcb_preprocess_image(tcb_ctx* ctx, const uint8_t* src_dev, int n, int h, int w,
+                         long long src_row_stride, long long src_img_stride, int channel_swap,
+                         int mode, int out_h, int out_w, float div, const float sub[3],
+                         int pad_value, float* dst_dev, float* inv_affine_host, void* stream);
+
+/* ---- YOLOv5 postprocess ---------------------------------------------------- */
+
+/*
+ * Confidence filter + conf=obj*cls + best class + xywh2xyxy + class-aware greedy NMS + max_det, for a
+ * whole batch, entirely on device. Replaces Yolov5postprocess.extract_boxes
+ * (clients/postprocess/yolov5_postprocess.py:28-125; twin utils/postprocess.py:105-199) from the
+ * reshape at :37 on; the per-element struct.unpack of :36 (base_postprocess.py:15-25) disappears
+ * because the little-endian wire bytes are the f32 tensor.
+ * pred_dev: [b, n, 5+nc] f32 rows (cx, cy, w, h, obj, cls...). Arithmetic is float64 exactly where the
+ * reference's is (Python-float products, float64 torchvision.ops.nms on boxes offset by cls*4096),
+ * boxes are rounded to f32 where the reference rounds them (:79). Order: score descending, ties by
+ * lower row index (torchvision's stable sort on the row-ordered candidates).
+ * classes_host: optional whitelist (n_classes ints, host memory; ids < 256), NULL/0 = all.
+ * out_dev: [b, max_det, 6] f64 rows (x1,y1,x2,y2,conf,cls); count_dev: [b] rows valid per image;
+ * xc_count_dev (optional): [b] number of rows with obj > conf_thres (the reference asserts any() :44).
+ * max_det <= 1024. Needs tcb_yolo_nms_workspace(b, n) bytes of context workspace.
+ */
+size_t tcb_yolo_nms_workspace(int b, int n);
+int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, int nc, double conf_thres,
+                 double iou_thres, const int* classes_host, int n_classes, int agnostic, int max_det,
+                 int max_nms, double* out_dev, int* count_dev, int* xc_count_dev, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TCB200_H */

@@ -1,0 +1,16 @@
+"""CPU oracle for the triton_client pre/post hot path — TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+
+Everything under oracle/ is a CPU restatement of the reference's algorithm (niqbal996/triton_client,
+mounted read-only at /root/reference while building), each function citing the reference file:line it
+follows. Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import it, and only as the checker or as the timed CPU baseline. triton_client_b200 never imports it.
+
+Pinning status (see DESIGN.md §"Oracle"):
+  * pre2d, yolo_post, yolo_head(v4), box3d (ResidualCoder / anchors / CenterPoint decode), pillar_vfe:
+    checked against the UNMODIFIED reference functions run in the build container; the generating
+    script is oracle/make_golden.py and its outputs are committed under tests/golden/.
+  * rotated IoU: checked against the reference's own iou3d_cpu.cpp compiled into oracle/_ref/.
+  * voxelize (spconv / det3d points_to_voxel), letterbox + YOLOv5 Detect decode (ultralytics),
+    detectron2 dense-detector inference: the arithmetic lives in un-vendored, un-pinned third-party
+    packages and the reference has no tests -> PARITY UNPINNED; restated from the published algorithms.
+"""

@@ -1,0 +1,85 @@
+"""Generates tests/golden/*.npz by running the UNMODIFIED reference (/root/reference) on small seeded
+inputs. Run in the build container: `python -m oracle.make_golden`. The fixtures are committed; the
+GPU box (where /root/reference does not exist) checks oracle and CUDA outputs against them.
+Test infrastructure only.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from oracle import ref_harness  # noqa: E402
+from oracle.yolo_post import FakeResponse  # noqa: E402
+from triton_client_b200 import synth  # noqa: E402
+
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def save(name, **arrays):
+    path = os.path.join(GOLD, name + ".npz")
+    np.savez_compressed(path, **arrays)
+    print(f"wrote {path} ({os.path.getsize(path)} B)")
+
+
+def golden_pre2d():
+    """Reference 2D preprocess: cv2.resize (communicator/ros_inference.py:140) + Yolov5preprocess /
+    FCOSpreprocess.image_adjust, on small frames (kept small so the fixture stays a few KB)."""
+    import cv2
+    c = ref_harness.clients()
+    ypre = c.Yolov5client().get_preprocess()
+    fpre = c.FCOS_client().get_preprocess()
+    out = {}
+    cases = [(36, 64, 32, 32), (45, 80, 40, 40), (30, 40, 64, 48), (64, 64, 32, 32), (33, 51, 33, 51)]
+    for k, (h, w, oh, ow) in enumerate(cases):
+        img = synth.image_noise(h, w, synth.seed_for(1, k))
+        resized = cv2.resize(img, (ow, oh))
+        out[f"img{k}"] = img
+        out[f"shape{k}"] = np.array([h, w, oh, ow])
+        out[f"yolo{k}"] = ypre.image_adjust(resized)
+        if k == 0:
+            out[f"fcos{k}"] = fpre.image_adjust(resized)
+    save("pre2d", **out)
+
+
+def golden_yolo_post():
+    """Reference Yolov5postprocess.extract_boxes on small synthetic responses (wire bytes included)."""
+    c = ref_harness.clients()
+    post = c.Yolov5client().get_postprocess()
+    out = {}
+    cases = [dict(b=2, n=600, nc=2, conf=0.3, iou=0.45, classes=None, agnostic=False, max_det=300),
+             dict(b=1, n=300, nc=80, conf=0.3, iou=0.45, classes=None, agnostic=False, max_det=300),
+             dict(b=2, n=500, nc=5, conf=0.25, iou=0.6, classes=[0, 3], agnostic=False, max_det=300),
+             dict(b=1, n=700, nc=3, conf=0.3, iou=0.3, classes=None, agnostic=True, max_det=20)]
+    for k, cs in enumerate(cases):
+        pred = synth.yolo_output(cs["b"], cs["n"], cs["nc"], synth.seed_for(2, k), objects=8, rows_per_object=12, tie_frac=0.3)
+        res = post.extract_boxes(FakeResponse([pred]), conf_thres=cs["conf"], iou_thres=cs["iou"], classes=cs["classes"],
+                                 agnostic=cs["agnostic"], max_det=cs["max_det"])
+        assert isinstance(res, list), res
+        out[f"pred{k}"] = pred
+        out[f"cfg{k}"] = np.array([cs["conf"], cs["iou"], float(cs["agnostic"]), cs["max_det"]])
+        out[f"classes{k}"] = np.array(cs["classes"] if cs["classes"] is not None else [], dtype=np.int64)
+        for bi, t in enumerate(res):
+            out[f"out{k}_{bi}"] = t.numpy().astype(np.float64)
+    # an all-background response: the reference returns the AssertionError object
+    bg = np.zeros((1, 64, 7), dtype=np.float32)
+    res = post.extract_boxes(FakeResponse([bg]), conf_thres=0.3)
+    assert isinstance(res, AssertionError)
+    out["empty_msg"] = np.array(str(res))
+    save("yolo_post", **out)
+
+
+def main():
+    assert ref_harness.available(), "reference not mounted"
+    os.makedirs(GOLD, exist_ok=True)
+    which = sys.argv[1:] or [n[len("golden_"):] for n in globals() if n.startswith("golden_")]
+    for w in which:
+        globals()["golden_" + w]()
+
+
+if __name__ == "__main__":
+    torch.set_num_threads(1)
+    main()

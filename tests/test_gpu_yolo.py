@@ -1,0 +1,99 @@
+"""GPU parity: YOLOv5 postprocess (filter + decode + ordering + NMS through the C ABI) vs the
+reference's golden outputs and the oracle. Bit-exact: keep lists, class ids, float64 rows."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import golden
+from oracle import yolo_post
+from triton_client_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _gpu(engine, pred, **kw):
+    out, cnt, xc = engine.yolo_nms(torch.from_numpy(pred).cuda(), **kw)
+    torch.cuda.synchronize()
+    out, cnt = out.cpu().numpy(), cnt.cpu().numpy()
+    return [out[b, :cnt[b]] for b in range(pred.shape[0])], xc.cpu().numpy()
+
+
+def _same(got, want):
+    assert len(got) == len(want)
+    for b, (g, w) in enumerate(zip(got, want)):
+        w = w.numpy().astype(np.float64).reshape(-1, 6) if isinstance(w, torch.Tensor) else np.asarray(w).reshape(-1, 6)
+        assert g.shape == w.shape, (b, g.shape, w.shape)
+        assert np.array_equal(g, w), (b, np.abs(g - w).max())
+
+
+def test_golden_reference_vectors(engine):
+    g = golden("yolo_post")
+    for k in range(4):
+        conf, iou, agn, max_det = g[f"cfg{k}"]
+        classes = g[f"classes{k}"].tolist() or None
+        pred = g[f"pred{k}"]
+        got, _ = _gpu(engine, pred, conf_thres=float(conf), iou_thres=float(iou), classes=classes,
+                      agnostic=bool(agn), max_det=int(max_det))
+        _same(got, [g[f"out{k}_{b}"] for b in range(pred.shape[0])])
+
+
+@pytest.mark.parametrize("b,n,nc,conf", [(1, 25200, 80, 0.3), (4, 25200, 2, 0.3), (1, 16128, 2, 0.3), (3, 1000, 1, 0.6), (2, 5000, 33, 0.25)])
+def test_matches_oracle_bit_exact(engine, b, n, nc, conf):
+    pred = synth.yolo_output(b, n, nc, 500 + n + nc)
+    want = yolo_post.extract_boxes(pred, conf_thres=conf, as_written=False)
+    got, xc = _gpu(engine, pred, conf_thres=conf)
+    _same(got, want)
+    assert np.array_equal(xc, (pred[..., 4].astype(np.float64) > conf).sum(1))
+
+
+def test_ties_agnostic_filter_and_max_det(engine):
+    pred = synth.yolo_output(2, 4000, 6, 77, objects=60, rows_per_object=40, tie_frac=0.6)
+    for kw in [dict(conf_thres=0.3, agnostic=True), dict(conf_thres=0.3, classes=[1, 4]), dict(conf_thres=0.3, max_det=7),
+               dict(conf_thres=0.3, iou_thres=0.0), dict(conf_thres=0.3, iou_thres=1.0), dict(conf_thres=0.0, iou_thres=0.45)]:
+        want = yolo_post.extract_boxes(pred, as_written=False, **kw)
+        got, _ = _gpu(engine, pred, **kw)
+        _same(got, want)
+
+
+def test_many_candidates_sorts_in_global_scratch(engine):
+    """> 4096 candidates per image: the ordering falls back to global scratch; dense overlapping boxes."""
+    rng = np.random.default_rng(8)
+    n = 9000
+    pred = np.zeros((1, n, 7), np.float32)
+    pred[0, :, 0:2] = rng.uniform(100, 400, (n, 2))
+    pred[0, :, 2:4] = rng.uniform(20, 90, (n, 2))
+    pred[0, :, 4] = rng.uniform(0.5, 1, n)
+    pred[0, :, 5:] = rng.uniform(0.6, 1, (n, 2))
+    want = yolo_post.extract_boxes(pred, conf_thres=0.25, as_written=False)
+    got, _ = _gpu(engine, pred, conf_thres=0.25)
+    _same(got, want)
+
+
+def test_empty_and_ragged(engine):
+    pred = synth.yolo_output(3, 300, 2, 5)
+    pred[1, :, 4] = 0.0  # image 1 has no candidate at all
+    got, xc = _gpu(engine, pred, conf_thres=0.3)
+    want = yolo_post.extract_boxes(pred, conf_thres=0.3, as_written=False)
+    _same(got, want)
+    assert got[1].shape == (0, 6) and xc[1] == 0
+    got, xc = _gpu(engine, np.zeros((2, 64, 7), np.float32), conf_thres=0.3)
+    assert all(g.shape == (0, 6) for g in got) and xc.sum() == 0
+
+
+def test_full_batch_c2_properties(engine):
+    """BASELINE config 2 at full size (64x25200x7): every image equals its single-image result, kept
+    boxes are score-sorted, and re-running NMS on the kept set is the identity (idempotence)."""
+    pred = synth.yolo_output(64, 25200, 2, 2002)
+    dev = torch.from_numpy(pred).cuda()
+    out, cnt, _ = engine.yolo_nms(dev, conf_thres=0.3)
+    one, cnt1, _ = engine.yolo_nms(dev[9:10].contiguous(), conf_thres=0.3)
+    torch.cuda.synchronize()
+    assert int(cnt1[0]) == int(cnt[9]) and torch.equal(out[9, :cnt[9]], one[0, :cnt1[0]])
+    want = yolo_post.extract_boxes(pred[9:10], conf_thres=0.3, as_written=False)[0]
+    assert torch.equal(out[9, :cnt[9]].cpu(), want)
+    for b in (0, 31, 63):
+        k = out[b, :cnt[b]].cpu()
+        assert torch.all(k[:-1, 4] >= k[1:, 4])
+        import torchvision
+        keep = torchvision.ops.nms(k[:, :4] + k[:, 5:6] * 4096, k[:, 4], 0.45)
+        assert keep.numel() == k.shape[0]

@@ -1,0 +1,47 @@
+"""Mirror of clients/postprocess/base_postprocess.py: the helpers every postprocess object inherits.
+Wire parsing is a reinterpretation, not a per-element loop; the numeric helpers run on the GPU."""
+from abc import ABC, abstractmethod
+
+import numpy as np
+import torch
+
+from .. import wire
+
+
+class Postprocess(ABC):
+    def __init__(self, engine=None):
+        self._engine = engine
+        self._stager = None
+
+    @property
+    def engine(self):
+        if self._engine is None:
+            self._engine = wire.default_engine()
+        return self._engine
+
+    @property
+    def stager(self):
+        if self._stager is None:
+            self._stager = wire.Stager(self.engine.device)
+        return self._stager
+
+    # base_postprocess.py:15-25 — same values and dtype (object array of Python floats), no struct loop
+    def deserialize_bytes_float(self, encoded_tensor):
+        return np.frombuffer(encoded_tensor, dtype="<f4").astype(np.float64).astype(np.object_)
+
+    # base_postprocess.py:27-37 — 'l' (8 bytes, native) as in clients/; utils/postprocess.py uses 'i'
+    def deserialize_bytes_int(self, encoded_tensor):
+        return np.frombuffer(encoded_tensor, dtype="<i8").astype(np.object_)
+
+    # base_postprocess.py:39-46
+    def xywh2xyxy(self, x):
+        y = x.clone() if isinstance(x, torch.Tensor) else np.copy(x)
+        y[:, 0] = x[:, 0] - x[:, 2] / 2
+        y[:, 1] = x[:, 1] - x[:, 3] / 2
+        y[:, 2] = x[:, 0] + x[:, 2] / 2
+        y[:, 3] = x[:, 1] + x[:, 3] / 2
+        return y
+
+    @abstractmethod
+    def postprocess(self):
+        """ """

@@ -1,0 +1,82 @@
+// Shared host/device helpers for libtcb200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include <string.h>
+#include "../../include/tcb200.h"
+
+#define TCB_ERRLEN 512
+
+struct tcb_ctx {
+    int device;
+    int num_sms;
+    char* ws;          // device workspace (one allocation, made in tcb_create)
+    size_t ws_bytes;
+    size_t ws_used;    // bump pointer, reset at the start of every entry point
+    long long launches;
+    char err[TCB_ERRLEN];
+};
+
+int tcb_fail(tcb_ctx* ctx, int code, const char* fmt, ...);
+void tcb_clear_error(tcb_ctx* ctx);
+
+// Bump allocation out of the context workspace (256 B aligned). Returns nullptr when exhausted.
+static inline void* tcb_ws_alloc(tcb_ctx* ctx, size_t bytes) {
+    size_t off = (ctx->ws_used + 255) & ~(size_t)255;
+    if (off + bytes > ctx->ws_bytes) return nullptr;
+    ctx->ws_used = off + bytes;
+    return ctx->ws + off;
+}
+static inline void tcb_ws_reset(tcb_ctx* ctx) { ctx->ws_used = 0; }
+
+#define TCB_CHECK_CTX(ctx)                                                     \
+    do {                                                                       \
+        if (!(ctx)) return tcb_fail(nullptr, TCB_ERR_ARG, "%s: null context", __func__); \
+        tcb_clear_error(ctx);                                                  \
+        tcb_ws_reset(ctx);                                                     \
+    } while (0)
+
+#define TCB_REQUIRE(ctx, cond, ...)                                            \
+    do {                                                                       \
+        if (!(cond)) return tcb_fail((ctx), TCB_ERR_ARG, __VA_ARGS__);         \
+    } while (0)
+
+#define TCB_CUDA(ctx, call)                                                    \
+    do {                                                                       \
+        cudaError_t e__ = (call);                                              \
+        if (e__ != cudaSuccess)                                                \
+            return tcb_fail((ctx), TCB_ERR_CUDA, "%s: %s -> %s", __func__, #call, cudaGetErrorString(e__)); \
+    } while (0)
+
+// After a kernel launch: count it and surface launch-configuration errors.
+#define TCB_LAUNCHED(ctx)                                                      \
+    do {                                                                       \
+        (ctx)->launches++;                                                     \
+        cudaError_t e__ = cudaGetLastError();                                  \
+        if (e__ != cudaSuccess)                                                \
+            return tcb_fail((ctx), TCB_ERR_CUDA, "%s: launch failed: %s", __func__, cudaGetErrorString(e__)); \
+    } while (0)
+
+#define TCB_WS(ctx, ptr, type, count)                                          \
+    type* ptr = (type*)tcb_ws_alloc((ctx), sizeof(type) * (size_t)(count));    \
+    if (!ptr) return tcb_fail((ctx), TCB_ERR_WORKSPACE, "%s: workspace too small (need > %zu B, have %zu B)", \
+                              __func__, (ctx)->ws_used + sizeof(type) * (size_t)(count), (ctx)->ws_bytes)
+
+static inline int tcb_div_up(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+#ifdef __CUDACC__
+// 128-bit streaming load/store (read-once inputs, write-once outputs: keep them out of L1).
+__device__ __forceinline__ uint4 ld_stream_u4(const void* p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void st_stream_f4(float* p, float4 v) {
+    asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ unsigned lane_id() { return threadIdx.x & 31; }
+#endif

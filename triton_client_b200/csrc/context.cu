@@ -1,0 +1,61 @@
+// Context, error reporting and workspace ownership for libtcb200 (SURVEY.md §8b "error convention").
+#include "common.cuh"
+#include <new>
+
+static thread_local char g_err[TCB_ERRLEN] = "";
+
+int tcb_fail(tcb_ctx* ctx, int code, const char* fmt, ...) {
+    char* dst = ctx ? ctx->err : g_err;
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(dst, TCB_ERRLEN, fmt, ap);
+    va_end(ap);
+    if (ctx) { strncpy(g_err, dst, TCB_ERRLEN - 1); g_err[TCB_ERRLEN - 1] = 0; }
+    return code;
+}
+
+void tcb_clear_error(tcb_ctx* ctx) { if (ctx) ctx->err[0] = 0; }
+
+extern "C" {
+
+const char* tcb_version(void) { return "tcb200 0.1 (sm_100a)"; }
+
+int tcb_create(int device, size_t workspace_bytes, tcb_ctx** out) {
+    if (!out) return tcb_fail(nullptr, TCB_ERR_ARG, "tcb_create: out is null");
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess) return tcb_fail(nullptr, TCB_ERR_CUDA, "tcb_create: cudaGetDeviceCount -> %s", cudaGetErrorString(e));
+    if (device < 0 || device >= ndev) return tcb_fail(nullptr, TCB_ERR_ARG, "tcb_create: device %d out of range [0,%d)", device, ndev);
+    e = cudaSetDevice(device);
+    if (e != cudaSuccess) return tcb_fail(nullptr, TCB_ERR_CUDA, "tcb_create: cudaSetDevice -> %s", cudaGetErrorString(e));
+    tcb_ctx* c = new (std::nothrow) tcb_ctx();
+    if (!c) return tcb_fail(nullptr, TCB_ERR_ALLOC, "tcb_create: host allocation failed");
+    memset(c, 0, sizeof(*c));
+    c->device = device;
+    cudaDeviceGetAttribute(&c->num_sms, cudaDevAttrMultiProcessorCount, device);
+    if (c->num_sms <= 0) c->num_sms = 148;
+    if (workspace_bytes) {
+        e = cudaMalloc((void**)&c->ws, workspace_bytes);
+        if (e != cudaSuccess) {
+            delete c;
+            return tcb_fail(nullptr, TCB_ERR_ALLOC, "tcb_create: cudaMalloc(%zu) -> %s", workspace_bytes, cudaGetErrorString(e));
+        }
+    }
+    c->ws_bytes = workspace_bytes;
+    *out = c;
+    return TCB_OK;
+}
+
+int tcb_destroy(tcb_ctx* ctx) {
+    if (!ctx) return TCB_OK;
+    if (ctx->ws) cudaFree(ctx->ws);
+    delete ctx;
+    return TCB_OK;
+}
+
+const char* tcb_last_error(const tcb_ctx* ctx) { return ctx ? ctx->err : g_err; }
+size_t tcb_workspace_bytes(const tcb_ctx* ctx) { return ctx ? ctx->ws_bytes : 0; }
+long long tcb_launch_count(const tcb_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+}  // extern "C"

@@ -1,0 +1,347 @@
+// Fused 2D preprocess: u8 HWC -> OpenCV-exact bilinear resample -> channel order -> x/div - sub -> f32 NCHW.
+// One pass over each frame. HBM-bound: 3hw bytes in, 12 out_h out_w bytes out.
+//
+// Tiling: one CTA of 256 threads owns a 128-column x TH-row output tile. The source footprint of the
+// tile (a few KB..tens of KB of u8) is staged into shared memory with 16-byte global loads, then each
+// warp walks RPW consecutive output rows, each lane producing 4 adjacent pixels x 3 channels and
+// issuing three 16-byte streaming stores (one per colour plane, 512 B contiguous per warp).
+// The horizontal pass of a source row is kept in registers and reused by the next output row when
+// both need it (vertical scale near 1).
+#include "common.cuh"
+#include <math.h>
+
+namespace {
+
+constexpr int TW = 128;       // output tile width (32 lanes x 4 px)
+constexpr int NTHREADS = 256; // 8 warps
+
+struct PreParams {
+    const uint8_t* src;
+    const uint8_t* batch_end;  // one past the last valid source byte of the whole batch
+    long long img_stride, row_stride;
+    int h, w;
+    float* dst;
+    int out_h, out_w;
+    int left, top, new_w, new_h;  // content rectangle inside the output
+    int swap;
+    int exact_recip;  // 1: v/div == fma-corrected v*rdiv for every v in 0..255 (checked on the host)
+    float div, rdiv;
+    float sub[3];
+    float padv[3];  // normalised pad value per output channel
+    double scale_x, scale_y;
+    int th;     // output rows per tile (8, 16 or 32)
+    int pitch;  // shared-memory row pitch in bytes (multiple of 16)
+    int vec_store;
+};
+
+// u8 -> normalised f32, identical to numpy's `x.astype(float32) / div - sub` (true IEEE division).
+__device__ __forceinline__ float norm_px(int v, const PreParams& p, int c) {
+    float f = __int_as_float(0x4B000000 | v) - 8388608.0f;  // exact int->float for 0..255 without I2F
+    float q;
+    if (p.exact_recip) {
+        float q0 = f * p.rdiv;
+        float e = __fmaf_rn(-q0, p.div, f);
+        q = __fmaf_rn(e, p.rdiv, q0);
+    } else {
+        q = f / p.div;
+    }
+    return q - p.sub[c];
+}
+
+// OpenCV resizeLinear column taps for destination column dx (modules/imgproc resize.cpp semantics,
+// restated from its documented behaviour: half-pixel centres, clamp to edge with zero weight, 11-bit taps).
+__device__ __forceinline__ void x_tap(int dx, double scale, int w, int& sx, int& a0, int& a1) {
+    float f = (float)(((double)dx + 0.5) * scale - 0.5);
+    int s = (int)floorf(f);
+    f -= (float)s;
+    if (s < 0) { f = 0.f; s = 0; }
+    if (s >= w - 1) { f = 0.f; s = w - 1; }
+    a0 = __float2int_rn((1.f - f) * 2048.f);
+    a1 = __float2int_rn(f * 2048.f);
+    sx = s;
+}
+// Row taps: weights are NOT clamped, only the two row indices are (so border rows blend a row with itself).
+__device__ __forceinline__ void y_tap(int dy, double scale, int h, int& r0, int& r1, int& b0, int& b1) {
+    float f = (float)(((double)dy + 0.5) * scale - 0.5);
+    int s = (int)floorf(f);
+    f -= (float)s;
+    b0 = __float2int_rn((1.f - f) * 2048.f);
+    b1 = __float2int_rn(f * 2048.f);
+    r0 = min(max(s, 0), h - 1);
+    r1 = min(max(s + 1, 0), h - 1);
+}
+
+template <bool AREA, bool STAGED>
+__global__ void __launch_bounds__(NTHREADS) preprocess_kernel(const PreParams p) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int z = blockIdx.z;
+    const int tx0 = blockIdx.x * TW, ty0 = blockIdx.y * p.th;
+    const int tx1 = min(tx0 + TW, p.out_w) - 1, ty1 = min(ty0 + p.th, p.out_h) - 1;
+    const uint8_t* img = p.src + (long long)z * p.img_stride;
+
+    // ---- content part of this tile, in content coordinates --------------------------------------
+    const int cx0 = max(tx0 - p.left, 0), cx1 = min(tx1 - p.left, p.new_w - 1);
+    const int cy0 = max(ty0 - p.top, 0), cy1 = min(ty1 - p.top, p.new_h - 1);
+    const bool has_content = (cx0 <= cx1) && (cy0 <= cy1);
+
+    int xmin = 0, xmax = 0, rmin = 0, rmax = 0;
+    if (has_content) {
+        if (AREA) {
+            xmin = 2 * cx0; xmax = 2 * cx1 + 1; rmin = 2 * cy0; rmax = 2 * cy1 + 1;
+        } else {
+            int s, a, b, r0, r1;
+            x_tap(cx0, p.scale_x, p.w, s, a, b); xmin = s;
+            x_tap(cx1, p.scale_x, p.w, s, a, b); xmax = min(s + 1, p.w - 1);
+            y_tap(cy0, p.scale_y, p.h, r0, r1, a, b); rmin = r0;
+            y_tap(cy1, p.scale_y, p.h, r0, r1, a, b); rmax = r1;
+        }
+    }
+
+    // ---- stage the source footprint: rows rmin..rmax, bytes xmin*3 .. xmax*3+2 -------------------
+    if (STAGED && has_content) {
+        const int nrows = rmax - rmin + 1;
+        const int seg = (xmax - xmin + 1) * 3;
+        const int cpr = p.pitch >> 4;  // 16-byte chunks per staged row
+        for (int q = tid; q < nrows * cpr; q += NTHREADS) {
+            const int r = q / cpr, k = q - r * cpr;
+            const uint8_t* a = img + (long long)(rmin + r) * p.row_stride + (long long)xmin * 3;
+            const uint8_t* g = (const uint8_t*)((uintptr_t)a & ~(uintptr_t)15) + 16 * k;
+            if (g >= a + seg) continue;
+            uint4 v;
+            if (g >= p.src && g + 16 <= p.batch_end) {
+                v = ld_stream_u4(g);
+            } else {  // first/last few bytes of the caller's buffer: never read outside it
+                uint8_t t[16];
+#pragma unroll
+                for (int i = 0; i < 16; i++) t[i] = (g + i >= p.src && g + i < p.batch_end) ? g[i] : 0;
+                v = *reinterpret_cast<uint4*>(t);
+            }
+            *reinterpret_cast<uint4*>(smem + (size_t)r * p.pitch + 16 * k) = v;
+        }
+    }
+    __syncthreads();
+
+    // ---- per-lane column taps (fixed for the whole tile) -----------------------------------------
+    const int ox0 = tx0 + lane * 4;
+    int off0[4], d1[4], a0[4], a1[4];
+    bool inx[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const int dx = ox0 + i - p.left;
+        inx[i] = has_content && dx >= 0 && dx < p.new_w;
+        off0[i] = 0; d1[i] = 0; a0[i] = 0; a1[i] = 0;
+        if (inx[i]) {
+            if (AREA) {
+                off0[i] = (2 * dx - xmin) * 3;
+            } else {
+                int s;
+                x_tap(dx, p.scale_x, p.w, s, a0[i], a1[i]);
+                off0[i] = (s - xmin) * 3;
+                d1[i] = (min(s + 1, p.w - 1) - s) * 3;
+            }
+        }
+    }
+    if (ox0 >= p.out_w) return;
+
+    const int rpw = p.th >> 3;  // consecutive rows per warp
+    int hprev[12];
+    int rprev = -1;
+#pragma unroll
+    for (int i = 0; i < 12; i++) hprev[i] = 0;
+
+    for (int rr = 0; rr < rpw; rr++) {
+        const int oy = ty0 + warp * rpw + rr;
+        if (oy >= p.out_h) break;
+        const int dy = oy - p.top;
+        const bool iny = has_content && dy >= 0 && dy < p.new_h;
+        float o[3][4];
+        if (!iny) {
+#pragma unroll
+            for (int c = 0; c < 3; c++)
+#pragma unroll
+                for (int i = 0; i < 4; i++) o[c][i] = p.padv[c];
+        } else {
+            int r0, r1, b0 = 0, b1 = 0;
+            if (AREA) { r0 = 2 * dy; r1 = 2 * dy + 1; }
+            else y_tap(dy, p.scale_y, p.h, r0, r1, b0, b1);
+            const uint8_t *s0, *s1;
+            if (STAGED) {
+                const uint8_t* g0 = img + (long long)r0 * p.row_stride + (long long)xmin * 3;
+                const uint8_t* g1 = img + (long long)r1 * p.row_stride + (long long)xmin * 3;
+                s0 = smem + (size_t)(r0 - rmin) * p.pitch + ((uintptr_t)g0 & 15);
+                s1 = smem + (size_t)(r1 - rmin) * p.pitch + ((uintptr_t)g1 & 15);
+            } else {
+                s0 = img + (long long)r0 * p.row_stride + (long long)xmin * 3;
+                s1 = img + (long long)r1 * p.row_stride + (long long)xmin * 3;
+            }
+            if (AREA) {
+#pragma unroll
+                for (int i = 0; i < 4; i++)
+#pragma unroll
+                    for (int c = 0; c < 3; c++) {
+                        const int cc = p.swap ? 2 - c : c;
+                        if (inx[i]) {
+                            const int k = off0[i] + c;
+                            const int v = ((int)s0[k] + (int)s0[k + 3] + (int)s1[k] + (int)s1[k + 3] + 2) >> 2;
+                            o[cc][i] = norm_px(v, p, cc);
+                        } else {
+                            o[cc][i] = p.padv[cc];
+                        }
+                    }
+            } else {
+                int h0[12], h1[12];
+                const bool reuse = (r0 == rprev);
+#pragma unroll
+                for (int i = 0; i < 4; i++)
+#pragma unroll
+                    for (int c = 0; c < 3; c++) {
+                        const int k = off0[i] + c;
+                        h0[i * 3 + c] = reuse ? hprev[i * 3 + c] : (int)s0[k] * a0[i] + (int)s0[k + d1[i]] * a1[i];
+                    }
+                if (r1 == r0) {
+#pragma unroll
+                    for (int i = 0; i < 12; i++) h1[i] = h0[i];
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 4; i++)
+#pragma unroll
+                        for (int c = 0; c < 3; c++) {
+                            const int k = off0[i] + c;
+                            h1[i * 3 + c] = (int)s1[k] * a0[i] + (int)s1[k + d1[i]] * a1[i];
+                        }
+                }
+#pragma unroll
+                for (int i = 0; i < 4; i++)
+#pragma unroll
+                    for (int c = 0; c < 3; c++) {
+                        const int cc = p.swap ? 2 - c : c;
+                        if (inx[i]) {
+                            const int v = (((b0 * (h0[i * 3 + c] >> 4)) >> 16) + ((b1 * (h1[i * 3 + c] >> 4)) >> 16) + 2) >> 2;
+                            o[cc][i] = norm_px(v, p, cc);
+                        } else {
+                            o[cc][i] = p.padv[cc];
+                        }
+                    }
+#pragma unroll
+                for (int i = 0; i < 12; i++) hprev[i] = h1[i];
+                rprev = r1;
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            float* d = p.dst + (((long long)z * 3 + c) * p.out_h + oy) * (long long)p.out_w + ox0;
+            if (p.vec_store) {
+                st_stream_f4(d, make_float4(o[c][0], o[c][1], o[c][2], o[c][3]));
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; i++)
+                    if (ox0 + i < p.out_w) d[i] = o[c][i];
+            }
+        }
+    }
+}
+
+int iround_half_even(double v) { return (int)nearbyint(v); }  // python round() == ties-to-even
+
+}  // namespace
+
+extern "C" int tcb_preprocess_image(tcb_ctx* ctx, const uint8_t* src_dev, int n, int h, int w,
+                                    long long src_row_stride, long long src_img_stride, int channel_swap,
+                                    int mode, int out_h, int out_w, float div, const float sub[3],
+                                    int pad_value, float* dst_dev, float* inv_affine_host, void* stream) {
+    TCB_CHECK_CTX(ctx);
+    TCB_REQUIRE(ctx, src_dev && dst_dev, "tcb_preprocess_image: null buffer");
+    TCB_REQUIRE(ctx, n >= 0 && h > 0 && w > 0 && out_h > 0 && out_w > 0, "tcb_preprocess_image: bad shape n=%d h=%d w=%d out=%dx%d", n, h, w, out_h, out_w);
+    TCB_REQUIRE(ctx, n <= 65535, "tcb_preprocess_image: at most 65535 frames per call (got %d)", n);
+    TCB_REQUIRE(ctx, src_row_stride >= (long long)w * 3, "tcb_preprocess_image: row stride %lld < w*3", src_row_stride);
+    TCB_REQUIRE(ctx, src_img_stride >= src_row_stride * (h - 1) + (long long)w * 3 || n <= 1, "tcb_preprocess_image: frame stride %lld too small", src_img_stride);
+    TCB_REQUIRE(ctx, mode == TCB_RESIZE_STRETCH || mode == TCB_RESIZE_LETTERBOX || mode == TCB_RESIZE_PAD, "tcb_preprocess_image: unknown mode %d", mode);
+    TCB_REQUIRE(ctx, div != 0.f && div == div, "tcb_preprocess_image: div must be a non-zero number");
+    TCB_REQUIRE(ctx, pad_value >= 0 && pad_value <= 255, "tcb_preprocess_image: pad_value %d not a byte", pad_value);
+
+    PreParams p;
+    memset(&p, 0, sizeof(p));
+    p.src = src_dev;
+    p.batch_end = src_dev + (long long)(n > 0 ? n - 1 : 0) * src_img_stride + (long long)(h - 1) * src_row_stride + (long long)w * 3;
+    p.img_stride = src_img_stride; p.row_stride = src_row_stride;
+    p.h = h; p.w = w; p.dst = dst_dev; p.out_h = out_h; p.out_w = out_w;
+    p.swap = channel_swap ? 1 : 0;
+
+    double gain_x, gain_y;
+    if (mode == TCB_RESIZE_STRETCH) {
+        p.left = 0; p.top = 0; p.new_w = out_w; p.new_h = out_h;
+        gain_x = (double)out_w / w; gain_y = (double)out_h / h;
+    } else if (mode == TCB_RESIZE_LETTERBOX) {
+        // ultralytics letterbox: r=min(S/h,S/w); new=round(w r),round(h r); pads split with round(+-0.1)
+        double r = fmin((double)out_h / h, (double)out_w / w);
+        p.new_w = iround_half_even(w * r); p.new_h = iround_half_even(h * r);
+        if (p.new_w < 1) p.new_w = 1;
+        if (p.new_h < 1) p.new_h = 1;
+        if (p.new_w > out_w) p.new_w = out_w;
+        if (p.new_h > out_h) p.new_h = out_h;
+        double dw = (out_w - p.new_w) / 2.0, dh = (out_h - p.new_h) / 2.0;
+        p.left = iround_half_even(dw - 0.1); p.top = iround_half_even(dh - 0.1);
+        gain_x = r; gain_y = r;
+    } else {
+        TCB_REQUIRE(ctx, h <= out_h && w <= out_w, "tcb_preprocess_image: PAD mode needs src (%dx%d) <= out (%dx%d)", h, w, out_h, out_w);
+        p.left = 0; p.top = 0; p.new_w = w; p.new_h = h;
+        gain_x = 1.0; gain_y = 1.0;
+    }
+    if (inv_affine_host) {
+        inv_affine_host[0] = (float)gain_x; inv_affine_host[1] = (float)gain_y;
+        inv_affine_host[2] = (float)p.left; inv_affine_host[3] = (float)p.top;
+    }
+    if (n == 0) return TCB_OK;
+
+    // cv2: inv_scale = dsize/ssize (double); scale = 1/inv_scale
+    p.scale_x = 1.0 / ((double)p.new_w / (double)w);
+    p.scale_y = 1.0 / ((double)p.new_h / (double)h);
+    const bool area = (w == 2 * p.new_w) && (h == 2 * p.new_h);
+
+    p.div = div; p.rdiv = 1.0f / div;
+    p.exact_recip = 1;
+    for (int v = 0; v < 256; v++) {
+        float f = (float)v, q0 = f * p.rdiv;
+        float q = fmaf(fmaf(-q0, div, f), p.rdiv, q0);
+        if (q != f / div) { p.exact_recip = 0; break; }
+    }
+    for (int c = 0; c < 3; c++) {
+        p.sub[c] = sub ? sub[c] : 0.f;
+        p.padv[c] = (float)pad_value / div - p.sub[c];
+    }
+    p.vec_store = (out_w % 4 == 0) && (((uintptr_t)dst_dev & 15) == 0);
+
+    // choose the tile height so that the staged footprint fits comfortably (several CTAs per SM)
+    const size_t SMEM_BUDGET = 64 * 1024;
+    bool staged = false;
+    size_t smem = 0;
+    const double sx = area ? 2.0 : p.scale_x, sy = area ? 2.0 : p.scale_y;
+    for (int th = 32; th >= 8; th >>= 1) {
+        long long cols = (long long)floor((TW - 1) * sx) + 4;
+        if (cols > w) cols = w;
+        long long rows = (long long)floor((th - 1) * sy) + 4;
+        if (rows > h) rows = h;
+        long long pitch = ((cols * 3 + 15) / 16) * 16 + 16;
+        p.th = th; p.pitch = (int)pitch;
+        if ((size_t)(rows * pitch) <= SMEM_BUDGET) { staged = true; smem = (size_t)(rows * pitch); break; }
+    }
+    if (!staged) { p.th = 8; p.pitch = 16; smem = 0; }
+
+    dim3 grid(tcb_div_up(out_w, TW), tcb_div_up(out_h, p.th), n);
+    TCB_REQUIRE(ctx, grid.y <= 65535, "tcb_preprocess_image: output too tall (%d rows)", out_h);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (staged && smem > 48 * 1024) {  // opt in to > 48 KB dynamic shared memory
+        TCB_CUDA(ctx, cudaFuncSetAttribute(area ? (const void*)preprocess_kernel<true, true> : (const void*)preprocess_kernel<false, true>,
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BUDGET));
+    }
+    if (area) {
+        if (staged) preprocess_kernel<true, true><<<grid, NTHREADS, smem, st>>>(p);
+        else preprocess_kernel<true, false><<<grid, NTHREADS, 0, st>>>(p);
+    } else {
+        if (staged) preprocess_kernel<false, true><<<grid, NTHREADS, smem, st>>>(p);
+        else preprocess_kernel<false, false><<<grid, NTHREADS, 0, st>>>(p);
+    }
+    TCB_LAUNCHED(ctx);
+    return TCB_OK;
+}

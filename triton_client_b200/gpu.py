@@ -1,0 +1,88 @@
+"""Device-level Python wrappers: torch CUDA tensors in, torch CUDA tensors out, every op one call
+through the C ABI of libtcb200.so. No op here has a CPU or eager-PyTorch fallback.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import c_float, c_int, c_void_p
+
+STRETCH, LETTERBOX, PAD = 0, 1, 2
+_MODES = {"stretch": STRETCH, "letterbox": LETTERBOX, "pad": PAD}
+
+
+def _ptr(t):
+    return c_void_p(t.data_ptr())
+
+
+def _need_cuda(*tensors):
+    for t in tensors:
+        if not (isinstance(t, torch.Tensor) and t.is_cuda):
+            raise TypeError("triton_client_b200.gpu ops take CUDA tensors only (there is no CPU path)")
+
+
+class Engine:
+    """A tcb_ctx plus the torch plumbing around it. One per pre/post object (one frame in flight)."""
+
+    def __init__(self, device=0, workspace_bytes=256 << 20):
+        if not torch.cuda.is_available():
+            raise RuntimeError("triton_client_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+        self.device = torch.device("cuda", int(device))
+        torch.cuda.set_device(self.device)
+        torch.zeros(1, device=self.device)  # make sure the primary context exists before the library uses it
+        self.ctx = _lib.Context(int(device), int(workspace_bytes))
+        self.lib = _lib.lib()
+
+    @property
+    def launches(self):
+        return self.ctx.launches
+
+    # ---- 2D preprocess ---------------------------------------------------------------------------
+    def preprocess_images(self, src, out_h, out_w, mode="stretch", swap=False, div=255.0, sub=None,
+                          pad_value=114, out=None):
+        """src: uint8 CUDA tensor [n,h,w,3] (or [h,w,3]), any row/frame stride with contiguous pixels.
+        Returns (f32 [n,3,out_h,out_w], inv_affine[4] = gain_x, gain_y, pad_left, pad_top)."""
+        _need_cuda(src)
+        if src.dtype != torch.uint8:
+            raise TypeError("preprocess_images: src must be uint8")
+        if src.dim() == 3:
+            src = src.unsqueeze(0)
+        n, h, w, c = src.shape
+        if c != 3 or src.stride(3) != 1 or src.stride(2) != 3:
+            raise ValueError("preprocess_images: need packed 3-channel pixels (HWC, 3 bytes per pixel)")
+        if out is None:
+            out = torch.empty((n, 3, out_h, out_w), dtype=torch.float32, device=src.device)
+        elif tuple(out.shape) != (n, 3, out_h, out_w) or out.dtype != torch.float32 or not out.is_contiguous():
+            raise ValueError("preprocess_images: bad `out` tensor")
+        sub_arr = (c_float * 3)(*(sub if sub is not None else (0.0, 0.0, 0.0)))
+        aff = (c_float * 4)()
+        self.ctx.call("tcb_preprocess_image", _ptr(src), n, h, w, src.stride(1), src.stride(0) if n > 1 else h * src.stride(1),
+                      1 if swap else 0, _MODES[mode] if isinstance(mode, str) else int(mode), out_h, out_w,
+                      float(div), sub_arr, int(pad_value), _ptr(out), aff, _lib.stream_ptr())
+        return out, np.array(list(aff), dtype=np.float32)
+
+    # ---- YOLOv5 postprocess ----------------------------------------------------------------------
+    def yolo_nms_workspace(self, b, n):
+        return int(self.lib.tcb_yolo_nms_workspace(int(b), int(n)))
+
+    def yolo_nms(self, pred, conf_thres=0.6, iou_thres=0.45, classes=None, agnostic=False, max_det=300,
+                 max_nms=30000, out=None, counts=None):
+        """pred: f32 CUDA tensor [b,n,5+nc]. Returns (out f64 [b,max_det,6], counts i32 [b], xc i32 [b])."""
+        _need_cuda(pred)
+        if pred.dtype != torch.float32 or pred.dim() != 3 or not pred.is_contiguous():
+            raise TypeError("yolo_nms: pred must be a contiguous float32 [b,n,5+nc] tensor")
+        b, n, c = pred.shape
+        if out is None:
+            out = torch.zeros((b, max_det, 6), dtype=torch.float64, device=pred.device)
+        if counts is None:
+            counts = torch.zeros((2, b), dtype=torch.int32, device=pred.device)
+        cls_arr, ncls = None, 0
+        if classes is not None:
+            ncls = len(classes)
+            cls_arr = (c_int * max(ncls, 1))(*[int(v) for v in classes])
+        self.ctx.call("tcb_yolo_nms", _ptr(pred), b, n, c - 5, float(conf_thres), float(iou_thres), cls_arr, ncls,
+                      1 if agnostic else 0, int(max_det), int(max_nms), _ptr(out), _ptr(counts[0]), _ptr(counts[1]),
+                      _lib.stream_ptr())
+        return out, counts[0], counts[1]

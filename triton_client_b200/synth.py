@@ -1,0 +1,60 @@
+"""Seeded synthetic inputs for every BASELINE.json config.
+
+The Triton model call is replaced by synthetic model outputs of the exact named shapes; camera frames
+and LiDAR sweeps are synthetic too (no datasets in the image). All generators are
+numpy.random.default_rng(seed) with seed = 1000*config + frame_idx.
+"""
+import numpy as np
+
+
+def seed_for(config, frame):
+    return 1000 * int(config) + int(frame)
+
+
+# ---- C1/C2 camera frames -------------------------------------------------------------------------
+def image_noise(h, w, seed):
+    return np.random.default_rng(seed).integers(0, 256, (h, w, 3), dtype=np.uint8)
+
+
+def image_smooth(h, w, seed):
+    """Sum of 8 random 2-D sinusoids per channel + sigma=8 noise, clipped to u8."""
+    rng = np.random.default_rng(seed)
+    yy, xx = np.mgrid[0:h, 0:w].astype(np.float32)
+    out = np.empty((h, w, 3), dtype=np.float32)
+    for c in range(3):
+        acc = np.full((h, w), 128.0, dtype=np.float32)
+        for _ in range(8):
+            fx, fy = rng.uniform(-0.05, 0.05, 2)
+            ph, amp = rng.uniform(0, 2 * np.pi), rng.uniform(5, 25)
+            acc += amp * np.sin(fx * xx + fy * yy + ph)
+        out[:, :, c] = acc
+    out += rng.normal(0, 8, out.shape).astype(np.float32)
+    return np.clip(np.rint(out), 0, 255).astype(np.uint8)
+
+
+# ---- C1/C2 decoded YOLOv5 head output [B, N, 5+nc] ------------------------------------------------
+def yolo_output(batch, n, nc, seed, img=640, objects=40, rows_per_object=30, tie_frac=0.05):
+    """40 'objects' per frame each spawning 30 jittered rows with high objectness; background rows have
+    obj in U(0,0.05); 5 % of all scores are quantised to 1/1024 to force score ties."""
+    rng = np.random.default_rng(seed)
+    out = np.empty((batch, n, 5 + nc), dtype=np.float32)
+    out[:, :, 0:2] = rng.uniform(0, img, (batch, n, 2))
+    out[:, :, 2:4] = np.exp(rng.normal(np.log(60.0), 0.7, (batch, n, 2)))
+    out[:, :, 4] = rng.uniform(0, 0.05, (batch, n))
+    out[:, :, 5:] = rng.uniform(0, 0.05, (batch, n, nc))
+    k = objects * rows_per_object
+    for b in range(batch):
+        cxy = rng.uniform(0, img, (objects, 2))
+        wh = np.exp(rng.normal(np.log(60.0), 0.7, (objects, 2)))
+        cls = rng.integers(0, nc, objects)
+        rows = rng.choice(n, size=min(k, n), replace=False)
+        obj_id = np.arange(len(rows)) % objects
+        out[b, rows, 0:2] = cxy[obj_id] + rng.normal(0, 4.0, (len(rows), 2))
+        out[b, rows, 2:4] = wh[obj_id] * np.exp(rng.normal(0, 0.05, (len(rows), 2)))
+        out[b, rows, 4] = rng.uniform(0.3, 1.0, len(rows))
+        out[b, rows, 5 + cls[obj_id]] = rng.uniform(0.5, 1.0, len(rows))
+    q = rng.random((batch, n)) < tie_frac
+    out[:, :, 4] = np.where(q, np.round(out[:, :, 4] * 1024) / 1024, out[:, :, 4])
+    qc = rng.random((batch, n, nc)) < tie_frac
+    out[:, :, 5:] = np.where(qc, np.round(out[:, :, 5:] * 1024) / 1024, out[:, :, 5:])
+    return out.astype(np.float32)
