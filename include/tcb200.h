@@ -105,6 +105,27 @@ int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, int nc, doub
                  double iou_thres, const int* classes_host, int n_classes, int agnostic, int max_det,
                  int max_nms, double* out_dev, int* count_dev, int* xc_count_dev, void* stream);
 
+/*
+ * tcb_yolo_nms without a context and without any allocation. No counterpart in the reference: it is
+ * here for callers that are not allowed to allocate GPU memory — a plugin inside a host process that
+ * has already committed all of HBM to its own pools, or a per-frame callback that cannot afford the
+ * device-wide synchronisation and unbounded latency of cudaMalloc/cudaFree (tcb_create performs one).
+ * Same arguments, results and error codes as tcb_yolo_nms; errors are read with tcb_last_error(NULL).
+ * Scratch is one fixed device array of tcb_yolo_nms_static_scratch_bytes() (about 8.4 MB) that every
+ * GPU loading the library holds until process exit, so:
+ *   - limits: b <= 64, b*n <= 131072, and b*pow2ceil(n) <= 262144 when n > 4096; beyond that the call
+ *     returns TCB_ERR_LIMIT and nothing is launched;
+ *   - all calls share the array: calls that overlap on the GPU race (keep them on one stream); the
+ *     array keeps the previous call's contents and the call clears the counters it needs zeroed;
+ *   - the first call on a device does a one-time set-up (device address of the array, kernel
+ *     attribute); make it with that device current and before any stream capture begins.
+ * The device that owns pred_dev/out_dev must be the current device.
+ */
+size_t tcb_yolo_nms_static_scratch_bytes(void);
+int tcb_yolo_nms_static(const float* pred_dev, int b, int n, int nc, double conf_thres, double iou_thres,
+                        const int* classes_host, int n_classes, int agnostic, int max_det, int max_nms,
+                        double* out_dev, int* count_dev, int* xc_count_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -329,3 +329,136 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
         TCB_CUDA(ctx, cudaMemcpyAsync(xc_count_dev, xc_count, sizeof(int) * (size_t)b, cudaMemcpyDeviceToDevice, st));
     return TCB_OK;
 }
+
+// =================================================================================================
+// tcb_yolo_nms_static — the same two kernels, for callers that must not allocate GPU memory.
+//
+// Who that is: a plugin living inside somebody else's process (a Triton backend, a ROS nodelet next to
+// the inference server) whose host has already handed all of HBM to its own pools, so a cudaMalloc of
+// ours would fail or eat into a budget we do not own; and latency-bound frame callbacks, for which
+// cudaMalloc/cudaFree are off limits because they synchronise the whole device and take unbounded time.
+// tcb_create makes exactly such an allocation (the context workspace), so this entry point takes no
+// context at all: its scratch is the fixed array below, which every GPU that loads libtcb200.so keeps
+// resident until the process exits (TCB_STATIC_SCRATCH_BYTES, about 8.4 MB).
+//
+// Consequences of sharing one array, which the caller has to respect:
+//   * sizes are capped: b <= 64, b*n <= 131072 rows, b*pow2ceil(n) <= 262144 sort slots when n > 4096;
+//     anything larger is refused with TCB_ERR_LIMIT (use tcb_yolo_nms with a context instead);
+//   * the array still holds the previous call's candidates; the per-image counters are the only part
+//     that has to start at zero and they are cleared on the caller's stream at the start of every call;
+//   * two calls that overlap on the GPU (different streams, different threads) race on it — issue them
+//     on one stream or serialise them yourself;
+//   * the first call on each device looks up the array's device address and opts the NMS kernel in to
+//     its shared-memory size; make that first call with the device current and before starting any
+//     stream capture.
+// =================================================================================================
+#include <mutex>
+
+namespace {
+
+constexpr int STATIC_MAX_B = 64;
+constexpr long long STATIC_MAX_ROWS = 131072;        // b * n
+constexpr long long STATIC_MAX_SORT = 262144;        // b * pow2ceil(n), only when pow2ceil(n) > SORT_SMEM_CAP
+constexpr size_t ST_OFF_COUNTS = 0;                                             // 2*b ints
+constexpr size_t ST_OFF_SCORE = 1024;                                           // rows doubles
+constexpr size_t ST_OFF_BOX = ST_OFF_SCORE + STATIC_MAX_ROWS * sizeof(double);  // rows float4
+constexpr size_t ST_OFF_META = ST_OFF_BOX + STATIC_MAX_ROWS * sizeof(float4);   // rows int2
+constexpr size_t ST_OFF_SORT = ST_OFF_META + STATIC_MAX_ROWS * sizeof(int2);    // sort slots
+constexpr size_t TCB_STATIC_SCRATCH_BYTES = ST_OFF_SORT + STATIC_MAX_SORT * sizeof(SortEnt);
+
+// In host code this name is only a handle for cudaGetSymbolAddress, never a pointer to pass to a kernel.
+static __device__ __align__(256) unsigned char g_yolo_static_scratch[TCB_STATIC_SCRATCH_BYTES];
+
+constexpr int STATIC_MAX_DEVICES = 64;
+std::mutex g_static_mu;
+unsigned char* g_static_ptr[STATIC_MAX_DEVICES] = {nullptr};
+
+// One-time set-up for the current device: resolve the device address of the scratch array.
+int static_scratch_for_current_device(unsigned char** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return tcb_fail(nullptr, TCB_ERR_CUDA, "tcb_yolo_nms_static: cudaGetDevice -> %s", cudaGetErrorString(e));
+    if (dev < 0 || dev >= STATIC_MAX_DEVICES) return tcb_fail(nullptr, TCB_ERR_LIMIT, "tcb_yolo_nms_static: device index %d >= %d", dev, STATIC_MAX_DEVICES);
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (!g_static_ptr[dev]) {
+        unsigned char* p = nullptr;
+        e = cudaGetSymbolAddress((void**)&p, g_yolo_static_scratch);
+        if (e != cudaSuccess || !p)
+            return tcb_fail(nullptr, TCB_ERR_CUDA, "tcb_yolo_nms_static: cudaGetSymbolAddress -> %s", cudaGetErrorString(e));
+        e = cudaFuncSetAttribute(yolo_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)(sizeof(NmsShared) + sizeof(SortEnt) * SORT_SMEM_CAP));
+        if (e != cudaSuccess)
+            return tcb_fail(nullptr, TCB_ERR_CUDA, "tcb_yolo_nms_static: cudaFuncSetAttribute -> %s", cudaGetErrorString(e));
+        g_static_ptr[dev] = p;
+    }
+    *out = g_static_ptr[dev];
+    return TCB_OK;
+}
+
+}  // namespace
+
+extern "C" size_t tcb_yolo_nms_static_scratch_bytes(void) { return TCB_STATIC_SCRATCH_BYTES; }
+
+extern "C" int tcb_yolo_nms_static(const float* pred_dev, int b, int n, int nc, double conf_thres, double iou_thres,
+                                   const int* classes_host, int n_classes, int agnostic, int max_det, int max_nms,
+                                   double* out_dev, int* count_dev, int* xc_count_dev, void* stream) {
+#define ST_REQUIRE(cond, ...) do { if (!(cond)) return tcb_fail(nullptr, TCB_ERR_ARG, __VA_ARGS__); } while (0)
+#define ST_CUDA(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) \
+        return tcb_fail(nullptr, TCB_ERR_CUDA, "tcb_yolo_nms_static: %s -> %s", #call, cudaGetErrorString(e__)); } while (0)
+    ST_REQUIRE(pred_dev && out_dev && count_dev, "tcb_yolo_nms_static: null buffer");
+    ST_REQUIRE(b >= 0 && n >= 0 && nc >= 0, "tcb_yolo_nms_static: bad shape b=%d n=%d nc=%d", b, n, nc);
+    ST_REQUIRE(conf_thres >= 0.0 && conf_thres <= 1.0, "tcb_yolo_nms_static: Invalid Confidence threshold %g, valid values are between 0.0 and 1.0", conf_thres);
+    ST_REQUIRE(iou_thres >= 0.0 && iou_thres <= 1.0, "tcb_yolo_nms_static: Invalid IoU %g, valid values are between 0.0 and 1.0", iou_thres);
+    ST_REQUIRE(max_det >= 1 && max_nms >= 1, "tcb_yolo_nms_static: max_det and max_nms must be >= 1");
+    ST_REQUIRE(n_classes == 0 || classes_host, "tcb_yolo_nms_static: classes_host is null");
+    if (max_det > MAX_DET_CAP) return tcb_fail(nullptr, TCB_ERR_LIMIT, "tcb_yolo_nms_static: max_det %d > compiled limit %d", max_det, MAX_DET_CAP);
+    int npad = 1;
+    while (npad < n) npad <<= 1;
+    if (b > STATIC_MAX_B || (long long)b * n > STATIC_MAX_ROWS || (npad > SORT_SMEM_CAP && (long long)b * npad > STATIC_MAX_SORT))
+        return tcb_fail(nullptr, TCB_ERR_LIMIT,
+                        "tcb_yolo_nms_static: b=%d n=%d exceeds the static scratch (b <= %d, b*n <= %lld, b*pow2ceil(n) <= %lld); "
+                        "use tcb_yolo_nms with a context workspace for larger batches", b, n, STATIC_MAX_B, STATIC_MAX_ROWS, STATIC_MAX_SORT);
+    if (b == 0) return TCB_OK;
+
+    ClassMask cm;
+    memset(&cm, 0, sizeof(cm));
+    for (int i = 0; i < n_classes; i++) {
+        const int c = classes_host[i];
+        if (c >= 256) return tcb_fail(nullptr, TCB_ERR_LIMIT, "tcb_yolo_nms_static: class filter id %d >= 256", c);
+        if (c >= 0) cm.w[c >> 6] |= 1ull << (c & 63);
+    }
+
+    unsigned char* scratch = nullptr;  // device address of g_yolo_static_scratch on the current device
+    const int rc = static_scratch_for_current_device(&scratch);
+    if (rc != TCB_OK) return rc;
+    int* counts = reinterpret_cast<int*>(scratch + ST_OFF_COUNTS);
+    double* c_score = reinterpret_cast<double*>(scratch + ST_OFF_SCORE);
+    float4* c_box = reinterpret_cast<float4*>(scratch + ST_OFF_BOX);
+    int2* c_meta = reinterpret_cast<int2*>(scratch + ST_OFF_META);
+    SortEnt* gsort = reinterpret_cast<SortEnt*>(scratch + ST_OFF_SORT);
+    int* c_count = counts;
+    int* xc_count = counts + b;
+
+    cudaStream_t st = (cudaStream_t)stream;
+    ST_CUDA(cudaMemsetAsync(counts, 0, sizeof(int) * 2 * (size_t)b, st));  // the only state that must start at zero
+    if (n > 0) {
+        int num_sms = 148;
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+        const long long groups = (long long)b * ((n + 31) / 32);
+        long long blocks = (groups + 7) / 8;
+        if (blocks > (long long)num_sms * 16) blocks = (long long)num_sms * 16;
+        yolo_filter_kernel<<<(int)blocks, 256, 0, st>>>(pred_dev, b, n, nc, conf_thres, n_classes > 0, cm,
+                                                        c_score, c_box, c_meta, c_count, xc_count);
+        ST_CUDA(cudaGetLastError());
+    }
+    const size_t smem = sizeof(NmsShared) + sizeof(SortEnt) * SORT_SMEM_CAP;
+    yolo_nms_kernel<<<b, NMS_THREADS, smem, st>>>(n > 0 ? n : 1, c_score, c_box, c_meta, c_count, gsort, npad,
+                                                  iou_thres, agnostic ? 0.0 : 4096.0, max_det, max_nms, out_dev, count_dev);
+    ST_CUDA(cudaGetLastError());
+    if (xc_count_dev) ST_CUDA(cudaMemcpyAsync(xc_count_dev, xc_count, sizeof(int) * (size_t)b, cudaMemcpyDeviceToDevice, st));
+    return TCB_OK;
+#undef ST_REQUIRE
+#undef ST_CUDA
+}

@@ -86,3 +86,32 @@ class Engine:
                       1 if agnostic else 0, int(max_det), int(max_nms), _ptr(out), _ptr(counts[0]), _ptr(counts[1]),
                       _lib.stream_ptr())
         return out, counts[0], counts[1]
+
+
+def yolo_nms_static(pred, conf_thres=0.6, iou_thres=0.45, classes=None, agnostic=False, max_det=300,
+                    max_nms=30000, out=None, counts=None):
+    """tcb_yolo_nms_static: the YOLOv5 postprocess for callers that may not allocate GPU memory (a plugin
+    in a host process that owns all of HBM, a frame callback that cannot take cudaMalloc's device-wide
+    sync). Needs no Engine/context; scratch is a fixed ~8.4 MB device array inside the library, so sizes
+    are capped (b <= 64, b*n <= 131072) and overlapping calls race — keep them on one stream. Pass `out`
+    ([b,max_det,6] f64) and `counts` ([2,b] i32) to keep this wrapper allocation-free as well."""
+    _need_cuda(pred)
+    if pred.dtype != torch.float32 or pred.dim() != 3 or not pred.is_contiguous():
+        raise TypeError("yolo_nms_static: pred must be a contiguous float32 [b,n,5+nc] tensor")
+    b, n, c = pred.shape
+    if out is None:
+        out = torch.zeros((b, max_det, 6), dtype=torch.float64, device=pred.device)
+    if counts is None:
+        counts = torch.zeros((2, b), dtype=torch.int32, device=pred.device)
+    cls_arr, ncls = None, 0
+    if classes is not None:
+        ncls = len(classes)
+        cls_arr = (c_int * max(ncls, 1))(*[int(v) for v in classes])
+    l = _lib.lib()
+    with torch.cuda.device(pred.device):
+        rc = l.tcb_yolo_nms_static(_ptr(pred), b, n, c - 5, float(conf_thres), float(iou_thres), cls_arr, ncls,
+                                   1 if agnostic else 0, int(max_det), int(max_nms), _ptr(out), _ptr(counts[0]),
+                                   _ptr(counts[1]), _lib.stream_ptr())
+    if rc != 0:
+        raise _lib.TcbError(rc, (l.tcb_last_error(None) or b"").decode())
+    return out, counts[0], counts[1]
