@@ -31,21 +31,23 @@ struct PreParams {
     double scale_x, scale_y;
     int th;     // output rows per tile (8, 16 or 32)
     int pitch;  // shared-memory row pitch in bytes (multiple of 16)
+    int tpr_shift;  // log2(threads cooperating on one staged row)
     int vec_store;
 };
 
 // u8 -> normalised f32, identical to numpy's `x.astype(float32) / div - sub` (true IEEE division).
-__device__ __forceinline__ float norm_px(int v, const PreParams& p, int c) {
-    float f = __int_as_float(0x4B000000 | v) - 8388608.0f;  // exact int->float for 0..255 without I2F
+// EXACT: v*(1/div) corrected by two FMAs equals v/div for every v in 0..255 (verified on the host).
+template <bool EXACT>
+__device__ __forceinline__ float norm_px(int v, float div, float rdiv, float sub) {
+    const float f = __int_as_float(0x4B000000 | v) - 8388608.0f;  // exact int->float for 0..255 without I2F
     float q;
-    if (p.exact_recip) {
-        float q0 = f * p.rdiv;
-        float e = __fmaf_rn(-q0, p.div, f);
-        q = __fmaf_rn(e, p.rdiv, q0);
+    if (EXACT) {
+        const float q0 = f * rdiv;
+        q = __fmaf_rn(__fmaf_rn(-q0, div, f), rdiv, q0);
     } else {
-        q = f / p.div;
+        q = f / div;
     }
-    return q - p.sub[c];
+    return q - sub;
 }
 
 // OpenCV resizeLinear column taps for destination column dx (modules/imgproc resize.cpp semantics,
@@ -71,7 +73,121 @@ __device__ __forceinline__ void y_tap(int dy, double scale, int h, int& r0, int&
     r1 = min(max(s + 1, 0), h - 1);
 }
 
-template <bool AREA, bool STAGED>
+// Rows of one warp. INTERIOR: every pixel of the lane's 4 columns and every row lies inside the content
+// rectangle, so no per-pixel predicate is needed (the common case: all tiles but the borders).
+template <bool AREA, bool STAGED, bool EXACT, bool INTERIOR>
+__device__ __forceinline__ void tile_rows(const PreParams& p, const uint8_t* __restrict__ smem, const uint8_t* __restrict__ img,
+                                          int z, int ox0, int ty0, int warp, int xmin, int rmin, bool has_content,
+                                          const int (&off0)[4], const int (&d1)[4], const int (&a0)[4], const int (&a1)[4],
+                                          const bool (&inx)[4]) {
+    const int rpw = p.th >> 3;  // consecutive rows per warp
+    // channel c of the source lands in plane pl[c]; normalisation constants follow the plane
+    int pl[3];
+    float subc[3], padc[3];
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        pl[c] = p.swap ? 2 - c : c;
+        subc[c] = p.swap ? p.sub[2 - c] : p.sub[c];
+        padc[c] = p.swap ? p.padv[2 - c] : p.padv[c];
+    }
+    int hprev[12];
+    int rprev = -1;
+#pragma unroll
+    for (int i = 0; i < 12; i++) hprev[i] = 0;
+
+    for (int rr = 0; rr < rpw; rr++) {
+        const int oy = ty0 + warp * rpw + rr;
+        if (oy >= p.out_h) break;
+        const int dy = oy - p.top;
+        const bool iny = INTERIOR || (has_content && dy >= 0 && dy < p.new_h);
+        int v[12];
+        if (iny) {
+            int r0, r1, b0 = 0, b1 = 0;
+            if (AREA) { r0 = 2 * dy; r1 = 2 * dy + 1; }
+            else y_tap(dy, p.scale_y, p.h, r0, r1, b0, b1);
+            const uint8_t *s0, *s1;
+            if (STAGED) {
+                const long long g0 = (long long)r0 * p.row_stride + (long long)xmin * 3;
+                const long long g1 = (long long)r1 * p.row_stride + (long long)xmin * 3;
+                s0 = smem + (r0 - rmin) * p.pitch + (int)((uintptr_t)(img + g0) & 15);
+                s1 = smem + (r1 - rmin) * p.pitch + (int)((uintptr_t)(img + g1) & 15);
+            } else {
+                s0 = img + (long long)r0 * p.row_stride + (long long)xmin * 3;
+                s1 = img + (long long)r1 * p.row_stride + (long long)xmin * 3;
+            }
+            if (AREA) {
+                int t[48];
+#pragma unroll
+                for (int i = 0; i < 4; i++)
+#pragma unroll
+                    for (int c = 0; c < 3; c++) {
+                        const int k = off0[i] + c;
+                        const bool ok = INTERIOR || inx[i];
+                        t[(i * 3 + c) * 4 + 0] = ok ? (int)s0[k] : 0;
+                        t[(i * 3 + c) * 4 + 1] = ok ? (int)s0[k + 3] : 0;
+                        t[(i * 3 + c) * 4 + 2] = ok ? (int)s1[k] : 0;
+                        t[(i * 3 + c) * 4 + 3] = ok ? (int)s1[k + 3] : 0;
+                    }
+#pragma unroll
+                for (int j = 0; j < 12; j++) v[j] = (t[j * 4] + t[j * 4 + 1] + t[j * 4 + 2] + t[j * 4 + 3] + 2) >> 2;
+            } else {
+                int h0[12], h1[12];
+                const bool reuse = (r0 == rprev);
+                if (reuse) {
+#pragma unroll
+                    for (int j = 0; j < 12; j++) h0[j] = hprev[j];
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 4; i++)
+#pragma unroll
+                        for (int c = 0; c < 3; c++) {
+                            const int k = off0[i] + c;
+                            const bool ok = INTERIOR || inx[i];
+                            h0[i * 3 + c] = ok ? (int)s0[k] * a0[i] + (int)s0[k + d1[i]] * a1[i] : 0;
+                        }
+                }
+                if (r1 == r0) {
+#pragma unroll
+                    for (int j = 0; j < 12; j++) h1[j] = h0[j];
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 4; i++)
+#pragma unroll
+                        for (int c = 0; c < 3; c++) {
+                            const int k = off0[i] + c;
+                            const bool ok = INTERIOR || inx[i];
+                            h1[i * 3 + c] = ok ? (int)s1[k] * a0[i] + (int)s1[k + d1[i]] * a1[i] : 0;
+                        }
+                }
+#pragma unroll
+                for (int j = 0; j < 12; j++) {
+                    v[j] = (((b0 * (h0[j] >> 4)) >> 16) + ((b1 * (h1[j] >> 4)) >> 16) + 2) >> 2;
+                    hprev[j] = h1[j];
+                }
+                rprev = r1;
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            float o[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const bool ok = INTERIOR || (iny && inx[i]);
+                o[i] = ok ? norm_px<EXACT>(v[i * 3 + c], p.div, p.rdiv, subc[c]) : padc[c];
+            }
+            float* d = p.dst + (((long long)z * 3 + pl[c]) * p.out_h + oy) * (long long)p.out_w + ox0;
+            if (p.vec_store) {
+                st_stream_f4(d, make_float4(o[0], o[1], o[2], o[3]));
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; i++)
+                    if (ox0 + i < p.out_w) d[i] = o[i];
+            }
+        }
+    }
+}
+
+template <bool AREA, bool STAGED, bool EXACT>
 __global__ void __launch_bounds__(NTHREADS) preprocess_kernel(const PreParams p) {
     extern __shared__ __align__(16) uint8_t smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -84,6 +200,9 @@ __global__ void __launch_bounds__(NTHREADS) preprocess_kernel(const PreParams p)
     const int cx0 = max(tx0 - p.left, 0), cx1 = min(tx1 - p.left, p.new_w - 1);
     const int cy0 = max(ty0 - p.top, 0), cy1 = min(ty1 - p.top, p.new_h - 1);
     const bool has_content = (cx0 <= cx1) && (cy0 <= cy1);
+    // whole 128 x th tile inside the content rectangle?
+    const bool interior = has_content && (tx0 - p.left >= 0) && (tx0 + TW - 1 - p.left < p.new_w) && (tx0 + TW <= p.out_w) &&
+                          (ty0 - p.top >= 0) && (ty0 + p.th - 1 - p.top < p.new_h) && (ty0 + p.th <= p.out_h);
 
     int xmin = 0, xmax = 0, rmin = 0, rmax = 0;
     if (has_content) {
@@ -99,25 +218,29 @@ __global__ void __launch_bounds__(NTHREADS) preprocess_kernel(const PreParams p)
     }
 
     // ---- stage the source footprint: rows rmin..rmax, bytes xmin*3 .. xmax*3+2 -------------------
+    // 2^tpr_shift threads walk the 16-byte chunks of one row; the rest of the CTA takes other rows.
     if (STAGED && has_content) {
         const int nrows = rmax - rmin + 1;
         const int seg = (xmax - xmin + 1) * 3;
-        const int cpr = p.pitch >> 4;  // 16-byte chunks per staged row
-        for (int q = tid; q < nrows * cpr; q += NTHREADS) {
-            const int r = q / cpr, k = q - r * cpr;
-            const uint8_t* a = img + (long long)(rmin + r) * p.row_stride + (long long)xmin * 3;
-            const uint8_t* g = (const uint8_t*)((uintptr_t)a & ~(uintptr_t)15) + 16 * k;
-            if (g >= a + seg) continue;
-            uint4 v;
-            if (g >= p.src && g + 16 <= p.batch_end) {
-                v = ld_stream_u4(g);
-            } else {  // first/last few bytes of the caller's buffer: never read outside it
-                uint8_t t[16];
+        const int cpr = p.pitch >> 4;
+        const int k = tid & ((1 << p.tpr_shift) - 1);
+        const int rstep = NTHREADS >> p.tpr_shift;
+        if (k < cpr) {
+            for (int r = tid >> p.tpr_shift; r < nrows; r += rstep) {
+                const uint8_t* a = img + (long long)(rmin + r) * p.row_stride + (long long)xmin * 3;
+                const uint8_t* g = (const uint8_t*)((uintptr_t)a & ~(uintptr_t)15) + 16 * k;
+                if (g >= a + seg) continue;
+                uint4 v;
+                if (g >= p.src && g + 16 <= p.batch_end) {
+                    v = ld_stream_u4(g);
+                } else {  // first/last few bytes of the caller's buffer: never read outside it
+                    uint8_t t[16];
 #pragma unroll
-                for (int i = 0; i < 16; i++) t[i] = (g + i >= p.src && g + i < p.batch_end) ? g[i] : 0;
-                v = *reinterpret_cast<uint4*>(t);
+                    for (int i = 0; i < 16; i++) t[i] = (g + i >= p.src && g + i < p.batch_end) ? g[i] : 0;
+                    v = *reinterpret_cast<uint4*>(t);
+                }
+                *reinterpret_cast<uint4*>(smem + r * p.pitch + 16 * k) = v;
             }
-            *reinterpret_cast<uint4*>(smem + (size_t)r * p.pitch + 16 * k) = v;
         }
     }
     __syncthreads();
@@ -143,103 +266,8 @@ __global__ void __launch_bounds__(NTHREADS) preprocess_kernel(const PreParams p)
         }
     }
     if (ox0 >= p.out_w) return;
-
-    const int rpw = p.th >> 3;  // consecutive rows per warp
-    int hprev[12];
-    int rprev = -1;
-#pragma unroll
-    for (int i = 0; i < 12; i++) hprev[i] = 0;
-
-    for (int rr = 0; rr < rpw; rr++) {
-        const int oy = ty0 + warp * rpw + rr;
-        if (oy >= p.out_h) break;
-        const int dy = oy - p.top;
-        const bool iny = has_content && dy >= 0 && dy < p.new_h;
-        float o[3][4];
-        if (!iny) {
-#pragma unroll
-            for (int c = 0; c < 3; c++)
-#pragma unroll
-                for (int i = 0; i < 4; i++) o[c][i] = p.padv[c];
-        } else {
-            int r0, r1, b0 = 0, b1 = 0;
-            if (AREA) { r0 = 2 * dy; r1 = 2 * dy + 1; }
-            else y_tap(dy, p.scale_y, p.h, r0, r1, b0, b1);
-            const uint8_t *s0, *s1;
-            if (STAGED) {
-                const uint8_t* g0 = img + (long long)r0 * p.row_stride + (long long)xmin * 3;
-                const uint8_t* g1 = img + (long long)r1 * p.row_stride + (long long)xmin * 3;
-                s0 = smem + (size_t)(r0 - rmin) * p.pitch + ((uintptr_t)g0 & 15);
-                s1 = smem + (size_t)(r1 - rmin) * p.pitch + ((uintptr_t)g1 & 15);
-            } else {
-                s0 = img + (long long)r0 * p.row_stride + (long long)xmin * 3;
-                s1 = img + (long long)r1 * p.row_stride + (long long)xmin * 3;
-            }
-            if (AREA) {
-#pragma unroll
-                for (int i = 0; i < 4; i++)
-#pragma unroll
-                    for (int c = 0; c < 3; c++) {
-                        const int cc = p.swap ? 2 - c : c;
-                        if (inx[i]) {
-                            const int k = off0[i] + c;
-                            const int v = ((int)s0[k] + (int)s0[k + 3] + (int)s1[k] + (int)s1[k + 3] + 2) >> 2;
-                            o[cc][i] = norm_px(v, p, cc);
-                        } else {
-                            o[cc][i] = p.padv[cc];
-                        }
-                    }
-            } else {
-                int h0[12], h1[12];
-                const bool reuse = (r0 == rprev);
-#pragma unroll
-                for (int i = 0; i < 4; i++)
-#pragma unroll
-                    for (int c = 0; c < 3; c++) {
-                        const int k = off0[i] + c;
-                        h0[i * 3 + c] = reuse ? hprev[i * 3 + c] : (int)s0[k] * a0[i] + (int)s0[k + d1[i]] * a1[i];
-                    }
-                if (r1 == r0) {
-#pragma unroll
-                    for (int i = 0; i < 12; i++) h1[i] = h0[i];
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 4; i++)
-#pragma unroll
-                        for (int c = 0; c < 3; c++) {
-                            const int k = off0[i] + c;
-                            h1[i * 3 + c] = (int)s1[k] * a0[i] + (int)s1[k + d1[i]] * a1[i];
-                        }
-                }
-#pragma unroll
-                for (int i = 0; i < 4; i++)
-#pragma unroll
-                    for (int c = 0; c < 3; c++) {
-                        const int cc = p.swap ? 2 - c : c;
-                        if (inx[i]) {
-                            const int v = (((b0 * (h0[i * 3 + c] >> 4)) >> 16) + ((b1 * (h1[i * 3 + c] >> 4)) >> 16) + 2) >> 2;
-                            o[cc][i] = norm_px(v, p, cc);
-                        } else {
-                            o[cc][i] = p.padv[cc];
-                        }
-                    }
-#pragma unroll
-                for (int i = 0; i < 12; i++) hprev[i] = h1[i];
-                rprev = r1;
-            }
-        }
-#pragma unroll
-        for (int c = 0; c < 3; c++) {
-            float* d = p.dst + (((long long)z * 3 + c) * p.out_h + oy) * (long long)p.out_w + ox0;
-            if (p.vec_store) {
-                st_stream_f4(d, make_float4(o[c][0], o[c][1], o[c][2], o[c][3]));
-            } else {
-#pragma unroll
-                for (int i = 0; i < 4; i++)
-                    if (ox0 + i < p.out_w) d[i] = o[c][i];
-            }
-        }
-    }
+    if (interior) tile_rows<AREA, STAGED, EXACT, true>(p, smem, img, z, ox0, ty0, warp, xmin, rmin, has_content, off0, d1, a0, a1, inx);
+    else tile_rows<AREA, STAGED, EXACT, false>(p, smem, img, z, ox0, ty0, warp, xmin, rmin, has_content, off0, d1, a0, a1, inx);
 }
 
 int iround_half_even(double v) { return (int)nearbyint(v); }  // python round() == ties-to-even
@@ -312,36 +340,42 @@ extern "C" int tcb_preprocess_image(tcb_ctx* ctx, const uint8_t* src_dev, int n,
     }
     p.vec_store = (out_w % 4 == 0) && (((uintptr_t)dst_dev & 15) == 0);
 
-    // choose the tile height so that the staged footprint fits comfortably (several CTAs per SM)
-    const size_t SMEM_BUDGET = 64 * 1024;
+    // tile height: the largest of 32/16/8 rows whose staged footprint leaves 8 CTAs per SM (<= 28 KB);
+    // failing that the largest that fits 64 KB; failing that read the source straight from global memory.
+    const size_t SMEM_MAX = 64 * 1024, SMEM_GOOD = 28 * 1024;
     bool staged = false;
     size_t smem = 0;
     const double sx = area ? 2.0 : p.scale_x, sy = area ? 2.0 : p.scale_y;
-    for (int th = 32; th >= 8; th >>= 1) {
-        long long cols = (long long)floor((TW - 1) * sx) + 4;
-        if (cols > w) cols = w;
-        long long rows = (long long)floor((th - 1) * sy) + 4;
-        if (rows > h) rows = h;
-        long long pitch = ((cols * 3 + 15) / 16) * 16 + 16;
-        p.th = th; p.pitch = (int)pitch;
-        if ((size_t)(rows * pitch) <= SMEM_BUDGET) { staged = true; smem = (size_t)(rows * pitch); break; }
+    for (int pass = 0; pass < 2 && !staged; pass++) {
+        for (int th = 32; th >= 8; th >>= 1) {
+            long long cols = (long long)floor((TW - 1) * sx) + 4;
+            if (cols > w) cols = w;
+            long long rows = (long long)floor((th - 1) * sy) + 4;
+            if (rows > h) rows = h;
+            long long pitch = ((cols * 3 + 15) / 16) * 16 + 16;
+            if ((size_t)(rows * pitch) <= (pass == 0 ? SMEM_GOOD : SMEM_MAX)) {
+                staged = true; smem = (size_t)(rows * pitch); p.th = th; p.pitch = (int)pitch;
+                break;
+            }
+        }
     }
     if (!staged) { p.th = 8; p.pitch = 16; smem = 0; }
+    p.tpr_shift = 0;
+    while ((1 << p.tpr_shift) < (p.pitch >> 4) && p.tpr_shift < 8) p.tpr_shift++;
 
     dim3 grid(tcb_div_up(out_w, TW), tcb_div_up(out_h, p.th), n);
     TCB_REQUIRE(ctx, grid.y <= 65535, "tcb_preprocess_image: output too tall (%d rows)", out_h);
     cudaStream_t st = (cudaStream_t)stream;
-    if (staged && smem > 48 * 1024) {  // opt in to > 48 KB dynamic shared memory
-        TCB_CUDA(ctx, cudaFuncSetAttribute(area ? (const void*)preprocess_kernel<true, true> : (const void*)preprocess_kernel<false, true>,
-                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BUDGET));
-    }
-    if (area) {
-        if (staged) preprocess_kernel<true, true><<<grid, NTHREADS, smem, st>>>(p);
-        else preprocess_kernel<true, false><<<grid, NTHREADS, 0, st>>>(p);
-    } else {
-        if (staged) preprocess_kernel<false, true><<<grid, NTHREADS, smem, st>>>(p);
-        else preprocess_kernel<false, false><<<grid, NTHREADS, 0, st>>>(p);
-    }
+    typedef void (*kern_t)(const PreParams);
+    static const kern_t table[2][2][2] = {
+        {{preprocess_kernel<false, false, false>, preprocess_kernel<false, false, true>},
+         {preprocess_kernel<false, true, false>, preprocess_kernel<false, true, true>}},
+        {{preprocess_kernel<true, false, false>, preprocess_kernel<true, false, true>},
+         {preprocess_kernel<true, true, false>, preprocess_kernel<true, true, true>}}};
+    kern_t kern = table[area ? 1 : 0][staged ? 1 : 0][p.exact_recip ? 1 : 0];
+    if (smem > 48 * 1024)  // opt in to > 48 KB dynamic shared memory
+        TCB_CUDA(ctx, cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX));
+    kern<<<grid, NTHREADS, smem, st>>>(p);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }

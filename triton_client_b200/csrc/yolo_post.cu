@@ -29,6 +29,19 @@ struct ClassMask { unsigned long long w[4]; };  // whitelist for classes 0..255
 // Pass 1: filter + decode. One warp scans 32 rows at a time (one objectness load per lane), then the
 // whole warp cooperates on each surviving row (coalesced class-score loads, shuffle arg-max).
 // ---------------------------------------------------------------------------------------------
+constexpr int FILTER_UNROLL = 4;   // 32-row groups in flight per warp (independent objectness loads)
+constexpr int FILTER_SMALL_NC = 8;  // up to this many classes a surviving lane decodes its own row
+
+__device__ __forceinline__ void emit_candidate(const float* __restrict__ rp, int r, double best, int bidx, long long k,
+                                               double* __restrict__ c_score, float4* __restrict__ c_box, int2* __restrict__ c_meta) {
+    const double x = (double)__ldg(rp), y = (double)__ldg(rp + 1);
+    const double w = (double)__ldg(rp + 2), h = (double)__ldg(rp + 3);
+    float4 bx;
+    bx.x = (float)(x - w / 2); bx.y = (float)(y - h / 2);
+    bx.z = (float)(x + w / 2); bx.w = (float)(y + h / 2);
+    c_score[k] = best; c_box[k] = bx; c_meta[k] = make_int2(r, bidx);
+}
+
 __global__ void __launch_bounds__(256) yolo_filter_kernel(
     const float* __restrict__ pred, int B, int N, int nc, double conf_thres, int use_filter, ClassMask cmask,
     double* __restrict__ c_score, float4* __restrict__ c_box, int2* __restrict__ c_meta,
@@ -40,52 +53,82 @@ __global__ void __launch_bounds__(256) yolo_filter_kernel(
     const long long groups_per_img = (N + 31) / 32;
     const long long total_groups = groups_per_img * B;
 
-    for (long long g = warp_global; g < total_groups; g += nwarps) {
-        const int b = (int)(g / groups_per_img);
-        const int row0 = (int)(g - (long long)b * groups_per_img) * 32;
-        const int row = row0 + lane;
-        const float* base = pred + ((long long)b * N) * stride;
-        float obj = 0.f;
-        bool pass = false;
-        if (row < N) {
-            obj = __ldg(base + (long long)row * stride + 4);
-            pass = (double)obj > conf_thres;
-        }
-        unsigned m = __ballot_sync(0xffffffffu, pass);
-        if (lane == 0 && m) atomicAdd(&xc_count[b], __popc(m));
-        while (m) {
-            const int src_lane = __ffs(m) - 1;
-            m &= m - 1;
-            const int r = row0 + src_lane;
-            const double o = (double)__shfl_sync(0xffffffffu, obj, src_lane);
-            const float* rp = base + (long long)r * stride;
-            double best = -1.0;
-            int bidx = 0x7fffffff;
-            bool nan = false;
-            for (int c = lane; c < nc; c += 32) {
-                const double v = (double)__ldg(rp + 5 + c) * o;
-                nan |= (v != v);
-                if (v > best) { best = v; bidx = c; }  // strict: first index wins inside a lane
-            }
+    for (long long g0 = warp_global * FILTER_UNROLL; g0 < total_groups; g0 += nwarps * FILTER_UNROLL) {
+        float obj[FILTER_UNROLL];
 #pragma unroll
-            for (int s = 16; s > 0; s >>= 1) {
-                const double ob = __shfl_xor_sync(0xffffffffu, best, s);
-                const int oi = __shfl_xor_sync(0xffffffffu, bidx, s);
-                if (ob > best || (ob == best && oi < bidx)) { best = ob; bidx = oi; }
+        for (int u = 0; u < FILTER_UNROLL; u++) {  // all objectness loads first
+            const long long g = g0 + u;
+            obj[u] = -1.f;
+            if (g < total_groups) {
+                const int b = (int)(g / groups_per_img);
+                const int row = (int)(g - (long long)b * groups_per_img) * 32 + lane;
+                if (row < N) obj[u] = __ldg(pred + ((long long)b * N + row) * stride + 4);
             }
-            nan = __any_sync(0xffffffffu, nan);
-            if (lane == 0 && !nan && nc > 0 && best > conf_thres) {
-                bool ok = true;
-                if (use_filter) ok = (bidx < 256) && ((cmask.w[bidx >> 6] >> (bidx & 63)) & 1ull);
-                if (ok) {
-                    const double x = (double)__ldg(rp), y = (double)__ldg(rp + 1);
-                    const double w = (double)__ldg(rp + 2), h = (double)__ldg(rp + 3);
-                    float4 bx;
-                    bx.x = (float)(x - w / 2); bx.y = (float)(y - h / 2);
-                    bx.z = (float)(x + w / 2); bx.w = (float)(y + h / 2);
-                    const int slot = atomicAdd(&c_count[b], 1);
-                    const long long k = (long long)b * N + slot;
-                    c_score[k] = best; c_box[k] = bx; c_meta[k] = make_int2(r, bidx);
+        }
+#pragma unroll
+        for (int u = 0; u < FILTER_UNROLL; u++) {
+            const long long g = g0 + u;
+            if (g >= total_groups) break;
+            const int b = (int)(g / groups_per_img);
+            const int row0 = (int)(g - (long long)b * groups_per_img) * 32;
+            const float* base = pred + ((long long)b * N) * stride;
+            const bool pass = (double)obj[u] > conf_thres;  // padding lanes hold -1 and conf_thres >= 0
+            unsigned m = __ballot_sync(0xffffffffu, pass);
+            if (m == 0) continue;
+            if (lane == 0) atomicAdd(&xc_count[b], __popc(m));
+            if (nc <= FILTER_SMALL_NC) {
+                // few classes: each surviving lane decodes its own row (the lines are already in L1)
+                double best = -1.0;
+                int bidx = 0;
+                bool ok = false;
+                const float* rp = base + (long long)(row0 + lane) * stride;
+                if (pass) {
+                    const double o = (double)obj[u];
+                    bool nan = false;
+                    for (int c = 0; c < nc; c++) {
+                        const double v = (double)__ldg(rp + 5 + c) * o;
+                        nan |= (v != v);
+                        if (v > best) { best = v; bidx = c; }  // strict: first index wins
+                    }
+                    ok = !nan && nc > 0 && best > conf_thres;
+                    if (ok && use_filter) ok = (cmask.w[bidx >> 6] >> (bidx & 63)) & 1ull;
+                }
+                const unsigned em = __ballot_sync(0xffffffffu, ok);
+                if (em) {
+                    int basei = 0;
+                    if (lane == 0) basei = atomicAdd(&c_count[b], __popc(em));
+                    basei = __shfl_sync(0xffffffffu, basei, 0);
+                    if (ok) emit_candidate(rp, row0 + lane, best, bidx, (long long)b * N + basei + __popc(em & ((1u << lane) - 1)),
+                                           c_score, c_box, c_meta);
+                }
+            } else {
+                // many classes: the warp cooperates on each surviving row (coalesced loads, shuffle arg-max)
+                while (m) {
+                    const int src_lane = __ffs(m) - 1;
+                    m &= m - 1;
+                    const int r = row0 + src_lane;
+                    const double o = (double)__shfl_sync(0xffffffffu, obj[u], src_lane);
+                    const float* rp = base + (long long)r * stride;
+                    double best = -1.0;
+                    int bidx = 0x7fffffff;
+                    bool nan = false;
+                    for (int c = lane; c < nc; c += 32) {
+                        const double v = (double)__ldg(rp + 5 + c) * o;
+                        nan |= (v != v);
+                        if (v > best) { best = v; bidx = c; }  // strict: first index wins inside a lane
+                    }
+#pragma unroll
+                    for (int s = 16; s > 0; s >>= 1) {
+                        const double ob = __shfl_xor_sync(0xffffffffu, best, s);
+                        const int oi = __shfl_xor_sync(0xffffffffu, bidx, s);
+                        if (ob > best || (ob == best && oi < bidx)) { best = ob; bidx = oi; }
+                    }
+                    nan = __any_sync(0xffffffffu, nan);
+                    if (lane == 0 && !nan && best > conf_thres) {
+                        bool ok = true;
+                        if (use_filter) ok = (bidx < 256) && ((cmask.w[bidx >> 6] >> (bidx & 63)) & 1ull);
+                        if (ok) emit_candidate(rp, r, best, bidx, (long long)b * N + atomicAdd(&c_count[b], 1), c_score, c_box, c_meta);
+                    }
                 }
             }
         }
@@ -135,6 +178,7 @@ struct NmsShared {
     double cx1[CHUNK], cy1[CHUNK], cx2[CHUNK], cy2[CHUNK], carea[CHUNK];
     unsigned long long mask[CHUNK][CHUNK / 64];
     int alive[CHUNK];
+    unsigned kslot[MAX_DET_CAP];
     int nkept;
 };
 
@@ -217,14 +261,15 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
             S.mask[ci][part] = bits;
         }
         __syncthreads();
-        // (3) serial sweep by one warp, hopping from kept box to kept box
+        // (3) serial sweep by one warp, hopping from kept box to kept box (shared memory only: the
+        //     output rows are written by the whole CTA after the last round)
         if (tid < 32) {
             unsigned long long avail[CHUNK / 64];
 #pragma unroll
             for (int w = 0; w < CHUNK / 64; w++) {
-                unsigned long long a = 0ull;
-                for (int jj = 0; jj < 64; jj++) a |= (unsigned long long)(S.alive[w * 64 + jj] != 0) << jj;
-                avail[w] = a;
+                const unsigned lo = __ballot_sync(0xffffffffu, S.alive[w * 64 + tid] != 0);
+                const unsigned hi = __ballot_sync(0xffffffffu, S.alive[w * 64 + 32 + tid] != 0);
+                avail[w] = ((unsigned long long)hi << 32) | lo;
             }
             int kept = nk;
             while (kept < max_det) {
@@ -234,17 +279,15 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
                     if (avail[w]) i = w * 64 + __ffsll((long long)avail[w]) - 1;
                 if (i < 0) break;
 #pragma unroll
-                for (int w = 0; w < CHUNK / 64; w++) avail[w] &= ~S.mask[i][w];
-                avail[i >> 6] &= ~(1ull << (i & 63));
+                for (int w = 0; w < CHUNK / 64; w++) {
+                    unsigned long long mrow = S.mask[i][w];
+                    if (w == (i >> 6)) mrow |= 1ull << (i & 63);
+                    avail[w] &= ~mrow;
+                }
                 if (tid == 0) {
                     S.kx1[kept] = S.cx1[i]; S.ky1[kept] = S.cy1[i]; S.kx2[kept] = S.cx2[i]; S.ky2[kept] = S.cy2[i];
                     S.karea[kept] = S.carea[i];
-                    const unsigned slot = buf[c0 + i].slot;
-                    const float4 bx = c_box[cbase + slot];
-                    double* o = orow + (long long)kept * 6;
-                    o[0] = (double)bx.x; o[1] = (double)bx.y; o[2] = (double)bx.z; o[3] = (double)bx.w;
-                    o[4] = c_score[cbase + slot];
-                    o[5] = (double)c_meta[cbase + slot].y;
+                    S.kslot[kept] = buf[c0 + i].slot;
                 }
                 kept++;
             }
@@ -252,6 +295,17 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
         }
         __syncthreads();
         if (S.nkept >= max_det) break;
+    }
+    __syncthreads();
+    // ---- write the kept rows: [x1,y1,x2,y2 (f32 box widened), conf (f64), cls] -------------------------
+    const int nk_final = S.nkept;
+    for (int k = tid; k < nk_final; k += NMS_THREADS) {
+        const unsigned slot = S.kslot[k];
+        const float4 bx = c_box[cbase + slot];
+        double* o = orow + (long long)k * 6;
+        o[0] = (double)bx.x; o[1] = (double)bx.y; o[2] = (double)bx.z; o[3] = (double)bx.w;
+        o[4] = c_score[cbase + slot];
+        o[5] = (double)c_meta[cbase + slot].y;
     }
     if (tid == 0) out_count[b] = S.nkept;
 }
