@@ -72,6 +72,30 @@ def golden_yolo_post():
     save("yolo_post", **out)
 
 
+def golden_pillar_vfe():
+    """Reference PillarVFE.forward decoration (pillar_vfe.py:94-118, PFN layers removed) on voxels produced
+    by the oracle voxeliser from a small synthetic sweep; KITTI pillar config and the nuScenes one."""
+    from oracle import voxelize as ov
+    out = {}
+    cfgs = [([0, -39.68, -3, 69.12, 39.68, 1], [0.16, 0.16, 4], 32, 4), ([-51.2, -51.2, -5.0, 51.2, 51.2, 3.0], [0.2, 0.2, 8], 20, 5)]
+    for k, (rng, vs, p, f) in enumerate(cfgs):
+        pts = synth.lidar_sweep(synth.seed_for(4, k), beams=16, azimuths=200, full_circle=(k == 1))
+        if f == 5:
+            pts = np.concatenate([pts, np.zeros((len(pts), 1), np.float32)], 1)
+        voxels, coords, num = ov.points_to_voxel(pts, rng, vs, p, 400, "continue")
+        coords4 = np.pad(coords, ((0, 0), (1, 0)))
+        vfe = ref_harness.pillar_vfe(vs, np.array(rng, np.float32) if k == 0 else rng, f)
+        bd = {"voxels": torch.from_numpy(voxels), "voxel_num_points": torch.from_numpy(num), "voxel_coords": torch.from_numpy(coords4)}
+        feats = vfe.forward(bd)["pillar_features"].numpy()
+        assert feats.shape == (voxels.shape[0], p, f + 6), feats.shape
+        out[f"points{k}"] = pts
+        out[f"range{k}"] = np.array(rng, np.float64)
+        out[f"vsize{k}"] = np.array(vs, np.float64)
+        out[f"maxpts{k}"] = np.array(p)
+        out[f"feats{k}"] = feats
+    save("pillar_vfe", **out)
+
+
 def main():
     assert ref_harness.available(), "reference not mounted"
     os.makedirs(GOLD, exist_ok=True)

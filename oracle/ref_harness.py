@@ -90,3 +90,36 @@ def centernet_utils():
 
 def common_utils():
     return load_file("ref_common_utils", "utils/export_models/OpenPCDet/pcdet/utils/common_utils.py", stubs=("SharedArray",))
+
+
+def load_package(pkgname, reldir, files):
+    """Load a few sibling files of the reference as a synthetic package so their relative imports work."""
+    pkg = types.ModuleType(pkgname)
+    pkg.__path__ = [os.path.join(REF, reldir)]
+    sys.modules[pkgname] = pkg
+    mods = {}
+    for f in files:
+        name = f"{pkgname}.{f[:-3]}"
+        spec = importlib.util.spec_from_file_location(name, os.path.join(REF, reldir, f))
+        mod = importlib.util.module_from_spec(spec)
+        sys.modules[name] = mod
+        spec.loader.exec_module(mod)
+        setattr(pkg, f[:-3], mod)
+        mods[f[:-3]] = mod
+    return mods
+
+
+class _Cfg(dict):
+    """EasyDict stand-in (attribute access + .get)."""
+    __getattr__ = dict.__getitem__
+
+
+def pillar_vfe(voxel_size, point_cloud_range, num_point_features=4):
+    """The reference's PillarVFE (OPCD/pcdet/models/backbones_3d/vfe/pillar_vfe.py) with the PFN layers
+    removed, so forward() returns the decorated (M,P,F+6) features of lines :94-118."""
+    import torch
+    mods = load_package("ref_vfe", "utils/export_models/OpenPCDet/pcdet/models/backbones_3d/vfe", ["vfe_template.py", "pillar_vfe.py"])
+    cfg = _Cfg(USE_NORM=True, WITH_DISTANCE=False, USE_ABSLOTE_XYZ=True, NUM_FILTERS=[64])
+    vfe = mods["pillar_vfe"].PillarVFE(cfg, num_point_features, voxel_size, point_cloud_range)
+    vfe.pfn_layers = torch.nn.ModuleList([])
+    return vfe

@@ -1,0 +1,108 @@
+"""GPU parity: voxelisation (bit-exact voxel order, coords, counts and point slots) and pillar decoration
+(<= 1e-5 relative, north_star's float standard) through the C ABI vs the oracle / reference golden vectors."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import golden
+from oracle import voxelize as ov
+from triton_client_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+KITTI = ([0, -39.68, -3, 69.12, 39.68, 1], [0.16, 0.16, 4])
+NUSC = ([-51.2, -51.2, -5.0, 51.2, 51.2, 3.0], [0.2, 0.2, 8])
+SHIPPED = ([0, -40, -3, 70.4, 40, 1], [0.05, 0.05, 0.1])
+
+
+def _gpu_vox(engine, pts, rng, vs, p, mv, **kw):
+    v, c, n, m = engine.voxelize(torch.from_numpy(pts).cuda(), rng, vs, p, mv, **kw)
+    torch.cuda.synchronize()
+    m = int(m.item())
+    return v[:m].cpu().numpy(), c[:m].cpu().numpy(), n[:m].cpu().numpy()
+
+
+def _check(got, want, batch_col=True):
+    v, c, n = got
+    wv, wc, wn = want
+    assert v.shape == wv.shape, (v.shape, wv.shape)
+    assert np.array_equal(c[:, 1:] if batch_col else c, wc) and (not batch_col or (c[:, 0] == 0).all())
+    assert np.array_equal(n, wn)
+    assert np.array_equal(v, wv)
+
+
+@pytest.mark.parametrize("cfg,p,mv,overflow", [
+    (KITTI, 32, 12000, "continue"), (KITTI, 32, 40000, "continue"), (KITTI, 32, 12000, "break"),
+    (SHIPPED, 5, 40000, "continue"), (KITTI, 3, 500, "break"), (KITTI, 40, 100000, "continue"),
+])
+def test_c4_bit_exact(engine, cfg, p, mv, overflow):
+    pts = synth.lidar_sweep(synth.seed_for(4, 1))
+    want = ov.points_to_voxel(pts, cfg[0], cfg[1], p, mv, overflow)
+    _check(_gpu_vox(engine, pts, cfg[0], cfg[1], p, mv, overflow=overflow), want)
+
+
+def test_c5_nuscenes_break_mode_f32_and_f64(engine):
+    pts = synth.lidar_multisweep(synth.seed_for(5, 1))
+    for f64 in (False, True):
+        want = ov.points_to_voxel(pts, NUSC[0], NUSC[1], 20, 60000, "break", f64_math=f64)
+        _check(_gpu_vox(engine, pts, NUSC[0], NUSC[1], 20, 60000, overflow="break", f64_math=f64), want)
+    want = ov.points_to_voxel(pts, NUSC[0], NUSC[1], 20, 5000, "break")   # overflow actually hit
+    _check(_gpu_vox(engine, pts, NUSC[0], NUSC[1], 20, 5000, overflow="break"), want)
+
+
+def test_range_mask_conditioning_and_strided_rows(engine):
+    raw = synth.lidar_sweep(77, beams=32, azimuths=600)
+    raw[:, 3] *= 37.0
+    wide = np.concatenate([raw, np.full((len(raw), 2), 9.0, np.float32)], axis=1)  # 6 columns, 4 used
+    cond = ov.condition_points(raw, 1.5)
+    d = ov.filter_pc_pointpillar(cond, *KITTI, 32, 40000)
+    v, c, n, m = engine.voxelize(torch.from_numpy(wide).cuda(), KITTI[0], KITTI[1], 32, 40000, range_mask=True, z_offset=1.5,
+                                 intensity_col=3, nfeat=4)
+    m = int(m.item())
+    assert np.array_equal(c[:m].cpu().numpy(), d["voxel_coords"]) and np.array_equal(n[:m].cpu().numpy(), d["voxel_num_points"])
+    assert np.array_equal(v[:m].cpu().numpy(), d["voxels"])
+
+
+def test_dense_pillars_more_points_than_slots(engine):
+    rng = np.random.default_rng(3)
+    pts = np.concatenate([rng.uniform([10, 0, -1, 0], [10.15, 0.15, 0, 1], (5000, 4)),      # one pillar with 5000 points
+                          rng.uniform([20, -5, -1, 0], [22, 5, 0, 1], (3000, 4))]).astype(np.float32)
+    pts = pts[rng.permutation(len(pts))]
+    want = ov.points_to_voxel(pts, *KITTI, 32, 12000)
+    assert want[2].max() == 32
+    _check(_gpu_vox(engine, pts, *KITTI, 32, 12000), want)
+
+
+def test_empty_and_all_outside(engine):
+    got = _gpu_vox(engine, np.zeros((0, 4), np.float32), *KITTI, 32, 100)
+    assert got[0].shape == (0, 32, 4)
+    far = np.full((100, 4), 1e4, np.float32)
+    assert _gpu_vox(engine, far, *KITTI, 32, 100)[0].shape[0] == 0
+    nan = np.full((10, 4), np.nan, np.float32)
+    assert _gpu_vox(engine, nan, *KITTI, 32, 100)[0].shape[0] == 0
+
+
+def test_golden_pillar_decoration(engine):
+    g = golden("pillar_vfe")
+    for k in range(2):
+        rng, vs, p = g[f"range{k}"].tolist(), g[f"vsize{k}"].tolist(), int(g[f"maxpts{k}"])
+        v, c, n, m = engine.voxelize(torch.from_numpy(g[f"points{k}"]).cuda(), rng, vs, p, 400)
+        feats = engine.pillar_decorate(v, c, n, vs, rng, m=m)
+        mm = int(m.item())
+        want = g[f"feats{k}"]
+        assert mm == want.shape[0]
+        np.testing.assert_allclose(feats[:mm].cpu().numpy(), want, rtol=1e-5, atol=2e-5)
+
+
+def test_decorate_full_size_vs_oracle(engine):
+    pts = synth.lidar_sweep(synth.seed_for(4, 2))
+    v, c, n, m = engine.voxelize(torch.from_numpy(pts).cuda(), *KITTI, 32, 12000)
+    feats = engine.pillar_decorate(v, c, n, KITTI[1], KITTI[0], m=m)
+    mm = int(m.item())
+    want = ov.pillar_decorate(v[:mm].cpu().numpy(), c[:mm].cpu().numpy(), n[:mm].cpu().numpy(), KITTI[1], np.array(KITTI[0], np.float32))
+    np.testing.assert_allclose(feats[:mm].cpu().numpy(), want, rtol=1e-5, atol=2e-5)
+    # property: padded slots are exactly zero, kept slots carry the raw features unchanged
+    f = feats[:mm].cpu().numpy()
+    slot = np.arange(32)[None, :]
+    pad = slot >= n[:mm].cpu().numpy()[:, None]
+    assert (f[pad] == 0).all() and np.array_equal(f[..., :4][~pad], v[:mm].cpu().numpy()[~pad])

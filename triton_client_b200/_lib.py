@@ -40,6 +40,11 @@ SIGNATURES = {
     "tcb_yolo_nms_workspace": (c_size_t, [c_int, c_int]),
     "tcb_yolo_nms": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_double, c_double, P(c_int), c_int, c_int,
                              c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "tcb_voxelize_workspace": (c_size_t, [c_int, c_int]),
+    "tcb_voxelize": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, P(c_double), P(c_double), c_int, c_int, c_int, c_int,
+                             c_int, c_float, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "tcb_pillar_decorate": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, P(c_double),
+                                    P(c_double), c_void_p, c_void_p]),
     "tcb_yolo_nms_static_scratch_bytes": (c_size_t, []),
     "tcb_yolo_nms_static": (c_int, [c_void_p, c_int, c_int, c_int, c_double, c_double, P(c_int), c_int, c_int,
                                     c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),

@@ -1,0 +1,396 @@
+// Hard voxelisation + pillar feature decoration on device.
+//
+// The reference voxelises on the CPU with a sequential first-seen scan (spconv VoxelGenerator through
+// OPCD/pcdet/datasets/processor/data_processor.py:15-60,115-143, or det3d's VoxelGenerator through
+// clients/preprocess/voxelize.py:19-24,38-42). A GPU hash is unordered, so determinism is rebuilt from
+// point indices: voxel id = rank of the cell's FIRST point among all first points, slot inside the voxel
+// = rank of the point among the cell's points — bit-identical to the sequential scan.
+//
+//   K1 cells+hash : per point, x/y range mask (common_utils.py:60-63, inclusive, no z test), cell =
+//                   floor((p - min)/size) per axis in f32 (or f64), atomicCAS open-addressing insert of
+//                   the linear cell id, atomicMin(first point index), atomicAdd(point count)
+//   K2 count      : per 1024-point block, how many points are the first of their cell
+//   K3 scan       : exclusive scan of the block counts (one CTA)
+//   K4 assign     : voxel id = block offset + in-block rank; coords; CSR segment; overflow break point
+//   K5 scatter    : point index -> its voxel's CSR segment (unordered, atomicAdd cursor)
+//   K6 gather     : one warp per voxel orders the segment by point index, keeps the first P, writes
+//                   the zero-padded (P, F) block and the count
+//   decorate      : PillarVFE.forward decoration (OPCD/pcdet/models/backbones_3d/vfe/pillar_vfe.py:94-118)
+#include "common.cuh"
+#include <limits.h>
+
+namespace {
+
+constexpr int VB = 1024;  // points per block in the ordered passes
+
+struct VoxParams {
+    const float* pts; int n; int pt_stride; int nfeat;
+    double rmin[3], rmax_x, rmax_y, rmin_x, rmin_y;  // range
+    double vs[3];
+    float rminf[3], vsf[3], mx0, mx1, my0, my1;  // f32 copies (f32 mode and range mask)
+    int grid[3];
+    int max_pts, max_vox, break_mode, f64_math, range_mask;
+    float z_offset; int intensity_col; const float* intensity_max;  // b1 conditioning (optional)
+    int H;  // hash size (power of two)
+};
+
+__device__ __forceinline__ float cond_feature(const VoxParams& p, const float* row, int j) {
+    float v = __ldg(row + j);
+    if (j == 2) v = v + p.z_offset;
+    if (j == p.intensity_col) v = v / __ldg(p.intensity_max);
+    return v;
+}
+
+// cell id of point i, or -1 when masked / outside the grid
+__device__ __forceinline__ int point_cell(const VoxParams& p, int i, int& cx, int& cy, int& cz) {
+    const float* row = p.pts + (long long)i * p.pt_stride;
+    const float x = cond_feature(p, row, 0), y = cond_feature(p, row, 1), z = cond_feature(p, row, 2);
+    if (p.range_mask && !(x >= p.mx0 && x <= p.mx1 && y >= p.my0 && y <= p.my1)) return -1;
+    int c[3];
+    const float q[3] = {x, y, z};
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+        if (p.f64_math) {
+            const double f = floor(((double)q[j] - p.rmin[j]) / p.vs[j]);
+            if (!(f >= 0.0 && f < (double)p.grid[j])) return -1;
+            c[j] = (int)f;
+        } else {
+            const float f = floorf((q[j] - p.rminf[j]) / p.vsf[j]);
+            if (!(f >= 0.f && f < (float)p.grid[j])) return -1;
+            c[j] = (int)f;
+        }
+    }
+    cx = c[0]; cy = c[1]; cz = c[2];
+    return (cz * p.grid[1] + cy) * p.grid[0] + cx;
+}
+
+__device__ __forceinline__ unsigned hash_cell(int cell, int H) {
+    return ((unsigned)cell * 2654435761u) >> 7 & (unsigned)(H - 1);
+}
+
+__global__ void __launch_bounds__(256) vox_hash_kernel(const VoxParams p, int* __restrict__ pslot,
+                                                       int* __restrict__ hkey, int* __restrict__ hmin, int* __restrict__ hcnt) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= p.n) return;
+    int cx, cy, cz;
+    const int cell = point_cell(p, i, cx, cy, cz);
+    if (cell < 0) { pslot[i] = -1; return; }
+    unsigned h = hash_cell(cell, p.H);
+    while (true) {
+        const int prev = atomicCAS(&hkey[h], -1, cell);
+        if (prev == -1 || prev == cell) break;
+        h = (h + 1) & (unsigned)(p.H - 1);
+    }
+    atomicMin(&hmin[h], i);
+    atomicAdd(&hcnt[h], 1);
+    pslot[i] = (int)h;
+}
+
+__device__ __forceinline__ int block_sum(int v, int* sh) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) v += __shfl_xor_sync(0xffffffffu, v, s);
+    if (lane == 0) sh[warp] = v;
+    __syncthreads();
+    int t = (threadIdx.x < (blockDim.x >> 5)) ? sh[threadIdx.x] : 0;
+    if (warp == 0) {
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1) t += __shfl_xor_sync(0xffffffffu, t, s);
+        if (lane == 0) sh[0] = t;
+    }
+    __syncthreads();
+    const int r = sh[0];
+    __syncthreads();
+    return r;
+}
+
+__global__ void __launch_bounds__(VB) vox_count_kernel(int n, const int* __restrict__ pslot, const int* __restrict__ hmin,
+                                                       int* __restrict__ blocksum) {
+    __shared__ int sh[32];
+    const int i = blockIdx.x * VB + threadIdx.x;
+    int first = 0;
+    if (i < n) { const int s = pslot[i]; first = (s >= 0 && hmin[s] == i); }
+    const int tot = block_sum(first, sh);
+    if (threadIdx.x == 0) blocksum[blockIdx.x] = tot;
+}
+
+// exclusive scan of up to 1024*1024 points' block sums by one CTA (nblk <= 4096)
+__global__ void __launch_bounds__(1024) vox_scan_kernel(int nblk, int* __restrict__ blocksum, int max_vox,
+                                                        int* __restrict__ scalars, int* __restrict__ m_out) {
+    __shared__ int sh[32];
+    __shared__ int carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < nblk; base += 1024) {
+        const int i = base + threadIdx.x;
+        const int v = (i < nblk) ? blocksum[i] : 0;
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        int inc = v;
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, s); if (lane >= s) inc += t; }
+        if (lane == 31) sh[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            int w = sh[lane];
+#pragma unroll
+            for (int s = 1; s < 32; s <<= 1) { const int t = __shfl_up_sync(0xffffffffu, w, s); if (lane >= s) w += t; }
+            sh[lane] = w;
+        }
+        __syncthreads();
+        const int prefix = carry + (warp ? sh[warp - 1] : 0) + inc - v;
+        if (i < nblk) blocksum[i] = prefix;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = prefix + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        const int total = carry;
+        scalars[0] = total;                              // occupied cells
+        scalars[1] = INT_MAX;                            // break point index (break mode)
+        scalars[2] = 0;                                  // CSR cursor
+        *m_out = total < max_vox ? total : max_vox;
+    }
+}
+
+__global__ void __launch_bounds__(VB) vox_assign_kernel(const VoxParams p, const int* __restrict__ pslot, const int* __restrict__ hmin,
+                                                        const int* __restrict__ hcnt, const int* __restrict__ blockoff,
+                                                        int* __restrict__ hvid, int* __restrict__ hseg, int* __restrict__ vslot,
+                                                        int* __restrict__ scalars, int* __restrict__ coords) {
+    __shared__ int sh[32];
+    const int i = blockIdx.x * VB + threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int s = -1, first = 0;
+    if (i < p.n) { s = pslot[i]; first = (s >= 0 && hmin[s] == i); }
+    // in-block exclusive rank of `first`
+    const unsigned bal = __ballot_sync(0xffffffffu, first);
+    if (lane == 0) sh[warp] = __popc(bal);
+    __syncthreads();
+    if (warp == 0) {
+        int w = sh[lane];
+#pragma unroll
+        for (int k = 1; k < 32; k <<= 1) { const int t = __shfl_up_sync(0xffffffffu, w, k); if (lane >= k) w += t; }
+        sh[lane] = w;
+    }
+    __syncthreads();
+    if (!first) return;
+    const int vid = blockoff[blockIdx.x] + (warp ? sh[warp - 1] : 0) + __popc(bal & ((1u << lane) - 1));
+    hvid[s] = vid;
+    if (vid < p.max_vox) {
+        int cx, cy, cz;
+        point_cell(p, i, cx, cy, cz);
+        reinterpret_cast<int4*>(coords)[vid] = make_int4(0, cz, cy, cx);  // [batch, z, y, x] (preprocess_3d.py:50)
+        vslot[vid] = s;
+        hseg[s] = atomicAdd(&scalars[2], hcnt[s]);
+    } else if (vid == p.max_vox) {
+        scalars[1] = i;  // the point at which the SECOND/det3d scan breaks
+    }
+}
+
+__global__ void __launch_bounds__(256) vox_scatter_kernel(const VoxParams p, const int* __restrict__ pslot, const int* __restrict__ hvid,
+                                                          const int* __restrict__ hseg, int* __restrict__ hfill,
+                                                          const int* __restrict__ scalars, int* __restrict__ csr) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= p.n) return;
+    const int s = pslot[i];
+    if (s < 0) return;
+    if (hvid[s] >= p.max_vox) return;                 // "continue": the voxel was never created
+    if (p.break_mode && i >= scalars[1]) return;      // "break": the scan stopped before this point
+    csr[hseg[s] + atomicAdd(&hfill[s], 1)] = i;
+}
+
+// One warp per voxel: keep the max_pts smallest point indices of the segment, in ascending order.
+__global__ void __launch_bounds__(256) vox_gather_kernel(const VoxParams p, const int* __restrict__ m_dev, const int* __restrict__ vslot,
+                                                         const int* __restrict__ hseg, const int* __restrict__ hfill,
+                                                         const int* __restrict__ csr, float* __restrict__ voxels, int* __restrict__ num_pts) {
+    const int lane = threadIdx.x & 31;
+    const int v = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (v >= *m_dev) return;
+    const int s = vslot[v];
+    const int L = hfill[s];
+    const int* seg = csr + hseg[s];
+    const int P = p.max_pts, F = p.nfeat;
+    const int keep = L < P ? L : P;
+    float* vout = voxels + (long long)v * P * F;
+    if (lane == 0) num_pts[v] = keep;
+    if (L <= 32) {
+        const int mine = lane < L ? seg[lane] : INT_MAX;
+        int rank = 0;
+        for (int t = 0; t < L; t++) rank += (__shfl_sync(0xffffffffu, mine, t) < mine);
+        if (lane < L && rank < P) {
+            const float* row = p.pts + (long long)mine * p.pt_stride;
+            for (int j = 0; j < F; j++) vout[rank * F + j] = cond_feature(p, row, j);
+        }
+    } else {
+        int last = -1;
+        for (int r = 0; r < keep; r++) {  // selection: next smallest index greater than `last`
+            int best = INT_MAX;
+            for (int t = lane; t < L; t += 32) { const int q = seg[t]; if (q > last && q < best) best = q; }
+#pragma unroll
+            for (int k = 16; k > 0; k >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, k));
+            last = best;
+            const float* row = p.pts + (long long)best * p.pt_stride;
+            for (int j = lane; j < F; j += 32) vout[r * F + j] = cond_feature(p, row, j);
+        }
+    }
+    for (int e = keep * F + lane; e < P * F; e += 32) vout[e] = 0.f;  // zero padding
+}
+
+// per-frame max of one feature column (b1: intensity /= max(intensity)); values assumed finite
+__global__ void __launch_bounds__(256) vox_colmax_kernel(const float* __restrict__ pts, int n, int stride, int col, float* __restrict__ out) {
+    float m = -INFINITY;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) m = fmaxf(m, __ldg(pts + (long long)i * stride + col));
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, s));
+    if ((threadIdx.x & 31) == 0) {
+        // float atomic max through the ordered-int trick
+        if (m >= 0.f) atomicMax(reinterpret_cast<int*>(out), __float_as_int(m));
+        else atomicMin(reinterpret_cast<unsigned*>(out), __float_as_uint(m));
+    }
+}
+
+__global__ void vox_init_max_kernel(float* out) { *out = -INFINITY; }
+
+// ---- pillar decoration ---------------------------------------------------------------------------
+// out[v, s, :] = mask * [feat(F), xyz - mean(3), xyz - pillar centre(3)]      (pillar_vfe.py:94-118)
+__global__ void __launch_bounds__(256) pillar_decorate_kernel(const float* __restrict__ voxels, const int* __restrict__ coords,
+                                                              const int* __restrict__ num_pts, const int* __restrict__ m_dev, int m_host,
+                                                              int P, int F, float vx, float vy, float vz, float xo, float yo, float zo,
+                                                              float* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int v = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int M = m_dev ? *m_dev : m_host;
+    if (v >= M) return;
+    const float* vin = voxels + (long long)v * P * F;
+    const int n = num_pts[v];
+    const int4 c = reinterpret_cast<const int4*>(coords)[v];  // b, z, y, x
+    float sx = 0.f, sy = 0.f, sz = 0.f;
+    for (int s = lane; s < P; s += 32) { sx += vin[s * F]; sy += vin[s * F + 1]; sz += vin[s * F + 2]; }
+#pragma unroll
+    for (int k = 16; k > 0; k >>= 1) {
+        sx += __shfl_xor_sync(0xffffffffu, sx, k); sy += __shfl_xor_sync(0xffffffffu, sy, k); sz += __shfl_xor_sync(0xffffffffu, sz, k);
+    }
+    const float fn = (float)n;
+    const float mx = sx / fn, my = sy / fn, mz = sz / fn;
+    const float px = (float)c.w * vx + xo, py = (float)c.z * vy + yo, pz = (float)c.y * vz + zo;
+    const int FO = F + 6;
+    float* vo = out + (long long)v * P * FO;
+    for (int s = lane; s < P; s += 32) {
+        const float mask = (n > s) ? 1.f : 0.f;
+        const float x = vin[s * F], y = vin[s * F + 1], z = vin[s * F + 2];
+        float* o = vo + s * FO;
+        for (int j = 0; j < F; j++) o[j] = vin[s * F + j] * mask;
+        o[F + 0] = (x - mx) * mask; o[F + 1] = (y - my) * mask; o[F + 2] = (z - mz) * mask;
+        o[F + 3] = (x - px) * mask; o[F + 4] = (y - py) * mask; o[F + 5] = (z - pz) * mask;
+    }
+}
+
+int next_pow2(long long v) { int r = 1024; while (r < v) r <<= 1; return r; }
+
+}  // namespace
+
+extern "C" size_t tcb_voxelize_workspace(int n, int max_vox) {
+    if (n < 0) n = 0;
+    if (max_vox < 0) max_vox = 0;
+    const size_t H = (size_t)next_pow2(2LL * (n > 0 ? n : 1));
+    size_t bytes = 4096;
+    bytes += 2 * ((size_t)n * 4 + 256);          // pslot, csr
+    bytes += 6 * (H * 4 + 256);                  // hkey, hmin, hcnt, hvid, hseg, hfill
+    bytes += ((size_t)n / VB + 2) * 4 + 256;     // block sums
+    bytes += (size_t)max_vox * 4 + 256;          // vslot
+    return bytes;
+}
+
+extern "C" int tcb_voxelize(tcb_ctx* ctx, const float* pts_dev, int n, int pt_stride, int nfeat, const double range[6],
+                            const double vsize[3], int max_pts, int max_vox, int overflow_mode, int f64_math,
+                            int range_mask_xy, float z_offset, int intensity_col, float* voxels_dev, int* coords_dev,
+                            int* num_pts_dev, int* m_out_dev, void* stream) {
+    TCB_CHECK_CTX(ctx);
+    TCB_REQUIRE(ctx, range && vsize && voxels_dev && coords_dev && num_pts_dev && m_out_dev, "tcb_voxelize: null argument");
+    TCB_REQUIRE(ctx, n >= 0 && (n == 0 || pts_dev), "tcb_voxelize: bad points");
+    TCB_REQUIRE(ctx, nfeat >= 3 && pt_stride >= nfeat, "tcb_voxelize: need nfeat >= 3 and pt_stride >= nfeat (got %d, %d)", nfeat, pt_stride);
+    TCB_REQUIRE(ctx, max_pts >= 1 && max_vox >= 1, "tcb_voxelize: max_pts and max_vox must be >= 1");
+    TCB_REQUIRE(ctx, overflow_mode == 0 || overflow_mode == 1, "tcb_voxelize: overflow_mode must be 0 (continue) or 1 (break)");
+    TCB_REQUIRE(ctx, intensity_col < nfeat, "tcb_voxelize: intensity_col out of range");
+    if (n > (1 << 26)) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_voxelize: more than 2^26 points");
+    cudaStream_t st = (cudaStream_t)stream;
+
+    VoxParams p;
+    memset(&p, 0, sizeof(p));
+    p.pts = pts_dev; p.n = n; p.pt_stride = pt_stride; p.nfeat = nfeat;
+    long long cells = 1;
+    for (int j = 0; j < 3; j++) {
+        TCB_REQUIRE(ctx, vsize[j] > 0 && range[j + 3] > range[j], "tcb_voxelize: bad range/voxel size on axis %d", j);
+        p.rmin[j] = range[j]; p.vs[j] = vsize[j];
+        p.rminf[j] = (float)range[j]; p.vsf[j] = (float)vsize[j];
+        // grid = round((max - min) / size), in the arithmetic of the chosen precision (data_processor.py:117-118)
+        const double g = f64_math ? (range[j + 3] - range[j]) / vsize[j]
+                                  : (double)(((float)range[j + 3] - (float)range[j]) / (float)vsize[j]);
+        p.grid[j] = (int)nearbyint(g);
+        TCB_REQUIRE(ctx, p.grid[j] >= 1, "tcb_voxelize: empty grid on axis %d", j);
+        cells *= p.grid[j];
+    }
+    if (cells >= INT_MAX) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_voxelize: grid of %lld cells does not fit a 32-bit key", cells);
+    p.mx0 = (float)range[0]; p.mx1 = (float)range[3]; p.my0 = (float)range[1]; p.my1 = (float)range[4];
+    p.max_pts = max_pts; p.max_vox = max_vox; p.break_mode = overflow_mode; p.f64_math = f64_math ? 1 : 0;
+    p.range_mask = range_mask_xy ? 1 : 0; p.z_offset = z_offset; p.intensity_col = intensity_col;
+    p.H = next_pow2(2LL * (n > 0 ? n : 1));
+
+    const int nblk = tcb_div_up(n > 0 ? n : 1, VB);
+    if (nblk > 65536) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_voxelize: too many points");
+    TCB_WS(ctx, scalars, int, 64);
+    TCB_WS(ctx, pslot, int, n > 0 ? n : 1);
+    TCB_WS(ctx, csr, int, n > 0 ? n : 1);
+    TCB_WS(ctx, htab, int, (size_t)p.H * 6);
+    TCB_WS(ctx, blocksum, int, nblk + 1);
+    TCB_WS(ctx, vslot, int, max_vox);
+    int *hkey = htab, *hmin = htab + p.H, *hcnt = htab + 2 * (size_t)p.H, *hfill = htab + 3 * (size_t)p.H,
+        *hvid = htab + 4 * (size_t)p.H, *hseg = htab + 5 * (size_t)p.H;
+    float* imax = reinterpret_cast<float*>(scalars + 8);
+    p.intensity_max = imax;
+
+    // hkey = -1, hmin = INT_MAX (0x7f7f7f7f is large enough: indices < 2^26), hcnt = hfill = 0
+    TCB_CUDA(ctx, cudaMemsetAsync(hkey, 0xff, (size_t)p.H * 4, st));
+    TCB_CUDA(ctx, cudaMemsetAsync(hmin, 0x7f, (size_t)p.H * 4, st));
+    TCB_CUDA(ctx, cudaMemsetAsync(hcnt, 0, (size_t)p.H * 8, st));
+    if (intensity_col >= 0 && n > 0) {
+        vox_init_max_kernel<<<1, 1, 0, st>>>(imax);
+        TCB_LAUNCHED(ctx);
+        vox_colmax_kernel<<<ctx->num_sms * 2, 256, 0, st>>>(pts_dev, n, pt_stride, intensity_col, imax);
+        TCB_LAUNCHED(ctx);
+    }
+    if (n > 0) {
+        vox_hash_kernel<<<tcb_div_up(n, 256), 256, 0, st>>>(p, pslot, hkey, hmin, hcnt);
+        TCB_LAUNCHED(ctx);
+        vox_count_kernel<<<nblk, VB, 0, st>>>(n, pslot, hmin, blocksum);
+        TCB_LAUNCHED(ctx);
+    } else {
+        TCB_CUDA(ctx, cudaMemsetAsync(blocksum, 0, sizeof(int) * (nblk + 1), st));
+    }
+    vox_scan_kernel<<<1, 1024, 0, st>>>(nblk, blocksum, max_vox, scalars, m_out_dev);
+    TCB_LAUNCHED(ctx);
+    if (n > 0) {
+        vox_assign_kernel<<<nblk, VB, 0, st>>>(p, pslot, hmin, hcnt, blocksum, hvid, hseg, vslot, scalars, coords_dev);
+        TCB_LAUNCHED(ctx);
+        vox_scatter_kernel<<<tcb_div_up(n, 256), 256, 0, st>>>(p, pslot, hvid, hseg, hfill, scalars, csr);
+        TCB_LAUNCHED(ctx);
+        vox_gather_kernel<<<tcb_div_up((long long)max_vox * 32, 256), 256, 0, st>>>(p, m_out_dev, vslot, hseg, hfill, csr, voxels_dev, num_pts_dev);
+        TCB_LAUNCHED(ctx);
+    }
+    return TCB_OK;
+}
+
+extern "C" int tcb_pillar_decorate(tcb_ctx* ctx, const float* voxels_dev, const int* coords_dev, const int* num_pts_dev,
+                                   const int* m_dev, int m_max, int max_pts, int nfeat, const double vsize[3],
+                                   const double range_min[3], float* out_dev, void* stream) {
+    TCB_CHECK_CTX(ctx);
+    TCB_REQUIRE(ctx, voxels_dev && coords_dev && num_pts_dev && out_dev && vsize && range_min, "tcb_pillar_decorate: null argument");
+    TCB_REQUIRE(ctx, m_max >= 0 && max_pts >= 1 && nfeat >= 3, "tcb_pillar_decorate: bad shape");
+    if (m_max == 0) return TCB_OK;
+    // offsets exactly as PillarVFE.__init__ computes them (pillar_vfe.py:76-81): Python doubles, used as f32 scalars
+    const float vx = (float)vsize[0], vy = (float)vsize[1], vz = (float)vsize[2];
+    const float xo = (float)(vsize[0] / 2 + range_min[0]), yo = (float)(vsize[1] / 2 + range_min[1]), zo = (float)(vsize[2] / 2 + range_min[2]);
+    pillar_decorate_kernel<<<tcb_div_up((long long)m_max * 32, 256), 256, 0, (cudaStream_t)stream>>>(
+        voxels_dev, coords_dev, num_pts_dev, m_dev, m_max, max_pts, nfeat, vx, vy, vz, xo, yo, zo, out_dev);
+    TCB_LAUNCHED(ctx);
+    return TCB_OK;
+}

@@ -13,15 +13,13 @@
 namespace {
 
 constexpr int NMS_THREADS = 1024;
-constexpr int CHUNK = 256;          // candidates resolved per greedy round
 constexpr int SORT_SMEM_CAP = 4096; // entries sorted in shared memory; larger sets sort in global scratch
 constexpr int MAX_DET_CAP = 1024;
 
-struct SortEnt {
-    unsigned long long key;  // f64 score bits (scores are > conf_thres >= 0, so bit order == numeric order)
-    unsigned row;            // row index inside the image: the deterministic tie-break (lower first)
-    unsigned slot;           // position in the unordered candidate arrays
-};
+// Sort record, stored as two arrays so a compare touches 8 bytes and only a swap (or a tie) touches the rest:
+//   key  : f64 score bits (scores are > conf_thres >= 0, so bit order == numeric order)
+//   meta : x = row index inside the image (the deterministic tie-break, lower first), y = slot in the candidate arrays
+struct SortEnt { unsigned long long key; uint2 meta; };  // 16 bytes per slot of sort scratch
 
 struct ClassMask { unsigned long long w[4]; };  // whitelist for classes 0..255
 
@@ -46,32 +44,26 @@ __global__ void __launch_bounds__(256) yolo_filter_kernel(
     const float* __restrict__ pred, int B, int N, int nc, double conf_thres, int use_filter, ClassMask cmask,
     double* __restrict__ c_score, float4* __restrict__ c_box, int2* __restrict__ c_meta,
     int* __restrict__ c_count, int* __restrict__ xc_count) {
+    // grid: x = warps striding over the 32-row groups of one image, y = image (no index division needed)
     const int lane = threadIdx.x & 31;
-    const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    const int warp_in_img = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int nwarps = (gridDim.x * blockDim.x) >> 5;
     const int stride = 5 + nc;
-    const long long groups_per_img = (N + 31) / 32;
-    const long long total_groups = groups_per_img * B;
+    const int groups = (N + 31) / 32;
+    const int b = blockIdx.y;
+    const float* base = pred + ((long long)b * N) * stride;
 
-    for (long long g0 = warp_global * FILTER_UNROLL; g0 < total_groups; g0 += nwarps * FILTER_UNROLL) {
+    for (int g0 = warp_in_img * FILTER_UNROLL; g0 < groups; g0 += nwarps * FILTER_UNROLL) {
         float obj[FILTER_UNROLL];
 #pragma unroll
         for (int u = 0; u < FILTER_UNROLL; u++) {  // all objectness loads first
-            const long long g = g0 + u;
-            obj[u] = -1.f;
-            if (g < total_groups) {
-                const int b = (int)(g / groups_per_img);
-                const int row = (int)(g - (long long)b * groups_per_img) * 32 + lane;
-                if (row < N) obj[u] = __ldg(pred + ((long long)b * N + row) * stride + 4);
-            }
+            const int row = (g0 + u) * 32 + lane;
+            obj[u] = (row < N) ? __ldg(base + (long long)row * stride + 4) : -1.f;
         }
 #pragma unroll
         for (int u = 0; u < FILTER_UNROLL; u++) {
-            const long long g = g0 + u;
-            if (g >= total_groups) break;
-            const int b = (int)(g / groups_per_img);
-            const int row0 = (int)(g - (long long)b * groups_per_img) * 32;
-            const float* base = pred + ((long long)b * N) * stride;
+            const int row0 = (g0 + u) * 32;
+            if (row0 >= N) break;
             const bool pass = (double)obj[u] > conf_thres;  // padding lanes hold -1 and conf_thres >= 0
             unsigned m = __ballot_sync(0xffffffffu, pass);
             if (m == 0) continue;
@@ -138,20 +130,24 @@ __global__ void __launch_bounds__(256) yolo_filter_kernel(
 // ---------------------------------------------------------------------------------------------
 // Pass 2: per-image ordering + greedy NMS.
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ bool ent_before(const SortEnt& a, const SortEnt& b) {
-    return a.key > b.key || (a.key == b.key && a.row < b.row);
-}
-
-// Bitonic sort of npad (power of two) entries by the whole CTA; buf may be shared or global memory.
-__device__ void bitonic_sort(SortEnt* buf, int npad) {
+// Bitonic sort of npad (power of two) records by the whole CTA into (key descending, row ascending) order;
+// one compare-exchange per thread and stage (thread p owns the pair i < i|j). Inlined per call site so that
+// shared/global loads are typed.
+__device__ __forceinline__ void bitonic_sort(unsigned long long* keys, uint2* meta, int npad) {
+    const int npairs = npad >> 1;
     for (int k = 2; k <= npad; k <<= 1) {
         for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int i = threadIdx.x; i < npad; i += blockDim.x) {
-                const int ixj = i ^ j;
-                if (ixj > i) {
-                    SortEnt a = buf[i], b = buf[ixj];
-                    const bool up = ((i & k) == 0);
-                    if (up ? ent_before(b, a) : ent_before(a, b)) { buf[i] = b; buf[ixj] = a; }
+            for (int p = threadIdx.x; p < npairs; p += blockDim.x) {
+                const int i = ((p & ~(j - 1)) << 1) | (p & (j - 1));
+                const int q = i | j;
+                const unsigned long long ka = keys[i], kb = keys[q];
+                const bool up = ((i & k) == 0);
+                bool swap;
+                if (ka != kb) swap = up ? (kb > ka) : (ka > kb);   // "before" = larger key
+                else { const unsigned ra = meta[i].x, rb = meta[q].x; swap = up ? (rb < ra) : (ra < rb); }
+                if (swap) {
+                    const uint2 ma = meta[i], mb = meta[q];
+                    keys[i] = kb; keys[q] = ka; meta[i] = mb; meta[q] = ma;
                 }
             }
             __syncthreads();
@@ -159,28 +155,154 @@ __device__ void bitonic_sort(SortEnt* buf, int npad) {
     }
 }
 
-// torchvision/csrc/ops/cpu/nms_kernel.cpp arithmetic in double: suppress iff inter/(ai+aj-inter) > thr.
-__device__ __forceinline__ bool iou_gt(double ax1, double ay1, double ax2, double ay2, double aarea,
-                                       double bx1, double by1, double bx2, double by2, double barea, double thr) {
-    const double xx1 = fmax(ax1, bx1), xx2 = fmin(ax2, bx2);
-    const double w = fmax(0.0, xx2 - xx1);
-    if (w == 0.0) return false;  // inter == 0 -> ovr is 0 (or NaN): never > thr for thr >= 0
-    const double yy1 = fmax(ay1, by1), yy2 = fmin(ay2, by2);
-    const double h = fmax(0.0, yy2 - yy1);
-    if (h == 0.0) return false;
-    const double inter = w * h;
-    const double ovr = inter / (aarea + barea - inter);
-    return ovr > thr;
+// Register-resident bitonic sort for up to 1024*E records (E per thread, record i = tid + u*1024):
+// strides below 32 are exchanged with warp shuffles, strides >= 1024 inside the thread, and only the
+// strides in between go through shared memory (as a mailbox: every thread rewrites only its own record).
+__device__ __forceinline__ bool rec_before(unsigned long long ka, unsigned ra, unsigned long long kb, unsigned rb) {
+    return ka > kb || (ka == kb && ra < rb);
 }
 
+template <int E>
+__device__ __forceinline__ void bitonic_sort_regs(unsigned long long* skeys, uint2* smeta, int n) {
+    const int tid = threadIdx.x;
+    unsigned long long k[E];
+    uint2 m[E];
+#pragma unroll
+    for (int u = 0; u < E; u++) {
+        const int i = tid + u * 1024;
+        k[u] = skeys[i]; m[u] = smeta[i];
+    }
+    for (int kk = 2; kk <= 1024 * E; kk <<= 1) {
+        for (int j = kk >> 1; j > 0; j >>= 1) {
+            if (j >= 1024) {
+                const int du = j >> 10;
+#pragma unroll
+                for (int dc = 1; dc < E; dc <<= 1) {  // compile-time partner distance keeps k[], m[] in registers
+                    if (du != dc) continue;
+#pragma unroll
+                    for (int u = 0; u < E; u++) {
+                        if ((u & dc) == 0) {
+                            const int v = u | dc;
+                            const bool up = (((tid + u * 1024) & kk) == 0);
+                            const bool ub = rec_before(k[u], m[u].x, k[v], m[v].x);
+                            if (ub != up) {  // ascending block wants the "before" record at the lower index
+                                const unsigned long long tk = k[u]; k[u] = k[v]; k[v] = tk;
+                                const uint2 tm = m[u]; m[u] = m[v]; m[v] = tm;
+                            }
+                        }
+                    }
+                }
+            } else {
+                if (j >= 32) {
+#pragma unroll
+                    for (int u = 0; u < E; u++) { const int i = tid + u * 1024; skeys[i] = k[u]; smeta[i] = m[u]; }
+                    __syncthreads();
+                }
+#pragma unroll
+                for (int u = 0; u < E; u++) {
+                    const int i = tid + u * 1024;
+                    unsigned long long pk;
+                    uint2 pm;
+                    if (j >= 32) {
+                        pk = skeys[i ^ j]; pm = smeta[i ^ j];
+                    } else {
+                        pk = __shfl_xor_sync(0xffffffffu, k[u], j);
+                        pm.x = __shfl_xor_sync(0xffffffffu, m[u].x, j);
+                        pm.y = __shfl_xor_sync(0xffffffffu, m[u].y, j);
+                    }
+                    const bool lower = ((i & j) == 0), up = ((i & kk) == 0);
+                    const bool want_before = (lower == up);
+                    if (rec_before(k[u], m[u].x, pk, pm.x) != want_before) { k[u] = pk; m[u] = pm; }
+                }
+                if (j >= 32) __syncthreads();
+            }
+        }
+    }
+#pragma unroll
+    for (int u = 0; u < E; u++) { const int i = tid + u * 1024; skeys[i] = k[u]; smeta[i] = m[u]; }
+    __syncthreads();
+}
+
+constexpr int ROUND = 1024;      // candidates examined per greedy round (one per thread)
+constexpr int ACAP = 64;         // survivors of a round resolved against each other at once (one mask word per row)
+constexpr int RESIDENT = 4096;   // sorted candidates kept in shared memory (== SORT_SMEM_CAP: the arrays reuse the sort buffer)
+constexpr int MAX_NMS_CAP = 65536;  // size of the resolved-candidate bitmap
+constexpr int SMALL_BIT = 1 << 30;
+
+// Offset box in double precision as the reference's float64 tensors hold it: x1,y1,x2,y2 (+cls*off) and area.
+struct DBox { double x1, y1, x2, y2, area; };
+
+__device__ __forceinline__ DBox make_dbox(const float4 b, const int cls, const double off) {
+    const double o = (double)(cls & (SMALL_BIT - 1)) * off;
+    DBox d;
+    d.x1 = (double)b.x + o; d.y1 = (double)b.y + o; d.x2 = (double)b.z + o; d.y2 = (double)b.w + o;
+    d.area = (d.x2 - d.x1) * (d.y2 - d.y1);
+    return d;
+}
+
+// fl(inter/denom) > thr, without the division unless the quotient is within a few ulp of thr:
+// r = fma(-thr, denom, inter) has the exact sign of inter - thr*denom; |r| > 4e-16*denom puts the real
+// quotient more than 2 ulp away from thr (quotients are <= 1), so rounding cannot change the outcome.
+__device__ __forceinline__ bool iou_exceeds(const DBox& a, const DBox& b, const double thr) {
+    const double w = fmax(0.0, fmin(a.x2, b.x2) - fmax(a.x1, b.x1));
+    if (w == 0.0) return false;
+    const double h = fmax(0.0, fmin(a.y2, b.y2) - fmax(a.y1, b.y1));
+    if (h == 0.0) return false;
+    const double inter = w * h;
+    const double denom = a.area + b.area - inter;
+    if (denom > 0.0) {
+        const double r = __fma_rn(-thr, denom, inter), tol = 4e-16 * denom;
+        if (r > tol) return true;
+        if (r < -tol) return false;
+    }
+    return inter / denom > thr;
+}
+
+// Can the earlier (higher-score) box `a` be ruled out as a suppressor of `b` without float64 work?
+// torchvision's NMS (torchvision/csrc/ops/cpu/nms_kernel.cpp) runs on boxes offset by class*off
+// (yolov5_postprocess.py:106-108); inter == 0 gives ovr == 0 (or NaN), never > thr for thr >= 0. Exact shortcuts:
+//   same class  : offsets are equal and x -> fl(x+off) is monotonic, so min(x2) <= max(x1) in f32 implies w == 0;
+//   other class : if every coordinate of both boxes is inside (-2048, 2048) the 4096-spaced offsets cannot overlap.
+__device__ __forceinline__ bool cannot_overlap(const float4 a, const int ca, const float4 b, const int cb, const double off) {
+    const int cla = ca & (SMALL_BIT - 1), clb = cb & (SMALL_BIT - 1);
+    if (off == 0.0 || cla == clb) return fminf(a.z, b.z) <= fmaxf(a.x, b.x) || fminf(a.w, b.w) <= fmaxf(a.y, b.y);
+    return (ca & cb & SMALL_BIT) != 0;
+}
+
+// Same-class (or class-agnostic) pairs: decide fl64(inter/denom) > thr from a float32 evaluation when it is not
+// close. Both evaluations start from the same f32 coordinates; the f32 one carries a relative error < 2e-6
+// (each of its ~10 operations rounds to 2^-24) and the reference's f64 one < 1e-9 (offset rounding), so a
+// float32 margin of 2e-5*denom on inter - thr*denom is decisive with a 10x reserve. Returns 1 = suppress,
+// 0 = keep, -1 = too close: evaluate in float64 exactly like the reference.
+__device__ __forceinline__ int iou32_decide(const float4 a, const float4 b, const float thr) {
+    const float w = fminf(a.z, b.z) - fmaxf(a.x, b.x), h = fminf(a.w, b.w) - fmaxf(a.y, b.y);  // > 0: cannot_overlap was false
+    const float inter = w * h;
+    const float denom = (a.z - a.x) * (a.w - a.y) + (b.z - b.x) * (b.w - b.y) - inter;
+    if (!(denom > 0.f) || !(inter > 0.f)) return -1;
+    const float r = inter - thr * denom, tol = 2e-5f * denom;
+    return r > tol ? 1 : (r < -tol ? 0 : -1);
+}
+
+#ifdef TCB_NMS_PROFILE
+__device__ long long g_nms_prof[8];
+#define PROF_T(k) do { __syncthreads(); if (blockIdx.x == 0 && threadIdx.x == 0) { long long t_ = clock64(); atomicAdd((unsigned long long*)&g_nms_prof[k], (unsigned long long)(t_ - prof_t0)); prof_t0 = t_; } } while (0)
+#else
+#define PROF_T(k) do {} while (0)
+#endif
+
 struct NmsShared {
-    double kx1[MAX_DET_CAP], ky1[MAX_DET_CAP], kx2[MAX_DET_CAP], ky2[MAX_DET_CAP], karea[MAX_DET_CAP];
-    double cx1[CHUNK], cy1[CHUNK], cx2[CHUNK], cy2[CHUNK], carea[CHUNK];
-    unsigned long long mask[CHUNK][CHUNK / 64];
-    int alive[CHUNK];
-    unsigned kslot[MAX_DET_CAP];
-    int nkept;
+    float4 kbox[MAX_DET_CAP]; int kcls[MAX_DET_CAP]; unsigned kslot[MAX_DET_CAP];  // kept so far
+    DBox kd[MAX_DET_CAP];                  // kept boxes, class-offset, float64 (what the reference's NMS sees)
+    unsigned resolved[MAX_NMS_CAP / 32];   // bit c: sorted candidate c is kept or suppressed
+    unsigned long long mask[ACAP];         // bit j of row i: survivor i suppresses survivor j (i < j)
+    int aidx[ACAP];                        // sorted positions of this round's survivors, in score order
+    int knew[ACAP];                        // survivors the sweep kept
+    int warp_cnt[32];
+    int nkept, next_pos, a_total;
 };
+// After the sort the 64 KB sort buffer is reused for the sorted candidates themselves.
+struct CandShared { float4 box[RESIDENT]; int cls[RESIDENT]; unsigned slot[RESIDENT]; };
+static_assert(sizeof(CandShared) <= sizeof(SortEnt) * SORT_SMEM_CAP + 32 * 1024, "candidate arrays overflow their region");
 
 __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
     int N, const double* __restrict__ c_score, const float4* __restrict__ c_box, const int2* __restrict__ c_meta,
@@ -189,126 +311,230 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
     double* __restrict__ out, int* __restrict__ out_count) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     NmsShared& S = *reinterpret_cast<NmsShared*>(smem_raw);
-    SortEnt* ssort = reinterpret_cast<SortEnt*>(smem_raw + sizeof(NmsShared));
+    unsigned long long* skeys = reinterpret_cast<unsigned long long*>(smem_raw + sizeof(NmsShared));
+    uint2* smeta = reinterpret_cast<uint2*>(skeys + SORT_SMEM_CAP);
+    CandShared& C = *reinterpret_cast<CandShared*>(smem_raw + sizeof(NmsShared));
 
-    const int b = blockIdx.x, tid = threadIdx.x;
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+#ifdef TCB_NMS_PROFILE
+    long long prof_t0 = clock64();
+#endif
     int n = min(c_count[b], N);
     const long long cbase = (long long)b * N;
     if (tid == 0) S.nkept = 0;
+    for (int i = tid; i < MAX_NMS_CAP / 32; i += NMS_THREADS) S.resolved[i] = 0u;
 
     // ---- order candidates: score descending, row ascending ------------------------------------
     int npad = 1;
     while (npad < n) npad <<= 1;
-    SortEnt* buf = (npad <= SORT_SMEM_CAP) ? ssort : (gsort + (long long)b * gsort_stride);
-    for (int i = tid; i < npad; i += NMS_THREADS) {
-        SortEnt e;
+    const bool sort_in_smem = npad <= SORT_SMEM_CAP;
+    // global sort scratch of image b: npad keys followed by npad metas
+    unsigned long long* gkeys = reinterpret_cast<unsigned long long*>(gsort + (long long)b * gsort_stride);
+    uint2* gmeta = reinterpret_cast<uint2*>(gkeys + gsort_stride);
+    unsigned long long* keys = sort_in_smem ? skeys : gkeys;
+    uint2* meta = sort_in_smem ? smeta : gmeta;
+    const int nfill = sort_in_smem ? (npad <= 1024 ? 1024 : (npad <= 2048 ? 2048 : 4096)) : npad;
+    for (int i = tid; i < nfill; i += NMS_THREADS) {
         if (i < n) {
-            e.key = (unsigned long long)__double_as_longlong(c_score[cbase + i]);
-            e.row = (unsigned)c_meta[cbase + i].x;
-            e.slot = (unsigned)i;
+            keys[i] = (unsigned long long)__double_as_longlong(c_score[cbase + i]);
+            meta[i] = make_uint2((unsigned)c_meta[cbase + i].x, (unsigned)i);
         } else {
-            e.key = 0ull; e.row = 0xffffffffu; e.slot = 0u;
+            keys[i] = 0ull; meta[i] = make_uint2(0xffffffffu, 0u);
         }
-        buf[i] = e;
     }
     __syncthreads();
-    bitonic_sort(buf, npad);
+    PROF_T(0);
+    if (sort_in_smem) {
+        if (nfill == 1024) bitonic_sort_regs<1>(skeys, smeta, n);
+        else if (nfill == 2048) bitonic_sort_regs<2>(skeys, smeta, n);
+        else bitonic_sort_regs<4>(skeys, smeta, n);
+    } else {
+        bitonic_sort(gkeys, gmeta, npad);
+    }
+    PROF_T(1);
     if (n > max_nms) n = max_nms;
 
-    // ---- greedy NMS, CHUNK candidates per round -------------------------------------------------
-    double* orow = out + (long long)b * max_det * 6;
-    for (int c0 = 0; c0 < n; c0 += CHUNK) {
-        const int cn = min(CHUNK, n - c0);
-        if (tid < CHUNK) {
-            int alive = 0;
+    // ---- make the sorted candidates resident: box, class (+SMALL flag), slot ----------------------
+    // resident mode (n <= RESIDENT): C.*[c] is sorted candidate c, loaded once (over the dead sort buffer);
+    // streaming mode: C.*[t] is candidate pos+t of the current round, gathered every round.
+    const bool resident = n <= RESIDENT && sort_in_smem;
+    if (resident) {
+        unsigned myslot[RESIDENT / NMS_THREADS];
+#pragma unroll
+        for (int u = 0; u < RESIDENT / NMS_THREADS; u++) {
+            const int c = tid + u * NMS_THREADS;
+            myslot[u] = c < n ? smeta[c].y : 0u;
+        }
+        __syncthreads();  // every slot is in registers; the sort buffer may now be overwritten
+#pragma unroll
+        for (int u = 0; u < RESIDENT / NMS_THREADS; u++) {
+            const int c = tid + u * NMS_THREADS;
+            if (c < n) {
+                const float4 bx = c_box[cbase + myslot[u]];
+                int cl = c_meta[cbase + myslot[u]].y;
+                if (fabsf(bx.x) < 2048.f && fabsf(bx.y) < 2048.f && fabsf(bx.z) < 2048.f && fabsf(bx.w) < 2048.f) cl |= SMALL_BIT;
+                C.box[c] = bx; C.cls[c] = cl; C.slot[c] = myslot[u];
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- greedy NMS in rounds ---------------------------------------------------------------------
+    const float thr32 = (float)iou_thres;
+    int pos = 0, prev_end = 0, nk_prev = 0;
+    while (pos < n) {
+        const int cn = min(ROUND, n - pos);
+        const int c = pos + tid;               // sorted position of this thread's candidate
+        const int ci = resident ? c : tid;     // where it lives in C
+        if (!resident) {
             if (tid < cn) {
-                const unsigned slot = buf[c0 + tid].slot;
+                const unsigned slot = meta[c].y;
                 const float4 bx = c_box[cbase + slot];
-                const double off = (double)c_meta[cbase + slot].y * class_offset;
-                const double x1 = (double)bx.x + off, y1 = (double)bx.y + off;
-                const double x2 = (double)bx.z + off, y2 = (double)bx.w + off;
-                S.cx1[tid] = x1; S.cy1[tid] = y1; S.cx2[tid] = x2; S.cy2[tid] = y2;
-                S.carea[tid] = (x2 - x1) * (y2 - y1);
-                alive = 1;
+                int cl = c_meta[cbase + slot].y;
+                if (fabsf(bx.x) < 2048.f && fabsf(bx.y) < 2048.f && fabsf(bx.z) < 2048.f && fabsf(bx.w) < 2048.f) cl |= SMALL_BIT;
+                C.box[tid] = bx; C.cls[tid] = cl; C.slot[tid] = slot;
             }
-            S.alive[tid] = alive;
+            __syncthreads();
         }
-        __syncthreads();
+        PROF_T(2);
+        // (1) against the boxes kept since this candidate was last examined
         const int nk = S.nkept;
-        const int ci = tid & (CHUNK - 1), part = tid >> 8;  // 4 threads share one candidate
-        // (1) against everything kept in earlier rounds
-        if (ci < cn) {
-            const double x1 = S.cx1[ci], y1 = S.cy1[ci], x2 = S.cx2[ci], y2 = S.cy2[ci], ar = S.carea[ci];
-            bool dead = false;
-            for (int k = part; k < nk && !dead; k += NMS_THREADS / CHUNK)
-                dead = iou_gt(S.kx1[k], S.ky1[k], S.kx2[k], S.ky2[k], S.karea[k], x1, y1, x2, y2, ar, iou_thres);
-            if (dead) S.alive[ci] = 0;
+        bool alive = tid < cn && !((S.resolved[c >> 5] >> (c & 31)) & 1u);
+        if (alive) {
+            const float4 bx = C.box[ci];
+            const int cl = C.cls[ci];
+            DBox dbx;
+            bool have_d = false;
+            for (int k = (c < prev_end) ? nk_prev : 0; k < nk; k++) {
+                const float4 kb = S.kbox[k];
+                const int kc = S.kcls[k];
+                if (cannot_overlap(kb, kc, bx, cl, class_offset)) continue;
+                int dec = -1;
+                if (class_offset == 0.0 || ((kc ^ cl) & (SMALL_BIT - 1)) == 0) dec = iou32_decide(kb, bx, thr32);
+                if (dec < 0) {
+                    if (!have_d) { dbx = make_dbox(bx, cl, class_offset); have_d = true; }
+                    dec = iou_exceeds(S.kd[k], dbx, iou_thres) ? 1 : 0;
+                }
+                if (dec) { alive = false; break; }
+            }
+            if (!alive) atomicOr(&S.resolved[c >> 5], 1u << (c & 31));
+        }
+        // ordered compaction of the survivors
+        const unsigned bal = __ballot_sync(0xffffffffu, alive);
+        if (lane == 0) S.warp_cnt[warp] = __popc(bal);
+        __syncthreads();
+        if (warp == 0) {
+            int w = S.warp_cnt[lane];
+#pragma unroll
+            for (int k = 1; k < 32; k <<= 1) { const int t = __shfl_up_sync(0xffffffffu, w, k); if (lane >= k) w += t; }
+            S.warp_cnt[lane] = w;
+            if (lane == 31) { S.a_total = w; S.next_pos = pos + cn; }
         }
         __syncthreads();
-        // (2) suppression bitmask inside the chunk: bit j of row i set iff i precedes j and iou(i,j) > thr
+        const int rank = (warp ? S.warp_cnt[warp - 1] : 0) + __popc(bal & ((1u << lane) - 1));
+        if (alive) {
+            if (rank < ACAP) S.aidx[rank] = c;
+            else if (rank == ACAP) S.next_pos = c;  // survivors beyond ACAP wait for the next round
+        }
+        __syncthreads();
+        const int A = min(S.a_total, ACAP);
+        PROF_T(3);
+        // (2) suppression mask among the A survivors: 16 threads per row, 4 columns each
         {
+            const int ri = tid >> 4, l16 = tid & 15;
             unsigned long long bits = 0ull;
-            if (ci < cn && S.alive[ci]) {
-                const double x1 = S.cx1[ci], y1 = S.cy1[ci], x2 = S.cx2[ci], y2 = S.cy2[ci], ar = S.carea[ci];
-                const int j0 = part * 64;
-                for (int jj = 0; jj < 64; jj++) {
-                    const int j = j0 + jj;
-                    if (j > ci && j < cn && S.alive[j] &&
-                        iou_gt(x1, y1, x2, y2, ar, S.cx1[j], S.cy1[j], S.cx2[j], S.cy2[j], S.carea[j], iou_thres))
-                        bits |= 1ull << jj;
+            if (ri < A) {
+                const int pi = resident ? S.aidx[ri] : S.aidx[ri] - pos;
+                const float4 bi = C.box[pi];
+                const int cli = C.cls[pi];
+                DBox di;
+                bool have_d = false;
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    const int j = l16 * 4 + q;
+                    if (j > ri && j < A) {
+                        const int pj = resident ? S.aidx[j] : S.aidx[j] - pos;
+                        const float4 bj = C.box[pj];
+                        const int clj = C.cls[pj];
+                        if (!cannot_overlap(bi, cli, bj, clj, class_offset)) {
+                            int dec = -1;
+                            if (class_offset == 0.0 || ((cli ^ clj) & (SMALL_BIT - 1)) == 0) dec = iou32_decide(bi, bj, thr32);
+                            if (dec < 0) {
+                                if (!have_d) { di = make_dbox(bi, cli, class_offset); have_d = true; }
+                                dec = iou_exceeds(di, make_dbox(bj, clj, class_offset), iou_thres) ? 1 : 0;
+                            }
+                            if (dec) bits |= 1ull << j;
+                        }
+                    }
                 }
             }
-            S.mask[ci][part] = bits;
+#pragma unroll
+            for (int sft = 1; sft < 16; sft <<= 1) bits |= __shfl_xor_sync(0xffffffffu, bits, sft);
+            if (l16 == 0 && ri < ACAP) S.mask[ri] = bits;
         }
         __syncthreads();
-        // (3) serial sweep by one warp, hopping from kept box to kept box (shared memory only: the
-        //     output rows are written by the whole CTA after the last round)
-        if (tid < 32) {
-            unsigned long long avail[CHUNK / 64];
-#pragma unroll
-            for (int w = 0; w < CHUNK / 64; w++) {
-                const unsigned lo = __ballot_sync(0xffffffffu, S.alive[w * 64 + tid] != 0);
-                const unsigned hi = __ballot_sync(0xffffffffu, S.alive[w * 64 + 32 + tid] != 0);
-                avail[w] = ((unsigned long long)hi << 32) | lo;
-            }
+        PROF_T(4);
+        // (3) serial sweep: hop from kept survivor to kept survivor
+        if (tid == 0) {
+            unsigned long long avail = A >= 64 ? ~0ull : ((1ull << A) - 1);
             int kept = nk;
-            while (kept < max_det) {
-                int i = -1;
-#pragma unroll
-                for (int w = CHUNK / 64 - 1; w >= 0; w--)
-                    if (avail[w]) i = w * 64 + __ffsll((long long)avail[w]) - 1;
-                if (i < 0) break;
-#pragma unroll
-                for (int w = 0; w < CHUNK / 64; w++) {
-                    unsigned long long mrow = S.mask[i][w];
-                    if (w == (i >> 6)) mrow |= 1ull << (i & 63);
-                    avail[w] &= ~mrow;
-                }
-                if (tid == 0) {
-                    S.kx1[kept] = S.cx1[i]; S.ky1[kept] = S.cy1[i]; S.kx2[kept] = S.cx2[i]; S.ky2[kept] = S.cy2[i];
-                    S.karea[kept] = S.carea[i];
-                    S.kslot[kept] = buf[c0 + i].slot;
-                }
+            while (kept < max_det && avail) {
+                const int i = __ffsll((long long)avail) - 1;
+                avail &= ~(S.mask[i] | (1ull << i));
+                S.knew[kept - nk] = i;
                 kept++;
             }
-            if (tid == 0) S.nkept = kept;
+            S.nkept = kept;
         }
         __syncthreads();
-        if (S.nkept >= max_det) break;
+        const int nk_new = S.nkept;
+        if (tid < nk_new - nk) {  // append the kept survivors
+            const int cs = S.aidx[S.knew[tid]];
+            const int pi = resident ? cs : cs - pos;
+            const float4 bx = C.box[pi];
+            const int cl = C.cls[pi];
+            S.kbox[nk + tid] = bx; S.kcls[nk + tid] = cl; S.kslot[nk + tid] = C.slot[pi];
+            S.kd[nk + tid] = make_dbox(bx, cl, class_offset);
+        }
+        if (tid < A) { const int cs = S.aidx[tid]; atomicOr(&S.resolved[cs >> 5], 1u << (cs & 31)); }  // all A are decided now
+        prev_end = pos + cn; nk_prev = nk;
+        const int np = S.next_pos;
+        __syncthreads();
+        PROF_T(5);
+#ifdef TCB_NMS_PROFILE
+        if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd((unsigned long long*)&g_nms_prof[7], 1000000000ull);
+#endif
+        if (nk_new >= max_det) break;
+        pos = np;
     }
     __syncthreads();
     // ---- write the kept rows: [x1,y1,x2,y2 (f32 box widened), conf (f64), cls] -------------------------
+    double* orow = out + (long long)b * max_det * 6;
     const int nk_final = S.nkept;
     for (int k = tid; k < nk_final; k += NMS_THREADS) {
         const unsigned slot = S.kslot[k];
-        const float4 bx = c_box[cbase + slot];
+        const float4 bx = S.kbox[k];
         double* o = orow + (long long)k * 6;
         o[0] = (double)bx.x; o[1] = (double)bx.y; o[2] = (double)bx.z; o[3] = (double)bx.w;
         o[4] = c_score[cbase + slot];
-        o[5] = (double)c_meta[cbase + slot].y;
+        o[5] = (double)(S.kcls[k] & (SMALL_BIT - 1));
     }
-    if (tid == 0) out_count[b] = S.nkept;
+    if (tid == 0) out_count[b] = nk_final;
+    PROF_T(6);
+#ifdef TCB_NMS_PROFILE
+    if (blockIdx.x == 0 && threadIdx.x == 0) { atomicAdd((unsigned long long*)&g_nms_prof[7], (unsigned long long)nk_final * 1000000ull + (unsigned long long)n); }
+#endif
 }
+#ifdef TCB_NMS_PROFILE
+}  // namespace
+extern "C" void tcb_debug_nms_prof(long long* out8, int reset) {
+    cudaMemcpyFromSymbol(out8, g_nms_prof, sizeof(long long) * 8);
+    if (reset) { long long z[8] = {0}; cudaMemcpyToSymbol(g_nms_prof, z, sizeof(z)); }
+}
+namespace {
+#endif
+
+constexpr size_t NMS_SMEM_BYTES = sizeof(NmsShared) + (sizeof(CandShared) > sizeof(SortEnt) * SORT_SMEM_CAP ? sizeof(CandShared) : sizeof(SortEnt) * SORT_SMEM_CAP);
 
 size_t yolo_ws_bytes(int b, int n) {
     size_t per = (size_t)b * n;
@@ -337,6 +563,7 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
     TCB_REQUIRE(ctx, iou_thres >= 0.0 && iou_thres <= 1.0, "tcb_yolo_nms: Invalid IoU %g, valid values are between 0.0 and 1.0", iou_thres);
     TCB_REQUIRE(ctx, max_det >= 1 && max_nms >= 1, "tcb_yolo_nms: max_det and max_nms must be >= 1");
     if (max_det > MAX_DET_CAP) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_yolo_nms: max_det %d > compiled limit %d", max_det, MAX_DET_CAP);
+    if (max_nms > MAX_NMS_CAP) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_yolo_nms: max_nms %d > compiled limit %d", max_nms, MAX_NMS_CAP);
     TCB_REQUIRE(ctx, n_classes == 0 || classes_host, "tcb_yolo_nms: classes_host is null");
     cudaStream_t st = (cudaStream_t)stream;
     if (b == 0) return TCB_OK;
@@ -366,15 +593,17 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
     TCB_CUDA(ctx, cudaMemsetAsync(counts, 0, sizeof(int) * 2 * (size_t)b, st));
 
     if (n > 0) {
-        const long long groups = (long long)b * ((n + 31) / 32);
-        long long blocks = (groups + 7) / 8;
-        const long long cap = (long long)ctx->num_sms * 16;
-        if (blocks > cap) blocks = cap;
-        yolo_filter_kernel<<<(int)blocks, 256, 0, st>>>(pred_dev, b, n, nc, conf_thres, n_classes > 0, cm,
+        // 8 warps per CTA, FILTER_UNROLL 32-row groups per warp and pass; y = image
+        int bx = tcb_div_up((n + 31) / 32, 8 * FILTER_UNROLL);
+        const int cap = tcb_div_up(ctx->num_sms * 16, b);
+        if (bx > cap) bx = cap;
+        if (bx < 1) bx = 1;
+        TCB_REQUIRE(ctx, b <= 65535, "tcb_yolo_nms: batch %d > 65535", b);
+        yolo_filter_kernel<<<dim3(bx, b), 256, 0, st>>>(pred_dev, b, n, nc, conf_thres, n_classes > 0, cm,
                                                         c_score, c_box, c_meta, c_count, xc_count);
         TCB_LAUNCHED(ctx);
     }
-    const size_t smem = sizeof(NmsShared) + sizeof(SortEnt) * SORT_SMEM_CAP;
+    const size_t smem = NMS_SMEM_BYTES;
     TCB_CUDA(ctx, cudaFuncSetAttribute(yolo_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     yolo_nms_kernel<<<b, NMS_THREADS, smem, st>>>(n > 0 ? n : 1, c_score, c_box, c_meta, c_count, gsort, npad,
                                                   iou_thres, agnostic ? 0.0 : 4096.0, max_det, max_nms, out_dev, count_dev);
@@ -440,7 +669,7 @@ int static_scratch_for_current_device(unsigned char** out) {
         if (e != cudaSuccess || !p)
             return tcb_fail(nullptr, TCB_ERR_CUDA, "tcb_yolo_nms_static: cudaGetSymbolAddress -> %s", cudaGetErrorString(e));
         e = cudaFuncSetAttribute(yolo_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)(sizeof(NmsShared) + sizeof(SortEnt) * SORT_SMEM_CAP));
+                                 (int)NMS_SMEM_BYTES);
         if (e != cudaSuccess)
             return tcb_fail(nullptr, TCB_ERR_CUDA, "tcb_yolo_nms_static: cudaFuncSetAttribute -> %s", cudaGetErrorString(e));
         g_static_ptr[dev] = p;
@@ -466,6 +695,7 @@ extern "C" int tcb_yolo_nms_static(const float* pred_dev, int b, int n, int nc, 
     ST_REQUIRE(max_det >= 1 && max_nms >= 1, "tcb_yolo_nms_static: max_det and max_nms must be >= 1");
     ST_REQUIRE(n_classes == 0 || classes_host, "tcb_yolo_nms_static: classes_host is null");
     if (max_det > MAX_DET_CAP) return tcb_fail(nullptr, TCB_ERR_LIMIT, "tcb_yolo_nms_static: max_det %d > compiled limit %d", max_det, MAX_DET_CAP);
+    if (max_nms > MAX_NMS_CAP) return tcb_fail(nullptr, TCB_ERR_LIMIT, "tcb_yolo_nms_static: max_nms %d > compiled limit %d", max_nms, MAX_NMS_CAP);
     int npad = 1;
     while (npad < n) npad <<= 1;
     if (b > STATIC_MAX_B || (long long)b * n > STATIC_MAX_ROWS || (npad > SORT_SMEM_CAP && (long long)b * npad > STATIC_MAX_SORT))
@@ -500,14 +730,15 @@ extern "C" int tcb_yolo_nms_static(const float* pred_dev, int b, int n, int nc, 
         int dev = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-        const long long groups = (long long)b * ((n + 31) / 32);
-        long long blocks = (groups + 7) / 8;
-        if (blocks > (long long)num_sms * 16) blocks = (long long)num_sms * 16;
-        yolo_filter_kernel<<<(int)blocks, 256, 0, st>>>(pred_dev, b, n, nc, conf_thres, n_classes > 0, cm,
+        int bx = tcb_div_up((n + 31) / 32, 8 * FILTER_UNROLL);
+        const int cap = tcb_div_up(num_sms * 16, b);
+        if (bx > cap) bx = cap;
+        if (bx < 1) bx = 1;
+        yolo_filter_kernel<<<dim3(bx, b), 256, 0, st>>>(pred_dev, b, n, nc, conf_thres, n_classes > 0, cm,
                                                         c_score, c_box, c_meta, c_count, xc_count);
         ST_CUDA(cudaGetLastError());
     }
-    const size_t smem = sizeof(NmsShared) + sizeof(SortEnt) * SORT_SMEM_CAP;
+    const size_t smem = NMS_SMEM_BYTES;
     yolo_nms_kernel<<<b, NMS_THREADS, smem, st>>>(n > 0 ? n : 1, c_score, c_box, c_meta, c_count, gsort, npad,
                                                   iou_thres, agnostic ? 0.0 : 4096.0, max_det, max_nms, out_dev, count_dev);
     ST_CUDA(cudaGetLastError());

@@ -58,3 +58,44 @@ def yolo_output(batch, n, nc, seed, img=640, objects=40, rows_per_object=30, tie
     qc = rng.random((batch, n, nc)) < tie_frac
     out[:, :, 5:] = np.where(qc, np.round(out[:, :, 5:] * 1024) / 1024, out[:, :, 5:])
     return out.astype(np.float32)
+
+
+# ---- C4/C5 LiDAR sweeps ---------------------------------------------------------------------------
+def lidar_sweep(seed, beams=64, azimuths=1875, n_boxes=30, dropout=0.1, max_range=75.0, sensor_h=1.73, full_circle=False):
+    """Spinning-LiDAR-like sweep: each beam/azimuth ray hits the ground plane (z=-sensor_h) or one of
+    n_boxes random upright boxes; 10 % dropout. Returns (N,4) f32 x,y,z,intensity (C4: 64x1875=120k rays)."""
+    rng = np.random.default_rng(seed)
+    elev = np.deg2rad(np.linspace(-24.8, 2.0, beams))[:, None]
+    span = np.pi if not full_circle else 2 * np.pi
+    az = (np.linspace(-span / 2, span / 2, azimuths, endpoint=False) + rng.uniform(0, 1e-3))[None, :]
+    dx, dy, dz = np.cos(elev) * np.cos(az), np.cos(elev) * np.sin(az), np.sin(elev) * np.ones_like(az)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        t = np.where(dz < -1e-3, -sensor_h / dz, np.inf)
+    t = np.minimum(t, max_range)
+    # boxes: centre (cx, cy), half sizes, height
+    bc = rng.uniform([5, -30], [60, 30], (n_boxes, 2)) if not full_circle else rng.uniform(-45, 45, (n_boxes, 2))
+    bh = rng.uniform([0.8, 0.8], [2.5, 1.2], (n_boxes, 2))
+    bz = rng.uniform(1.4, 3.0, n_boxes)
+    for k in range(n_boxes):  # slab test in xy, then check the hit height
+        with np.errstate(divide="ignore", invalid="ignore"):
+            tx1, tx2 = (bc[k, 0] - bh[k, 0]) / dx, (bc[k, 0] + bh[k, 0]) / dx
+            ty1, ty2 = (bc[k, 1] - bh[k, 1]) / dy, (bc[k, 1] + bh[k, 1]) / dy
+        tn = np.maximum(np.minimum(tx1, tx2), np.minimum(ty1, ty2))
+        tf = np.minimum(np.maximum(tx1, tx2), np.maximum(ty1, ty2))
+        hit = (tn < tf) & (tn > 0) & (tn < t) & ((tn * dz) < (bz[k] - sensor_h))
+        t = np.where(hit, tn, t)
+    t = t * (1 + rng.normal(0, 0.002, t.shape))
+    keep = (rng.random(t.shape) > dropout) & np.isfinite(t)
+    pts = np.stack([t * dx, t * dy, t * dz, rng.random(t.shape)], axis=-1)[keep]
+    return pts.astype(np.float32)
+
+
+def lidar_multisweep(seed, sweeps=10, beams=32, azimuths=940):
+    """C5: 10 accumulated nuScenes-like sweeps (32 beams x 940 az ~ 30k each), 5th feature = time lag."""
+    out = []
+    for s in range(sweeps):
+        p = lidar_sweep(seed * 100 + s, beams=beams, azimuths=azimuths, n_boxes=25, dropout=0.0, max_range=60.0,
+                        sensor_h=1.84, full_circle=True)
+        p[:, 3] *= 255.0
+        out.append(np.concatenate([p, np.full((len(p), 1), 0.05 * s, np.float32)], axis=1))
+    return np.concatenate(out, axis=0).astype(np.float32)
