@@ -146,6 +146,70 @@ int tcb_pillar_decorate(tcb_ctx* ctx, const float* voxels_dev, const int* coords
                         const int* m_dev, int m_max, int max_pts, int nfeat, const double vsize[3],
                         const double range_min[3], float* out_dev, void* stream);
 
+/* ---- 3D detection postprocess ------------------------------------------------ */
+
+/* Rotated BEV IoU matrix out[n,m] of [x,y,z,dx,dy,dz,heading] boxes — boxes_iou_bev
+ * (OPCD/pcdet/ops/iou3d_nms/iou3d_nms_utils.py:12-36; kernel src/iou3d_nms_kernel.cu:104-265, CPU twin
+ * src/iou3d_cpu.cpp:232-252). Same float32 operation order as the reference. */
+int tcb_rotated_iou(tcb_ctx* ctx, const float* boxes_a_dev, int n, const float* boxes_b_dev, int m,
+                    float* out_dev, void* stream);
+
+/* class_agnostic_nms without the score cut (OPCD/pcdet/models/model_utils/model_nms_utils.py:13-19) =
+ * topk(min(pre_max, n)) by score + nms_gpu (iou3d_nms_utils.py:84-99, src/iou3d_nms.cpp:90-136,
+ * nms_kernel src/iou3d_nms_kernel.cu:267-311) + [:post_max]. Order: score descending, ties by lower
+ * index. keep_dev[post_max]: indices into the input, in kept order; count_dev[1].
+ * pre_max <= 4096, post_max <= 1024. */
+int tcb_rotated_nms(tcb_ctx* ctx, const float* boxes_dev, const float* scores_dev, int n, float thresh,
+                    int pre_max, int post_max, int* keep_dev, int* count_dev, void* stream);
+
+/*
+ * PointPillars anchor head post for one frame: analytic anchors (AnchorGenerator.generate_anchors,
+ * OPCD/pcdet/models/dense_heads/target_assigner/anchor_generator.py:17-60, align_center False, one size per
+ * class) + ResidualCoder.decode_torch (OPCD/pcdet/utils/box_coder_utils.py:45-77) + direction bins
+ * (generate_predicted_boxes, OPCD/pcdet/models/dense_heads/anchor_head_template.py:225-272, limit_period
+ * OPCD/pcdet/utils/common_utils.py:21-24) + post_processing (OPCD/pcdet/models/detectors/detector3d_template.py:
+ * 178-284: sigmoid, max over classes, label+1) + class_agnostic_nms(score_thresh, pre_max, nms_thresh, post_max).
+ * cls_dev [h,w,A*num_class], box_dev [h,w,A*7], dir_dev [h,w,A*num_dir_bins] (NULL = no direction classifier),
+ * A = num_class*num_rot anchors per location ordered (class, rotation); anchor_sizes [num_class*3] (dx,dy,dz),
+ * anchor_bottoms [num_class], anchor_rotations [num_class*num_rot] are host arrays.
+ * Outputs: boxes [post_max,7], scores [post_max], labels [post_max] int64 (1-based), count [1].
+ */
+size_t tcb_pp_anchor_post_workspace(int h, int w, int num_class, int num_rot);
+int tcb_pp_anchor_post(tcb_ctx* ctx, const float* cls_dev, const float* box_dev, const float* dir_dev, int h, int w,
+                       int num_class, int num_rot, const float anchor_range[6], const float* anchor_sizes,
+                       const float* anchor_bottoms, const float* anchor_rotations, float dir_offset,
+                       float dir_limit_offset, int num_dir_bins, float score_thresh, float nms_thresh, int pre_max,
+                       int post_max, float* out_boxes_dev, float* out_scores_dev, long long* out_labels_dev,
+                       int* out_count_dev, void* stream);
+
+/*
+ * CenterPoint head post for one frame: CenterHead.generate_predicted_boxes
+ * (OPCD/pcdet/models/dense_heads/center_head.py:253-304) = per head sigmoid + exp, _topk and
+ * decode_bbox_from_heatmap (OPCD/pcdet/models/model_utils/centernet_utils.py:136-216), centre-range and
+ * score > thresh mask, class id mapping, class_agnostic_nms(pre_max, nms_thresh, post_max); heads concatenated,
+ * labels + 1. Per-head tensors are NCHW planes of one frame: hm [c,h,w], center [2,h,w], center_z [1,h,w],
+ * dim [3,h,w] (log), rot [2,h,w] (cos, sin), vel [2,h,w] (vel_dev or its entries may be NULL).
+ * The `*_dev` arguments are HOST arrays of num_heads device pointers; head_num_class [num_heads] and
+ * class_id_map (concatenated per head, 0-based) are host arrays. Outputs: boxes [heads*post_max, 9],
+ * scores, labels int64 (1-based), count [1]. K <= 4096.
+ */
+size_t tcb_centerpoint_post_workspace(int num_heads, int pre_max, int post_max);
+int tcb_centerpoint_post(tcb_ctx* ctx, int num_heads, const float* const* hm_dev, const float* const* center_dev,
+                         const float* const* center_z_dev, const float* const* dim_dev, const float* const* rot_dev,
+                         const float* const* vel_dev, const int* head_num_class, const int* class_id_map, int h, int w,
+                         int feature_map_stride, const float voxel_size_xy[2], const float range_min_xy[2],
+                         const float limit_range[6], int k, float score_thresh, float nms_thresh, int pre_max, int post_max,
+                         float* out_boxes_dev, float* out_scores_dev, long long* out_labels_dev, int* out_count_dev,
+                         void* stream);
+
+/* Per-class score cut of PointPillarPostprocess.remove_low_score_nu / get_annotations_indices
+ * (clients/postprocess/detector_3d_postprocess.py:55-64,98-133): for each (class, threshold) group in the
+ * given order, the ascending indices i with labels[i] == class and scores[i] >= threshold, concatenated.
+ * labels int64, group tables are host arrays (<= 64 groups); out_idx_dev holds up to n_groups*n indices. */
+int tcb_class_score_filter(tcb_ctx* ctx, const long long* labels_dev, const float* scores_dev, int n, int n_groups,
+                           const int* group_class_host, const float* group_thresh_host, int* out_idx_dev,
+                           int* out_count_dev, void* stream);
+
 /*
  * tcb_yolo_nms without a context and without any allocation. No counterpart in the reference: it is
  * here for callers that are not allowed to allocate GPU memory — a plugin inside a host process that

@@ -96,6 +96,61 @@ def golden_pillar_vfe():
     save("pillar_vfe", **out)
 
 
+def golden_box3d():
+    """Reference 3D decode pieces run unmodified on CPU: ResidualCoder.decode_torch (box_coder_utils.py:45-77),
+    limit_period (common_utils.py:21-24), AnchorGenerator.generate_anchors (anchor_generator.py:17-60, with
+    Tensor.cuda() patched to a no-op: there is no GPU in the build container) and decode_bbox_from_heatmap
+    (centernet_utils.py:154-216) on tie-free heatmaps."""
+    rng = np.random.default_rng(77)
+    out = {}
+    bc = ref_harness.box_coder_utils()
+    anchors = torch.from_numpy(synth.random_boxes7(300, 1))
+    enc = torch.from_numpy(rng.normal(0, 0.4, (300, 7)).astype(np.float32))
+    out["dec_anchors"], out["dec_enc"] = anchors.numpy(), enc.numpy()
+    out["dec_out"] = bc.ResidualCoder().decode_torch(enc, anchors).numpy()
+    cu = ref_harness.common_utils()
+    val = torch.from_numpy(rng.uniform(-10, 10, 500).astype(np.float32))
+    out["lp_val"] = val.numpy()
+    out["lp_out"] = cu.limit_period(val - 0.78539, 0.0, 2 * np.pi / 2).numpy()
+    # anchors
+    ag = ref_harness.load_file("ref_anchor_generator", "utils/export_models/OpenPCDet/pcdet/models/dense_heads/target_assigner/anchor_generator.py")
+    cfg = [{"anchor_sizes": [[3.9, 1.6, 1.56]], "anchor_rotations": [0, 1.57], "anchor_bottom_heights": [-1.78]},
+           {"anchor_sizes": [[0.8, 0.6, 1.73]], "anchor_rotations": [0, 1.57], "anchor_bottom_heights": [-0.6]},
+           {"anchor_sizes": [[1.76, 0.6, 1.73]], "anchor_rotations": [0, 1.57], "anchor_bottom_heights": [-0.6]}]
+    pc_range = np.array([0, -39.68, -3, 69.12, 39.68, 1], np.float32)
+    saved = torch.Tensor.cuda
+    torch.Tensor.cuda = lambda self, *a, **k: self
+    try:
+        gen = ag.AnchorGenerator(anchor_range=pc_range, anchor_generator_config=cfg)
+        grid = [np.array([216, 248])] * 3
+        alist, _ = gen.generate_anchors(grid)
+    finally:
+        torch.Tensor.cuda = saved
+    full = torch.cat(alist, dim=-3).view(-1, 7).numpy()
+    assert full.shape == (321408, 7)
+    pick = rng.choice(full.shape[0], 4000, replace=False)
+    pick.sort()
+    out["anchor_idx"], out["anchor_val"] = pick.astype(np.int64), full[pick]
+    out["anchor_first_last"] = np.stack([full[0], full[-1]])
+    # centerpoint decode (K small, continuous logits -> no ties)
+    cn = ref_harness.centernet_utils()
+    h = w = 24
+    hm = torch.from_numpy(rng.normal(-3, 2, (1, 2, h, w)).astype(np.float32)).sigmoid()
+    parts = {"center": rng.uniform(0, 1, (1, 2, h, w)), "center_z": rng.normal(-1, .5, (1, 1, h, w)), "dim": np.exp(rng.normal(.7, .3, (1, 3, h, w))),
+             "rot_cos": rng.normal(0, 1, (1, 1, h, w)), "rot_sin": rng.normal(0, 1, (1, 1, h, w)), "vel": rng.normal(0, 2, (1, 2, h, w))}
+    parts = {k: torch.from_numpy(v.astype(np.float32)) for k, v in parts.items()}
+    limit = torch.tensor([-61.2, -61.2, -10.0, 61.2, 61.2, 10.0]).float()
+    res = cn.decode_bbox_from_heatmap(heatmap=hm, rot_cos=parts["rot_cos"], rot_sin=parts["rot_sin"], center=parts["center"],
+                                      center_z=parts["center_z"], dim=parts["dim"], vel=parts["vel"],
+                                      point_cloud_range=[-51.2, -51.2, -5.0, 51.2, 51.2, 3.0], voxel_size=[0.2, 0.2, 8], feature_map_stride=4,
+                                      K=40, score_thresh=0.1, post_center_limit_range=limit)[0]
+    out["cp_hm"] = hm.numpy()
+    for k, v in parts.items():
+        out["cp_" + k] = v.numpy()
+    out["cp_boxes"], out["cp_scores"], out["cp_labels"] = res["pred_boxes"].numpy(), res["pred_scores"].numpy(), res["pred_labels"].numpy()
+    save("box3d", **out)
+
+
 def main():
     assert ref_harness.available(), "reference not mounted"
     os.makedirs(GOLD, exist_ok=True)

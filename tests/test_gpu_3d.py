@@ -1,0 +1,143 @@
+"""GPU parity for the 3D postprocess through the C ABI. Keep lists, labels and counts must be identical;
+float boxes/scores within north_star's 1e-5 relative (transcendentals differ by ulps between libm and CUDA)."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import golden
+from oracle import box3d
+from triton_client_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+KITTI_ANCHORS = dict(anchor_range=[0, -39.68, -3, 69.12, 39.68, 1],
+                     anchor_sizes=[[3.9, 1.6, 1.56], [0.8, 0.6, 1.73], [1.76, 0.6, 1.73]],
+                     anchor_bottoms=[-1.78, -0.6, -0.6], anchor_rotations=[[0, 1.57]] * 3)
+NUSC = dict(point_cloud_range=[-51.2, -51.2, -5.0, 51.2, 51.2, 3.0], voxel_size=[0.2, 0.2, 8], feature_map_stride=4,
+            post_center_limit_range=[-61.2, -61.2, -10.0, 61.2, 61.2, 10.0])
+CLASS_MAP = [[0], [1, 2], [3, 4], [5], [6, 7], [8, 9]]
+
+
+def _close(a, b, rtol=1e-5, atol=1e-6):
+    np.testing.assert_allclose(np.asarray(a, np.float64), np.asarray(b, np.float64), rtol=rtol, atol=atol)
+
+
+def test_rotated_iou_matrix(engine):
+    a, b = synth.random_boxes7(500, 11, extent=25), synth.random_boxes7(600, 12, extent=25)
+    b[:50] = a[:50]
+    b[50:100, :2] += 0.02
+    want = box3d.boxes_iou_bev(a, b)
+    got = engine.rotated_iou(torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda()).cpu().numpy()
+    assert (want > 0).sum() > 5000
+    # sin/cos/atan2 differ by ulps; the polygon area is continuous in them
+    _close(got, want, rtol=1e-4, atol=2e-6)
+
+
+@pytest.mark.parametrize("n,thresh,pre,post", [(4096, 0.01, 4096, 500), (3000, 0.2, 1000, 83), (9000, 0.1, 4096, 500), (50, 0.5, 4096, 500), (1, 0.1, 10, 10)])
+def test_rotated_nms_keep_lists(engine, n, thresh, pre, post):
+    boxes = synth.random_boxes7(n, 20 + n, extent=60)
+    scores = np.round(np.random.default_rng(n).uniform(0, 1, n) * 4096) / 4096    # ties -> index order
+    scores = scores.astype(np.float32)
+    sel, _ = box3d.class_agnostic_nms(torch.from_numpy(scores), torch.from_numpy(boxes), thresh, pre, post)
+    keep, cnt = engine.rotated_nms(torch.from_numpy(boxes).cuda(), torch.from_numpy(scores).cuda(), thresh, pre, post)
+    k = int(cnt.item())
+    assert keep[:k].cpu().tolist() == sel.tolist()
+
+
+def test_rotated_nms_empty(engine):
+    keep, cnt = engine.rotated_nms(torch.zeros((0, 7)).cuda(), torch.zeros((0,)).cuda(), 0.1)
+    assert int(cnt.item()) == 0
+
+
+def _pp_gpu(engine, cls, box, dirp, **kw):
+    ob, osc, ol, cnt = engine.pp_anchor_post(torch.from_numpy(cls).cuda(), torch.from_numpy(box).cuda(),
+                                             torch.from_numpy(dirp).cuda() if dirp is not None else None, **kw)
+    k = int(cnt.item())
+    return ob[:k].cpu().numpy(), osc[:k].cpu().numpy(), ol[:k].cpu().numpy()
+
+
+def test_pp_golden_decode_pieces(engine):
+    """Anchors + ResidualCoder decode + direction bins against the reference's golden vectors: feed encodings for a
+    handful of anchors with huge scores so that every one of them comes back, then compare box by box."""
+    g = golden("box3d")
+    h, w = 248, 216
+    rng = np.random.default_rng(3)
+    cls = np.full((h, w, 18), -8.0, np.float32)
+    box = rng.normal(0, 0.3, (h, w, 42)).astype(np.float32)
+    idx = g["anchor_idx"][::40][:90]
+    flat_cls = cls.reshape(-1, 3)
+    flat_cls[idx, 0] = 8.0 - np.arange(len(idx)) / 64.0   # distinct, descending scores
+    far = box3d.generate_anchors((w, h), **{k: KITTI_ANCHORS[k] for k in ("anchor_range", "anchor_sizes", "anchor_rotations", "anchor_bottoms")})
+    gb, gs, gl = _pp_gpu(engine, cls, box, None, score_thresh=0.5, nms_thresh=1.0, **KITTI_ANCHORS)   # thresh 1.0: nothing suppressed
+    assert len(gs) == len(idx) and (gl == 1).all()
+    want = box3d.decode_torch(torch.from_numpy(box.reshape(-1, 7)[idx]), far[idx]).numpy()
+    _close(far[g["anchor_idx"]].numpy(), g["anchor_val"], rtol=1e-6, atol=1e-6)
+    _close(gb, want, rtol=1e-5, atol=1e-6)
+    assert np.array_equal(gb[:, [2, 6]], want[:, [2, 6]])   # no transcendental, no arange on these: bit-exact
+
+
+@pytest.mark.parametrize("seed", [4001, 4002])
+def test_pp_full_frame_c4(engine, seed):
+    cls, box, dirp = synth.pp_head_outputs(seed)
+    want = box3d.pp_anchor_post(cls, box, dirp, **KITTI_ANCHORS)
+    gb, gs, gl = _pp_gpu(engine, cls, box, dirp, **KITTI_ANCHORS)
+    assert gb.shape == tuple(want["pred_boxes"].shape)
+    assert np.array_equal(gl, want["pred_labels"].numpy())
+    _close(gs, want["pred_scores"].numpy())
+    _close(gb, want["pred_boxes"].numpy(), rtol=1e-5, atol=1e-5)
+
+
+def test_pp_no_candidates_and_no_dir(engine):
+    cls = np.full((20, 24, 18), -8.0, np.float32)
+    box = np.zeros((20, 24, 42), np.float32)
+    gb, gs, gl = _pp_gpu(engine, cls, box, None, **KITTI_ANCHORS)
+    assert gb.shape == (0, 7)
+    cls2, box2, _ = synth.pp_head_outputs(5, h=20, w=24, planted=6)
+    want = box3d.pp_anchor_post(cls2, box2, None, **KITTI_ANCHORS)
+    gb, gs, gl = _pp_gpu(engine, cls2, box2, None, **KITTI_ANCHORS)
+    assert np.array_equal(gl, want["pred_labels"].numpy())
+    _close(gb, want["pred_boxes"].numpy(), rtol=1e-5, atol=1e-5)
+
+
+def _cp_gpu(engine, heads, class_map=None, **kw):
+    dev = [{k: torch.from_numpy(v).cuda() for k, v in hd.items()} for hd in heads]
+    ob, osc, ol, cnt = engine.centerpoint_post(dev, class_map or CLASS_MAP[:len(heads)], NUSC["feature_map_stride"], NUSC["voxel_size"],
+                                               NUSC["point_cloud_range"], NUSC["post_center_limit_range"], **kw)
+    k = int(cnt.item())
+    return ob[:k].cpu().numpy(), osc[:k].cpu().numpy(), ol[:k].cpu().numpy()
+
+
+@pytest.mark.parametrize("seed", [5001, 5002])
+def test_centerpoint_full_frame_c5(engine, seed):
+    heads = synth.centerpoint_head_outputs(seed)
+    want = box3d.centerhead_generate_predicted_boxes(heads, CLASS_MAP, **NUSC)
+    gb, gs, gl = _cp_gpu(engine, heads)
+    assert gb.shape == tuple(want["pred_boxes"].shape)
+    assert np.array_equal(gl, want["pred_labels"].numpy())
+    _close(gs, want["pred_scores"].numpy())
+    _close(gb, want["pred_boxes"].numpy(), rtol=1e-5, atol=1e-5)
+
+
+def test_centerpoint_golden_decode(engine):
+    """decode_bbox_from_heatmap golden (reference code, tie-free heatmap): NMS disabled (thresh 1.0), K=40."""
+    g = golden("box3d")
+    p = 1e-7
+    hm = np.log(np.clip(g["cp_hm"][0], p, 1 - p) / (1 - np.clip(g["cp_hm"][0], p, 1 - p))).astype(np.float32)
+    head = {"hm": hm, "center": g["cp_center"][0], "center_z": g["cp_center_z"][0], "dim": np.log(g["cp_dim"][0]).astype(np.float32),
+            "rot": np.concatenate([g["cp_rot_cos"][0], g["cp_rot_sin"][0]]), "vel": g["cp_vel"][0]}
+    gb, gs, gl = _cp_gpu(engine, [head], class_map=[[0, 1]], k=40, nms_thresh=2.0, pre_max=1000, post_max=83)  # 2.0: identical boxes of two classes can reach IoU 1+ulp
+    # logit(sigmoid(x)) is not exact, so compare as sets of decoded rows ordered by score with a loose score tolerance
+    assert gb.shape == g["cp_boxes"].shape
+    _close(gb[:, [0, 1, 2, 6, 7, 8]], g["cp_boxes"][:, [0, 1, 2, 6, 7, 8]], rtol=1e-5, atol=1e-5)
+    _close(gb[:, 3:6], g["cp_boxes"][:, 3:6], rtol=1e-4)
+    _close(gs, g["cp_scores"], rtol=1e-4)
+    assert np.array_equal(gl - 1, g["cp_labels"])
+
+
+def test_class_score_filter(engine):
+    rng = np.random.default_rng(1)
+    labels = rng.integers(0, 10, 400).astype(np.int64)
+    scores = (np.round(rng.uniform(0, 1, 400) * 20) / 20).astype(np.float32)
+    want = box3d.remove_low_score_nu({"labels": labels, "scores": scores, "i": np.arange(400)})["i"]
+    idx, cnt = engine.class_score_filter(torch.from_numpy(labels).cuda(), torch.from_numpy(scores).cuda(), box3d.NUSC_GROUPS)
+    assert idx[:int(cnt.item())].cpu().tolist() == want.tolist()

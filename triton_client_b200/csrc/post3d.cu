@@ -1,0 +1,553 @@
+// 3D detection postprocess on device: rotated BEV IoU / NMS, PointPillars anchor
+// decode + class-agnostic NMS, CenterPoint heatmap top-K decode + per-head NMS, nuScenes per-class score filter.
+//
+// In the reference these run inside the Triton Python backend (examples/pointpillar_kitti/1/model.py:163) through
+// the vendored pcdet code cited at each kernel; the drop-in runs them client-side behind PointPillarPostprocess.
+// One 1024-thread CTA per frame (or per frame x head) does ordering + greedy NMS entirely in shared memory —
+// no N x N/64 mask in global memory, no D2H of it, no serial host sweep (iou3d_nms.cpp:105-134).
+#include "common.cuh"
+#include "cta_select.cuh"
+#include "rotated.cuh"
+
+namespace {
+
+constexpr int T = sel::THREADS;
+constexpr int PRE_CAP = sel::KCAP;  // NMS_PRE_MAXSIZE limit (4096: PointPillars' value, data/pointpillar.yaml:141)
+constexpr int POST_CAP = 1024;      // NMS_POST_MAXSIZE limit
+constexpr int ACAP = 64;            // survivors of a greedy round resolved against each other at once
+
+// ---------------------------------------------------------------------------------------------------------
+// rotated IoU matrix  (boxes_iou_bev_kernel, iou3d_nms_kernel.cu:251-265)
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) rotated_iou_kernel(const float* __restrict__ a, int n, const float* __restrict__ b, int m,
+                                                          float* __restrict__ out) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)n * m) return;
+    const int ia = (int)(i / m), ib = (int)(i - (long long)ia * m);
+    const rot::RBox ra = rot::make_rbox(a + 7 * ia), rb = rot::make_rbox(b + 7 * ib);
+    out[i] = rot::far_apart(ra, rb) ? 0.f : rot::iou_bev(ra, rb);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// greedy rotated NMS over m boxes already in descending score order, resident in shared memory
+//   nms_gpu (iou3d_nms_utils.py:84-99) = nms_kernel bitmask (iou3d_nms_kernel.cu:267-311) + host sweep
+//   (iou3d_nms.cpp:116-132): box i is kept unless an earlier kept box k has iou_bev(k, i) > thresh.
+// ---------------------------------------------------------------------------------------------------------
+struct NmsShared {
+    rot::RBox kept[POST_CAP];
+    int kpos[POST_CAP];                  // sorted position of each kept box
+    unsigned resolved[PRE_CAP / 32];     // bit c: sorted box c is kept or suppressed
+    unsigned long long mask[ACAP];
+    int aidx[ACAP], knew[ACAP];
+    int warp_cnt[32];
+    int nkept, next_pos, a_total;
+};
+
+__device__ __forceinline__ bool rot_suppresses(const rot::RBox& a, const rot::RBox& b, float thresh) {
+    if (rot::far_apart(a, b)) return false;  // the reference's polygon is empty: IoU 0, never > thresh (>= 0)
+    return rot::iou_bev(a, b) > thresh;
+}
+
+__device__ int cta_rotated_nms(const rot::RBox* __restrict__ R, int m, float thresh, int post_max, NmsShared& S) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) S.nkept = 0;
+    for (int i = tid; i < PRE_CAP / 32; i += T) S.resolved[i] = 0u;
+    __syncthreads();
+    int pos = 0, prev_end = 0, nk_prev = 0;
+    while (pos < m) {
+        const int cn = min(T, m - pos);
+        const int c = pos + tid;
+        const int nk = S.nkept;
+        bool alive = tid < cn && !((S.resolved[c >> 5] >> (c & 31)) & 1u);
+        if (alive) {  // (1) against the boxes kept since this candidate was last examined
+            const rot::RBox bx = R[c];
+            for (int k = (c < prev_end) ? nk_prev : 0; k < nk; k++)
+                if (rot_suppresses(S.kept[k], bx, thresh)) { alive = false; break; }
+            if (!alive) atomicOr(&S.resolved[c >> 5], 1u << (c & 31));
+        }
+        const unsigned bal = __ballot_sync(0xffffffffu, alive);
+        if (lane == 0) S.warp_cnt[warp] = __popc(bal);
+        __syncthreads();
+        if (warp == 0) {
+            int w = S.warp_cnt[lane];
+#pragma unroll
+            for (int k = 1; k < 32; k <<= 1) { const int t = __shfl_up_sync(0xffffffffu, w, k); if (lane >= k) w += t; }
+            S.warp_cnt[lane] = w;
+            if (lane == 31) { S.a_total = w; S.next_pos = pos + cn; }
+        }
+        __syncthreads();
+        const int rank = (warp ? S.warp_cnt[warp - 1] : 0) + __popc(bal & ((1u << lane) - 1));
+        if (alive) {
+            if (rank < ACAP) S.aidx[rank] = c;
+            else if (rank == ACAP) S.next_pos = c;
+        }
+        __syncthreads();
+        const int A = min(S.a_total, ACAP);
+        {  // (2) suppression mask among the A survivors: 16 threads per row, 4 columns each
+            const int ri = tid >> 4, l16 = tid & 15;
+            unsigned long long bits = 0ull;
+            if (ri < A) {
+                const rot::RBox bi = R[S.aidx[ri]];
+#pragma unroll 1
+                for (int q = 0; q < 4; q++) {
+                    const int j = l16 * 4 + q;
+                    if (j > ri && j < A && rot_suppresses(bi, R[S.aidx[j]], thresh)) bits |= 1ull << j;
+                }
+            }
+#pragma unroll
+            for (int sft = 1; sft < 16; sft <<= 1) bits |= __shfl_xor_sync(0xffffffffu, bits, sft);
+            if (l16 == 0 && ri < ACAP) S.mask[ri] = bits;
+        }
+        __syncthreads();
+        if (tid == 0) {  // (3) serial sweep, hopping from kept survivor to kept survivor
+            unsigned long long avail = A >= 64 ? ~0ull : ((1ull << A) - 1);
+            int kept = nk;
+            while (kept < post_max && avail) {
+                const int i = __ffsll((long long)avail) - 1;
+                avail &= ~(S.mask[i] | (1ull << i));
+                S.knew[kept - nk] = i;
+                kept++;
+            }
+            S.nkept = kept;
+        }
+        __syncthreads();
+        const int nk_new = S.nkept;
+        if (tid < nk_new - nk) { const int cs = S.aidx[S.knew[tid]]; S.kept[nk + tid] = R[cs]; S.kpos[nk + tid] = cs; }
+        if (tid < A) { const int cs = S.aidx[tid]; atomicOr(&S.resolved[cs >> 5], 1u << (cs & 31)); }
+        prev_end = pos + cn; nk_prev = nk;
+        const int np = S.next_pos;
+        __syncthreads();
+        if (nk_new >= post_max) break;
+        pos = np;
+    }
+    __syncthreads();
+    return S.nkept;
+}
+
+// shared memory of the one-CTA-per-frame kernels
+struct FrameShared {
+    unsigned long long skeys[sel::KCAP];
+    rot::RBox R[PRE_CAP];
+    sel::Scratch sel;
+    NmsShared nms;
+};
+
+// ---------------------------------------------------------------------------------------------------------
+// tcb_rotated_nms: scores + boxes in any order -> top pre_max by score -> greedy NMS -> keep indices
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(T, 1) rotated_nms_kernel(const float* __restrict__ boxes, const float* __restrict__ scores, int n,
+                                                           float thresh, int pre_max, int post_max,
+                                                           int* __restrict__ keep, int* __restrict__ count) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    FrameShared& S = *reinterpret_cast<FrameShared*>(smem_raw);
+    auto key_of = [&](int i) { return sel::make_key(__ldg(scores + i), (unsigned)i); };
+    const int m = sel::cta_topk_sorted(key_of, n, pre_max, S.skeys, S.sel);
+    for (int c = threadIdx.x; c < m; c += T) S.R[c] = rot::make_rbox(boxes + 7ll * sel::key_index(S.skeys[c]));
+    __syncthreads();
+    const int nk = cta_rotated_nms(S.R, m, thresh, post_max, S.nms);
+    for (int k = threadIdx.x; k < nk; k += T) keep[k] = (int)sel::key_index(S.skeys[S.nms.kpos[k]]);
+    if (threadIdx.x == 0) *count = nk;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// PointPillars anchor head post (d2-d4)
+// ---------------------------------------------------------------------------------------------------------
+constexpr int PP_MAX_CLASSES = 8, PP_MAX_ROT = 4;
+struct PPParams {
+    int H, W, num_class, num_rot, num_dir_bins;
+    float x0, y0;
+    double x_stride, y_stride;                   // anchor grid (align_center = False: stride = range/(n-1), float64 in pcdet)
+    float size[PP_MAX_CLASSES][3];               // dx, dy, dz per class
+    float zc[PP_MAX_CLASSES];                    // anchor centre height = bottom + dz/2 (anchor_generator.py:58)
+    float rot[PP_MAX_CLASSES][PP_MAX_ROT];
+    float dir_offset, dir_limit_offset, period;
+    float score_thresh, nms_thresh;
+    int pre_max, post_max;
+};
+
+__device__ __forceinline__ float sigmoidf_ref(float x) { return 1.f / (1.f + expf(-x)); }  // torch.sigmoid
+
+// per anchor: sigmoid of every class logit, max / first arg-max (detector3d_template.py:217,251), keep score >= thresh
+__global__ void __launch_bounds__(256) pp_candidates_kernel(const float* __restrict__ cls, int n_anchors, int num_class, float thresh,
+                                                            unsigned long long* __restrict__ cand, int* __restrict__ cand_count) {
+    const int a = blockIdx.x * blockDim.x + threadIdx.x;
+    bool ok = false;
+    float best = 0.f;
+    if (a < n_anchors) {
+        const float* p = cls + (long long)a * num_class;
+        best = sigmoidf_ref(__ldg(p));
+        for (int c = 1; c < num_class; c++) best = fmaxf(best, sigmoidf_ref(__ldg(p + c)));
+        ok = best >= thresh;
+    }
+    const unsigned em = __ballot_sync(0xffffffffu, ok);
+    if (em) {
+        const int lane = threadIdx.x & 31;
+        int base = 0;
+        if (lane == 0) base = atomicAdd(cand_count, __popc(em));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (ok) cand[base + __popc(em & ((1u << lane) - 1))] = sel::make_key(best, (unsigned)a);
+    }
+}
+
+// anchor a -> decoded box (anchor_generator.py:17-60 analytically, box_coder_utils.py:45-77, anchor_head_template.py:253-263)
+__device__ __forceinline__ void pp_decode(const PPParams& p, int a, const float* __restrict__ box_preds, const float* __restrict__ dir_preds,
+                                          float* out7) {
+    const int per_loc = p.num_class * p.num_rot;
+    const int loc = a / per_loc, k = a - loc * per_loc;
+    const int yy = loc / p.W, xx = loc - yy * p.W;
+    const int cls = k / p.num_rot, ri = k - cls * p.num_rot;
+    const float xa = (float)((double)p.x0 + p.x_stride * (double)xx);   // torch.arange(start, end, step): start + step*i in double
+    const float ya = (float)((double)p.y0 + p.y_stride * (double)yy);
+    const float za = p.zc[cls];
+    const float dxa = p.size[cls][0], dya = p.size[cls][1], dza = p.size[cls][2], ra = p.rot[cls][ri];
+    const float* t = box_preds + (long long)a * 7;
+    const float xt = __ldg(t), yt = __ldg(t + 1), zt = __ldg(t + 2), dxt = __ldg(t + 3), dyt = __ldg(t + 4), dzt = __ldg(t + 5), rt = __ldg(t + 6);
+    const float diagonal = sqrtf(dxa * dxa + dya * dya);
+    out7[0] = xt * diagonal + xa;
+    out7[1] = yt * diagonal + ya;
+    out7[2] = zt * dza + za;
+    out7[3] = expf(dxt) * dxa;
+    out7[4] = expf(dyt) * dya;
+    out7[5] = expf(dzt) * dza;
+    float rg = rt + ra;
+    if (dir_preds) {
+        const float* d = dir_preds + (long long)a * p.num_dir_bins;
+        int label = 0;
+        float bestd = __ldg(d);
+        for (int q = 1; q < p.num_dir_bins; q++) { const float v = __ldg(d + q); if (v > bestd) { bestd = v; label = q; } }
+        const float val = rg - p.dir_offset;
+        const float dir_rot = val - floorf(val / p.period + p.dir_limit_offset) * p.period;   // common_utils.limit_period
+        rg = dir_rot + p.dir_offset + p.period * (float)label;
+    }
+    out7[6] = rg;
+}
+
+__global__ void __launch_bounds__(T, 1) pp_post_kernel(const PPParams p, const float* __restrict__ cls, const float* __restrict__ box_preds,
+                                                       const float* __restrict__ dir_preds, const unsigned long long* __restrict__ cand,
+                                                       const int* __restrict__ cand_count, int cand_cap, float* __restrict__ sorted_boxes,
+                                                       float* __restrict__ out_boxes, float* __restrict__ out_scores,
+                                                       long long* __restrict__ out_labels, int* __restrict__ out_count) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    FrameShared& S = *reinterpret_cast<FrameShared*>(smem_raw);
+    const int tid = threadIdx.x;
+    const int nc = min(*cand_count, cand_cap);
+    auto key_of = [&](int i) { return cand[i]; };
+    const int m = sel::cta_topk_sorted(key_of, nc, p.pre_max, S.skeys, S.sel);   // class_agnostic_nms topk (model_nms_utils.py:15)
+    for (int c = tid; c < m; c += T) {
+        float b7[7];
+        pp_decode(p, (int)sel::key_index(S.skeys[c]), box_preds, dir_preds, b7);
+#pragma unroll
+        for (int j = 0; j < 7; j++) sorted_boxes[c * 7 + j] = b7[j];
+        S.R[c] = rot::make_rbox(b7);
+    }
+    __syncthreads();
+    const int nk = cta_rotated_nms(S.R, m, p.nms_thresh, p.post_max, S.nms);
+    for (int k = tid; k < nk; k += T) {
+        const int c = S.nms.kpos[k];
+        const unsigned long long key = S.skeys[c];
+        const int a = (int)sel::key_index(key);
+#pragma unroll
+        for (int j = 0; j < 7; j++) out_boxes[k * 7 + j] = sorted_boxes[c * 7 + j];
+        out_scores[k] = sel::key_score(key);
+        const float* q = cls + (long long)a * p.num_class;   // label = first arg-max of the sigmoids, + 1 (detector3d_template.py:251,256)
+        int label = 0;
+        float best = sigmoidf_ref(__ldg(q));
+        for (int cc = 1; cc < p.num_class; cc++) { const float v = sigmoidf_ref(__ldg(q + cc)); if (v > best) { best = v; label = cc; } }
+        out_labels[k] = (long long)(label + 1);
+    }
+    if (tid == 0) *out_count = nk;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// CenterPoint head post (d6): one CTA per head
+// ---------------------------------------------------------------------------------------------------------
+constexpr int CP_MAX_HEADS = 8, CP_MAX_HEAD_CLASSES = 4;
+struct CPHead {
+    const float *hm, *center, *center_z, *dim, *rot, *vel;  // NCHW planes of one frame
+    int num_class;
+    int class_map[CP_MAX_HEAD_CLASSES];
+};
+struct CPParams {
+    CPHead head[CP_MAX_HEADS];
+    int num_heads, H, W, K;
+    float stride, vx, vy, rx, ry;        // feature_map_stride, voxel size, range min
+    float limit[6];                      // POST_CENTER_LIMIT_RANGE
+    float score_thresh, nms_thresh;
+    int pre_max, post_max;
+};
+
+__global__ void __launch_bounds__(T, 1) cp_head_kernel(const CPParams p, float* __restrict__ head_boxes, float* __restrict__ head_scores,
+                                                       int* __restrict__ head_labels, int* __restrict__ head_count) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    FrameShared& S = *reinterpret_cast<FrameShared*>(smem_raw);
+    const int tid = threadIdx.x, h = blockIdx.x;
+    const CPHead& hd = p.head[h];
+    const int HW = p.H * p.W, n = hd.num_class * HW;
+    // _topk (centernet_utils.py:136-151): per-class top-K then top-K across classes == global top-K of the sigmoids
+    auto key_of = [&](int i) { return sel::make_key(sigmoidf_ref(__ldg(hd.hm + i)), (unsigned)i); };
+    const int m = sel::cta_topk_sorted(key_of, n, p.K, S.skeys, S.sel);
+    // decode_bbox_from_heatmap (centernet_utils.py:154-216) + range/score mask, order preserved
+    // scratch rows: [0, heads*post_max) final rows per head, then per head pre_max rows of masked, still sorted boxes
+    float* boxes = head_boxes + (long long)h * p.post_max * 9;
+    // masked compaction must preserve score order: do it in chunks of T with an ordered scan
+    int base = 0;
+    for (int c0 = 0; c0 < m; c0 += T) {
+        const int c = c0 + tid;
+        bool ok = false;
+        float b9[9];
+        float score = 0.f;
+        int cls = 0;
+        if (c < m) {
+            const unsigned long long key = S.skeys[c];
+            const int i = (int)sel::key_index(key);
+            score = sel::key_score(key);
+            cls = i / HW;
+            const int ind = i - cls * HW;
+            const float ys = (float)(ind / p.W), xs = (float)(ind % p.W);
+            const float cx = __ldg(hd.center + ind), cy = __ldg(hd.center + HW + ind);
+            b9[0] = (xs + cx) * p.stride * p.vx + p.rx;
+            b9[1] = (ys + cy) * p.stride * p.vy + p.ry;
+            b9[2] = __ldg(hd.center_z + ind);
+            b9[3] = expf(__ldg(hd.dim + ind)); b9[4] = expf(__ldg(hd.dim + HW + ind)); b9[5] = expf(__ldg(hd.dim + 2 * HW + ind));
+            b9[6] = atan2f(__ldg(hd.rot + HW + ind), __ldg(hd.rot + ind));   // rot[:,1] = sin, rot[:,0] = cos (center_head.py:266-267)
+            b9[7] = hd.vel ? __ldg(hd.vel + ind) : 0.f;
+            b9[8] = hd.vel ? __ldg(hd.vel + HW + ind) : 0.f;
+            ok = b9[0] >= p.limit[0] && b9[1] >= p.limit[1] && b9[2] >= p.limit[2] &&
+                 b9[0] <= p.limit[3] && b9[1] <= p.limit[4] && b9[2] <= p.limit[5] && score > p.score_thresh;
+        }
+        int total;
+        const int r = sel::cta_exclusive_scan(ok ? 1 : 0, S.sel.warp_tot, total);
+        if (ok && base + r < p.pre_max) {   // class_agnostic_nms topk(min(NMS_PRE_MAXSIZE, n)) on an already sorted list
+            const int d = base + r;
+            S.R[d] = rot::make_rbox(b9);
+            float* row = head_boxes + ((long long)p.num_heads * p.post_max + (long long)h * p.pre_max + d) * 9;
+#pragma unroll
+            for (int j = 0; j < 9; j++) row[j] = b9[j];
+            head_scores[p.num_heads * p.post_max + h * p.pre_max + d] = score;
+            head_labels[p.num_heads * p.post_max + h * p.pre_max + d] = hd.class_map[cls];
+        }
+        base += total;
+        __syncthreads();
+    }
+    const int mv = min(base, p.pre_max);
+    __syncthreads();
+    const int nk = cta_rotated_nms(S.R, mv, p.nms_thresh, p.post_max, S.nms);
+    for (int k = tid; k < nk; k += T) {
+        const int c = S.nms.kpos[k];
+        const long long src = (long long)p.num_heads * p.post_max + (long long)h * p.pre_max + c;
+#pragma unroll
+        for (int j = 0; j < 9; j++) boxes[k * 9 + j] = head_boxes[src * 9 + j];
+        head_scores[h * p.post_max + k] = head_scores[src];
+        head_labels[h * p.post_max + k] = head_labels[src];
+    }
+    if (tid == 0) head_count[h] = nk;
+}
+
+// concatenate the heads in order, labels + 1 (center_head.py:299-302)
+__global__ void __launch_bounds__(256) cp_concat_kernel(int num_heads, int post_max, const float* __restrict__ head_boxes,
+                                                        const float* __restrict__ head_scores, const int* __restrict__ head_labels,
+                                                        const int* __restrict__ head_count, float* __restrict__ out_boxes,
+                                                        float* __restrict__ out_scores, long long* __restrict__ out_labels, int* __restrict__ out_count) {
+    int off = 0;
+    for (int h = 0; h < num_heads; h++) {
+        const int n = head_count[h];
+        for (int k = threadIdx.x; k < n; k += blockDim.x) {
+            for (int j = 0; j < 9; j++) out_boxes[(off + k) * 9 + j] = head_boxes[((long long)h * post_max + k) * 9 + j];
+            out_scores[off + k] = head_scores[h * post_max + k];
+            out_labels[off + k] = (long long)head_labels[h * post_max + k] + 1;
+        }
+        off += n;
+    }
+    if (threadIdx.x == 0) *out_count = off;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// nuScenes per-class score cut (clients/postprocess/detector_3d_postprocess.py:55-64,98-133): indices of
+// label == cls && score >= thr[cls], concatenated in the reference's fixed class order.
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024) class_filter_kernel(const long long* __restrict__ labels, const float* __restrict__ scores, int n,
+                                                            int n_groups, const int* __restrict__ group_cls, const float* __restrict__ group_thr,
+                                                            int* __restrict__ out_idx, int* __restrict__ out_count) {
+    __shared__ int warp_tot[32];
+    int base = 0;
+    for (int g = 0; g < n_groups; g++) {
+        const int cls = group_cls[g];
+        const float thr = group_thr[g];
+        for (int c0 = 0; c0 < n; c0 += 1024) {
+            const int i = c0 + threadIdx.x;
+            const bool ok = i < n && labels[i] == (long long)cls && scores[i] >= thr;
+            int total;
+            const int r = sel::cta_exclusive_scan(ok ? 1 : 0, warp_tot, total);
+            if (ok) out_idx[base + r] = i;
+            base += total;
+        }
+    }
+    if (threadIdx.x == 0) *out_count = base;
+}
+
+}  // namespace
+
+// =========================================================================================================
+// C ABI
+// =========================================================================================================
+extern "C" int tcb_rotated_iou(tcb_ctx* ctx, const float* boxes_a_dev, int n, const float* boxes_b_dev, int m, float* out_dev, void* stream) {
+    TCB_CHECK_CTX(ctx);
+    TCB_REQUIRE(ctx, n >= 0 && m >= 0, "tcb_rotated_iou: bad sizes");
+    if (n == 0 || m == 0) return TCB_OK;
+    TCB_REQUIRE(ctx, boxes_a_dev && boxes_b_dev && out_dev, "tcb_rotated_iou: null buffer");
+    rotated_iou_kernel<<<tcb_div_up((long long)n * m, 256), 256, 0, (cudaStream_t)stream>>>(boxes_a_dev, n, boxes_b_dev, m, out_dev);
+    TCB_LAUNCHED(ctx);
+    return TCB_OK;
+}
+
+static int check_nms_limits(tcb_ctx* ctx, const char* who, float thresh, int pre_max, int post_max) {
+    if (!(thresh >= 0.f)) return tcb_fail(ctx, TCB_ERR_ARG, "%s: nms threshold must be >= 0", who);
+    if (pre_max < 1 || post_max < 1) return tcb_fail(ctx, TCB_ERR_ARG, "%s: pre/post max size must be >= 1", who);
+    if (pre_max > PRE_CAP) return tcb_fail(ctx, TCB_ERR_LIMIT, "%s: NMS_PRE_MAXSIZE %d > compiled limit %d", who, pre_max, PRE_CAP);
+    if (post_max > POST_CAP) return tcb_fail(ctx, TCB_ERR_LIMIT, "%s: NMS_POST_MAXSIZE %d > compiled limit %d", who, post_max, POST_CAP);
+    return TCB_OK;
+}
+
+template <typename K>
+static int opt_in_smem(tcb_ctx* ctx, K kernel) {
+    TCB_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FrameShared)));
+    return TCB_OK;
+}
+
+extern "C" int tcb_rotated_nms(tcb_ctx* ctx, const float* boxes_dev, const float* scores_dev, int n, float thresh, int pre_max,
+                               int post_max, int* keep_dev, int* count_dev, void* stream) {
+    TCB_CHECK_CTX(ctx);
+    TCB_REQUIRE(ctx, n >= 0 && keep_dev && count_dev && (n == 0 || (boxes_dev && scores_dev)), "tcb_rotated_nms: bad arguments");
+    int rc = check_nms_limits(ctx, "tcb_rotated_nms", thresh, pre_max, post_max);
+    if (rc) return rc;
+    if ((rc = opt_in_smem(ctx, rotated_nms_kernel))) return rc;
+    rotated_nms_kernel<<<1, T, sizeof(FrameShared), (cudaStream_t)stream>>>(boxes_dev, scores_dev, n, thresh, pre_max, post_max, keep_dev, count_dev);
+    TCB_LAUNCHED(ctx);
+    return TCB_OK;
+}
+
+extern "C" size_t tcb_pp_anchor_post_workspace(int h, int w, int num_class, int num_rot) {
+    const size_t n = (size_t)h * w * num_class * num_rot;
+    return n * 8 + (size_t)PRE_CAP * 7 * 4 + 4096;
+}
+
+extern "C" int tcb_pp_anchor_post(tcb_ctx* ctx, const float* cls_dev, const float* box_dev, const float* dir_dev, int h, int w,
+                                  int num_class, int num_rot, const float anchor_range[6], const float* anchor_sizes,
+                                  const float* anchor_bottoms, const float* anchor_rotations, float dir_offset,
+                                  float dir_limit_offset, int num_dir_bins, float score_thresh, float nms_thresh, int pre_max,
+                                  int post_max, float* out_boxes_dev, float* out_scores_dev, long long* out_labels_dev,
+                                  int* out_count_dev, void* stream) {
+    TCB_CHECK_CTX(ctx);
+    TCB_REQUIRE(ctx, cls_dev && box_dev && anchor_range && anchor_sizes && anchor_bottoms && anchor_rotations &&
+                     out_boxes_dev && out_scores_dev && out_labels_dev && out_count_dev, "tcb_pp_anchor_post: null argument");
+    TCB_REQUIRE(ctx, h >= 2 && w >= 2, "tcb_pp_anchor_post: feature map must be at least 2x2");
+    if (num_class < 1 || num_class > PP_MAX_CLASSES || num_rot < 1 || num_rot > PP_MAX_ROT)
+        return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_pp_anchor_post: num_class %d (<= %d) / num_rot %d (<= %d)", num_class, PP_MAX_CLASSES, num_rot, PP_MAX_ROT);
+    TCB_REQUIRE(ctx, dir_dev == nullptr || num_dir_bins >= 1, "tcb_pp_anchor_post: num_dir_bins must be >= 1");
+    int rc = check_nms_limits(ctx, "tcb_pp_anchor_post", nms_thresh, pre_max, post_max);
+    if (rc) return rc;
+    const long long n_anchors = (long long)h * w * num_class * num_rot;
+    if (n_anchors > (1ll << 30)) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_pp_anchor_post: too many anchors");
+    cudaStream_t st = (cudaStream_t)stream;
+
+    PPParams p;
+    memset(&p, 0, sizeof(p));
+    p.H = h; p.W = w; p.num_class = num_class; p.num_rot = num_rot; p.num_dir_bins = num_dir_bins;
+    // anchor_generator.py:28-31: float32 range difference divided by a numpy int64 grid size -> float64 stride
+    p.x0 = anchor_range[0]; p.y0 = anchor_range[1];
+    p.x_stride = (double)(anchor_range[3] - anchor_range[0]) / (double)(w - 1);
+    p.y_stride = (double)(anchor_range[4] - anchor_range[1]) / (double)(h - 1);
+    for (int c = 0; c < num_class; c++) {
+        for (int j = 0; j < 3; j++) p.size[c][j] = anchor_sizes[c * 3 + j];
+        p.zc[c] = anchor_bottoms[c] + p.size[c][2] / 2;
+        for (int r = 0; r < num_rot; r++) p.rot[c][r] = anchor_rotations[c * num_rot + r];
+    }
+    p.dir_offset = dir_offset; p.dir_limit_offset = dir_limit_offset;
+    p.period = (float)(2.0 * 3.141592653589793 / (double)(num_dir_bins > 0 ? num_dir_bins : 1));
+    p.score_thresh = score_thresh; p.nms_thresh = nms_thresh; p.pre_max = pre_max; p.post_max = post_max;
+
+    TCB_WS(ctx, cand_count, int, 64);
+    TCB_WS(ctx, cand, unsigned long long, n_anchors);
+    TCB_WS(ctx, sorted_boxes, float, (size_t)PRE_CAP * 7);
+    TCB_CUDA(ctx, cudaMemsetAsync(cand_count, 0, sizeof(int), st));
+    pp_candidates_kernel<<<tcb_div_up(n_anchors, 256), 256, 0, st>>>(cls_dev, (int)n_anchors, num_class, score_thresh, cand, cand_count);
+    TCB_LAUNCHED(ctx);
+    if ((rc = opt_in_smem(ctx, pp_post_kernel))) return rc;
+    pp_post_kernel<<<1, T, sizeof(FrameShared), st>>>(p, cls_dev, box_dev, dir_dev, cand, cand_count, (int)n_anchors, sorted_boxes,
+                                                       out_boxes_dev, out_scores_dev, out_labels_dev, out_count_dev);
+    TCB_LAUNCHED(ctx);
+    return TCB_OK;
+}
+
+extern "C" size_t tcb_centerpoint_post_workspace(int num_heads, int pre_max, int post_max) {
+    return (size_t)num_heads * (size_t)(pre_max + post_max) * (9 * 4 + 4 + 4) + 4096;
+}
+
+extern "C" int tcb_centerpoint_post(tcb_ctx* ctx, int num_heads, const float* const* hm_dev, const float* const* center_dev,
+                                    const float* const* center_z_dev, const float* const* dim_dev, const float* const* rot_dev,
+                                    const float* const* vel_dev, const int* head_num_class, const int* class_id_map, int h, int w,
+                                    int feature_map_stride, const float voxel_size_xy[2], const float range_min_xy[2],
+                                    const float limit_range[6], int k, float score_thresh, float nms_thresh, int pre_max, int post_max,
+                                    float* out_boxes_dev, float* out_scores_dev, long long* out_labels_dev, int* out_count_dev,
+                                    void* stream) {
+    TCB_CHECK_CTX(ctx);
+    TCB_REQUIRE(ctx, hm_dev && center_dev && center_z_dev && dim_dev && rot_dev && head_num_class && class_id_map && voxel_size_xy &&
+                     range_min_xy && limit_range && out_boxes_dev && out_scores_dev && out_labels_dev && out_count_dev,
+                "tcb_centerpoint_post: null argument");
+    if (num_heads < 1 || num_heads > CP_MAX_HEADS) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_centerpoint_post: %d heads (limit %d)", num_heads, CP_MAX_HEADS);
+    TCB_REQUIRE(ctx, h >= 1 && w >= 1 && k >= 1, "tcb_centerpoint_post: bad shape");
+    if (k > PRE_CAP) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_centerpoint_post: K %d > %d", k, PRE_CAP);
+    int rc = check_nms_limits(ctx, "tcb_centerpoint_post", nms_thresh, pre_max, post_max);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+
+    CPParams p;
+    memset(&p, 0, sizeof(p));
+    p.num_heads = num_heads; p.H = h; p.W = w; p.K = k;
+    int cm = 0;
+    for (int i = 0; i < num_heads; i++) {
+        CPHead& hd = p.head[i];
+        hd.hm = hm_dev[i]; hd.center = center_dev[i]; hd.center_z = center_z_dev[i]; hd.dim = dim_dev[i]; hd.rot = rot_dev[i];
+        hd.vel = vel_dev ? vel_dev[i] : nullptr;
+        hd.num_class = head_num_class[i];
+        if (hd.num_class < 1 || hd.num_class > CP_MAX_HEAD_CLASSES)
+            return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_centerpoint_post: head %d has %d classes (limit %d)", i, hd.num_class, CP_MAX_HEAD_CLASSES);
+        TCB_REQUIRE(ctx, hd.hm && hd.center && hd.center_z && hd.dim && hd.rot, "tcb_centerpoint_post: head %d has a null tensor", i);
+        for (int c = 0; c < hd.num_class; c++) hd.class_map[c] = class_id_map[cm++];
+    }
+    p.stride = (float)feature_map_stride; p.vx = voxel_size_xy[0]; p.vy = voxel_size_xy[1]; p.rx = range_min_xy[0]; p.ry = range_min_xy[1];
+    for (int j = 0; j < 6; j++) p.limit[j] = limit_range[j];
+    p.score_thresh = score_thresh; p.nms_thresh = nms_thresh; p.pre_max = pre_max; p.post_max = post_max;
+
+    const size_t rows = (size_t)num_heads * (size_t)(pre_max + post_max);
+    TCB_WS(ctx, head_count, int, 64);
+    TCB_WS(ctx, head_boxes, float, rows * 9);
+    TCB_WS(ctx, head_scores, float, rows);
+    TCB_WS(ctx, head_labels, int, rows);
+    if ((rc = opt_in_smem(ctx, cp_head_kernel))) return rc;
+    cp_head_kernel<<<num_heads, T, sizeof(FrameShared), st>>>(p, head_boxes, head_scores, head_labels, head_count);
+    TCB_LAUNCHED(ctx);
+    cp_concat_kernel<<<1, 256, 0, st>>>(num_heads, post_max, head_boxes, head_scores, head_labels, head_count, out_boxes_dev,
+                                        out_scores_dev, out_labels_dev, out_count_dev);
+    TCB_LAUNCHED(ctx);
+    return TCB_OK;
+}
+
+extern "C" int tcb_class_score_filter(tcb_ctx* ctx, const long long* labels_dev, const float* scores_dev, int n, int n_groups,
+                                      const int* group_class_host, const float* group_thresh_host, int* out_idx_dev,
+                                      int* out_count_dev, void* stream) {
+    TCB_CHECK_CTX(ctx);
+    TCB_REQUIRE(ctx, n >= 0 && n_groups >= 0 && n_groups <= 64 && out_idx_dev && out_count_dev, "tcb_class_score_filter: bad arguments");
+    TCB_REQUIRE(ctx, n == 0 || (labels_dev && scores_dev), "tcb_class_score_filter: null input");
+    TCB_REQUIRE(ctx, n_groups == 0 || (group_class_host && group_thresh_host), "tcb_class_score_filter: null group tables");
+    cudaStream_t st = (cudaStream_t)stream;
+    TCB_WS(ctx, gcls, int, 64);
+    TCB_WS(ctx, gthr, float, 64);
+    if (n_groups) {
+        TCB_CUDA(ctx, cudaMemcpyAsync(gcls, group_class_host, sizeof(int) * n_groups, cudaMemcpyHostToDevice, st));
+        TCB_CUDA(ctx, cudaMemcpyAsync(gthr, group_thresh_host, sizeof(float) * n_groups, cudaMemcpyHostToDevice, st));
+    }
+    class_filter_kernel<<<1, 1024, 0, st>>>(labels_dev, scores_dev, n, n_groups, gcls, gthr, out_idx_dev, out_count_dev);
+    TCB_LAUNCHED(ctx);
+    return TCB_OK;
+}

@@ -120,6 +120,102 @@ class Engine:
                       mm, p, f, vs, r0, _ptr(out), _lib.stream_ptr())
         return out
 
+    # ---- 3D detection postprocess --------------------------------------------------------------------
+    def rotated_iou(self, boxes_a, boxes_b):
+        """boxes_iou_bev: (N,7),(M,7) f32 CUDA -> (N,M) f32."""
+        _need_cuda(boxes_a, boxes_b)
+        a, b = boxes_a.contiguous().float(), boxes_b.contiguous().float()
+        out = torch.empty((a.shape[0], b.shape[0]), dtype=torch.float32, device=a.device)
+        self.ctx.call("tcb_rotated_iou", _ptr(a), a.shape[0], _ptr(b), b.shape[0], _ptr(out), _lib.stream_ptr())
+        return out
+
+    def rotated_nms(self, boxes, scores, thresh, pre_max=4096, post_max=500):
+        """topk(pre_max) + nms_gpu + [:post_max]. Returns (keep int32 [post_max] indices into the input, count [1])."""
+        _need_cuda(boxes, scores)
+        b, s = boxes.contiguous().float(), scores.contiguous().float()
+        keep = torch.empty((post_max,), dtype=torch.int32, device=b.device)
+        cnt = torch.zeros((1,), dtype=torch.int32, device=b.device)
+        self.ctx.call("tcb_rotated_nms", _ptr(b), _ptr(s), b.shape[0], float(thresh), int(pre_max), int(post_max), _ptr(keep), _ptr(cnt),
+                      _lib.stream_ptr())
+        return keep, cnt
+
+    def pp_anchor_post(self, cls_preds, box_preds, dir_preds, anchor_range, anchor_sizes, anchor_bottoms, anchor_rotations,
+                       dir_offset=0.78539, dir_limit_offset=0.0, num_dir_bins=2, score_thresh=0.1, nms_thresh=0.01,
+                       pre_max=4096, post_max=500):
+        """One frame of PointPillars head outputs: cls (H,W,A*nc), box (H,W,A*7), dir (H,W,A*bins) or None.
+        Returns device tensors (boxes [post_max,7], scores [post_max], labels int64 [post_max], count [1])."""
+        _need_cuda(cls_preds, box_preds)
+        h, w = cls_preds.shape[-3], cls_preds.shape[-2]
+        nc = len(anchor_sizes)
+        nrot = len(anchor_rotations[0])
+        dev = cls_preds.device
+        ob = torch.zeros((post_max, 7), dtype=torch.float32, device=dev)
+        osc = torch.zeros((post_max,), dtype=torch.float32, device=dev)
+        ol = torch.zeros((post_max,), dtype=torch.int64, device=dev)
+        cnt = torch.zeros((1,), dtype=torch.int32, device=dev)
+        rng = (c_float * 6)(*[float(np.float32(v)) for v in anchor_range])
+        sizes = (c_float * (nc * 3))(*[float(v) for s in anchor_sizes for v in s])
+        bots = (c_float * nc)(*[float(v) for v in anchor_bottoms])
+        rots = (c_float * (nc * nrot))(*[float(v) for r in anchor_rotations for v in r])
+        self.ctx.call("tcb_pp_anchor_post", _ptr(cls_preds.contiguous()), _ptr(box_preds.contiguous()),
+                      _ptr(dir_preds.contiguous()) if dir_preds is not None else None, h, w, nc, nrot, rng, sizes, bots, rots,
+                      float(dir_offset), float(dir_limit_offset), int(num_dir_bins), float(score_thresh), float(nms_thresh),
+                      int(pre_max), int(post_max), _ptr(ob), _ptr(osc), _ptr(ol), _ptr(cnt), _lib.stream_ptr())
+        return ob, osc, ol, cnt
+
+    def centerpoint_post(self, heads, class_id_map, feature_map_stride, voxel_size, point_range, limit_range, k=500,
+                         score_thresh=0.1, nms_thresh=0.2, pre_max=1000, post_max=83):
+        """heads: list of dicts with CUDA f32 tensors hm [c,H,W], center [2,H,W], center_z [1,H,W], dim [3,H,W],
+        rot [2,H,W], optional vel [2,H,W]; class_id_map: list (per head) of global 0-based class ids.
+        Returns (boxes [heads*post_max,9], scores, labels int64 1-based, count [1])."""
+        nh = len(heads)
+        keep_alive = []
+
+        def ptrs(name, optional=False):
+            arr = (c_void_p * nh)()
+            for i, hd in enumerate(heads):
+                t = hd.get(name)
+                if t is None:
+                    if not optional:
+                        raise KeyError(name)
+                    arr[i] = None
+                else:
+                    t = t.contiguous()
+                    keep_alive.append(t)
+                    arr[i] = t.data_ptr()
+            return arr
+
+        hm = heads[0]["hm"]
+        _need_cuda(hm)
+        h, w = hm.shape[-2], hm.shape[-1]
+        dev = hm.device
+        ncls = (c_int * nh)(*[int(hd["hm"].shape[-3]) for hd in heads])
+        cmap = [int(v) for m in class_id_map for v in m]
+        cmap_arr = (c_int * len(cmap))(*cmap)
+        ob = torch.zeros((nh * post_max, 9), dtype=torch.float32, device=dev)
+        osc = torch.zeros((nh * post_max,), dtype=torch.float32, device=dev)
+        ol = torch.zeros((nh * post_max,), dtype=torch.int64, device=dev)
+        cnt = torch.zeros((1,), dtype=torch.int32, device=dev)
+        has_vel = all(hd.get("vel") is not None for hd in heads)
+        self.ctx.call("tcb_centerpoint_post", nh, ptrs("hm"), ptrs("center"), ptrs("center_z"), ptrs("dim"), ptrs("rot"),
+                      ptrs("vel", True) if has_vel else None, ncls, cmap_arr, h, w, int(feature_map_stride),
+                      (c_float * 2)(float(voxel_size[0]), float(voxel_size[1])), (c_float * 2)(float(point_range[0]), float(point_range[1])),
+                      (c_float * 6)(*[float(v) for v in limit_range]), int(k), float(score_thresh), float(nms_thresh),
+                      int(pre_max), int(post_max), _ptr(ob), _ptr(osc), _ptr(ol), _ptr(cnt), _lib.stream_ptr())
+        return ob, osc, ol, cnt
+
+    def class_score_filter(self, labels, scores, groups):
+        """groups: list of (class, threshold) in output order. Returns (indices int32 [len(groups)*n], count [1])."""
+        _need_cuda(labels, scores)
+        n = labels.shape[0]
+        lab, sc = labels.contiguous().to(torch.int64), scores.contiguous().float()
+        out = torch.empty((max(1, len(groups) * n),), dtype=torch.int32, device=lab.device)
+        cnt = torch.zeros((1,), dtype=torch.int32, device=lab.device)
+        gc = (c_int * max(1, len(groups)))(*[int(g[0]) for g in groups])
+        gt = (c_float * max(1, len(groups)))(*[float(g[1]) for g in groups])
+        self.ctx.call("tcb_class_score_filter", _ptr(lab), _ptr(sc), n, len(groups), gc, gt, _ptr(out), _ptr(cnt), _lib.stream_ptr())
+        return out, cnt
+
 
 def yolo_nms_static(pred, conf_thres=0.6, iou_thres=0.45, classes=None, agnostic=False, max_det=300,
                     max_nms=30000, out=None, counts=None):

@@ -99,3 +99,57 @@ def lidar_multisweep(seed, sweeps=10, beams=32, azimuths=940):
         p[:, 3] *= 255.0
         out.append(np.concatenate([p, np.full((len(p), 1), 0.05 * s, np.float32)], axis=1))
     return np.concatenate(out, axis=0).astype(np.float32)
+
+
+# ---- C4 PointPillars head outputs / C5 CenterPoint head outputs ------------------------------------
+def _quantise(x, step=1.0 / 64):
+    """Logits on a 1/64 grid: two distinct logits then differ by >= 1e-5 relative after the sigmoid for every
+    |x| < 9, so no two libm implementations of exp() can order a pair of scores differently."""
+    return (np.round(x / step) * step).astype(np.float32)
+
+
+def pp_head_outputs(seed, h=248, w=216, num_class=3, num_rot=2, planted=50):
+    """cls (h,w,A*nc) ~ N(-5,1.2) with planted object clusters (+6), box (h,w,A*7) ~ N(0,0.3), dir (h,w,A*2) ~ N(0,1)."""
+    rng = np.random.default_rng(seed)
+    a = num_class * num_rot
+    cls = rng.normal(-5.0, 1.2, (h, w, a, num_class))
+    for _ in range(planted):
+        y, x = rng.integers(2, h - 2), rng.integers(2, w - 2)
+        k, c = rng.integers(0, a), rng.integers(0, num_class)
+        cls[y - 1:y + 2, x - 1:x + 2, k, c] += rng.uniform(4, 8)
+    box = rng.normal(0, 0.3, (h, w, a * 7)).astype(np.float32)
+    dirp = _quantise(rng.normal(0, 1, (h, w, a * 2)))
+    return _quantise(np.clip(cls, -8.9, 8.9)).reshape(h, w, a * num_class), box, dirp
+
+
+def centerpoint_head_outputs(seed, classes_per_head=(1, 2, 2, 1, 2, 2), h=128, w=128, peaks=80):
+    """Per head: hm logits N(-6,1) + Gaussian peaks (sigma 1.5 px, amp +8), center U(0,1), center_z N(-1,.5),
+    dim (log) N(.7,.3), rot unit vectors, vel N(0,2). NCHW planes of one frame."""
+    rng = np.random.default_rng(seed)
+    yy, xx = np.mgrid[0:h, 0:w]
+    heads = []
+    for c in classes_per_head:
+        hm = rng.normal(-6, 1, (c, h, w))
+        for _ in range(max(1, peaks // len(classes_per_head))):
+            k, py, px = rng.integers(0, c), rng.uniform(0, h), rng.uniform(0, w)
+            hm[k] += 8.0 * np.exp(-((yy - py) ** 2 + (xx - px) ** 2) / (2 * 1.5 ** 2))
+        ang = rng.uniform(-np.pi, np.pi, (h, w))
+        heads.append({
+            "hm": _quantise(np.clip(hm, -8.9, 8.9)),
+            "center": rng.uniform(0, 1, (2, h, w)).astype(np.float32),
+            "center_z": rng.normal(-1, 0.5, (1, h, w)).astype(np.float32),
+            "dim": rng.normal(0.7, 0.3, (3, h, w)).astype(np.float32),
+            "rot": np.stack([np.cos(ang), np.sin(ang)]).astype(np.float32),
+            "vel": rng.normal(0, 2, (2, h, w)).astype(np.float32),
+        })
+    return heads
+
+
+def random_boxes7(n, seed, extent=40.0):
+    rng = np.random.default_rng(seed)
+    b = np.zeros((n, 7), np.float32)
+    b[:, 0:2] = rng.uniform(0, extent, (n, 2))
+    b[:, 2] = rng.uniform(-2, 0, n)
+    b[:, 3:6] = rng.uniform(0.5, 5, (n, 3))
+    b[:, 6] = rng.uniform(-4, 4, n)
+    return b
