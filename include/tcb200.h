@@ -105,6 +105,66 @@ int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, int nc, doub
                  double iou_thres, const int* classes_host, int n_classes, int agnostic, int max_det,
                  int max_nms, double* out_dev, int* count_dev, int* xc_count_dev, void* stream);
 
+/* ---- YOLO raw-head decode, YOLOv4-style postprocess, axis-aligned helpers ------ */
+
+/*
+ * Decode one detection head [b, A*(5+nc), h, w] (NCHW, as the network emits it) into rows ordered
+ * (anchor, y, x), written at row_offset of a [b, total_rows, ...] output so that several heads concatenate.
+ * variant 0 — YOLOv4, tools/yolo_layer.py:148-288 (yolo_forward_dynamic; YoloLayer.forward :313-321 divides the
+ *   anchors by the stride first; heads are concatenated by get_region_boxes, tools/torch_utils.py:48-64):
+ *   boxes_dev [b,total_rows,4] = normalised xyxy (the reference's [b,N,1,4]), confs_dev [b,total_rows,nc] =
+ *   sigmoid(cls)*sigmoid(obj). anchors_host = 2*A floats (w,h) already divided by the stride.
+ * variant 1 — YOLOv5 Detect (ultralytics; not in the reference): pred_dev [b,total_rows,5+nc] =
+ *   (xy = (2s-0.5+grid)*stride, wh = (2s)^2*anchor, obj, cls), anchors in pixels — the tensor tcb_yolo_nms takes.
+ */
+int tcb_yolo_head_decode(tcb_ctx* ctx, const float* head_dev, int b, int h, int w, int num_anchors, int num_classes,
+                         const float* anchors_host, int variant, double scale_x_y, float stride, int row_offset,
+                         int total_rows, float* boxes_dev, float* confs_dev, float* pred_dev, void* stream);
+
+/*
+ * numpy greedy NMS of Postprocess.nms_cpu (clients/postprocess/base_postprocess.py:72-106 = utils/postprocess.py:69-103
+ * = tools/utils.py:61-95), float32: order by score descending (ties: lower index first — the reference's
+ * argsort()[::-1] leaves ties unspecified), suppress unless over <= thresh, over = inter/(a_i+a_j-inter) or
+ * inter/min(a_i,a_j) when min_mode. keep_dev[post_max] int32 indices, count_dev[2] = {kept, 1 if n > 4096
+ * (only the 4096 best-scoring boxes are considered)}. post_max <= 1024.
+ */
+int tcb_nms_axis_aligned(tcb_ctx* ctx, const float* boxes_dev, const float* scores_dev, int n, float thresh, int min_mode,
+                         int post_max, int* keep_dev, int* count_dev, void* stream);
+
+/*
+ * YOLOv4 two-tensor postprocess: extract_boxes_onnx (utils/postprocess.py:265-322) / post_processing
+ * (tools/utils.py:166-233): max and first arg-max over classes, keep max > conf_thresh, per-class nms_cpu(nms_thresh),
+ * rows [x1,y1,x2,y2,conf,conf,cls] grouped by class ascending, score descending inside a class.
+ * boxes_dev [b,n,4] (the reference's [b,n,1,4]), confs_dev [b,n,nc]; out_dev [b,post_max,7] f32, count_dev [b].
+ * At most 4096 candidates per image pass the confidence cut into NMS; post_max <= 1024.
+ */
+size_t tcb_yolo4_post_workspace(int b, int n);
+int tcb_yolo4_post(tcb_ctx* ctx, const float* boxes_dev, const float* confs_dev, int b, int n, int nc, float conf_thresh,
+                   float nms_thresh, int post_max, float* out_dev, int* count_dev, void* stream);
+
+/* Pairwise IoU of xyxy boxes, Postprocess.box_iou (clients/postprocess/base_postprocess.py:48-70): out[n,m] f32. */
+int tcb_box_iou(tcb_ctx* ctx, const float* boxes_a_dev, int n, const float* boxes_b_dev, int m, float* out_dev, void* stream);
+
+/*
+ * detectron2 dense-detector inference for one image (RetinaNet variant 0, FCOS variant 1) — the part of the served
+ * model that produces what FCOSpostprocess.extract_boxes unpacks (clients/postprocess/detectron_postprocess.py:26-37,
+ * utils/postprocess.py:368-468; tensors per examples/RetinaNet_detectron/config.pbtxt:13-33). detectron2 is not
+ * vendored by the reference: restated from its published algorithm, parity unpinned.
+ * Per level l: logits [A*K, h_l, w_l], deltas [A*4, h_l, w_l] (FCOS: + centerness [1,h_l,w_l], score =
+ * sqrt(sigmoid(cls)*sigmoid(ctr))); keep score > score_thresh, top-k by score, decode against the anchors
+ * (location*stride + cell anchor; Box2BoxTransform with dw,dh clamped at log(1000/16), or linear ltrb*size for
+ * FCOS); concatenate levels, clip to (img_h,img_w), torchvision batched_nms(nms_thresh), keep max_det.
+ * The `*_dev` level arguments are HOST arrays of device pointers; h, w, strides host int arrays; cell_anchors_host
+ * [num_levels*A*4] (x0,y0,x1,y1). Outputs: boxes [max_det,4], scores [max_det], classes int64 [max_det], count [1].
+ * topk <= 4096; if more than 4096 boxes reach the NMS the lowest-scoring ones are dropped; max_det <= 1024.
+ */
+size_t tcb_detectron_post_workspace(int num_levels, const int* h, const int* w, int num_anchors, int num_classes, int topk);
+int tcb_detectron_post(tcb_ctx* ctx, int num_levels, const float* const* logits_dev, const float* const* deltas_dev,
+                       const float* const* ctrness_dev, const int* h, const int* w, const int* strides, int num_anchors,
+                       int num_classes, const float* cell_anchors_host, int variant, float score_thresh, int topk,
+                       float nms_thresh, int max_det, int img_h, int img_w, float* out_boxes_dev, float* out_scores_dev,
+                       long long* out_classes_dev, int* out_count_dev, void* stream);
+
 /* ---- LiDAR voxelisation + pillar decoration --------------------------------- */
 
 enum { TCB_VOX_CONTINUE = 0, TCB_VOX_BREAK = 1 };
@@ -145,6 +205,21 @@ int tcb_voxelize(tcb_ctx* ctx, const float* pts_dev, int n, int pt_stride, int n
 int tcb_pillar_decorate(tcb_ctx* ctx, const float* voxels_dev, const int* coords_dev, const int* num_pts_dev,
                         const int* m_dev, int m_max, int max_pts, int nfeat, const double vsize[3],
                         const double range_min[3], float* out_dev, void* stream);
+
+/*
+ * Dynamic pillarisation, DynamicPillarVFE.forward up to the PFN layers
+ * (OPCD/pcdet/models/backbones_3d/vfe/dynamic_pillar_vfe.py:90-142): in-grid mask on x,y, pillar key
+ * b*gx*gy + cx*gy + cy, pillars numbered in sorted key order (torch.unique), per-pillar mean of xyz
+ * (torch_scatter.scatter_mean), per-POINT features [point features, xyz - mean, xy - pillar centre, z - z centre].
+ * pts_dev: [n, ncol] rows (batch_idx, x, y, z, extra features...). Outputs for the n_valid in-grid points, input
+ * order kept: feats_dev [n, (ncol-1)+6], unq_inv_dev [n] int64 (pillar id of each point), voxel_coords_dev
+ * [n, 4] int32 (b, 0, y, x) for the n_unique pillars; counts_dev [2] = {n_valid, n_unique}. Pillar means are
+ * accumulated in float64 (order independent to well below one float32 ulp).
+ */
+size_t tcb_dynamic_pillar_workspace(int n, int batch, int gx, int gy);
+int tcb_dynamic_pillar(tcb_ctx* ctx, const float* pts_dev, int n, int ncol, int batch, const double range[6],
+                       const double vsize[3], float* feats_dev, long long* unq_inv_dev, int* voxel_coords_dev,
+                       int* counts_dev, void* stream);
 
 /* ---- 3D detection postprocess ------------------------------------------------ */
 

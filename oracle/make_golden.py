@@ -151,6 +151,30 @@ def golden_box3d():
     save("box3d", **out)
 
 
+def golden_yolo4():
+    """Reference YOLOv4 path run unmodified: tools/yolo_layer.py YoloLayer.forward (-> yolo_forward_dynamic) on small
+    synthetic heads, and utils/postprocess.py extract_boxes_onnx on its output (scores made tie-free)."""
+    rng = np.random.default_rng(404)
+    yl = ref_harness.yolo_layer()
+    up = ref_harness.utils_postprocess()
+    nc, anchors = 4, [12, 16, 19, 36, 40, 28, 36, 75, 76, 55, 72, 146, 142, 110, 192, 243, 459, 401]
+    out = {"anchors": np.array(anchors)}
+    bc = []
+    for hi, (mask, stride, hw) in enumerate([([0, 1, 2], 8, 12), ([3, 4, 5], 16, 6), ([6, 7, 8], 32, 3)]):
+        head = rng.normal(0, 1.5, (2, 3 * (5 + nc), hw, hw)).astype(np.float32)
+        layer = yl.YoloLayer(anchor_mask=mask, num_classes=nc, anchors=anchors, num_anchors=9, stride=stride)
+        layer.eval()
+        b, c = layer(torch.from_numpy(head))
+        out[f"head{hi}"] = head
+        out[f"boxes{hi}"], out[f"confs{hi}"] = b.numpy(), c.numpy()
+        bc.append((b, c))
+    boxes, confs = torch.cat([b for b, _ in bc], 1).numpy(), torch.cat([c for _, c in bc], 1).numpy()
+    res = up.extract_boxes_onnx(0.2, 0.4, [boxes, confs])
+    for i, rows in enumerate(res):
+        out[f"post{i}"] = np.array(rows, dtype=np.float32).reshape(-1, 7)
+    save("yolo4", **out)
+
+
 def main():
     assert ref_harness.available(), "reference not mounted"
     os.makedirs(GOLD, exist_ok=True)

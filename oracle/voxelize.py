@@ -133,3 +133,38 @@ def pillar_decorate(voxels, coords, num_points, voxel_size, point_range):
     mask = torch.unsqueeze(mask, -1).type_as(voxel_features)
     features *= mask
     return features.numpy()
+
+
+# --- reference: OPCD/pcdet/models/backbones_3d/vfe/dynamic_pillar_vfe.py:90-142 (up to the PFN layers) ------
+def dynamic_pillar_vfe(points, voxel_size, point_cloud_range, grid_size):
+    """points (N, 1+F) rows (batch_idx, x, y, z, ...). torch_scatter (absent here) is restated: scatter_mean =
+    index_add of the rows in input order / counts. Returns (features (N', F+6), unq_inv, voxel_coords (U,4))."""
+    points = torch.as_tensor(points, dtype=torch.float32)
+    pc_range = torch.tensor(point_cloud_range).float()
+    vsize = torch.tensor(voxel_size).float()
+    gsize = torch.tensor(grid_size)
+    voxel_x, voxel_y, voxel_z = voxel_size
+    x_offset = voxel_x / 2 + point_cloud_range[0]
+    y_offset = voxel_y / 2 + point_cloud_range[1]
+    z_offset = voxel_z / 2 + point_cloud_range[2]
+    scale_xy, scale_y = grid_size[0] * grid_size[1], grid_size[1]
+    points_coords = torch.floor((points[:, [1, 2]] - pc_range[[0, 1]]) / vsize[[0, 1]]).int()
+    mask = ((points_coords >= 0) & (points_coords < gsize[[0, 1]])).all(dim=1)
+    points = points[mask]
+    points_coords = points_coords[mask]
+    points_xyz = points[:, [1, 2, 3]].contiguous()
+    merge_coords = points[:, 0].int() * scale_xy + points_coords[:, 0] * scale_y + points_coords[:, 1]
+    unq_coords, unq_inv, unq_cnt = torch.unique(merge_coords, return_inverse=True, return_counts=True, dim=0)
+    sums = torch.zeros((unq_coords.shape[0], 3), dtype=torch.float32).index_add_(0, unq_inv, points_xyz)
+    points_mean = sums / unq_cnt.float().unsqueeze(1)
+    f_cluster = points_xyz - points_mean[unq_inv, :]
+    f_center = torch.zeros_like(points_xyz)
+    f_center[:, 0] = points_xyz[:, 0] - (points_coords[:, 0].to(points_xyz.dtype) * voxel_x + x_offset)
+    f_center[:, 1] = points_xyz[:, 1] - (points_coords[:, 1].to(points_xyz.dtype) * voxel_y + y_offset)
+    f_center[:, 2] = points_xyz[:, 2] - z_offset
+    features = torch.cat([points[:, 1:], f_cluster, f_center], dim=-1)
+    unq_coords = unq_coords.int()
+    voxel_coords = torch.stack((unq_coords // scale_xy, (unq_coords % scale_xy) // scale_y, unq_coords % scale_y,
+                                torch.zeros(unq_coords.shape[0]).int()), dim=1)
+    voxel_coords = voxel_coords[:, [0, 3, 2, 1]]
+    return features.numpy(), unq_inv.numpy(), voxel_coords.numpy()

@@ -1,0 +1,50 @@
+"""GPU parity: detectron2-style dense-detector inference (RetinaNet 201 600 anchors / FCOS 22 400 locations at
+800x1333) vs the oracle restatement (parity unpinned: detectron2 is not vendored by the reference)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import detectron_post as dp
+from triton_client_b200 import synth
+
+pytestmark = pytest.mark.gpu
+STRIDES = (8, 16, 32, 64, 128)
+HW = (800, 1333)
+
+
+def _run(engine, logits, deltas, cells, ctr=None, **kw):
+    c = lambda ts: [torch.from_numpy(t).cuda() for t in ts]
+    ob, osc, oc, cnt = engine.detectron_post(c(logits), c(deltas), STRIDES, cells, HW, ctrness=c(ctr) if ctr is not None else None, **kw)
+    k = int(cnt.item())
+    return ob[:k].cpu().numpy(), osc[:k].cpu().numpy(), oc[:k].cpu().numpy()
+
+
+def _check(got, want):
+    assert got[0].shape == want[0].shape and got[0].shape[0] > 10
+    assert np.array_equal(got[2], want[2])
+    np.testing.assert_allclose(got[1], want[1], rtol=1e-5)
+    np.testing.assert_allclose(got[0], want[0], rtol=1e-5, atol=1e-3)
+
+
+@pytest.mark.parametrize("seed", [3001, 3002])
+def test_retinanet_c3(engine, seed):
+    logits, deltas = synth.detectron_head_outputs(seed)
+    cells = dp.retinanet_cell_anchors()
+    assert sum(l.shape[1] * l.shape[2] * 9 for l in logits) == 201600
+    _check(_run(engine, logits, deltas, cells), dp.dense_inference(logits, deltas, STRIDES, cells, HW))
+
+
+def test_fcos_c3(engine):
+    logits, deltas, ctr = synth.detectron_head_outputs(3003, anchors_per_loc=1, fcos=True, planted=400)
+    cells = dp.fcos_cell_anchors(STRIDES)
+    assert sum(l.shape[1] * l.shape[2] for l in logits) == 22400
+    kw = dict(score_thresh=0.2, nms_thresh=0.6)
+    _check(_run(engine, logits, deltas, cells, ctr, **kw), dp.dense_inference(logits, deltas, STRIDES, cells, HW, ctrness=ctr, **kw))
+
+
+def test_many_candidates_and_nothing(engine):
+    logits, deltas = synth.detectron_head_outputs(3004, num_classes=4, planted=3000)
+    cells = dp.retinanet_cell_anchors()
+    _check(_run(engine, logits, deltas, cells, topk=300, max_det=200), dp.dense_inference(logits, deltas, STRIDES, cells, HW, topk=300, max_det=200))
+    empty = [np.full_like(l, -8.0) for l in logits]
+    assert _run(engine, empty, deltas, cells)[0].shape[0] == 0

@@ -106,3 +106,24 @@ def test_decorate_full_size_vs_oracle(engine):
     slot = np.arange(32)[None, :]
     pad = slot >= n[:mm].cpu().numpy()[:, None]
     assert (f[pad] == 0).all() and np.array_equal(f[..., :4][~pad], v[:mm].cpu().numpy()[~pad])
+
+
+def test_dynamic_pillar_vfe_c5(engine):
+    """b7: DynamicPillarVFE decoration on the 10-sweep nuScenes-like cloud, batch of 2."""
+    a, b = synth.lidar_multisweep(51), synth.lidar_multisweep(52)[:150000]
+    pts = np.concatenate([np.concatenate([np.zeros((len(a), 1), np.float32), a], 1),
+                          np.concatenate([np.ones((len(b), 1), np.float32), b], 1)])
+    want_f, want_inv, want_c = ov.dynamic_pillar_vfe(pts, NUSC[1], NUSC[0], [512, 512, 1])
+    f, inv, c, counts = engine.dynamic_pillar(torch.from_numpy(pts).cuda(), NUSC[0], NUSC[1], batch_size=2)
+    nv, nu = (int(v) for v in counts.cpu())
+    assert nv == want_f.shape[0] and nu == want_c.shape[0]
+    assert np.array_equal(inv[:nv].cpu().numpy(), want_inv)
+    assert np.array_equal(c[:nu].cpu().numpy(), want_c)
+    got = f[:nv].cpu().numpy()
+    assert np.array_equal(got[:, :5], want_f[:, :5]) and np.array_equal(got[:, 8:], want_f[:, 8:])   # raw + centre offsets: exact
+    np.testing.assert_allclose(got[:, 5:8], want_f[:, 5:8], rtol=1e-5, atol=2e-5)                  # cluster offsets: mean in f64 vs f32
+
+
+def test_dynamic_pillar_empty(engine):
+    f, inv, c, counts = engine.dynamic_pillar(torch.full((10, 6), 1e4).cuda(), NUSC[0], NUSC[1])
+    assert counts.cpu().tolist() == [0, 0]

@@ -40,11 +40,24 @@ SIGNATURES = {
     "tcb_yolo_nms_workspace": (c_size_t, [c_int, c_int]),
     "tcb_yolo_nms": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_double, c_double, P(c_int), c_int, c_int,
                              c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "tcb_yolo_head_decode": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, P(c_float), c_int, c_double, c_float,
+                                     c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "tcb_nms_axis_aligned": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_float, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "tcb_yolo4_post_workspace": (c_size_t, [c_int, c_int]),
+    "tcb_yolo4_post": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_float, c_int, c_void_p, c_void_p, c_void_p]),
+    "tcb_box_iou": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p]),
+    "tcb_detectron_post_workspace": (c_size_t, [c_int, P(c_int), P(c_int), c_int, c_int, c_int]),
+    "tcb_detectron_post": (c_int, [c_void_p, c_int, P(c_void_p), P(c_void_p), P(c_void_p), P(c_int), P(c_int), P(c_int), c_int, c_int,
+                                   P(c_float), c_int, c_float, c_int, c_float, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                   c_void_p, c_void_p]),
     "tcb_voxelize_workspace": (c_size_t, [c_int, c_int]),
     "tcb_voxelize": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, P(c_double), P(c_double), c_int, c_int, c_int, c_int,
                              c_int, c_float, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "tcb_pillar_decorate": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, P(c_double),
                                     P(c_double), c_void_p, c_void_p]),
+    "tcb_dynamic_pillar_workspace": (c_size_t, [c_int, c_int, c_int, c_int]),
+    "tcb_dynamic_pillar": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, P(c_double), P(c_double), c_void_p, c_void_p, c_void_p,
+                                   c_void_p, c_void_p]),
     "tcb_rotated_iou": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p]),
     "tcb_rotated_nms": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_float, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "tcb_pp_anchor_post_workspace": (c_size_t, [c_int, c_int, c_int, c_int]),

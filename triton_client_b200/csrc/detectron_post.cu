@@ -1,0 +1,221 @@
+// detectron2 dense-detector inference (RetinaNet / FCOS) for one image.
+// In the reference this runs inside the served TorchScript model (examples/RetinaNet_detectron/config.pbtxt:1-34);
+// the client only unpacks its three output tensors (clients/postprocess/detectron_postprocess.py:26-37,
+// utils/postprocess.py:368-468). detectron2 is neither vendored nor pinned: PARITY UNPINNED, restated from its
+// published algorithm — per level sigmoid > score_thresh, top-k, delta decode; levels concatenated, clipped to the
+// image, torchvision-style batched NMS, max_detections kept.
+#include "common.cuh"
+#include "cta_select.cuh"
+#include "cta_nms.cuh"
+
+namespace {
+
+constexpr int T = sel::THREADS;
+constexpr int PRE_CAP = sel::KCAP;
+constexpr int POST_CAP = 1024;
+constexpr int MAX_LEVELS = 8, MAX_ANCHORS = 16;
+
+__device__ __forceinline__ float sigmoidf_ref(float x) { return 1.f / (1.f + expf(-x)); }
+
+struct Level {
+    const float *logits, *deltas, *ctrness;   // [A*K,H,W], [A*4,H,W], FCOS: [1,H,W]
+    int H, W, stride;
+    float cell[MAX_ANCHORS][4];               // cell anchors (x0,y0,x1,y1) around the location
+    unsigned long long* cand; int* cand_count; // this level's candidates (score, flat index in (y,x,a,k) order)
+};
+struct DetParams {
+    Level lv[MAX_LEVELS];
+    int num_levels, A, K, variant, topk, max_det, img_h, img_w;
+    float score_thresh, nms_thresh;
+};
+
+// one thread per logit, NCHW order (coalesced); keeps sigmoid > thresh
+__global__ void __launch_bounds__(256) det_candidates_kernel(const DetParams p, int l) {
+    const Level& L = p.lv[l];
+    const int HW = L.H * L.W;
+    const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    bool ok = false;
+    unsigned long long key = 0ull;
+    if (e < (long long)p.A * p.K * HW) {
+        const int ch = (int)(e / HW), sp = (int)(e - (long long)ch * HW);
+        const int a = ch / p.K, k = ch - a * p.K;
+        float s = sigmoidf_ref(__ldg(L.logits + e));
+        if (p.variant == 1) s = sqrtf(s * sigmoidf_ref(__ldg(L.ctrness + sp)));   // FCOS: sqrt(cls * centerness)
+        ok = s > p.score_thresh;
+        key = sel::make_key(s, (unsigned)(((long long)sp * p.A + a) * p.K + k));
+    }
+    const unsigned em = __ballot_sync(0xffffffffu, ok);
+    if (em) {
+        const int lane = threadIdx.x & 31;
+        int base = 0;
+        if (lane == 0) base = atomicAdd(L.cand_count, __popc(em));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (ok) L.cand[base + __popc(em & ((1u << lane) - 1))] = key;
+    }
+}
+
+struct ABox { float x1, y1, x2, y2, area; int cls; };
+struct TvPred {   // torchvision nms: suppress iff inter/(a_i + a_j - inter) > thr; class handled by offsets or by equality
+    float thresh; int vanilla;
+    __device__ __forceinline__ bool operator()(const ABox& a, const ABox& b) const {
+        if (vanilla && a.cls != b.cls) return false;
+        const float w = fmaxf(0.f, fminf(a.x2, b.x2) - fmaxf(a.x1, b.x1)), h = fmaxf(0.f, fminf(a.y2, b.y2) - fmaxf(a.y1, b.y1));
+        const float inter = w * h;
+        return inter / (a.area + b.area - inter) > thresh;
+    }
+};
+typedef nms::Shared<ABox, POST_CAP, PRE_CAP> DNmsShared;
+struct DFrameShared {
+    unsigned long long skeys[sel::KCAP];
+    ABox R[PRE_CAP];
+    sel::Scratch sel;
+    DNmsShared nms;
+    float red[32];
+    int total;
+};
+
+__global__ void __launch_bounds__(T, 1) det_post_kernel(const DetParams p, float4* __restrict__ mbox, float* __restrict__ mscore,
+                                                        int* __restrict__ mcls, unsigned long long* __restrict__ mkeys,
+                                                        float* __restrict__ out_boxes, float* __restrict__ out_scores,
+                                                        long long* __restrict__ out_classes, int* __restrict__ out_count) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    DFrameShared& S = *reinterpret_cast<DFrameShared*>(smem_raw);
+    const int tid = threadIdx.x;
+    const float scale_clamp = logf(1000.f / 16.f);
+    int M = 0;
+    for (int l = 0; l < p.num_levels; l++) {   // per level: top-k of the survivors, decode, append
+        const Level& L = p.lv[l];
+        const int cap = p.A * p.K * L.H * L.W;
+        const int n = min(*L.cand_count, cap);
+        const unsigned long long* ck = L.cand;
+        auto key_of = [&](int i) { return ck[i]; };
+        const int m = sel::cta_topk_sorted(key_of, n, p.topk, S.skeys, S.sel);
+        const int HW = L.H * L.W;
+        for (int c = tid; c < m; c += T) {
+            const unsigned long long key = S.skeys[c];
+            const unsigned flat = sel::key_index(key);
+            const int k = flat % p.K, a = (flat / p.K) % p.A, sp = flat / (p.K * p.A);
+            const int y = sp / L.W, x = sp - y * L.W;
+            const float d0 = __ldg(L.deltas + (a * 4 + 0) * HW + sp), d1 = __ldg(L.deltas + (a * 4 + 1) * HW + sp);
+            const float d2 = __ldg(L.deltas + (a * 4 + 2) * HW + sp), d3 = __ldg(L.deltas + (a * 4 + 3) * HW + sp);
+            const float sx = (float)(x * L.stride), sy = (float)(y * L.stride);
+            const float ax0 = sx + L.cell[a][0], ay0 = sy + L.cell[a][1], ax1 = sx + L.cell[a][2], ay1 = sy + L.cell[a][3];
+            float4 bx;
+            if (p.variant == 0) {   // Box2BoxTransform.apply_deltas, weights (1,1,1,1)
+                const float w = ax1 - ax0, h = ay1 - ay0, cx = ax0 + 0.5f * w, cy = ay0 + 0.5f * h;
+                const float dw = fminf(d2, scale_clamp), dh = fminf(d3, scale_clamp);
+                const float pcx = d0 * w + cx, pcy = d1 * h + cy, pw = expf(dw) * w, ph = expf(dh) * h;
+                bx = make_float4(pcx - 0.5f * pw, pcy - 0.5f * ph, pcx + 0.5f * pw, pcy + 0.5f * ph);
+            } else {                // Box2BoxTransformLinear(normalize_by_size): distances * anchor size from the centre
+                const float w = ax1 - ax0, h = ay1 - ay0, cx = (ax0 + ax1) / 2, cy = (ay0 + ay1) / 2;
+                const float l0 = fmaxf(d0, 0.f) * w, t0 = fmaxf(d1, 0.f) * h, r0 = fmaxf(d2, 0.f) * w, b0 = fmaxf(d3, 0.f) * h;
+                bx = make_float4(cx - l0, cy - t0, cx + r0, cy + b0);
+            }
+            // Boxes.clip(image_size)
+            bx.x = fminf(fmaxf(bx.x, 0.f), (float)p.img_w); bx.z = fminf(fmaxf(bx.z, 0.f), (float)p.img_w);
+            bx.y = fminf(fmaxf(bx.y, 0.f), (float)p.img_h); bx.w = fminf(fmaxf(bx.w, 0.f), (float)p.img_h);
+            const int g = M + c;
+            mbox[g] = bx; mscore[g] = sel::key_score(key); mcls[g] = k;
+            mkeys[g] = sel::make_key(sel::key_score(key), (unsigned)g);
+        }
+        M += m;
+        __syncthreads();
+    }
+    // torchvision.ops.batched_nms as the served (CUDA) model runs it: coordinate trick unless boxes.numel() > 20000
+    auto mkey_of = [&](int i) { return mkeys[i]; };
+    const int m = sel::cta_topk_sorted(mkey_of, M, PRE_CAP, S.skeys, S.sel);
+    const int vanilla = (long long)M * 4 > 20000 ? 1 : 0;
+    float mx = -INFINITY;
+    for (int c = tid; c < M; c += T) { const float4 b = mbox[c]; mx = fmaxf(mx, fmaxf(fmaxf(b.x, b.y), fmaxf(b.z, b.w))); }
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, s));
+    if ((tid & 31) == 0) S.red[tid >> 5] = mx;
+    __syncthreads();
+    if (tid < 32) {
+        float v = S.red[tid];
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, s));
+        if (tid == 0) S.red[0] = v;
+    }
+    __syncthreads();
+    const float max_coord = S.red[0];
+    for (int c = tid; c < m; c += T) {
+        const int g = (int)sel::key_index(S.skeys[c]);
+        const float4 b = mbox[g];
+        const int cls = mcls[g];
+        const float off = vanilla ? 0.f : (float)cls * (max_coord + 1.f);   // offsets = idxs.to(boxes) * (max_coordinate + 1)
+        ABox r;
+        r.x1 = b.x + off; r.y1 = b.y + off; r.x2 = b.z + off; r.y2 = b.w + off;
+        r.area = (r.x2 - r.x1) * (r.y2 - r.y1);
+        r.cls = cls;
+        S.R[c] = r;
+    }
+    __syncthreads();
+    const int nk = nms::cta_greedy_nms(S.R, m, TvPred{p.nms_thresh, vanilla}, min(p.max_det, POST_CAP), S.nms);
+    for (int k = tid; k < nk; k += T) {
+        const int g = (int)sel::key_index(S.skeys[S.nms.kpos[k]]);
+        const float4 b = mbox[g];
+        out_boxes[k * 4] = b.x; out_boxes[k * 4 + 1] = b.y; out_boxes[k * 4 + 2] = b.z; out_boxes[k * 4 + 3] = b.w;
+        out_scores[k] = mscore[g];
+        out_classes[k] = (long long)mcls[g];
+    }
+    if (tid == 0) *out_count = nk;
+}
+
+}  // namespace
+
+extern "C" size_t tcb_detectron_post_workspace(int num_levels, const int* h, const int* w, int num_anchors, int num_classes, int topk) {
+    size_t bytes = 8192;
+    for (int l = 0; l < num_levels; l++) bytes += (size_t)h[l] * w[l] * num_anchors * num_classes * 8 + 512;
+    bytes += (size_t)num_levels * (size_t)topk * (16 + 4 + 4 + 8) + 2048;
+    return bytes;
+}
+
+extern "C" int tcb_detectron_post(tcb_ctx* ctx, int num_levels, const float* const* logits_dev, const float* const* deltas_dev,
+                                  const float* const* ctrness_dev, const int* h, const int* w, const int* strides, int num_anchors,
+                                  int num_classes, const float* cell_anchors_host, int variant, float score_thresh, int topk,
+                                  float nms_thresh, int max_det, int img_h, int img_w, float* out_boxes_dev, float* out_scores_dev,
+                                  long long* out_classes_dev, int* out_count_dev, void* stream) {
+    TCB_CHECK_CTX(ctx);
+    TCB_REQUIRE(ctx, logits_dev && deltas_dev && h && w && strides && cell_anchors_host && out_boxes_dev && out_scores_dev &&
+                     out_classes_dev && out_count_dev, "tcb_detectron_post: null argument");
+    if (num_levels < 1 || num_levels > MAX_LEVELS || num_anchors < 1 || num_anchors > MAX_ANCHORS)
+        return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_detectron_post: levels %d (<= %d), anchors %d (<= %d)", num_levels, MAX_LEVELS, num_anchors, MAX_ANCHORS);
+    TCB_REQUIRE(ctx, variant == 0 || (variant == 1 && ctrness_dev), "tcb_detectron_post: variant 0 (RetinaNet) or 1 (FCOS, needs centerness)");
+    TCB_REQUIRE(ctx, num_classes >= 1 && topk >= 1 && max_det >= 1 && nms_thresh >= 0.f, "tcb_detectron_post: bad parameters");
+    if (topk > PRE_CAP || (long long)topk * num_levels > 16384) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_detectron_post: topk %d too large", topk);
+    if (max_det > POST_CAP) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_detectron_post: max_det %d > %d", max_det, POST_CAP);
+    cudaStream_t st = (cudaStream_t)stream;
+    DetParams p;
+    memset(&p, 0, sizeof(p));
+    p.num_levels = num_levels; p.A = num_anchors; p.K = num_classes; p.variant = variant; p.topk = topk; p.max_det = max_det;
+    p.img_h = img_h; p.img_w = img_w; p.score_thresh = score_thresh; p.nms_thresh = nms_thresh;
+    TCB_WS(ctx, counts, int, 64);
+    TCB_CUDA(ctx, cudaMemsetAsync(counts, 0, sizeof(int) * 64, st));
+    for (int l = 0; l < num_levels; l++) {
+        Level& L = p.lv[l];
+        L.logits = logits_dev[l]; L.deltas = deltas_dev[l]; L.ctrness = ctrness_dev ? ctrness_dev[l] : nullptr;
+        L.H = h[l]; L.W = w[l]; L.stride = strides[l];
+        TCB_REQUIRE(ctx, L.logits && L.deltas && L.H >= 1 && L.W >= 1 && (variant == 0 || L.ctrness), "tcb_detectron_post: level %d incomplete", l);
+        const long long n = (long long)L.H * L.W * num_anchors * num_classes;
+        if (n > (1ll << 30)) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_detectron_post: level %d too large", l);
+        for (int a = 0; a < num_anchors; a++)
+            for (int j = 0; j < 4; j++) L.cell[a][j] = cell_anchors_host[((size_t)l * num_anchors + a) * 4 + j];
+        TCB_WS(ctx, cand, unsigned long long, n);
+        L.cand = cand; L.cand_count = counts + l;
+    }
+    const size_t mcap = (size_t)num_levels * topk;
+    TCB_WS(ctx, mbox, float4, mcap);
+    TCB_WS(ctx, mscore, float, mcap);
+    TCB_WS(ctx, mcls, int, mcap);
+    TCB_WS(ctx, mkeys, unsigned long long, mcap);
+    for (int l = 0; l < num_levels; l++) {
+        const long long n = (long long)p.lv[l].H * p.lv[l].W * num_anchors * num_classes;
+        det_candidates_kernel<<<tcb_div_up(n, 256), 256, 0, st>>>(p, l);
+        TCB_LAUNCHED(ctx);
+    }
+    TCB_CUDA(ctx, cudaFuncSetAttribute(det_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DFrameShared)));
+    det_post_kernel<<<1, T, sizeof(DFrameShared), st>>>(p, mbox, mscore, mcls, mkeys, out_boxes_dev, out_scores_dev, out_classes_dev, out_count_dev);
+    TCB_LAUNCHED(ctx);
+    return TCB_OK;
+}

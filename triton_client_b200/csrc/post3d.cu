@@ -8,13 +8,13 @@
 #include "common.cuh"
 #include "cta_select.cuh"
 #include "rotated.cuh"
+#include "cta_nms.cuh"
 
 namespace {
 
 constexpr int T = sel::THREADS;
 constexpr int PRE_CAP = sel::KCAP;  // NMS_PRE_MAXSIZE limit (4096: PointPillars' value, data/pointpillar.yaml:141)
 constexpr int POST_CAP = 1024;      // NMS_POST_MAXSIZE limit
-constexpr int ACAP = 64;            // survivors of a greedy round resolved against each other at once
 
 // ---------------------------------------------------------------------------------------------------------
 // rotated IoU matrix  (boxes_iou_bev_kernel, iou3d_nms_kernel.cu:251-265)
@@ -33,95 +33,17 @@ __global__ void __launch_bounds__(256) rotated_iou_kernel(const float* __restric
 //   nms_gpu (iou3d_nms_utils.py:84-99) = nms_kernel bitmask (iou3d_nms_kernel.cu:267-311) + host sweep
 //   (iou3d_nms.cpp:116-132): box i is kept unless an earlier kept box k has iou_bev(k, i) > thresh.
 // ---------------------------------------------------------------------------------------------------------
-struct NmsShared {
-    rot::RBox kept[POST_CAP];
-    int kpos[POST_CAP];                  // sorted position of each kept box
-    unsigned resolved[PRE_CAP / 32];     // bit c: sorted box c is kept or suppressed
-    unsigned long long mask[ACAP];
-    int aidx[ACAP], knew[ACAP];
-    int warp_cnt[32];
-    int nkept, next_pos, a_total;
-};
-
-__device__ __forceinline__ bool rot_suppresses(const rot::RBox& a, const rot::RBox& b, float thresh) {
-    if (rot::far_apart(a, b)) return false;  // the reference's polygon is empty: IoU 0, never > thresh (>= 0)
-    return rot::iou_bev(a, b) > thresh;
-}
-
-__device__ int cta_rotated_nms(const rot::RBox* __restrict__ R, int m, float thresh, int post_max, NmsShared& S) {
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) S.nkept = 0;
-    for (int i = tid; i < PRE_CAP / 32; i += T) S.resolved[i] = 0u;
-    __syncthreads();
-    int pos = 0, prev_end = 0, nk_prev = 0;
-    while (pos < m) {
-        const int cn = min(T, m - pos);
-        const int c = pos + tid;
-        const int nk = S.nkept;
-        bool alive = tid < cn && !((S.resolved[c >> 5] >> (c & 31)) & 1u);
-        if (alive) {  // (1) against the boxes kept since this candidate was last examined
-            const rot::RBox bx = R[c];
-            for (int k = (c < prev_end) ? nk_prev : 0; k < nk; k++)
-                if (rot_suppresses(S.kept[k], bx, thresh)) { alive = false; break; }
-            if (!alive) atomicOr(&S.resolved[c >> 5], 1u << (c & 31));
-        }
-        const unsigned bal = __ballot_sync(0xffffffffu, alive);
-        if (lane == 0) S.warp_cnt[warp] = __popc(bal);
-        __syncthreads();
-        if (warp == 0) {
-            int w = S.warp_cnt[lane];
-#pragma unroll
-            for (int k = 1; k < 32; k <<= 1) { const int t = __shfl_up_sync(0xffffffffu, w, k); if (lane >= k) w += t; }
-            S.warp_cnt[lane] = w;
-            if (lane == 31) { S.a_total = w; S.next_pos = pos + cn; }
-        }
-        __syncthreads();
-        const int rank = (warp ? S.warp_cnt[warp - 1] : 0) + __popc(bal & ((1u << lane) - 1));
-        if (alive) {
-            if (rank < ACAP) S.aidx[rank] = c;
-            else if (rank == ACAP) S.next_pos = c;
-        }
-        __syncthreads();
-        const int A = min(S.a_total, ACAP);
-        {  // (2) suppression mask among the A survivors: 16 threads per row, 4 columns each
-            const int ri = tid >> 4, l16 = tid & 15;
-            unsigned long long bits = 0ull;
-            if (ri < A) {
-                const rot::RBox bi = R[S.aidx[ri]];
-#pragma unroll 1
-                for (int q = 0; q < 4; q++) {
-                    const int j = l16 * 4 + q;
-                    if (j > ri && j < A && rot_suppresses(bi, R[S.aidx[j]], thresh)) bits |= 1ull << j;
-                }
-            }
-#pragma unroll
-            for (int sft = 1; sft < 16; sft <<= 1) bits |= __shfl_xor_sync(0xffffffffu, bits, sft);
-            if (l16 == 0 && ri < ACAP) S.mask[ri] = bits;
-        }
-        __syncthreads();
-        if (tid == 0) {  // (3) serial sweep, hopping from kept survivor to kept survivor
-            unsigned long long avail = A >= 64 ? ~0ull : ((1ull << A) - 1);
-            int kept = nk;
-            while (kept < post_max && avail) {
-                const int i = __ffsll((long long)avail) - 1;
-                avail &= ~(S.mask[i] | (1ull << i));
-                S.knew[kept - nk] = i;
-                kept++;
-            }
-            S.nkept = kept;
-        }
-        __syncthreads();
-        const int nk_new = S.nkept;
-        if (tid < nk_new - nk) { const int cs = S.aidx[S.knew[tid]]; S.kept[nk + tid] = R[cs]; S.kpos[nk + tid] = cs; }
-        if (tid < A) { const int cs = S.aidx[tid]; atomicOr(&S.resolved[cs >> 5], 1u << (cs & 31)); }
-        prev_end = pos + cn; nk_prev = nk;
-        const int np = S.next_pos;
-        __syncthreads();
-        if (nk_new >= post_max) break;
-        pos = np;
+struct RotPred {
+    float thresh;
+    __device__ __forceinline__ bool operator()(const rot::RBox& a, const rot::RBox& b) const {
+        if (rot::far_apart(a, b)) return false;  // the reference's polygon is empty: IoU 0, never > thresh (>= 0)
+        return rot::iou_bev(a, b) > thresh;
     }
-    __syncthreads();
-    return S.nkept;
+};
+typedef nms::Shared<rot::RBox, POST_CAP, PRE_CAP> NmsShared;
+
+__device__ __forceinline__ int cta_rotated_nms(const rot::RBox* __restrict__ R, int m, float thresh, int post_max, NmsShared& S) {
+    return nms::cta_greedy_nms(R, m, RotPred{thresh}, post_max, S);
 }
 
 // shared memory of the one-CTA-per-frame kernels

@@ -284,6 +284,120 @@ __global__ void __launch_bounds__(256) pillar_decorate_kernel(const float* __res
     }
 }
 
+// ---- dynamic pillarisation (b7) --------------------------------------------------------------------
+// DynamicPillarVFE.forward up to the PFN layers (OPCD/pcdet/models/backbones_3d/vfe/dynamic_pillar_vfe.py:90-142):
+// no point cap per pillar; pillars are numbered in sorted key order (torch.unique), which on a dense BEV grid is
+// the exclusive scan of the occupancy flags — no sort needed.
+struct DynParams {
+    const float* pts; int n, ncol;   // rows (batch_idx, x, y, z, features...), ncol = 1 + F
+    float r0x, r0y, vx, vy;          // range min / voxel size as float32 tensors (:83-85)
+    float xo, yo, zo;                // voxel/2 + range_min, Python doubles used as f32 scalars (:76-78)
+    int gx, gy, batch;
+};
+
+__global__ void __launch_bounds__(256) dyn_mark_kernel(const DynParams p, int* __restrict__ valid, int* __restrict__ pkey,
+                                                       int* __restrict__ mark, double* __restrict__ sums, int* __restrict__ cnt) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= p.n) return;
+    const float* row = p.pts + (long long)i * p.ncol;
+    const float x = __ldg(row + 1), y = __ldg(row + 2), z = __ldg(row + 3);
+    const float fx = floorf((x - p.r0x) / p.vx), fy = floorf((y - p.r0y) / p.vy);
+    const int b = (int)__ldg(row);
+    const bool ok = fx >= 0.f && fx < (float)p.gx && fy >= 0.f && fy < (float)p.gy && b >= 0 && b < p.batch;
+    valid[i] = ok ? 1 : 0;
+    if (!ok) { pkey[i] = -1; return; }
+    const int key = b * (p.gx * p.gy) + (int)fx * p.gy + (int)fy;   // merge_coords (:99-101)
+    pkey[i] = key;
+    mark[key] = 1;
+    atomicAdd(&sums[3ll * key], (double)x); atomicAdd(&sums[3ll * key + 1], (double)y); atomicAdd(&sums[3ll * key + 2], (double)z);
+    atomicAdd(&cnt[key], 1);
+}
+
+// block-local exclusive scan of 0/1 flags + per-block totals; offsets are added by the consumers
+__global__ void __launch_bounds__(VB) scan_local_kernel(const int* __restrict__ flags, int n, int* __restrict__ pos, int* __restrict__ blocksum) {
+    __shared__ int sh[32];
+    const int i = blockIdx.x * VB + threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int f = (i < n) ? flags[i] : 0;
+    const unsigned bal = __ballot_sync(0xffffffffu, f != 0);
+    if (lane == 0) sh[warp] = __popc(bal);
+    __syncthreads();
+    if (warp == 0) {
+        int w = sh[lane];
+#pragma unroll
+        for (int k = 1; k < 32; k <<= 1) { const int t = __shfl_up_sync(0xffffffffu, w, k); if (lane >= k) w += t; }
+        sh[lane] = w;
+    }
+    __syncthreads();
+    if (i < n) pos[i] = (warp ? sh[warp - 1] : 0) + __popc(bal & ((1u << lane) - 1));
+    if (threadIdx.x == 0) blocksum[blockIdx.x] = sh[31];
+}
+
+__global__ void __launch_bounds__(1024) scan_blocks_kernel(int nblk, int* __restrict__ blocksum, int* __restrict__ total_out) {
+    __shared__ int sh[32];
+    __shared__ int carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < nblk; base += 1024) {
+        const int i = base + threadIdx.x;
+        const int v = (i < nblk) ? blocksum[i] : 0;
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        int inc = v;
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, s); if (lane >= s) inc += t; }
+        if (lane == 31) sh[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            int w = sh[lane];
+#pragma unroll
+            for (int s = 1; s < 32; s <<= 1) { const int t = __shfl_up_sync(0xffffffffu, w, s); if (lane >= s) w += t; }
+            sh[lane] = w;
+        }
+        __syncthreads();
+        const int prefix = carry + (warp ? sh[warp - 1] : 0) + inc - v;
+        if (i < nblk) blocksum[i] = prefix;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = prefix + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *total_out = carry;
+}
+
+__global__ void __launch_bounds__(256) dyn_features_kernel(const DynParams p, const int* __restrict__ valid, const int* __restrict__ pkey,
+                                                           const int* __restrict__ ppos, const int* __restrict__ pblk,
+                                                           const int* __restrict__ crank, const int* __restrict__ cblk,
+                                                           const double* __restrict__ sums, const int* __restrict__ cnt,
+                                                           float* __restrict__ feats, long long* __restrict__ unq_inv) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= p.n || !valid[i]) return;
+    const int key = pkey[i];
+    const long long o = (long long)ppos[i] + pblk[i / VB];      // row among the in-grid points, input order kept
+    const int u = crank[key] + cblk[key / VB];                   // pillar id = rank of the key among occupied cells
+    const float* row = p.pts + (long long)i * p.ncol;
+    const int F = p.ncol - 1;
+    float* out = feats + o * (F + 6);
+    const float x = __ldg(row + 1), y = __ldg(row + 2), z = __ldg(row + 3);
+    const float fc = (float)cnt[key];
+    const float mx = (float)sums[3ll * key] / fc, my = (float)sums[3ll * key + 1] / fc, mz = (float)sums[3ll * key + 2] / fc;
+    const int within = key % (p.gx * p.gy);
+    const int cx = within / p.gy, cy = within - cx * p.gy;
+    for (int j = 0; j < F; j++) out[j] = __ldg(row + 1 + j);
+    out[F] = x - mx; out[F + 1] = y - my; out[F + 2] = z - mz;
+    out[F + 3] = x - ((float)cx * p.vx + p.xo);
+    out[F + 4] = y - ((float)cy * p.vy + p.yo);
+    out[F + 5] = z - p.zo;
+    unq_inv[o] = (long long)u;
+}
+
+__global__ void __launch_bounds__(256) dyn_coords_kernel(int cells, int gx, int gy, const int* __restrict__ mark, const int* __restrict__ crank,
+                                                         const int* __restrict__ cblk, int* __restrict__ coords) {
+    const int key = blockIdx.x * blockDim.x + threadIdx.x;
+    if (key >= cells || !mark[key]) return;
+    const int u = crank[key] + cblk[key / VB];
+    const int b = key / (gx * gy), within = key - b * (gx * gy), cx = within / gy, cy = within - cx * gy;
+    reinterpret_cast<int4*>(coords)[u] = make_int4(b, 0, cy, cx);   // [:, [0,3,2,1]] of (b, cx, cy, 0)  (:132-138)
+}
+
 int next_pow2(long long v) { int r = 1024; while (r < v) r <<= 1; return r; }
 
 }  // namespace
@@ -391,6 +505,66 @@ extern "C" int tcb_pillar_decorate(tcb_ctx* ctx, const float* voxels_dev, const 
     const float xo = (float)(vsize[0] / 2 + range_min[0]), yo = (float)(vsize[1] / 2 + range_min[1]), zo = (float)(vsize[2] / 2 + range_min[2]);
     pillar_decorate_kernel<<<tcb_div_up((long long)m_max * 32, 256), 256, 0, (cudaStream_t)stream>>>(
         voxels_dev, coords_dev, num_pts_dev, m_dev, m_max, max_pts, nfeat, vx, vy, vz, xo, yo, zo, out_dev);
+    TCB_LAUNCHED(ctx);
+    return TCB_OK;
+}
+
+extern "C" size_t tcb_dynamic_pillar_workspace(int n, int batch, int gx, int gy) {
+    const size_t cells = (size_t)(batch > 0 ? batch : 1) * (size_t)(gx > 0 ? gx : 1) * (size_t)(gy > 0 ? gy : 1);
+    const size_t nn = (size_t)(n > 0 ? n : 1);
+    return nn * 4 * 3 + cells * (4 + 4 + 4 + 24) + (nn / VB + cells / VB + 8) * 4 + 8192;
+}
+
+extern "C" int tcb_dynamic_pillar(tcb_ctx* ctx, const float* pts_dev, int n, int ncol, int batch, const double range[6],
+                                  const double vsize[3], float* feats_dev, long long* unq_inv_dev, int* voxel_coords_dev,
+                                  int* counts_dev, void* stream) {
+    TCB_CHECK_CTX(ctx);
+    TCB_REQUIRE(ctx, range && vsize && feats_dev && unq_inv_dev && voxel_coords_dev && counts_dev, "tcb_dynamic_pillar: null argument");
+    TCB_REQUIRE(ctx, n >= 0 && (n == 0 || pts_dev) && ncol >= 4 && batch >= 1, "tcb_dynamic_pillar: bad shape (n=%d ncol=%d batch=%d)", n, ncol, batch);
+    cudaStream_t st = (cudaStream_t)stream;
+    DynParams p;
+    memset(&p, 0, sizeof(p));
+    p.pts = pts_dev; p.n = n; p.ncol = ncol; p.batch = batch;
+    p.r0x = (float)range[0]; p.r0y = (float)range[1]; p.vx = (float)vsize[0]; p.vy = (float)vsize[1];
+    p.xo = (float)(vsize[0] / 2 + range[0]); p.yo = (float)(vsize[1] / 2 + range[1]); p.zo = (float)(vsize[2] / 2 + range[2]);
+    p.gx = (int)nearbyint((range[3] - range[0]) / vsize[0]);
+    p.gy = (int)nearbyint((range[4] - range[1]) / vsize[1]);
+    TCB_REQUIRE(ctx, p.gx >= 1 && p.gy >= 1, "tcb_dynamic_pillar: empty grid");
+    const long long cells = (long long)batch * p.gx * p.gy;
+    if (cells > (1ll << 24)) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_dynamic_pillar: %lld BEV cells > 2^24", cells);
+    if (n > (1 << 26)) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_dynamic_pillar: more than 2^26 points");
+    const int nn = n > 0 ? n : 1;
+    const int pb = tcb_div_up(nn, VB), cb = tcb_div_up(cells, VB);
+    TCB_WS(ctx, valid, int, nn);
+    TCB_WS(ctx, pkey, int, nn);
+    TCB_WS(ctx, ppos, int, nn);
+    TCB_WS(ctx, pblk, int, pb + 1);
+    TCB_WS(ctx, mark, int, cells);
+    TCB_WS(ctx, cnt, int, cells);
+    TCB_WS(ctx, crank, int, cells);
+    TCB_WS(ctx, cblk, int, cb + 1);
+    TCB_WS(ctx, sums, double, cells * 3);
+    TCB_CUDA(ctx, cudaMemsetAsync(mark, 0, sizeof(int) * cells, st));
+    TCB_CUDA(ctx, cudaMemsetAsync(cnt, 0, sizeof(int) * cells, st));
+    TCB_CUDA(ctx, cudaMemsetAsync(sums, 0, sizeof(double) * cells * 3, st));
+    TCB_CUDA(ctx, cudaMemsetAsync(valid, 0, sizeof(int) * nn, st));
+    if (n > 0) {
+        dyn_mark_kernel<<<tcb_div_up(n, 256), 256, 0, st>>>(p, valid, pkey, mark, sums, cnt);
+        TCB_LAUNCHED(ctx);
+    }
+    scan_local_kernel<<<pb, VB, 0, st>>>(valid, n, ppos, pblk);
+    TCB_LAUNCHED(ctx);
+    scan_blocks_kernel<<<1, 1024, 0, st>>>(pb, pblk, counts_dev);
+    TCB_LAUNCHED(ctx);
+    scan_local_kernel<<<cb, VB, 0, st>>>(mark, (int)cells, crank, cblk);
+    TCB_LAUNCHED(ctx);
+    scan_blocks_kernel<<<1, 1024, 0, st>>>(cb, cblk, counts_dev + 1);
+    TCB_LAUNCHED(ctx);
+    if (n > 0) {
+        dyn_features_kernel<<<tcb_div_up(n, 256), 256, 0, st>>>(p, valid, pkey, ppos, pblk, crank, cblk, sums, cnt, feats_dev, unq_inv_dev);
+        TCB_LAUNCHED(ctx);
+    }
+    dyn_coords_kernel<<<tcb_div_up(cells, 256), 256, 0, st>>>((int)cells, p.gx, p.gy, mark, crank, cblk, voxel_coords_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }

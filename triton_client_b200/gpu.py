@@ -87,6 +87,97 @@ class Engine:
                       _lib.stream_ptr())
         return out, counts[0], counts[1]
 
+    # ---- YOLO head decode, YOLOv4 post, axis-aligned helpers ------------------------------------------
+    def yolo_head_decode_v4(self, heads, anchors_per_head, num_classes, scale_x_y=1.0):
+        """heads: list of CUDA f32 [B, A*(5+nc), H, W]; anchors_per_head: list of flat [w0,h0,w1,h1,...] already divided by
+        the stride (YoloLayer.forward). Returns (boxes [B,N,1,4], confs [B,N,nc]) with the heads concatenated."""
+        b = heads[0].shape[0]
+        rows = [len(a) // 2 * h.shape[2] * h.shape[3] for h, a in zip(heads, anchors_per_head)]
+        total = sum(rows)
+        boxes = torch.empty((b, total, 1, 4), dtype=torch.float32, device=heads[0].device)
+        confs = torch.empty((b, total, num_classes), dtype=torch.float32, device=heads[0].device)
+        off = 0
+        for h, a, r in zip(heads, anchors_per_head, rows):
+            _need_cuda(h)
+            arr = (c_float * len(a))(*[float(v) for v in a])
+            self.ctx.call("tcb_yolo_head_decode", _ptr(h.contiguous()), b, h.shape[2], h.shape[3], len(a) // 2, num_classes, arr, 0,
+                          float(scale_x_y), 1.0, off, total, _ptr(boxes), _ptr(confs), None, _lib.stream_ptr())
+            off += r
+        return boxes, confs
+
+    def yolo_head_decode_v5(self, heads, anchors_per_head, strides, num_classes):
+        """YOLOv5 Detect: heads [B, A*(5+nc), H, W] -> pred [B, N, 5+nc] (the input of yolo_nms); anchors in pixels."""
+        b = heads[0].shape[0]
+        rows = [len(a) // 2 * h.shape[2] * h.shape[3] for h, a in zip(heads, anchors_per_head)]
+        total = sum(rows)
+        pred = torch.empty((b, total, 5 + num_classes), dtype=torch.float32, device=heads[0].device)
+        off = 0
+        for h, a, st, r in zip(heads, anchors_per_head, strides, rows):
+            _need_cuda(h)
+            arr = (c_float * len(a))(*[float(v) for v in a])
+            self.ctx.call("tcb_yolo_head_decode", _ptr(h.contiguous()), b, h.shape[2], h.shape[3], len(a) // 2, num_classes, arr, 1,
+                          1.0, float(st), off, total, None, None, _ptr(pred), _lib.stream_ptr())
+            off += r
+        return pred
+
+    def nms_axis_aligned(self, boxes, scores, thresh=0.5, min_mode=False, post_max=1024):
+        """nms_cpu on the GPU: returns (keep int32 [post_max], count int32 [2] = kept, overflow flag)."""
+        _need_cuda(boxes, scores)
+        b, s = boxes.contiguous().float(), scores.contiguous().float()
+        keep = torch.empty((post_max,), dtype=torch.int32, device=b.device)
+        cnt = torch.zeros((2,), dtype=torch.int32, device=b.device)
+        self.ctx.call("tcb_nms_axis_aligned", _ptr(b), _ptr(s), b.shape[0], float(thresh), 1 if min_mode else 0, int(post_max),
+                      _ptr(keep), _ptr(cnt), _lib.stream_ptr())
+        return keep, cnt
+
+    def yolo4_post(self, boxes, confs, conf_thresh=0.4, nms_thresh=0.6, post_max=1024):
+        """extract_boxes_onnx: boxes [B,N,1,4] (or [B,N,4]), confs [B,N,nc] -> (rows [B,post_max,7], counts [B])."""
+        _need_cuda(boxes, confs)
+        b, n, nc = confs.shape
+        bx = boxes.reshape(b, n, 4).contiguous().float()
+        out = torch.zeros((b, post_max, 7), dtype=torch.float32, device=bx.device)
+        cnt = torch.zeros((b,), dtype=torch.int32, device=bx.device)
+        self.ctx.call("tcb_yolo4_post", _ptr(bx), _ptr(confs.contiguous().float()), b, n, nc, float(conf_thresh), float(nms_thresh),
+                      int(post_max), _ptr(out), _ptr(cnt), _lib.stream_ptr())
+        return out, cnt
+
+    def box_iou(self, box1, box2):
+        _need_cuda(box1, box2)
+        a, b = box1.contiguous().float(), box2.contiguous().float()
+        out = torch.empty((a.shape[0], b.shape[0]), dtype=torch.float32, device=a.device)
+        self.ctx.call("tcb_box_iou", _ptr(a), a.shape[0], _ptr(b), b.shape[0], _ptr(out), _lib.stream_ptr())
+        return out
+
+    def detectron_post(self, logits, deltas, strides, cell_anchors, image_hw, ctrness=None, score_thresh=0.05, topk=1000,
+                       nms_thresh=0.5, max_det=100):
+        """RetinaNet (ctrness None) / FCOS dense-detector inference for one image. logits[l]: CUDA f32 [A*K,H,W],
+        deltas[l]: [A*4,H,W], cell_anchors[l]: A rows (x0,y0,x1,y1). Returns (boxes [max_det,4], scores, classes, count)."""
+        nl = len(logits)
+        a = len(cell_anchors[0])
+        k = logits[0].shape[0] // a
+        keep = [t.contiguous() for t in list(logits) + list(deltas) + (list(ctrness) if ctrness is not None else [])]
+
+        def arr(ts):
+            out = (c_void_p * nl)()
+            for i, t in enumerate(ts):
+                out[i] = t.contiguous().data_ptr()
+            return out
+
+        dev = logits[0].device
+        hs = (c_int * nl)(*[int(t.shape[-2]) for t in logits])
+        ws = (c_int * nl)(*[int(t.shape[-1]) for t in logits])
+        ss = (c_int * nl)(*[int(v) for v in strides])
+        flat = [float(v) for lv in cell_anchors for row in lv for v in row]
+        ca = (c_float * len(flat))(*flat)
+        ob = torch.zeros((max_det, 4), dtype=torch.float32, device=dev)
+        osc = torch.zeros((max_det,), dtype=torch.float32, device=dev)
+        oc = torch.zeros((max_det,), dtype=torch.int64, device=dev)
+        cnt = torch.zeros((1,), dtype=torch.int32, device=dev)
+        self.ctx.call("tcb_detectron_post", nl, arr(keep[:nl]), arr(keep[nl:2 * nl]), arr(keep[2 * nl:]) if ctrness is not None else None,
+                      hs, ws, ss, a, k, ca, 0 if ctrness is None else 1, float(score_thresh), int(topk), float(nms_thresh), int(max_det),
+                      int(image_hw[0]), int(image_hw[1]), _ptr(ob), _ptr(osc), _ptr(oc), _ptr(cnt), _lib.stream_ptr())
+        return ob, osc, oc, cnt
+
     # ---- LiDAR voxelisation + pillar decoration ------------------------------------------------------
     def voxelize(self, points, point_range, voxel_size, max_pts, max_vox, overflow="continue", f64_math=False,
                  range_mask=False, z_offset=0.0, intensity_col=-1, nfeat=None):
@@ -119,6 +210,23 @@ class Engine:
         self.ctx.call("tcb_pillar_decorate", _ptr(voxels), _ptr(coords), _ptr(num_points), _ptr(m) if m is not None else None,
                       mm, p, f, vs, r0, _ptr(out), _lib.stream_ptr())
         return out
+
+    def dynamic_pillar(self, points, point_range, voxel_size, batch_size=1):
+        """DynamicPillarVFE decoration: points f32 CUDA [n, 1+F] (batch_idx, x, y, z, ...). Returns device tensors
+        (features [n, F+6], unq_inv int64 [n], voxel_coords int32 [n,4], counts int32 [2] = n_valid, n_unique)."""
+        _need_cuda(points)
+        pts = points.contiguous().float()
+        n, ncol = pts.shape
+        dev = pts.device
+        feats = torch.empty((max(n, 1), ncol - 1 + 6), dtype=torch.float32, device=dev)
+        inv = torch.empty((max(n, 1),), dtype=torch.int64, device=dev)
+        coords = torch.empty((max(n, 1), 4), dtype=torch.int32, device=dev)
+        counts = torch.zeros((2,), dtype=torch.int32, device=dev)
+        rng = (ctypes.c_double * 6)(*[float(v) for v in point_range])
+        vs = (ctypes.c_double * 3)(*[float(v) for v in voxel_size])
+        self.ctx.call("tcb_dynamic_pillar", _ptr(pts), n, ncol, int(batch_size), rng, vs, _ptr(feats), _ptr(inv), _ptr(coords),
+                      _ptr(counts), _lib.stream_ptr())
+        return feats, inv, coords, counts
 
     # ---- 3D detection postprocess --------------------------------------------------------------------
     def rotated_iou(self, boxes_a, boxes_b):

@@ -153,3 +153,20 @@ def random_boxes7(n, seed, extent=40.0):
     b[:, 3:6] = rng.uniform(0.5, 5, (n, 3))
     b[:, 6] = rng.uniform(-4, 4, n)
     return b
+
+
+# ---- C3 FCOS / RetinaNet head outputs at 800x1333 (padded 800x1344) --------------------------------
+def detectron_head_outputs(seed, anchors_per_loc=9, num_classes=80, image_hw=(800, 1344), strides=(8, 16, 32, 64, 128), planted=60, fcos=False):
+    """Per level l: logits (A*K,H_l,W_l) ~ N(-6,1.5) with planted positives N(+2,1), deltas (A*4,H_l,W_l) ~ N(0,0.4);
+    FCOS adds centerness (1,H_l,W_l) ~ N(0,1). Logits on a 1/64 grid (see _quantise)."""
+    rng = np.random.default_rng(seed)
+    logits, deltas, ctr = [], [], []
+    for s in strides:
+        h, w = -(-image_hw[0] // s), -(-image_hw[1] // s)
+        lg = rng.normal(-6, 1.5, (anchors_per_loc * num_classes, h, w))
+        for _ in range(planted // len(strides) + 1):
+            lg[rng.integers(0, lg.shape[0]), rng.integers(0, h), rng.integers(0, w)] = rng.normal(2, 1)
+        logits.append(_quantise(np.clip(lg, -8.9, 8.9)))
+        deltas.append(rng.normal(0, 0.4, (anchors_per_loc * 4, h, w)).astype(np.float32))
+        ctr.append(_quantise(rng.normal(0, 1, (1, h, w))))
+    return (logits, deltas, ctr) if fcos else (logits, deltas)
