@@ -5,8 +5,10 @@ from .base_client import Client
 from .detectron_client import FCOS_client
 from .postprocess import *  # noqa: F401,F403
 from .preprocess import *  # noqa: F401,F403
+from .detector_3d_client import Pointpillars_client
 from .wire import HostResponse
 
 # north_star spellings
 YOLOv5Client = Yolov5client
 DetectronClient = FCOS_client
+Detector3DClient = Pointpillars_client

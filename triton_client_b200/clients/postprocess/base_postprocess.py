@@ -42,6 +42,21 @@ class Postprocess(ABC):
         y[:, 3] = x[:, 1] + x[:, 3] / 2
         return y
 
+    # base_postprocess.py:48-70 — pairwise IoU, on the GPU (tcb_box_iou); returns a CPU tensor like the reference
+    def box_iou(self, box1, box2):
+        dev = self.engine.device
+        a = torch.as_tensor(box1, dtype=torch.float32).to(dev)
+        b = torch.as_tensor(box2, dtype=torch.float32).to(dev)
+        return self.engine.box_iou(a, b).cpu()
+
+    # base_postprocess.py:72-106 — numpy greedy NMS, on the GPU (tcb_nms_axis_aligned); returns np.array of kept indices
+    def nms_cpu(self, boxes, confs, nms_thresh=0.5, min_mode=False):
+        dev = self.engine.device
+        b = torch.as_tensor(np.asarray(boxes, dtype=np.float32)).to(dev)
+        s = torch.as_tensor(np.asarray(confs, dtype=np.float32)).to(dev)
+        keep, cnt = self.engine.nms_axis_aligned(b, s, nms_thresh, min_mode)
+        return keep[:int(cnt[0].item())].cpu().numpy().astype(np.int64)
+
     @abstractmethod
     def postprocess(self):
         """ """

@@ -1,0 +1,48 @@
+"""Drop-in for clients/preprocess/voxelize.py (det3DPreprocess, the CenterPoint / nuScenes path): zero feature
+column appended, det3d VoxelGenerator semantics ('break' at max_voxels), voxels float32, batch column prepended."""
+import numpy as np
+
+from .base_preprocess import Preprocess
+from .preprocess_3d import PointpillarPreprocess  # noqa: F401  (same engine plumbing)
+from .. import wire
+
+# data/nusc_centerpoint_pp_02voxel_two_pfn_10sweep.py:138-143 of the reference
+_NUSC_DEFAULT = dict(range=[-51.2, -51.2, -5.0, 51.2, 51.2, 3.0], voxel_size=[0.2, 0.2, 8], max_points_in_voxel=20, max_voxel_num=[20000, 60000])
+
+
+class det3DPreprocess(Preprocess):
+    def __init__(self, cfg=None, engine=None, f64_math=True, **overrides):
+        c = dict(_NUSC_DEFAULT)
+        c.update(overrides)
+        self._engine = engine
+        self._stager = None
+        self.range = c["range"]
+        self.voxel_size = c["voxel_size"]
+        self.max_points_in_voxel = c["max_points_in_voxel"]
+        self.max_voxel_num = c["max_voxel_num"]
+        # the reference hands det3d a float64 array (np.concatenate with a float64 zero column, voxelize.py:38-39), so its
+        # cell indices are computed in double; f64_math=False gives the float32 arithmetic of a .bin / Triton FP32 pipeline
+        self.f64_math = f64_math
+
+    @property
+    def engine(self):
+        if self._engine is None:
+            self._engine = wire.default_engine()
+        return self._engine
+
+    def preprocess(self):
+        pass
+
+    def filter_pc_device(self, pointcloud_array):
+        import torch
+        pts = np.ascontiguousarray(pointcloud_array, dtype=np.float32)
+        pts = np.concatenate((pts, np.zeros((pts.shape[0], 1), np.float32)), axis=1)      # voxelize.py:38-39
+        dev = torch.from_numpy(pts).to(self.engine.device)
+        return self.engine.voxelize(dev, self.range, self.voxel_size, self.max_points_in_voxel, self.max_voxel_num[0],   # [0] as the reference (:23)
+                                    overflow="break", f64_math=self.f64_math)
+
+    def filter_pc(self, pointcloud_array):
+        voxels, coords, num, m = self.filter_pc_device(pointcloud_array)
+        m = int(m.item())
+        self.points = [voxels[:m].cpu().numpy().astype(np.float32), coords[:m].cpu().numpy(), num[:m].cpu().numpy()]
+        return self.points

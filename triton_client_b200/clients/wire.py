@@ -75,8 +75,12 @@ class Stager:
             if isinstance(raw, np.ndarray):
                 arr = np.ascontiguousarray(raw)
                 host = torch.from_numpy(arr.view(np.uint8).reshape(-1))
-            else:
-                host = torch.frombuffer(memoryview(raw), dtype=torch.uint8) if len(raw) else torch.empty(0, dtype=torch.uint8)
+            else:   # bytes / bytearray / memoryview straight from gRPC: one memcpy into the pinned buffer
+                arr = np.frombuffer(raw, dtype=np.uint8)
+                stage = self.pinned(key, arr.size)
+                if arr.size:
+                    stage.numpy()[:] = arr
+                return stage.to(self.device, non_blocking=True).view(tdtype).reshape(shape)
         stage = self.pinned(key, host.numel())
         stage.copy_(host)
         return stage.to(self.device, non_blocking=True).view(tdtype).reshape(shape)
