@@ -153,3 +153,16 @@ def test_utils_and_tools_twins(engine):
     sc = np.random.default_rng(2).permutation(30).astype(np.float32)
     assert np.array_equal(up.nms_cpu(bx, sc, 0.3), yolo_post.nms_cpu(bx, sc, 0.3))
     assert torch.equal(up.box_iou(torch.from_numpy(bx), torch.from_numpy(bx[:5])), yolo_post.box_iou(torch.from_numpy(bx), torch.from_numpy(bx[:5])))
+
+
+def test_pipelined_batch_equals_single_shot(engine):
+    """image_adjust_batch cuts big batches into chunks over three streams; results must not depend on that."""
+    pre = Yolov5client(engine=engine).get_preprocess()
+    frames = np.stack([synth.image_noise(180, 320, 900 + i) for i in range(19)])          # 19: ragged last chunk
+    a = pre.image_adjust_batch(frames, (160, 160), mode="letterbox", chunks=4)
+    b = pre.image_adjust_batch(torch.from_numpy(frames).pin_memory(), (160, 160), mode="letterbox", chunks=1)
+    c = pre.image_adjust_batch(frames, (160, 160), mode="letterbox", chunks=4, copy=False)
+    want = np.concatenate([pre2d.preprocess_frame(f, 160, 160, mode="letterbox") for f in frames])
+    assert np.array_equal(a, want) and np.array_equal(b, want) and np.array_equal(c, want)
+    a2 = pre.image_adjust_batch(frames[::-1].copy(), (160, 160), mode="letterbox", chunks=4)   # buffers reused across calls
+    assert np.array_equal(a2, want[::-1])

@@ -47,13 +47,76 @@ class _ImagePreprocess(Preprocess):
         dev, aff = self.image_adjust_device(cv_image[None] if cv_image.ndim == 3 else cv_image, size_hw, mode, swap, pad_value)
         return self.stager.to_host(dev, "pre_out"), aff
 
-    def image_adjust_batch(self, frames, size_hw=None, mode="stretch", swap=False, pad_value=114, copy=True):
+    def image_adjust_batch(self, frames, size_hw=None, mode="stretch", swap=False, pad_value=114, copy=True, chunks=8):
         """frames: (n,h,w,3) uint8 host array/tensor -> (n,3,H,W) float32 host ndarray.
-        copy=False hands back a view of the pinned staging buffer (valid until the next call)."""
+        copy=False hands back a view of the pinned staging buffer (valid until the next call).
+        Large batches are cut into `chunks` pieces that flow through three streams (H2D, kernel, D2H), so the
+        upload of chunk k+1 overlaps the download of chunk k on the full-duplex PCIe link."""
         if size_hw is None:
             size_hw = tuple(frames.shape[1:3])
-        dev, _ = self.image_adjust_device(frames, size_hw, mode, swap, pad_value)
-        return self.stager.to_host(dev, "pre_out", copy=copy)
+        n = int(frames.shape[0])
+        if n < 2 * chunks or chunks < 2:
+            dev, _ = self.image_adjust_device(frames, size_hw, mode, swap, pad_value)
+            return self.stager.to_host(dev, "pre_out", copy=copy)
+        return self._pipelined_batch(frames, size_hw, mode, swap, pad_value, copy, chunks)
+
+    def _pipelined_batch(self, frames, size_hw, mode, swap, pad_value, copy, chunks):
+        eng, st = self.engine, self.stager
+        dev = eng.device
+        n, h, w, _ = (int(v) for v in frames.shape)
+        oh, ow = int(size_hw[0]), int(size_hw[1])
+        if isinstance(frames, np.ndarray):
+            src = torch.from_numpy(np.ascontiguousarray(frames))
+        else:
+            src = frames.contiguous()
+        if not src.is_pinned():   # pageable source: stage it once (a pinned caller buffer avoids this memcpy)
+            pin = st.pinned("pre_in_host", src.numel()).view(n, h, w, 3)
+            pin.copy_(src)
+            src = pin
+        host_out = st.pinned("pre_out", n * 3 * oh * ow * 4).view(torch.float32).view(n, 3, oh, ow)
+        if getattr(self, "_streams", None) is None:
+            self._streams = (torch.cuda.Stream(dev), torch.cuda.Stream(dev), torch.cuda.Stream(dev))
+        s_in, s_cmp, s_out = self._streams
+        per = (n + chunks - 1) // chunks
+        key = (per, h, w, oh, ow)
+        if getattr(self, "_pipe_key", None) != key:
+            self._pipe_in = [torch.empty((per, h, w, 3), dtype=torch.uint8, device=dev) for _ in range(2)]
+            self._pipe_out = [torch.empty((per, 3, oh, ow), dtype=torch.float32, device=dev) for _ in range(2)]
+            self._pipe_key = key
+        cur = torch.cuda.current_stream(dev)
+        for s in self._streams:
+            s.wait_stream(cur)
+        ev_cmp, ev_out = [], []
+        for k in range(chunks):
+            a, b = k * per, min(n, (k + 1) * per)
+            if a >= b:
+                break
+            m = b - a
+            din, dout = self._pipe_in[k % 2], self._pipe_out[k % 2]
+            with torch.cuda.stream(s_in):
+                if k >= 2:
+                    s_in.wait_event(ev_cmp[k - 2])      # the kernel that last read this input buffer is done
+                din[:m].copy_(src[a:b], non_blocking=True)
+                e_in = torch.cuda.Event()
+                e_in.record(s_in)
+            with torch.cuda.stream(s_cmp):
+                s_cmp.wait_event(e_in)
+                if k >= 2:
+                    s_cmp.wait_event(ev_out[k - 2])     # the download that last read this output buffer is done
+                eng.preprocess_images(din[:m], oh, ow, mode=mode, swap=swap, div=self.DIV, pad_value=pad_value, out=dout[:m])
+                e_c = torch.cuda.Event()
+                e_c.record(s_cmp)
+                ev_cmp.append(e_c)
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(e_c)
+                host_out[a:b].copy_(dout[:m], non_blocking=True)
+                e_o = torch.cuda.Event()
+                e_o.record(s_out)
+                ev_out.append(e_o)
+        s_out.synchronize()
+        cur.wait_stream(s_cmp)
+        res = host_out.numpy()
+        return res.copy() if copy else res
 
     def image_adjust_device(self, frames, size_hw, mode="stretch", swap=False, pad_value=114, out=None):
         """Same, result left on the device (torch CUDA tensor) for callers that keep going on the GPU."""
