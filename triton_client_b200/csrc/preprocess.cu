@@ -32,6 +32,9 @@ struct PreParams {
     int th;     // output rows per tile (8, 16 or 32)
     int pitch;  // shared-memory row pitch in bytes (multiple of 16)
     int tpr_shift;  // log2(threads cooperating on one staged row)
+    int stage_bytes, hs_bytes, nr_cap;  // two-pass kernel: staged-byte area, 16-bit row buffer (3 planes x nr_cap rows x TW)
+    float rlo;  // float32 residual of 1/div (two-instruction exact division)
+    int exact2;  // fma(v, rdiv, v*rlo) == v/div for all 256 inputs
     int vec_store;
 };
 
@@ -52,25 +55,32 @@ __device__ __forceinline__ float norm_px(int v, float div, float rdiv, float sub
 
 // OpenCV resizeLinear column taps for destination column dx (modules/imgproc resize.cpp semantics,
 // restated from its documented behaviour: half-pixel centres, clamp to edge with zero weight, 11-bit taps).
-__device__ __forceinline__ void x_tap(int dx, double scale, int w, int& sx, int& a0, int& a1) {
+__host__ __device__ __forceinline__ int round_i(float v) {
+#ifdef __CUDA_ARCH__
+    return __float2int_rn(v);
+#else
+    return (int)nearbyintf(v);   // default rounding mode: ties to even, like cvRound
+#endif
+}
+__host__ __device__ __forceinline__ void x_tap(int dx, double scale, int w, int& sx, int& a0, int& a1) {
     float f = (float)(((double)dx + 0.5) * scale - 0.5);
     int s = (int)floorf(f);
     f -= (float)s;
     if (s < 0) { f = 0.f; s = 0; }
     if (s >= w - 1) { f = 0.f; s = w - 1; }
-    a0 = __float2int_rn((1.f - f) * 2048.f);
-    a1 = __float2int_rn(f * 2048.f);
+    a0 = round_i((1.f - f) * 2048.f);
+    a1 = round_i(f * 2048.f);
     sx = s;
 }
 // Row taps: weights are NOT clamped, only the two row indices are (so border rows blend a row with itself).
-__device__ __forceinline__ void y_tap(int dy, double scale, int h, int& r0, int& r1, int& b0, int& b1) {
+__host__ __device__ __forceinline__ void y_tap(int dy, double scale, int h, int& r0, int& r1, int& b0, int& b1) {
     float f = (float)(((double)dy + 0.5) * scale - 0.5);
     int s = (int)floorf(f);
     f -= (float)s;
-    b0 = __float2int_rn((1.f - f) * 2048.f);
-    b1 = __float2int_rn(f * 2048.f);
-    r0 = min(max(s, 0), h - 1);
-    r1 = min(max(s + 1, 0), h - 1);
+    b0 = round_i((1.f - f) * 2048.f);
+    b1 = round_i(f * 2048.f);
+    r0 = s < 0 ? 0 : (s > h - 1 ? h - 1 : s);
+    r1 = s + 1 < 0 ? 0 : (s + 1 > h - 1 ? h - 1 : s + 1);
 }
 
 // Rows of one warp. INTERIOR: every pixel of the lane's 4 columns and every row lies inside the content
@@ -270,6 +280,251 @@ __global__ void __launch_bounds__(NTHREADS) preprocess_kernel(const PreParams p)
     else tile_rows<AREA, STAGED, EXACT, false>(p, smem, img, z, ox0, ty0, warp, xmin, rmin, has_content, off0, d1, a0, a1, inx);
 }
 
+// -------------------------------------------------------------------------------------------------------------
+// Two-pass tile kernel (the staged path): like OpenCV itself, first the horizontal pass of every staged source row
+// into a 16-bit row buffer, then the vertical pass. Compared with recomputing the horizontal taps per output row this
+// halves the byte loads, and the vertical pass reads 12 consecutive 16-bit values per lane with 8-byte loads.
+//   stage : cp.async 16-byte copies of the footprint (all in flight at once), tap tables built meanwhile
+//   pass H: thread = (column, row parity): hs[r][x*3+c] = (p0*a0 + p1*a1) >> 4        (AREA: p0 + p1)
+//   pass V: warp = output rows, lane = 4 columns: v = (umulhi(b0<<16, h0) + umulhi(b1<<16, h1) + 2) >> 2
+//           (AREA: (h0 + h1 + 2) >> 2), normalise, three 16-byte streaming stores per row
+// -------------------------------------------------------------------------------------------------------------
+struct XTap { int off; short a0, a1; };          // byte offset of the left tap inside the staged row; weights
+struct YTap { int r0, r1; unsigned b0s, b1s; };  // staged-row indices; weights << 16; r0 < 0: row outside the content
+
+
+// Source footprint of every tile column / tile row, computed once on the host with the same tap arithmetic
+// (count 0 = no content in that tile column/row). Passed by value with the kernel parameters.
+constexpr int GEO_MAX_TX = 64, GEO_MAX_TY = 1024;
+struct TileGeo {
+    int xmin[GEO_MAX_TX]; short xcnt[GEO_MAX_TX];
+    int rmin[GEO_MAX_TY]; short rcnt[GEO_MAX_TY];
+    int first_ty, last_ty;   // first / last tile row with content (the only ones that can touch the ends of the caller's buffer)
+};
+
+struct TileHdr { int xmin, xmax, rmin, rmax, has_content, interior, safe; };
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned phase) {
+    unsigned done = 0;
+    while (!done) {
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                     : "=r"(done) : "r"(smem_u32(bar)), "r"(phase) : "memory");
+    }
+}
+
+// u8 -> normalised f32 with two FP instructions when the host has verified, for all 256 inputs, that
+// fma(v, r, fl(v*rlo)) == v/div (r = fl(1/div), rlo = its float32 residual); otherwise the IEEE division.
+template <bool EXACT, bool HAS_SUB>
+__device__ __forceinline__ float norm2(int v, float div, float r, float rlo, float sub) {
+    const float f = (float)v;
+    float q = EXACT ? __fmaf_rn(f, r, f * rlo) : f / div;
+    if (HAS_SUB) q = q - sub;
+    return q;
+}
+
+template <bool AREA, bool EXACT, bool HAS_SUB, bool INTERIOR>
+__device__ __forceinline__ void pass_v(const PreParams& p, const unsigned short* __restrict__ hs, const XTap* __restrict__ xt,
+                                       const YTap* __restrict__ yt, int nr_cap, int z, int tx0, int ty0) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int ox0 = tx0 + lane * 4;
+    if (ox0 >= p.out_w) return;
+    bool inx[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) inx[i] = INTERIOR || xt[lane * 4 + i].off >= 0;
+    const int rpw = p.th >> 3;
+    const long long plane = (long long)p.out_h * p.out_w;
+    float* d0 = p.dst + ((long long)z * 3) * plane + (long long)(ty0 + warp * rpw) * p.out_w + ox0;
+    for (int rr = 0; rr < rpw; rr++, d0 += p.out_w) {
+        const int j = warp * rpw + rr;
+        if (ty0 + j >= p.out_h) break;
+        const YTap y = yt[j];
+        const bool iny = INTERIOR || y.r0 >= 0;
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            const int cc = p.swap ? 2 - c : c;   // destination plane of source channel c
+            float o[4];
+            if (iny) {
+                const uint2 a = *reinterpret_cast<const uint2*>(hs + (c * nr_cap + y.r0) * TW + lane * 4);
+                const uint2 b = *reinterpret_cast<const uint2*>(hs + (c * nr_cap + y.r1) * TW + lane * 4);
+                const unsigned av[4] = {a.x & 0xffffu, a.x >> 16, a.y & 0xffffu, a.y >> 16};
+                const unsigned bv[4] = {b.x & 0xffffu, b.x >> 16, b.y & 0xffffu, b.y >> 16};
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const int v = AREA ? (int)((av[i] + bv[i] + 2u) >> 2) : (int)((__umulhi(y.b0s, av[i]) + __umulhi(y.b1s, bv[i]) + 2u) >> 2);
+                    o[i] = (INTERIOR || inx[i]) ? norm2<EXACT, HAS_SUB>(v, p.div, p.rdiv, p.rlo, p.sub[cc]) : p.padv[cc];
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; i++) o[i] = p.padv[cc];
+            }
+            float* d = d0 + cc * plane;
+            if (p.vec_store) {
+                st_stream_f4(d, make_float4(o[0], o[1], o[2], o[3]));
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; i++)
+                    if (ox0 + i < p.out_w) d[i] = o[i];
+            }
+        }
+    }
+}
+
+template <bool AREA, bool EXACT, bool HAS_SUB>
+__global__ void __launch_bounds__(NTHREADS) preprocess2_kernel(const PreParams p, const TileGeo geo) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    const int tid = threadIdx.x;
+    const int z = blockIdx.z;
+    const int tx0 = blockIdx.x * TW, ty0 = blockIdx.y * p.th;
+    const uint8_t* img = p.src + (long long)z * p.img_stride;
+    // shared layout: staged bytes | hs (u16, 3 planes x nr_cap rows x TW) | x taps | y taps | mbarrier
+    uint8_t* stg = smem;
+    unsigned short* hs = reinterpret_cast<unsigned short*>(smem + p.stage_bytes);
+    XTap* xt = reinterpret_cast<XTap*>(smem + p.stage_bytes + p.hs_bytes);
+    YTap* yt = reinterpret_cast<YTap*>(xt + TW);
+    unsigned long long* bar = reinterpret_cast<unsigned long long*>(yt + 32);
+    const int nr_cap = p.nr_cap;
+
+    // ---- tile geometry from the host table (no arithmetic here) ----------------------------------------------------
+    TileHdr H;
+    H.xmin = geo.xmin[blockIdx.x]; H.rmin = geo.rmin[blockIdx.y];
+    const int xcnt = geo.xcnt[blockIdx.x], rcnt = geo.rcnt[blockIdx.y];
+    H.has_content = xcnt > 0 && rcnt > 0;
+    H.xmax = H.xmin + xcnt - 1; H.rmax = H.rmin + rcnt - 1;
+    H.interior = H.has_content && (tx0 - p.left >= 0) && (tx0 + TW - 1 - p.left < p.new_w) && (tx0 + TW <= p.out_w) &&
+                 (ty0 - p.top >= 0) && (ty0 + p.th - 1 - p.top < p.new_h) && (ty0 + p.th <= p.out_h);
+    // 16-byte-granular copies can only leave the caller's buffer before its first / after its last content row
+    H.safe = !((z == 0 && (int)blockIdx.y == geo.first_ty) || (z == (int)gridDim.z - 1 && (int)blockIdx.y == geo.last_ty));
+    const int nrows = H.has_content ? rcnt : 0;
+    const int seg = xcnt * 3;
+
+    // ---- stage the footprint: one bulk async copy (TMA unit) per source row, completion on an mbarrier ----------------
+    if (tid == 0 && H.has_content && H.safe) mbar_init(bar, nrows);
+    __syncthreads();
+    if (H.has_content) {
+        if (H.safe) {
+            for (int r = tid; r < nrows; r += NTHREADS) {   // one arrival + one bulk copy per row (barrier count == nrows)
+                const uint8_t* a = img + (long long)(H.rmin + r) * p.row_stride + (long long)H.xmin * 3;
+                const uint8_t* g = (const uint8_t*)((uintptr_t)a & ~(uintptr_t)15);
+                const unsigned bytes = (unsigned)(((a + seg) - g + 15) & ~(long long)15);
+                mbar_arrive_expect_tx(bar, bytes);
+                bulk_g2s(stg + r * p.pitch, g, bytes, bar);
+            }
+        } else {   // tiles touching the ends of the caller's buffer: chunk by chunk, never reading outside it
+            const int k = tid & ((1 << p.tpr_shift) - 1);
+            const int rstep = NTHREADS >> p.tpr_shift;
+            if (k < (p.pitch >> 4)) {
+                for (int r = tid >> p.tpr_shift; r < nrows; r += rstep) {
+                    const uint8_t* a = img + (long long)(H.rmin + r) * p.row_stride + (long long)H.xmin * 3;
+                    const uint8_t* g = (const uint8_t*)((uintptr_t)a & ~(uintptr_t)15) + 16 * k;
+                    if (g >= a + seg) continue;
+                    uint8_t t[16];
+#pragma unroll
+                    for (int i = 0; i < 16; i++) t[i] = (g + i >= p.src && g + i < p.batch_end) ? g[i] : 0;
+                    *reinterpret_cast<uint4*>(stg + r * p.pitch + 16 * k) = *reinterpret_cast<uint4*>(t);
+                }
+            }
+        }
+    }
+    // ---- tap tables (overlap the copies) ---------------------------------------------------------------------------
+    if (tid >= NTHREADS - TW) {
+        const int c = tid - (NTHREADS - TW);
+        const int dx = tx0 + c - p.left;
+        XTap e; e.off = -1; e.a0 = 0; e.a1 = 0;
+        if (H.has_content && dx >= 0 && dx < p.new_w && tx0 + c < p.out_w) {
+            if (AREA) { e.off = (2 * dx - H.xmin) * 3; e.a0 = 1; e.a1 = 1; }
+            else {
+                int s, a0, a1;
+                x_tap(dx, p.scale_x, p.w, s, a0, a1);
+                e.off = (s - H.xmin) * 3; e.a0 = (short)a0; e.a1 = (short)a1;   // s == w-1 has a1 == 0: the right tap may read padding
+            }
+        }
+        xt[c] = e;
+    } else if (tid >= NTHREADS - TW - p.th) {
+        const int j = tid - (NTHREADS - TW - p.th);
+        const int dy = ty0 + j - p.top;
+        YTap e; e.r0 = -1; e.r1 = -1; e.b0s = 0; e.b1s = 0;
+        if (H.has_content && dy >= 0 && dy < p.new_h && ty0 + j < p.out_h) {
+            if (AREA) { e.r0 = 2 * dy - H.rmin; e.r1 = 2 * dy + 1 - H.rmin; }
+            else {
+                int r0, r1, b0, b1;
+                y_tap(dy, p.scale_y, p.h, r0, r1, b0, b1);
+                e.r0 = r0 - H.rmin; e.r1 = r1 - H.rmin; e.b0s = (unsigned)b0 << 16; e.b1s = (unsigned)b1 << 16;
+            }
+        }
+        yt[j] = e;
+    }
+    if (H.has_content && H.safe) mbar_wait(bar, 0);
+    __syncthreads();
+
+    // ---- pass H: thread = (column, row parity); 6 source bytes per row come in as three aligned words -----------------
+    {
+        const int col = tid & (TW - 1), par = tid >> 7;  // NTHREADS == 2*TW
+        const XTap e = xt[col];
+        if (e.off >= 0) {
+            const unsigned wts = (unsigned)(unsigned short)e.a0 | ((unsigned)(unsigned short)e.a1 << 16);
+            unsigned addr0 = (unsigned)((uintptr_t)(img + (long long)(H.rmin + par) * p.row_stride + (long long)H.xmin * 3) & 15u);
+            const unsigned astep = (unsigned)((2 * p.row_stride) & 15);
+            unsigned short* d = hs + par * TW + col;
+            const int plane = nr_cap * TW;
+            if (astep == 0 && (p.row_stride & 15) == 0) {
+                // every staged row has the same alignment shift: constant word offset and funnel distance
+                const unsigned b = addr0 + (unsigned)e.off;
+                const unsigned* w = reinterpret_cast<const unsigned*>(stg + par * p.pitch + (b & ~3u));
+                const unsigned sh = (b & 3u) * 8u;
+                const int wstep = (2 * p.pitch) >> 2;
+                for (int r = par; r < nrows; r += 2, w += wstep, d += 2 * TW) {
+                    const unsigned x0 = __funnelshift_r(w[0], w[1], sh), x1 = __funnelshift_r(w[1], w[2], sh);
+                    const unsigned p0 = __byte_perm(x0, x1, 0x4430), p1 = __byte_perm(x0, x1, 0x4441), p2 = __byte_perm(x0, x1, 0x4452);
+                    if (AREA) {
+                        d[0] = (unsigned short)((p0 & 0xff) + ((p0 >> 8) & 0xff));
+                        d[plane] = (unsigned short)((p1 & 0xff) + ((p1 >> 8) & 0xff));
+                        d[2 * plane] = (unsigned short)((p2 & 0xff) + ((p2 >> 8) & 0xff));
+                    } else {
+                        d[0] = (unsigned short)(__dp2a_lo(wts, p0, 0u) >> 4);
+                        d[plane] = (unsigned short)(__dp2a_lo(wts, p1, 0u) >> 4);
+                        d[2 * plane] = (unsigned short)(__dp2a_lo(wts, p2, 0u) >> 4);
+                    }
+                }
+            } else {
+                for (int r = par; r < nrows; r += 2, addr0 = (addr0 + astep) & 15u, d += 2 * TW) {
+                    const unsigned b = (unsigned)(r * p.pitch) + addr0 + (unsigned)e.off;   // byte offset of the left tap in the staged area
+                    const unsigned* w = reinterpret_cast<const unsigned*>(stg + (b & ~3u));
+                    const unsigned sh = (b & 3u) * 8u;
+                    const unsigned x0 = __funnelshift_r(w[0], w[1], sh), x1 = __funnelshift_r(w[1], w[2], sh);   // bytes b..b+3, b+4..b+7
+                    // (left, right) taps of channel c are bytes c and c+3
+                    const unsigned p0 = __byte_perm(x0, x1, 0x4430), p1 = __byte_perm(x0, x1, 0x4441), p2 = __byte_perm(x0, x1, 0x4452);
+                    if (AREA) {
+                        d[0] = (unsigned short)((p0 & 0xff) + ((p0 >> 8) & 0xff));
+                        d[plane] = (unsigned short)((p1 & 0xff) + ((p1 >> 8) & 0xff));
+                        d[2 * plane] = (unsigned short)((p2 & 0xff) + ((p2 >> 8) & 0xff));
+                    } else {
+                        d[0] = (unsigned short)(__dp2a_lo(wts, p0, 0u) >> 4);
+                        d[plane] = (unsigned short)(__dp2a_lo(wts, p1, 0u) >> 4);
+                        d[2 * plane] = (unsigned short)(__dp2a_lo(wts, p2, 0u) >> 4);
+                    }
+                }
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- pass V: warp = output rows, lane = 4 columns ---------------------------------------------------------------
+    if (H.interior) pass_v<AREA, EXACT, HAS_SUB, true>(p, hs, xt, yt, nr_cap, z, tx0, ty0);
+    else pass_v<AREA, EXACT, HAS_SUB, false>(p, hs, xt, yt, nr_cap, z, tx0, ty0);
+}
+
 int iround_half_even(double v) { return (int)nearbyint(v); }  // python round() == ties-to-even
 
 }  // namespace
@@ -334,15 +589,22 @@ extern "C" int tcb_preprocess_image(tcb_ctx* ctx, const uint8_t* src_dev, int n,
         float q = fmaf(fmaf(-q0, div, f), p.rdiv, q0);
         if (q != f / div) { p.exact_recip = 0; break; }
     }
+    p.rlo = (float)(1.0 / (double)div - (double)p.rdiv);
+    p.exact2 = 1;
+    for (int v = 0; v < 256; v++) {
+        const float f = (float)v;
+        if (fmaf(f, p.rdiv, f * p.rlo) != f / div) { p.exact2 = 0; break; }
+    }
     for (int c = 0; c < 3; c++) {
         p.sub[c] = sub ? sub[c] : 0.f;
         p.padv[c] = (float)pad_value / div - p.sub[c];
     }
     p.vec_store = (out_w % 4 == 0) && (((uintptr_t)dst_dev & 15) == 0);
 
-    // tile height: the largest of 32/16/8 rows whose staged footprint leaves 8 CTAs per SM (<= 28 KB);
-    // failing that the largest that fits 64 KB; failing that read the source straight from global memory.
-    const size_t SMEM_MAX = 64 * 1024, SMEM_GOOD = 28 * 1024;
+    // Tile height: the largest of 32/16/8 output rows whose shared-memory need (staged source bytes + 16-bit row
+    // buffer + tap tables) stays <= 36 KB, so that six CTAs fit an SM; failing that the largest that fits 100 KB;
+    // failing that (extreme down-scaling) the one-pass kernel that reads the source straight from global memory.
+    const size_t SMEM_MAX = 100 * 1024, SMEM_GOOD = 36 * 1024;
     bool staged = false;
     size_t smem = 0;
     const double sx = area ? 2.0 : p.scale_x, sy = area ? 2.0 : p.scale_y;
@@ -352,9 +614,11 @@ extern "C" int tcb_preprocess_image(tcb_ctx* ctx, const uint8_t* src_dev, int n,
             if (cols > w) cols = w;
             long long rows = (long long)floor((th - 1) * sy) + 4;
             if (rows > h) rows = h;
-            long long pitch = ((cols * 3 + 15) / 16) * 16 + 16;
-            if ((size_t)(rows * pitch) <= (pass == 0 ? SMEM_GOOD : SMEM_MAX)) {
-                staged = true; smem = (size_t)(rows * pitch); p.th = th; p.pitch = (int)pitch;
+            const long long pitch = ((cols * 3 + 15) / 16) * 16 + 32;   // +16 alignment shift, +16 so a clamped right tap stays inside
+            const size_t stage = (size_t)(rows * pitch), hsb = (size_t)rows * TW * 3 * 2;
+            const size_t need = stage + hsb + TW * sizeof(XTap) + 32 * sizeof(YTap) + 16;   // + the mbarrier
+            if (need <= (pass == 0 ? SMEM_GOOD : SMEM_MAX)) {
+                staged = true; smem = need; p.th = th; p.pitch = (int)pitch; p.stage_bytes = (int)stage; p.hs_bytes = (int)hsb; p.nr_cap = (int)rows;
                 break;
             }
         }
@@ -366,16 +630,66 @@ extern "C" int tcb_preprocess_image(tcb_ctx* ctx, const uint8_t* src_dev, int n,
     dim3 grid(tcb_div_up(out_w, TW), tcb_div_up(out_h, p.th), n);
     TCB_REQUIRE(ctx, grid.y <= 65535, "tcb_preprocess_image: output too tall (%d rows)", out_h);
     cudaStream_t st = (cudaStream_t)stream;
-    typedef void (*kern_t)(const PreParams);
-    static const kern_t table[2][2][2] = {
-        {{preprocess_kernel<false, false, false>, preprocess_kernel<false, false, true>},
-         {preprocess_kernel<false, true, false>, preprocess_kernel<false, true, true>}},
-        {{preprocess_kernel<true, false, false>, preprocess_kernel<true, false, true>},
-         {preprocess_kernel<true, true, false>, preprocess_kernel<true, true, true>}}};
-    kern_t kern = table[area ? 1 : 0][staged ? 1 : 0][p.exact_recip ? 1 : 0];
-    if (smem > 48 * 1024)  // opt in to > 48 KB dynamic shared memory
-        TCB_CUDA(ctx, cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX));
-    kern<<<grid, NTHREADS, smem, st>>>(p);
+    if (staged && ((int)grid.x > GEO_MAX_TX || (int)grid.y > GEO_MAX_TY)) {   // geometry table too small: one-pass kernel
+        staged = false; p.th = 8; smem = 0;
+        grid = dim3(tcb_div_up(out_w, TW), tcb_div_up(out_h, p.th), n);
+        TCB_REQUIRE(ctx, grid.y <= 65535, "tcb_preprocess_image: output too tall (%d rows)", out_h);
+    }
+    typedef void (*kern1_t)(const PreParams);
+    typedef void (*kern2_t)(const PreParams, const TileGeo);
+    static const kern1_t one_pass[2][2] = {{preprocess_kernel<false, false, false>, preprocess_kernel<false, false, true>},
+                                           {preprocess_kernel<true, false, false>, preprocess_kernel<true, false, true>}};
+    static const kern2_t two_pass[2][2][2] = {
+        {{preprocess2_kernel<false, false, false>, preprocess2_kernel<false, false, true>},
+         {preprocess2_kernel<false, true, false>, preprocess2_kernel<false, true, true>}},
+        {{preprocess2_kernel<true, false, false>, preprocess2_kernel<true, false, true>},
+         {preprocess2_kernel<true, true, false>, preprocess2_kernel<true, true, true>}}};
+    const bool has_sub = p.sub[0] != 0.f || p.sub[1] != 0.f || p.sub[2] != 0.f;
+    if (staged) {
+        // source footprint of every tile column / row, with the kernel's own tap arithmetic
+        static thread_local TileGeo geo;
+        geo.first_ty = -1; geo.last_ty = -1;
+        for (int tx = 0; tx < (int)grid.x; tx++) {
+            const int t0 = tx * TW, t1 = (t0 + TW < out_w ? t0 + TW : out_w) - 1;
+            const int c0 = t0 - p.left > 0 ? t0 - p.left : 0, c1 = t1 - p.left < p.new_w - 1 ? t1 - p.left : p.new_w - 1;
+            geo.xmin[tx] = 0; geo.xcnt[tx] = 0;
+            if (c0 <= c1) {
+                int lo, hi;
+                if (area) { lo = 2 * c0; hi = 2 * c1 + 1; }
+                else {
+                    int s0, s1, a, b;
+                    x_tap(c0, p.scale_x, w, s0, a, b);
+                    x_tap(c1, p.scale_x, w, s1, a, b);
+                    lo = s0; hi = s1 + 1 < w - 1 ? s1 + 1 : w - 1;
+                }
+                geo.xmin[tx] = lo; geo.xcnt[tx] = (short)(hi - lo + 1);
+            }
+        }
+        for (int ty = 0; ty < (int)grid.y; ty++) {
+            const int t0 = ty * p.th, t1 = (t0 + p.th < out_h ? t0 + p.th : out_h) - 1;
+            const int c0 = t0 - p.top > 0 ? t0 - p.top : 0, c1 = t1 - p.top < p.new_h - 1 ? t1 - p.top : p.new_h - 1;
+            geo.rmin[ty] = 0; geo.rcnt[ty] = 0;
+            if (c0 <= c1) {
+                int lo, hi;
+                if (area) { lo = 2 * c0; hi = 2 * c1 + 1; }
+                else {
+                    int r0, r1, a, b;
+                    y_tap(c0, p.scale_y, h, r0, r1, a, b); lo = r0;
+                    y_tap(c1, p.scale_y, h, r0, r1, a, b); hi = r1;
+                }
+                geo.rmin[ty] = lo; geo.rcnt[ty] = (short)(hi - lo + 1);
+                if (geo.first_ty < 0) geo.first_ty = ty;
+                geo.last_ty = ty;
+            }
+        }
+        kern2_t kern = two_pass[area ? 1 : 0][p.exact2 ? 1 : 0][has_sub ? 1 : 0];
+        if (smem > 48 * 1024)  // opt in to > 48 KB dynamic shared memory
+            TCB_CUDA(ctx, cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX));
+        kern<<<grid, NTHREADS, smem, st>>>(p, geo);
+    } else {
+        kern1_t kern = one_pass[area ? 1 : 0][p.exact_recip ? 1 : 0];
+        kern<<<grid, NTHREADS, smem, st>>>(p);
+    }
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }
