@@ -55,7 +55,10 @@ __global__ void __launch_bounds__(256) det_candidates_kernel(const DetParams p, 
 }
 
 struct ABox { float x1, y1, x2, y2, area; int cls; };
-struct TvPred {   // torchvision nms: suppress iff inter/(a_i + a_j - inter) > thr; class handled by offsets or by equality
+struct TvPred {
+    static constexpr bool kQueue = false;   // cheap predicate: tested in place
+    __device__ __forceinline__ bool maybe(const ABox&, const ABox&) const { return true; }
+    __device__ __forceinline__ bool exact(const ABox& a, const ABox& b) const { return (*this)(a, b); }   // torchvision nms: suppress iff inter/(a_i + a_j - inter) > thr; class handled by offsets or by equality
     float thresh; int vanilla;
     __device__ __forceinline__ bool operator()(const ABox& a, const ABox& b) const {
         if (vanilla && a.cls != b.cls) return false;

@@ -33,14 +33,16 @@ __global__ void __launch_bounds__(256) rotated_iou_kernel(const float* __restric
 //   nms_gpu (iou3d_nms_utils.py:84-99) = nms_kernel bitmask (iou3d_nms_kernel.cu:267-311) + host sweep
 //   (iou3d_nms.cpp:116-132): box i is kept unless an earlier kept box k has iou_bev(k, i) > thresh.
 // ---------------------------------------------------------------------------------------------------------
+constexpr int QCAP = 8192;   // pending exact IoU tests per greedy round
 struct RotPred {
+    static constexpr bool kQueue = true;
     float thresh;
-    __device__ __forceinline__ bool operator()(const rot::RBox& a, const rot::RBox& b) const {
-        if (rot::far_apart(a, b)) return false;  // the reference's polygon is empty: IoU 0, never > thresh (>= 0)
-        return rot::iou_bev(a, b) > thresh;
-    }
+    // far apart: the reference's polygon is empty, IoU 0, never > thresh (>= 0)
+    __device__ __forceinline__ bool maybe(const rot::RBox& a, const rot::RBox& b) const { return !rot::far_apart(a, b); }
+    __device__ __forceinline__ bool exact(const rot::RBox& a, const rot::RBox& b) const { return rot::iou_bev(a, b) > thresh; }
+    __device__ __forceinline__ bool operator()(const rot::RBox& a, const rot::RBox& b) const { return maybe(a, b) && exact(a, b); }
 };
-typedef nms::Shared<rot::RBox, POST_CAP, PRE_CAP> NmsShared;
+typedef nms::Shared<rot::RBox, POST_CAP, PRE_CAP, QCAP> NmsShared;
 
 __device__ __forceinline__ int cta_rotated_nms(const rot::RBox* __restrict__ R, int m, float thresh, int post_max, NmsShared& S) {
     return nms::cta_greedy_nms(R, m, RotPred{thresh}, post_max, S);
@@ -53,6 +55,7 @@ struct FrameShared {
     sel::Scratch sel;
     NmsShared nms;
 };
+static_assert(sizeof(FrameShared) <= 227 * 1024, "FrameShared exceeds the 227 KB of shared memory a CTA can opt in to");
 
 // ---------------------------------------------------------------------------------------------------------
 // tcb_rotated_nms: scores + boxes in any order -> top pre_max by score -> greedy NMS -> keep indices

@@ -70,6 +70,9 @@ __global__ void __launch_bounds__(256) yolo_head_decode_kernel(const DecodeParam
 struct ABox { float x1, y1, x2, y2, area; int cls; };
 
 struct NumpyNmsPred {
+    static constexpr bool kQueue = false;   // cheap predicate: tested in place
+    __device__ __forceinline__ bool maybe(const ABox&, const ABox&) const { return true; }
+    __device__ __forceinline__ bool exact(const ABox& a, const ABox& b) const { return (*this)(a, b); }
     float thresh; int min_mode;
     __device__ __forceinline__ bool operator()(const ABox& a, const ABox& b) const {
         if (a.cls != b.cls) return false;  // per-class NMS (extract_boxes_onnx :296-303)
