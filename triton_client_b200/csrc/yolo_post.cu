@@ -69,7 +69,7 @@ __global__ void __launch_bounds__(256) yolo_filter_kernel(
             if (m == 0) continue;
             if (lane == 0) atomicAdd(&xc_count[b], __popc(m));
             if (nc <= FILTER_SMALL_NC) {
-                // few classes: each surviving lane decodes its own row (the lines are already in L1)
+                // few classes: each surviving lane decodes its own row
                 double best = -1.0;
                 int bidx = 0;
                 bool ok = false;
@@ -124,6 +124,83 @@ __global__ void __launch_bounds__(256) yolo_filter_kernel(
                 }
             }
         }
+    }
+}
+
+// Small class counts (rows of <= 13 floats): every 32-byte sector of the tensor is touched anyway, so each warp
+// first pulls its 128 rows into shared memory with fully coalesced loads (one DRAM round trip instead of the
+// objectness -> class scores -> box chain of dependent sector fetches), then filters and decodes from there.
+constexpr int FS_ROWS = 128;   // rows per warp and pass
+__global__ void __launch_bounds__(256) yolo_filter_small_kernel(
+    const float* __restrict__ pred, int B, int N, int nc, double conf_thres, int use_filter, ClassMask cmask,
+    double* __restrict__ c_score, float4* __restrict__ c_box, int2* __restrict__ c_meta,
+    int* __restrict__ c_count, int* __restrict__ xc_count) {
+    extern __shared__ __align__(16) float fs_smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int stride = 5 + nc;
+    float* rows = fs_smem + warp * (FS_ROWS * stride);
+    const int b = blockIdx.y;
+    const float* base = pred + ((long long)b * N) * stride;
+    const int chunks = (N + FS_ROWS - 1) / FS_ROWS;
+    const int wpi = (gridDim.x * blockDim.x) >> 5;
+    for (int ch = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5); ch < chunks; ch += wpi) {
+        const int row0 = ch * FS_ROWS;
+        const int nrow = min(FS_ROWS, N - row0);
+        const float* src = base + (long long)row0 * stride;
+        const int nfl = nrow * stride;
+        if ((((uintptr_t)src) & 15) == 0) {
+            const int n4 = nfl >> 2;
+            for (int i0 = 0; i0 < n4; i0 += 8 * 32) {   // 8 independent 16-byte loads in flight per lane before the first store
+                float4 v[8];
+#pragma unroll
+                for (int q = 0; q < 8; q++) { const int i = i0 + q * 32 + lane; if (i < n4) v[q] = __ldg(reinterpret_cast<const float4*>(src) + i); }
+#pragma unroll
+                for (int q = 0; q < 8; q++) { const int i = i0 + q * 32 + lane; if (i < n4) reinterpret_cast<float4*>(rows)[i] = v[q]; }
+            }
+            for (int i = (n4 << 2) + lane; i < nfl; i += 32) rows[i] = __ldg(src + i);
+        } else {
+            for (int i = lane; i < nfl; i += 32) rows[i] = __ldg(src + i);
+        }
+        __syncwarp();
+#pragma unroll
+        for (int u = 0; u < FS_ROWS / 32; u++) {
+            const int r = u * 32 + lane;
+            const float* rp = rows + r * stride;
+            const float obj = (r < nrow) ? rp[4] : -1.f;
+            const bool pass = (double)obj > conf_thres;
+            const unsigned m = __ballot_sync(0xffffffffu, pass);
+            if (m == 0) continue;
+            if (lane == 0) atomicAdd(&xc_count[b], __popc(m));
+            double best = -1.0;
+            int bidx = 0;
+            bool ok = false;
+            if (pass) {
+                const double o = (double)obj;
+                bool nan = false;
+                for (int c = 0; c < nc; c++) {
+                    const double v = (double)rp[5 + c] * o;
+                    nan |= (v != v);
+                    if (v > best) { best = v; bidx = c; }  // strict: first index wins
+                }
+                ok = !nan && nc > 0 && best > conf_thres;
+                if (ok && use_filter) ok = (cmask.w[bidx >> 6] >> (bidx & 63)) & 1ull;
+            }
+            const unsigned em = __ballot_sync(0xffffffffu, ok);
+            if (em) {
+                int basei = 0;
+                if (lane == 0) basei = atomicAdd(&c_count[b], __popc(em));
+                basei = __shfl_sync(0xffffffffu, basei, 0);
+                if (ok) {
+                    const double x = (double)rp[0], y = (double)rp[1], w = (double)rp[2], h = (double)rp[3];
+                    float4 bx;
+                    bx.x = (float)(x - w / 2); bx.y = (float)(y - h / 2);
+                    bx.z = (float)(x + w / 2); bx.w = (float)(y + h / 2);
+                    const long long k = (long long)b * N + basei + __popc(em & ((1u << lane) - 1));
+                    c_score[k] = best; c_box[k] = bx; c_meta[k] = make_int2(row0 + r, bidx);
+                }
+            }
+        }
+        __syncwarp();
     }
 }
 
@@ -599,8 +676,18 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
         if (bx > cap) bx = cap;
         if (bx < 1) bx = 1;
         TCB_REQUIRE(ctx, b <= 65535, "tcb_yolo_nms: batch %d > 65535", b);
-        yolo_filter_kernel<<<dim3(bx, b), 256, 0, st>>>(pred_dev, b, n, nc, conf_thres, n_classes > 0, cm,
-                                                        c_score, c_box, c_meta, c_count, xc_count);
+        if (nc <= FILTER_SMALL_NC) {
+            int gx = tcb_div_up((n + FS_ROWS - 1) / FS_ROWS, 8);
+            if (gx > cap) gx = cap;
+            if (gx < 1) gx = 1;
+            const size_t fsm = 8 * FS_ROWS * (5 + nc) * sizeof(float);
+            if (fsm > 48 * 1024) TCB_CUDA(ctx, cudaFuncSetAttribute(yolo_filter_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+            yolo_filter_small_kernel<<<dim3(gx, b), 256, fsm, st>>>(
+                pred_dev, b, n, nc, conf_thres, n_classes > 0, cm, c_score, c_box, c_meta, c_count, xc_count);
+        } else {
+            yolo_filter_kernel<<<dim3(bx, b), 256, 0, st>>>(pred_dev, b, n, nc, conf_thres, n_classes > 0, cm,
+                                                            c_score, c_box, c_meta, c_count, xc_count);
+        }
         TCB_LAUNCHED(ctx);
     }
     const size_t smem = NMS_SMEM_BYTES;
