@@ -30,6 +30,14 @@ RING = 3  # distinct input batches cycled through so no step re-reads what the p
 WORKLOAD = "configs[1]: YOLOv5nCROP batch 64, 1280x720 frames letterboxed to 640 + decode/class-aware NMS of 64x25200x7"
 
 
+def ncu_traffic():
+    """DRAM bytes per launch of the roofline kernel from the committed ncu capture (profiles/r01_pre_kernel.json)."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "r01_pre_kernel.json")))["dram_traffic_bytes_per_launch"]
+    except Exception:
+        return None
+
+
 def peaks():
     try:
         return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"], "measured"
@@ -299,8 +307,9 @@ def run_gpu(args):
                        "l2": f"inputs cycle through {RING} distinct batches of 222 MB each (> 126 MB L2); no flush needed",
                        "parallelism": f"frame stream sharded over {world} rank(s), no data-path collective"},
             "kernel_ms": {"preprocess": pre_ms, "yolo_post": post_ms},
-            "roofline": {"bound": "hbm", "kernel": "preprocess_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "peak_source": which, "bytes_per_launch": pre_bytes, "traffic": None},
+            "roofline": {"bound": "hbm", "kernel": "preprocess2_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "peak_source": which + " copy bandwidth (MEASURED_PEAKS.json hbm_gbs)",
+                         "bytes_per_launch": pre_bytes, "traffic": ncu_traffic()},
             "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": e2e_steps, "api": "Yolov5preprocess.image_adjust_batch + Yolov5postprocess.extract_boxes"},
             "gpu_launches": launches, "clocks": sampler.result(),
