@@ -189,6 +189,64 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def latency_c1(eng, dev, frames=1000):
+    """p50 per-frame latency at batch 1 (BASELINE.json configs[0]: 640x640 frame -> image_adjust, 1x25200x85 -> decode/NMS),
+    device-resident inputs cycled over 8 distinct frames, one CUDA-event pair per frame and stage; also replayed from a
+    CUDA graph of the two calls (launch overhead removed)."""
+    import torch
+    from triton_client_b200 import synth
+    imgs = [torch.from_numpy(synth.image_smooth(640, 640, 900 + i)).to(dev).unsqueeze(0) for i in range(8)]
+    preds = [torch.from_numpy(synth.yolo_output(1, NROWS, 80, 950 + i)).to(dev) for i in range(8)]
+    out = torch.empty((1, 3, 640, 640), dtype=torch.float32, device=dev)
+    det = torch.zeros((1, MAX_DET, 6), dtype=torch.float64, device=dev)
+    cnt = torch.zeros((2, 1), dtype=torch.int32, device=dev)
+
+    def one(i):
+        eng.preprocess_images(imgs[i % 8], 640, 640, mode="stretch", div=255.0, out=out)
+        eng.yolo_nms(preds[i % 8], conf_thres=CONF, iou_thres=IOU, max_det=MAX_DET, out=det, counts=cnt)
+
+    for i in range(20):
+        one(i)
+    torch.cuda.synchronize()
+    pre_t, post_t, tot_t = [], [], []
+    for i in range(frames):
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        e[0].record()
+        eng.preprocess_images(imgs[i % 8], 640, 640, mode="stretch", div=255.0, out=out)
+        e[1].record()
+        eng.yolo_nms(preds[i % 8], conf_thres=CONF, iou_thres=IOU, max_det=MAX_DET, out=det, counts=cnt)
+        e[2].record()
+        e[2].synchronize()
+        pre_t.append(e[0].elapsed_time(e[1]))
+        post_t.append(e[1].elapsed_time(e[2]))
+        tot_t.append(e[0].elapsed_time(e[2]))
+    res = {"config": "configs[0]: YOLOv5n COCO 640x640 batch 1 (image_adjust + decode/NMS of 1x25200x85)", "frames": frames,
+           "pre_ms": statistics.median(pre_t), "post_ms": statistics.median(post_t), "pre_post_ms": statistics.median(tot_t),
+           "graph_pre_post_ms": None}
+    try:   # the same two calls captured once and replayed: what a steady-state caller pays without launch overhead
+        g = torch.cuda.CUDAGraph()
+        s = torch.cuda.Stream(dev)
+        s.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(s):
+            one(0)
+        torch.cuda.current_stream(dev).wait_stream(s)
+        with torch.cuda.graph(g, stream=s):
+            one(0)
+        torch.cuda.synchronize()
+        ts = []
+        for i in range(frames):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            g.replay()
+            b.record()
+            b.synchronize()
+            ts.append(a.elapsed_time(b))
+        res["graph_pre_post_ms"] = statistics.median(ts)
+    except Exception as ex:  # graph capture is an extra, never a reason to lose the bench line
+        res["graph_error"] = str(ex)[:200]
+    return res
+
+
 def run_gpu(args):
     import torch
     import torch.distributed as dist
@@ -293,6 +351,7 @@ def run_gpu(args):
     h2d = frames_h[0].nbytes + preds_h[0].nbytes
     d2h = BATCH * 3 * OUT * OUT * 4 + det.numel() * 8 + cnt.numel() * 4
 
+    latency = latency_c1(eng, dev) if rank == 0 else None
     if rank == 0:
         peak, which = peaks()
         # letterboxed C2 frame: the kernel reads the 3*h*w source once and writes 12*S*S output once
@@ -312,7 +371,7 @@ def run_gpu(args):
                          "bytes_per_launch": pre_bytes, "traffic": ncu_traffic()},
             "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": e2e_steps, "api": "Yolov5preprocess.image_adjust_batch + Yolov5postprocess.extract_boxes"},
-            "gpu_launches": launches, "clocks": sampler.result(),
+            "gpu_launches": launches, "clocks": sampler.result(), "p50_latency": latency,
         }
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline()
