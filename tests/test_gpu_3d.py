@@ -33,9 +33,13 @@ def test_rotated_iou_matrix(engine):
     _close(got, want, rtol=1e-4, atol=2e-6)
 
 
-@pytest.mark.parametrize("n,thresh,pre,post", [(4096, 0.01, 4096, 500), (3000, 0.2, 1000, 83), (9000, 0.1, 4096, 500), (50, 0.5, 4096, 500), (1, 0.1, 10, 10)])
-def test_rotated_nms_keep_lists(engine, n, thresh, pre, post):
-    boxes = synth.random_boxes7(n, 20 + n, extent=60)
+# above 512 candidates the mask is built by the whole grid and swept by one CTA; at or below, one CTA does everything
+@pytest.mark.parametrize("n,thresh,pre,post,extent", [
+    (4096, 0.01, 4096, 500, 60), (3000, 0.2, 1000, 83, 60), (9000, 0.1, 4096, 500, 60), (50, 0.5, 4096, 500, 60), (1, 0.1, 10, 10, 60),
+    (513, 0.3, 4096, 500, 20), (512, 0.3, 4096, 500, 20), (1000, 0.05, 777, 1000, 30), (4096, 0.9, 4096, 1024, 80),
+    (4096, 0.0, 4096, 500, 12), (2111, 0.1, 4096, 64, 25), (5000, 0.3, 641, 640, 40)])
+def test_rotated_nms_keep_lists(engine, n, thresh, pre, post, extent):
+    boxes = synth.random_boxes7(n, 20 + n, extent=extent)
     scores = np.round(np.random.default_rng(n).uniform(0, 1, n) * 4096) / 4096    # ties -> index order
     scores = scores.astype(np.float32)
     sel, _ = box3d.class_agnostic_nms(torch.from_numpy(scores), torch.from_numpy(boxes), thresh, pre, post)

@@ -3,8 +3,9 @@
 //
 // In the reference these run inside the Triton Python backend (examples/pointpillar_kitti/1/model.py:163) through
 // the vendored pcdet code cited at each kernel; the drop-in runs them client-side behind PointPillarPostprocess.
-// One 1024-thread CTA per frame (or per frame x head) does ordering + greedy NMS entirely in shared memory —
-// no N x N/64 mask in global memory, no D2H of it, no serial host sweep (iou3d_nms.cpp:105-134).
+// Up to 512 candidates one 1024-thread CTA per frame (or per frame x head) does ordering + greedy NMS entirely in
+// shared memory; above that the pairwise IoU mask is built by the whole grid and swept by one CTA ("wide path"
+// below). Either way nothing leaves the device: no D2H of the mask, no serial host sweep (iou3d_nms.cpp:105-134).
 #include "common.cuh"
 #include "cta_select.cuh"
 #include "rotated.cuh"
@@ -71,6 +72,181 @@ __global__ void __launch_bounds__(T, 1) rotated_nms_kernel(const float* __restri
     __syncthreads();
     const int nk = cta_rotated_nms(S.R, m, thresh, post_max, S.nms);
     for (int k = threadIdx.x; k < nk; k += T) keep[k] = (int)sel::key_index(S.skeys[S.nms.kpos[k]]);
+    if (threadIdx.x == 0) *count = nk;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Wide path for large candidate sets (NMS_PRE_MAXSIZE > WIDE_MIN): the exact rotated IoU tests are the bulk of
+// the work and a single CTA cannot run them faster than ~0.4 ms at 4096 boxes, so they are spread over the
+// whole GPU as the reference does (nms_kernel, iou3d_nms_kernel.cu:267-311: one 64-bit word per row and
+// 64-column block) — but the mask stays on the device and the sweep over it (iou3d_nms.cpp:116-132, a serial
+// host loop there) is done by one CTA in rounds of 64 open candidates.
+//   order kernel (1 CTA)  : top pre_max by score, sorted; RBox of each in score order -> workspace
+//   mask kernel (grid)    : 64x64 tiles of the upper triangle; cheap distance test first, the surviving pairs
+//                           are listed in shared memory and evaluated one pair per thread
+//   sweep kernel (1 CTA)  : greedy pass over the mask, writes the results
+// ---------------------------------------------------------------------------------------------------------
+constexpr int WIDE_MIN = 512;
+constexpr int MW = PRE_CAP / 64;      // mask words per row
+constexpr int MASK_T = 256;
+
+struct OrderShared {
+    unsigned long long skeys[sel::KCAP];
+    sel::Scratch sel;
+};
+
+__global__ void __launch_bounds__(MASK_T) rot_mask_kernel(const rot::RBox* __restrict__ R, const int* __restrict__ m_dev, float thresh,
+                                                          unsigned long long* __restrict__ mask) {
+    const int bi = blockIdx.y, bj = blockIdx.x;   // row tile, column tile
+    const int m = *m_dev;
+    if (bj < bi || bj * 64 >= m) return;          // lower triangle / past the last candidate: never read
+    __shared__ rot::RBox rows[64], cols[64];
+    __shared__ unsigned long long tmask[64];
+    __shared__ unsigned short queue[64 * 64];
+    __shared__ int qn;
+    const int tid = threadIdx.x, lane = tid & 31;
+    if (tid < 64) {
+        const int g = bi * 64 + tid;
+        if (g < m) rows[tid] = R[g];
+        tmask[tid] = 0ull;
+    } else if (tid < 128) {
+        const int g = bj * 64 + tid - 64;
+        if (g < m) cols[tid - 64] = R[g];
+    }
+    if (tid == 0) qn = 0;
+    __syncthreads();
+    for (int e = tid; e < 64 * 64; e += MASK_T) {
+        const int i = e >> 6, j = e & 63;
+        const int gi = bi * 64 + i, gj = bj * 64 + j;
+        const bool near = gj > gi && gj < m && !rot::far_apart(rows[i], cols[j]);
+        const unsigned bal = __ballot_sync(0xffffffffu, near);
+        if (bal) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(&qn, __popc(bal));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (near) queue[base + __popc(bal & ((1u << lane) - 1))] = (unsigned short)e;
+        }
+    }
+    __syncthreads();
+    const int nq = qn;
+    for (int q = tid; q < nq; q += MASK_T) {
+        const int e = queue[q];
+        const int i = e >> 6, j = e & 63;
+        if (rot::iou_bev(rows[i], cols[j]) > thresh) atomicOr(&tmask[i], 1ull << j);
+    }
+    __syncthreads();
+    if (tid < 64 && bi * 64 + tid < m) mask[(size_t)(bi * 64 + tid) * MW + bj] = tmask[tid];
+}
+
+struct SweepShared {
+    unsigned long long removed[MW];        // bit c: candidate c is suppressed, taken, or beyond m
+    unsigned long long sub[nms::ACAP];     // suppression among the open candidates of this round
+    int aidx[nms::ACAP], knew[nms::ACAP];
+    int kpos[POST_CAP];                    // position (in score order) of each kept box
+    int nkept, a_count;
+};
+
+// Greedy pass over a mask written by rot_mask_kernel. Returns the number kept; S.kpos holds their positions.
+__device__ int cta_mask_sweep(const unsigned long long* __restrict__ mask, int m, int post_max, SweepShared& S) {
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int words = (m + 63) >> 6;
+    if (tid < MW) {
+        const int lo = tid * 64;
+        S.removed[tid] = lo + 64 <= m ? 0ull : (lo >= m ? ~0ull : ~((1ull << (m - lo)) - 1ull));
+    }
+    if (tid == 0) S.nkept = 0;
+    __syncthreads();
+    while (true) {
+        const int nk = S.nkept;
+        // (a) the first ACAP candidates still open, in order: warp 0, two mask words per lane
+        if (tid < 32) {
+            unsigned long long o0 = ~S.removed[2 * lane], o1 = ~S.removed[2 * lane + 1];
+            const int c0 = __popcll(o0), c1 = __popcll(o1);
+            int inc = c0 + c1;
+#pragma unroll
+            for (int s = 1; s < 32; s <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, s); if (lane >= s) inc += t; }
+            int rank = inc - c0 - c1;
+            while (o0 && rank < nms::ACAP) { S.aidx[rank++] = 128 * lane + __ffsll((long long)o0) - 1; o0 &= o0 - 1; }
+            rank = inc - c1;
+            while (o1 && rank < nms::ACAP) { S.aidx[rank++] = 128 * lane + 64 + __ffsll((long long)o1) - 1; o1 &= o1 - 1; }
+            if (lane == 31) S.a_count = min(inc, nms::ACAP);
+        }
+        __syncthreads();
+        const int A = S.a_count;
+        if (A == 0) break;
+        // (b) suppression among them: 16 threads per row, 4 columns each, bits gathered from the global mask
+        {
+            const int ri = tid >> 4, l16 = tid & 15;
+            unsigned long long bits = 0ull;
+            if (ri < A) {
+                const unsigned long long* mr = mask + (size_t)S.aidx[ri] * MW;
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    const int j = l16 * 4 + q;
+                    if (j > ri && j < A) {
+                        const int cj = S.aidx[j];
+                        if ((__ldg(mr + (cj >> 6)) >> (cj & 63)) & 1ull) bits |= 1ull << j;
+                    }
+                }
+            }
+#pragma unroll
+            for (int sft = 1; sft < 16; sft <<= 1) bits |= __shfl_xor_sync(0xffffffffu, bits, sft);
+            if (l16 == 0) S.sub[ri] = bits;
+        }
+        __syncthreads();
+        if (tid == 0) {  // (c) serial sweep over at most ACAP rows
+            unsigned long long avail = A >= 64 ? ~0ull : ((1ull << A) - 1);
+            int kept = nk;
+            while (kept < post_max && avail) {
+                const int i = __ffsll((long long)avail) - 1;
+                avail &= ~(S.sub[i] | (1ull << i));
+                S.knew[kept - nk] = i;
+                S.kpos[kept] = S.aidx[i];
+                kept++;
+            }
+            S.nkept = kept;
+        } else if (tid >= 32 && tid < 32 + A) {
+            const int cs = S.aidx[tid - 32];
+            atomicOr(&S.removed[cs >> 6], 1ull << (cs & 63));
+        }
+        __syncthreads();
+        const int nn = S.nkept - nk;
+        if (nk + nn >= post_max) break;
+        // (d) everything the newly kept boxes suppress
+        for (int e = tid; e < nn * words; e += T) {
+            const int r = e / words, w = e - r * words;
+            const int row = S.aidx[S.knew[r]];
+            if (w >= (row >> 6)) {
+                const unsigned long long v = __ldg(mask + (size_t)row * MW + w);
+                if (v) atomicOr(&S.removed[w], v);
+            }
+        }
+        __syncthreads();
+    }
+    __syncthreads();
+    return S.nkept;
+}
+
+__global__ void __launch_bounds__(T, 1) rot_order_kernel(const float* __restrict__ boxes, const float* __restrict__ scores, int n, int pre_max,
+                                                         unsigned long long* __restrict__ skeys_out, rot::RBox* __restrict__ R_out,
+                                                         int* __restrict__ m_out) {
+    __shared__ OrderShared S;
+    auto key_of = [&](int i) { return sel::make_key(__ldg(scores + i), (unsigned)i); };
+    const int m = sel::cta_topk_sorted(key_of, n, pre_max, S.skeys, S.sel);
+    for (int c = threadIdx.x; c < m; c += T) {
+        const unsigned long long k = S.skeys[c];
+        skeys_out[c] = k;
+        R_out[c] = rot::make_rbox(boxes + 7ll * sel::key_index(k));
+    }
+    if (threadIdx.x == 0) *m_out = m;
+}
+
+__global__ void __launch_bounds__(T, 1) rot_sweep_kernel(const unsigned long long* __restrict__ mask, const unsigned long long* __restrict__ skeys,
+                                                         const int* __restrict__ m_dev, int post_max, int* __restrict__ keep,
+                                                         int* __restrict__ count) {
+    __shared__ SweepShared S;
+    const int nk = cta_mask_sweep(mask, *m_dev, post_max, S);
+    for (int k = threadIdx.x; k < nk; k += T) keep[k] = (int)sel::key_index(skeys[S.kpos[k]]);
     if (threadIdx.x == 0) *count = nk;
 }
 
@@ -175,6 +351,52 @@ __global__ void __launch_bounds__(T, 1) pp_post_kernel(const PPParams p, const f
         for (int j = 0; j < 7; j++) out_boxes[k * 7 + j] = sorted_boxes[c * 7 + j];
         out_scores[k] = sel::key_score(key);
         const float* q = cls + (long long)a * p.num_class;   // label = first arg-max of the sigmoids, + 1 (detector3d_template.py:251,256)
+        int label = 0;
+        float best = sigmoidf_ref(__ldg(q));
+        for (int cc = 1; cc < p.num_class; cc++) { const float v = sigmoidf_ref(__ldg(q + cc)); if (v > best) { best = v; label = cc; } }
+        out_labels[k] = (long long)(label + 1);
+    }
+    if (tid == 0) *out_count = nk;
+}
+
+// wide path (see rot_mask_kernel): the same steps as pp_post_kernel with the IoU work between them on the whole GPU
+__global__ void __launch_bounds__(T, 1) pp_order_kernel(const PPParams p, const float* __restrict__ box_preds, const float* __restrict__ dir_preds,
+                                                        const unsigned long long* __restrict__ cand, const int* __restrict__ cand_count,
+                                                        int cand_cap, float* __restrict__ sorted_boxes, unsigned long long* __restrict__ skeys_out,
+                                                        rot::RBox* __restrict__ R_out, int* __restrict__ m_out) {
+    __shared__ OrderShared S;
+    const int tid = threadIdx.x;
+    const int nc = min(*cand_count, cand_cap);
+    auto key_of = [&](int i) { return cand[i]; };
+    const int m = sel::cta_topk_sorted(key_of, nc, p.pre_max, S.skeys, S.sel);
+    for (int c = tid; c < m; c += T) {
+        const unsigned long long k = S.skeys[c];
+        float b7[7];
+        pp_decode(p, (int)sel::key_index(k), box_preds, dir_preds, b7);
+#pragma unroll
+        for (int j = 0; j < 7; j++) sorted_boxes[c * 7 + j] = b7[j];
+        skeys_out[c] = k;
+        R_out[c] = rot::make_rbox(b7);
+    }
+    if (tid == 0) *m_out = m;
+}
+
+__global__ void __launch_bounds__(T, 1) pp_finish_kernel(const PPParams p, const float* __restrict__ cls, const unsigned long long* __restrict__ mask,
+                                                         const unsigned long long* __restrict__ skeys, const int* __restrict__ m_dev,
+                                                         const float* __restrict__ sorted_boxes, float* __restrict__ out_boxes,
+                                                         float* __restrict__ out_scores, long long* __restrict__ out_labels,
+                                                         int* __restrict__ out_count) {
+    __shared__ SweepShared S;
+    const int tid = threadIdx.x;
+    const int nk = cta_mask_sweep(mask, *m_dev, p.post_max, S);
+    for (int k = tid; k < nk; k += T) {
+        const int c = S.kpos[k];
+        const unsigned long long key = skeys[c];
+        const int a = (int)sel::key_index(key);
+#pragma unroll
+        for (int j = 0; j < 7; j++) out_boxes[k * 7 + j] = sorted_boxes[c * 7 + j];
+        out_scores[k] = sel::key_score(key);
+        const float* q = cls + (long long)a * p.num_class;
         int label = 0;
         float best = sigmoidf_ref(__ldg(q));
         for (int cc = 1; cc < p.num_class; cc++) { const float v = sigmoidf_ref(__ldg(q + cc)); if (v > best) { best = v; label = cc; } }
@@ -339,21 +561,53 @@ static int opt_in_smem(tcb_ctx* ctx, K kernel) {
     return TCB_OK;
 }
 
+// workspace of the wide path; false (nothing taken) when the context's workspace has no room for it
+struct WideBufs {
+    unsigned long long* skeys;
+    rot::RBox* R;
+    unsigned long long* mask;
+    int* m;
+};
+static size_t wide_bytes(int m_max) {
+    return (size_t)PRE_CAP * (8 + sizeof(rot::RBox)) + (size_t)m_max * MW * 8 + 4 * 256 + 256;
+}
+static bool wide_bufs(tcb_ctx* ctx, int m_max, WideBufs& wb) {
+    if (((ctx->ws_used + 255) & ~(size_t)255) + wide_bytes(m_max) > ctx->ws_bytes) return false;
+    wb.skeys = (unsigned long long*)tcb_ws_alloc(ctx, (size_t)PRE_CAP * 8);
+    wb.R = (rot::RBox*)tcb_ws_alloc(ctx, (size_t)PRE_CAP * sizeof(rot::RBox));
+    wb.mask = (unsigned long long*)tcb_ws_alloc(ctx, (size_t)m_max * MW * 8);
+    wb.m = (int*)tcb_ws_alloc(ctx, 256);
+    return wb.skeys && wb.R && wb.mask && wb.m;
+}
+
 extern "C" int tcb_rotated_nms(tcb_ctx* ctx, const float* boxes_dev, const float* scores_dev, int n, float thresh, int pre_max,
                                int post_max, int* keep_dev, int* count_dev, void* stream) {
     TCB_CHECK_CTX(ctx);
     TCB_REQUIRE(ctx, n >= 0 && keep_dev && count_dev && (n == 0 || (boxes_dev && scores_dev)), "tcb_rotated_nms: bad arguments");
     int rc = check_nms_limits(ctx, "tcb_rotated_nms", thresh, pre_max, post_max);
     if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    WideBufs wb;
+    const int m_max = n < pre_max ? n : pre_max;
+    if (m_max > WIDE_MIN && wide_bufs(ctx, m_max, wb)) {
+        rot_order_kernel<<<1, T, 0, st>>>(boxes_dev, scores_dev, n, pre_max, wb.skeys, wb.R, wb.m);
+        TCB_LAUNCHED(ctx);
+        const int nb = tcb_div_up(m_max, 64);
+        rot_mask_kernel<<<dim3(nb, nb), MASK_T, 0, st>>>(wb.R, wb.m, thresh, wb.mask);
+        TCB_LAUNCHED(ctx);
+        rot_sweep_kernel<<<1, T, 0, st>>>(wb.mask, wb.skeys, wb.m, post_max, keep_dev, count_dev);
+        TCB_LAUNCHED(ctx);
+        return TCB_OK;
+    }
     if ((rc = opt_in_smem(ctx, rotated_nms_kernel))) return rc;
-    rotated_nms_kernel<<<1, T, sizeof(FrameShared), (cudaStream_t)stream>>>(boxes_dev, scores_dev, n, thresh, pre_max, post_max, keep_dev, count_dev);
+    rotated_nms_kernel<<<1, T, sizeof(FrameShared), st>>>(boxes_dev, scores_dev, n, thresh, pre_max, post_max, keep_dev, count_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }
 
 extern "C" size_t tcb_pp_anchor_post_workspace(int h, int w, int num_class, int num_rot) {
     const size_t n = (size_t)h * w * num_class * num_rot;
-    return n * 8 + (size_t)PRE_CAP * 7 * 4 + 4096;
+    return n * 8 + (size_t)PRE_CAP * 7 * 4 + 4096 + wide_bytes(PRE_CAP);
 }
 
 extern "C" int tcb_pp_anchor_post(tcb_ctx* ctx, const float* cls_dev, const float* box_dev, const float* dir_dev, int h, int w,
@@ -397,6 +651,19 @@ extern "C" int tcb_pp_anchor_post(tcb_ctx* ctx, const float* cls_dev, const floa
     TCB_CUDA(ctx, cudaMemsetAsync(cand_count, 0, sizeof(int), st));
     pp_candidates_kernel<<<tcb_div_up(n_anchors, 256), 256, 0, st>>>(cls_dev, (int)n_anchors, num_class, score_thresh, cand, cand_count);
     TCB_LAUNCHED(ctx);
+    WideBufs wb;
+    const int m_max = (int)(n_anchors < pre_max ? n_anchors : pre_max);
+    if (m_max > WIDE_MIN && wide_bufs(ctx, m_max, wb)) {
+        pp_order_kernel<<<1, T, 0, st>>>(p, box_dev, dir_dev, cand, cand_count, (int)n_anchors, sorted_boxes, wb.skeys, wb.R, wb.m);
+        TCB_LAUNCHED(ctx);
+        const int nb = tcb_div_up(m_max, 64);
+        rot_mask_kernel<<<dim3(nb, nb), MASK_T, 0, st>>>(wb.R, wb.m, nms_thresh, wb.mask);
+        TCB_LAUNCHED(ctx);
+        pp_finish_kernel<<<1, T, 0, st>>>(p, cls_dev, wb.mask, wb.skeys, wb.m, sorted_boxes, out_boxes_dev, out_scores_dev, out_labels_dev,
+                                          out_count_dev);
+        TCB_LAUNCHED(ctx);
+        return TCB_OK;
+    }
     if ((rc = opt_in_smem(ctx, pp_post_kernel))) return rc;
     pp_post_kernel<<<1, T, sizeof(FrameShared), st>>>(p, cls_dev, box_dev, dir_dev, cand, cand_count, (int)n_anchors, sorted_boxes,
                                                        out_boxes_dev, out_scores_dev, out_labels_dev, out_count_dev);
