@@ -285,6 +285,37 @@ int tcb_class_score_filter(tcb_ctx* ctx, const long long* labels_dev, const floa
                            const int* group_class_host, const float* group_thresh_host, int* out_idx_dev,
                            int* out_count_dev, void* stream);
 
+/* ---- the step after the path: box rescale + overlay drawing ------------------ */
+
+/* _scale_box_array (communicator/evaluate_inference.py:237-256) / _scale_boxes (communicator/ros_inference.py:
+ * 100-115) on n rows [x1,y1,x2,y2,conf,cls] float64: x *= orig_w / input_size0 (sic: the reference divides the
+ * width by input_size[0]), y = y * orig_h / input_size1; normalized != 0: x *= orig_w, y *= orig_h. Columns 4,5
+ * are copied. math_mode picks the arithmetic the reference's expression runs in:
+ *   0  float64 throughout (the array version)
+ *   1  box rounded to float32, float64 arithmetic  (np.float32 scalar * Python number under numpy < 2)
+ *   2  box rounded to float32, float32 arithmetic  (same expression under numpy >= 2) */
+int tcb_scale_boxes(tcb_ctx* ctx, const double* det_dev, int n, int orig_h, int orig_w, int input_size0, int input_size1,
+                    int normalized, int math_mode, double* out_dev, void* stream);
+
+/* The per-detection drawing loop of RosInference._callback (communicator/ros_inference.py:148-169), in place on b
+ * device frames (h x w x 3 uint8, row_stride / frame_stride in bytes): each of the first count_dev[f] (NULL:
+ * max_det) rows of det_dev[f] (max_det x 6 float64, model-input pixels) is scaled like _scale_boxes (math_mode 1
+ * or 2; orig size = h, w), truncated like Python's int(), and drawn as cv2.rectangle(thickness 1 or 2) plus, when
+ * labels != 0, cv2.putText('{:.2f} {}'.format(conf, name), (x1, int(y1 - 10)), FONT_HERSHEY_SIMPLEX, 0.5, thickness
+ * 2). Detections are painted in order (a later one overwrites an earlier one). class_names: host memory,
+ * num_classes strings back to back, each '\0'-terminated (<= 128 classes, <= 2560 bytes; labels longer than 64
+ * characters are cut). colors: host memory, 3 bytes in frame channel order, or num_classes x 3 when
+ * per_class_color != 0 (Yolov5postprocess.plot_boxes_cv2's per-class colours,
+ * clients/postprocess/yolov5_postprocess.py:127-169; its 1.2-scale labels are not available). Rectangles are
+ * identical to OpenCV's everywhere; labels are identical when they lie inside the frame — a label cut by the
+ * frame edge can differ in a few pixels (OpenCV clips stroke outlines before rasterising them). */
+size_t tcb_draw_detections_workspace(int b, int max_det);
+int tcb_draw_detections(tcb_ctx* ctx, unsigned char* frames_dev, int b, int h, int w, long long row_stride,
+                        long long frame_stride, const double* det_dev, const int* count_dev, int max_det,
+                        int input_size0, int input_size1, int normalized, int math_mode, const char* class_names,
+                        int num_classes, const unsigned char* colors, int per_class_color, int thickness, int labels,
+                        void* stream);
+
 /*
  * tcb_yolo_nms without a context and without any allocation. No counterpart in the reference: it is
  * here for callers that are not allowed to allocate GPU memory — a plugin inside a host process that

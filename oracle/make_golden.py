@@ -175,6 +175,82 @@ def golden_yolo4():
     save("yolo4", **out)
 
 
+def overlay_pred(seed, n, nc, size, objects, margin):
+    """Small YOLO response with `objects` planted boxes whose centres keep `margin` model pixels from the edge."""
+    rng = np.random.default_rng(seed)
+    out = np.zeros((1, n, 5 + nc), np.float32)
+    out[0, :, 0:2] = rng.uniform(0, size, (n, 2))
+    out[0, :, 2:4] = rng.uniform(8, 40, (n, 2))
+    out[0, :, 4] = rng.uniform(0, 0.05, n)
+    out[0, :, 5:] = rng.uniform(0, 0.05, (n, nc))
+    cxy = rng.uniform(margin, size - margin, (objects, 2))
+    wh = rng.uniform(12, 2 * margin if margin > 12 else 60, (objects, 2))
+    cls = rng.integers(0, nc, objects)
+    rows = rng.choice(n, size=objects * 5, replace=False)
+    oid = np.arange(len(rows)) % objects
+    out[0, rows, 0:2] = cxy[oid] + rng.normal(0, 1.5, (len(rows), 2))
+    out[0, rows, 2:4] = wh[oid] * np.exp(rng.normal(0, 0.03, (len(rows), 2)))
+    out[0, rows, 4] = rng.uniform(0.4, 1.0, len(rows))
+    out[0, rows, 5 + cls[oid]] = rng.uniform(0.6, 1.0, len(rows))
+    return out
+
+
+def golden_overlay():
+    """The unmodified RosInference._callback (communicator/ros_inference.py:119-175) run end to end on one frame:
+    cv2.resize -> image_adjust -> [fake Triton response] -> extract_boxes -> _scale_boxes -> cv2.rectangle/putText.
+    ROS and gRPC objects are fakes that only carry data. Stored per case: the frame's seed/shape, the response, the
+    detections the reference extracted, the request bytes' checksum and the set of pixels it painted.
+    numpy here is %s: np.float32 scalar * Python number stays float32 (the oracle's f64=False mode)."""
+    import types
+    import zlib
+    comm = ref_harness.communicator()
+    c = ref_harness.clients()
+    client = c.Yolov5client()
+    out = {}
+    cases = [dict(h=180, w=320, size=160, n=300, objects=7, margin=40),     # every label inside the frame
+             dict(h=240, w=200, size=128, n=300, objects=9, margin=0)]      # boxes and labels cut by the frame edge
+    for k, cs in enumerate(cases):
+        frame = synth.image_noise(cs["h"], cs["w"], synth.seed_for(7, k))
+        pred = overlay_pred(synth.seed_for(8, k), cs["n"], 2, cs["size"], cs["objects"], cs["margin"])
+
+        class Req:
+            def __init__(self):
+                self.inputs, self.raw_input_contents = [], []
+
+            def ClearField(self, name):
+                getattr(self, name).clear()
+
+        chan = types.SimpleNamespace(input=types.SimpleNamespace(shape=[3, cs["size"], cs["size"]]), request=Req(),
+                                     do_inference=lambda pred=pred: FakeResponse([pred]))
+        published = []
+        node = object.__new__(comm.RosInference)
+        node.channel, node.client = chan, client
+        node.br = types.SimpleNamespace(imgmsg_to_cv2=lambda msg, desired_encoding: msg.frame,
+                                        cv2_to_imgmsg=lambda img, encoding: types.SimpleNamespace(img=img, header=None))
+        node.color, node.topic_exists, node.image = (0, 255, 0), True, None
+        node.client_postprocess, node.client_preprocess = client.get_postprocess(), client.get_preprocess()
+        node.class_names = ["crop", "weed"]
+        node.input_size = [cs["size"], cs["size"]]
+        node.detection = types.SimpleNamespace(publish=published.append)
+        node._callback(types.SimpleNamespace(format="rgb8", frame=frame, header=None))
+        annotated = published[0].img
+        assert annotated.shape == frame.shape and isinstance(node.prediction, list)
+        painted = (annotated != frame).any(-1)
+        assert (annotated[painted] == np.array(node.color, np.uint8)).all()
+        out[f"cfg{k}"] = np.array([cs["h"], cs["w"], cs["size"], synth.seed_for(7, k)])
+        out[f"frame_crc{k}"] = np.array(zlib.crc32(frame.tobytes()))
+        out[f"pred{k}"] = pred
+        out[f"det{k}"] = node.prediction[0].numpy().astype(np.float64)
+        out[f"request_crc{k}"] = np.array(zlib.crc32(chan.request.raw_input_contents[0]))
+        out[f"painted{k}"] = np.packbits(painted)
+        print(f"overlay case {k}: {len(node.prediction[0])} detections, {int(painted.sum())} pixels painted")
+    out["numpy_version"] = np.array(np.__version__)
+    save("overlay", **out)
+
+
+golden_overlay.__doc__ = golden_overlay.__doc__ % np.__version__
+
+
 def main():
     assert ref_harness.available(), "reference not mounted"
     os.makedirs(GOLD, exist_ok=True)

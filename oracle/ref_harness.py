@@ -123,3 +123,45 @@ def pillar_vfe(voxel_size, point_cloud_range, num_point_features=4):
     vfe = mods["pillar_vfe"].PillarVFE(cfg, num_point_features, voxel_size, point_cloud_range)
     vfe.pfn_layers = torch.nn.ModuleList([])
     return vfe
+
+
+class _AnyModule(types.ModuleType):
+    """Stand-in for a ROS package: any attribute is a placeholder class (so `from x.msg import Image` works)."""
+
+    def __getattr__(self, name):
+        if name.startswith("__"):
+            raise AttributeError(name)
+        cls = type(name, (), {})
+        setattr(self, name, cls)
+        return cls
+
+
+_communicator = None
+
+
+def communicator():
+    """The reference's `communicator` package (RosInference._callback / _scale_boxes, EvaluateInference) with the
+    ROS middleware stubbed out: rospy, sensor_msgs, vision_msgs, cv_bridge are placeholders, never called by the
+    pieces the golden scripts run (those get fake bridge / channel / publisher objects)."""
+    global _communicator
+    if _communicator is None:
+        clients()
+        for n in ["rospy", "rosbag", "sensor_msgs", "sensor_msgs.msg", "vision_msgs", "vision_msgs.msg", "cv_bridge",
+                  "geometry_msgs", "geometry_msgs.msg", "ros_numpy"]:
+            if n not in sys.modules:
+                m = _AnyModule(n)
+                sys.modules[n] = m
+                if "." in n:
+                    setattr(sys.modules[n.rsplit(".", 1)[0]], n.rsplit(".", 1)[1], m)
+        for n in ["service_pb2", "service_pb2_grpc", "model_config_pb2"]:
+            setattr(sys.modules["tritonclient.grpc"], n, sys.modules["tritonclient.grpc." + n])
+        saved_path, saved_cwd = list(sys.path), os.getcwd()
+        sys.path.insert(0, REF)
+        os.chdir(REF)
+        try:
+            import communicator as c  # noqa
+            _communicator = c
+        finally:
+            os.chdir(saved_cwd)
+            sys.path[:] = saved_path
+    return _communicator

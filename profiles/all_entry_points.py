@@ -76,5 +76,11 @@ eng.nms_axis_aligned(c(np.abs(bx[:, :4])), c(sc), 0.5)
 eng.box_iou(c(np.abs(bx[:64, :4])), c(np.abs(bx[64:128, :4])))
 lg, dl = synth.detectron_head_outputs(6, num_classes=4, image_hw=(128, 160), planted=40)
 eng.detectron_post([c(t) for t in lg], [c(t) for t in dl], (8, 16, 32, 64, 128), detectron_post.retinanet_cell_anchors(), (128, 160))
+from oracle import overlay  # noqa: E402
+fr = synth.image_noise(120, 200, 6)
+dd = np.array([[10, 40, 60, 80, 0.875, 1], [-5, 20, 30, 50, 0.5, 0]], np.float64)
+got = eng.draw_detections(c(fr), c(dd[None]), None, ["crop", "weed"], (0, 255, 0), [100, 100], math_mode=1)
+assert np.array_equal(got.cpu().numpy(), overlay.draw_detections(fr.copy(), dd, ["crop", "weed"], (0, 255, 0), [100, 100]))
+assert np.array_equal(eng.scale_boxes(c(dd), (120, 200), (100, 100)).cpu().numpy(), overlay.scale_box_array(dd, (120, 200), (100, 100)))
 torch.cuda.synchronize()
 print(f"all_entry_points: every entry point ran and matched the oracle ({eng.launches} kernel launches)")

@@ -194,6 +194,28 @@ def main():
     row("d5 rotated IoU matrix", "1000x1000", lambda i: eng.rotated_iou(bxd[:1000], bxd[1000:2000]), 1000 * 1000 * 4 + 2000 * 28, 1,
         lambda: box3d.boxes_iou_bev(bx[:1000], bx[1000:2000]), "compute-bound (polygon clipping)")
 
+    # ---- after the path: box rescale + overlay (8f rank 2) ---------------------------------------------------------
+    if not args.only or args.only in "f2 box rescale + overlay":
+        from oracle import overlay
+        predo = torch.from_numpy(synth.yolo_output(64, 25200, 2, 5)).cuda()
+        deto, cnto, _ = eng.yolo_nms(predo, conf_thres=0.3)
+        base = torch.from_numpy(synth.image_smooth(720, 1280, 3)).cuda()
+        ring = [base.unsqueeze(0).repeat(64, 1, 1, 1).contiguous() for _ in range(RING)]
+        host_frame, host_det = base.cpu().numpy(), deto[0, :int(cnto[0])].cpu().numpy()
+        eng.draw_detections(ring[0], deto, cnto, ["crop", "weed"], (0, 255, 0), [640, 640], math_mode=1)
+        painted = int((ring[0] != base.unsqueeze(0)).any(-1).sum())
+
+        def cv2_loop():   # the reference's own host loop (ros_inference.py:148-169) on one frame
+            import cv2
+            img = host_frame.copy()
+            for row_ in host_det:
+                b = overlay.scale_box(row_[:4].astype(np.float32), (720, 1280), [640, 640], f64=True)
+                cv2.rectangle(img, (int(b[0]), int(b[1])), (int(b[2]), int(b[3])), (0, 255, 0), 2)
+                cv2.putText(img, overlay.label_text(row_[4], ["crop", "weed"][int(row_[5])]), (int(b[0]), int(b[1] - 10)),
+                            cv2.FONT_HERSHEY_SIMPLEX, 0.5, (0, 255, 0), 2)
+        row("f2 box rescale + overlay", f"C2 64x1280x720, {int(cnto.sum())} detections", lambda i: eng.draw_detections(ring[i % RING], deto, cnto, ["crop", "weed"], (0, 255, 0), [640, 640], math_mode=1),
+            int(cnto.sum()) * 48 + painted * 3, 64, cv2_loop, "CPU column: the reference's cv2 loop on one frame; launch-bound (two kernels)")
+
     print("\n| row | config | GPU p50 ms | GPU ms/frame | CPU oracle ms/frame | alg. bytes | GB/s | frac of measured HBM |")
     print("|---|---|---:|---:|---:|---:|---:|---:|")
     for r in rows:

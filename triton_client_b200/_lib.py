@@ -69,6 +69,10 @@ SIGNATURES = {
                                      P(c_int), P(c_int), c_int, c_int, c_int, P(c_float), P(c_float), P(c_float), c_int,
                                      c_float, c_float, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "tcb_class_score_filter": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, P(c_int), P(c_float), c_void_p, c_void_p, c_void_p]),
+    "tcb_scale_boxes": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "tcb_draw_detections_workspace": (c_size_t, [c_int, c_int]),
+    "tcb_draw_detections": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_ll, c_ll, c_void_p, c_void_p, c_int,
+                                    c_int, c_int, c_int, c_int, ctypes.c_char_p, c_int, ctypes.c_char_p, c_int, c_int, c_int, c_void_p]),
     "tcb_yolo_nms_static_scratch_bytes": (c_size_t, []),
     "tcb_yolo_nms_static": (c_int, [c_void_p, c_int, c_int, c_int, c_double, c_double, P(c_int), c_int, c_int,
                                     c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),

@@ -204,6 +204,130 @@ __global__ void __launch_bounds__(256) yolo_filter_small_kernel(
     }
 }
 
+// The same filter as a stream: every warp owns two row buffers and keeps a bulk copy (TMA, completion on an
+// mbarrier) of its next 128-row chunk in flight while it filters the current one, and reserves output slots once
+// per chunk (one returning atomic instead of one per 32 rows). Chunks that are not 16-byte aligned/sized (the last
+// one of a frame, odd strides, unaligned tensors) are copied by the lanes instead.
+__device__ __forceinline__ unsigned yf_smem(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void yf_bar_init(unsigned long long* bar) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(yf_smem(bar)) : "memory");
+}
+__device__ __forceinline__ void yf_bulk_load(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(yf_smem(bar)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(yf_smem(dst)), "l"(src), "r"(bytes), "r"(yf_smem(bar)) : "memory");
+}
+__device__ __forceinline__ void yf_bar_wait(unsigned long long* bar, unsigned phase) {
+    unsigned done = 0;
+    while (!done) {
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                     : "=r"(done) : "r"(yf_smem(bar)), "r"(phase) : "memory");
+    }
+}
+
+constexpr int FS_WARPS = 8;
+__global__ void __launch_bounds__(32 * FS_WARPS) yolo_filter_stream_kernel(
+    const float* __restrict__ pred, int B, int N, int nc, double conf_thres, int use_filter, ClassMask cmask,
+    double* __restrict__ c_score, float4* __restrict__ c_box, int2* __restrict__ c_meta,
+    int* __restrict__ c_count, int* __restrict__ xc_count) {
+    extern __shared__ __align__(128) unsigned char ys_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int stride = 5 + nc;
+    const int buf_floats = FS_ROWS * stride;                        // FS_ROWS = 128: a multiple of 4 floats, 16-byte sized
+    unsigned long long* bars = reinterpret_cast<unsigned long long*>(ys_raw);            // [FS_WARPS][2]
+    float* bufs = reinterpret_cast<float*>(ys_raw + 128) + (size_t)warp * 2 * buf_floats;
+    unsigned long long* bar = bars + 2 * warp;
+    if (lane == 0) { yf_bar_init(bar); yf_bar_init(bar + 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+    __syncwarp();
+    const int chunks = (N + FS_ROWS - 1) / FS_ROWS;
+    const long long total = (long long)B * chunks;
+    const long long nwarps = (long long)gridDim.x * FS_WARPS;
+    long long ch = (long long)blockIdx.x * FS_WARPS + warp;
+    unsigned phase0 = 0, phase1 = 0;
+
+    auto chunk_src = [&](long long c, int& b, int& row0, int& nrow) -> const float* {
+        b = (int)(c / chunks);
+        row0 = (int)(c - (long long)b * chunks) * FS_ROWS;
+        nrow = min(FS_ROWS, N - row0);
+        return pred + ((long long)b * N + row0) * stride;
+    };
+    auto bulk_ok = [&](const float* src, int nrow) { return ((((uintptr_t)src) | (uintptr_t)(nrow * stride * 4)) & 15) == 0; };
+    auto issue = [&](long long c, int slot) {
+        int b, row0, nrow;
+        const float* src = chunk_src(c, b, row0, nrow);
+        if (lane == 0 && bulk_ok(src, nrow)) yf_bulk_load(bufs + slot * buf_floats, src, (unsigned)(nrow * stride * 4), bar + slot);
+    };
+
+    if (ch < total) issue(ch, 0);
+    for (int it = 0; ch < total; ch += nwarps, it++) {
+        const int slot = it & 1;
+        if (ch + nwarps < total) issue(ch + nwarps, slot ^ 1);     // the other buffer was released by the __syncwarp below
+        int b, row0, nrow;
+        const float* src = chunk_src(ch, b, row0, nrow);
+        float* rows = bufs + slot * buf_floats;
+        if (bulk_ok(src, nrow)) {
+            yf_bar_wait(bar + slot, slot ? phase1 : phase0);
+            if (slot) phase1 ^= 1u; else phase0 ^= 1u;
+        } else {
+            for (int i = lane; i < nrow * stride; i += 32) rows[i] = __ldg(src + i);
+            __syncwarp();
+        }
+        // filter the chunk: 4 groups of 32 rows, results held until the slots are reserved
+        double best[FS_ROWS / 32];
+        int bidx[FS_ROWS / 32];
+        unsigned okm[FS_ROWS / 32];
+        int n_pass = 0, n_ok = 0;
+#pragma unroll
+        for (int u = 0; u < FS_ROWS / 32; u++) {
+            const int r = u * 32 + lane;
+            const float* rp = rows + r * stride;
+            const float obj = (r < nrow) ? rp[4] : -1.f;
+            const bool pass = (double)obj > conf_thres;
+            best[u] = -1.0; bidx[u] = 0;
+            bool ok = false;
+            if (pass) {
+                const double o = (double)obj;
+                bool nan = false;
+                for (int c = 0; c < nc; c++) {
+                    const double v = (double)rp[5 + c] * o;
+                    nan |= (v != v);
+                    if (v > best[u]) { best[u] = v; bidx[u] = c; }  // strict: first index wins
+                }
+                ok = !nan && nc > 0 && best[u] > conf_thres;
+                if (ok && use_filter) ok = (cmask.w[bidx[u] >> 6] >> (bidx[u] & 63)) & 1ull;
+            }
+            n_pass += __popc(__ballot_sync(0xffffffffu, pass));
+            okm[u] = __ballot_sync(0xffffffffu, ok);
+            n_ok += __popc(okm[u]);
+        }
+        if (n_pass) {
+            int basei = 0;
+            if (lane == 0) {
+                atomicAdd(&xc_count[b], n_pass);
+                if (n_ok) basei = atomicAdd(&c_count[b], n_ok);
+            }
+            if (n_ok) {
+                basei = __shfl_sync(0xffffffffu, basei, 0);
+#pragma unroll
+                for (int u = 0; u < FS_ROWS / 32; u++) {
+                    if ((okm[u] >> lane) & 1u) {
+                        const int r = u * 32 + lane;
+                        const float* rp = rows + r * stride;
+                        const double x = (double)rp[0], y = (double)rp[1], w = (double)rp[2], h = (double)rp[3];
+                        float4 bx;
+                        bx.x = (float)(x - w / 2); bx.y = (float)(y - h / 2);
+                        bx.z = (float)(x + w / 2); bx.w = (float)(y + h / 2);
+                        const long long k = (long long)b * N + basei + __popc(okm[u] & ((1u << lane) - 1));
+                        c_score[k] = best[u]; c_box[k] = bx; c_meta[k] = make_int2(row0 + r, bidx[u]);
+                    }
+                    basei += __popc(okm[u]);
+                }
+            }
+        }
+        __syncwarp();   // every lane is done with this buffer before lane 0 lets the next copy land in it
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Pass 2: per-image ordering + greedy NMS.
 // ---------------------------------------------------------------------------------------------
@@ -680,9 +804,15 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
             int gx = tcb_div_up((n + FS_ROWS - 1) / FS_ROWS, 8);
             if (gx > cap) gx = cap;
             if (gx < 1) gx = 1;
-            const size_t fsm = 8 * FS_ROWS * (5 + nc) * sizeof(float);
-            if (fsm > 48 * 1024) TCB_CUDA(ctx, cudaFuncSetAttribute(yolo_filter_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-            yolo_filter_small_kernel<<<dim3(gx, b), 256, fsm, st>>>(
+            (void)gx;
+            // two row buffers per warp; as many CTAs as fit, each warp streaming its share of the b * ceil(n/128) chunks
+            const size_t fsm = 128 + (size_t)FS_WARPS * 2 * FS_ROWS * (5 + nc) * sizeof(float);
+            TCB_CUDA(ctx, cudaFuncSetAttribute(yolo_filter_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsm));
+            const int per_sm = (int)((220 * 1024) / (fsm + 1024)) < 4 ? (int)((220 * 1024) / (fsm + 1024)) : 4;
+            const long long chunks_total = (long long)b * ((n + FS_ROWS - 1) / FS_ROWS);
+            long long grid = tcb_div_up(chunks_total, FS_WARPS);
+            if (grid > (long long)ctx->num_sms * per_sm) grid = (long long)ctx->num_sms * per_sm;
+            yolo_filter_stream_kernel<<<(int)grid, 32 * FS_WARPS, fsm, st>>>(
                 pred_dev, b, n, nc, conf_thres, n_classes > 0, cm, c_score, c_box, c_meta, c_count, xc_count);
         } else {
             yolo_filter_kernel<<<dim3(bx, b), 256, 0, st>>>(pred_dev, b, n, nc, conf_thres, n_classes > 0, cm,

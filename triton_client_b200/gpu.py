@@ -324,6 +324,38 @@ class Engine:
         self.ctx.call("tcb_class_score_filter", _ptr(lab), _ptr(sc), n, len(groups), gc, gt, _ptr(out), _ptr(cnt), _lib.stream_ptr())
         return out, cnt
 
+    # ---- after the path: box rescale + overlay -------------------------------------
+    def scale_boxes(self, det, orig_size, input_size, normalized=False, math_mode=0):
+        """_scale_box_array (evaluate_inference.py:237-256) on (n,6) float64 CUDA rows; math_mode 1/2 = _scale_boxes
+        (ros_inference.py:100-115) under numpy < 2 / >= 2."""
+        _need_cuda(det)
+        d = det.contiguous().to(torch.float64).reshape(-1, 6)
+        out = torch.empty_like(d)
+        self.ctx.call("tcb_scale_boxes", _ptr(d), d.shape[0], int(orig_size[0]), int(orig_size[1]), int(input_size[0]), int(input_size[1]),
+                      int(bool(normalized)), int(math_mode), _ptr(out), _lib.stream_ptr())
+        return out
+
+    def draw_detections(self, frames, det, counts, class_names, color, input_size, thickness=2, labels=True, math_mode=1,
+                        normalized=False, per_class_color=False):
+        """The drawing loop of RosInference._callback (ros_inference.py:148-169) in place on CUDA frames
+        [b,h,w,3] (or [h,w,3]) uint8; det [b,max_det,6] float64 + counts [b] int32 as extract_boxes_device returns."""
+        _need_cuda(frames, det)
+        if frames.dtype != torch.uint8 or frames.shape[-1] != 3 or frames.dim() not in (3, 4):
+            raise TypeError("draw_detections: frames must be uint8 [b,h,w,3] or [h,w,3]")
+        f4 = frames if frames.dim() == 4 else frames.unsqueeze(0)
+        if f4.stride(3) != 1 or f4.stride(2) != 3:
+            raise TypeError("draw_detections: pixels must be packed (stride 3,1); rows and frames may be strided")
+        b, h, w = f4.shape[:3]
+        d = det.contiguous().to(torch.float64).reshape(b, -1, 6)
+        cnt = None if counts is None else counts.contiguous().to(torch.int32)
+        names = b"".join(str(n).encode("latin-1", "replace") + b"\0" for n in class_names)
+        cols = bytes(int(v) & 255 for c in (color if per_class_color else [color]) for v in c)
+        self.ctx.call("tcb_draw_detections", _ptr(f4), b, h, w, f4.stride(1), f4.stride(0) if b > 1 else h * f4.stride(1), _ptr(d),
+                      _ptr(cnt) if cnt is not None else None, d.shape[1], int(input_size[0]), int(input_size[1]), int(bool(normalized)),
+                      int(math_mode), names, len(class_names), cols, int(bool(per_class_color)), int(thickness), int(bool(labels)),
+                      _lib.stream_ptr())
+        return frames
+
 
 def yolo_nms_static(pred, conf_thres=0.6, iou_thres=0.45, classes=None, agnostic=False, max_det=300,
                     max_nms=30000, out=None, counts=None):
