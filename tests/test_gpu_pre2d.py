@@ -61,6 +61,41 @@ def test_letterbox_matches_oracle_exactly(engine, h, w, oh, ow):
     assert np.allclose(aff, [r, r, left, top])
 
 
+@pytest.mark.parametrize("h,w,oh,ow,mode", [
+    (256, 160, 128, 128, "letterbox"),   # 2:1, left pad 24 (a multiple of 4): fused 2x2 pass
+    (256, 168, 128, 128, "letterbox"),   # 2:1, left pad 22: falls back to the two-pass kernel
+    (64, 96, 32, 48, "stretch"),         # 2:1 stretch, one tile
+    (600, 1032, 300, 516, "stretch"),    # 2:1, ragged right tile, several tile rows
+    (720, 1280, 360, 640, "stretch"),
+    (2, 8, 1, 4, "stretch"),
+    (480, 1280, 512, 640, "stretch"),    # width halved, height up-scaled: fused pass with bilinear rows
+    (100, 64, 37, 32, "stretch"),
+    (375, 1242, 200, 621, "stretch"),    # width halved but 621 is not a multiple of 4: general kernel
+])
+def test_exact_half_scale_paths(engine, h, w, oh, ow, mode):
+    """cv2's INTER_LINEAR at exactly 2:1 is the 2x2 box mean; aligned cases take the fused pass, the rest the general
+    kernel. Also with channel swap + mean subtraction, a batch (first/last tile rows copy chunk-wise) and a row-strided,
+    4-byte aligned source that is not 16-byte aligned (fallback)."""
+    imgs = [synth.image_noise(h, w, 70 + i) for i in range(3)]
+    got, _ = _run(engine, imgs, oh, ow, mode=mode, div=255.0, pad_value=114)
+    for i, img in enumerate(imgs):
+        assert np.array_equal(got[i:i + 1], pre2d.preprocess_frame(img, oh, ow, mode=mode, div=255.0, pad_value=114)), (h, w, i)
+    got, _ = _run(engine, imgs[:1], oh, ow, mode=mode, swap=True, div=127.5, sub=(1, 1, 1))
+    want = pre2d.preprocess_frame(np.ascontiguousarray(imgs[0][..., ::-1]), oh, ow, mode=mode, div=127.5, pad_value=114) - np.float32(1)
+    if mode == "stretch":
+        assert np.array_equal(got, want)
+    if w >= 16:
+        big = torch.from_numpy(synth.image_noise(h + 3, w + 8, 80)).cuda()
+        view = big[1:h + 1, 4:w + 4]
+        out, _ = engine.preprocess_images(view, oh, ow, mode=mode, pad_value=114)
+        assert np.array_equal(out.cpu().numpy(), pre2d.preprocess_frame(view.cpu().numpy(), oh, ow, mode=mode, pad_value=114))
+    if w % 16 == 0:   # strided but 16-byte aligned rows: still the fused pass
+        big = torch.from_numpy(synth.image_noise(h, w + 16, 81)).cuda()
+        view = big[:, 16:]
+        out, _ = engine.preprocess_images(view, oh, ow, mode=mode, pad_value=114)
+        assert np.array_equal(out.cpu().numpy(), pre2d.preprocess_frame(view.cpu().numpy(), oh, ow, mode=mode, pad_value=114))
+
+
 def test_scaling_modes_swap_and_pad(engine):
     img = synth.image_noise(90, 160, 5)
     for scaling, div, sub in [("INCEPTION", 127.5, (1, 1, 1)), ("VGG", 1.0, (123, 117, 104)), ("COCO", 255.0, (0, 0, 0)), ("NONE", 1.0, (0, 0, 0))]:

@@ -36,6 +36,7 @@ struct PreParams {
     float rlo;  // float32 residual of 1/div (two-instruction exact division)
     int exact2;  // fma(v, rdiv, v*rlo) == v/div for all 256 inputs
     int vec_store;
+    int fast_area;  // exact 2:1 with 8-byte aligned column groups: one fused pass straight from the staged bytes
 };
 
 // u8 -> normalised f32, identical to numpy's `x.astype(float32) / div - sub` (true IEEE division).
@@ -381,6 +382,82 @@ __device__ __forceinline__ void pass_v(const PreParams& p, const unsigned short*
     }
 }
 
+// Width halved exactly (the reference's own 1280 -> 640, and the 2:1 letterbox), fused into one pass: warp = output
+// rows, lane = 4 output columns = 24 contiguous source bytes on each of two staged rows, read as three 8-byte words
+// per row (stride 24 B across lanes: conflict-free). Channel c of output pixel k is bytes 6k+c and 6k+c+3; each
+// horizontal sum is a short dp4a chain with constant byte weights.
+//   AREA  (height halved too): cv2's INTER_LINEAR is the 2x2 box mean (a+b+c+d+2)>>2; weights 1, the 2 rides in as
+//         the accumulator
+//   !AREA (any height): the x taps are (1024, 1024), so cv2's horizontal pass >> 4 is 64*(l + r): weights 64; the
+//         vertical pass is the general one
+// The host only selects this path when every 4-column group is entirely content or entirely padding and the
+// column offsets are 8-byte aligned (tcb_preprocess_image: fast_area).
+template <bool AREA, bool EXACT, bool HAS_SUB, bool INTERIOR>
+__device__ __forceinline__ void pass_area(const PreParams& p, const uint8_t* __restrict__ stg, const XTap* __restrict__ xt,
+                                          const YTap* __restrict__ yt, unsigned shift, int z, int tx0, int ty0) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int ox0 = tx0 + lane * 4;
+    if (ox0 >= p.out_w) return;
+    const int xoff = xt[lane * 4].off;
+    const bool inx = INTERIOR || xoff >= 0;
+    const uint8_t* colbase = stg + shift + (inx ? xoff : 0);
+    const int rpw = p.th >> 3;
+    const long long plane = (long long)p.out_h * p.out_w;
+    float* d0 = p.dst + ((long long)z * 3) * plane + (long long)(ty0 + warp * rpw) * p.out_w + ox0;
+    for (int rr = 0; rr < rpw; rr++, d0 += p.out_w) {
+        const int j = warp * rpw + rr;
+        if (ty0 + j >= p.out_h) break;
+        const YTap y = yt[j];
+        float o[3][4];
+        if (inx && (INTERIOR || y.r0 >= 0)) {
+            const uint2* r0 = reinterpret_cast<const uint2*>(colbase + y.r0 * p.pitch);
+            const uint2* r1 = reinterpret_cast<const uint2*>(colbase + y.r1 * p.pitch);
+            const uint2 a0 = r0[0], a1 = r0[1], a2 = r0[2], b0 = r1[0], b1 = r1[1], b2 = r1[2];
+            const unsigned A[6] = {a0.x, a0.y, a1.x, a1.y, a2.x, a2.y}, B[6] = {b0.x, b0.y, b1.x, b1.y, b2.x, b2.y};
+#pragma unroll
+            for (int h = 0; h < 2; h++) {   // pixel pair h: bytes 12h .. 12h+11 = words 3h .. 3h+2
+                const unsigned u0 = A[3 * h], u1 = A[3 * h + 1], u2 = A[3 * h + 2], v0 = B[3 * h], v1 = B[3 * h + 1], v2 = B[3 * h + 2];
+                unsigned s[6];
+                if (AREA) {
+                    s[0] = __dp4a(v0, 0x01000001u, __dp4a(u0, 0x01000001u, 2u));                                                        // B0 + B3
+                    s[1] = __dp4a(v1, 0x00000001u, __dp4a(v0, 0x00000100u, __dp4a(u1, 0x00000001u, __dp4a(u0, 0x00000100u, 2u))));    // B1 + B4
+                    s[2] = __dp4a(v1, 0x00000100u, __dp4a(v0, 0x00010000u, __dp4a(u1, 0x00000100u, __dp4a(u0, 0x00010000u, 2u))));    // B2 + B5
+                    s[3] = __dp4a(v2, 0x00000100u, __dp4a(v1, 0x00010000u, __dp4a(u2, 0x00000100u, __dp4a(u1, 0x00010000u, 2u))));    // B6 + B9
+                    s[4] = __dp4a(v2, 0x00010000u, __dp4a(v1, 0x01000000u, __dp4a(u2, 0x00010000u, __dp4a(u1, 0x01000000u, 2u))));    // B7 + B10
+                    s[5] = __dp4a(v2, 0x01000001u, __dp4a(u2, 0x01000001u, 2u));                                                        // B8 + B11
+                } else {
+                    // x taps (1024, 1024): cv2's horizontal pass gives 1024*(l + r), its >> 4 leaves 64*(l + r) (weights 0x40);
+                    // then the vertical pass as everywhere else: ((b0*S0) >> 16) + ((b1*S1) >> 16) + 2
+                    const unsigned t0[6] = {__dp4a(u0, 0x40000040u, 0u), __dp4a(u1, 0x00000040u, __dp4a(u0, 0x00004000u, 0u)),
+                                            __dp4a(u1, 0x00004000u, __dp4a(u0, 0x00400000u, 0u)), __dp4a(u2, 0x00004000u, __dp4a(u1, 0x00400000u, 0u)),
+                                            __dp4a(u2, 0x00400000u, __dp4a(u1, 0x40000000u, 0u)), __dp4a(u2, 0x40000040u, 0u)};
+                    const unsigned t1[6] = {__dp4a(v0, 0x40000040u, 0u), __dp4a(v1, 0x00000040u, __dp4a(v0, 0x00004000u, 0u)),
+                                            __dp4a(v1, 0x00004000u, __dp4a(v0, 0x00400000u, 0u)), __dp4a(v2, 0x00004000u, __dp4a(v1, 0x00400000u, 0u)),
+                                            __dp4a(v2, 0x00400000u, __dp4a(v1, 0x40000000u, 0u)), __dp4a(v2, 0x40000040u, 0u)};
+#pragma unroll
+                    for (int q = 0; q < 6; q++) s[q] = __umulhi(y.b0s, t0[q]) + __umulhi(y.b1s, t1[q]) + 2u;
+                }
+#pragma unroll
+                for (int k = 0; k < 2; k++)
+#pragma unroll
+                    for (int c = 0; c < 3; c++) {
+                        const int cc = p.swap ? 2 - c : c;
+                        o[c][2 * h + k] = norm2<EXACT, HAS_SUB>((int)(s[3 * k + c] >> 2), p.div, p.rdiv, p.rlo, p.sub[cc]);
+                    }
+            }
+        } else {
+#pragma unroll
+            for (int c = 0; c < 3; c++) {
+                const float pv = p.padv[p.swap ? 2 - c : c];
+#pragma unroll
+                for (int i = 0; i < 4; i++) o[c][i] = pv;
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < 3; c++) st_stream_f4(d0 + (p.swap ? 2 - c : c) * plane, make_float4(o[c][0], o[c][1], o[c][2], o[c][3]));
+    }
+}
+
 template <bool AREA, bool EXACT, bool HAS_SUB>
 __global__ void __launch_bounds__(NTHREADS) preprocess2_kernel(const PreParams p, const TileGeo geo) {
     extern __shared__ __align__(16) uint8_t smem[];
@@ -468,6 +545,12 @@ __global__ void __launch_bounds__(NTHREADS) preprocess2_kernel(const PreParams p
     if (H.has_content && H.safe) mbar_wait(bar, 0);
     __syncthreads();
 
+    if (p.fast_area) {   // AREA: 2x2 box mean; otherwise x exactly 2:1 with bilinear y
+        const unsigned shift = (unsigned)((uintptr_t)(img + (long long)H.rmin * p.row_stride + (long long)H.xmin * 3) & 15u);
+        if (H.interior) pass_area<AREA, EXACT, HAS_SUB, true>(p, stg, xt, yt, shift, z, tx0, ty0);
+        else pass_area<AREA, EXACT, HAS_SUB, false>(p, stg, xt, yt, shift, z, tx0, ty0);
+        return;
+    }
     // ---- pass H: thread = (column, row parity); 6 source bytes per row come in as three aligned words -----------------
     {
         const int col = tid & (TW - 1), par = tid >> 7;  // NTHREADS == 2*TW
@@ -604,6 +687,9 @@ extern "C" int tcb_preprocess_image(tcb_ctx* ctx, const uint8_t* src_dev, int n,
     // Tile height: the largest of 32/16/8 output rows whose shared-memory need (staged source bytes + 16-bit row
     // buffer + tap tables) stays <= 36 KB, so that six CTAs fit an SM; failing that the largest that fits 100 KB;
     // failing that (extreme down-scaling) the one-pass kernel that reads the source straight from global memory.
+    const bool half_x = (w == 2 * p.new_w);   // x taps are then (1024, 1024) on columns 2dx, 2dx+1 for every dx
+    p.fast_area = (area || half_x) && p.vec_store && (((uintptr_t)src_dev & 15) == 0) && (src_row_stride % 16 == 0) &&
+                  (n == 1 || src_img_stride % 16 == 0) && (p.left % 4 == 0) && (p.new_w % 4 == 0);
     const size_t SMEM_MAX = 100 * 1024, SMEM_GOOD = 36 * 1024;
     bool staged = false;
     size_t smem = 0;
@@ -615,7 +701,7 @@ extern "C" int tcb_preprocess_image(tcb_ctx* ctx, const uint8_t* src_dev, int n,
             long long rows = (long long)floor((th - 1) * sy) + 4;
             if (rows > h) rows = h;
             const long long pitch = ((cols * 3 + 15) / 16) * 16 + 32;   // +16 alignment shift, +16 so a clamped right tap stays inside
-            const size_t stage = (size_t)(rows * pitch), hsb = (size_t)rows * TW * 3 * 2;
+            const size_t stage = (size_t)(rows * pitch), hsb = p.fast_area ? 0 : (size_t)rows * TW * 3 * 2;
             const size_t need = stage + hsb + TW * sizeof(XTap) + 32 * sizeof(YTap) + 16;   // + the mbarrier
             if (need <= (pass == 0 ? SMEM_GOOD : SMEM_MAX)) {
                 staged = true; smem = need; p.th = th; p.pitch = (int)pitch; p.stage_bytes = (int)stage; p.hs_bytes = (int)hsb; p.nr_cap = (int)rows;
