@@ -135,7 +135,7 @@ class FakeResponse:
 
 # --- reference: clients/postprocess/yolov5_postprocess.py:28-125 ----------------------------------
 def extract_boxes(prediction, conf_thres=0.6, iou_thres=0.45, classes=None, agnostic=False, max_det=300,
-                  as_written=True, nms="torchvision"):
+                  as_written=True, nms="torchvision", max_nms=30000):
     """`prediction`: FakeResponse (wire bytes) or an f32 ndarray [B,N,5+nc]. Returns what the reference
     returns: list of (n,6) float64 tensors, or the caught exception object (:124-125)."""
     if isinstance(prediction, np.ndarray):
@@ -152,7 +152,7 @@ def extract_boxes(prediction, conf_thres=0.6, iou_thres=0.45, classes=None, agno
         assert 0 <= conf_thres <= 1, f'Invalid Confidence threshold {conf_thres}, valid values are between 0.0 and 1.0'
         assert 0 <= iou_thres <= 1, f'Invalid IoU {iou_thres}, valid values are between 0.0 and 1.0'
         max_wh = 4096
-        max_nms = 30000
+        # max_nms: 30000 in the reference (a local there; a parameter here so the tests can reach the cut)
         output = [torch.zeros((0, 6))] * prediction.shape[0]
         for xi, x in enumerate(prediction):
             x = x[xc[xi]]

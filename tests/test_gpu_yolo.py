@@ -69,6 +69,31 @@ def test_many_candidates_sorts_in_global_scratch(engine):
     _same(got, want)
 
 
+def test_class_groups_and_their_fallbacks(engine):
+    """Class-aware NMS runs as independent per-class-group CTAs merged by score. Frames where that split is not exact
+    are done whole: boxes reaching beyond +-2048 px (classes 4096 apart can then overlap and suppress each other, as
+    they do in the reference), and frames with more candidates than max_nms (the reference keeps the max_nms best over
+    all classes first)."""
+    pred = synth.yolo_output(3, 3000, 5, 91, objects=30, rows_per_object=25, tie_frac=0.4)
+    rng = np.random.default_rng(4)
+    huge = rng.choice(3000, 60, replace=False)          # frame 1: giant boxes of several classes around the same centre
+    pred[1, huge, 0:2] = 3000 + rng.normal(0, 30, (60, 2))
+    pred[1, huge, 2:4] = rng.uniform(5000, 9000, (60, 2))
+    pred[1, huge, 4] = rng.uniform(0.5, 1, 60)
+    pred[1, huge, 5:] = rng.uniform(0, 0.3, (60, 5))
+    pred[1, huge, 5 + rng.integers(0, 5, 60)] = rng.uniform(0.7, 1, 60)
+    for kw in [dict(conf_thres=0.3), dict(conf_thres=0.3, max_det=11), dict(conf_thres=0.3, iou_thres=0.2)]:
+        want = yolo_post.extract_boxes(pred, as_written=False, **kw)
+        got, _ = _gpu(engine, pred, **kw)
+        _same(got, want)
+    assert len({int(c) for c in want[1][:, 5]}) >= 1
+    # more candidates than max_nms
+    dev = torch.from_numpy(pred).cuda()
+    out, cnt, _ = engine.yolo_nms(dev, conf_thres=0.3, max_nms=200)
+    want = yolo_post.extract_boxes(pred, conf_thres=0.3, as_written=False, max_nms=200)
+    _same([out[i, :int(cnt[i])].cpu().numpy() for i in range(3)], want)
+
+
 def test_empty_and_ragged(engine):
     pred = synth.yolo_output(3, 300, 2, 5)
     pred[1, :, 4] = 0.0  # image 1 has no candidate at all

@@ -542,7 +542,7 @@ __global__ void __launch_bounds__(NTHREADS) preprocess2_kernel(const PreParams p
         }
         yt[j] = e;
     }
-    if (H.has_content && H.safe) mbar_wait(bar, 0);
+    if (H.has_content && H.safe && tid < 32) mbar_wait(bar, 0);   // one warp polls; the rest sleep in the barrier below
     __syncthreads();
 
     if (p.fast_area) {   // AREA: 2x2 box mean; otherwise x exactly 2:1 with bilinear y

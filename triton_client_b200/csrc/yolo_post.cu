@@ -30,20 +30,29 @@ struct ClassMask { unsigned long long w[4]; };  // whitelist for classes 0..255
 constexpr int FILTER_UNROLL = 4;   // 32-row groups in flight per warp (independent objectness loads)
 constexpr int FILTER_SMALL_NC = 8;  // up to this many classes a surviving lane decodes its own row
 
+// A frame whose candidates all have every coordinate inside (-2048, 2048) cannot have boxes of different classes
+// overlap after the reference's class * 4096 offset, so its NMS splits exactly into independent per-class problems
+// (yolo_nms_kernel, class groups). The filters raise big[b] for the frames where that is not guaranteed.
+__device__ __forceinline__ void note_big(const float4 bx, int* __restrict__ big, int b) {
+    if (big && !(fabsf(bx.x) < 2048.f && fabsf(bx.y) < 2048.f && fabsf(bx.z) < 2048.f && fabsf(bx.w) < 2048.f)) atomicOr(&big[b], 1);
+}
+
 __device__ __forceinline__ void emit_candidate(const float* __restrict__ rp, int r, double best, int bidx, long long k,
-                                               double* __restrict__ c_score, float4* __restrict__ c_box, int2* __restrict__ c_meta) {
+                                               double* __restrict__ c_score, float4* __restrict__ c_box, int2* __restrict__ c_meta,
+                                               int* __restrict__ big, int b) {
     const double x = (double)__ldg(rp), y = (double)__ldg(rp + 1);
     const double w = (double)__ldg(rp + 2), h = (double)__ldg(rp + 3);
     float4 bx;
     bx.x = (float)(x - w / 2); bx.y = (float)(y - h / 2);
     bx.z = (float)(x + w / 2); bx.w = (float)(y + h / 2);
     c_score[k] = best; c_box[k] = bx; c_meta[k] = make_int2(r, bidx);
+    note_big(bx, big, b);
 }
 
 __global__ void __launch_bounds__(256) yolo_filter_kernel(
     const float* __restrict__ pred, int B, int N, int nc, double conf_thres, int use_filter, ClassMask cmask,
     double* __restrict__ c_score, float4* __restrict__ c_box, int2* __restrict__ c_meta,
-    int* __restrict__ c_count, int* __restrict__ xc_count) {
+    int* __restrict__ c_count, int* __restrict__ xc_count, int* __restrict__ big) {
     // grid: x = warps striding over the 32-row groups of one image, y = image (no index division needed)
     const int lane = threadIdx.x & 31;
     const int warp_in_img = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -91,7 +100,7 @@ __global__ void __launch_bounds__(256) yolo_filter_kernel(
                     if (lane == 0) basei = atomicAdd(&c_count[b], __popc(em));
                     basei = __shfl_sync(0xffffffffu, basei, 0);
                     if (ok) emit_candidate(rp, row0 + lane, best, bidx, (long long)b * N + basei + __popc(em & ((1u << lane) - 1)),
-                                           c_score, c_box, c_meta);
+                                           c_score, c_box, c_meta, big, b);
                 }
             } else {
                 // many classes: the warp cooperates on each surviving row (coalesced loads, shuffle arg-max)
@@ -119,7 +128,7 @@ __global__ void __launch_bounds__(256) yolo_filter_kernel(
                     if (lane == 0 && !nan && best > conf_thres) {
                         bool ok = true;
                         if (use_filter) ok = (bidx < 256) && ((cmask.w[bidx >> 6] >> (bidx & 63)) & 1ull);
-                        if (ok) emit_candidate(rp, r, best, bidx, (long long)b * N + atomicAdd(&c_count[b], 1), c_score, c_box, c_meta);
+                        if (ok) emit_candidate(rp, r, best, bidx, (long long)b * N + atomicAdd(&c_count[b], 1), c_score, c_box, c_meta, big, b);
                     }
                 }
             }
@@ -127,84 +136,11 @@ __global__ void __launch_bounds__(256) yolo_filter_kernel(
     }
 }
 
-// Small class counts (rows of <= 13 floats): every 32-byte sector of the tensor is touched anyway, so each warp
-// first pulls its 128 rows into shared memory with fully coalesced loads (one DRAM round trip instead of the
-// objectness -> class scores -> box chain of dependent sector fetches), then filters and decodes from there.
+// Small class counts (rows of <= 13 floats): every 32-byte sector of the tensor is touched anyway, so the rows are
+// pulled into shared memory whole (one DRAM round trip instead of the objectness -> class scores -> box chain of
+// dependent sector fetches) and filtered / decoded from there.
 constexpr int FS_ROWS = 128;   // rows per warp and pass
-__global__ void __launch_bounds__(256) yolo_filter_small_kernel(
-    const float* __restrict__ pred, int B, int N, int nc, double conf_thres, int use_filter, ClassMask cmask,
-    double* __restrict__ c_score, float4* __restrict__ c_box, int2* __restrict__ c_meta,
-    int* __restrict__ c_count, int* __restrict__ xc_count) {
-    extern __shared__ __align__(16) float fs_smem[];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int stride = 5 + nc;
-    float* rows = fs_smem + warp * (FS_ROWS * stride);
-    const int b = blockIdx.y;
-    const float* base = pred + ((long long)b * N) * stride;
-    const int chunks = (N + FS_ROWS - 1) / FS_ROWS;
-    const int wpi = (gridDim.x * blockDim.x) >> 5;
-    for (int ch = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5); ch < chunks; ch += wpi) {
-        const int row0 = ch * FS_ROWS;
-        const int nrow = min(FS_ROWS, N - row0);
-        const float* src = base + (long long)row0 * stride;
-        const int nfl = nrow * stride;
-        if ((((uintptr_t)src) & 15) == 0) {
-            const int n4 = nfl >> 2;
-            for (int i0 = 0; i0 < n4; i0 += 8 * 32) {   // 8 independent 16-byte loads in flight per lane before the first store
-                float4 v[8];
-#pragma unroll
-                for (int q = 0; q < 8; q++) { const int i = i0 + q * 32 + lane; if (i < n4) v[q] = __ldg(reinterpret_cast<const float4*>(src) + i); }
-#pragma unroll
-                for (int q = 0; q < 8; q++) { const int i = i0 + q * 32 + lane; if (i < n4) reinterpret_cast<float4*>(rows)[i] = v[q]; }
-            }
-            for (int i = (n4 << 2) + lane; i < nfl; i += 32) rows[i] = __ldg(src + i);
-        } else {
-            for (int i = lane; i < nfl; i += 32) rows[i] = __ldg(src + i);
-        }
-        __syncwarp();
-#pragma unroll
-        for (int u = 0; u < FS_ROWS / 32; u++) {
-            const int r = u * 32 + lane;
-            const float* rp = rows + r * stride;
-            const float obj = (r < nrow) ? rp[4] : -1.f;
-            const bool pass = (double)obj > conf_thres;
-            const unsigned m = __ballot_sync(0xffffffffu, pass);
-            if (m == 0) continue;
-            if (lane == 0) atomicAdd(&xc_count[b], __popc(m));
-            double best = -1.0;
-            int bidx = 0;
-            bool ok = false;
-            if (pass) {
-                const double o = (double)obj;
-                bool nan = false;
-                for (int c = 0; c < nc; c++) {
-                    const double v = (double)rp[5 + c] * o;
-                    nan |= (v != v);
-                    if (v > best) { best = v; bidx = c; }  // strict: first index wins
-                }
-                ok = !nan && nc > 0 && best > conf_thres;
-                if (ok && use_filter) ok = (cmask.w[bidx >> 6] >> (bidx & 63)) & 1ull;
-            }
-            const unsigned em = __ballot_sync(0xffffffffu, ok);
-            if (em) {
-                int basei = 0;
-                if (lane == 0) basei = atomicAdd(&c_count[b], __popc(em));
-                basei = __shfl_sync(0xffffffffu, basei, 0);
-                if (ok) {
-                    const double x = (double)rp[0], y = (double)rp[1], w = (double)rp[2], h = (double)rp[3];
-                    float4 bx;
-                    bx.x = (float)(x - w / 2); bx.y = (float)(y - h / 2);
-                    bx.z = (float)(x + w / 2); bx.w = (float)(y + h / 2);
-                    const long long k = (long long)b * N + basei + __popc(em & ((1u << lane) - 1));
-                    c_score[k] = best; c_box[k] = bx; c_meta[k] = make_int2(row0 + r, bidx);
-                }
-            }
-        }
-        __syncwarp();
-    }
-}
-
-// The same filter as a stream: every warp owns two row buffers and keeps a bulk copy (TMA, completion on an
+// As a stream: every warp owns two row buffers and keeps a bulk copy (TMA, completion on an
 // mbarrier) of its next 128-row chunk in flight while it filters the current one, and reserves output slots once
 // per chunk (one returning atomic instead of one per 32 rows). Chunks that are not 16-byte aligned/sized (the last
 // one of a frame, odd strides, unaligned tensors) are copied by the lanes instead.
@@ -229,7 +165,7 @@ constexpr int FS_WARPS = 8;
 __global__ void __launch_bounds__(32 * FS_WARPS) yolo_filter_stream_kernel(
     const float* __restrict__ pred, int B, int N, int nc, double conf_thres, int use_filter, ClassMask cmask,
     double* __restrict__ c_score, float4* __restrict__ c_box, int2* __restrict__ c_meta,
-    int* __restrict__ c_count, int* __restrict__ xc_count) {
+    int* __restrict__ c_count, int* __restrict__ xc_count, int* __restrict__ big) {
     extern __shared__ __align__(128) unsigned char ys_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int stride = 5 + nc;
@@ -319,6 +255,7 @@ __global__ void __launch_bounds__(32 * FS_WARPS) yolo_filter_stream_kernel(
                         bx.z = (float)(x + w / 2); bx.w = (float)(y + h / 2);
                         const long long k = (long long)b * N + basei + __popc(okm[u] & ((1u << lane) - 1));
                         c_score[k] = best[u]; c_box[k] = bx; c_meta[k] = make_int2(row0 + r, bidx[u]);
+                        note_big(bx, big, b);
                     }
                     basei += __popc(okm[u]);
                 }
@@ -505,11 +442,25 @@ struct NmsShared {
 struct CandShared { float4 box[RESIDENT]; int cls[RESIDENT]; unsigned slot[RESIDENT]; };
 static_assert(sizeof(CandShared) <= sizeof(SortEnt) * SORT_SMEM_CAP + 32 * 1024, "candidate arrays overflow their region");
 
+// Class groups (gridDim.y = G > 1): class-aware NMS of a frame whose boxes all lie inside (-2048, 2048) is G
+// independent problems (classes c with c % G == g), one CTA each; every CTA leaves its kept rows, in order, in a
+// staging list and the last one of the frame to finish merges the G lists by (score desc, row asc) into the
+// output. Frames that cannot be split (big[b], or more candidates than max_nms: the reference cuts to the max_nms
+// best over all classes first) are done whole by the g == 0 CTA; the merge is then a copy.
+struct GroupOut {
+    double* rows;                // [b*G][max_det][6]
+    unsigned long long* key;     // [b*G][max_det] score bits of each kept row
+    unsigned* krow;              // [b*G][max_det] its row in the prediction tensor
+    int* count;                  // [b*G]
+    int* done;                   // [b] CTAs of the frame that have finished (zeroed per call)
+    const int* big;              // [b]
+};
+
 __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
     int N, const double* __restrict__ c_score, const float4* __restrict__ c_box, const int2* __restrict__ c_meta,
     const int* __restrict__ c_count, SortEnt* __restrict__ gsort, int gsort_stride,
     double iou_thres, double class_offset, int max_det, int max_nms,
-    double* __restrict__ out, int* __restrict__ out_count) {
+    double* __restrict__ out, int* __restrict__ out_count, const GroupOut go) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     NmsShared& S = *reinterpret_cast<NmsShared*>(smem_raw);
     unsigned long long* skeys = reinterpret_cast<unsigned long long*>(smem_raw + sizeof(NmsShared));
@@ -520,32 +471,66 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
 #ifdef TCB_NMS_PROFILE
     long long prof_t0 = clock64();
 #endif
-    int n = min(c_count[b], N);
+    const int G = gridDim.y, g = blockIdx.y;
+    const int n_all = min(c_count[b], N);
+    const bool split = G > 1 && go.big[b] == 0 && n_all <= max_nms;
     const long long cbase = (long long)b * N;
     if (tid == 0) S.nkept = 0;
     for (int i = tid; i < MAX_NMS_CAP / 32; i += NMS_THREADS) S.resolved[i] = 0u;
+    int n = n_all;
+    if (G > 1) {
+        if (split) {   // candidates of this CTA's classes
+            int mine = 0;
+            for (int i = tid; i < n_all; i += NMS_THREADS) mine += (c_meta[cbase + i].y % G) == g;
+#pragma unroll
+            for (int sft = 16; sft > 0; sft >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, sft);
+            if (lane == 0) S.warp_cnt[warp] = mine;
+            __syncthreads();
+            n = 0;
+            for (int w = 0; w < NMS_THREADS / 32; w++) n += S.warp_cnt[w];
+            __syncthreads();
+            if (tid == 0) S.a_total = 0;   // compaction cursor
+        } else if (g > 0) {
+            n = 0;
+        }
+    }
 
     // ---- order candidates: score descending, row ascending ------------------------------------
     int npad = 1;
     while (npad < n) npad <<= 1;
     const bool sort_in_smem = npad <= SORT_SMEM_CAP;
     // global sort scratch of image b: npad keys followed by npad metas
-    unsigned long long* gkeys = reinterpret_cast<unsigned long long*>(gsort + (long long)b * gsort_stride);
+    unsigned long long* gkeys = reinterpret_cast<unsigned long long*>(gsort + ((long long)b * G + g) * gsort_stride);
     uint2* gmeta = reinterpret_cast<uint2*>(gkeys + gsort_stride);
     unsigned long long* keys = sort_in_smem ? skeys : gkeys;
     uint2* meta = sort_in_smem ? smeta : gmeta;
     const int nfill = sort_in_smem ? (npad <= 1024 ? 1024 : (npad <= 2048 ? 2048 : 4096)) : npad;
-    for (int i = tid; i < nfill; i += NMS_THREADS) {
-        if (i < n) {
-            keys[i] = (unsigned long long)__double_as_longlong(c_score[cbase + i]);
-            meta[i] = make_uint2((unsigned)c_meta[cbase + i].x, (unsigned)i);
-        } else {
-            keys[i] = 0ull; meta[i] = make_uint2(0xffffffffu, 0u);
+    if (split) {   // gather this group's candidates (any order: the sort below fixes it), then pad
+        __syncthreads();
+        for (int i = tid; i < n_all; i += NMS_THREADS) {
+            const int2 m = c_meta[cbase + i];
+            if ((m.y % G) == g) {
+                const int q = atomicAdd(&S.a_total, 1);
+                keys[q] = (unsigned long long)__double_as_longlong(c_score[cbase + i]);
+                meta[q] = make_uint2((unsigned)m.x, (unsigned)i);
+            }
+        }
+        for (int i = n + tid; i < nfill; i += NMS_THREADS) { keys[i] = 0ull; meta[i] = make_uint2(0xffffffffu, 0u); }
+    } else {
+        for (int i = tid; i < nfill; i += NMS_THREADS) {
+            if (i < n) {
+                keys[i] = (unsigned long long)__double_as_longlong(c_score[cbase + i]);
+                meta[i] = make_uint2((unsigned)c_meta[cbase + i].x, (unsigned)i);
+            } else {
+                keys[i] = 0ull; meta[i] = make_uint2(0xffffffffu, 0u);
+            }
         }
     }
     __syncthreads();
     PROF_T(0);
-    if (sort_in_smem) {
+    if (n < 2) {
+        // nothing to order
+    } else if (sort_in_smem) {
         if (nfill == 1024) bitonic_sort_regs<1>(skeys, smeta, n);
         else if (nfill == 2048) bitonic_sort_regs<2>(skeys, smeta, n);
         else bitonic_sort_regs<4>(skeys, smeta, n);
@@ -710,17 +695,62 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
     }
     __syncthreads();
     // ---- write the kept rows: [x1,y1,x2,y2 (f32 box widened), conf (f64), cls] -------------------------
-    double* orow = out + (long long)b * max_det * 6;
+    const long long list = (long long)b * G + g;
+    double* orow = G > 1 ? go.rows + list * max_det * 6 : out + (long long)b * max_det * 6;
     const int nk_final = S.nkept;
     for (int k = tid; k < nk_final; k += NMS_THREADS) {
         const unsigned slot = S.kslot[k];
         const float4 bx = S.kbox[k];
         double* o = orow + (long long)k * 6;
+        const double sc = c_score[cbase + slot];
         o[0] = (double)bx.x; o[1] = (double)bx.y; o[2] = (double)bx.z; o[3] = (double)bx.w;
-        o[4] = c_score[cbase + slot];
+        o[4] = sc;
         o[5] = (double)(S.kcls[k] & (SMALL_BIT - 1));
+        if (G > 1) {
+            go.key[list * max_det + k] = (unsigned long long)__double_as_longlong(sc);
+            go.krow[list * max_det + k] = (unsigned)c_meta[cbase + slot].x;
+        }
     }
-    if (tid == 0) out_count[b] = nk_final;
+    if (G == 1) {
+        if (tid == 0) out_count[b] = nk_final;
+    } else {
+        if (tid == 0) go.count[list] = nk_final;
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) S.next_pos = atomicAdd(&go.done[b], 1);
+        __syncthreads();
+        if (S.next_pos == G - 1) {   // last CTA of the frame: merge the G ordered lists
+            __threadfence();
+            int total = 0;
+            for (int q = 0; q < G; q++) total += __ldcg(&go.count[(long long)b * G + q]);
+            for (int e = tid; e < G * max_det; e += NMS_THREADS) {
+                const int q = e / max_det, i = e - q * max_det;
+                const long long lq = (long long)b * G + q;
+                if (i >= __ldcg(&go.count[lq])) continue;
+                const unsigned long long ke = __ldcg(&go.key[lq * max_det + i]);
+                const unsigned re = __ldcg(&go.krow[lq * max_det + i]);
+                int rank = i;
+                for (int o2 = 0; o2 < G; o2++) {
+                    if (o2 == q) continue;
+                    const long long lo2 = (long long)b * G + o2;
+                    int lo = 0, hi = __ldcg(&go.count[lo2]);   // entries of list o2 that come before e
+                    while (lo < hi) {
+                        const int mid = (lo + hi) >> 1;
+                        if (rec_before(__ldcg(&go.key[lo2 * max_det + mid]), __ldcg(&go.krow[lo2 * max_det + mid]), ke, re)) lo = mid + 1;
+                        else hi = mid;
+                    }
+                    rank += lo;
+                }
+                if (rank < max_det) {
+                    const double* src = go.rows + (lq * max_det + i) * 6;
+                    double* dst = out + ((long long)b * max_det + rank) * 6;
+#pragma unroll
+                    for (int c = 0; c < 6; c++) dst[c] = __ldcg(src + c);
+                }
+            }
+            if (tid == 0) out_count[b] = min(total, max_det);
+        }
+    }
     PROF_T(6);
 #ifdef TCB_NMS_PROFILE
     if (blockIdx.x == 0 && threadIdx.x == 0) { atomicAdd((unsigned long long*)&g_nms_prof[7], (unsigned long long)nk_final * 1000000ull + (unsigned long long)n); }
@@ -735,6 +765,7 @@ extern "C" void tcb_debug_nms_prof(long long* out8, int reset) {
 namespace {
 #endif
 
+constexpr int MAX_GROUPS = 8;   // class groups per frame (CTAs sharing one frame's NMS)
 constexpr size_t NMS_SMEM_BYTES = sizeof(NmsShared) + (sizeof(CandShared) > sizeof(SortEnt) * SORT_SMEM_CAP ? sizeof(CandShared) : sizeof(SortEnt) * SORT_SMEM_CAP);
 
 size_t yolo_ws_bytes(int b, int n) {
@@ -743,10 +774,14 @@ size_t yolo_ws_bytes(int b, int n) {
     bytes += per * sizeof(double) + 256;
     bytes += per * sizeof(float4) + 256;
     bytes += per * sizeof(int2) + 256;
-    bytes += (size_t)b * 2 * sizeof(int) + 256;
+    bytes += (size_t)b * 4 * sizeof(int) + 256;
     int npad = 1;
     while (npad < n) npad <<= 1;
-    if (npad > SORT_SMEM_CAP) bytes += (size_t)b * npad * sizeof(SortEnt) + 256;
+    // class groups: b * G lists with G <= SMs / b, so never more than max(b, SM count) lists (256 bounds today's parts)
+    size_t lists = (size_t)b * MAX_GROUPS;
+    if (lists > 256) lists = b > 256 ? (size_t)b : 256;
+    if (npad > SORT_SMEM_CAP) bytes += lists * npad * sizeof(SortEnt) + 256;
+    bytes += lists * ((size_t)MAX_DET_CAP * (6 * 8 + 8 + 4) + 4) + 4 * 256;   // staging lists
     return bytes;
 }
 
@@ -778,7 +813,15 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
     }
 
     const size_t per = (size_t)b * (n > 0 ? n : 1);
-    TCB_WS(ctx, counts, int, (size_t)b * 2);
+    // class groups: as many CTAs per frame as the SM count allows, never more than classes; class-agnostic NMS is one problem
+    int G = 1;
+    if (!agnostic && nc > 1) {
+        G = ctx->num_sms / b;
+        if (G > nc) G = nc;
+        if (G > MAX_GROUPS) G = MAX_GROUPS;
+        if (G < 1) G = 1;
+    }
+    TCB_WS(ctx, counts, int, (size_t)b * 4);
     TCB_WS(ctx, c_score, double, per);
     TCB_WS(ctx, c_box, float4, per);
     TCB_WS(ctx, c_meta, int2, per);
@@ -786,12 +829,22 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
     while (npad < n) npad <<= 1;
     SortEnt* gsort = nullptr;
     if (npad > SORT_SMEM_CAP) {
-        TCB_WS(ctx, gs, SortEnt, (size_t)b * npad);
+        TCB_WS(ctx, gs, SortEnt, (size_t)b * G * npad);
         gsort = gs;
     }
     int* c_count = counts;
     int* xc_count = counts + b;
-    TCB_CUDA(ctx, cudaMemsetAsync(counts, 0, sizeof(int) * 2 * (size_t)b, st));
+    int* big = counts + 2 * (size_t)b;
+    GroupOut go;
+    memset(&go, 0, sizeof(go));
+    if (G > 1) {
+        TCB_WS(ctx, g_rows, double, (size_t)b * G * max_det * 6);
+        TCB_WS(ctx, g_key, unsigned long long, (size_t)b * G * max_det);
+        TCB_WS(ctx, g_krow, unsigned, (size_t)b * G * max_det);
+        TCB_WS(ctx, g_count, int, (size_t)b * G);
+        go.rows = g_rows; go.key = g_key; go.krow = g_krow; go.count = g_count; go.done = counts + 3 * (size_t)b; go.big = big;
+    }
+    TCB_CUDA(ctx, cudaMemsetAsync(counts, 0, sizeof(int) * 4 * (size_t)b, st));
 
     if (n > 0) {
         // 8 warps per CTA, FILTER_UNROLL 32-row groups per warp and pass; y = image
@@ -813,17 +866,17 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
             long long grid = tcb_div_up(chunks_total, FS_WARPS);
             if (grid > (long long)ctx->num_sms * per_sm) grid = (long long)ctx->num_sms * per_sm;
             yolo_filter_stream_kernel<<<(int)grid, 32 * FS_WARPS, fsm, st>>>(
-                pred_dev, b, n, nc, conf_thres, n_classes > 0, cm, c_score, c_box, c_meta, c_count, xc_count);
+                pred_dev, b, n, nc, conf_thres, n_classes > 0, cm, c_score, c_box, c_meta, c_count, xc_count, big);
         } else {
             yolo_filter_kernel<<<dim3(bx, b), 256, 0, st>>>(pred_dev, b, n, nc, conf_thres, n_classes > 0, cm,
-                                                            c_score, c_box, c_meta, c_count, xc_count);
+                                                            c_score, c_box, c_meta, c_count, xc_count, big);
         }
         TCB_LAUNCHED(ctx);
     }
     const size_t smem = NMS_SMEM_BYTES;
     TCB_CUDA(ctx, cudaFuncSetAttribute(yolo_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    yolo_nms_kernel<<<b, NMS_THREADS, smem, st>>>(n > 0 ? n : 1, c_score, c_box, c_meta, c_count, gsort, npad,
-                                                  iou_thres, agnostic ? 0.0 : 4096.0, max_det, max_nms, out_dev, count_dev);
+    yolo_nms_kernel<<<dim3(b, G), NMS_THREADS, smem, st>>>(n > 0 ? n : 1, c_score, c_box, c_meta, c_count, gsort, npad,
+                                                           iou_thres, agnostic ? 0.0 : 4096.0, max_det, max_nms, out_dev, count_dev, go);
     TCB_LAUNCHED(ctx);
     if (xc_count_dev)
         TCB_CUDA(ctx, cudaMemcpyAsync(xc_count_dev, xc_count, sizeof(int) * (size_t)b, cudaMemcpyDeviceToDevice, st));
@@ -952,12 +1005,14 @@ extern "C" int tcb_yolo_nms_static(const float* pred_dev, int b, int n, int nc, 
         if (bx > cap) bx = cap;
         if (bx < 1) bx = 1;
         yolo_filter_kernel<<<dim3(bx, b), 256, 0, st>>>(pred_dev, b, n, nc, conf_thres, n_classes > 0, cm,
-                                                        c_score, c_box, c_meta, c_count, xc_count);
+                                                        c_score, c_box, c_meta, c_count, xc_count, nullptr);
         ST_CUDA(cudaGetLastError());
     }
     const size_t smem = NMS_SMEM_BYTES;
+    GroupOut one_group;   // one CTA per frame: the fixed scratch has no room for class-group staging
+    memset(&one_group, 0, sizeof(one_group));
     yolo_nms_kernel<<<b, NMS_THREADS, smem, st>>>(n > 0 ? n : 1, c_score, c_box, c_meta, c_count, gsort, npad,
-                                                  iou_thres, agnostic ? 0.0 : 4096.0, max_det, max_nms, out_dev, count_dev);
+                                                  iou_thres, agnostic ? 0.0 : 4096.0, max_det, max_nms, out_dev, count_dev, one_group);
     ST_CUDA(cudaGetLastError());
     if (xc_count_dev) ST_CUDA(cudaMemcpyAsync(xc_count_dev, xc_count, sizeof(int) * (size_t)b, cudaMemcpyDeviceToDevice, st));
     return TCB_OK;
