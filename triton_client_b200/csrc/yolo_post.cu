@@ -163,7 +163,7 @@ __device__ __forceinline__ void yf_bar_wait(unsigned long long* bar, unsigned ph
 
 constexpr int FS_WARPS = 8;
 __global__ void __launch_bounds__(32 * FS_WARPS) yolo_filter_stream_kernel(
-    const float* __restrict__ pred, int B, int N, int nc, double conf_thres, int use_filter, ClassMask cmask,
+    const float* __restrict__ pred, int B, int N, int nc, double conf_thres, float conf_floor32, int use_filter, ClassMask cmask,
     double* __restrict__ c_score, float4* __restrict__ c_box, int2* __restrict__ c_meta,
     int* __restrict__ c_count, int* __restrict__ xc_count, int* __restrict__ big) {
     extern __shared__ __align__(128) unsigned char ys_raw[];
@@ -176,19 +176,19 @@ __global__ void __launch_bounds__(32 * FS_WARPS) yolo_filter_stream_kernel(
     if (lane == 0) { yf_bar_init(bar); yf_bar_init(bar + 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
     __syncwarp();
     const int chunks = (N + FS_ROWS - 1) / FS_ROWS;
-    const long long total = (long long)B * chunks;
-    const long long nwarps = (long long)gridDim.x * FS_WARPS;
-    long long ch = (long long)blockIdx.x * FS_WARPS + warp;
+    const int total = B * chunks;                 // the host keeps b * ceil(n/128) below 2^31
+    const int nwarps = (int)gridDim.x * FS_WARPS;
+    int ch = (int)blockIdx.x * FS_WARPS + warp;
     unsigned phase0 = 0, phase1 = 0;
 
-    auto chunk_src = [&](long long c, int& b, int& row0, int& nrow) -> const float* {
-        b = (int)(c / chunks);
-        row0 = (int)(c - (long long)b * chunks) * FS_ROWS;
+    auto chunk_src = [&](int c, int& b, int& row0, int& nrow) -> const float* {
+        b = c / chunks;
+        row0 = (c - b * chunks) * FS_ROWS;
         nrow = min(FS_ROWS, N - row0);
         return pred + ((long long)b * N + row0) * stride;
     };
     auto bulk_ok = [&](const float* src, int nrow) { return ((((uintptr_t)src) | (uintptr_t)(nrow * stride * 4)) & 15) == 0; };
-    auto issue = [&](long long c, int slot) {
+    auto issue = [&](int c, int slot) {
         int b, row0, nrow;
         const float* src = chunk_src(c, b, row0, nrow);
         if (lane == 0 && bulk_ok(src, nrow)) yf_bulk_load(bufs + slot * buf_floats, src, (unsigned)(nrow * stride * 4), bar + slot);
@@ -218,7 +218,7 @@ __global__ void __launch_bounds__(32 * FS_WARPS) yolo_filter_stream_kernel(
             const int r = u * 32 + lane;
             const float* rp = rows + r * stride;
             const float obj = (r < nrow) ? rp[4] : -1.f;
-            const bool pass = (double)obj > conf_thres;
+            const bool pass = obj > conf_floor32;   // == ((double)obj > conf_thres): conf_floor32 is the largest float <= conf_thres
             best[u] = -1.0; bidx[u] = 0;
             bool ok = false;
             if (pass) {
@@ -460,7 +460,8 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
     int N, const double* __restrict__ c_score, const float4* __restrict__ c_box, const int2* __restrict__ c_meta,
     const int* __restrict__ c_count, SortEnt* __restrict__ gsort, int gsort_stride,
     double iou_thres, double class_offset, int max_det, int max_nms,
-    double* __restrict__ out, int* __restrict__ out_count, const GroupOut go) {
+    double* __restrict__ out, int* __restrict__ out_count, const GroupOut go,
+    const int* __restrict__ xc_count, int* __restrict__ xc_out) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     NmsShared& S = *reinterpret_cast<NmsShared*>(smem_raw);
     unsigned long long* skeys = reinterpret_cast<unsigned long long*>(smem_raw + sizeof(NmsShared));
@@ -712,7 +713,7 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
         }
     }
     if (G == 1) {
-        if (tid == 0) out_count[b] = nk_final;
+        if (tid == 0) { out_count[b] = nk_final; if (xc_out) xc_out[b] = xc_count[b]; }
     } else {
         if (tid == 0) go.count[list] = nk_final;
         __threadfence();
@@ -748,7 +749,7 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
                     for (int c = 0; c < 6; c++) dst[c] = __ldcg(src + c);
                 }
             }
-            if (tid == 0) out_count[b] = min(total, max_det);
+            if (tid == 0) { out_count[b] = min(total, max_det); if (xc_out) xc_out[b] = xc_count[b]; }
         }
     }
     PROF_T(6);
@@ -863,10 +864,13 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
             TCB_CUDA(ctx, cudaFuncSetAttribute(yolo_filter_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsm));
             const int per_sm = (int)((220 * 1024) / (fsm + 1024)) < 4 ? (int)((220 * 1024) / (fsm + 1024)) : 4;
             const long long chunks_total = (long long)b * ((n + FS_ROWS - 1) / FS_ROWS);
+            if (chunks_total >= (1ll << 30)) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_yolo_nms: b*n too large (%d x %d)", b, n);
             long long grid = tcb_div_up(chunks_total, FS_WARPS);
             if (grid > (long long)ctx->num_sms * per_sm) grid = (long long)ctx->num_sms * per_sm;
+            float conf_floor32 = (float)conf_thres;   // objectness test in float32, exactly equivalent to the float64 one
+            if ((double)conf_floor32 > conf_thres) conf_floor32 = nextafterf(conf_floor32, -INFINITY);
             yolo_filter_stream_kernel<<<(int)grid, 32 * FS_WARPS, fsm, st>>>(
-                pred_dev, b, n, nc, conf_thres, n_classes > 0, cm, c_score, c_box, c_meta, c_count, xc_count, big);
+                pred_dev, b, n, nc, conf_thres, conf_floor32, n_classes > 0, cm, c_score, c_box, c_meta, c_count, xc_count, big);
         } else {
             yolo_filter_kernel<<<dim3(bx, b), 256, 0, st>>>(pred_dev, b, n, nc, conf_thres, n_classes > 0, cm,
                                                             c_score, c_box, c_meta, c_count, xc_count, big);
@@ -876,10 +880,9 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
     const size_t smem = NMS_SMEM_BYTES;
     TCB_CUDA(ctx, cudaFuncSetAttribute(yolo_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     yolo_nms_kernel<<<dim3(b, G), NMS_THREADS, smem, st>>>(n > 0 ? n : 1, c_score, c_box, c_meta, c_count, gsort, npad,
-                                                           iou_thres, agnostic ? 0.0 : 4096.0, max_det, max_nms, out_dev, count_dev, go);
+                                                           iou_thres, agnostic ? 0.0 : 4096.0, max_det, max_nms, out_dev, count_dev, go,
+                                                           xc_count, xc_count_dev);
     TCB_LAUNCHED(ctx);
-    if (xc_count_dev)
-        TCB_CUDA(ctx, cudaMemcpyAsync(xc_count_dev, xc_count, sizeof(int) * (size_t)b, cudaMemcpyDeviceToDevice, st));
     return TCB_OK;
 }
 
@@ -1012,9 +1015,9 @@ extern "C" int tcb_yolo_nms_static(const float* pred_dev, int b, int n, int nc, 
     GroupOut one_group;   // one CTA per frame: the fixed scratch has no room for class-group staging
     memset(&one_group, 0, sizeof(one_group));
     yolo_nms_kernel<<<b, NMS_THREADS, smem, st>>>(n > 0 ? n : 1, c_score, c_box, c_meta, c_count, gsort, npad,
-                                                  iou_thres, agnostic ? 0.0 : 4096.0, max_det, max_nms, out_dev, count_dev, one_group);
+                                                  iou_thres, agnostic ? 0.0 : 4096.0, max_det, max_nms, out_dev, count_dev, one_group,
+                                                  xc_count, xc_count_dev);
     ST_CUDA(cudaGetLastError());
-    if (xc_count_dev) ST_CUDA(cudaMemcpyAsync(xc_count_dev, xc_count, sizeof(int) * (size_t)b, cudaMemcpyDeviceToDevice, st));
     return TCB_OK;
 #undef ST_REQUIRE
 #undef ST_CUDA
