@@ -316,6 +316,31 @@ int tcb_draw_detections(tcb_ctx* ctx, unsigned char* frames_dev, int b, int h, i
                         int num_classes, const unsigned char* colors, int per_class_color, int thickness, int labels,
                         void* stream);
 
+/* ---- ROS message decode/encode around the 3D path ----------------------------- */
+
+/* np.array(list(sensor_msgs.point_cloud2.read_points(msg, field_names, skip_nans))) of
+ * communicator/ros_inference3d.py:125, from the message bytes on the device. sensor_msgs is not part of the
+ * reference tree; restated from its published algorithm: points in storage order (row v at v*row_step, point u at
+ * +u*point_step), the selected fields unpacked in ascending byte offset (pass them in that order; PointField
+ * datatypes 1 INT8, 2 UINT8, 3 INT16, 4 UINT16, 7 FLOAT32 — the ones float32 rows hold exactly), a point dropped
+ * when skip_nans != 0 and any selected value is NaN. out_dev: [width*height, nfields] f32; rows [0, count) are the
+ * kept points, the rest is filled with NaN (columns 0-2) / -inf (other columns) so that tcb_voxelize, which ignores
+ * points with NaN coordinates and -inf in its column maximum, can take all width*height rows without a host sync.
+ * field tables are host arrays. */
+size_t tcb_pointcloud2_unpack_workspace(int width, int height);
+int tcb_pointcloud2_unpack(tcb_ctx* ctx, const unsigned char* data_dev, int width, int height, int point_step,
+                           long long row_step, int nfields, const int* field_offsets, const int* field_datatypes,
+                           int is_bigendian, int skip_nans, float* out_dev, int* count_dev, void* stream);
+
+/* The BoundingBoxArray fields RosInference3D publishes (communicator/ros_inference3d.py:150-177): the ascending
+ * indices i with labels[i] == label_sel and scores[i] > score_thresh (the reference: 2 and 0.5), and per index 12
+ * float64 values: position x, y, z - z_offset; orientation x, y, z, w of pyquaternion's Quaternion(axis=[0,0,1],
+ * radians=yaw) = (0*s, 0*s, s, c) with s, c = sin, cos(yaw/2) in float64; dimensions box[4], box[3], box[5] (x and y
+ * swapped as the reference does); score; label. boxes [n,7] f32, scores [n] f32, labels [n] int64. */
+int tcb_boxes_to_jsk(tcb_ctx* ctx, const float* boxes_dev, const float* scores_dev, const long long* labels_dev, int n,
+                     long long label_sel, float score_thresh, double z_offset, double* out_dev, int* out_idx_dev,
+                     int* out_count_dev, void* stream);
+
 /*
  * tcb_yolo_nms without a context and without any allocation. No counterpart in the reference: it is
  * here for callers that are not allowed to allocate GPU memory — a plugin inside a host process that

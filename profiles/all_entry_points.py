@@ -82,5 +82,15 @@ dd = np.array([[10, 40, 60, 80, 0.875, 1], [-5, 20, 30, 50, 0.5, 0]], np.float64
 got = eng.draw_detections(c(fr), c(dd[None]), None, ["crop", "weed"], (0, 255, 0), [100, 100], math_mode=1)
 assert np.array_equal(got.cpu().numpy(), overlay.draw_detections(fr.copy(), dd, ["crop", "weed"], (0, 255, 0), [100, 100]))
 assert np.array_equal(eng.scale_boxes(c(dd), (120, 200), (100, 100)).cpu().numpy(), overlay.scale_box_array(dd, (120, 200), (100, 100)))
+from oracle import pointcloud2 as opc2  # noqa: E402
+sw = synth.lidar_sweep(3, beams=8, azimuths=100)[:640]
+sw[::11, 1] = np.nan
+flds = [opc2.make_field(nm, 4 * k, 7) for k, nm in enumerate(("x", "y", "z", "intensity"))]
+cloud = opc2.make_cloud(dict(x=sw[:, 0], y=sw[:, 1], z=sw[:, 2], intensity=sw[:, 3]), flds, 20, height=4, row_pad=5)
+rows_, cnt_ = eng.pointcloud2_unpack(c(np.frombuffer(cloud.data, np.uint8)), cloud.width, 4, 20, cloud.row_step, [0, 4, 8, 12], [7] * 4)
+want_ = np.array(list(opc2.read_points(cloud, skip_nans=True)))
+assert int(cnt_) == len(want_) and np.array_equal(rows_[:int(cnt_)].cpu().numpy().astype(np.float64), want_)
+jr, ji, jc = eng.boxes_to_jsk(c(bx[:100]), c(sc[:100]), c(lab % 3 + 1))
+assert ji[:int(jc)].cpu().tolist() == opc2.jsk_rows(bx[:100], sc[:100], lab % 3 + 1)[0]
 torch.cuda.synchronize()
 print(f"all_entry_points: every entry point ran and matched the oracle ({eng.launches} kernel launches)")

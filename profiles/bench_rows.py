@@ -216,6 +216,30 @@ def main():
         row("f2 box rescale + overlay", f"C2 64x1280x720, {int(cnto.sum())} detections", lambda i: eng.draw_detections(ring[i % RING], deto, cnto, ["crop", "weed"], (0, 255, 0), [640, 640], math_mode=1),
             int(cnto.sum()) * 48 + painted * 3, 64, cv2_loop, "CPU column: the reference's cv2 loop on one frame; launch-bound (two kernels)")
 
+    # ---- ROS message rows (8f rank 3) ----------------------------------------------------------------------------------
+    if not args.only or args.only in "g1 PointCloud2 unpack" or args.only in "g2 BoundingBoxArray fields":
+        from oracle import pointcloud2 as opc2
+        sweep = synth.lidar_sweep(11)
+        sweep[::37, 0] = np.nan
+        fields = [opc2.make_field("x", 0, 7), opc2.make_field("y", 4, 7), opc2.make_field("z", 8, 7), opc2.make_field("intensity", 16, 7),
+                  opc2.make_field("ring", 20, 4)]
+        npts = len(sweep)
+        raw = np.zeros((npts, 32), np.uint8)
+        raw[:, 0:12] = sweep[:, :3].copy().view(np.uint8).reshape(npts, 12)
+        raw[:, 16:20] = sweep[:, 3:4].copy().view(np.uint8).reshape(npts, 4)
+        from types import SimpleNamespace
+        msg = SimpleNamespace(width=npts // 64, height=64, point_step=32, row_step=(npts // 64) * 32, data=raw.tobytes(), is_bigendian=False, fields=fields)
+        devs = [torch.from_numpy(raw.reshape(-1).copy()).cuda() for _ in range(RING)]
+        row("g1 PointCloud2 unpack", f"C4 {npts} points x 32 B, 4 fields, skip_nans", lambda i: eng.pointcloud2_unpack(devs[i % RING], msg.width, 64, 32, msg.row_step, [0, 4, 8, 16], [7, 7, 7, 7]),
+            npts * 32 + npts * 16, 1, lambda: np.array(list(opc2.read_points(msg, field_names=("x", "y", "z", "intensity"), skip_nans=True))),
+            "CPU column: read_points' per-point struct.unpack generator; launch-bound (4 kernels)")
+        bxj = synth.random_boxes7(500, 5, extent=40)
+        scj = np.random.default_rng(5).uniform(0, 1, 500).astype(np.float32)
+        lbj = np.random.default_rng(6).integers(1, 4, 500)
+        bj, sj, lj = torch.from_numpy(bxj).cuda(), torch.from_numpy(scj).cuda(), torch.from_numpy(lbj).cuda()
+        row("g2 BoundingBoxArray fields", "500 detections", lambda i: eng.boxes_to_jsk(bj, sj, lj), 500 * 40 + 100 * 96, 1,
+            lambda: opc2.jsk_rows(bxj, scj, lbj), "launch-bound (1 CTA)")
+
     print("\n| row | config | GPU p50 ms | GPU ms/frame | CPU oracle ms/frame | alg. bytes | GB/s | frac of measured HBM |")
     print("|---|---|---:|---:|---:|---:|---:|---:|")
     for r in rows:

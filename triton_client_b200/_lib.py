@@ -73,6 +73,11 @@ SIGNATURES = {
     "tcb_draw_detections_workspace": (c_size_t, [c_int, c_int]),
     "tcb_draw_detections": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_ll, c_ll, c_void_p, c_void_p, c_int,
                                     c_int, c_int, c_int, c_int, ctypes.c_char_p, c_int, ctypes.c_char_p, c_int, c_int, c_int, c_void_p]),
+    "tcb_pointcloud2_unpack_workspace": (c_size_t, [c_int, c_int]),
+    "tcb_pointcloud2_unpack": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_ll, c_int, P(c_int), P(c_int), c_int, c_int,
+                                       c_void_p, c_void_p, c_void_p]),
+    "tcb_boxes_to_jsk": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_ll, c_float, c_double, c_void_p, c_void_p,
+                                 c_void_p, c_void_p]),
     "tcb_yolo_nms_static_scratch_bytes": (c_size_t, []),
     "tcb_yolo_nms_static": (c_int, [c_void_p, c_int, c_int, c_int, c_double, c_double, P(c_int), c_int, c_int,
                                     c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),

@@ -400,6 +400,111 @@ __global__ void __launch_bounds__(256) dyn_coords_kernel(int cells, int gx, int 
 
 int next_pow2(long long v) { int r = 1024; while (r < v) r <<= 1; return r; }
 
+// ---------------------------------------------------------------------------------------------------------
+// PointCloud2 -> point rows: what
+//   np.array(list(point_cloud2.read_points(msg, field_names=(...), skip_nans=True)))   (communicator/ros_inference3d.py:125)
+// produces, without the per-point Python generator. sensor_msgs.point_cloud2 is a ROS library that is not part of
+// the reference tree; restated from its published algorithm: the selected fields are unpacked in order of their
+// byte offset (not of field_names), a point is dropped when any selected value is NaN, points keep their order.
+// Rows at and after the returned count are filled with NaN in the first three columns and -inf in the others:
+// tcb_voxelize drops points with a NaN coordinate and its column maximum ignores -inf, so the whole width*height
+// buffer can be handed on without reading the count back to the host.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int PC2_MAX_FIELDS = 8;
+struct Pc2Params {
+    const unsigned char* data;
+    int width, height, point_step, nfields, bigendian, skip_nans;
+    long long row_step;
+    int offset[PC2_MAX_FIELDS], datatype[PC2_MAX_FIELDS];   // sensor_msgs/PointField: 1 i8, 2 u8, 3 i16, 4 u16, 7 f32
+};
+
+__device__ __forceinline__ bool pc2_decode(const Pc2Params& p, int i, float* v) {
+    const int row = i / p.width, col = i - row * p.width;
+    const unsigned char* src = p.data + (long long)row * p.row_step + (long long)col * p.point_step;
+    bool ok = true;
+    for (int f = 0; f < p.nfields; f++) {
+        const unsigned char* q = src + p.offset[f];
+        float val;
+        switch (p.datatype[f]) {
+            case 1: val = (float)(signed char)q[0]; break;
+            case 2: val = (float)q[0]; break;
+            case 3: { const unsigned u = p.bigendian ? ((unsigned)q[0] << 8 | q[1]) : ((unsigned)q[1] << 8 | q[0]); val = (float)(short)u; break; }
+            case 4: { const unsigned u = p.bigendian ? ((unsigned)q[0] << 8 | q[1]) : ((unsigned)q[1] << 8 | q[0]); val = (float)u; break; }
+            default: {
+                const unsigned u = p.bigendian ? ((unsigned)q[0] << 24 | (unsigned)q[1] << 16 | (unsigned)q[2] << 8 | q[3])
+                                               : ((unsigned)q[3] << 24 | (unsigned)q[2] << 16 | (unsigned)q[1] << 8 | q[0]);
+                val = __uint_as_float(u);
+            }
+        }
+        if (p.skip_nans && val != val) ok = false;
+        v[f] = val;
+    }
+    return ok;
+}
+
+__global__ void __launch_bounds__(256) pc2_flags_kernel(const Pc2Params p, int n, int* __restrict__ flags) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float v[PC2_MAX_FIELDS];
+    flags[i] = pc2_decode(p, i, v) ? 1 : 0;
+}
+
+__global__ void __launch_bounds__(256) pc2_scatter_kernel(const Pc2Params p, int n, const int* __restrict__ flags, const int* __restrict__ pos,
+                                                          const int* __restrict__ blockoff, const int* __restrict__ count,
+                                                          float* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (flags[i]) {
+        float v[PC2_MAX_FIELDS];
+        pc2_decode(p, i, v);
+        float* d = out + (long long)(pos[i] + blockoff[i / VB]) * p.nfields;
+        for (int f = 0; f < p.nfields; f++) d[f] = v[f];
+    }
+    if (i >= *count) {   // tail: rows no kept point lands in
+        float* d = out + (long long)i * p.nfields;
+        for (int f = 0; f < p.nfields; f++) d[f] = f < 3 ? __int_as_float(0x7fc00000) : -INFINITY;
+    }
+}
+
+// BoundingBoxArray fields of the detections the reference publishes (communicator/ros_inference3d.py:150-177):
+// indices with labels == label_sel and scores > score_thresh, ascending; per box position (z - offset), the
+// quaternion of a yaw about z as pyquaternion builds it (w = cos(yaw/2), x = 0*s, y = 0*s, z = s = sin(yaw/2), in
+// float64 from the float32 yaw), dimensions with x and y swapped, score, label.
+__global__ void __launch_bounds__(1024) jsk_boxes_kernel(const float* __restrict__ boxes, const float* __restrict__ scores,
+                                                         const long long* __restrict__ labels, int n, long long label_sel, float score_thresh,
+                                                         double z_offset, double* __restrict__ out, int* __restrict__ out_idx,
+                                                         int* __restrict__ out_count) {
+    __shared__ int warp_tot[32];
+    __shared__ int carry;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < n; base += 1024) {
+        const int i = base + tid;
+        const bool sel = i < n && labels[i] == label_sel && scores[i] > score_thresh;
+        const unsigned bal = __ballot_sync(0xffffffffu, sel);
+        if (lane == 0) warp_tot[warp] = __popc(bal);
+        __syncthreads();
+        int before = carry;
+        for (int w = 0; w < warp; w++) before += warp_tot[w];
+        if (sel) {
+            const int k = before + __popc(bal & ((1u << lane) - 1));
+            const float* b = boxes + 7ll * i;
+            const double half = (double)b[6] / 2.0, sn = sin(half), cs = cos(half);
+            double* o = out + 12ll * k;
+            o[0] = (double)b[0]; o[1] = (double)b[1]; o[2] = (double)b[2] - z_offset;
+            o[3] = 0.0 * sn; o[4] = 0.0 * sn; o[5] = 1.0 * sn; o[6] = cs;          // orientation x, y, z, w
+            o[7] = (double)b[4]; o[8] = (double)b[3]; o[9] = (double)b[5];          // dimensions x, y, z
+            o[10] = (double)scores[i]; o[11] = (double)labels[i];
+            out_idx[k] = i;
+        }
+        __syncthreads();
+        if (tid == 0) { int t = 0; for (int w = 0; w < 32; w++) t += warp_tot[w]; carry += t; }
+        __syncthreads();
+    }
+    if (tid == 0) *out_count = carry;
+}
+
 }  // namespace
 
 extern "C" size_t tcb_voxelize_workspace(int n, int max_vox) {
@@ -565,6 +670,66 @@ extern "C" int tcb_dynamic_pillar(tcb_ctx* ctx, const float* pts_dev, int n, int
         TCB_LAUNCHED(ctx);
     }
     dyn_coords_kernel<<<tcb_div_up(cells, 256), 256, 0, st>>>((int)cells, p.gx, p.gy, mark, crank, cblk, voxel_coords_dev);
+    TCB_LAUNCHED(ctx);
+    return TCB_OK;
+}
+
+extern "C" size_t tcb_pointcloud2_unpack_workspace(int width, int height) {
+    const size_t n = (size_t)(width > 0 ? width : 0) * (size_t)(height > 0 ? height : 0);
+    return n * 8 + (n / VB + 2) * 4 + 4 * 256;
+}
+
+extern "C" int tcb_pointcloud2_unpack(tcb_ctx* ctx, const unsigned char* data_dev, int width, int height, int point_step,
+                                      long long row_step, int nfields, const int* field_offsets, const int* field_datatypes,
+                                      int is_bigendian, int skip_nans, float* out_dev, int* count_dev, void* stream) {
+    TCB_CHECK_CTX(ctx);
+    TCB_REQUIRE(ctx, width >= 0 && height >= 0 && point_step > 0, "tcb_pointcloud2_unpack: bad cloud shape");
+    TCB_REQUIRE(ctx, count_dev != nullptr, "tcb_pointcloud2_unpack: count_dev is null");
+    TCB_REQUIRE(ctx, nfields >= 1 && field_offsets && field_datatypes, "tcb_pointcloud2_unpack: no fields");
+    if (nfields > PC2_MAX_FIELDS) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_pointcloud2_unpack: %d fields > compiled limit %d", nfields, PC2_MAX_FIELDS);
+    const long long n = (long long)width * height;
+    TCB_REQUIRE(ctx, n < (1ll << 30), "tcb_pointcloud2_unpack: too many points");
+    TCB_REQUIRE(ctx, row_step >= (long long)width * point_step || height <= 1, "tcb_pointcloud2_unpack: row_step smaller than a row");
+    Pc2Params p;
+    memset(&p, 0, sizeof(p));
+    p.data = data_dev; p.width = width; p.height = height; p.point_step = point_step; p.row_step = row_step;
+    p.nfields = nfields; p.bigendian = is_bigendian ? 1 : 0; p.skip_nans = skip_nans ? 1 : 0;
+    for (int f = 0; f < nfields; f++) {
+        const int dt = field_datatypes[f];
+        const int size = (dt == 1 || dt == 2) ? 1 : ((dt == 3 || dt == 4) ? 2 : 4);
+        if (!(dt == 1 || dt == 2 || dt == 3 || dt == 4 || dt == 7))
+            return tcb_fail(ctx, TCB_ERR_ARG, "tcb_pointcloud2_unpack: field %d has datatype %d; only INT8/UINT8/INT16/UINT16/FLOAT32 are exact in "
+                                              "float32 rows (the reference carries INT32/UINT32/FLOAT64 as float64)", f, dt);
+        TCB_REQUIRE(ctx, field_offsets[f] >= 0 && field_offsets[f] + size <= point_step, "tcb_pointcloud2_unpack: field %d lies outside the point", f);
+        TCB_REQUIRE(ctx, f == 0 || field_offsets[f] > field_offsets[f - 1], "tcb_pointcloud2_unpack: fields must come in ascending byte offset (read_points' order)");
+        p.offset[f] = field_offsets[f]; p.datatype[f] = dt;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n == 0) { TCB_CUDA(ctx, cudaMemsetAsync(count_dev, 0, sizeof(int), st)); return TCB_OK; }
+    TCB_REQUIRE(ctx, data_dev && out_dev, "tcb_pointcloud2_unpack: null buffer");
+    const int nb = tcb_div_up(n, VB);
+    TCB_WS(ctx, flags, int, n);
+    TCB_WS(ctx, pos, int, n);
+    TCB_WS(ctx, blk, int, nb + 1);
+    pc2_flags_kernel<<<tcb_div_up(n, 256), 256, 0, st>>>(p, (int)n, flags);
+    TCB_LAUNCHED(ctx);
+    scan_local_kernel<<<nb, VB, 0, st>>>(flags, (int)n, pos, blk);
+    TCB_LAUNCHED(ctx);
+    scan_blocks_kernel<<<1, 1024, 0, st>>>(nb, blk, count_dev);
+    TCB_LAUNCHED(ctx);
+    pc2_scatter_kernel<<<tcb_div_up(n, 256), 256, 0, st>>>(p, (int)n, flags, pos, blk, count_dev, out_dev);
+    TCB_LAUNCHED(ctx);
+    return TCB_OK;
+}
+
+extern "C" int tcb_boxes_to_jsk(tcb_ctx* ctx, const float* boxes_dev, const float* scores_dev, const long long* labels_dev, int n,
+                                long long label_sel, float score_thresh, double z_offset, double* out_dev, int* out_idx_dev,
+                                int* out_count_dev, void* stream) {
+    TCB_CHECK_CTX(ctx);
+    TCB_REQUIRE(ctx, n >= 0 && out_count_dev, "tcb_boxes_to_jsk: bad arguments");
+    TCB_REQUIRE(ctx, n == 0 || (boxes_dev && scores_dev && labels_dev && out_dev && out_idx_dev), "tcb_boxes_to_jsk: null buffer");
+    jsk_boxes_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(boxes_dev, scores_dev, labels_dev, n, label_sel, score_thresh, z_offset, out_dev,
+                                                          out_idx_dev, out_count_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }

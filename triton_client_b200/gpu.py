@@ -356,6 +356,36 @@ class Engine:
                       _lib.stream_ptr())
         return frames
 
+    # ---- ROS message decode/encode around the 3D path ------------------------------
+    def pointcloud2_unpack(self, data, width, height, point_step, row_step, offsets, datatypes, is_bigendian=False, skip_nans=True):
+        """read_points(...) of ros_inference3d.py:125 on the device. data: CUDA uint8 tensor with the message bytes; offsets /
+        datatypes of the selected fields in ascending offset. Returns (points f32 [width*height, k] with sentinel rows
+        after the kept ones, count int32 [1])."""
+        _need_cuda(data)
+        d = data.contiguous().view(torch.uint8).reshape(-1)
+        n, k = int(width) * int(height), len(offsets)
+        need = (int(height) - 1) * int(row_step) + int(width) * int(point_step) if n else 0
+        if d.numel() < need:
+            raise ValueError(f"pointcloud2_unpack: message data holds {d.numel()} bytes, the layout needs {need}")
+        out = torch.empty((n, k), dtype=torch.float32, device=d.device)
+        cnt = torch.zeros((1,), dtype=torch.int32, device=d.device)
+        offs, dts = (c_int * max(1, k))(*[int(v) for v in offsets]), (c_int * max(1, k))(*[int(v) for v in datatypes])
+        self.ctx.call("tcb_pointcloud2_unpack", _ptr(d) if n else None, int(width), int(height), int(point_step), int(row_step), k, offs, dts,
+                      int(bool(is_bigendian)), int(bool(skip_nans)), _ptr(out) if n else None, _ptr(cnt), _lib.stream_ptr())
+        return out, cnt
+
+    def boxes_to_jsk(self, boxes, scores, labels, label_sel=2, score_thresh=0.5, z_offset=1.5):
+        """BoundingBoxArray fields (ros_inference3d.py:150-177). Returns (rows f64 [n,12], indices int32 [n], count int32 [1])."""
+        _need_cuda(boxes, scores, labels)
+        b, s, l = boxes.contiguous().float().reshape(-1, 7), scores.contiguous().float(), labels.contiguous().to(torch.int64)
+        n = b.shape[0]
+        out = torch.zeros((max(1, n), 12), dtype=torch.float64, device=b.device)
+        idx = torch.zeros((max(1, n),), dtype=torch.int32, device=b.device)
+        cnt = torch.zeros((1,), dtype=torch.int32, device=b.device)
+        self.ctx.call("tcb_boxes_to_jsk", _ptr(b) if n else None, _ptr(s) if n else None, _ptr(l) if n else None, n, int(label_sel),
+                      float(score_thresh), float(z_offset), _ptr(out), _ptr(idx), _ptr(cnt), _lib.stream_ptr())
+        return out, idx, cnt
+
 
 def yolo_nms_static(pred, conf_thres=0.6, iou_thres=0.45, classes=None, agnostic=False, max_det=300,
                     max_nms=30000, out=None, counts=None):
