@@ -2,6 +2,8 @@ import ctypes, torch, numpy as np, sys
 sys.path.insert(0,'.')
 from triton_client_b200 import synth, _lib
 from triton_client_b200.gpu import Engine
+import os
+_lib.LIB_PATH=os.path.join('profiles','probes','libtcb200_prof.so')   # yolo_post.cu built with -DTCB_NMS_PROFILE
 eng=Engine(0)
 pred=torch.from_numpy(synth.yolo_output(64,25200,2,2002)).cuda()
 l=_lib.lib()

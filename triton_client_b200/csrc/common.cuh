@@ -16,8 +16,11 @@ struct tcb_ctx {
     size_t ws_bytes;
     size_t ws_used;    // bump pointer, reset at the start of every entry point
     long long launches;
+    int* tickets;      // TCB_TICKETS ints behind the workspace, zero between calls: "last CTA of a group" counters that
+                       // the kernel using them resets itself, so no per-call memset is needed
     char err[TCB_ERRLEN];
 };
+#define TCB_TICKETS 65536
 
 int tcb_fail(tcb_ctx* ctx, int code, const char* fmt, ...);
 void tcb_clear_error(tcb_ctx* ctx);

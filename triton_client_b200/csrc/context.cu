@@ -35,13 +35,16 @@ int tcb_create(int device, size_t workspace_bytes, tcb_ctx** out) {
     c->device = device;
     cudaDeviceGetAttribute(&c->num_sms, cudaDevAttrMultiProcessorCount, device);
     if (c->num_sms <= 0) c->num_sms = 148;
-    if (workspace_bytes) {
-        e = cudaMalloc((void**)&c->ws, workspace_bytes);
-        if (e != cudaSuccess) {
-            delete c;
-            return tcb_fail(nullptr, TCB_ERR_ALLOC, "tcb_create: cudaMalloc(%zu) -> %s", workspace_bytes, cudaGetErrorString(e));
-        }
+    // one allocation: the caller's workspace, then the self-resetting ticket counters
+    const size_t ws_round = (workspace_bytes + 255) & ~(size_t)255;
+    e = cudaMalloc((void**)&c->ws, ws_round + sizeof(int) * TCB_TICKETS);
+    if (e == cudaSuccess) e = cudaMemset(c->ws + ws_round, 0, sizeof(int) * TCB_TICKETS);
+    if (e != cudaSuccess) {
+        if (c->ws) cudaFree(c->ws);
+        delete c;
+        return tcb_fail(nullptr, TCB_ERR_ALLOC, "tcb_create: cudaMalloc(%zu) -> %s", workspace_bytes, cudaGetErrorString(e));
     }
+    c->tickets = reinterpret_cast<int*>(c->ws + ws_round);
     c->ws_bytes = workspace_bytes;
     *out = c;
     return TCB_OK;

@@ -164,8 +164,7 @@ __device__ __forceinline__ void yf_bar_wait(unsigned long long* bar, unsigned ph
 constexpr int FS_WARPS = 8;
 __global__ void __launch_bounds__(32 * FS_WARPS) yolo_filter_stream_kernel(
     const float* __restrict__ pred, int B, int N, int nc, double conf_thres, float conf_floor32, int use_filter, ClassMask cmask,
-    double* __restrict__ c_score, float4* __restrict__ c_box, int2* __restrict__ c_meta,
-    int* __restrict__ c_count, int* __restrict__ xc_count, int* __restrict__ big) {
+    double* __restrict__ c_score, float4* __restrict__ c_box, int2* __restrict__ c_meta, int2* __restrict__ chunk_info) {
     extern __shared__ __align__(128) unsigned char ys_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int stride = 5 + nc;
@@ -208,7 +207,7 @@ __global__ void __launch_bounds__(32 * FS_WARPS) yolo_filter_stream_kernel(
             for (int i = lane; i < nrow * stride; i += 32) rows[i] = __ldg(src + i);
             __syncwarp();
         }
-        // filter the chunk: 4 groups of 32 rows, results held until the slots are reserved
+        // filter the chunk: 4 groups of 32 rows, results held in registers until the chunk's count is known
         double best[FS_ROWS / 32];
         int bidx[FS_ROWS / 32];
         unsigned okm[FS_ROWS / 32];
@@ -236,31 +235,29 @@ __global__ void __launch_bounds__(32 * FS_WARPS) yolo_filter_stream_kernel(
             okm[u] = __ballot_sync(0xffffffffu, ok);
             n_ok += __popc(okm[u]);
         }
-        if (n_pass) {
+        // The chunk's candidates go to slots row0, row0+1, ... of the frame (its own region: no slot reservation, no
+        // atomics); the counts and the "a box reaches beyond +-2048" flag go to chunk_info for the NMS kernel.
+        bool bigc = false;
+        if (n_ok) {
             int basei = 0;
-            if (lane == 0) {
-                atomicAdd(&xc_count[b], n_pass);
-                if (n_ok) basei = atomicAdd(&c_count[b], n_ok);
-            }
-            if (n_ok) {
-                basei = __shfl_sync(0xffffffffu, basei, 0);
 #pragma unroll
-                for (int u = 0; u < FS_ROWS / 32; u++) {
-                    if ((okm[u] >> lane) & 1u) {
-                        const int r = u * 32 + lane;
-                        const float* rp = rows + r * stride;
-                        const double x = (double)rp[0], y = (double)rp[1], w = (double)rp[2], h = (double)rp[3];
-                        float4 bx;
-                        bx.x = (float)(x - w / 2); bx.y = (float)(y - h / 2);
-                        bx.z = (float)(x + w / 2); bx.w = (float)(y + h / 2);
-                        const long long k = (long long)b * N + basei + __popc(okm[u] & ((1u << lane) - 1));
-                        c_score[k] = best[u]; c_box[k] = bx; c_meta[k] = make_int2(row0 + r, bidx[u]);
-                        note_big(bx, big, b);
-                    }
-                    basei += __popc(okm[u]);
+            for (int u = 0; u < FS_ROWS / 32; u++) {
+                if ((okm[u] >> lane) & 1u) {
+                    const int r = u * 32 + lane;
+                    const float* rp = rows + r * stride;
+                    const double x = (double)rp[0], y = (double)rp[1], w = (double)rp[2], h = (double)rp[3];
+                    float4 bx;
+                    bx.x = (float)(x - w / 2); bx.y = (float)(y - h / 2);
+                    bx.z = (float)(x + w / 2); bx.w = (float)(y + h / 2);
+                    const long long k = (long long)b * N + row0 + basei + __popc(okm[u] & ((1u << lane) - 1));
+                    c_score[k] = best[u]; c_box[k] = bx; c_meta[k] = make_int2(row0 + r, bidx[u]);
+                    bigc |= !(fabsf(bx.x) < 2048.f && fabsf(bx.y) < 2048.f && fabsf(bx.z) < 2048.f && fabsf(bx.w) < 2048.f);
                 }
+                basei += __popc(okm[u]);
             }
+            bigc = __any_sync(0xffffffffu, bigc);
         }
+        if (lane == 0) chunk_info[ch] = make_int2(n_ok | (bigc ? (int)0x80000000 : 0), n_pass);
         __syncwarp();   // every lane is done with this buffer before lane 0 lets the next copy land in it
     }
 }
@@ -461,7 +458,7 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
     const int* __restrict__ c_count, SortEnt* __restrict__ gsort, int gsort_stride,
     double iou_thres, double class_offset, int max_det, int max_nms,
     double* __restrict__ out, int* __restrict__ out_count, const GroupOut go,
-    const int* __restrict__ xc_count, int* __restrict__ xc_out) {
+    const int* __restrict__ xc_count, int* __restrict__ xc_out, const int2* __restrict__ chunk_info, int chunks) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     NmsShared& S = *reinterpret_cast<NmsShared*>(smem_raw);
     unsigned long long* skeys = reinterpret_cast<unsigned long long*>(smem_raw + sizeof(NmsShared));
@@ -473,60 +470,86 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
     long long prof_t0 = clock64();
 #endif
     const int G = gridDim.y, g = blockIdx.y;
-    const int n_all = min(c_count[b], N);
-    const bool split = G > 1 && go.big[b] == 0 && n_all <= max_nms;
     const long long cbase = (long long)b * N;
-    if (tid == 0) S.nkept = 0;
-    for (int i = tid; i < MAX_NMS_CAP / 32; i += NMS_THREADS) S.resolved[i] = 0u;
-    int n = n_all;
-    if (G > 1) {
-        if (split) {   // candidates of this CTA's classes
-            int mine = 0;
-            for (int i = tid; i < n_all; i += NMS_THREADS) mine += (c_meta[cbase + i].y % G) == g;
+    if (tid == 0) { S.nkept = 0; S.a_total = 0; }
+
+    // ---- this frame's candidates. Two layouts: a dense list of c_count[b] entries (general filter), or one region
+    //      per 128-row chunk, chunk_info[b][c] = (count | big << 31, rows passing the objectness test), candidates of
+    //      chunk c at slots 128c, 128c+1, ... (streaming filter: nothing to zero, nothing reserved atomically) ----
+    int n_all, xc_total = 0;
+    bool big;
+    const int2* cinfo = chunk_info ? chunk_info + (long long)b * chunks : nullptr;
+    int* cprefix = reinterpret_cast<int*>(S.resolved);   // chunks + 1 exclusive prefix sums of the chunk counts (chunks < 2048);
+                                                         // the bitmap proper is cleared after the gather
+    if (cinfo) {
+        // thread t owns chunks 2t, 2t+1: one coalesced read of the table, then a CTA-wide scan
+        const int c0 = 2 * tid, c1 = 2 * tid + 1;
+        const int2 v0 = c0 < chunks ? cinfo[c0] : make_int2(0, 0), v1 = c1 < chunks ? cinfo[c1] : make_int2(0, 0);
+        const int a0 = v0.x & 0x7fffffff, a1 = v1.x & 0x7fffffff;
+        int inc = a0 + a1, x = v0.y + v1.y, bg = (int)(((unsigned)v0.x | (unsigned)v1.x) >> 31);
 #pragma unroll
-            for (int sft = 16; sft > 0; sft >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, sft);
-            if (lane == 0) S.warp_cnt[warp] = mine;
-            __syncthreads();
-            n = 0;
-            for (int w = 0; w < NMS_THREADS / 32; w++) n += S.warp_cnt[w];
-            __syncthreads();
-            if (tid == 0) S.a_total = 0;   // compaction cursor
-        } else if (g > 0) {
-            n = 0;
-        }
+        for (int sft = 1; sft < 32; sft <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, sft); if (lane >= sft) inc += t; }
+#pragma unroll
+        for (int sft = 16; sft > 0; sft >>= 1) { x += __shfl_xor_sync(0xffffffffu, x, sft); bg |= __shfl_xor_sync(0xffffffffu, bg, sft); }
+        if (lane == 31) S.warp_cnt[warp] = inc;
+        if (lane == 0) { S.aidx[warp] = x; S.knew[warp] = bg; }
+        __syncthreads();
+        int before = 0, tot = 0, xs = 0, bgs = 0;
+        for (int w = 0; w < NMS_THREADS / 32; w++) { const int t = S.warp_cnt[w]; if (w < warp) before += t; tot += t; xs += S.aidx[w]; bgs |= S.knew[w]; }
+        const int excl = before + inc - (a0 + a1);
+        if (c0 <= chunks) cprefix[c0] = excl;            // entry `chunks` (the total) is written by whoever owns it
+        if (c1 <= chunks) cprefix[c1] = excl + a0;
+        n_all = tot; xc_total = xs; big = bgs != 0;
+    } else {
+        n_all = min(c_count[b], N);
+        xc_total = xc_count ? xc_count[b] : 0;
+        big = G > 1 && go.big[b] != 0;
     }
+    const bool split = G > 1 && !big && n_all <= max_nms;
+    const int n_bound = (G > 1 && !split && g > 0) ? 0 : n_all;   // an unsplit frame is done whole by its g == 0 CTA
 
     // ---- order candidates: score descending, row ascending ------------------------------------
     int npad = 1;
-    while (npad < n) npad <<= 1;
+    while (npad < n_bound) npad <<= 1;
     const bool sort_in_smem = npad <= SORT_SMEM_CAP;
-    // global sort scratch of image b: npad keys followed by npad metas
+    // global sort scratch of this CTA: gsort_stride keys followed by gsort_stride metas
     unsigned long long* gkeys = reinterpret_cast<unsigned long long*>(gsort + ((long long)b * G + g) * gsort_stride);
     uint2* gmeta = reinterpret_cast<uint2*>(gkeys + gsort_stride);
     unsigned long long* keys = sort_in_smem ? skeys : gkeys;
     uint2* meta = sort_in_smem ? smeta : gmeta;
-    const int nfill = sort_in_smem ? (npad <= 1024 ? 1024 : (npad <= 2048 ? 2048 : 4096)) : npad;
-    if (split) {   // gather this group's candidates (any order: the sort below fixes it), then pad
-        __syncthreads();
-        for (int i = tid; i < n_all; i += NMS_THREADS) {
-            const int2 m = c_meta[cbase + i];
-            if ((m.y % G) == g) {
-                const int q = atomicAdd(&S.a_total, 1);
-                keys[q] = (unsigned long long)__double_as_longlong(c_score[cbase + i]);
-                meta[q] = make_uint2((unsigned)m.x, (unsigned)i);
+    __syncthreads();
+    // gather (any order: the sort fixes it), keeping this CTA's classes when the frame is split
+    if (n_bound > 0) {
+        if (cinfo) {
+            for (int i = tid; i < n_all; i += NMS_THREADS) {   // candidate i of the frame -> its chunk by bisection of the prefix sums
+                int lo = 0, hi = chunks;                       // invariant: cprefix[lo] <= i < cprefix[hi]
+                while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (cprefix[mid] <= i) lo = mid; else hi = mid; }
+                const int slot = lo * FS_ROWS + (i - cprefix[lo]);
+                const int2 m = c_meta[cbase + slot];
+                if (!split || (m.y % G) == g) {
+                    const int q = atomicAdd(&S.a_total, 1);
+                    keys[q] = (unsigned long long)__double_as_longlong(c_score[cbase + slot]);
+                    meta[q] = make_uint2((unsigned)m.x, (unsigned)slot);
+                }
             }
-        }
-        for (int i = n + tid; i < nfill; i += NMS_THREADS) { keys[i] = 0ull; meta[i] = make_uint2(0xffffffffu, 0u); }
-    } else {
-        for (int i = tid; i < nfill; i += NMS_THREADS) {
-            if (i < n) {
-                keys[i] = (unsigned long long)__double_as_longlong(c_score[cbase + i]);
-                meta[i] = make_uint2((unsigned)c_meta[cbase + i].x, (unsigned)i);
-            } else {
-                keys[i] = 0ull; meta[i] = make_uint2(0xffffffffu, 0u);
+        } else {
+            for (int i = tid; i < n_all; i += NMS_THREADS) {
+                const int2 m = c_meta[cbase + i];
+                if (!split || (m.y % G) == g) {
+                    const int q = atomicAdd(&S.a_total, 1);
+                    keys[q] = (unsigned long long)__double_as_longlong(c_score[cbase + i]);
+                    meta[q] = make_uint2((unsigned)m.x, (unsigned)i);
+                }
             }
         }
     }
+    __syncthreads();
+    for (int i = tid; i < MAX_NMS_CAP / 32; i += NMS_THREADS) S.resolved[i] = 0u;   // (the prefix sums lived here)
+    int n = S.a_total;
+    npad = 1;
+    while (npad < n) npad <<= 1;
+    const int nfill = sort_in_smem ? (npad <= 1024 ? 1024 : (npad <= 2048 ? 2048 : 4096)) : npad;
+    for (int i = n + tid; i < nfill; i += NMS_THREADS) { keys[i] = 0ull; meta[i] = make_uint2(0xffffffffu, 0u); }
     __syncthreads();
     PROF_T(0);
     if (n < 2) {
@@ -713,7 +736,7 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
         }
     }
     if (G == 1) {
-        if (tid == 0) { out_count[b] = nk_final; if (xc_out) xc_out[b] = xc_count[b]; }
+        if (tid == 0) { out_count[b] = nk_final; if (xc_out) xc_out[b] = xc_total; }
     } else {
         if (tid == 0) go.count[list] = nk_final;
         __threadfence();
@@ -749,7 +772,7 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
                     for (int c = 0; c < 6; c++) dst[c] = __ldcg(src + c);
                 }
             }
-            if (tid == 0) { out_count[b] = min(total, max_det); if (xc_out) xc_out[b] = xc_count[b]; }
+            if (tid == 0) { out_count[b] = min(total, max_det); if (xc_out) xc_out[b] = xc_total; go.done[b] = 0; }   // the ticket resets itself
         }
     }
     PROF_T(6);
@@ -776,6 +799,7 @@ size_t yolo_ws_bytes(int b, int n) {
     bytes += per * sizeof(float4) + 256;
     bytes += per * sizeof(int2) + 256;
     bytes += (size_t)b * 4 * sizeof(int) + 256;
+    bytes += (size_t)b * ((n + FS_ROWS - 1) / FS_ROWS) * sizeof(int2) + 256;
     int npad = 1;
     while (npad < n) npad <<= 1;
     // class groups: b * G lists with G <= SMs / b, so never more than max(b, SM count) lists (256 bounds today's parts)
@@ -822,7 +846,16 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
         if (G > MAX_GROUPS) G = MAX_GROUPS;
         if (G < 1) G = 1;
     }
+    TCB_REQUIRE(ctx, b <= 65535 && b <= TCB_TICKETS, "tcb_yolo_nms: batch %d > 65535", b);
+    const int chunks = (n + FS_ROWS - 1) / FS_ROWS;
+    // small rows: streaming filter with per-chunk candidate regions (the NMS kernel holds chunks + 1 prefix sums in a 2048-int table)
+    const bool stream_filter = nc <= FILTER_SMALL_NC && n > 0 && chunks < MAX_NMS_CAP / 32;
     TCB_WS(ctx, counts, int, (size_t)b * 4);
+    int2* chunk_info = nullptr;
+    if (stream_filter) {
+        TCB_WS(ctx, ci, int2, (size_t)b * chunks);
+        chunk_info = ci;
+    }
     TCB_WS(ctx, c_score, double, per);
     TCB_WS(ctx, c_box, float4, per);
     TCB_WS(ctx, c_meta, int2, per);
@@ -843,9 +876,11 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
         TCB_WS(ctx, g_key, unsigned long long, (size_t)b * G * max_det);
         TCB_WS(ctx, g_krow, unsigned, (size_t)b * G * max_det);
         TCB_WS(ctx, g_count, int, (size_t)b * G);
-        go.rows = g_rows; go.key = g_key; go.krow = g_krow; go.count = g_count; go.done = counts + 3 * (size_t)b; go.big = big;
+        go.rows = g_rows; go.key = g_key; go.krow = g_krow; go.count = g_count; go.done = ctx->tickets; go.big = big;
     }
-    TCB_CUDA(ctx, cudaMemsetAsync(counts, 0, sizeof(int) * 4 * (size_t)b, st));
+    // dense-list layout only: its three per-frame counters start at zero (the chunk layout has nothing to clear, and
+    // the class-group tickets reset themselves)
+    if (!stream_filter) TCB_CUDA(ctx, cudaMemsetAsync(counts, 0, sizeof(int) * 3 * (size_t)b, st));
 
     if (n > 0) {
         // 8 warps per CTA, FILTER_UNROLL 32-row groups per warp and pass; y = image
@@ -853,12 +888,7 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
         const int cap = tcb_div_up(ctx->num_sms * 16, b);
         if (bx > cap) bx = cap;
         if (bx < 1) bx = 1;
-        TCB_REQUIRE(ctx, b <= 65535, "tcb_yolo_nms: batch %d > 65535", b);
-        if (nc <= FILTER_SMALL_NC) {
-            int gx = tcb_div_up((n + FS_ROWS - 1) / FS_ROWS, 8);
-            if (gx > cap) gx = cap;
-            if (gx < 1) gx = 1;
-            (void)gx;
+        if (stream_filter) {
             // two row buffers per warp; as many CTAs as fit, each warp streaming its share of the b * ceil(n/128) chunks
             const size_t fsm = 128 + (size_t)FS_WARPS * 2 * FS_ROWS * (5 + nc) * sizeof(float);
             TCB_CUDA(ctx, cudaFuncSetAttribute(yolo_filter_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsm));
@@ -870,7 +900,7 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
             float conf_floor32 = (float)conf_thres;   // objectness test in float32, exactly equivalent to the float64 one
             if ((double)conf_floor32 > conf_thres) conf_floor32 = nextafterf(conf_floor32, -INFINITY);
             yolo_filter_stream_kernel<<<(int)grid, 32 * FS_WARPS, fsm, st>>>(
-                pred_dev, b, n, nc, conf_thres, conf_floor32, n_classes > 0, cm, c_score, c_box, c_meta, c_count, xc_count, big);
+                pred_dev, b, n, nc, conf_thres, conf_floor32, n_classes > 0, cm, c_score, c_box, c_meta, chunk_info);
         } else {
             yolo_filter_kernel<<<dim3(bx, b), 256, 0, st>>>(pred_dev, b, n, nc, conf_thres, n_classes > 0, cm,
                                                             c_score, c_box, c_meta, c_count, xc_count, big);
@@ -881,7 +911,7 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
     TCB_CUDA(ctx, cudaFuncSetAttribute(yolo_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     yolo_nms_kernel<<<dim3(b, G), NMS_THREADS, smem, st>>>(n > 0 ? n : 1, c_score, c_box, c_meta, c_count, gsort, npad,
                                                            iou_thres, agnostic ? 0.0 : 4096.0, max_det, max_nms, out_dev, count_dev, go,
-                                                           xc_count, xc_count_dev);
+                                                           xc_count, xc_count_dev, chunk_info, chunks);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }
@@ -1016,7 +1046,7 @@ extern "C" int tcb_yolo_nms_static(const float* pred_dev, int b, int n, int nc, 
     memset(&one_group, 0, sizeof(one_group));
     yolo_nms_kernel<<<b, NMS_THREADS, smem, st>>>(n > 0 ? n : 1, c_score, c_box, c_meta, c_count, gsort, npad,
                                                   iou_thres, agnostic ? 0.0 : 4096.0, max_det, max_nms, out_dev, count_dev, one_group,
-                                                  xc_count, xc_count_dev);
+                                                  xc_count, xc_count_dev, nullptr, 0);
     ST_CUDA(cudaGetLastError());
     return TCB_OK;
 #undef ST_REQUIRE
