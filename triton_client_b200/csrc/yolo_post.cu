@@ -139,11 +139,13 @@ __global__ void __launch_bounds__(256) yolo_filter_kernel(
 // Small class counts (rows of <= 13 floats): every 32-byte sector of the tensor is touched anyway, so the rows are
 // pulled into shared memory whole (one DRAM round trip instead of the objectness -> class scores -> box chain of
 // dependent sector fetches) and filtered / decoded from there.
-constexpr int FS_ROWS = 128;   // rows per warp and pass
-// As a stream: every warp owns two row buffers and keeps a bulk copy (TMA, completion on an
-// mbarrier) of its next 128-row chunk in flight while it filters the current one, and reserves output slots once
-// per chunk (one returning atomic instead of one per 32 rows). Chunks that are not 16-byte aligned/sized (the last
-// one of a frame, odd strides, unaligned tensors) are copied by the lanes instead.
+constexpr int FS_ROWS = 128;   // rows per chunk (one warp, one pass)
+constexpr int FS_NBUF = 2;     // chunk buffers per warp: one bulk copy in flight behind the chunk being filtered (3 and 4 measured no faster)
+// As a stream: every warp owns FS_NBUF buffers of FS_ROWS rows and keeps bulk copies (TMA, completion on one
+// mbarrier per buffer) of its next chunks in flight while it filters the current one. The candidates of a chunk go
+// to the chunk's own slots (FS_ROWS*c + 0, 1, ...) and its counts to chunk_info, so nothing is reserved atomically
+// and nothing has to be zeroed. Chunks that are not 16-byte aligned/sized (the last one of a frame, odd strides,
+// unaligned tensors) are copied by the lanes instead.
 __device__ __forceinline__ unsigned yf_smem(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void yf_bar_init(unsigned long long* bar) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(yf_smem(bar)) : "memory");
@@ -168,17 +170,20 @@ __global__ void __launch_bounds__(32 * FS_WARPS) yolo_filter_stream_kernel(
     extern __shared__ __align__(128) unsigned char ys_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int stride = 5 + nc;
-    const int buf_floats = FS_ROWS * stride;                        // FS_ROWS = 128: a multiple of 4 floats, 16-byte sized
-    unsigned long long* bars = reinterpret_cast<unsigned long long*>(ys_raw);            // [FS_WARPS][2]
-    float* bufs = reinterpret_cast<float*>(ys_raw + 128) + (size_t)warp * 2 * buf_floats;
-    unsigned long long* bar = bars + 2 * warp;
-    if (lane == 0) { yf_bar_init(bar); yf_bar_init(bar + 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+    const int buf_floats = FS_ROWS * stride;                        // FS_ROWS rows: a multiple of 4 floats, 16-byte sized
+    unsigned long long* bars = reinterpret_cast<unsigned long long*>(ys_raw);            // [FS_WARPS][FS_NBUF]
+    float* bufs = reinterpret_cast<float*>(ys_raw + 8 * FS_WARPS * FS_NBUF) + (size_t)warp * FS_NBUF * buf_floats;
+    unsigned long long* bar = bars + FS_NBUF * warp;
+    if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < FS_NBUF; k++) yf_bar_init(bar + k);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     __syncwarp();
     const int chunks = (N + FS_ROWS - 1) / FS_ROWS;
-    const int total = B * chunks;                 // the host keeps b * ceil(n/128) below 2^31
+    const int total = B * chunks;                 // the host keeps b * chunks below 2^30
     const int nwarps = (int)gridDim.x * FS_WARPS;
     int ch = (int)blockIdx.x * FS_WARPS + warp;
-    unsigned phase0 = 0, phase1 = 0;
 
     auto chunk_src = [&](int c, int& b, int& row0, int& nrow) -> const float* {
         b = c / chunks;
@@ -193,21 +198,23 @@ __global__ void __launch_bounds__(32 * FS_WARPS) yolo_filter_stream_kernel(
         if (lane == 0 && bulk_ok(src, nrow)) yf_bulk_load(bufs + slot * buf_floats, src, (unsigned)(nrow * stride * 4), bar + slot);
     };
 
-    if (ch < total) issue(ch, 0);
+#pragma unroll
+    for (int k = 0; k < FS_NBUF - 1; k++)
+        if (ch + k * nwarps < total) issue(ch + k * nwarps, k);
     for (int it = 0; ch < total; ch += nwarps, it++) {
-        const int slot = it & 1;
-        if (ch + nwarps < total) issue(ch + nwarps, slot ^ 1);     // the other buffer was released by the __syncwarp below
+        const int slot = it % FS_NBUF;
+        // refill the buffer filtered in the previous iteration (released by the __syncwarp at the end of it)
+        if (ch + (FS_NBUF - 1) * nwarps < total) issue(ch + (FS_NBUF - 1) * nwarps, (it + FS_NBUF - 1) % FS_NBUF);
         int b, row0, nrow;
         const float* src = chunk_src(ch, b, row0, nrow);
         float* rows = bufs + slot * buf_floats;
         if (bulk_ok(src, nrow)) {
-            yf_bar_wait(bar + slot, slot ? phase1 : phase0);
-            if (slot) phase1 ^= 1u; else phase0 ^= 1u;
+            yf_bar_wait(bar + slot, (unsigned)(it / FS_NBUF) & 1u);   // buffer `slot` completes once every FS_NBUF iterations
         } else {
             for (int i = lane; i < nrow * stride; i += 32) rows[i] = __ldg(src + i);
             __syncwarp();
         }
-        // filter the chunk: 4 groups of 32 rows, results held in registers until the chunk's count is known
+        // filter the chunk in groups of 32 rows, results held in registers until the chunk's count is known
         double best[FS_ROWS / 32];
         int bidx[FS_ROWS / 32];
         unsigned okm[FS_ROWS / 32];
@@ -474,8 +481,8 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
     if (tid == 0) { S.nkept = 0; S.a_total = 0; }
 
     // ---- this frame's candidates. Two layouts: a dense list of c_count[b] entries (general filter), or one region
-    //      per 128-row chunk, chunk_info[b][c] = (count | big << 31, rows passing the objectness test), candidates of
-    //      chunk c at slots 128c, 128c+1, ... (streaming filter: nothing to zero, nothing reserved atomically) ----
+    //      per FS_ROWS-row chunk, chunk_info[b][c] = (count | big << 31, rows passing the objectness test), candidates
+    //      of chunk c at slots FS_ROWS*c + 0, 1, ... (streaming filter: nothing to zero, nothing reserved atomically) ----
     int n_all, xc_total = 0;
     bool big;
     const int2* cinfo = chunk_info ? chunk_info + (long long)b * chunks : nullptr;
@@ -889,8 +896,8 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
         if (bx > cap) bx = cap;
         if (bx < 1) bx = 1;
         if (stream_filter) {
-            // two row buffers per warp; as many CTAs as fit, each warp streaming its share of the b * ceil(n/128) chunks
-            const size_t fsm = 128 + (size_t)FS_WARPS * 2 * FS_ROWS * (5 + nc) * sizeof(float);
+            // FS_NBUF row buffers per warp; as many CTAs as fit, each warp streaming its share of the b * chunks chunks
+            const size_t fsm = 8 * FS_WARPS * FS_NBUF + (size_t)FS_WARPS * FS_NBUF * FS_ROWS * (5 + nc) * sizeof(float);
             TCB_CUDA(ctx, cudaFuncSetAttribute(yolo_filter_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsm));
             const int per_sm = (int)((220 * 1024) / (fsm + 1024)) < 4 ? (int)((220 * 1024) / (fsm + 1024)) : 4;
             const long long chunks_total = (long long)b * ((n + FS_ROWS - 1) / FS_ROWS);
