@@ -108,9 +108,20 @@ __device__ __forceinline__ void sort_desc_n(unsigned long long* skeys, int m) { 
 
 // The K (<= KCAP) largest of the n keys key_of(i), sorted descending into skeys[0..m), m = min(n, K).
 // skeys must hold KCAP entries. Every thread of the 1024-thread CTA must call this.
+// cache (optional, shared memory, cache_cap entries): the first cache_cap keys are fetched once, with all loads in
+// flight together, and the seven passes of the selection read them from there instead of paying the global-memory
+// latency of key_of on every pass.
 template <typename KeyFn>
-__device__ int cta_topk_sorted(KeyFn key_of, int n, int K, unsigned long long* skeys, Scratch& S) {
+__device__ int cta_topk_sorted(KeyFn key_of_src, int n, int K, unsigned long long* skeys, Scratch& S,
+                               unsigned long long* cache = nullptr, int cache_cap = 0) {
     const int tid = threadIdx.x;
+    const int cached = (cache != nullptr && n > K) ? (n < cache_cap ? n : cache_cap) : 0;
+    if (cached) {
+#pragma unroll 8
+        for (int i = tid; i < cached; i += THREADS) cache[i] = key_of_src(i);
+        __syncthreads();
+    }
+    auto key_of = [&](int i) { return i < cached ? cache[i] : key_of_src(i); };
     const int m = n < K ? n : K;
     const int fill = m <= 1024 ? 1024 : (m <= 2048 ? 2048 : 4096);
     if (n <= K) {

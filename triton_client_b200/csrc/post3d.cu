@@ -81,29 +81,35 @@ __global__ void __launch_bounds__(T, 1) rotated_nms_kernel(const float* __restri
 // whole GPU as the reference does (nms_kernel, iou3d_nms_kernel.cu:267-311: one 64-bit word per row and
 // 64-column block) — but the mask stays on the device and the sweep over it (iou3d_nms.cpp:116-132, a serial
 // host loop there) is done by one warp that streams the rows of still-open candidates through shared memory.
-//   order kernel (1 CTA)  : top pre_max by score, sorted; RBox of each in score order -> workspace
-//   mask kernel (grid)    : 64x64 tiles of the upper triangle; cheap distance test first, the surviving pairs
-//                           are listed in shared memory and evaluated one pair per thread
+//   order kernel (1 CTA)  : top pre_max by score, sorted -> workspace; a grid-wide kernel then gathers / decodes
+//                           their boxes in that order
+//   mask kernels (grid)   : 64x64 tiles of the upper triangle run the cheap distance test and list the surviving
+//                           pairs; a second kernel evaluates the listed pairs, one per thread
 //   sweep kernel (1 warp) : greedy pass over the mask (rows streamed through shared memory), writes the results
 // ---------------------------------------------------------------------------------------------------------
 constexpr int WIDE_MIN = 512;
 constexpr int MW = PRE_CAP / 64;      // mask words per row
 constexpr int MASK_T = 256;
 
+constexpr int ORDER_CACHE = 16384;   // keys the order kernels keep in (dynamic) shared memory across the selection passes
 struct OrderShared {
     unsigned long long skeys[sel::KCAP];
     sel::Scratch sel;
 };
 
-__global__ void __launch_bounds__(MASK_T) rot_mask_kernel(const rot::RBox* __restrict__ R, const int* __restrict__ m_dev, float thresh,
-                                                          unsigned long long* __restrict__ mask) {
+// Mask, step 1: per 64x64 tile of the upper triangle, the cheap distance test. Pairs it cannot rule out go to a global
+// list (one slot reservation per tile) for rot_pairs_kernel; the tile's mask words are written as zeros. Should the
+// list be full, the tile evaluates its pairs itself.
+// m_dev[0] = number of candidates, m_dev[1] = pairs listed so far (zeroed by the order kernel).
+__global__ void __launch_bounds__(MASK_T) rot_mask_kernel(const rot::RBox* __restrict__ R, int* __restrict__ m_dev, float thresh,
+                                                          unsigned long long* __restrict__ mask, unsigned* __restrict__ pairs, int pair_cap) {
     const int bi = blockIdx.y, bj = blockIdx.x;   // row tile, column tile
-    const int m = *m_dev;
+    const int m = m_dev[0];
     if (bj < bi || bj * 64 >= m) return;          // lower triangle / past the last candidate: never read
     __shared__ rot::RBox rows[64], cols[64];
     __shared__ unsigned long long tmask[64];
     __shared__ unsigned short queue[64 * 64];
-    __shared__ int qn;
+    __shared__ int qn, qbase;
     const int tid = threadIdx.x, lane = tid & 31;
     if (tid < 64) {
         const int g = bi * 64 + tid;
@@ -129,13 +135,37 @@ __global__ void __launch_bounds__(MASK_T) rot_mask_kernel(const rot::RBox* __res
     }
     __syncthreads();
     const int nq = qn;
-    for (int q = tid; q < nq; q += MASK_T) {
-        const int e = queue[q];
-        const int i = e >> 6, j = e & 63;
-        if (rot::iou_bev(rows[i], cols[j]) > thresh) atomicOr(&tmask[i], 1ull << j);
-    }
+    if (tid == 0) qbase = nq ? atomicAdd(&m_dev[1], nq) : 0;
     __syncthreads();
+    const int base = qbase;
+    if (base + nq <= pair_cap) {
+        for (int q = tid; q < nq; q += MASK_T) {
+            const int e = queue[q];
+            pairs[base + q] = ((unsigned)(bi * 64 + (e >> 6)) << 16) | (unsigned)(bj * 64 + (e & 63));
+        }
+    } else {   // list full: blank whatever part of the reservation lies inside it, evaluate here
+        for (int q = tid; q < nq; q += MASK_T) {
+            if (base + q < pair_cap) pairs[base + q] = 0xffffffffu;
+            const int e = queue[q];
+            const int i = e >> 6, j = e & 63;
+            if (rot::iou_bev(rows[i], cols[j]) > thresh) atomicOr(&tmask[i], 1ull << j);
+        }
+        __syncthreads();
+    }
     if (tid < 64 && bi * 64 + tid < m) mask[(size_t)(bi * 64 + tid) * MW + bj] = tmask[tid];
+}
+
+// Mask, step 2: the exact rotated IoU of every listed pair, one pair per thread with all lanes busy (inside the tiles
+// the few pairs that survive the distance test would each run with most of their warp idle).
+__global__ void __launch_bounds__(256) rot_pairs_kernel(const rot::RBox* __restrict__ R, const int* __restrict__ m_dev, float thresh,
+                                                        const unsigned* __restrict__ pairs, int pair_cap, unsigned long long* __restrict__ mask) {
+    const int total = min(m_dev[1], pair_cap);
+    for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < total; q += gridDim.x * blockDim.x) {
+        const unsigned e = pairs[q];
+        if (e == 0xffffffffu) continue;
+        const int gi = (int)(e >> 16), gj = (int)(e & 0xffffu);
+        if (rot::iou_bev(R[gi], R[gj]) > thresh) atomicOr(&mask[(size_t)gi * MW + (gj >> 6)], 1ull << (gj & 63));
+    }
 }
 
 // The sweep over the mask (iou3d_nms.cpp:116-132 does it on the host) is a chain over the kept boxes: keep the first
@@ -287,18 +317,22 @@ __device__ int warp_mask_sweep(const unsigned long long* __restrict__ mask, int 
     return nk;
 }
 
-__global__ void __launch_bounds__(T, 1) rot_order_kernel(const float* __restrict__ boxes, const float* __restrict__ scores, int n, int pre_max,
-                                                         unsigned long long* __restrict__ skeys_out, rot::RBox* __restrict__ R_out,
-                                                         int* __restrict__ m_out) {
+__global__ void __launch_bounds__(T, 1) rot_order_kernel(const float* __restrict__ scores, int n, int pre_max,
+                                                         unsigned long long* __restrict__ skeys_out, int* __restrict__ m_out) {
     __shared__ OrderShared S;
+    extern __shared__ __align__(16) unsigned long long key_cache[];
     auto key_of = [&](int i) { return sel::make_key(__ldg(scores + i), (unsigned)i); };
-    const int m = sel::cta_topk_sorted(key_of, n, pre_max, S.skeys, S.sel);
-    for (int c = threadIdx.x; c < m; c += T) {
-        const unsigned long long k = S.skeys[c];
-        skeys_out[c] = k;
-        R_out[c] = rot::make_rbox(boxes + 7ll * sel::key_index(k));
-    }
-    if (threadIdx.x == 0) *m_out = m;
+    const int m = sel::cta_topk_sorted(key_of, n, pre_max, S.skeys, S.sel, key_cache, ORDER_CACHE);
+    for (int c = threadIdx.x; c < m; c += T) skeys_out[c] = S.skeys[c];
+    if (threadIdx.x == 0) { m_out[0] = m; m_out[1] = 0; }
+}
+
+// the ordered candidates' boxes, one thread each over the whole grid (inside the one-CTA order kernel the four
+// dependent rounds of scattered loads per thread cost more than the selection itself)
+__global__ void __launch_bounds__(256) rot_rbox_kernel(const float* __restrict__ boxes, const unsigned long long* __restrict__ skeys,
+                                                       const int* __restrict__ m_dev, rot::RBox* __restrict__ R_out) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < m_dev[0]) R_out[c] = rot::make_rbox(boxes + 7ll * sel::key_index(skeys[c]));
 }
 
 __global__ void __launch_bounds__(SWEEP_T, 1) rot_sweep_kernel(const unsigned long long* __restrict__ mask, const unsigned long long* __restrict__ skeys,
@@ -424,25 +458,29 @@ __global__ void __launch_bounds__(T, 1) pp_post_kernel(const PPParams p, const f
 }
 
 // wide path (see rot_mask_kernel): the same steps as pp_post_kernel with the IoU work between them on the whole GPU
-__global__ void __launch_bounds__(T, 1) pp_order_kernel(const PPParams p, const float* __restrict__ box_preds, const float* __restrict__ dir_preds,
-                                                        const unsigned long long* __restrict__ cand, const int* __restrict__ cand_count,
-                                                        int cand_cap, float* __restrict__ sorted_boxes, unsigned long long* __restrict__ skeys_out,
-                                                        rot::RBox* __restrict__ R_out, int* __restrict__ m_out) {
+__global__ void __launch_bounds__(T, 1) pp_order_kernel(const PPParams p, const unsigned long long* __restrict__ cand, const int* __restrict__ cand_count,
+                                                        int cand_cap, unsigned long long* __restrict__ skeys_out, int* __restrict__ m_out) {
     __shared__ OrderShared S;
+    extern __shared__ __align__(16) unsigned long long key_cache[];
     const int tid = threadIdx.x;
     const int nc = min(*cand_count, cand_cap);
     auto key_of = [&](int i) { return cand[i]; };
-    const int m = sel::cta_topk_sorted(key_of, nc, p.pre_max, S.skeys, S.sel);
-    for (int c = tid; c < m; c += T) {
-        const unsigned long long k = S.skeys[c];
-        float b7[7];
-        pp_decode(p, (int)sel::key_index(k), box_preds, dir_preds, b7);
+    const int m = sel::cta_topk_sorted(key_of, nc, p.pre_max, S.skeys, S.sel, key_cache, ORDER_CACHE);
+    for (int c = tid; c < m; c += T) skeys_out[c] = S.skeys[c];
+    if (tid == 0) { m_out[0] = m; m_out[1] = 0; }
+}
+
+// lazy decode of the ordered candidates only (<= pre_max of the 321 408 anchors), one thread each over the grid
+__global__ void __launch_bounds__(256) pp_decode_kernel(const PPParams p, const float* __restrict__ box_preds, const float* __restrict__ dir_preds,
+                                                        const unsigned long long* __restrict__ skeys, const int* __restrict__ m_dev,
+                                                        float* __restrict__ sorted_boxes, rot::RBox* __restrict__ R_out) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= m_dev[0]) return;
+    float b7[7];
+    pp_decode(p, (int)sel::key_index(skeys[c]), box_preds, dir_preds, b7);
 #pragma unroll
-        for (int j = 0; j < 7; j++) sorted_boxes[c * 7 + j] = b7[j];
-        skeys_out[c] = k;
-        R_out[c] = rot::make_rbox(b7);
-    }
-    if (tid == 0) *m_out = m;
+    for (int j = 0; j < 7; j++) sorted_boxes[c * 7 + j] = b7[j];
+    R_out[c] = rot::make_rbox(b7);
 }
 
 __global__ void __launch_bounds__(SWEEP_T, 1) pp_finish_kernel(const PPParams p, const float* __restrict__ cls, const unsigned long long* __restrict__ mask,
@@ -635,9 +673,15 @@ struct WideBufs {
     rot::RBox* R;
     unsigned long long* mask;
     int* m;
+    unsigned* pairs;
+    int pair_cap;
 };
+static int wide_pair_cap(int m_max) {   // every pair of a small set; 2 M pairs (8 MB) beyond that, the tiles take the overflow
+    const long long all = (long long)m_max * (m_max - 1) / 2;
+    return (int)(all < (2ll << 20) ? (all > 0 ? all : 1) : (2ll << 20));
+}
 static size_t wide_bytes(int m_max) {
-    return (size_t)PRE_CAP * (8 + sizeof(rot::RBox)) + (size_t)m_max * MW * 8 + 4 * 256 + 256;
+    return (size_t)PRE_CAP * (8 + sizeof(rot::RBox)) + (size_t)m_max * MW * 8 + (size_t)wide_pair_cap(m_max) * 4 + 5 * 256 + 256;
 }
 static bool wide_bufs(tcb_ctx* ctx, int m_max, WideBufs& wb) {
     if (((ctx->ws_used + 255) & ~(size_t)255) + wide_bytes(m_max) > ctx->ws_bytes) return false;
@@ -645,7 +689,9 @@ static bool wide_bufs(tcb_ctx* ctx, int m_max, WideBufs& wb) {
     wb.R = (rot::RBox*)tcb_ws_alloc(ctx, (size_t)PRE_CAP * sizeof(rot::RBox));
     wb.mask = (unsigned long long*)tcb_ws_alloc(ctx, (size_t)m_max * MW * 8);
     wb.m = (int*)tcb_ws_alloc(ctx, 256);
-    return wb.skeys && wb.R && wb.mask && wb.m;
+    wb.pair_cap = wide_pair_cap(m_max);
+    wb.pairs = (unsigned*)tcb_ws_alloc(ctx, (size_t)wb.pair_cap * 4);
+    return wb.skeys && wb.R && wb.mask && wb.m && wb.pairs;
 }
 
 extern "C" int tcb_rotated_nms(tcb_ctx* ctx, const float* boxes_dev, const float* scores_dev, int n, float thresh, int pre_max,
@@ -658,10 +704,15 @@ extern "C" int tcb_rotated_nms(tcb_ctx* ctx, const float* boxes_dev, const float
     WideBufs wb;
     const int m_max = n < pre_max ? n : pre_max;
     if (m_max > WIDE_MIN && wide_bufs(ctx, m_max, wb)) {
-        rot_order_kernel<<<1, T, 0, st>>>(boxes_dev, scores_dev, n, pre_max, wb.skeys, wb.R, wb.m);
+        TCB_CUDA(ctx, cudaFuncSetAttribute(rot_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ORDER_CACHE * 8));
+        rot_order_kernel<<<1, T, ORDER_CACHE * 8, st>>>(scores_dev, n, pre_max, wb.skeys, wb.m);
+        TCB_LAUNCHED(ctx);
+        rot_rbox_kernel<<<tcb_div_up(m_max, 256), 256, 0, st>>>(boxes_dev, wb.skeys, wb.m, wb.R);
         TCB_LAUNCHED(ctx);
         const int nb = tcb_div_up(m_max, 64);
-        rot_mask_kernel<<<dim3(nb, nb), MASK_T, 0, st>>>(wb.R, wb.m, thresh, wb.mask);
+        rot_mask_kernel<<<dim3(nb, nb), MASK_T, 0, st>>>(wb.R, wb.m, thresh, wb.mask, wb.pairs, wb.pair_cap);
+        TCB_LAUNCHED(ctx);
+        rot_pairs_kernel<<<ctx->num_sms * 8, 256, 0, st>>>(wb.R, wb.m, thresh, wb.pairs, wb.pair_cap, wb.mask);
         TCB_LAUNCHED(ctx);
         TCB_CUDA(ctx, cudaFuncSetAttribute(rot_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SweepShared)));
         rot_sweep_kernel<<<1, SWEEP_T, sizeof(SweepShared), st>>>(wb.mask, wb.skeys, wb.m, post_max, keep_dev, count_dev);
@@ -723,10 +774,15 @@ extern "C" int tcb_pp_anchor_post(tcb_ctx* ctx, const float* cls_dev, const floa
     WideBufs wb;
     const int m_max = (int)(n_anchors < pre_max ? n_anchors : pre_max);
     if (m_max > WIDE_MIN && wide_bufs(ctx, m_max, wb)) {
-        pp_order_kernel<<<1, T, 0, st>>>(p, box_dev, dir_dev, cand, cand_count, (int)n_anchors, sorted_boxes, wb.skeys, wb.R, wb.m);
+        TCB_CUDA(ctx, cudaFuncSetAttribute(pp_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ORDER_CACHE * 8));
+        pp_order_kernel<<<1, T, ORDER_CACHE * 8, st>>>(p, cand, cand_count, (int)n_anchors, wb.skeys, wb.m);
+        TCB_LAUNCHED(ctx);
+        pp_decode_kernel<<<tcb_div_up(m_max, 256), 256, 0, st>>>(p, box_dev, dir_dev, wb.skeys, wb.m, sorted_boxes, wb.R);
         TCB_LAUNCHED(ctx);
         const int nb = tcb_div_up(m_max, 64);
-        rot_mask_kernel<<<dim3(nb, nb), MASK_T, 0, st>>>(wb.R, wb.m, nms_thresh, wb.mask);
+        rot_mask_kernel<<<dim3(nb, nb), MASK_T, 0, st>>>(wb.R, wb.m, nms_thresh, wb.mask, wb.pairs, wb.pair_cap);
+        TCB_LAUNCHED(ctx);
+        rot_pairs_kernel<<<ctx->num_sms * 8, 256, 0, st>>>(wb.R, wb.m, nms_thresh, wb.pairs, wb.pair_cap, wb.mask);
         TCB_LAUNCHED(ctx);
         TCB_CUDA(ctx, cudaFuncSetAttribute(pp_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SweepShared)));
         pp_finish_kernel<<<1, SWEEP_T, sizeof(SweepShared), st>>>(p, cls_dev, wb.mask, wb.skeys, wb.m, sorted_boxes, out_boxes_dev, out_scores_dev,
