@@ -6,6 +6,7 @@
 // Up to 512 candidates one 1024-thread CTA per frame (or per frame x head) does ordering + greedy NMS entirely in
 // shared memory; above that the pairwise IoU mask is built by the whole grid and swept by one CTA ("wide path"
 // below). Either way nothing leaves the device: no D2H of the mask, no serial host sweep (iou3d_nms.cpp:105-134).
+#include <cstddef>
 #include "common.cuh"
 #include "cta_select.cuh"
 #include "rotated.cuh"
@@ -537,7 +538,20 @@ __global__ void __launch_bounds__(T, 1) cp_head_kernel(const CPParams p, float* 
     const CPHead& hd = p.head[h];
     const int HW = p.H * p.W, n = hd.num_class * HW;
     // _topk (centernet_utils.py:136-151): per-class top-K then top-K across classes == global top-K of the sigmoids
-    auto key_of = [&](int i) { return sel::make_key(sigmoidf_ref(__ldg(hd.hm + i)), (unsigned)i); };
+    // The selection makes seven passes over the scores: compute each sigmoid once into shared memory (as ordered
+    // 32-bit patterns) — with K <= 1024 only the first 1024 slots of skeys are used, so the rest of skeys and all of
+    // R (not needed before the decode below) hold 34 816 scores, every cell of a 2-class 128x128 head.
+    unsigned* sc = reinterpret_cast<unsigned*>(&S.skeys[1024]);
+    constexpr int SC_CAP = (int)(((sel::KCAP - 1024) * sizeof(unsigned long long) + sizeof(S.R)) / sizeof(unsigned));
+    static_assert(offsetof(FrameShared, R) == sizeof(unsigned long long) * sel::KCAP, "score cache assumes R follows skeys");
+    const int cached = p.K <= 1024 ? min(n, SC_CAP) : 0;
+#pragma unroll 8
+    for (int i = tid; i < cached; i += T) sc[i] = sel::f32_ordered(sigmoidf_ref(__ldg(hd.hm + i)));
+    __syncthreads();
+    auto key_of = [&](int i) {
+        return i < cached ? (((unsigned long long)sc[i] << 32) | (unsigned long long)(0xffffffffu - (unsigned)i))
+                          : sel::make_key(sigmoidf_ref(__ldg(hd.hm + i)), (unsigned)i);
+    };
     const int m = sel::cta_topk_sorted(key_of, n, p.K, S.skeys, S.sel);
     // decode_bbox_from_heatmap (centernet_utils.py:154-216) + range/score mask, order preserved
     // scratch rows: [0, heads*post_max) final rows per head, then per head pre_max rows of masked, still sorted boxes
