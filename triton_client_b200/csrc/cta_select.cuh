@@ -113,7 +113,7 @@ __device__ __forceinline__ void sort_desc_n(unsigned long long* skeys, int m) { 
 // latency of key_of on every pass.
 template <typename KeyFn>
 __device__ int cta_topk_sorted(KeyFn key_of_src, int n, int K, unsigned long long* skeys, Scratch& S,
-                               unsigned long long* cache = nullptr, int cache_cap = 0) {
+                               unsigned long long* cache = nullptr, int cache_cap = 0, int list_cap = KCAP) {
     const int tid = threadIdx.x;
     const int cached = (cache != nullptr && n > K) ? (n < cache_cap ? n : cache_cap) : 0;
     if (cached) {
@@ -131,17 +131,27 @@ __device__ int cta_topk_sorted(KeyFn key_of_src, int n, int K, unsigned long lon
         return m;
     }
     // radix select of the K-th largest key, 11 bits at a time from the top (last digit 9 bits)
+    // As soon as the bin holding the K-th key has no more than list_cap (<= KCAP) keys, those keys (the only ones still undecided) are
+    // copied into skeys and the remaining passes run over that short list instead of all n keys.
     unsigned long long prefix = 0ull, pmask = 0ull;
     int remaining = K;
+    int listed = -1;   // >= 0: number of undecided keys held in skeys
     for (int shift = 53; shift >= -2; shift -= 11) {
         const int sh = shift < 0 ? 0 : shift;
         const int bits = shift < 0 ? 9 : 11;
         const unsigned long long dmask = (1ull << bits) - 1;
         for (int i = tid; i < BINS; i += THREADS) S.hist[i] = 0;
         __syncthreads();
-        for (int i = tid; i < n; i += THREADS) {
-            const unsigned long long k = key_of(i);
-            if ((k & pmask) == prefix) atomicAdd(&S.hist[(int)((k >> sh) & dmask)], 1);
+        if (listed >= 0) {
+            for (int i = tid; i < listed; i += THREADS) {
+                const unsigned long long k = skeys[i];
+                if ((k & pmask) == prefix) atomicAdd(&S.hist[(int)((k >> sh) & dmask)], 1);
+            }
+        } else {
+            for (int i = tid; i < n; i += THREADS) {
+                const unsigned long long k = key_of(i);
+                if ((k & pmask) == prefix) atomicAdd(&S.hist[(int)((k >> sh) & dmask)], 1);
+            }
         }
         __syncthreads();
         // thread t owns bins (BINS-1-2t, BINS-2-2t): scan from the top bin downwards
@@ -155,7 +165,19 @@ __device__ int cta_topk_sorted(KeyFn key_of_src, int n, int K, unsigned long lon
         prefix |= (unsigned long long)S.digit << sh;
         pmask |= dmask << sh;
         remaining -= S.above;
+        const int in_bin = S.hist[S.digit];
         __syncthreads();
+        if (listed < 0 && in_bin <= list_cap && shift > 0) {
+            if (tid == 0) S.count = 0;
+            __syncthreads();
+            for (int i = tid; i < n; i += THREADS) {
+                const unsigned long long k = key_of(i);
+                if ((k & pmask) == prefix) skeys[atomicAdd(&S.count, 1)] = k;
+            }
+            __syncthreads();
+            listed = S.count;
+            __syncthreads();
+        }
     }
     // prefix is now the K-th largest key exactly: gather everything >= it (exactly K keys)
     if (tid == 0) S.count = 0;

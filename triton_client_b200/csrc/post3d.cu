@@ -552,7 +552,7 @@ __global__ void __launch_bounds__(T, 1) cp_head_kernel(const CPParams p, float* 
         return i < cached ? (((unsigned long long)sc[i] << 32) | (unsigned long long)(0xffffffffu - (unsigned)i))
                           : sel::make_key(sigmoidf_ref(__ldg(hd.hm + i)), (unsigned)i);
     };
-    const int m = sel::cta_topk_sorted(key_of, n, p.K, S.skeys, S.sel);
+    const int m = sel::cta_topk_sorted(key_of, n, p.K, S.skeys, S.sel, nullptr, 0, cached ? 1024 : sel::KCAP);   // the score cache starts at skeys[1024]
     // decode_bbox_from_heatmap (centernet_utils.py:154-216) + range/score mask, order preserved
     // scratch rows: [0, heads*post_max) final rows per head, then per head pre_max rows of masked, still sorted boxes
     float* boxes = head_boxes + (long long)h * p.post_max * 9;
