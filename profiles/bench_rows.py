@@ -144,11 +144,15 @@ def main():
         lambda: yolo_head.extract_boxes_onnx(0.4, 0.6, [b4h, c4h]))
 
     # ---- detectron (c7) ----------------------------------------------------------------------------------------
-    lg, dl = synth.detectron_head_outputs(3001)
     cells = detectron_post.retinanet_cell_anchors()
-    lgd, dld = [torch.from_numpy(t).cuda() for t in lg], [torch.from_numpy(t).cuda() for t in dl]
-    row("c7 RetinaNet dense inference", "C3 201600 anchors x 80 classes", lambda i: eng.detectron_post(lgd, dld, (8, 16, 32, 64, 128), cells, (800, 1333)),
-        201600 * 84 * 4, 1, lambda: detectron_post.dense_inference(lg, dl, (8, 16, 32, 64, 128), cells, (800, 1333)))
+    if not args.only or args.only in "c7 RetinaNet dense inference":
+        for tag, bgd in (("", (-7.0, 1.2)), (" (stress: 2 % of the logits pass the threshold)", (-6.0, 1.5))):
+            lg, dl = synth.detectron_head_outputs(3001, background=bgd)
+            lgd, dld = [torch.from_numpy(t).cuda() for t in lg], [torch.from_numpy(t).cuda() for t in dl]
+            ncand = int(sum((t > np.log(0.05 / 0.95)).sum() for t in lg))
+            row("c7 RetinaNet dense inference", f"C3 201600 anchors x 80 classes, {ncand} candidates{tag}",
+                lambda i: eng.detectron_post(lgd, dld, (8, 16, 32, 64, 128), cells, (800, 1333)),
+                201600 * 84 * 4, 1, lambda: detectron_post.dense_inference(lg, dl, (8, 16, 32, 64, 128), cells, (800, 1333)))
 
     # ---- voxelise + decorate (b1-b7) ----------------------------------------------------------------------------
     def vox_row(name, config, pts_list, cfg, p, mv, overflow, f=None, **kw):

@@ -14,6 +14,7 @@ constexpr int T = sel::THREADS;
 constexpr int PRE_CAP = sel::KCAP;
 constexpr int POST_CAP = 1024;
 constexpr int MAX_LEVELS = 8, MAX_ANCHORS = 16;
+constexpr int DET_CACHE = 16384;   // candidate keys a level kernel keeps in shared memory across its selection passes
 
 __device__ __forceinline__ float sigmoidf_ref(float x) { return 1.f / (1.f + expf(-x)); }
 
@@ -29,29 +30,71 @@ struct DetParams {
     float score_thresh, nms_thresh;
 };
 
-// one thread per logit, NCHW order (coalesced); keeps sigmoid > thresh
-__global__ void __launch_bounds__(256) det_candidates_kernel(const DetParams p, int l) {
-    const Level& L = p.lv[l];
+// Candidates of every level in one launch: grid = (spatial chunks of 4096, channels A*K, levels), four 16-byte loads
+// per thread when the plane allows. HBM-bound: a logit below logit_floor cannot pass the
+// score threshold (logit_floor sits 0.01 below the threshold's logit, far more than expf's error), so the sigmoid is
+// only evaluated for the few that might; those are kept iff sigmoid > thresh exactly as before.
+constexpr int DC_Q = 4;                                   // 16-byte loads per thread
+constexpr int DC_SPAN = 256 * 4 * DC_Q;                   // logits per CTA
+__global__ void __launch_bounds__(256) det_candidates_kernel(const DetParams p, float logit_floor) {
+    const Level& L = p.lv[blockIdx.z];
     const int HW = L.H * L.W;
-    const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    bool ok = false;
-    unsigned long long key = 0ull;
-    if (e < (long long)p.A * p.K * HW) {
-        const int ch = (int)(e / HW), sp = (int)(e - (long long)ch * HW);
-        const int a = ch / p.K, k = ch - a * p.K;
-        float s = sigmoidf_ref(__ldg(L.logits + e));
-        if (p.variant == 1) s = sqrtf(s * sigmoidf_ref(__ldg(L.ctrness + sp)));   // FCOS: sqrt(cls * centerness)
-        ok = s > p.score_thresh;
-        key = sel::make_key(s, (unsigned)(((long long)sp * p.A + a) * p.K + k));
+    if ((int)blockIdx.x * DC_SPAN >= HW) return;  // (whole CTA)
+    __shared__ int s_count, s_base;
+    if (threadIdx.x == 0) s_count = 0;
+    __syncthreads();
+    const int ch = blockIdx.y;
+    const int a = ch / p.K, k = ch - a * p.K;
+    const float* plane = L.logits + (long long)ch * HW;
+    float x[DC_Q][4];
+#pragma unroll
+    for (int q = 0; q < DC_Q; q++) {              // all loads first
+        const int sp0 = blockIdx.x * DC_SPAN + (q * 256 + threadIdx.x) * 4;
+        const float* src = plane + sp0;
+        if (sp0 + 3 < HW && (((uintptr_t)src) & 15) == 0) {
+            const float4 v = __ldg(reinterpret_cast<const float4*>(src));
+            x[q][0] = v.x; x[q][1] = v.y; x[q][2] = v.z; x[q][3] = v.w;
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; j++) x[q][j] = sp0 + j < HW ? __ldg(src + j) : -INFINITY;
+        }
     }
-    const unsigned em = __ballot_sync(0xffffffffu, ok);
-    if (em) {
-        const int lane = threadIdx.x & 31;
-        int base = 0;
-        if (lane == 0) base = atomicAdd(L.cand_count, __popc(em));
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (ok) L.cand[base + __popc(em & ((1u << lane) - 1))] = key;
+    // slots: one shared-memory reservation per warp and element column, one global reservation per CTA (a dense head
+    // would otherwise serialise hundreds of thousands of atomics on the level's counter)
+    const int lane = threadIdx.x & 31;
+    unsigned long long key[DC_Q * 4];
+    int slot[DC_Q * 4];
+#pragma unroll
+    for (int q = 0; q < DC_Q; q++) {
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int e = q * 4 + j;
+            bool ok = false;
+            key[e] = 0ull;
+            if (x[q][j] > logit_floor) {
+                const int sp = blockIdx.x * DC_SPAN + (q * 256 + threadIdx.x) * 4 + j;
+                float s = sigmoidf_ref(x[q][j]);
+                if (p.variant == 1) s = sqrtf(s * sigmoidf_ref(__ldg(L.ctrness + sp)));   // FCOS: sqrt(cls * centerness)
+                ok = s > p.score_thresh;
+                key[e] = sel::make_key(s, (unsigned)(((long long)sp * p.A + a) * p.K + k));
+            }
+            slot[e] = -1;
+            const unsigned em = __ballot_sync(0xffffffffu, ok);
+            if (em) {
+                int base = 0;
+                if (lane == 0) base = atomicAdd(&s_count, __popc(em));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (ok) slot[e] = base + __popc(em & ((1u << lane) - 1));
+            }
+        }
     }
+    __syncthreads();
+    if (threadIdx.x == 0) s_base = s_count ? atomicAdd(L.cand_count, s_count) : 0;
+    __syncthreads();
+    const int gbase = s_base;
+#pragma unroll
+    for (int e = 0; e < DC_Q * 4; e++)
+        if (slot[e] >= 0) L.cand[gbase + slot[e]] = key[e];
 }
 
 struct ABox { float x1, y1, x2, y2, area; int cls; };
@@ -77,22 +120,28 @@ struct DFrameShared {
     int total;
 };
 
-__global__ void __launch_bounds__(T, 1) det_post_kernel(const DetParams p, float4* __restrict__ mbox, float* __restrict__ mscore,
-                                                        int* __restrict__ mcls, unsigned long long* __restrict__ mkeys,
-                                                        float* __restrict__ out_boxes, float* __restrict__ out_scores,
-                                                        long long* __restrict__ out_classes, int* __restrict__ out_count) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    DFrameShared& S = *reinterpret_cast<DFrameShared*>(smem_raw);
-    const int tid = threadIdx.x;
+// per level (one CTA each): top-k of the level's candidates, delta decode, clip; rows go to their place in the
+// concatenation of all levels (the offsets follow from the candidate counts)
+struct DLevelShared {
+    unsigned long long skeys[sel::KCAP];
+    sel::Scratch sel;
+};
+__global__ void __launch_bounds__(T, 1) det_level_kernel(const DetParams p, float4* __restrict__ mbox, float* __restrict__ mscore,
+                                                         int* __restrict__ mcls, unsigned long long* __restrict__ mkeys) {
+    __shared__ DLevelShared S;
+    extern __shared__ __align__(16) unsigned long long key_cache[];
+    const int tid = threadIdx.x, l = blockIdx.x;
     const float scale_clamp = logf(1000.f / 16.f);
     int M = 0;
-    for (int l = 0; l < p.num_levels; l++) {   // per level: top-k of the survivors, decode, append
+    for (int q = 0; q < l; q++) M += min(min(*p.lv[q].cand_count, p.A * p.K * p.lv[q].H * p.lv[q].W), p.topk);
+    {
         const Level& L = p.lv[l];
+
         const int cap = p.A * p.K * L.H * L.W;
         const int n = min(*L.cand_count, cap);
         const unsigned long long* ck = L.cand;
         auto key_of = [&](int i) { return ck[i]; };
-        const int m = sel::cta_topk_sorted(key_of, n, p.topk, S.skeys, S.sel);
+        const int m = sel::cta_topk_sorted(key_of, n, p.topk, S.skeys, S.sel, key_cache, DET_CACHE);
         const int HW = L.H * L.W;
         for (int c = tid; c < m; c += T) {
             const unsigned long long key = S.skeys[c];
@@ -121,9 +170,18 @@ __global__ void __launch_bounds__(T, 1) det_post_kernel(const DetParams p, float
             mbox[g] = bx; mscore[g] = sel::key_score(key); mcls[g] = k;
             mkeys[g] = sel::make_key(sel::key_score(key), (unsigned)g);
         }
-        M += m;
-        __syncthreads();
     }
+}
+
+__global__ void __launch_bounds__(T, 1) det_post_kernel(const DetParams p, float4* __restrict__ mbox, float* __restrict__ mscore,
+                                                        int* __restrict__ mcls, unsigned long long* __restrict__ mkeys,
+                                                        float* __restrict__ out_boxes, float* __restrict__ out_scores,
+                                                        long long* __restrict__ out_classes, int* __restrict__ out_count) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    DFrameShared& S = *reinterpret_cast<DFrameShared*>(smem_raw);
+    const int tid = threadIdx.x;
+    int M = 0;
+    for (int l = 0; l < p.num_levels; l++) M += min(min(*p.lv[l].cand_count, p.A * p.K * p.lv[l].H * p.lv[l].W), p.topk);
     // torchvision.ops.batched_nms as the served (CUDA) model runs it: coordinate trick unless boxes.numel() > 20000
     auto mkey_of = [&](int i) { return mkeys[i]; };
     const int m = sel::cta_topk_sorted(mkey_of, M, PRE_CAP, S.skeys, S.sel);
@@ -212,11 +270,19 @@ extern "C" int tcb_detectron_post(tcb_ctx* ctx, int num_levels, const float* con
     TCB_WS(ctx, mscore, float, mcap);
     TCB_WS(ctx, mcls, int, mcap);
     TCB_WS(ctx, mkeys, unsigned long long, mcap);
-    for (int l = 0; l < num_levels; l++) {
-        const long long n = (long long)p.lv[l].H * p.lv[l].W * num_anchors * num_classes;
-        det_candidates_kernel<<<tcb_div_up(n, 256), 256, 0, st>>>(p, l);
+    {
+        // sigmoid(x) > t needs x > logit(t); FCOS scores sqrt(cls * ctr) > t need cls > t*t. 0.01 below that: never a false reject
+        const double t = variant == 1 ? (double)score_thresh * (double)score_thresh : (double)score_thresh;
+        const float logit_floor = t <= 0.0 ? -INFINITY : (t >= 1.0 ? INFINITY : (float)(log(t / (1.0 - t)) - 0.01));
+        int hw_max = 1;
+        for (int l = 0; l < num_levels; l++) hw_max = hw_max > p.lv[l].H * p.lv[l].W ? hw_max : p.lv[l].H * p.lv[l].W;
+        TCB_REQUIRE(ctx, num_anchors * num_classes <= 65535, "tcb_detectron_post: more than 65535 channels");
+        det_candidates_kernel<<<dim3(tcb_div_up(hw_max, DC_SPAN), num_anchors * num_classes, num_levels), 256, 0, st>>>(p, logit_floor);
         TCB_LAUNCHED(ctx);
     }
+    TCB_CUDA(ctx, cudaFuncSetAttribute(det_level_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DET_CACHE * 8));
+    det_level_kernel<<<num_levels, T, DET_CACHE * 8, st>>>(p, mbox, mscore, mcls, mkeys);
+    TCB_LAUNCHED(ctx);
     TCB_CUDA(ctx, cudaFuncSetAttribute(det_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DFrameShared)));
     det_post_kernel<<<1, T, sizeof(DFrameShared), st>>>(p, mbox, mscore, mcls, mkeys, out_boxes_dev, out_scores_dev, out_classes_dev, out_count_dev);
     TCB_LAUNCHED(ctx);

@@ -156,14 +156,17 @@ def random_boxes7(n, seed, extent=40.0):
 
 
 # ---- C3 FCOS / RetinaNet head outputs at 800x1333 (padded 800x1344) --------------------------------
-def detectron_head_outputs(seed, anchors_per_loc=9, num_classes=80, image_hw=(800, 1344), strides=(8, 16, 32, 64, 128), planted=60, fcos=False):
-    """Per level l: logits (A*K,H_l,W_l) ~ N(-6,1.5) with planted positives N(+2,1), deltas (A*4,H_l,W_l) ~ N(0,0.4);
-    FCOS adds centerness (1,H_l,W_l) ~ N(0,1). Logits on a 1/64 grid (see _quantise)."""
+def detectron_head_outputs(seed, anchors_per_loc=9, num_classes=80, image_hw=(800, 1344), strides=(8, 16, 32, 64, 128), planted=60, fcos=False,
+                           background=(-6.0, 1.5)):
+    """Per level l: logits (A*K,H_l,W_l) ~ N(background) with planted positives N(+2,1), deltas (A*4,H_l,W_l) ~ N(0,0.4);
+    FCOS adds centerness (1,H_l,W_l) ~ N(0,1). Logits on a 1/64 grid (see _quantise). The default background leaves 2 % of
+    all logits above the 0.05 score threshold (250 k candidates on the stride-8 level of C3: a stress case); (-7, 1.2)
+    leaves 0.04 % (4 k there), the order of magnitude a trained focal-loss head produces."""
     rng = np.random.default_rng(seed)
     logits, deltas, ctr = [], [], []
     for s in strides:
         h, w = -(-image_hw[0] // s), -(-image_hw[1] // s)
-        lg = rng.normal(-6, 1.5, (anchors_per_loc * num_classes, h, w))
+        lg = rng.normal(background[0], background[1], (anchors_per_loc * num_classes, h, w))
         for _ in range(planted // len(strides) + 1):
             lg[rng.integers(0, lg.shape[0]), rng.integers(0, h), rng.integers(0, w)] = rng.normal(2, 1)
         logits.append(_quantise(np.clip(lg, -8.9, 8.9)))
