@@ -9,7 +9,7 @@ import subprocess
 import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libtcb200.so")
+LIB_PATH = os.environ.get("TCB_LIB_PATH") or os.path.join(_HERE, "libtcb200.so")   # TCB_LIB_PATH: A/B runs of two builds
 CSRC = os.path.join(_HERE, "csrc")
 
 _lib = None

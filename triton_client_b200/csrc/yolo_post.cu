@@ -139,7 +139,6 @@ __global__ void __launch_bounds__(256) yolo_filter_kernel(
 // Small class counts (rows of <= 13 floats): every 32-byte sector of the tensor is touched anyway, so the rows are
 // pulled into shared memory whole (one DRAM round trip instead of the objectness -> class scores -> box chain of
 // dependent sector fetches) and filtered / decoded from there.
-constexpr int FS_ROWS = 128;   // rows per chunk (one warp, one pass)
 constexpr int FS_NBUF = 2;     // chunk buffers per warp: one bulk copy in flight behind the chunk being filtered (3 and 4 measured no faster)
 // As a stream: every warp owns FS_NBUF buffers of FS_ROWS rows and keeps bulk copies (TMA, completion on one
 // mbarrier per buffer) of its next chunks in flight while it filters the current one. The candidates of a chunk go
@@ -164,6 +163,7 @@ __device__ __forceinline__ void yf_bar_wait(unsigned long long* bar, unsigned ph
 }
 
 constexpr int FS_WARPS = 8;
+template <int FS_ROWS>   // rows per chunk: 128 for rows of <= 13 floats, 32 for wide rows (COCO: 85 floats) on small batches
 __global__ void __launch_bounds__(32 * FS_WARPS) yolo_filter_stream_kernel(
     const float* __restrict__ pred, int B, int N, int nc, double conf_thres, float conf_floor32, int use_filter, ClassMask cmask,
     double* __restrict__ c_score, float4* __restrict__ c_box, int2* __restrict__ c_meta, int2* __restrict__ chunk_info) {
@@ -236,7 +236,7 @@ __global__ void __launch_bounds__(32 * FS_WARPS) yolo_filter_stream_kernel(
                     if (v > best[u]) { best[u] = v; bidx[u] = c; }  // strict: first index wins
                 }
                 ok = !nan && nc > 0 && best[u] > conf_thres;
-                if (ok && use_filter) ok = (cmask.w[bidx[u] >> 6] >> (bidx[u] & 63)) & 1ull;
+                if (ok && use_filter) ok = bidx[u] < 256 && ((cmask.w[bidx[u] >> 6] >> (bidx[u] & 63)) & 1ull);
             }
             n_pass += __popc(__ballot_sync(0xffffffffu, pass));
             okm[u] = __ballot_sync(0xffffffffu, ok);
@@ -304,17 +304,20 @@ __device__ __forceinline__ bool rec_before(unsigned long long ka, unsigned ra, u
     return ka > kb || (ka == kb && ra < rb);
 }
 
-template <int E>
+// size: number of slots sorted (a power of two); 1024 * E, or with E == 1 also 512 / 256 / 128 — the threads beyond
+// size then only keep the barriers company, and a quarter-size sort has 28 instead of 55 stages.
+template <int E, int size = 1024 * E>
 __device__ __forceinline__ void bitonic_sort_regs(unsigned long long* skeys, uint2* smeta, int n) {
     const int tid = threadIdx.x;
+    const bool act = size >= 1024 || tid < size;  // whole warps (size is a multiple of 32); compile-time true for the full sizes
     unsigned long long k[E];
     uint2 m[E];
 #pragma unroll
     for (int u = 0; u < E; u++) {
         const int i = tid + u * 1024;
-        k[u] = skeys[i]; m[u] = smeta[i];
+        if (act) { k[u] = skeys[i]; m[u] = smeta[i]; }
     }
-    for (int kk = 2; kk <= 1024 * E; kk <<= 1) {
+    for (int kk = 2; kk <= size; kk <<= 1) {
         for (int j = kk >> 1; j > 0; j >>= 1) {
             if (j >= 1024) {
                 const int du = j >> 10;
@@ -337,11 +340,12 @@ __device__ __forceinline__ void bitonic_sort_regs(unsigned long long* skeys, uin
             } else {
                 if (j >= 32) {
 #pragma unroll
-                    for (int u = 0; u < E; u++) { const int i = tid + u * 1024; skeys[i] = k[u]; smeta[i] = m[u]; }
+                    for (int u = 0; u < E; u++) { const int i = tid + u * 1024; if (act) { skeys[i] = k[u]; smeta[i] = m[u]; } }
                     __syncthreads();
                 }
 #pragma unroll
                 for (int u = 0; u < E; u++) {
+                    if (!act) continue;
                     const int i = tid + u * 1024;
                     unsigned long long pk;
                     uint2 pm;
@@ -361,7 +365,7 @@ __device__ __forceinline__ void bitonic_sort_regs(unsigned long long* skeys, uin
         }
     }
 #pragma unroll
-    for (int u = 0; u < E; u++) { const int i = tid + u * 1024; skeys[i] = k[u]; smeta[i] = m[u]; }
+    for (int u = 0; u < E; u++) { const int i = tid + u * 1024; if (act) { skeys[i] = k[u]; smeta[i] = m[u]; } }
     __syncthreads();
 }
 
@@ -465,7 +469,7 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
     const int* __restrict__ c_count, SortEnt* __restrict__ gsort, int gsort_stride,
     double iou_thres, double class_offset, int max_det, int max_nms,
     double* __restrict__ out, int* __restrict__ out_count, const GroupOut go,
-    const int* __restrict__ xc_count, int* __restrict__ xc_out, const int2* __restrict__ chunk_info, int chunks) {
+    const int* __restrict__ xc_count, int* __restrict__ xc_out, const int2* __restrict__ chunk_info, int chunks, int chunk_rows) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     NmsShared& S = *reinterpret_cast<NmsShared*>(smem_raw);
     unsigned long long* skeys = reinterpret_cast<unsigned long long*>(smem_raw + sizeof(NmsShared));
@@ -481,8 +485,8 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
     if (tid == 0) { S.nkept = 0; S.a_total = 0; }
 
     // ---- this frame's candidates. Two layouts: a dense list of c_count[b] entries (general filter), or one region
-    //      per FS_ROWS-row chunk, chunk_info[b][c] = (count | big << 31, rows passing the objectness test), candidates
-    //      of chunk c at slots FS_ROWS*c + 0, 1, ... (streaming filter: nothing to zero, nothing reserved atomically) ----
+    //      per chunk of chunk_rows rows, chunk_info[b][c] = (count | big << 31, rows passing the objectness test), candidates
+    //      of chunk c at slots chunk_rows*c + 0, 1, ... (streaming filter: nothing to zero, nothing reserved atomically) ----
     int n_all, xc_total = 0;
     bool big;
     const int2* cinfo = chunk_info ? chunk_info + (long long)b * chunks : nullptr;
@@ -531,7 +535,7 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
             for (int i = tid; i < n_all; i += NMS_THREADS) {   // candidate i of the frame -> its chunk by bisection of the prefix sums
                 int lo = 0, hi = chunks;                       // invariant: cprefix[lo] <= i < cprefix[hi]
                 while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (cprefix[mid] <= i) lo = mid; else hi = mid; }
-                const int slot = lo * FS_ROWS + (i - cprefix[lo]);
+                const int slot = lo * chunk_rows + (i - cprefix[lo]);
                 const int2 m = c_meta[cbase + slot];
                 if (!split || (m.y % G) == g) {
                     const int q = atomicAdd(&S.a_total, 1);
@@ -555,14 +559,17 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
     int n = S.a_total;
     npad = 1;
     while (npad < n) npad <<= 1;
-    const int nfill = sort_in_smem ? (npad <= 1024 ? 1024 : (npad <= 2048 ? 2048 : 4096)) : npad;
+    const int nfill = sort_in_smem ? (npad <= 128 ? 128 : (npad <= 1024 ? npad : (npad <= 2048 ? 2048 : 4096))) : npad;
     for (int i = n + tid; i < nfill; i += NMS_THREADS) { keys[i] = 0ull; meta[i] = make_uint2(0xffffffffu, 0u); }
     __syncthreads();
     PROF_T(0);
     if (n < 2) {
         // nothing to order
     } else if (sort_in_smem) {
-        if (nfill == 1024) bitonic_sort_regs<1>(skeys, smeta, n);
+        if (nfill == 128) bitonic_sort_regs<1, 128>(skeys, smeta, n);
+        else if (nfill == 256) bitonic_sort_regs<1, 256>(skeys, smeta, n);
+        else if (nfill == 512) bitonic_sort_regs<1, 512>(skeys, smeta, n);
+        else if (nfill == 1024) bitonic_sort_regs<1>(skeys, smeta, n);
         else if (nfill == 2048) bitonic_sort_regs<2>(skeys, smeta, n);
         else bitonic_sort_regs<4>(skeys, smeta, n);
     } else {
@@ -806,7 +813,7 @@ size_t yolo_ws_bytes(int b, int n) {
     bytes += per * sizeof(float4) + 256;
     bytes += per * sizeof(int2) + 256;
     bytes += (size_t)b * 4 * sizeof(int) + 256;
-    bytes += (size_t)b * ((n + FS_ROWS - 1) / FS_ROWS) * sizeof(int2) + 256;
+    bytes += (size_t)b * ((n + 31) / 32) * sizeof(int2) + 256;
     int npad = 1;
     while (npad < n) npad <<= 1;
     // class groups: b * G lists with G <= SMs / b, so never more than max(b, SM count) lists (256 bounds today's parts)
@@ -854,9 +861,16 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
         if (G < 1) G = 1;
     }
     TCB_REQUIRE(ctx, b <= 65535 && b <= TCB_TICKETS, "tcb_yolo_nms: batch %d > 65535", b);
-    const int chunks = (n + FS_ROWS - 1) / FS_ROWS;
-    // small rows: streaming filter with per-chunk candidate regions (the NMS kernel holds chunks + 1 prefix sums in a 2048-int table)
-    const bool stream_filter = nc <= FILTER_SMALL_NC && n > 0 && chunks < MAX_NMS_CAP / 32;
+    // Streaming filter with per-chunk candidate regions: every byte of the tensor is read, which costs nothing extra for
+    // small rows (<= 13 floats: every sector is touched anyway, 128-row chunks) and is the faster way for wide rows as
+    // long as the tensor is small (a COCO head of one frame is 8.6 MB: 2 us of HBM time against a chain of sparse
+    // sector fetches; 32-row chunks). Large batches of wide rows keep the sparse filter. The NMS kernel holds
+    // chunks + 1 prefix sums in a 2048-int table.
+    int chunk_rows = 0;
+    if (nc <= FILTER_SMALL_NC) chunk_rows = 128;
+    else if (nc <= 123 && (long long)b * n * (5 + nc) * 4 <= (64ll << 20)) chunk_rows = 32;
+    const int chunks = chunk_rows ? (n + chunk_rows - 1) / chunk_rows : 0;
+    const bool stream_filter = chunk_rows != 0 && n > 0 && chunks < MAX_NMS_CAP / 32;
     TCB_WS(ctx, counts, int, (size_t)b * 4);
     int2* chunk_info = nullptr;
     if (stream_filter) {
@@ -897,16 +911,17 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
         if (bx < 1) bx = 1;
         if (stream_filter) {
             // FS_NBUF row buffers per warp; as many CTAs as fit, each warp streaming its share of the b * chunks chunks
-            const size_t fsm = 8 * FS_WARPS * FS_NBUF + (size_t)FS_WARPS * FS_NBUF * FS_ROWS * (5 + nc) * sizeof(float);
-            TCB_CUDA(ctx, cudaFuncSetAttribute(yolo_filter_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsm));
+            const size_t fsm = 8 * FS_WARPS * FS_NBUF + (size_t)FS_WARPS * FS_NBUF * chunk_rows * (5 + nc) * sizeof(float);
+            auto kernel = chunk_rows == 128 ? yolo_filter_stream_kernel<128> : yolo_filter_stream_kernel<32>;
+            TCB_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsm));
             const int per_sm = (int)((220 * 1024) / (fsm + 1024)) < 4 ? (int)((220 * 1024) / (fsm + 1024)) : 4;
-            const long long chunks_total = (long long)b * ((n + FS_ROWS - 1) / FS_ROWS);
+            const long long chunks_total = (long long)b * chunks;
             if (chunks_total >= (1ll << 30)) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_yolo_nms: b*n too large (%d x %d)", b, n);
             long long grid = tcb_div_up(chunks_total, FS_WARPS);
             if (grid > (long long)ctx->num_sms * per_sm) grid = (long long)ctx->num_sms * per_sm;
             float conf_floor32 = (float)conf_thres;   // objectness test in float32, exactly equivalent to the float64 one
             if ((double)conf_floor32 > conf_thres) conf_floor32 = nextafterf(conf_floor32, -INFINITY);
-            yolo_filter_stream_kernel<<<(int)grid, 32 * FS_WARPS, fsm, st>>>(
+            kernel<<<(int)grid, 32 * FS_WARPS, fsm, st>>>(
                 pred_dev, b, n, nc, conf_thres, conf_floor32, n_classes > 0, cm, c_score, c_box, c_meta, chunk_info);
         } else {
             yolo_filter_kernel<<<dim3(bx, b), 256, 0, st>>>(pred_dev, b, n, nc, conf_thres, n_classes > 0, cm,
@@ -918,7 +933,7 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
     TCB_CUDA(ctx, cudaFuncSetAttribute(yolo_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     yolo_nms_kernel<<<dim3(b, G), NMS_THREADS, smem, st>>>(n > 0 ? n : 1, c_score, c_box, c_meta, c_count, gsort, npad,
                                                            iou_thres, agnostic ? 0.0 : 4096.0, max_det, max_nms, out_dev, count_dev, go,
-                                                           xc_count, xc_count_dev, chunk_info, chunks);
+                                                           xc_count, xc_count_dev, chunk_info, chunks, chunk_rows);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }
@@ -1053,7 +1068,7 @@ extern "C" int tcb_yolo_nms_static(const float* pred_dev, int b, int n, int nc, 
     memset(&one_group, 0, sizeof(one_group));
     yolo_nms_kernel<<<b, NMS_THREADS, smem, st>>>(n > 0 ? n : 1, c_score, c_box, c_meta, c_count, gsort, npad,
                                                   iou_thres, agnostic ? 0.0 : 4096.0, max_det, max_nms, out_dev, count_dev, one_group,
-                                                  xc_count, xc_count_dev, nullptr, 0);
+                                                  xc_count, xc_count_dev, nullptr, 0, 0);
     ST_CUDA(cudaGetLastError());
     return TCB_OK;
 #undef ST_REQUIRE
