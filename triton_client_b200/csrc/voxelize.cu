@@ -220,6 +220,23 @@ __global__ void __launch_bounds__(256) vox_gather_kernel(const VoxParams p, cons
             const float* row = p.pts + (long long)mine * p.pt_stride;
             for (int j = 0; j < F; j++) vout[rank * F + j] = cond_feature(p, row, j);
         }
+    } else if (L <= 32 * 8) {
+        // up to 256 points: the segment is read once into registers (8 per lane), then P rounds of "smallest index
+        // greater than the last one" run on registers and shuffles only
+        int q[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) q[u] = lane + 32 * u < L ? seg[lane + 32 * u] : INT_MAX;
+        int last = -1;
+        for (int r = 0; r < keep; r++) {
+            int best = INT_MAX;
+#pragma unroll
+            for (int u = 0; u < 8; u++) if (q[u] > last && q[u] < best) best = q[u];
+#pragma unroll
+            for (int k = 16; k > 0; k >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, k));
+            last = best;
+            const float* row = p.pts + (long long)best * p.pt_stride;
+            for (int j = lane; j < F; j += 32) vout[r * F + j] = cond_feature(p, row, j);
+        }
     } else {
         int last = -1;
         for (int r = 0; r < keep; r++) {  // selection: next smallest index greater than `last`
