@@ -71,6 +71,10 @@ def test_letterbox_matches_oracle_exactly(engine, h, w, oh, ow):
     (480, 1280, 512, 640, "stretch"),    # width halved, height up-scaled: fused pass with bilinear rows
     (100, 64, 37, 32, "stretch"),
     (375, 1242, 200, 621, "stretch"),    # width halved but 621 is not a multiple of 4: general kernel
+    (480, 640, 512, 640, "stretch"),     # width unchanged, height up-scaled: fused identity-width pass
+    (100, 64, 37, 64, "stretch"),        # width unchanged, height reduced
+    (300, 640, 640, 640, "letterbox"),   # scale 1, rows padded above and below
+    (64, 64, 64, 64, "stretch"),
 ])
 def test_exact_half_scale_paths(engine, h, w, oh, ow, mode):
     """cv2's INTER_LINEAR at exactly 2:1 is the 2x2 box mean; aligned cases take the fused pass, the rest the general

@@ -36,7 +36,7 @@ struct PreParams {
     float rlo;  // float32 residual of 1/div (two-instruction exact division)
     int exact2;  // fma(v, rdiv, v*rlo) == v/div for all 256 inputs
     int vec_store;
-    int fast_area;  // exact 2:1 with 8-byte aligned column groups: one fused pass straight from the staged bytes
+    int fast_area;  // 1: width halved exactly, 2: width unchanged — one fused pass straight from the staged bytes (aligned column groups)
 };
 
 // u8 -> normalised f32, identical to numpy's `x.astype(float32) / div - sub` (true IEEE division).
@@ -458,6 +458,55 @@ __device__ __forceinline__ void pass_area(const PreParams& p, const uint8_t* __r
     }
 }
 
+// Width unchanged (image_adjust on an already model-sized frame, padding modes, vertical-only resizes): the x taps are
+// (2048, 0), so cv2's horizontal pass >> 4 is 128*p and the vertical pass ((b0*128p0)>>16) + ((b1*128p1)>>16) equals
+// ((b0*p0)>>9) + ((b1*p1)>>9). Lane = 4 output columns = 12 contiguous staged bytes per row (three 4-byte words,
+// stride 12 B across lanes: conflict-free); no row buffer. Same host conditions as pass_area (4-byte aligned groups).
+template <bool EXACT, bool HAS_SUB, bool INTERIOR>
+__device__ __forceinline__ void pass_ident(const PreParams& p, const uint8_t* __restrict__ stg, const XTap* __restrict__ xt,
+                                           const YTap* __restrict__ yt, unsigned shift, int z, int tx0, int ty0) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int ox0 = tx0 + lane * 4;
+    if (ox0 >= p.out_w) return;
+    const int xoff = xt[lane * 4].off;
+    const bool inx = INTERIOR || xoff >= 0;
+    const uint8_t* colbase = stg + shift + (inx ? xoff : 0);
+    const int rpw = p.th >> 3;
+    const long long plane = (long long)p.out_h * p.out_w;
+    float* d0 = p.dst + ((long long)z * 3) * plane + (long long)(ty0 + warp * rpw) * p.out_w + ox0;
+    for (int rr = 0; rr < rpw; rr++, d0 += p.out_w) {
+        const int j = warp * rpw + rr;
+        if (ty0 + j >= p.out_h) break;
+        const YTap y = yt[j];
+        float o[3][4];
+        if (inx && (INTERIOR || y.r0 >= 0)) {
+            const unsigned* r0 = reinterpret_cast<const unsigned*>(colbase + y.r0 * p.pitch);
+            const unsigned* r1 = reinterpret_cast<const unsigned*>(colbase + y.r1 * p.pitch);
+            const unsigned b0 = y.b0s >> 16, b1 = y.b1s >> 16;
+            const unsigned A[3] = {r0[0], r0[1], r0[2]};
+            unsigned B[3] = {0u, 0u, 0u};
+            if (b1) { B[0] = r1[0]; B[1] = r1[1]; B[2] = r1[2]; }     // (uniform per output row)
+#pragma unroll
+            for (int e = 0; e < 12; e++) {                            // byte e = pixel e/3, channel e%3
+                const unsigned p0 = __byte_perm(A[e >> 2], 0u, 0x4440u | (unsigned)(e & 3));
+                const unsigned p1 = __byte_perm(B[e >> 2], 0u, 0x4440u | (unsigned)(e & 3));
+                const unsigned v = (((b0 * p0) >> 9) + ((b1 * p1) >> 9) + 2u) >> 2;
+                const int c = e % 3, k = e / 3;
+                o[c][k] = norm2<EXACT, HAS_SUB>((int)v, p.div, p.rdiv, p.rlo, p.sub[p.swap ? 2 - c : c]);
+            }
+        } else {
+#pragma unroll
+            for (int c = 0; c < 3; c++) {
+                const float pv = p.padv[p.swap ? 2 - c : c];
+#pragma unroll
+                for (int i = 0; i < 4; i++) o[c][i] = pv;
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < 3; c++) st_stream_f4(d0 + (p.swap ? 2 - c : c) * plane, make_float4(o[c][0], o[c][1], o[c][2], o[c][3]));
+    }
+}
+
 template <bool AREA, bool EXACT, bool HAS_SUB>
 __global__ void __launch_bounds__(NTHREADS) preprocess2_kernel(const PreParams p, const TileGeo geo) {
     extern __shared__ __align__(16) uint8_t smem[];
@@ -545,6 +594,12 @@ __global__ void __launch_bounds__(NTHREADS) preprocess2_kernel(const PreParams p
     if (H.has_content && H.safe && tid < 32) mbar_wait(bar, 0);   // one warp polls; the rest sleep in the barrier below
     __syncthreads();
 
+    if (p.fast_area == 2) {   // width unchanged
+        const unsigned shift = (unsigned)((uintptr_t)(img + (long long)H.rmin * p.row_stride + (long long)H.xmin * 3) & 15u);
+        if (H.interior) pass_ident<EXACT, HAS_SUB, true>(p, stg, xt, yt, shift, z, tx0, ty0);
+        else pass_ident<EXACT, HAS_SUB, false>(p, stg, xt, yt, shift, z, tx0, ty0);
+        return;
+    }
     if (p.fast_area) {   // AREA: 2x2 box mean; otherwise x exactly 2:1 with bilinear y
         const unsigned shift = (unsigned)((uintptr_t)(img + (long long)H.rmin * p.row_stride + (long long)H.xmin * 3) & 15u);
         if (H.interior) pass_area<AREA, EXACT, HAS_SUB, true>(p, stg, xt, yt, shift, z, tx0, ty0);
@@ -688,8 +743,10 @@ extern "C" int tcb_preprocess_image(tcb_ctx* ctx, const uint8_t* src_dev, int n,
     // buffer + tap tables) stays <= 36 KB, so that six CTAs fit an SM; failing that the largest that fits 100 KB;
     // failing that (extreme down-scaling) the one-pass kernel that reads the source straight from global memory.
     const bool half_x = (w == 2 * p.new_w);   // x taps are then (1024, 1024) on columns 2dx, 2dx+1 for every dx
-    p.fast_area = (area || half_x) && p.vec_store && (((uintptr_t)src_dev & 15) == 0) && (src_row_stride % 16 == 0) &&
+    const bool same_x = (w == p.new_w);       // x taps (2048, 0) on column dx
+    p.fast_area = (area || half_x || same_x) && p.vec_store && (((uintptr_t)src_dev & 15) == 0) && (src_row_stride % 16 == 0) &&
                   (n == 1 || src_img_stride % 16 == 0) && (p.left % 4 == 0) && (p.new_w % 4 == 0);
+    if (p.fast_area && same_x && !area && !half_x) p.fast_area = 2;
     const size_t SMEM_MAX = 100 * 1024, SMEM_GOOD = 36 * 1024;
     bool staged = false;
     size_t smem = 0;
