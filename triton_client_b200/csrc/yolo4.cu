@@ -9,6 +9,7 @@
 #include "common.cuh"
 #include "cta_select.cuh"
 #include "cta_nms.cuh"
+#include "wide_nms.cuh"
 
 namespace {
 
@@ -198,6 +199,79 @@ __global__ void __launch_bounds__(T, 1) yolo4_nms_kernel(const float* __restrict
     if (tid == 0) { out_count[b] = nk; }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Wide path (more than WIDE_MIN rows): order kernel (one CTA per image) -> wide::tile_mask_kernel over the grid ->
+// sweep kernel (wide::warp_mask_sweep). The single CTA above walks the candidates in rounds of 64 survivors, which with
+// thousands of kept boxes (80 classes) is hundreds of rounds.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int WIDE_MIN = 512;
+constexpr int ORDER_CACHE = 16384;   // keys held in dynamic shared memory across the selection passes
+struct OrderShared {
+    unsigned long long skeys[sel::KCAP];
+    sel::Scratch sel;
+};
+
+// mode 0: nms_cpu (scores + boxes, one set); mode 1: YOLOv4 candidates of image blockIdx.x
+__global__ void __launch_bounds__(T, 1) aa_order_kernel(int mode, const float* __restrict__ boxes, const float* __restrict__ scores, int N,
+                                                        const unsigned long long* __restrict__ cand, const int* __restrict__ cand_count,
+                                                        unsigned long long* __restrict__ skeys_out, ABox* __restrict__ R_out, int* __restrict__ m_out) {
+    __shared__ OrderShared S;
+    extern __shared__ __align__(16) unsigned long long key_cache[];
+    const int b = blockIdx.x, tid = threadIdx.x;
+    int m;
+    if (mode == 0) {
+        auto key_of = [&](int i) { return sel::make_key(__ldg(scores + i), (unsigned)i); };
+        m = sel::cta_topk_sorted(key_of, N, PRE_CAP, S.skeys, S.sel, key_cache, ORDER_CACHE);
+    } else {
+        const unsigned long long* ck = cand + (long long)b * N;
+        auto key_of = [&](int i) { return ck[i]; };
+        m = sel::cta_topk_sorted(key_of, min(cand_count[b], N), PRE_CAP, S.skeys, S.sel, key_cache, ORDER_CACHE);
+    }
+    for (int c = tid; c < m; c += T) {
+        const unsigned long long k = S.skeys[c];
+        skeys_out[(long long)b * PRE_CAP + c] = k;
+        if (mode == 0) R_out[c] = make_abox(boxes + 4ll * sel::key_index(k), 0);
+        else {
+            const int row = (int)(0xFFFFF - (unsigned)(k & 0xFFFFF)), cls = 4095 - (int)(k >> 52);
+            R_out[(long long)b * PRE_CAP + c] = make_abox(boxes + ((long long)b * N + row) * 4, cls);
+        }
+    }
+    if (tid == 0) m_out[b] = m;
+}
+
+__global__ void __launch_bounds__(wide::SWEEP_T, 1) aa_sweep_kernel(int mode, const unsigned long long* __restrict__ mask_all,
+                                                                   const unsigned long long* __restrict__ skeys_all, const ABox* __restrict__ R_all,
+                                                                   const int* __restrict__ m_all, int n_rows, int post_max,
+                                                                   int* __restrict__ keep, float* __restrict__ out, int* __restrict__ count) {
+    extern __shared__ __align__(128) unsigned char sweep_raw[];
+    wide::SweepShared& S = *reinterpret_cast<wide::SweepShared*>(sweep_raw);
+    __shared__ int nk_s;
+    const int b = blockIdx.x, tid = threadIdx.x;
+    const unsigned long long* skeys = skeys_all + (long long)b * PRE_CAP;
+    if (tid < 32) {
+        const int v = wide::warp_mask_sweep(mask_all + (size_t)b * PRE_CAP * wide::MW, m_all[b], post_max, S);
+        if (tid == 0) nk_s = v;
+    }
+    __syncthreads();
+    const int nk = nk_s;
+    if (mode == 0) {
+        for (int k = tid; k < nk; k += wide::SWEEP_T) keep[k] = (int)sel::key_index(skeys[S.kpos[k]]);
+        if (tid == 0) { count[0] = nk; count[1] = n_rows > PRE_CAP ? 1 : 0; }
+    } else {
+        const ABox* R = R_all + (long long)b * PRE_CAP;
+        float* o = out + (long long)b * post_max * 7;
+        for (int k = tid; k < nk; k += wide::SWEEP_T) {
+            const int c = S.kpos[k];
+            const unsigned long long key = skeys[c];
+            const ABox bx = R[c];
+            const float conf = sel::f32_from_ordered((unsigned)((key >> 20) & 0xFFFFFFFFull));
+            float* r = o + k * 7;  // [x1, y1, x2, y2, conf, conf, cls] (utils/postprocess.py:314-318)
+            r[0] = bx.x1; r[1] = bx.y1; r[2] = bx.x2; r[3] = bx.y2; r[4] = conf; r[5] = conf; r[6] = (float)bx.cls;
+        }
+        if (tid == 0) count[b] = nk;
+    }
+}
+
 // c5: pairwise IoU (base_postprocess.py:48-70), float32
 __global__ void __launch_bounds__(256) box_iou_kernel(const float* __restrict__ a, int n, const float* __restrict__ b, int m, float* __restrict__ out) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -241,19 +315,55 @@ extern "C" int tcb_yolo_head_decode(tcb_ctx* ctx, const float* head_dev, int b, 
     return TCB_OK;
 }
 
+// Workspace + launches of the wide path for `sets` independent candidate sets; false when the workspace has no room
+// (the caller then stays on the single-CTA kernels).
+struct AAWide { unsigned long long* skeys; ABox* R; unsigned long long* mask; int* m; };
+static bool aa_wide_bufs(tcb_ctx* ctx, int sets, AAWide& wb) {
+    const size_t per = (size_t)PRE_CAP * (8 + sizeof(ABox) + (size_t)wide::MW * 8) + 256;
+    if (((ctx->ws_used + 255) & ~(size_t)255) + per * sets + 4096 > ctx->ws_bytes) return false;
+    wb.skeys = (unsigned long long*)tcb_ws_alloc(ctx, (size_t)sets * PRE_CAP * 8);
+    wb.R = (ABox*)tcb_ws_alloc(ctx, (size_t)sets * PRE_CAP * sizeof(ABox));
+    wb.mask = (unsigned long long*)tcb_ws_alloc(ctx, (size_t)sets * PRE_CAP * wide::MW * 8);
+    wb.m = (int*)tcb_ws_alloc(ctx, (size_t)sets * sizeof(int) + 256);
+    return wb.skeys && wb.R && wb.mask && wb.m;
+}
+static int aa_wide_run(tcb_ctx* ctx, int mode, int sets, int n_rows, const float* boxes, const float* scores, const unsigned long long* cand,
+                       const int* cand_count, const AAWide& wb, NumpyNmsPred pred, int post_max, int* keep, float* out, int* count,
+                       cudaStream_t st) {
+    TCB_CUDA(ctx, cudaFuncSetAttribute(aa_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ORDER_CACHE * 8));
+    aa_order_kernel<<<sets, T, ORDER_CACHE * 8, st>>>(mode, boxes, scores, n_rows, cand, cand_count, wb.skeys, wb.R, wb.m);
+    TCB_LAUNCHED(ctx);
+    const int nb = tcb_div_up(n_rows < PRE_CAP ? n_rows : PRE_CAP, 64);
+    wide::tile_mask_kernel<ABox, NumpyNmsPred><<<dim3(nb, nb, sets), 64, 0, st>>>(wb.R, wb.m, 1, pred, wb.mask);
+    TCB_LAUNCHED(ctx);
+    TCB_CUDA(ctx, cudaFuncSetAttribute(aa_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(wide::SweepShared)));
+    aa_sweep_kernel<<<sets, wide::SWEEP_T, sizeof(wide::SweepShared), st>>>(mode, wb.mask, wb.skeys, wb.R, wb.m, n_rows, post_max, keep, out, count);
+    TCB_LAUNCHED(ctx);
+    return TCB_OK;
+}
+
 extern "C" int tcb_nms_axis_aligned(tcb_ctx* ctx, const float* boxes_dev, const float* scores_dev, int n, float thresh, int min_mode,
                                     int post_max, int* keep_dev, int* count_dev, void* stream) {
     TCB_CHECK_CTX(ctx);
     TCB_REQUIRE(ctx, n >= 0 && keep_dev && count_dev && (n == 0 || (boxes_dev && scores_dev)), "tcb_nms_axis_aligned: bad arguments");
     TCB_REQUIRE(ctx, post_max >= 1, "tcb_nms_axis_aligned: post_max must be >= 1");
     if (post_max > POST_CAP) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_nms_axis_aligned: post_max %d > compiled limit %d", post_max, POST_CAP);
+    AAWide wb;
+    if (n > WIDE_MIN && aa_wide_bufs(ctx, 1, wb))
+        return aa_wide_run(ctx, 0, 1, n, boxes_dev, scores_dev, nullptr, nullptr, wb, NumpyNmsPred{thresh, min_mode ? 1 : 0}, post_max, keep_dev, nullptr,
+                           count_dev, (cudaStream_t)stream);
     TCB_CUDA(ctx, cudaFuncSetAttribute(aa_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AFrameShared)));
     aa_nms_kernel<<<1, T, sizeof(AFrameShared), (cudaStream_t)stream>>>(boxes_dev, scores_dev, n, thresh, min_mode ? 1 : 0, post_max, keep_dev, count_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }
 
-extern "C" size_t tcb_yolo4_post_workspace(int b, int n) { return (size_t)(b > 0 ? b : 0) * (size_t)(n > 0 ? n : 0) * 8 + (size_t)(b > 0 ? b : 0) * 4 + 4096; }
+extern "C" size_t tcb_yolo4_post_workspace(int b, int n) {
+    const size_t bb = (size_t)(b > 0 ? b : 0), nn = (size_t)(n > 0 ? n : 0);
+    size_t bytes = bb * nn * 8 + bb * 4 + 4096;
+    if (n > WIDE_MIN) bytes += bb * ((size_t)PRE_CAP * (8 + sizeof(ABox) + (size_t)wide::MW * 8) + 256) + 8192;   // wide path (optional: without it one CTA per image does the NMS)
+    return bytes;
+}
 
 extern "C" int tcb_yolo4_post(tcb_ctx* ctx, const float* boxes_dev, const float* confs_dev, int b, int n, int nc, float conf_thresh,
                               float nms_thresh, int post_max, float* out_dev, int* count_dev, void* stream) {
@@ -272,6 +382,9 @@ extern "C" int tcb_yolo4_post(tcb_ctx* ctx, const float* boxes_dev, const float*
         yolo4_candidates_kernel<<<dim3(tcb_div_up(n, 256), b), 256, 0, st>>>(confs_dev, b, n, nc, conf_thresh, cand, cand_count);
         TCB_LAUNCHED(ctx);
     }
+    AAWide wb;
+    if (n > WIDE_MIN && aa_wide_bufs(ctx, b, wb))
+        return aa_wide_run(ctx, 1, b, n, boxes_dev, nullptr, cand, cand_count, wb, NumpyNmsPred{nms_thresh, 0}, post_max, nullptr, out_dev, count_dev, st);
     TCB_CUDA(ctx, cudaFuncSetAttribute(yolo4_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AFrameShared)));
     yolo4_nms_kernel<<<b, T, sizeof(AFrameShared), st>>>(boxes_dev, n > 0 ? n : 1, cand, cand_count, nms_thresh, post_max, out_dev, count_dev);
     TCB_LAUNCHED(ctx);
