@@ -37,7 +37,9 @@ def test_golden_reference_vectors(engine):
         _same(got, [g[f"out{k}_{b}"] for b in range(pred.shape[0])])
 
 
-@pytest.mark.parametrize("b,n,nc,conf", [(1, 25200, 80, 0.3), (4, 25200, 2, 0.3), (1, 16128, 2, 0.3), (3, 1000, 1, 0.6), (2, 5000, 33, 0.25)])
+# (3, 1003, 2) / (2, 777, 80) / (5, 333, 7): frame starts and last chunks that are not 16-byte aligned (lane copies instead of bulk copies)
+@pytest.mark.parametrize("b,n,nc,conf", [(1, 25200, 80, 0.3), (4, 25200, 2, 0.3), (1, 16128, 2, 0.3), (3, 1000, 1, 0.6), (2, 5000, 33, 0.25),
+                                         (3, 1003, 2, 0.3), (2, 777, 80, 0.3), (5, 333, 7, 0.25), (1, 31, 2, 0.1)])
 def test_matches_oracle_bit_exact(engine, b, n, nc, conf):
     pred = synth.yolo_output(b, n, nc, 500 + n + nc)
     want = yolo_post.extract_boxes(pred, conf_thres=conf, as_written=False)
