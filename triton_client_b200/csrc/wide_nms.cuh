@@ -51,7 +51,8 @@ struct SweepShared {
 
 static __device__ __forceinline__ unsigned sw_smem(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
 
-// Greedy pass over a mask written by rot_mask_kernel, called by the first warp of the CTA only. Returns the
+// Greedy pass over a mask in the layout above (row i, word w = columns 64w..64w+63, upper triangle), called by the
+// first warp of the CTA only; the other warps wait at the caller's barrier. Returns the
 // number kept; S.kpos holds their positions.
 static __device__ int warp_mask_sweep(const unsigned long long* __restrict__ mask, int m, int post_max, SweepShared& S) {
     const int lane = threadIdx.x & 31;
