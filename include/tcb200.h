@@ -342,6 +342,36 @@ int tcb_boxes_to_jsk(tcb_ctx* ctx, const float* boxes_dev, const float* scores_d
                      int* out_count_dev, void* stream);
 
 /*
+ * Evaluation math (communicator/evaluate_inference.py): calculate_metrics :400-446, ap_per_class :158-218, compute_ap
+ * :131-156, with box_iou (clients/postprocess/base_postprocess.py:48-70) in float64 as the reference's float64 arrays make
+ * it. A batch of frames per call, one CTA per frame. Rows are float64 [x1,y1,x2,y2,score,class] (gt_callback :363-374
+ * after xywh2xyxy; _scale_box_array :237-256 of extract_boxes' rows); frame f owns rows [offsets[f], offsets[f+1]) —
+ * the offset tables are HOST arrays of frames+1 ints. At most 2048 ground truths and 2048 predictions per frame.
+ *
+ * tcb_eval_match: IoU >= 0.5 with equal class, each detection to its highest-IoU label, each label to the first
+ *   detection that chose it; correct_dev u8 [total predictions, 10] at IoU 0.5..0.95 (float32 comparison as in :425),
+ *   matched_dev i32 [frames] = 0 where no pair passed (the reference records nothing for such a frame). Where the reference
+ *   leaves an order to an unstable sort (equal IoUs at :419), the later label wins.
+ * tcb_ap_per_class: per frame, tp u8 [n,nt] (nt <= 10), conf / pred_cls / target_cls float64 with an element stride
+ *   (6 when they are columns of the rows above, 1 when dense). Outputs per frame with room for max_classes (<= 256)
+ *   classes: num_classes i32 [frames] (the number of distinct target classes; if it exceeds max_classes the frame's
+ *   other outputs are incomplete), classes i32, p, r, f1 float64 [frames,max_classes], ap float64 [frames,max_classes,nt].
+ *   Equal confidences keep their input order.
+ * tcb_calculate_metrics: both, ap_per_class on each matched frame's own rows as :428-436 does.
+ */
+size_t tcb_eval_workspace(int frames, int max_classes);
+int tcb_eval_match(tcb_ctx* ctx, const double* gts_dev, const int* gt_offsets_host, const double* preds_dev,
+                   const int* pred_offsets_host, int frames, unsigned char* correct_dev, int* matched_dev, void* stream);
+int tcb_ap_per_class(tcb_ctx* ctx, const unsigned char* tp_dev, int nt, const double* conf_dev, const double* pred_cls_dev,
+                     long long pred_stride, const int* pred_offsets_host, const double* target_cls_dev, long long target_stride,
+                     const int* target_offsets_host, int frames, int max_classes, int* num_classes_dev, int* classes_dev,
+                     double* p_dev, double* r_dev, double* f1_dev, double* ap_dev, void* stream);
+int tcb_calculate_metrics(tcb_ctx* ctx, const double* gts_dev, const int* gt_offsets_host, const double* preds_dev,
+                          const int* pred_offsets_host, int frames, int max_classes, unsigned char* correct_dev,
+                          int* matched_dev, int* num_classes_dev, int* classes_dev, double* p_dev, double* r_dev,
+                          double* f1_dev, double* ap_dev, void* stream);
+
+/*
  * tcb_yolo_nms without a context and without any allocation. No counterpart in the reference: it is
  * here for callers that are not allowed to allocate GPU memory — a plugin inside a host process that
  * has already committed all of HBM to its own pools, or a per-frame callback that cannot afford the

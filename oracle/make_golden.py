@@ -248,6 +248,51 @@ def golden_overlay():
     save("overlay", **out)
 
 
+EVAL_CASES = [dict(n_gt=24, nc=2), dict(n_gt=40, nc=2, miss=0.3, false_pos=20), dict(n_gt=6, nc=3, dup=0.6),
+              dict(n_gt=12, nc=2, miss=1.0, false_pos=5),              # nothing matches: the frame is skipped
+              dict(n_gt=60, nc=5, dup=0.5, swap=0.2, false_pos=30), dict(n_gt=1, nc=1, miss=0.0, false_pos=0, dup=0.0, swap=0.0),
+              dict(n_gt=30, nc=2, jitter=14.0)]
+
+
+def golden_eval():
+    """The unmodified EvaluateInference.calculate_metrics / ap_per_class / compute_ap
+    (communicator/evaluate_inference.py:131-218, 400-446) on seeded frames of ground truths + predictions. The node is
+    built without its ROS/Prometheus set-up (object.__new__); the four Summary objects are recorders."""
+    import types
+    comm = ref_harness.communicator()
+    c = ref_harness.clients()
+    sys.modules["rospy"].loginfo = lambda *a, **k: None
+    node = object.__new__(comm.EvaluateInference)
+    node.client_postprocess = c.Yolov5client().get_postprocess()
+    node.img_processed = node.gt_processed = True
+    rec = {k: [] for k in ("p", "r", "f1", "ap_class")}
+    for k in rec:
+        setattr(node, k + "_summary", types.SimpleNamespace(observe=rec[k].append))
+    frames = [synth.eval_frame(synth.seed_for(9, k), **cs) for k, cs in enumerate(EVAL_CASES)]
+    node.all_groundtruths = [{"header": k, "ground_truths": g} for k, (g, _) in enumerate(frames)]
+    node.all_predictions = [{"header": k, "prediction": p} for k, (_, p) in enumerate(frames)]
+    stats = node.calculate_metrics()
+    out, si, pos = {}, 0, {k: 0 for k in rec}
+    for k, (g, p) in enumerate(frames):
+        out[f"gts{k}"], out[f"preds{k}"] = g, p
+        matched = si < len(stats) and np.shares_memory(stats[si][0][1], p)   # frames without a match leave no entry
+        out[f"matched{k}"] = np.array(bool(matched))
+        if not matched:
+            continue
+        correct = stats[si][0][0].numpy()
+        si += 1
+        pp, rr, ap, f1, cls = node.ap_per_class(correct, p[:, 4], p[:, 5], g[:, 5])
+        nc = len(cls)
+        for name, v in (("p", pp), ("r", rr), ("f1", f1), ("ap_class", cls)):      # what calculate_metrics itself observed
+            got = np.array(rec[name][pos[name]:pos[name] + nc])
+            pos[name] += nc
+            assert np.array_equal(got, v), name
+        out[f"correct{k}"], out[f"p{k}"], out[f"r{k}"], out[f"ap{k}"], out[f"f1{k}"], out[f"cls{k}"] = correct, pp, rr, ap, f1, cls
+        print(f"eval frame {k}: G={len(g)} D={len(p)} TP@0.5={int(correct[:, 0].sum())} classes={cls.tolist()} mAP50={ap[:, 0].mean():.4f}")
+    assert si == len(stats)
+    save("eval", **out)
+
+
 golden_overlay.__doc__ = golden_overlay.__doc__ % np.__version__
 
 

@@ -76,6 +76,12 @@ SIGNATURES = {
     "tcb_pointcloud2_unpack_workspace": (c_size_t, [c_int, c_int]),
     "tcb_pointcloud2_unpack": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_ll, c_int, P(c_int), P(c_int), c_int, c_int,
                                        c_void_p, c_void_p, c_void_p]),
+    "tcb_eval_workspace": (c_size_t, [c_int, c_int]),
+    "tcb_eval_match": (c_int, [c_void_p, c_void_p, P(c_int), c_void_p, P(c_int), c_int, c_void_p, c_void_p, c_void_p]),
+    "tcb_ap_per_class": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_ll, P(c_int), c_void_p, c_ll, P(c_int), c_int, c_int,
+                                 c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "tcb_calculate_metrics": (c_int, [c_void_p, c_void_p, P(c_int), c_void_p, P(c_int), c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                      c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "tcb_boxes_to_jsk": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_ll, c_float, c_double, c_void_p, c_void_p,
                                  c_void_p, c_void_p]),
     "tcb_yolo_nms_static_scratch_bytes": (c_size_t, []),

@@ -387,6 +387,60 @@ class Engine:
         return out, idx, cnt
 
 
+    # ---- evaluation math (§8f rank 4) --------------------------------------------------------------
+    @staticmethod
+    def _offsets(counts):
+        off = (c_int * (len(counts) + 1))()
+        for i, c in enumerate(counts):
+            off[i + 1] = off[i] + int(c)
+        return off
+
+    def _eval_outputs(self, frames, total_preds, max_classes, nt, dev):
+        z = lambda shape, dt: torch.zeros(shape, dtype=dt, device=dev)
+        return dict(correct=z((max(1, total_preds), 10), torch.uint8), matched=z((frames,), torch.int32),
+                    num_classes=z((frames,), torch.int32), classes=z((frames, max_classes), torch.int32),
+                    p=z((frames, max_classes), torch.float64), r=z((frames, max_classes), torch.float64),
+                    f1=z((frames, max_classes), torch.float64), ap=z((frames, max_classes, nt), torch.float64))
+
+    def eval_match(self, gts, gt_counts, preds, pred_counts):
+        """calculate_metrics' matching (evaluate_inference.py:408-425) for a batch of frames. gts / preds: CUDA float64
+        [total,6] rows [x1,y1,x2,y2,score,class], frame f owning `counts[f]` consecutive rows.
+        Returns (correct u8 [total_preds,10], matched i32 [frames])."""
+        _need_cuda(gts, preds)
+        g, p = gts.contiguous().double().reshape(-1, 6), preds.contiguous().double().reshape(-1, 6)
+        f = len(gt_counts)
+        o = self._eval_outputs(f, p.shape[0], 1, 10, g.device)
+        self.ctx.call("tcb_eval_match", _ptr(g), self._offsets(gt_counts), _ptr(p), self._offsets(pred_counts), f,
+                      _ptr(o["correct"]), _ptr(o["matched"]), _lib.stream_ptr())
+        return o["correct"][:p.shape[0]], o["matched"]
+
+    def ap_per_class(self, tp, conf, pred_cls, pred_counts, target_cls, target_counts, max_classes=16):
+        """ap_per_class (evaluate_inference.py:158-218) per frame: tp CUDA u8/bool [total,nt], conf / pred_cls float64
+        [total], target_cls float64 [total_targets]. Returns dict(num_classes, classes, p, r, f1, ap) of CUDA tensors."""
+        _need_cuda(tp, conf, pred_cls, target_cls)
+        t = tp.contiguous().to(torch.uint8)
+        c, pc, tc = conf.contiguous().double(), pred_cls.contiguous().double(), target_cls.contiguous().double()
+        f, nt = len(pred_counts), int(t.shape[1])
+        o = self._eval_outputs(f, 0, max_classes, nt, t.device)
+        self.ctx.call("tcb_ap_per_class", _ptr(t), nt, _ptr(c), _ptr(pc), 1, self._offsets(pred_counts), _ptr(tc), 1,
+                      self._offsets(target_counts), f, int(max_classes), _ptr(o["num_classes"]), _ptr(o["classes"]),
+                      _ptr(o["p"]), _ptr(o["r"]), _ptr(o["f1"]), _ptr(o["ap"]), _lib.stream_ptr())
+        return {k: o[k] for k in ("num_classes", "classes", "p", "r", "f1", "ap")}
+
+    def calculate_metrics(self, gts, gt_counts, preds, pred_counts, max_classes=16):
+        """Matching + per-frame ap_per_class in two launches (evaluate_inference.py:400-446). Returns the dict of
+        `_eval_outputs`; frames with matched == 0 have no statistics (the reference skips them)."""
+        _need_cuda(gts, preds)
+        g, p = gts.contiguous().double().reshape(-1, 6), preds.contiguous().double().reshape(-1, 6)
+        f = len(gt_counts)
+        o = self._eval_outputs(f, p.shape[0], max_classes, 10, g.device)
+        self.ctx.call("tcb_calculate_metrics", _ptr(g), self._offsets(gt_counts), _ptr(p), self._offsets(pred_counts), f,
+                      int(max_classes), _ptr(o["correct"]), _ptr(o["matched"]), _ptr(o["num_classes"]), _ptr(o["classes"]),
+                      _ptr(o["p"]), _ptr(o["r"]), _ptr(o["f1"]), _ptr(o["ap"]), _lib.stream_ptr())
+        o["correct"] = o["correct"][:p.shape[0]]
+        return o
+
+
 def yolo_nms_static(pred, conf_thres=0.6, iou_thres=0.45, classes=None, agnostic=False, max_det=300,
                     max_nms=30000, out=None, counts=None):
     """tcb_yolo_nms_static: the YOLOv5 postprocess for callers that may not allocate GPU memory (a plugin

@@ -173,3 +173,35 @@ def detectron_head_outputs(seed, anchors_per_loc=9, num_classes=80, image_hw=(80
         deltas.append(rng.normal(0, 0.4, (anchors_per_loc * 4, h, w)).astype(np.float32))
         ctr.append(_quantise(rng.normal(0, 1, (1, h, w))))
     return (logits, deltas, ctr) if fcos else (logits, deltas)
+
+
+# ---- evaluation frames (§8f rank 4): ground truths + predictions as EvaluateInference collects them ----------------
+def eval_frame(seed, n_gt=24, nc=2, img_wh=(1280, 720), miss=0.15, swap=0.1, dup=0.3, false_pos=8, jitter=6.0):
+    """One frame of evaluation input: `gts` (G,6) float64 rows [x1,y1,x2,y2,score,cls] (gt_callback after xywh2xyxy,
+    communicator/evaluate_inference.py:363-374) and `preds` (D,6) float64 rows [x1,y1,x2,y2,conf,cls]
+    (_scale_box_array of extract_boxes' rows, :237-256). Each ground truth is found (jittered box) unless missed, sometimes
+    twice, sometimes with the wrong class; false positives are added; rows come in descending confidence like NMS
+    output. Coordinates carry f32-derived fractions so IoUs are generic (no exact ties)."""
+    rng = np.random.default_rng(seed)
+    w, h = img_wh
+    cxy = rng.uniform([0, 0], [w, h], (n_gt, 2))
+    wh = np.exp(rng.normal(np.log(70.0), 0.5, (n_gt, 2)))
+    cls = rng.integers(0, nc, n_gt).astype(np.float64)
+    gts = np.concatenate([cxy - wh / 2, cxy + wh / 2, np.ones((n_gt, 1)), cls[:, None]], 1)
+    rows = []
+    for g in range(n_gt):
+        if rng.uniform() < miss:
+            continue
+        for _ in range(2 if rng.uniform() < dup else 1):
+            b = gts[g, :4] + rng.normal(0, jitter, 4)
+            c = cls[g] if rng.uniform() >= swap else float((int(cls[g]) + 1) % max(nc, 2))
+            rows.append([*b, rng.uniform(0.3, 1.0), c])
+    for _ in range(false_pos):
+        c0 = rng.uniform([0, 0], [w, h])
+        s = np.exp(rng.normal(np.log(70.0), 0.5, 2))
+        rows.append([*(c0 - s / 2), *(c0 + s / 2), rng.uniform(0.3, 0.7), float(rng.integers(0, nc))])
+    preds = np.array(rows, np.float64).reshape(-1, 6)
+    preds[:, :4] = preds[:, :4].astype(np.float32).astype(np.float64) * (w / 640.0)   # f32 boxes scaled in float64
+    gts[:, :4] *= w / 640.0
+    preds = preds[np.argsort(-preds[:, 4], kind="stable")]
+    return gts, preds
