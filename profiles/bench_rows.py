@@ -244,6 +244,18 @@ def main():
         row("g2 BoundingBoxArray fields", "500 detections", lambda i: eng.boxes_to_jsk(bj, sj, lj), 500 * 40 + 100 * 96, 1,
             lambda: opc2.jsk_rows(bxj, scj, lbj), "launch-bound (1 CTA)")
 
+    # ---- evaluation math (8f rank 4) -------------------------------------------------------------------------------------
+    if not args.only or args.only in "h1 evaluation metrics":
+        from oracle import eval_metrics as oem
+        ev = [synth.eval_frame(synth.seed_for(12, k), n_gt=40, nc=2, false_pos=12) for k in range(64)]
+        gcnt, pcnt = [len(g) for g, _ in ev], [len(p) for _, p in ev]
+        gd = torch.from_numpy(np.concatenate([g for g, _ in ev])).cuda()
+        pd = torch.from_numpy(np.concatenate([p for _, p in ev])).cuda()
+        row("h1 evaluation metrics", f"64 frames, {sum(gcnt)} labels, {sum(pcnt)} predictions, 2 classes",
+            lambda i: eng.calculate_metrics(gd, gcnt, pd, pcnt, max_classes=2), (sum(gcnt) + sum(pcnt)) * 48 + sum(pcnt) * 10 + 64 * 2 * 13 * 8, 64,
+            lambda: oem.calculate_metrics([ev[0][0]], [ev[0][1]]),
+            "CPU column: the oracle on one frame (the reference's torch+numpy version: about 1 ms per frame); latency-bound (two launches, one CTA per frame)")
+
     print("\n| row | config | GPU p50 ms | GPU ms/frame | CPU oracle ms/frame | alg. bytes | GB/s | frac of measured HBM |")
     print("|---|---|---:|---:|---:|---:|---:|---:|")
     for r in rows:

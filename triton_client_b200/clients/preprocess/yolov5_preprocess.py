@@ -47,7 +47,7 @@ class _ImagePreprocess(Preprocess):
         dev, aff = self.image_adjust_device(cv_image[None] if cv_image.ndim == 3 else cv_image, size_hw, mode, swap, pad_value)
         return self.stager.to_host(dev, "pre_out"), aff
 
-    def image_adjust_batch(self, frames, size_hw=None, mode="stretch", swap=False, pad_value=114, copy=True, chunks=8):
+    def image_adjust_batch(self, frames, size_hw=None, mode="stretch", swap=False, pad_value=114, copy=True, chunks=16):
         """frames: (n,h,w,3) uint8 host array/tensor -> (n,3,H,W) float32 host ndarray.
         copy=False hands back a view of the pinned staging buffer (valid until the next call).
         Large batches are cut into `chunks` pieces that flow through three streams (H2D, kernel, D2H), so the
@@ -55,7 +55,8 @@ class _ImagePreprocess(Preprocess):
         if size_hw is None:
             size_hw = tuple(frames.shape[1:3])
         n = int(frames.shape[0])
-        if n < 2 * chunks or chunks < 2:
+        chunks = min(int(chunks), n // 2)      # at least two frames per piece (measured on 64 frames: 8 pieces 6.53 ms, 16: 6.35, 32: 6.34)
+        if chunks < 2:
             dev, _ = self.image_adjust_device(frames, size_hw, mode, swap, pad_value)
             return self.stager.to_host(dev, "pre_out", copy=copy)
         return self._pipelined_batch(frames, size_hw, mode, swap, pad_value, copy, chunks)
