@@ -57,6 +57,32 @@ def test_ties_agnostic_filter_and_max_det(engine):
         _same(got, want)
 
 
+def test_score_distributions_of_the_counting_order(engine):
+    """The in-shared-memory ordering counts inside 1024 score buckets and falls back to the compare-exchange sort when a
+    bucket is crowded: equal scores, scores clustered in a sliver of the range, one outlier stretching the range, 1-4
+    records per thread — all must give the reference's order."""
+    rng = np.random.default_rng(21)
+    for n, mode in [(300, "equal"), (900, "equal"), (3000, "sliver"), (1500, "outlier"), (2500, "spread"), (4000, "two")]:
+        pred = np.zeros((2, n, 6), np.float32)
+        pred[:, :, 0:2] = rng.uniform(0, 640, (2, n, 2))
+        pred[:, :, 2:4] = rng.uniform(10, 60, (2, n, 2))
+        pred[:, :, 5] = 1.0
+        if mode == "equal":
+            pred[:, :, 4] = 0.75
+        elif mode == "sliver":
+            pred[:, :, 4] = 0.5 + rng.uniform(0, 1e-6, (2, n))
+        elif mode == "outlier":
+            pred[:, :, 4] = 0.5 + rng.uniform(0, 1e-3, (2, n))
+            pred[:, 7, 4] = 40.0
+        elif mode == "two":
+            pred[:, :, 4] = np.where(rng.uniform(0, 1, (2, n)) < 0.5, 0.4, 0.9)
+        else:
+            pred[:, :, 4] = rng.uniform(0.3, 1.0, (2, n))
+        want = yolo_post.extract_boxes(pred, conf_thres=0.25, as_written=False)
+        got, _ = _gpu(engine, pred, conf_thres=0.25)
+        _same(got, want)
+
+
 def test_many_candidates_sorts_in_global_scratch(engine):
     """> 4096 candidates per image: the ordering falls back to global scratch; dense overlapping boxes."""
     rng = np.random.default_rng(8)

@@ -172,8 +172,10 @@ __global__ void __launch_bounds__(32 * FS_WARPS) yolo_filter_stream_kernel(
     const int stride = 5 + nc;
     const int buf_floats = FS_ROWS * stride;                        // FS_ROWS rows: a multiple of 4 floats, 16-byte sized
     unsigned long long* bars = reinterpret_cast<unsigned long long*>(ys_raw);            // [FS_WARPS][FS_NBUF]
-    float* bufs = reinterpret_cast<float*>(ys_raw + 8 * FS_WARPS * FS_NBUF) + (size_t)warp * FS_NBUF * buf_floats;
+    unsigned char* plist = ys_raw + 8 * FS_WARPS * FS_NBUF + warp * FS_ROWS;            // rows of the current chunk that pass objectness
+    float* bufs = reinterpret_cast<float*>(ys_raw + 8 * FS_WARPS * FS_NBUF + FS_WARPS * FS_ROWS) + (size_t)warp * FS_NBUF * buf_floats;
     unsigned long long* bar = bars + FS_NBUF * warp;
+    const unsigned lt_mask = (1u << lane) - 1u;
     if (lane == 0) {
 #pragma unroll
         for (int k = 0; k < FS_NBUF; k++) yf_bar_init(bar + k);
@@ -214,56 +216,57 @@ __global__ void __launch_bounds__(32 * FS_WARPS) yolo_filter_stream_kernel(
             for (int i = lane; i < nrow * stride; i += 32) rows[i] = __ldg(src + i);
             __syncwarp();
         }
-        // filter the chunk in groups of 32 rows, results held in registers until the chunk's count is known
-        double best[FS_ROWS / 32];
-        int bidx[FS_ROWS / 32];
-        unsigned okm[FS_ROWS / 32];
-        int n_pass = 0, n_ok = 0;
+        // (1) objectness of every row, one load and one compare per row; the rows that pass (a few per cent) are listed
+        //     in row order. (2) the expensive part — float64 products over the classes, box conversion, stores — then
+        //     runs once per 32 listed rows with the lanes packed, instead of once per 32-row group with one or two
+        //     lanes active.
+        int n_pass = 0;
 #pragma unroll
         for (int u = 0; u < FS_ROWS / 32; u++) {
             const int r = u * 32 + lane;
-            const float* rp = rows + r * stride;
-            const float obj = (r < nrow) ? rp[4] : -1.f;
+            const float obj = (r < nrow) ? rows[r * stride + 4] : -1.f;
             const bool pass = obj > conf_floor32;   // == ((double)obj > conf_thres): conf_floor32 is the largest float <= conf_thres
-            best[u] = -1.0; bidx[u] = 0;
+            const unsigned m = __ballot_sync(0xffffffffu, pass);
+            if (pass) plist[n_pass + __popc(m & lt_mask)] = (unsigned char)r;
+            n_pass += __popc(m);
+        }
+        __syncwarp();
+        // The chunk's candidates go to slots row0, row0+1, ... of the frame (its own region: no slot reservation, no
+        // atomics); the counts and the "a box reaches beyond +-2048" flag go to chunk_info for the NMS kernel.
+        int n_ok = 0;
+        bool bigc = false;
+        for (int base = 0; base < n_pass; base += 32) {
+            const int k = base + lane;
             bool ok = false;
-            if (pass) {
-                const double o = (double)obj;
+            double best = -1.0;
+            int bidx = 0, r = 0;
+            const float* rp = rows;
+            if (k < n_pass) {
+                r = plist[k];
+                rp = rows + r * stride;
+                const double o = (double)rp[4];
                 bool nan = false;
                 for (int c = 0; c < nc; c++) {
                     const double v = (double)rp[5 + c] * o;
                     nan |= (v != v);
-                    if (v > best[u]) { best[u] = v; bidx[u] = c; }  // strict: first index wins
+                    if (v > best) { best = v; bidx = c; }  // strict: first index wins
                 }
-                ok = !nan && nc > 0 && best[u] > conf_thres;
-                if (ok && use_filter) ok = bidx[u] < 256 && ((cmask.w[bidx[u] >> 6] >> (bidx[u] & 63)) & 1ull);
+                ok = !nan && nc > 0 && best > conf_thres;
+                if (ok && use_filter) ok = bidx < 256 && ((cmask.w[bidx >> 6] >> (bidx & 63)) & 1ull);
             }
-            n_pass += __popc(__ballot_sync(0xffffffffu, pass));
-            okm[u] = __ballot_sync(0xffffffffu, ok);
-            n_ok += __popc(okm[u]);
-        }
-        // The chunk's candidates go to slots row0, row0+1, ... of the frame (its own region: no slot reservation, no
-        // atomics); the counts and the "a box reaches beyond +-2048" flag go to chunk_info for the NMS kernel.
-        bool bigc = false;
-        if (n_ok) {
-            int basei = 0;
-#pragma unroll
-            for (int u = 0; u < FS_ROWS / 32; u++) {
-                if ((okm[u] >> lane) & 1u) {
-                    const int r = u * 32 + lane;
-                    const float* rp = rows + r * stride;
-                    const double x = (double)rp[0], y = (double)rp[1], w = (double)rp[2], h = (double)rp[3];
-                    float4 bx;
-                    bx.x = (float)(x - w / 2); bx.y = (float)(y - h / 2);
-                    bx.z = (float)(x + w / 2); bx.w = (float)(y + h / 2);
-                    const long long k = (long long)b * N + row0 + basei + __popc(okm[u] & ((1u << lane) - 1));
-                    c_score[k] = best[u]; c_box[k] = bx; c_meta[k] = make_int2(row0 + r, bidx[u]);
-                    bigc |= !(fabsf(bx.x) < 2048.f && fabsf(bx.y) < 2048.f && fabsf(bx.z) < 2048.f && fabsf(bx.w) < 2048.f);
-                }
-                basei += __popc(okm[u]);
+            const unsigned okm = __ballot_sync(0xffffffffu, ok);
+            if (ok) {
+                const double x = (double)rp[0], y = (double)rp[1], w = (double)rp[2], h = (double)rp[3];
+                float4 bx;
+                bx.x = (float)(x - w / 2); bx.y = (float)(y - h / 2);
+                bx.z = (float)(x + w / 2); bx.w = (float)(y + h / 2);
+                const long long kk = (long long)b * N + row0 + n_ok + __popc(okm & lt_mask);
+                c_score[kk] = best; c_box[kk] = bx; c_meta[kk] = make_int2(row0 + r, bidx);
+                bigc |= !(fabsf(bx.x) < 2048.f && fabsf(bx.y) < 2048.f && fabsf(bx.z) < 2048.f && fabsf(bx.w) < 2048.f);
             }
-            bigc = __any_sync(0xffffffffu, bigc);
+            n_ok += __popc(okm);
         }
+        bigc = __any_sync(0xffffffffu, bigc);
         if (lane == 0) chunk_info[ch] = make_int2(n_ok | (bigc ? (int)0x80000000 : 0), n_pass);
         __syncwarp();   // every lane is done with this buffer before lane 0 lets the next copy land in it
     }
@@ -369,6 +372,94 @@ __device__ __forceinline__ void bitonic_sort_regs(unsigned long long* skeys, uin
     __syncthreads();
 }
 
+// Ordering by counting instead of comparing-and-swapping (what the candidate sets of a detector look like: a few
+// hundred to a few thousand scores spread over (conf_thres, 1]): the scores' range is cut into 1024 buckets, a shared
+// histogram + one scan gives every bucket its span of the output, and a record's final position is its bucket's start
+// plus the number of records of the same bucket that come before it in the full (score desc, row asc) order — so the
+// result is the bitonic sort's, bit for bit, for about a tenth of the instructions. Crowded buckets (equal or tightly
+// clustered scores) would make the in-bucket counting quadratic: then nothing is written and the caller sorts instead.
+constexpr int BK_N = 1024;       // buckets == threads
+constexpr int BK_CROWD = 64;     // give up above this many records in one bucket
+struct BucketScratch { int start[BK_N + 1]; int crowded; unsigned long long kmin, kmax; unsigned short perm[SORT_SMEM_CAP]; };
+
+template <int E>
+__device__ __forceinline__ bool bucket_order(unsigned long long* skeys, uint2* smeta, int n, BucketScratch& Q, int* wsum) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned long long k[E];
+    uint2 m[E];
+    unsigned long long lo = ~0ull, hi = 0ull;
+#pragma unroll
+    for (int u = 0; u < E; u++) {
+        const int i = tid + u * 1024;
+        if (i < n) { k[u] = skeys[i]; m[u] = smeta[i]; lo = min(lo, k[u]); hi = max(hi, k[u]); }
+    }
+    Q.start[tid] = 0;
+    if (tid == 0) { Q.crowded = 0; Q.kmin = ~0ull; Q.kmax = 0ull; }
+#pragma unroll
+    for (int sft = 16; sft > 0; sft >>= 1) {     // scores are positive doubles: their bit patterns order like the values
+        lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, sft));
+        hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, sft));
+    }
+    __syncthreads();
+    if (lane == 0 && hi >= lo) { atomicMin(&Q.kmin, lo); atomicMax(&Q.kmax, hi); }
+    __syncthreads();
+    const double smin = __longlong_as_double((long long)Q.kmin), smax = __longlong_as_double((long long)Q.kmax);
+    const double scale = (double)BK_N / (smax - smin);
+    int bk[E], ps[E];
+#pragma unroll
+    for (int u = 0; u < E; u++) {
+        const int i = tid + u * 1024;
+        if (i < n) {
+            const double x = (__longlong_as_double((long long)k[u]) - smin) * scale;      // monotone in the score
+            bk[u] = BK_N - 1 - (int)fmin(fmax(x, 0.0), (double)(BK_N - 1));              // higher scores first
+            ps[u] = atomicAdd(&Q.start[bk[u]], 1);
+        }
+    }
+    __syncthreads();
+    const int cnt = Q.start[tid];
+    int inc = cnt;
+#pragma unroll
+    for (int sft = 1; sft < 32; sft <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, sft); if (lane >= sft) inc += t; }
+    if (lane == 31) wsum[warp] = inc;
+    if (cnt > BK_CROWD) Q.crowded = 1;
+    __syncthreads();
+    int before = 0;
+    for (int w = 0; w < warp; w++) before += wsum[w];
+    Q.start[tid] = before + inc - cnt;
+    if (tid == 0) Q.start[BK_N] = n;
+    const bool crowded = Q.crowded != 0;
+    __syncthreads();
+    if (crowded) return false;
+#pragma unroll
+    for (int u = 0; u < E; u++) {
+        const int i = tid + u * 1024;
+        if (i < n) Q.perm[Q.start[bk[u]] + ps[u]] = (unsigned short)i;
+    }
+    __syncthreads();
+    int rank[E];
+#pragma unroll
+    for (int u = 0; u < E; u++) {
+        const int i = tid + u * 1024;
+        if (i < n) {
+            const int s0 = Q.start[bk[u]], e0 = Q.start[bk[u] + 1];
+            int r = s0;
+            for (int x = s0; x < e0; x++) {
+                const int j = Q.perm[x];
+                if (j != i && rec_before(skeys[j], smeta[j].x, k[u], m[u].x)) r++;
+            }
+            rank[u] = r;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int u = 0; u < E; u++) {
+        const int i = tid + u * 1024;
+        if (i < n) { skeys[rank[u]] = k[u]; smeta[rank[u]] = m[u]; }
+    }
+    __syncthreads();
+    return true;
+}
+
 constexpr int ROUND = 1024;      // candidates examined per greedy round (one per thread)
 constexpr int ACAP = 64;         // survivors of a round resolved against each other at once (one mask word per row)
 constexpr int RESIDENT = 4096;   // sorted candidates kept in shared memory (== SORT_SMEM_CAP: the arrays reuse the sort buffer)
@@ -448,6 +539,7 @@ struct NmsShared {
 };
 // After the sort the 64 KB sort buffer is reused for the sorted candidates themselves.
 struct CandShared { float4 box[RESIDENT]; int cls[RESIDENT]; unsigned slot[RESIDENT]; };
+static_assert(sizeof(BucketScratch) <= sizeof(DBox) * MAX_DET_CAP, "bucket tables overflow the kept-box array they borrow");
 static_assert(sizeof(CandShared) <= sizeof(SortEnt) * SORT_SMEM_CAP + 32 * 1024, "candidate arrays overflow their region");
 
 // Class groups (gridDim.y = G > 1): class-aware NMS of a frame whose boxes all lie inside (-2048, 2048) is G
@@ -566,7 +658,14 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
     if (n < 2) {
         // nothing to order
     } else if (sort_in_smem) {
-        if (nfill == 128) bitonic_sort_regs<1, 128>(skeys, smeta, n);
+        // the kept-box array is idle until the greedy rounds: its first 12 KB hold the bucket tables
+        BucketScratch& Q = *reinterpret_cast<BucketScratch*>(S.kd);
+        bool done;
+        if (nfill <= 1024) done = bucket_order<1>(skeys, smeta, n, Q, S.warp_cnt);
+        else if (nfill == 2048) done = bucket_order<2>(skeys, smeta, n, Q, S.warp_cnt);
+        else done = bucket_order<4>(skeys, smeta, n, Q, S.warp_cnt);
+        if (done) {
+        } else if (nfill == 128) bitonic_sort_regs<1, 128>(skeys, smeta, n);
         else if (nfill == 256) bitonic_sort_regs<1, 256>(skeys, smeta, n);
         else if (nfill == 512) bitonic_sort_regs<1, 512>(skeys, smeta, n);
         else if (nfill == 1024) bitonic_sort_regs<1>(skeys, smeta, n);
@@ -911,7 +1010,7 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
         if (bx < 1) bx = 1;
         if (stream_filter) {
             // FS_NBUF row buffers per warp; as many CTAs as fit, each warp streaming its share of the b * chunks chunks
-            const size_t fsm = 8 * FS_WARPS * FS_NBUF + (size_t)FS_WARPS * FS_NBUF * chunk_rows * (5 + nc) * sizeof(float);
+            const size_t fsm = 8 * FS_WARPS * FS_NBUF + (size_t)FS_WARPS * chunk_rows + (size_t)FS_WARPS * FS_NBUF * chunk_rows * (5 + nc) * sizeof(float);
             auto kernel = chunk_rows == 128 ? yolo_filter_stream_kernel<128> : yolo_filter_stream_kernel<32>;
             TCB_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsm));
             const int per_sm = (int)((220 * 1024) / (fsm + 1024)) < 4 ? (int)((220 * 1024) / (fsm + 1024)) : 4;
