@@ -621,28 +621,32 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
     unsigned long long* keys = sort_in_smem ? skeys : gkeys;
     uint2* meta = sort_in_smem ? smeta : gmeta;
     __syncthreads();
-    // gather (any order: the sort fixes it), keeping this CTA's classes when the frame is split
+    // gather (any order: the sort fixes it), keeping this CTA's classes when the frame is split; both loads of a
+    // candidate are issued together and a warp reserves its output slots with one shared-memory atomic
     if (n_bound > 0) {
-        if (cinfo) {
-            for (int i = tid; i < n_all; i += NMS_THREADS) {   // candidate i of the frame -> its chunk by bisection of the prefix sums
+        for (int i0 = 0; i0 < n_all; i0 += NMS_THREADS) {
+            const int i = i0 + tid;
+            int slot = 0;
+            bool take = i < n_all;
+            if (take && cinfo) {                               // candidate i of the frame -> its chunk by bisection of the prefix sums
                 int lo = 0, hi = chunks;                       // invariant: cprefix[lo] <= i < cprefix[hi]
                 while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (cprefix[mid] <= i) lo = mid; else hi = mid; }
-                const int slot = lo * chunk_rows + (i - cprefix[lo]);
-                const int2 m = c_meta[cbase + slot];
-                if (!split || (m.y % G) == g) {
-                    const int q = atomicAdd(&S.a_total, 1);
-                    keys[q] = (unsigned long long)__double_as_longlong(c_score[cbase + slot]);
-                    meta[q] = make_uint2((unsigned)m.x, (unsigned)slot);
-                }
+                slot = lo * chunk_rows + (i - cprefix[lo]);
+            } else if (take) {
+                slot = i;
             }
-        } else {
-            for (int i = tid; i < n_all; i += NMS_THREADS) {
-                const int2 m = c_meta[cbase + i];
-                if (!split || (m.y % G) == g) {
-                    const int q = atomicAdd(&S.a_total, 1);
-                    keys[q] = (unsigned long long)__double_as_longlong(c_score[cbase + i]);
-                    meta[q] = make_uint2((unsigned)m.x, (unsigned)i);
-                }
+            int2 m = make_int2(0, 0);
+            double sc = 0.0;
+            if (take) { m = c_meta[cbase + slot]; sc = c_score[cbase + slot]; }
+            take = take && (!split || (m.y % G) == g);
+            const unsigned bal = __ballot_sync(0xffffffffu, take);
+            int base = 0;
+            if (lane == 0 && bal) base = atomicAdd(&S.a_total, __popc(bal));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (take) {
+                const int q = base + __popc(bal & ((1u << lane) - 1u));
+                keys[q] = (unsigned long long)__double_as_longlong(sc);
+                meta[q] = make_uint2((unsigned)m.x, (unsigned)slot);
             }
         }
     }
@@ -858,28 +862,41 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
         __syncthreads();
         if (S.next_pos == G - 1) {   // last CTA of the frame: merge the G ordered lists
             __threadfence();
+            // the G lists' sort keys come into shared memory with one round trip (the candidate arrays are dead by now);
+            // the bisections then run there instead of as chains of dependent L2 reads
+            unsigned long long* mk = reinterpret_cast<unsigned long long*>(smem_raw + sizeof(NmsShared));
+            unsigned* mr = reinterpret_cast<unsigned*>(mk + G * max_det);
+            if (tid < G) S.warp_cnt[tid] = __ldcg(&go.count[(long long)b * G + tid]);
+            __syncthreads();
             int total = 0;
-            for (int q = 0; q < G; q++) total += __ldcg(&go.count[(long long)b * G + q]);
+            for (int q = 0; q < G; q++) total += S.warp_cnt[q];
             for (int e = tid; e < G * max_det; e += NMS_THREADS) {
                 const int q = e / max_det, i = e - q * max_det;
-                const long long lq = (long long)b * G + q;
-                if (i >= __ldcg(&go.count[lq])) continue;
-                const unsigned long long ke = __ldcg(&go.key[lq * max_det + i]);
-                const unsigned re = __ldcg(&go.krow[lq * max_det + i]);
+                if (i < S.warp_cnt[q]) {
+                    const long long lq = (long long)b * G + q;
+                    mk[e] = __ldcg(&go.key[lq * max_det + i]);
+                    mr[e] = __ldcg(&go.krow[lq * max_det + i]);
+                }
+            }
+            __syncthreads();
+            for (int e = tid; e < G * max_det; e += NMS_THREADS) {
+                const int q = e / max_det, i = e - q * max_det;
+                if (i >= S.warp_cnt[q]) continue;
+                const unsigned long long ke = mk[e];
+                const unsigned re = mr[e];
                 int rank = i;
                 for (int o2 = 0; o2 < G; o2++) {
                     if (o2 == q) continue;
-                    const long long lo2 = (long long)b * G + o2;
-                    int lo = 0, hi = __ldcg(&go.count[lo2]);   // entries of list o2 that come before e
+                    int lo = 0, hi = S.warp_cnt[o2];   // entries of list o2 that come before e
                     while (lo < hi) {
                         const int mid = (lo + hi) >> 1;
-                        if (rec_before(__ldcg(&go.key[lo2 * max_det + mid]), __ldcg(&go.krow[lo2 * max_det + mid]), ke, re)) lo = mid + 1;
+                        if (rec_before(mk[o2 * max_det + mid], mr[o2 * max_det + mid], ke, re)) lo = mid + 1;
                         else hi = mid;
                     }
                     rank += lo;
                 }
                 if (rank < max_det) {
-                    const double* src = go.rows + (lq * max_det + i) * 6;
+                    const double* src = go.rows + (((long long)b * G + q) * max_det + i) * 6;
                     double* dst = out + ((long long)b * max_det + rank) * 6;
 #pragma unroll
                     for (int c = 0; c < 6; c++) dst[c] = __ldcg(src + c);
