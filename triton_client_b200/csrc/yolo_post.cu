@@ -423,9 +423,15 @@ __device__ __forceinline__ bool bucket_order(unsigned long long* skeys, uint2* s
     if (lane == 31) wsum[warp] = inc;
     if (cnt > BK_CROWD) Q.crowded = 1;
     __syncthreads();
-    int before = 0;
-    for (int w = 0; w < warp; w++) before += wsum[w];
-    Q.start[tid] = before + inc - cnt;
+    if (warp == 0) {
+        const int t = wsum[lane];
+        int ti = t;
+#pragma unroll
+        for (int sft = 1; sft < 32; sft <<= 1) { const int u = __shfl_up_sync(0xffffffffu, ti, sft); if (lane >= sft) ti += u; }
+        wsum[lane] = ti - t;
+    }
+    __syncthreads();
+    Q.start[tid] = wsum[warp] + inc - cnt;
     if (tid == 0) Q.start[BK_N] = n;
     const bool crowded = Q.crowded != 0;
     __syncthreads();
@@ -521,7 +527,8 @@ __device__ __forceinline__ int iou32_decide(const float4 a, const float4 b, cons
 }
 
 #ifdef TCB_NMS_PROFILE
-__device__ long long g_nms_prof[8];
+__device__ long long g_nms_prof[16];
+__device__ long long g_nms_cta[4096];   // per CTA: cycles, candidates, rounds, kept
 #define PROF_T(k) do { __syncthreads(); if (blockIdx.x == 0 && threadIdx.x == 0) { long long t_ = clock64(); atomicAdd((unsigned long long*)&g_nms_prof[k], (unsigned long long)(t_ - prof_t0)); prof_t0 = t_; } } while (0)
 #else
 #define PROF_T(k) do {} while (0)
@@ -571,6 +578,8 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 #ifdef TCB_NMS_PROFILE
     long long prof_t0 = clock64();
+    const long long prof_start = prof_t0;
+    int prof_rounds = 0;
 #endif
     const int G = gridDim.y, g = blockIdx.y;
     const long long cbase = (long long)b * N;
@@ -597,8 +606,19 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
         if (lane == 31) S.warp_cnt[warp] = inc;
         if (lane == 0) { S.aidx[warp] = x; S.knew[warp] = bg; }
         __syncthreads();
-        int before = 0, tot = 0, xs = 0, bgs = 0;
-        for (int w = 0; w < NMS_THREADS / 32; w++) { const int t = S.warp_cnt[w]; if (w < warp) before += t; tot += t; xs += S.aidx[w]; bgs |= S.knew[w]; }
+        if (warp == 0) {   // one warp combines the 32 warp totals (every thread walking them costs 3 K shared-memory reads per CTA)
+            const int t = S.warp_cnt[lane];
+            int ti = t, xw = S.aidx[lane], bw = S.knew[lane];
+#pragma unroll
+            for (int sft = 1; sft < 32; sft <<= 1) { const int u = __shfl_up_sync(0xffffffffu, ti, sft); if (lane >= sft) ti += u; }
+#pragma unroll
+            for (int sft = 16; sft > 0; sft >>= 1) { xw += __shfl_xor_sync(0xffffffffu, xw, sft); bw |= __shfl_xor_sync(0xffffffffu, bw, sft); }
+            __syncwarp();
+            S.warp_cnt[lane] = ti - t;                                  // candidates in the warps before this one
+            if (lane == 31) { S.knew[0] = ti; S.knew[1] = xw; S.knew[2] = bw; }
+        }
+        __syncthreads();
+        const int before = S.warp_cnt[warp], tot = S.knew[0], xs = S.knew[1], bgs = S.knew[2];
         const int excl = before + inc - (a0 + a1);
         if (c0 <= chunks) cprefix[c0] = excl;            // entry `chunks` (the total) is written by whoever owns it
         if (c1 <= chunks) cprefix[c1] = excl + a0;
@@ -621,6 +641,7 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
     unsigned long long* keys = sort_in_smem ? skeys : gkeys;
     uint2* meta = sort_in_smem ? smeta : gmeta;
     __syncthreads();
+    PROF_T(8);
     // gather (any order: the sort fixes it), keeping this CTA's classes when the frame is split; both loads of a
     // candidate are issued together and a warp reserves its output slots with one shared-memory atomic
     if (n_bound > 0) {
@@ -651,6 +672,7 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
         }
     }
     __syncthreads();
+    PROF_T(9);
     for (int i = tid; i < MAX_NMS_CAP / 32; i += NMS_THREADS) S.resolved[i] = 0u;   // (the prefix sums lived here)
     int n = S.a_total;
     npad = 1;
@@ -830,6 +852,7 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
         PROF_T(5);
 #ifdef TCB_NMS_PROFILE
         if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd((unsigned long long*)&g_nms_prof[7], 1000000000ull);
+        prof_rounds++;
 #endif
         if (nk_new >= max_det) break;
         pos = np;
@@ -856,10 +879,12 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
         if (tid == 0) { out_count[b] = nk_final; if (xc_out) xc_out[b] = xc_total; }
     } else {
         if (tid == 0) go.count[list] = nk_final;
+        PROF_T(10);
         __threadfence();
         __syncthreads();
         if (tid == 0) S.next_pos = atomicAdd(&go.done[b], 1);
         __syncthreads();
+        PROF_T(11);
         if (S.next_pos == G - 1) {   // last CTA of the frame: merge the G ordered lists
             __threadfence();
             // the G lists' sort keys come into shared memory with one round trip (the candidate arrays are dead by now);
@@ -908,13 +933,18 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
     PROF_T(6);
 #ifdef TCB_NMS_PROFILE
     if (blockIdx.x == 0 && threadIdx.x == 0) { atomicAdd((unsigned long long*)&g_nms_prof[7], (unsigned long long)nk_final * 1000000ull + (unsigned long long)n); }
+    if (threadIdx.x == 0) {
+        const int cta = (blockIdx.x * gridDim.y + blockIdx.y) & 1023;
+        g_nms_cta[cta * 4 + 0] = clock64() - prof_start; g_nms_cta[cta * 4 + 1] = n; g_nms_cta[cta * 4 + 2] = prof_rounds; g_nms_cta[cta * 4 + 3] = nk_final;
+    }
 #endif
 }
 #ifdef TCB_NMS_PROFILE
 }  // namespace
+extern "C" void tcb_debug_nms_cta(long long* out4096) { cudaMemcpyFromSymbol(out4096, g_nms_cta, sizeof(long long) * 4096); }
 extern "C" void tcb_debug_nms_prof(long long* out8, int reset) {
-    cudaMemcpyFromSymbol(out8, g_nms_prof, sizeof(long long) * 8);
-    if (reset) { long long z[8] = {0}; cudaMemcpyToSymbol(g_nms_prof, z, sizeof(z)); }
+    cudaMemcpyFromSymbol(out8, g_nms_prof, sizeof(long long) * 16);
+    if (reset) { long long z[16] = {0}; cudaMemcpyToSymbol(g_nms_prof, z, sizeof(z)); }
 }
 namespace {
 #endif
