@@ -166,3 +166,46 @@ def test_pipelined_batch_equals_single_shot(engine):
     assert np.array_equal(a, want) and np.array_equal(b, want) and np.array_equal(c, want)
     a2 = pre.image_adjust_batch(frames[::-1].copy(), (160, 160), mode="letterbox", chunks=4)   # buffers reused across calls
     assert np.array_equal(a2, want[::-1])
+
+
+def test_extract_boxes_async_equals_extract_boxes(engine):
+    """The pipelined variant: queued on its own stream while a batch preprocess runs on the others; same results, same
+    return-the-exception convention."""
+    client = Yolov5client(engine=engine)
+    pre, post = client.get_preprocess(), client.get_postprocess()
+    frames = torch.from_numpy(np.stack([synth.image_noise(180, 320, 700 + i) for i in range(24)])).pin_memory()
+    for k in range(3):
+        pred = torch.from_numpy(synth.yolo_output(4, 5000, 2, 40 + k)).pin_memory()
+        want = post.extract_boxes(HostResponse([pred]), conf_thres=0.3)
+        hx = pre.image_adjust_batch_async(frames, (160, 160), mode="letterbox", chunks=4, copy=False)
+        pending = post.extract_boxes_async(HostResponse([pred]), conf_thres=0.3)
+        x, got = hx.result(), pending.result()
+        assert isinstance(got, list) and len(got) == len(want) and pending.result() is got
+        for a, b in zip(got, want):
+            assert torch.equal(a, b)
+        assert np.array_equal(x[3], pre2d.preprocess_frame(frames[3].numpy(), 160, 160, mode="letterbox")[0])
+    bg = np.zeros((1, 64, 7), np.float32)
+    r = post.extract_boxes_async(HostResponse([bg]), conf_thres=0.3).result()
+    assert isinstance(r, AssertionError) and str(r) == str(golden("yolo_post")["empty_msg"])
+    r = post.extract_boxes_async(HostResponse([bg]), conf_thres=0.3, iou_thres=2.0).result()
+    assert isinstance(r, AssertionError)
+    assert isinstance(post.extract_boxes_async(object()).result(), Exception)
+
+
+def test_two_batches_in_flight(engine):
+    """Deferred calls alternate between two sets of host buffers: the second batch is queued before the first result is read."""
+    client = Yolov5client(engine=engine)
+    pre, post = client.get_preprocess(), client.get_postprocess()
+    fa = torch.from_numpy(np.stack([synth.image_noise(180, 320, 800 + i) for i in range(16)])).pin_memory()
+    fb = torch.from_numpy(np.stack([synth.image_noise(180, 320, 850 + i) for i in range(16)])).pin_memory()
+    pa, pb = (torch.from_numpy(synth.yolo_output(3, 4000, 2, 60 + k)).pin_memory() for k in range(2))
+    want = [post.extract_boxes(HostResponse([p]), conf_thres=0.3) for p in (pa, pb)]
+    for _ in range(3):
+        h1 = (pre.image_adjust_batch_async(fa, (160, 160), mode="letterbox", chunks=4, copy=False), post.extract_boxes_async(HostResponse([pa]), conf_thres=0.3))
+        h2 = (pre.image_adjust_batch_async(fb, (160, 160), mode="letterbox", chunks=4, copy=False), post.extract_boxes_async(HostResponse([pb]), conf_thres=0.3))
+        xa, da = h1[0].result(), h1[1].result()
+        xb, db = h2[0].result(), h2[1].result()
+        for frames, x in ((fa, xa), (fb, xb)):
+            assert np.array_equal(x, np.concatenate([pre2d.preprocess_frame(f.numpy(), 160, 160, mode="letterbox") for f in frames]))
+        for got, w in ((da, want[0]), (db, want[1])):
+            assert all(torch.equal(a, b) for a, b in zip(got, w))

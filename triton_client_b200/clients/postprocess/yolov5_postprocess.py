@@ -11,6 +11,23 @@ from .base_postprocess import Postprocess
 _DATA = os.path.join(os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))), "data")
 
 
+class PendingBoxes:
+    """Handle returned by Yolov5postprocess.extract_boxes_async: `.result()` waits for the queued work and returns what
+    extract_boxes returns (the list of (n,6) tensors, or the exception object)."""
+
+    def __init__(self, finish=None, value=None, keep=()):
+        self._finish, self._value, self._keep = finish, value, keep
+
+    def result(self):
+        if self._finish is not None:
+            try:
+                self._value = self._finish()
+            except Exception as e:     # same convention as extract_boxes: errors are returned
+                self._value = e
+            self._finish, self._keep = None, ()
+        return self._value
+
+
 class Yolov5postprocess(Postprocess):
     def __init__(self, engine=None):
         super().__init__(engine)
@@ -47,6 +64,50 @@ class Yolov5postprocess(Postprocess):
             return output
         except Exception as e:
             return e
+
+    def extract_boxes_async(self, prediction, conf_thres=0.6, iou_thres=0.45, classes=None, agnostic=False,
+                            multi_label=False, labels=(), max_det=300):
+        """extract_boxes for a pipelined caller (no counterpart in the reference, whose loop is one frame at a time):
+        the upload of the response, the kernels and the download of the <= max_det rows are queued on this object's own
+        stream and the call returns at once, so the caller can run the next batch's preprocess meanwhile (the response's
+        upload then shares the PCIe link with the preprocess download instead of waiting for it). `.result()` on the
+        returned handle gives exactly what extract_boxes returns. The response must stay unchanged until then; at most two
+        calls in flight."""
+        try:
+            if not (0 <= conf_thres <= 1 and 0 <= iou_thres <= 1) or multi_label or (labels and any(len(l) for l in labels)):
+                return PendingBoxes(value=self.extract_boxes(prediction, conf_thres, iou_thres, classes, agnostic, multi_label, labels, max_det))
+            dev = self.engine.device
+            if getattr(self, "_side", None) is None:
+                self._side = torch.cuda.Stream(dev)
+            side = self._side
+            side.wait_stream(torch.cuda.current_stream(dev))
+            shape = tuple(int(v) for v in prediction.outputs[0].shape)
+            self._turn = turn = (getattr(self, "_turn", 0) + 1) & 1     # two sets of host buffers: at most two calls in flight
+            with torch.cuda.stream(side):
+                pred = self.stager.to_device(prediction.raw_output_contents[0], np.float32, shape, f"yolo_in_async{turn}")
+                out, cnt, xc = self.engine.yolo_nms(pred, conf_thres=conf_thres, iou_thres=iou_thres, classes=classes,
+                                                    agnostic=agnostic, max_det=max_det)
+                both = torch.stack((cnt, xc))
+                hb = self.stager.pinned(f"yolo_counts{turn}", both.numel() * 4).view(torch.int32).reshape(both.shape)
+                hb.copy_(both, non_blocking=True)
+                hr = self.stager.pinned(f"yolo_out_async{turn}", out.numel() * 8).view(torch.float64).reshape(out.shape)
+                hr.copy_(out, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(side)
+
+            def finish():
+                ev.synchronize()
+                counts, rows = hb.numpy(), hr.numpy()
+                assert counts[1].sum() > 0, 'No valid detections found'
+                output = [torch.zeros((0, 6))] * shape[0]
+                for xi in range(shape[0]):
+                    n = int(counts[0, xi])
+                    if n:
+                        output[xi] = torch.from_numpy(rows[xi, :n].copy())
+                return output
+            return PendingBoxes(finish=finish, keep=(pred, out, both, prediction))
+        except Exception as e:
+            return PendingBoxes(value=e)
 
     def extract_boxes_device(self, pred, conf_thres=0.6, iou_thres=0.45, classes=None, agnostic=False,
                              multi_label=False, labels=(), max_det=300):

@@ -61,7 +61,20 @@ class _ImagePreprocess(Preprocess):
             return self.stager.to_host(dev, "pre_out", copy=copy)
         return self._pipelined_batch(frames, size_hw, mode, swap, pad_value, copy, chunks)
 
-    def _pipelined_batch(self, frames, size_hw, mode, swap, pad_value, copy, chunks):
+    def image_adjust_batch_async(self, frames, size_hw=None, mode="stretch", swap=False, pad_value=114, copy=True, chunks=16):
+        """image_adjust_batch for a pipelined caller: every copy and kernel of the batch is queued and the call returns a
+        handle at once; `.result()` waits and returns the (n,3,H,W) float32 host array. Work queued afterwards on other
+        streams (an extract_boxes_async, the next batch's image_adjust_batch_async) shares the GPU and the PCIe link with
+        it. At most two batches in flight: results alternate between two host buffers."""
+        if size_hw is None:
+            size_hw = tuple(frames.shape[1:3])
+        n = int(frames.shape[0])
+        chunks = min(int(chunks), n // 2)
+        if chunks < 2:
+            return _Ready(self.image_adjust_batch(frames, size_hw, mode, swap, pad_value, copy, chunks))
+        return _Deferred(self._pipelined_batch(frames, size_hw, mode, swap, pad_value, copy, chunks, defer=True))
+
+    def _pipelined_batch(self, frames, size_hw, mode, swap, pad_value, copy, chunks, defer=False):
         eng, st = self.engine, self.stager
         dev = eng.device
         n, h, w, _ = (int(v) for v in frames.shape)
@@ -74,7 +87,10 @@ class _ImagePreprocess(Preprocess):
             pin = st.pinned("pre_in_host", src.numel()).view(n, h, w, 3)
             pin.copy_(src)
             src = pin
-        host_out = st.pinned("pre_out", n * 3 * oh * ow * 4).view(torch.float32).view(n, 3, oh, ow)
+        # deferred calls alternate between two host buffers, so that the next batch can be queued while the caller still
+        # reads the previous result (copy=False views stay valid until the next call but one)
+        self._out_turn = (getattr(self, "_out_turn", 0) + 1) & 1 if defer else 0
+        host_out = st.pinned("pre_out" if self._out_turn == 0 else "pre_out_b", n * 3 * oh * ow * 4).view(torch.float32).view(n, 3, oh, ow)
         if getattr(self, "_streams", None) is None:
             self._streams = (torch.cuda.Stream(dev), torch.cuda.Stream(dev), torch.cuda.Stream(dev))
         s_in, s_cmp, s_out = self._streams
@@ -87,6 +103,9 @@ class _ImagePreprocess(Preprocess):
         cur = torch.cuda.current_stream(dev)
         for s in self._streams:
             s.wait_stream(cur)
+        # a previous deferred call may still be running: its kernels read the input buffers, its downloads the output buffers
+        s_in.wait_stream(s_cmp)
+        s_cmp.wait_stream(s_out)
         ev_cmp, ev_out = [], []
         for k in range(chunks):
             a, b = k * per, min(n, (k + 1) * per)
@@ -114,10 +133,14 @@ class _ImagePreprocess(Preprocess):
                 e_o = torch.cuda.Event()
                 e_o.record(s_out)
                 ev_out.append(e_o)
-        s_out.synchronize()
-        cur.wait_stream(s_cmp)
-        res = host_out.numpy()
-        return res.copy() if copy else res
+        done = ev_out[-1]
+
+        def finish():
+            done.synchronize()             # this call's last download (a later call's work may already be queued behind it)
+            cur.wait_stream(s_cmp)
+            res = host_out.numpy()
+            return res.copy() if copy else res
+        return finish if defer else finish()
 
     def image_adjust_device(self, frames, size_hw, mode="stretch", swap=False, pad_value=114, out=None):
         """Same, result left on the device (torch CUDA tensor) for callers that keep going on the GPU."""
@@ -127,6 +150,25 @@ class _ImagePreprocess(Preprocess):
         src = self.stager.to_device(frames, np.uint8, shape, "pre_in")
         return self.engine.preprocess_images(src, int(size_hw[0]), int(size_hw[1]), mode=mode, swap=swap,
                                              div=self.DIV, pad_value=pad_value, out=out)
+
+
+
+class _Ready:
+    def __init__(self, value):
+        self._value = value
+
+    def result(self):
+        return self._value
+
+
+class _Deferred:
+    def __init__(self, finish):
+        self._finish, self._value = finish, None
+
+    def result(self):
+        if self._finish is not None:
+            self._value, self._finish = self._finish(), None
+        return self._value
 
 
 class Yolov5preprocess(_ImagePreprocess):
