@@ -16,6 +16,7 @@ struct tcb_ctx {
     size_t ws_bytes;
     size_t ws_used;    // bump pointer, reset at the start of every entry point
     long long launches;
+    int pdl;           // launch the hot kernels with programmatic stream serialization (TCB_PDL, default on)
     int* tickets;      // TCB_TICKETS ints behind the workspace, zero between calls: "last CTA of a group" counters that
                        // the kernel using them resets itself, so no per-call memset is needed
     char err[TCB_ERRLEN];
@@ -82,4 +83,24 @@ __device__ __forceinline__ void st_stream_f4(float* p, float4 v) {
                  :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 __device__ __forceinline__ unsigned lane_id() { return threadIdx.x & 31; }
+
+// Programmatic dependent launch. A kernel launched through tcb_launch(pdl = true) may become resident while the kernel
+// before it on the stream is still draining; it must call pdl_enter() before it touches global memory: that lets ITS
+// successor be scheduled early in turn, then waits until the predecessor has completed and its writes are visible.
+// Without the launch attribute both instructions do nothing.
+__device__ __forceinline__ void pdl_enter() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+template <typename... KA, typename... A>
+static inline cudaError_t tcb_launch(bool pdl, void (*kernel)(KA...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, A... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr = {};
+    attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr.val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, KA(args)...);
+}
 #endif

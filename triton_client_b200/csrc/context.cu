@@ -1,6 +1,7 @@
 // Context, error reporting and workspace ownership for libtcb200 (SURVEY.md §8b "error convention").
 #include "common.cuh"
 #include <new>
+#include <stdlib.h>
 
 static thread_local char g_err[TCB_ERRLEN] = "";
 
@@ -33,6 +34,7 @@ int tcb_create(int device, size_t workspace_bytes, tcb_ctx** out) {
     if (!c) return tcb_fail(nullptr, TCB_ERR_ALLOC, "tcb_create: host allocation failed");
     memset(c, 0, sizeof(*c));
     c->device = device;
+    { const char* e2 = getenv("TCB_PDL"); c->pdl = !(e2 && e2[0] == '0'); }
     cudaDeviceGetAttribute(&c->num_sms, cudaDevAttrMultiProcessorCount, device);
     if (c->num_sms <= 0) c->num_sms = 148;
     // one allocation: the caller's workspace, then the self-resetting ticket counters

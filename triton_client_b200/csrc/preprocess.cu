@@ -511,6 +511,7 @@ template <bool AREA, bool EXACT, bool HAS_SUB>
 __global__ void __launch_bounds__(NTHREADS) preprocess2_kernel(const PreParams p, const TileGeo geo) {
     extern __shared__ __align__(16) uint8_t smem[];
     const int tid = threadIdx.x;
+    pdl_enter();
     const int z = blockIdx.z;
     const int tx0 = blockIdx.x * TW, ty0 = blockIdx.y * p.th;
     const uint8_t* img = p.src + (long long)z * p.img_stride;
@@ -828,7 +829,7 @@ extern "C" int tcb_preprocess_image(tcb_ctx* ctx, const uint8_t* src_dev, int n,
         kern2_t kern = two_pass[area ? 1 : 0][p.exact2 ? 1 : 0][has_sub ? 1 : 0];
         if (smem > 48 * 1024)  // opt in to > 48 KB dynamic shared memory
             TCB_CUDA(ctx, cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX));
-        kern<<<grid, NTHREADS, smem, st>>>(p, geo);
+        TCB_CUDA(ctx, tcb_launch(ctx->pdl != 0, kern, grid, dim3(NTHREADS), smem, st, p, geo));
     } else {
         kern1_t kern = one_pass[area ? 1 : 0][p.exact_recip ? 1 : 0];
         kern<<<grid, NTHREADS, smem, st>>>(p);

@@ -170,6 +170,7 @@ __global__ void __launch_bounds__(32 * FS_WARPS) yolo_filter_stream_kernel(
     extern __shared__ __align__(128) unsigned char ys_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int stride = 5 + nc;
+    pdl_enter();
     const int buf_floats = FS_ROWS * stride;                        // FS_ROWS rows: a multiple of 4 floats, 16-byte sized
     unsigned long long* bars = reinterpret_cast<unsigned long long*>(ys_raw);            // [FS_WARPS][FS_NBUF]
     unsigned char* plist = ys_raw + 8 * FS_WARPS * FS_NBUF + warp * FS_ROWS;            // rows of the current chunk that pass objectness
@@ -576,6 +577,7 @@ __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
     CandShared& C = *reinterpret_cast<CandShared*>(smem_raw + sizeof(NmsShared));
 
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    pdl_enter();
 #ifdef TCB_NMS_PROFILE
     long long prof_t0 = clock64();
     const long long prof_start = prof_t0;
@@ -1067,8 +1069,8 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
             if (grid > (long long)ctx->num_sms * per_sm) grid = (long long)ctx->num_sms * per_sm;
             float conf_floor32 = (float)conf_thres;   // objectness test in float32, exactly equivalent to the float64 one
             if ((double)conf_floor32 > conf_thres) conf_floor32 = nextafterf(conf_floor32, -INFINITY);
-            kernel<<<(int)grid, 32 * FS_WARPS, fsm, st>>>(
-                pred_dev, b, n, nc, conf_thres, conf_floor32, n_classes > 0, cm, c_score, c_box, c_meta, chunk_info);
+            TCB_CUDA(ctx, tcb_launch(ctx->pdl != 0, kernel, dim3((unsigned)grid), dim3(32 * FS_WARPS), fsm, st,
+                                     pred_dev, b, n, nc, conf_thres, conf_floor32, (int)(n_classes > 0), cm, c_score, c_box, c_meta, chunk_info));
         } else {
             yolo_filter_kernel<<<dim3(bx, b), 256, 0, st>>>(pred_dev, b, n, nc, conf_thres, n_classes > 0, cm,
                                                             c_score, c_box, c_meta, c_count, xc_count, big);
@@ -1077,9 +1079,9 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
     }
     const size_t smem = NMS_SMEM_BYTES;
     TCB_CUDA(ctx, cudaFuncSetAttribute(yolo_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    yolo_nms_kernel<<<dim3(b, G), NMS_THREADS, smem, st>>>(n > 0 ? n : 1, c_score, c_box, c_meta, c_count, gsort, npad,
-                                                           iou_thres, agnostic ? 0.0 : 4096.0, max_det, max_nms, out_dev, count_dev, go,
-                                                           xc_count, xc_count_dev, chunk_info, chunks, chunk_rows);
+    TCB_CUDA(ctx, tcb_launch(ctx->pdl != 0, yolo_nms_kernel, dim3(b, G), dim3(NMS_THREADS), smem, st, n > 0 ? n : 1, c_score, c_box, c_meta,
+                             c_count, gsort, npad, iou_thres, agnostic ? 0.0 : 4096.0, max_det, max_nms, out_dev, count_dev, go, xc_count,
+                             xc_count_dev, chunk_info, chunks, chunk_rows));
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }
