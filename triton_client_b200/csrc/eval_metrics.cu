@@ -340,20 +340,23 @@ __global__ void __launch_bounds__(EV_T) eval_ap_kernel(ApArgs A) {
                 S.y[tid] = interp_np(x101_at(tid), L, mrec, mpre, S.env[0], S.env[L - 1]);
             }
             __syncthreads();
-            if (tid == 0) {
+            if (tid < 32) {
                 // np.trapz: (d * (y[1:] + y[:-1]) / 2.0).sum() — numpy adds a contiguous float64 vector of 100 with eight
-                // running sums over the first 96 and the last four in order.
-                double r8[8];
-                for (int k = 0; k < 100; k++) {
-                    const double term = (x101_at(k + 1) - x101_at(k)) * (S.y[k + 1] + S.y[k]) / 2.0;
-                    if (k < 8) r8[k] = term;
-                    else if (k < 96) r8[k & 7] = r8[k & 7] + term;
-                    else {
-                        if (k == 96) r8[0] = ((r8[0] + r8[1]) + (r8[2] + r8[3])) + ((r8[4] + r8[5]) + (r8[6] + r8[7]));
-                        r8[0] = r8[0] + term;
-                    }
+                // running sums over the first 96 terms (sum q takes terms q, q+8, ...), combines them pairwise, then adds
+                // the last four in order. Lanes 0-7 are the eight sums.
+                auto term = [&](int k) { return (x101_at(k + 1) - x101_at(k)) * (S.y[k + 1] + S.y[k]) / 2.0; };
+                double acc = 0.0;
+                if (tid < 8) {
+                    acc = term(tid);
+                    for (int k = tid + 8; k < 96; k += 8) acc = acc + term(k);
                 }
-                A.ap[((size_t)f * A.max_classes + ci) * nt + j] = r8[0];
+                acc = acc + __shfl_down_sync(0xffffffffu, acc, 1);      // lanes 0,2,4,6: r0+r1, r2+r3, r4+r5, r6+r7
+                acc = acc + __shfl_down_sync(0xffffffffu, acc, 2);      // lanes 0,4
+                acc = acc + __shfl_down_sync(0xffffffffu, acc, 4);      // lane 0
+                if (tid == 0) {
+                    for (int k = 96; k < 100; k++) acc = acc + term(k);
+                    A.ap[((size_t)f * A.max_classes + ci) * nt + j] = acc;
+                }
             }
             __syncthreads();
         }
