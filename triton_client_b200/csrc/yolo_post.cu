@@ -188,28 +188,40 @@ __global__ void __launch_bounds__(32 * FS_WARPS) yolo_filter_stream_kernel(
     const int nwarps = (int)gridDim.x * FS_WARPS;
     int ch = (int)blockIdx.x * FS_WARPS + warp;
 
-    auto chunk_src = [&](int c, int& b, int& row0, int& nrow) -> const float* {
-        b = c / chunks;
-        row0 = (c - b * chunks) * FS_ROWS;
+    // Chunk c of the stream is chunk (c % chunks) of frame (c / chunks). A warp visits c, c + nwarps, ...: the frame and
+    // the chunk inside it advance by a fixed step with one carry, so the loop has no division (two of them per chunk
+    // were a quarter of this kernel's instructions).
+    const int step_b = nwarps / chunks, step_c = nwarps - step_b * chunks;
+    struct Pos { int b, c; };
+    auto advance = [&](Pos& p) { p.b += step_b; p.c += step_c; if (p.c >= chunks) { p.c -= chunks; p.b++; } };
+    auto chunk_src = [&](const Pos& p, int& row0, int& nrow) -> const float* {
+        row0 = p.c * FS_ROWS;
         nrow = min(FS_ROWS, N - row0);
-        return pred + ((long long)b * N + row0) * stride;
+        return pred + ((long long)p.b * N + row0) * stride;
     };
     auto bulk_ok = [&](const float* src, int nrow) { return ((((uintptr_t)src) | (uintptr_t)(nrow * stride * 4)) & 15) == 0; };
-    auto issue = [&](int c, int slot) {
-        int b, row0, nrow;
-        const float* src = chunk_src(c, b, row0, nrow);
+    auto issue = [&](const Pos& p, int slot) {
+        int row0, nrow;
+        const float* src = chunk_src(p, row0, nrow);
         if (lane == 0 && bulk_ok(src, nrow)) yf_bulk_load(bufs + slot * buf_floats, src, (unsigned)(nrow * stride * 4), bar + slot);
     };
 
+    Pos cur, ahead;                               // the chunk being filtered and the one FS_NBUF - 1 visits further on
+    cur.b = ch / chunks; cur.c = ch - cur.b * chunks;
+    ahead = cur;
 #pragma unroll
-    for (int k = 0; k < FS_NBUF - 1; k++)
-        if (ch + k * nwarps < total) issue(ch + k * nwarps, k);
-    for (int it = 0; ch < total; ch += nwarps, it++) {
+    for (int k = 0; k < FS_NBUF - 1; k++) {
+        if (ch + k * nwarps < total) issue(ahead, k);
+        advance(ahead);
+    }
+    const int lane_off = lane * stride + 4, group_off = 32 * stride;
+    for (int it = 0; ch < total; ch += nwarps, it++, advance(cur), advance(ahead)) {
         const int slot = it % FS_NBUF;
         // refill the buffer filtered in the previous iteration (released by the __syncwarp at the end of it)
-        if (ch + (FS_NBUF - 1) * nwarps < total) issue(ch + (FS_NBUF - 1) * nwarps, (it + FS_NBUF - 1) % FS_NBUF);
-        int b, row0, nrow;
-        const float* src = chunk_src(ch, b, row0, nrow);
+        if (ch + (FS_NBUF - 1) * nwarps < total) issue(ahead, (it + FS_NBUF - 1) % FS_NBUF);
+        const int b = cur.b;
+        int row0, nrow;
+        const float* src = chunk_src(cur, row0, nrow);
         float* rows = bufs + slot * buf_floats;
         if (bulk_ok(src, nrow)) {
             yf_bar_wait(bar + slot, (unsigned)(it / FS_NBUF) & 1u);   // buffer `slot` completes once every FS_NBUF iterations
@@ -225,7 +237,7 @@ __global__ void __launch_bounds__(32 * FS_WARPS) yolo_filter_stream_kernel(
 #pragma unroll
         for (int u = 0; u < FS_ROWS / 32; u++) {
             const int r = u * 32 + lane;
-            const float obj = (r < nrow) ? rows[r * stride + 4] : -1.f;
+            const float obj = (r < nrow) ? rows[lane_off + u * group_off] : -1.f;
             const bool pass = obj > conf_floor32;   // == ((double)obj > conf_thres): conf_floor32 is the largest float <= conf_thres
             const unsigned m = __ballot_sync(0xffffffffu, pass);
             if (pass) plist[n_pass + __popc(m & lt_mask)] = (unsigned char)r;
