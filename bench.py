@@ -258,6 +258,8 @@ def run_gpu(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    from triton_client_b200.shard import bind_to_gpu_numa_node
+    numa = bind_to_gpu_numa_node(local)      # before any pinned buffer is allocated
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -421,7 +423,7 @@ def run_gpu(args):
             "data": "synthetic",
             "config": {"workload": WORKLOAD, "batch_per_gpu": BATCH, "conf_thres": CONF, "iou_thres": IOU, "max_det": MAX_DET,
                        "l2": f"inputs cycle through {RING} distinct batches of 222 MB each (> 126 MB L2); no flush needed",
-                       "parallelism": f"frame stream sharded over {world} rank(s), no data-path collective"},
+                       "parallelism": f"frame stream sharded over {world} rank(s), no data-path collective", "host_numa": numa},
             "kernel_ms": {"preprocess": pre_ms, "yolo_post": post_ms},
             "roofline": {"bound": "hbm", "kernel": "preprocess2_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "peak_source": which + " copy bandwidth (MEASURED_PEAKS.json hbm_gbs)",

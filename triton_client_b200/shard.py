@@ -4,8 +4,38 @@ Frames are independent (communicator/ros_inference.py:117-175 overwrites all per
 partitioned, one process per GPU, with no collective on the data path. The only communication is one gather of
 the per-frame detection counts and padded rows at the end (KBs): torch.distributed all_gather over NCCL on the
 GPU box, gloo in the CPU tests."""
+import os
+
 import torch
 import torch.distributed as dist
+
+
+def bind_to_gpu_numa_node(device_index):
+    """Host side of one process per GPU: run this process (and therefore first-touch its pinned staging buffers) on the
+    NUMA node the GPU hangs off, so that the per-step host<->device copies of every rank stay on their own socket's
+    memory instead of crossing the inter-socket link. Reads /sys (PCI numa_node, node cpulist); does nothing when the
+    box has one node or the files are missing. Returns a dict describing what was done."""
+    info = {"numa_node": None, "cpus": None, "bound": False}
+    try:
+        p = torch.cuda.get_device_properties(device_index)
+        bdf = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        node_path = f"/sys/bus/pci/devices/{str(bdf).lower()}/numa_node"
+        node = int(open(node_path).read().strip())
+        info["numa_node"] = node
+        nodes = [d for d in os.listdir("/sys/devices/system/node") if d.startswith("node") and d[4:].isdigit()]
+        if node < 0 or len(nodes) < 2:
+            return info
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        allowed = cpus & set(os.sched_getaffinity(0))
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+            info["cpus"], info["bound"] = len(allowed), True
+    except Exception as e:      # affinity is an optimisation, never a reason to fail
+        info["error"] = str(e)[:120]
+    return info
 
 
 def shard_frames(n_frames, rank, world, mode="interleave"):
