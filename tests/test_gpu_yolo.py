@@ -83,6 +83,32 @@ def test_score_distributions_of_the_counting_order(engine):
         _same(got, want)
 
 
+def test_random_shapes_against_the_oracle(engine):
+    """Seeded sweep over batch, row count, class count, thresholds, class whitelists and score distributions (the
+    counting order, the sort fallbacks, split and unsplit class groups, bulk and lane-copied chunks all get hit)."""
+    rng = np.random.default_rng(2024)
+    for case in range(24):
+        b = int(rng.integers(1, 6))
+        n = int(rng.choice([17, 128, 333, 1000, 2049, 4097, 6000]))
+        nc = int(rng.choice([1, 2, 3, 7, 20, 80]))
+        objects = int(rng.integers(1, 40))
+        pred = synth.yolo_output(b, n, nc, 9000 + case, objects=objects, rows_per_object=int(rng.integers(1, 60)),
+                                 tie_frac=float(rng.choice([0.0, 0.05, 0.5])))
+        if case % 4 == 1:
+            pred[..., 4] = np.round(pred[..., 4] * 8) / 8            # few distinct objectness values: crowded score buckets
+        if case % 6 == 2:
+            pred[..., 0:2] += 3000.0                                   # boxes beyond +-2048: class groups must not split
+        kw = dict(conf_thres=float(rng.choice([0.05, 0.25, 0.3, 0.6])), iou_thres=float(rng.choice([0.2, 0.45, 0.7])),
+                  agnostic=bool(case % 5 == 3), max_det=int(rng.choice([5, 100, 300, 1000])))
+        if case % 7 == 4 and nc > 2:
+            kw["classes"] = sorted(set(int(c) for c in rng.integers(0, nc, 3)))
+        want = yolo_post.extract_boxes(pred, as_written=False, **kw)
+        if isinstance(want, Exception):
+            continue
+        got, _ = _gpu(engine, pred, **kw)
+        _same(got, want)
+
+
 def test_many_candidates_sorts_in_global_scratch(engine):
     """> 4096 candidates per image: the ordering falls back to global scratch; dense overlapping boxes."""
     rng = np.random.default_rng(8)

@@ -63,6 +63,10 @@ static inline void tcb_ws_reset(tcb_ctx* ctx) { ctx->ws_used = 0; }
             return tcb_fail((ctx), TCB_ERR_CUDA, "%s: launch failed: %s", __func__, cudaGetErrorString(e__)); \
     } while (0)
 
+// Launch `kernel` (which must begin with pdl_enter()) with programmatic stream serialization when the context allows it.
+#define TCB_KLAUNCH(ctx, kernel, grid, block, smem, st, ...)                                             \
+    TCB_CUDA((ctx), tcb_launch((ctx)->pdl != 0, kernel, dim3(grid), dim3(block), (size_t)(smem), (st), __VA_ARGS__))
+
 #define TCB_WS(ctx, ptr, type, count)                                          \
     type* ptr = (type*)tcb_ws_alloc((ctx), sizeof(type) * (size_t)(count));    \
     if (!ptr) return tcb_fail((ctx), TCB_ERR_WORKSPACE, "%s: workspace too small (need > %zu B, have %zu B)", \

@@ -17,6 +17,13 @@
 //                   the zero-padded (P, F) block and the count
 //   decorate      : PillarVFE.forward decoration (OPCD/pcdet/models/backbones_3d/vfe/pillar_vfe.py:94-118)
 #include "common.cuh"
+// Kernels here are launched with programmatic stream serialization (TCB_KLAUNCH): a kernel can be resident before the
+// one that produces its inputs has finished, so inputs must not be read through the non-coherent path (ld.global.nc
+// is only valid for data that is read-only for the kernel's whole lifetime). That is why the const pointer
+// parameters carry no __restrict__ and nothing is read with __ldg: the compiler then emits coherent loads, which
+// griddepcontrol.wait orders. (The point rows themselves can come from tcb_pointcloud2_unpack on the same stream.)
+template <typename T>
+__device__ __forceinline__ T ld_coherent(const T* p) { return *p; }
 #include <limits.h>
 
 namespace {
@@ -35,9 +42,9 @@ struct VoxParams {
 };
 
 __device__ __forceinline__ float cond_feature(const VoxParams& p, const float* row, int j) {
-    float v = __ldg(row + j);
+    float v = ld_coherent(row + j);
     if (j == 2) v = v + p.z_offset;
-    if (j == p.intensity_col) v = v / __ldg(p.intensity_max);
+    if (j == p.intensity_col) v = v / ld_coherent(p.intensity_max);
     return v;
 }
 
@@ -70,6 +77,7 @@ __device__ __forceinline__ unsigned hash_cell(int cell, int H) {
 
 __global__ void __launch_bounds__(256) vox_hash_kernel(const VoxParams p, int* __restrict__ pslot,
                                                        int* __restrict__ hkey, int* __restrict__ hmin, int* __restrict__ hcnt) {
+    pdl_enter();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= p.n) return;
     int cx, cy, cz;
@@ -104,8 +112,9 @@ __device__ __forceinline__ int block_sum(int v, int* sh) {
     return r;
 }
 
-__global__ void __launch_bounds__(VB) vox_count_kernel(int n, const int* __restrict__ pslot, const int* __restrict__ hmin,
+__global__ void __launch_bounds__(VB) vox_count_kernel(int n, const int* pslot, const int* hmin,
                                                        int* __restrict__ blocksum) {
+    pdl_enter();
     __shared__ int sh[32];
     const int i = blockIdx.x * VB + threadIdx.x;
     int first = 0;
@@ -117,6 +126,7 @@ __global__ void __launch_bounds__(VB) vox_count_kernel(int n, const int* __restr
 // exclusive scan of up to 1024*1024 points' block sums by one CTA (nblk <= 4096)
 __global__ void __launch_bounds__(1024) vox_scan_kernel(int nblk, int* __restrict__ blocksum, int max_vox,
                                                         int* __restrict__ scalars, int* __restrict__ m_out) {
+    pdl_enter();
     __shared__ int sh[32];
     __shared__ int carry;
     if (threadIdx.x == 0) carry = 0;
@@ -152,10 +162,11 @@ __global__ void __launch_bounds__(1024) vox_scan_kernel(int nblk, int* __restric
     }
 }
 
-__global__ void __launch_bounds__(VB) vox_assign_kernel(const VoxParams p, const int* __restrict__ pslot, const int* __restrict__ hmin,
-                                                        const int* __restrict__ hcnt, const int* __restrict__ blockoff,
+__global__ void __launch_bounds__(VB) vox_assign_kernel(const VoxParams p, const int* pslot, const int* hmin,
+                                                        const int* hcnt, const int* blockoff,
                                                         int* __restrict__ hvid, int* __restrict__ hseg, int* __restrict__ vslot,
                                                         int* __restrict__ scalars, int* __restrict__ coords) {
+    pdl_enter();
     __shared__ int sh[32];
     const int i = blockIdx.x * VB + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -186,9 +197,10 @@ __global__ void __launch_bounds__(VB) vox_assign_kernel(const VoxParams p, const
     }
 }
 
-__global__ void __launch_bounds__(256) vox_scatter_kernel(const VoxParams p, const int* __restrict__ pslot, const int* __restrict__ hvid,
-                                                          const int* __restrict__ hseg, int* __restrict__ hfill,
-                                                          const int* __restrict__ scalars, int* __restrict__ csr) {
+__global__ void __launch_bounds__(256) vox_scatter_kernel(const VoxParams p, const int* pslot, const int* hvid,
+                                                          const int* hseg, int* __restrict__ hfill,
+                                                          const int* scalars, int* __restrict__ csr) {
+    pdl_enter();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= p.n) return;
     const int s = pslot[i];
@@ -199,9 +211,10 @@ __global__ void __launch_bounds__(256) vox_scatter_kernel(const VoxParams p, con
 }
 
 // One warp per voxel: keep the max_pts smallest point indices of the segment, in ascending order.
-__global__ void __launch_bounds__(256) vox_gather_kernel(const VoxParams p, const int* __restrict__ m_dev, const int* __restrict__ vslot,
-                                                         const int* __restrict__ hseg, const int* __restrict__ hfill,
-                                                         const int* __restrict__ csr, float* __restrict__ voxels, int* __restrict__ num_pts) {
+__global__ void __launch_bounds__(256) vox_gather_kernel(const VoxParams p, const int* m_dev, const int* vslot,
+                                                         const int* hseg, const int* hfill,
+                                                         const int* csr, float* __restrict__ voxels, int* __restrict__ num_pts) {
+    pdl_enter();
     const int lane = threadIdx.x & 31;
     const int v = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (v >= *m_dev) return;
@@ -253,9 +266,10 @@ __global__ void __launch_bounds__(256) vox_gather_kernel(const VoxParams p, cons
 }
 
 // per-frame max of one feature column (b1: intensity /= max(intensity)); values assumed finite
-__global__ void __launch_bounds__(256) vox_colmax_kernel(const float* __restrict__ pts, int n, int stride, int col, float* __restrict__ out) {
+__global__ void __launch_bounds__(256) vox_colmax_kernel(const float* pts, int n, int stride, int col, float* __restrict__ out) {
+    pdl_enter();
     float m = -INFINITY;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) m = fmaxf(m, __ldg(pts + (long long)i * stride + col));
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) m = fmaxf(m, ld_coherent(pts + (long long)i * stride + col));
 #pragma unroll
     for (int s = 16; s > 0; s >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, s));
     if ((threadIdx.x & 31) == 0) {
@@ -265,14 +279,18 @@ __global__ void __launch_bounds__(256) vox_colmax_kernel(const float* __restrict
     }
 }
 
-__global__ void vox_init_max_kernel(float* out) { *out = -INFINITY; }
+__global__ void vox_init_max_kernel(float* out) {
+    pdl_enter();
+    *out = -INFINITY;
+}
 
 // ---- pillar decoration ---------------------------------------------------------------------------
 // out[v, s, :] = mask * [feat(F), xyz - mean(3), xyz - pillar centre(3)]      (pillar_vfe.py:94-118)
-__global__ void __launch_bounds__(256) pillar_decorate_kernel(const float* __restrict__ voxels, const int* __restrict__ coords,
-                                                              const int* __restrict__ num_pts, const int* __restrict__ m_dev, int m_host,
+__global__ void __launch_bounds__(256) pillar_decorate_kernel(const float* voxels, const int* coords,
+                                                              const int* num_pts, const int* m_dev, int m_host,
                                                               int P, int F, float vx, float vy, float vz, float xo, float yo, float zo,
                                                               float* __restrict__ out) {
+    pdl_enter();
     const int lane = threadIdx.x & 31;
     const int v = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int M = m_dev ? *m_dev : m_host;
@@ -314,12 +332,13 @@ struct DynParams {
 
 __global__ void __launch_bounds__(256) dyn_mark_kernel(const DynParams p, int* __restrict__ valid, int* __restrict__ pkey,
                                                        int* __restrict__ mark, double* __restrict__ sums, int* __restrict__ cnt) {
+    pdl_enter();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= p.n) return;
     const float* row = p.pts + (long long)i * p.ncol;
-    const float x = __ldg(row + 1), y = __ldg(row + 2), z = __ldg(row + 3);
+    const float x = ld_coherent(row + 1), y = ld_coherent(row + 2), z = ld_coherent(row + 3);
     const float fx = floorf((x - p.r0x) / p.vx), fy = floorf((y - p.r0y) / p.vy);
-    const int b = (int)__ldg(row);
+    const int b = (int)ld_coherent(row);
     const bool ok = fx >= 0.f && fx < (float)p.gx && fy >= 0.f && fy < (float)p.gy && b >= 0 && b < p.batch;
     valid[i] = ok ? 1 : 0;
     if (!ok) { pkey[i] = -1; return; }
@@ -331,7 +350,8 @@ __global__ void __launch_bounds__(256) dyn_mark_kernel(const DynParams p, int* _
 }
 
 // block-local exclusive scan of 0/1 flags + per-block totals; offsets are added by the consumers
-__global__ void __launch_bounds__(VB) scan_local_kernel(const int* __restrict__ flags, int n, int* __restrict__ pos, int* __restrict__ blocksum) {
+__global__ void __launch_bounds__(VB) scan_local_kernel(const int* flags, int n, int* __restrict__ pos, int* __restrict__ blocksum) {
+    pdl_enter();
     __shared__ int sh[32];
     const int i = blockIdx.x * VB + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -351,6 +371,7 @@ __global__ void __launch_bounds__(VB) scan_local_kernel(const int* __restrict__ 
 }
 
 __global__ void __launch_bounds__(1024) scan_blocks_kernel(int nblk, int* __restrict__ blocksum, int* __restrict__ total_out) {
+    pdl_enter();
     __shared__ int sh[32];
     __shared__ int carry;
     if (threadIdx.x == 0) carry = 0;
@@ -380,11 +401,12 @@ __global__ void __launch_bounds__(1024) scan_blocks_kernel(int nblk, int* __rest
     if (threadIdx.x == 0) *total_out = carry;
 }
 
-__global__ void __launch_bounds__(256) dyn_features_kernel(const DynParams p, const int* __restrict__ valid, const int* __restrict__ pkey,
-                                                           const int* __restrict__ ppos, const int* __restrict__ pblk,
-                                                           const int* __restrict__ crank, const int* __restrict__ cblk,
-                                                           const double* __restrict__ sums, const int* __restrict__ cnt,
+__global__ void __launch_bounds__(256) dyn_features_kernel(const DynParams p, const int* valid, const int* pkey,
+                                                           const int* ppos, const int* pblk,
+                                                           const int* crank, const int* cblk,
+                                                           const double* sums, const int* cnt,
                                                            float* __restrict__ feats, long long* __restrict__ unq_inv) {
+    pdl_enter();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= p.n || !valid[i]) return;
     const int key = pkey[i];
@@ -393,12 +415,12 @@ __global__ void __launch_bounds__(256) dyn_features_kernel(const DynParams p, co
     const float* row = p.pts + (long long)i * p.ncol;
     const int F = p.ncol - 1;
     float* out = feats + o * (F + 6);
-    const float x = __ldg(row + 1), y = __ldg(row + 2), z = __ldg(row + 3);
+    const float x = ld_coherent(row + 1), y = ld_coherent(row + 2), z = ld_coherent(row + 3);
     const float fc = (float)cnt[key];
     const float mx = (float)sums[3ll * key] / fc, my = (float)sums[3ll * key + 1] / fc, mz = (float)sums[3ll * key + 2] / fc;
     const int within = key % (p.gx * p.gy);
     const int cx = within / p.gy, cy = within - cx * p.gy;
-    for (int j = 0; j < F; j++) out[j] = __ldg(row + 1 + j);
+    for (int j = 0; j < F; j++) out[j] = ld_coherent(row + 1 + j);
     out[F] = x - mx; out[F + 1] = y - my; out[F + 2] = z - mz;
     out[F + 3] = x - ((float)cx * p.vx + p.xo);
     out[F + 4] = y - ((float)cy * p.vy + p.yo);
@@ -406,8 +428,9 @@ __global__ void __launch_bounds__(256) dyn_features_kernel(const DynParams p, co
     unq_inv[o] = (long long)u;
 }
 
-__global__ void __launch_bounds__(256) dyn_coords_kernel(int cells, int gx, int gy, const int* __restrict__ mark, const int* __restrict__ crank,
-                                                         const int* __restrict__ cblk, int* __restrict__ coords) {
+__global__ void __launch_bounds__(256) dyn_coords_kernel(int cells, int gx, int gy, const int* mark, const int* crank,
+                                                         const int* cblk, int* __restrict__ coords) {
+    pdl_enter();
     const int key = blockIdx.x * blockDim.x + threadIdx.x;
     if (key >= cells || !mark[key]) return;
     const int u = crank[key] + cblk[key / VB];
@@ -460,15 +483,17 @@ __device__ __forceinline__ bool pc2_decode(const Pc2Params& p, int i, float* v) 
 }
 
 __global__ void __launch_bounds__(256) pc2_flags_kernel(const Pc2Params p, int n, int* __restrict__ flags) {
+    pdl_enter();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float v[PC2_MAX_FIELDS];
     flags[i] = pc2_decode(p, i, v) ? 1 : 0;
 }
 
-__global__ void __launch_bounds__(256) pc2_scatter_kernel(const Pc2Params p, int n, const int* __restrict__ flags, const int* __restrict__ pos,
-                                                          const int* __restrict__ blockoff, const int* __restrict__ count,
+__global__ void __launch_bounds__(256) pc2_scatter_kernel(const Pc2Params p, int n, const int* flags, const int* pos,
+                                                          const int* blockoff, const int* count,
                                                           float* __restrict__ out) {
+    pdl_enter();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     if (flags[i]) {
@@ -487,10 +512,11 @@ __global__ void __launch_bounds__(256) pc2_scatter_kernel(const Pc2Params p, int
 // indices with labels == label_sel and scores > score_thresh, ascending; per box position (z - offset), the
 // quaternion of a yaw about z as pyquaternion builds it (w = cos(yaw/2), x = 0*s, y = 0*s, z = s = sin(yaw/2), in
 // float64 from the float32 yaw), dimensions with x and y swapped, score, label.
-__global__ void __launch_bounds__(1024) jsk_boxes_kernel(const float* __restrict__ boxes, const float* __restrict__ scores,
+__global__ void __launch_bounds__(1024) jsk_boxes_kernel(const float* boxes, const float* scores,
                                                          const long long* __restrict__ labels, int n, long long label_sel, float score_thresh,
                                                          double z_offset, double* __restrict__ out, int* __restrict__ out_idx,
                                                          int* __restrict__ out_count) {
+    pdl_enter();
     __shared__ int warp_tot[32];
     __shared__ int carry;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -589,27 +615,27 @@ extern "C" int tcb_voxelize(tcb_ctx* ctx, const float* pts_dev, int n, int pt_st
     TCB_CUDA(ctx, cudaMemsetAsync(hmin, 0x7f, (size_t)p.H * 4, st));
     TCB_CUDA(ctx, cudaMemsetAsync(hcnt, 0, (size_t)p.H * 8, st));
     if (intensity_col >= 0 && n > 0) {
-        vox_init_max_kernel<<<1, 1, 0, st>>>(imax);
+        TCB_KLAUNCH(ctx, vox_init_max_kernel, 1, 1, 0, st, imax);
         TCB_LAUNCHED(ctx);
-        vox_colmax_kernel<<<ctx->num_sms * 2, 256, 0, st>>>(pts_dev, n, pt_stride, intensity_col, imax);
+        TCB_KLAUNCH(ctx, vox_colmax_kernel, ctx->num_sms * 2, 256, 0, st, pts_dev, n, pt_stride, intensity_col, imax);
         TCB_LAUNCHED(ctx);
     }
     if (n > 0) {
-        vox_hash_kernel<<<tcb_div_up(n, 256), 256, 0, st>>>(p, pslot, hkey, hmin, hcnt);
+        TCB_KLAUNCH(ctx, vox_hash_kernel, tcb_div_up(n, 256), 256, 0, st, p, pslot, hkey, hmin, hcnt);
         TCB_LAUNCHED(ctx);
-        vox_count_kernel<<<nblk, VB, 0, st>>>(n, pslot, hmin, blocksum);
+        TCB_KLAUNCH(ctx, vox_count_kernel, nblk, VB, 0, st, n, pslot, hmin, blocksum);
         TCB_LAUNCHED(ctx);
     } else {
         TCB_CUDA(ctx, cudaMemsetAsync(blocksum, 0, sizeof(int) * (nblk + 1), st));
     }
-    vox_scan_kernel<<<1, 1024, 0, st>>>(nblk, blocksum, max_vox, scalars, m_out_dev);
+    TCB_KLAUNCH(ctx, vox_scan_kernel, 1, 1024, 0, st, nblk, blocksum, max_vox, scalars, m_out_dev);
     TCB_LAUNCHED(ctx);
     if (n > 0) {
-        vox_assign_kernel<<<nblk, VB, 0, st>>>(p, pslot, hmin, hcnt, blocksum, hvid, hseg, vslot, scalars, coords_dev);
+        TCB_KLAUNCH(ctx, vox_assign_kernel, nblk, VB, 0, st, p, pslot, hmin, hcnt, blocksum, hvid, hseg, vslot, scalars, coords_dev);
         TCB_LAUNCHED(ctx);
-        vox_scatter_kernel<<<tcb_div_up(n, 256), 256, 0, st>>>(p, pslot, hvid, hseg, hfill, scalars, csr);
+        TCB_KLAUNCH(ctx, vox_scatter_kernel, tcb_div_up(n, 256), 256, 0, st, p, pslot, hvid, hseg, hfill, scalars, csr);
         TCB_LAUNCHED(ctx);
-        vox_gather_kernel<<<tcb_div_up((long long)max_vox * 32, 256), 256, 0, st>>>(p, m_out_dev, vslot, hseg, hfill, csr, voxels_dev, num_pts_dev);
+        TCB_KLAUNCH(ctx, vox_gather_kernel, tcb_div_up((long long)max_vox * 32, 256), 256, 0, st, p, m_out_dev, vslot, hseg, hfill, csr, voxels_dev, num_pts_dev);
         TCB_LAUNCHED(ctx);
     }
     return TCB_OK;
@@ -625,7 +651,7 @@ extern "C" int tcb_pillar_decorate(tcb_ctx* ctx, const float* voxels_dev, const 
     // offsets exactly as PillarVFE.__init__ computes them (pillar_vfe.py:76-81): Python doubles, used as f32 scalars
     const float vx = (float)vsize[0], vy = (float)vsize[1], vz = (float)vsize[2];
     const float xo = (float)(vsize[0] / 2 + range_min[0]), yo = (float)(vsize[1] / 2 + range_min[1]), zo = (float)(vsize[2] / 2 + range_min[2]);
-    pillar_decorate_kernel<<<tcb_div_up((long long)m_max * 32, 256), 256, 0, (cudaStream_t)stream>>>(
+    TCB_KLAUNCH(ctx, pillar_decorate_kernel, tcb_div_up((long long)m_max * 32, 256), 256, 0, (cudaStream_t)stream, 
         voxels_dev, coords_dev, num_pts_dev, m_dev, m_max, max_pts, nfeat, vx, vy, vz, xo, yo, zo, out_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
@@ -671,22 +697,22 @@ extern "C" int tcb_dynamic_pillar(tcb_ctx* ctx, const float* pts_dev, int n, int
     TCB_CUDA(ctx, cudaMemsetAsync(sums, 0, sizeof(double) * cells * 3, st));
     TCB_CUDA(ctx, cudaMemsetAsync(valid, 0, sizeof(int) * nn, st));
     if (n > 0) {
-        dyn_mark_kernel<<<tcb_div_up(n, 256), 256, 0, st>>>(p, valid, pkey, mark, sums, cnt);
+        TCB_KLAUNCH(ctx, dyn_mark_kernel, tcb_div_up(n, 256), 256, 0, st, p, valid, pkey, mark, sums, cnt);
         TCB_LAUNCHED(ctx);
     }
-    scan_local_kernel<<<pb, VB, 0, st>>>(valid, n, ppos, pblk);
+    TCB_KLAUNCH(ctx, scan_local_kernel, pb, VB, 0, st, valid, n, ppos, pblk);
     TCB_LAUNCHED(ctx);
-    scan_blocks_kernel<<<1, 1024, 0, st>>>(pb, pblk, counts_dev);
+    TCB_KLAUNCH(ctx, scan_blocks_kernel, 1, 1024, 0, st, pb, pblk, counts_dev);
     TCB_LAUNCHED(ctx);
-    scan_local_kernel<<<cb, VB, 0, st>>>(mark, (int)cells, crank, cblk);
+    TCB_KLAUNCH(ctx, scan_local_kernel, cb, VB, 0, st, mark, (int)cells, crank, cblk);
     TCB_LAUNCHED(ctx);
-    scan_blocks_kernel<<<1, 1024, 0, st>>>(cb, cblk, counts_dev + 1);
+    TCB_KLAUNCH(ctx, scan_blocks_kernel, 1, 1024, 0, st, cb, cblk, counts_dev + 1);
     TCB_LAUNCHED(ctx);
     if (n > 0) {
-        dyn_features_kernel<<<tcb_div_up(n, 256), 256, 0, st>>>(p, valid, pkey, ppos, pblk, crank, cblk, sums, cnt, feats_dev, unq_inv_dev);
+        TCB_KLAUNCH(ctx, dyn_features_kernel, tcb_div_up(n, 256), 256, 0, st, p, valid, pkey, ppos, pblk, crank, cblk, sums, cnt, feats_dev, unq_inv_dev);
         TCB_LAUNCHED(ctx);
     }
-    dyn_coords_kernel<<<tcb_div_up(cells, 256), 256, 0, st>>>((int)cells, p.gx, p.gy, mark, crank, cblk, voxel_coords_dev);
+    TCB_KLAUNCH(ctx, dyn_coords_kernel, tcb_div_up(cells, 256), 256, 0, st, (int)cells, p.gx, p.gy, mark, crank, cblk, voxel_coords_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }
@@ -728,13 +754,13 @@ extern "C" int tcb_pointcloud2_unpack(tcb_ctx* ctx, const unsigned char* data_de
     TCB_WS(ctx, flags, int, n);
     TCB_WS(ctx, pos, int, n);
     TCB_WS(ctx, blk, int, nb + 1);
-    pc2_flags_kernel<<<tcb_div_up(n, 256), 256, 0, st>>>(p, (int)n, flags);
+    TCB_KLAUNCH(ctx, pc2_flags_kernel, tcb_div_up(n, 256), 256, 0, st, p, (int)n, flags);
     TCB_LAUNCHED(ctx);
-    scan_local_kernel<<<nb, VB, 0, st>>>(flags, (int)n, pos, blk);
+    TCB_KLAUNCH(ctx, scan_local_kernel, nb, VB, 0, st, flags, (int)n, pos, blk);
     TCB_LAUNCHED(ctx);
-    scan_blocks_kernel<<<1, 1024, 0, st>>>(nb, blk, count_dev);
+    TCB_KLAUNCH(ctx, scan_blocks_kernel, 1, 1024, 0, st, nb, blk, count_dev);
     TCB_LAUNCHED(ctx);
-    pc2_scatter_kernel<<<tcb_div_up(n, 256), 256, 0, st>>>(p, (int)n, flags, pos, blk, count_dev, out_dev);
+    TCB_KLAUNCH(ctx, pc2_scatter_kernel, tcb_div_up(n, 256), 256, 0, st, p, (int)n, flags, pos, blk, count_dev, out_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }
@@ -745,8 +771,9 @@ extern "C" int tcb_boxes_to_jsk(tcb_ctx* ctx, const float* boxes_dev, const floa
     TCB_CHECK_CTX(ctx);
     TCB_REQUIRE(ctx, n >= 0 && out_count_dev, "tcb_boxes_to_jsk: bad arguments");
     TCB_REQUIRE(ctx, n == 0 || (boxes_dev && scores_dev && labels_dev && out_dev && out_idx_dev), "tcb_boxes_to_jsk: null buffer");
-    jsk_boxes_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(boxes_dev, scores_dev, labels_dev, n, label_sel, score_thresh, z_offset, out_dev,
-                                                          out_idx_dev, out_count_dev);
+    // plain launch: its inputs come from kernels of other files, and the compiler reads them through the non-coherent path
+    TCB_CUDA(ctx, tcb_launch(false, jsk_boxes_kernel, dim3(1), dim3(1024), 0, (cudaStream_t)stream, boxes_dev, scores_dev, labels_dev, n, label_sel, score_thresh, z_offset, out_dev,
+                                                          out_idx_dev, out_count_dev));
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }

@@ -577,11 +577,13 @@ struct GroupOut {
 };
 
 __global__ void __launch_bounds__(NMS_THREADS, 1) yolo_nms_kernel(
-    int N, const double* __restrict__ c_score, const float4* __restrict__ c_box, const int2* __restrict__ c_meta,
-    const int* __restrict__ c_count, SortEnt* __restrict__ gsort, int gsort_stride,
+    // (no __restrict__ on the filter's outputs: this kernel can be resident before the filter has finished, and the
+    //  non-coherent loads the qualifier allows are only valid for data that never changes during a kernel's lifetime)
+    int N, const double* c_score, const float4* c_box, const int2* c_meta,
+    const int* c_count, SortEnt* __restrict__ gsort, int gsort_stride,
     double iou_thres, double class_offset, int max_det, int max_nms,
     double* __restrict__ out, int* __restrict__ out_count, const GroupOut go,
-    const int* __restrict__ xc_count, int* __restrict__ xc_out, const int2* __restrict__ chunk_info, int chunks, int chunk_rows) {
+    const int* xc_count, int* __restrict__ xc_out, const int2* chunk_info, int chunks, int chunk_rows) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     NmsShared& S = *reinterpret_cast<NmsShared*>(smem_raw);
     unsigned long long* skeys = reinterpret_cast<unsigned long long*>(smem_raw + sizeof(NmsShared));
