@@ -96,6 +96,9 @@ __device__ __forceinline__ void pdl_enter() {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
 }
+// What kernels launched with the attribute use where they would otherwise write __ldg(p): a plain, coherent load.
+template <typename T>
+__device__ __forceinline__ T ld_coherent(const T* p) { return *p; }
 template <typename... KA, typename... A>
 static inline cudaError_t tcb_launch(bool pdl, void (*kernel)(KA...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, A... args) {
     cudaLaunchConfig_t cfg = {};

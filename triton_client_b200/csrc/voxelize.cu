@@ -22,8 +22,6 @@
 // is only valid for data that is read-only for the kernel's whole lifetime). That is why the const pointer
 // parameters carry no __restrict__ and nothing is read with __ldg: the compiler then emits coherent loads, which
 // griddepcontrol.wait orders. (The point rows themselves can come from tcb_pointcloud2_unpack on the same stream.)
-template <typename T>
-__device__ __forceinline__ T ld_coherent(const T* p) { return *p; }
 #include <limits.h>
 
 namespace {
