@@ -53,3 +53,14 @@ def test_gather_single_process():
     rows = torch.arange(12, dtype=torch.float64).view(2, 2, 3)
     out_r, out_c = shard.gather_detections(rows, torch.tensor([1, 2], dtype=torch.int32), [2, 0], 3)
     assert out_c.tolist() == [2, 0, 1] and torch.equal(out_r[2], rows[0])
+
+
+def test_bind_to_gpu_numa_node_never_raises():
+    """Affinity is an optimisation: without a GPU (or on a one-node box) the call reports and changes nothing."""
+    import os
+    from triton_client_b200.shard import bind_to_gpu_numa_node
+    before = os.sched_getaffinity(0)
+    info = bind_to_gpu_numa_node(0)
+    assert set(info) >= {"numa_node", "cpus", "bound"} and info["bound"] in (False, True)
+    if not info["bound"]:
+        assert os.sched_getaffinity(0) == before

@@ -167,6 +167,7 @@ struct ApShared {
     double f1sum[EV_NPX];
     double ucls[EV_MAX_CLASSES];
     double y[104];
+    double yw[EV_NT][104];                // interpolated envelope per threshold (one warp per threshold)
     u64 wtot[51];
     int sidx[EV_MAX];
     int ucount[EV_MAX_CLASSES];
@@ -314,7 +315,52 @@ __global__ void __launch_bounds__(EV_T) eval_ap_kernel(ApArgs A) {
             S.f1sum[t] = S.f1sum[t] + 2 * pv * rv / (pv + rv + 1e-16);       // f1.mean(0) adds the class rows in order
         }
         const int L = n_p + 2;
-        for (int j = 0; j < nt; j++) {
+        // Short curves (the usual case: a few dozen predictions per class and frame): the envelopes of all thresholds fit
+        // side by side, so warp j does threshold j on its own — suffix maximum by lane chunks + one shuffle scan (max is
+        // exact in any order), the 101 interpolated points, the pairwise trapezoid sum — with no CTA barrier in between.
+        const bool side_by_side = nt * L <= EV_MAX + 8;
+        if (side_by_side) {
+            const int wj = tid >> 5, lane = tid & 31;
+            if (wj < nt) {
+                const unsigned short* tpc = S.ctp[wj];
+                double* env = S.env + wj * L;
+                double* y = S.yw[wj];
+                for (int k = lane; k < L; k += 32) env[k] = k == 0 ? 1.0 : (k == L - 1 ? 0.0 : (double)tpc[k - 1] / (double)k);
+                __syncwarp();
+                const int C = (L + 31) / 32, a = lane * C, b = min(L, a + C);
+                double m = -INFINITY;
+                for (int k = b - 1; k >= a; k--) { m = fmax(m, env[k]); env[k] = m; }
+                double sfx = m;                                        // maximum over this lane's chunk and all later ones
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const double t = __shfl_down_sync(0xffffffffu, sfx, o);
+                    if (lane + o < 32) sfx = fmax(sfx, t);
+                }
+                double later = __shfl_down_sync(0xffffffffu, sfx, 1);
+                if (lane == 31) later = -INFINITY;
+                for (int k = a; k < b; k++) env[k] = fmax(env[k], later);
+                __syncwarp();
+                const MrecAt mrec{tpc, denom, L - 1};
+                const ArrayAt mpre{env};
+                for (int t = lane; t < 101; t += 32) y[t] = interp_np(x101_at(t), L, mrec, mpre, env[0], env[L - 1]);
+                __syncwarp();
+                auto term = [&](int k) { return (x101_at(k + 1) - x101_at(k)) * (y[k + 1] + y[k]) / 2.0; };
+                double acc = 0.0;
+                if (lane < 8) {
+                    acc = term(lane);
+                    for (int k = lane + 8; k < 96; k += 8) acc = acc + term(k);
+                }
+                acc = acc + __shfl_down_sync(0xffffffffu, acc, 1);
+                acc = acc + __shfl_down_sync(0xffffffffu, acc, 2);
+                acc = acc + __shfl_down_sync(0xffffffffu, acc, 4);
+                if (lane == 0) {
+                    for (int k = 96; k < 100; k++) acc = acc + term(k);
+                    A.ap[((size_t)f * A.max_classes + ci) * nt + wj] = acc;
+                }
+            }
+            __syncthreads();
+        }
+        for (int j = 0; j < (side_by_side ? 0 : nt); j++) {
             const unsigned short* tpc = S.ctp[j];
             // mpre = [1, precision.., 0], then the running maximum from the right (:143-148)
             for (int k = tid; k < L; k += EV_T) S.env[k] = k == 0 ? 1.0 : (k == L - 1 ? 0.0 : (double)tpc[k - 1] / (double)k);
