@@ -99,6 +99,10 @@ __device__ __forceinline__ void pdl_enter() {
 // What kernels launched with the attribute use where they would otherwise write __ldg(p): a plain, coherent load.
 template <typename T>
 __device__ __forceinline__ T ld_coherent(const T* p) { return *p; }
+// The cautious form: no early trigger, so this kernel's successor is scheduled only when every CTA here has exited (the
+// implicit trigger) — nothing of this kernel can still be loading when the successor becomes resident, and kernels that
+// read their inputs through the non-coherent path stay correct. What is saved is the successor's launch latency.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 template <typename... KA, typename... A>
 static inline cudaError_t tcb_launch(bool pdl, void (*kernel)(KA...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, A... args) {
     cudaLaunchConfig_t cfg = {};

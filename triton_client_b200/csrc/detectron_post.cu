@@ -37,6 +37,7 @@ struct DetParams {
 constexpr int DC_Q = 4;                                   // 16-byte loads per thread
 constexpr int DC_SPAN = 256 * 4 * DC_Q;                   // logits per CTA
 __global__ void __launch_bounds__(256) det_candidates_kernel(const DetParams p, float logit_floor) {
+    pdl_wait();
     const Level& L = p.lv[blockIdx.z];
     const int HW = L.H * L.W;
     if ((int)blockIdx.x * DC_SPAN >= HW) return;  // (whole CTA)
@@ -128,6 +129,7 @@ struct DLevelShared {
 };
 __global__ void __launch_bounds__(T, 1) det_level_kernel(const DetParams p, float4* __restrict__ mbox, float* __restrict__ mscore,
                                                          int* __restrict__ mcls, unsigned long long* __restrict__ mkeys) {
+    pdl_wait();
     __shared__ DLevelShared S;
     extern __shared__ __align__(16) unsigned long long key_cache[];
     const int tid = threadIdx.x, l = blockIdx.x;
@@ -177,6 +179,7 @@ __global__ void __launch_bounds__(T, 1) det_post_kernel(const DetParams p, float
                                                         int* __restrict__ mcls, unsigned long long* __restrict__ mkeys,
                                                         float* __restrict__ out_boxes, float* __restrict__ out_scores,
                                                         long long* __restrict__ out_classes, int* __restrict__ out_count) {
+    pdl_wait();
     extern __shared__ __align__(16) unsigned char smem_raw[];
     DFrameShared& S = *reinterpret_cast<DFrameShared*>(smem_raw);
     const int tid = threadIdx.x;
@@ -277,14 +280,14 @@ extern "C" int tcb_detectron_post(tcb_ctx* ctx, int num_levels, const float* con
         int hw_max = 1;
         for (int l = 0; l < num_levels; l++) hw_max = hw_max > p.lv[l].H * p.lv[l].W ? hw_max : p.lv[l].H * p.lv[l].W;
         TCB_REQUIRE(ctx, num_anchors * num_classes <= 65535, "tcb_detectron_post: more than 65535 channels");
-        det_candidates_kernel<<<dim3(tcb_div_up(hw_max, DC_SPAN), num_anchors * num_classes, num_levels), 256, 0, st>>>(p, logit_floor);
+        TCB_KLAUNCH(ctx, det_candidates_kernel, dim3(tcb_div_up(hw_max, DC_SPAN), num_anchors * num_classes, num_levels), 256, 0, st, p, logit_floor);
         TCB_LAUNCHED(ctx);
     }
     TCB_CUDA(ctx, cudaFuncSetAttribute(det_level_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DET_CACHE * 8));
-    det_level_kernel<<<num_levels, T, DET_CACHE * 8, st>>>(p, mbox, mscore, mcls, mkeys);
+    TCB_KLAUNCH(ctx, det_level_kernel, num_levels, T, DET_CACHE * 8, st, p, mbox, mscore, mcls, mkeys);
     TCB_LAUNCHED(ctx);
     TCB_CUDA(ctx, cudaFuncSetAttribute(det_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DFrameShared)));
-    det_post_kernel<<<1, T, sizeof(DFrameShared), st>>>(p, mbox, mscore, mcls, mkeys, out_boxes_dev, out_scores_dev, out_classes_dev, out_count_dev);
+    TCB_KLAUNCH(ctx, det_post_kernel, 1, T, sizeof(DFrameShared), st, p, mbox, mscore, mcls, mkeys, out_boxes_dev, out_scores_dev, out_classes_dev, out_count_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }

@@ -27,6 +27,7 @@ __constant__ float c_iouv[EV_NT] = {(float)0.5, (float)0.55, (float)0.6, (float)
 __global__ void __launch_bounds__(256) eval_match_kernel(const double* __restrict__ gts, const int* __restrict__ goff,
                                                          const double* __restrict__ preds, const int* __restrict__ poff,
                                                          unsigned char* __restrict__ correct, int* __restrict__ matched) {
+    pdl_wait();
     __shared__ int s_best[EV_MAX];
     __shared__ double s_iou[EV_MAX];
     __shared__ int s_first[EV_MAX];
@@ -182,6 +183,7 @@ __device__ __forceinline__ double px_at(int t) { return t == EV_NPX - 1 ? 1.0 : 
 __device__ __forceinline__ double x101_at(int t) { return t == 100 ? 1.0 : (double)t * (1.0 / 100); }                 // np.linspace(0, 1, 101)
 
 __global__ void __launch_bounds__(EV_T) eval_ap_kernel(ApArgs A) {
+    pdl_wait();
     extern __shared__ __align__(16) unsigned char smem_raw[];
     ApShared& S = *reinterpret_cast<ApShared*>(smem_raw);
     const int f = blockIdx.x, tid = threadIdx.x;
@@ -458,7 +460,7 @@ static int check_offsets(tcb_ctx* ctx, const char* who, const int* off, int fram
 
 static int launch_match(tcb_ctx* ctx, const double* gts, const int* goff_dev, const double* preds, const int* poff_dev, int frames,
                         unsigned char* correct, int* matched, cudaStream_t st) {
-    eval_match_kernel<<<frames, 256, 0, st>>>(gts, goff_dev, preds, poff_dev, correct, matched);
+    TCB_KLAUNCH(ctx, eval_match_kernel, frames, 256, 0, st, gts, goff_dev, preds, poff_dev, correct, matched);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }
@@ -469,7 +471,7 @@ static int launch_ap(tcb_ctx* ctx, ApArgs& a, int frames, cudaStream_t st) {
         TCB_CUDA(ctx, cudaFuncSetAttribute(eval_ap_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ApShared)));
         opted[ctx->device & 63] = true;
     }
-    eval_ap_kernel<<<frames, EV_T, sizeof(ApShared), st>>>(a);
+    TCB_KLAUNCH(ctx, eval_ap_kernel, frames, EV_T, sizeof(ApShared), st, a);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }

@@ -24,6 +24,7 @@ constexpr int POST_CAP = 1024;      // NMS_POST_MAXSIZE limit
 // ---------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) rotated_iou_kernel(const float* __restrict__ a, int n, const float* __restrict__ b, int m,
                                                           float* __restrict__ out) {
+    pdl_wait();
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (long long)n * m) return;
     const int ia = (int)(i / m), ib = (int)(i - (long long)ia * m);
@@ -66,6 +67,7 @@ static_assert(sizeof(FrameShared) <= 227 * 1024, "FrameShared exceeds the 227 KB
 __global__ void __launch_bounds__(T, 1) rotated_nms_kernel(const float* __restrict__ boxes, const float* __restrict__ scores, int n,
                                                            float thresh, int pre_max, int post_max,
                                                            int* __restrict__ keep, int* __restrict__ count) {
+    pdl_wait();
     extern __shared__ __align__(16) unsigned char smem_raw[];
     FrameShared& S = *reinterpret_cast<FrameShared*>(smem_raw);
     auto key_of = [&](int i) { return sel::make_key(__ldg(scores + i), (unsigned)i); };
@@ -106,6 +108,7 @@ struct OrderShared {
 // m_dev[0] = number of candidates, m_dev[1] = pairs listed so far (zeroed by the order kernel).
 __global__ void __launch_bounds__(MASK_T) rot_mask_kernel(const rot::RBox* __restrict__ R, int* __restrict__ m_dev, float thresh,
                                                           unsigned long long* __restrict__ mask, unsigned* __restrict__ pairs, int pair_cap) {
+    pdl_wait();
     const int bi = blockIdx.y, bj = blockIdx.x;   // row tile, column tile
     const int m = m_dev[0];
     if (bj < bi || bj * 64 >= m) return;          // lower triangle / past the last candidate: never read
@@ -162,6 +165,7 @@ __global__ void __launch_bounds__(MASK_T) rot_mask_kernel(const rot::RBox* __res
 // the few pairs that survive the distance test would each run with most of their warp idle).
 __global__ void __launch_bounds__(256) rot_pairs_kernel(const rot::RBox* __restrict__ R, const int* __restrict__ m_dev, float thresh,
                                                         const unsigned* __restrict__ pairs, int pair_cap, unsigned long long* __restrict__ mask) {
+    pdl_wait();
     const int total = min(m_dev[1], pair_cap);
     for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < total; q += gridDim.x * blockDim.x) {
         const unsigned e = pairs[q];
@@ -177,6 +181,7 @@ using wide::SWEEP_T;
 
 __global__ void __launch_bounds__(T, 1) rot_order_kernel(const float* __restrict__ scores, int n, int pre_max,
                                                          unsigned long long* __restrict__ skeys_out, int* __restrict__ m_out) {
+    pdl_wait();
     __shared__ OrderShared S;
     extern __shared__ __align__(16) unsigned long long key_cache[];
     auto key_of = [&](int i) { return sel::make_key(__ldg(scores + i), (unsigned)i); };
@@ -189,6 +194,7 @@ __global__ void __launch_bounds__(T, 1) rot_order_kernel(const float* __restrict
 // dependent rounds of scattered loads per thread cost more than the selection itself)
 __global__ void __launch_bounds__(256) rot_rbox_kernel(const float* __restrict__ boxes, const unsigned long long* __restrict__ skeys,
                                                        const int* __restrict__ m_dev, rot::RBox* __restrict__ R_out) {
+    pdl_wait();
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c < m_dev[0]) R_out[c] = rot::make_rbox(boxes + 7ll * sel::key_index(skeys[c]));
 }
@@ -196,6 +202,7 @@ __global__ void __launch_bounds__(256) rot_rbox_kernel(const float* __restrict__
 __global__ void __launch_bounds__(SWEEP_T, 1) rot_sweep_kernel(const unsigned long long* __restrict__ mask, const unsigned long long* __restrict__ skeys,
                                                           const int* __restrict__ m_dev, int post_max, int* __restrict__ keep,
                                                           int* __restrict__ count) {
+    pdl_wait();
     extern __shared__ __align__(128) unsigned char sweep_raw[];
     SweepShared& S = *reinterpret_cast<SweepShared*>(sweep_raw);
     __shared__ int nk_s;
@@ -227,6 +234,7 @@ __device__ __forceinline__ float sigmoidf_ref(float x) { return 1.f / (1.f + exp
 // per anchor: sigmoid of every class logit, max / first arg-max (detector3d_template.py:217,251), keep score >= thresh
 __global__ void __launch_bounds__(256) pp_candidates_kernel(const float* __restrict__ cls, int n_anchors, int num_class, float thresh,
                                                             unsigned long long* __restrict__ cand, int* __restrict__ cand_count) {
+    pdl_wait();
     const int a = blockIdx.x * blockDim.x + threadIdx.x;
     bool ok = false;
     float best = 0.f;
@@ -284,6 +292,7 @@ __global__ void __launch_bounds__(T, 1) pp_post_kernel(const PPParams p, const f
                                                        const int* __restrict__ cand_count, int cand_cap, float* __restrict__ sorted_boxes,
                                                        float* __restrict__ out_boxes, float* __restrict__ out_scores,
                                                        long long* __restrict__ out_labels, int* __restrict__ out_count) {
+    pdl_wait();
     extern __shared__ __align__(16) unsigned char smem_raw[];
     FrameShared& S = *reinterpret_cast<FrameShared*>(smem_raw);
     const int tid = threadIdx.x;
@@ -318,6 +327,7 @@ __global__ void __launch_bounds__(T, 1) pp_post_kernel(const PPParams p, const f
 // wide path (see rot_mask_kernel): the same steps as pp_post_kernel with the IoU work between them on the whole GPU
 __global__ void __launch_bounds__(T, 1) pp_order_kernel(const PPParams p, const unsigned long long* __restrict__ cand, const int* __restrict__ cand_count,
                                                         int cand_cap, unsigned long long* __restrict__ skeys_out, int* __restrict__ m_out) {
+    pdl_wait();
     __shared__ OrderShared S;
     extern __shared__ __align__(16) unsigned long long key_cache[];
     const int tid = threadIdx.x;
@@ -332,6 +342,7 @@ __global__ void __launch_bounds__(T, 1) pp_order_kernel(const PPParams p, const 
 __global__ void __launch_bounds__(256) pp_decode_kernel(const PPParams p, const float* __restrict__ box_preds, const float* __restrict__ dir_preds,
                                                         const unsigned long long* __restrict__ skeys, const int* __restrict__ m_dev,
                                                         float* __restrict__ sorted_boxes, rot::RBox* __restrict__ R_out) {
+    pdl_wait();
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= m_dev[0]) return;
     float b7[7];
@@ -346,6 +357,7 @@ __global__ void __launch_bounds__(SWEEP_T, 1) pp_finish_kernel(const PPParams p,
                                                           const float* __restrict__ sorted_boxes, float* __restrict__ out_boxes,
                                                           float* __restrict__ out_scores, long long* __restrict__ out_labels,
                                                           int* __restrict__ out_count) {
+    pdl_wait();
     extern __shared__ __align__(128) unsigned char sweep_raw[];
     SweepShared& S = *reinterpret_cast<SweepShared*>(sweep_raw);
     const int tid = threadIdx.x;
@@ -389,6 +401,7 @@ struct CPParams {
 
 __global__ void __launch_bounds__(T, 1) cp_head_kernel(const CPParams p, float* __restrict__ head_boxes, float* __restrict__ head_scores,
                                                        int* __restrict__ head_labels, int* __restrict__ head_count) {
+    pdl_wait();
     extern __shared__ __align__(16) unsigned char smem_raw[];
     FrameShared& S = *reinterpret_cast<FrameShared*>(smem_raw);
     const int tid = threadIdx.x, h = blockIdx.x;
@@ -472,6 +485,7 @@ __global__ void __launch_bounds__(256) cp_concat_kernel(int num_heads, int post_
                                                         const float* __restrict__ head_scores, const int* __restrict__ head_labels,
                                                         const int* __restrict__ head_count, float* __restrict__ out_boxes,
                                                         float* __restrict__ out_scores, long long* __restrict__ out_labels, int* __restrict__ out_count) {
+    pdl_wait();
     int off = 0;
     for (int h = 0; h < num_heads; h++) {
         const int n = head_count[h];
@@ -492,6 +506,7 @@ __global__ void __launch_bounds__(256) cp_concat_kernel(int num_heads, int post_
 __global__ void __launch_bounds__(1024) class_filter_kernel(const long long* __restrict__ labels, const float* __restrict__ scores, int n,
                                                             int n_groups, const int* __restrict__ group_cls, const float* __restrict__ group_thr,
                                                             int* __restrict__ out_idx, int* __restrict__ out_count) {
+    pdl_wait();
     __shared__ int warp_tot[32];
     int base = 0;
     for (int g = 0; g < n_groups; g++) {
@@ -519,7 +534,7 @@ extern "C" int tcb_rotated_iou(tcb_ctx* ctx, const float* boxes_a_dev, int n, co
     TCB_REQUIRE(ctx, n >= 0 && m >= 0, "tcb_rotated_iou: bad sizes");
     if (n == 0 || m == 0) return TCB_OK;
     TCB_REQUIRE(ctx, boxes_a_dev && boxes_b_dev && out_dev, "tcb_rotated_iou: null buffer");
-    rotated_iou_kernel<<<tcb_div_up((long long)n * m, 256), 256, 0, (cudaStream_t)stream>>>(boxes_a_dev, n, boxes_b_dev, m, out_dev);
+    TCB_KLAUNCH(ctx, rotated_iou_kernel, tcb_div_up((long long)n * m, 256), 256, 0, (cudaStream_t)stream, boxes_a_dev, n, boxes_b_dev, m, out_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }
@@ -576,22 +591,22 @@ extern "C" int tcb_rotated_nms(tcb_ctx* ctx, const float* boxes_dev, const float
     const int m_max = n < pre_max ? n : pre_max;
     if (m_max > WIDE_MIN && wide_bufs(ctx, m_max, wb)) {
         TCB_CUDA(ctx, cudaFuncSetAttribute(rot_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ORDER_CACHE * 8));
-        rot_order_kernel<<<1, T, ORDER_CACHE * 8, st>>>(scores_dev, n, pre_max, wb.skeys, wb.m);
+        TCB_KLAUNCH(ctx, rot_order_kernel, 1, T, ORDER_CACHE * 8, st, scores_dev, n, pre_max, wb.skeys, wb.m);
         TCB_LAUNCHED(ctx);
-        rot_rbox_kernel<<<tcb_div_up(m_max, 256), 256, 0, st>>>(boxes_dev, wb.skeys, wb.m, wb.R);
+        TCB_KLAUNCH(ctx, rot_rbox_kernel, tcb_div_up(m_max, 256), 256, 0, st, boxes_dev, wb.skeys, wb.m, wb.R);
         TCB_LAUNCHED(ctx);
         const int nb = tcb_div_up(m_max, 64);
-        rot_mask_kernel<<<dim3(nb, nb), MASK_T, 0, st>>>(wb.R, wb.m, thresh, wb.mask, wb.pairs, wb.pair_cap);
+        TCB_KLAUNCH(ctx, rot_mask_kernel, dim3(nb, nb), MASK_T, 0, st, wb.R, wb.m, thresh, wb.mask, wb.pairs, wb.pair_cap);
         TCB_LAUNCHED(ctx);
-        rot_pairs_kernel<<<ctx->num_sms * 8, 256, 0, st>>>(wb.R, wb.m, thresh, wb.pairs, wb.pair_cap, wb.mask);
+        TCB_KLAUNCH(ctx, rot_pairs_kernel, ctx->num_sms * 8, 256, 0, st, wb.R, wb.m, thresh, wb.pairs, wb.pair_cap, wb.mask);
         TCB_LAUNCHED(ctx);
         TCB_CUDA(ctx, cudaFuncSetAttribute(rot_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SweepShared)));
-        rot_sweep_kernel<<<1, SWEEP_T, sizeof(SweepShared), st>>>(wb.mask, wb.skeys, wb.m, post_max, keep_dev, count_dev);
+        TCB_KLAUNCH(ctx, rot_sweep_kernel, 1, SWEEP_T, sizeof(SweepShared), st, wb.mask, wb.skeys, wb.m, post_max, keep_dev, count_dev);
         TCB_LAUNCHED(ctx);
         return TCB_OK;
     }
     if ((rc = opt_in_smem(ctx, rotated_nms_kernel))) return rc;
-    rotated_nms_kernel<<<1, T, sizeof(FrameShared), st>>>(boxes_dev, scores_dev, n, thresh, pre_max, post_max, keep_dev, count_dev);
+    TCB_KLAUNCH(ctx, rotated_nms_kernel, 1, T, sizeof(FrameShared), st, boxes_dev, scores_dev, n, thresh, pre_max, post_max, keep_dev, count_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }
@@ -640,29 +655,29 @@ extern "C" int tcb_pp_anchor_post(tcb_ctx* ctx, const float* cls_dev, const floa
     TCB_WS(ctx, cand, unsigned long long, n_anchors);
     TCB_WS(ctx, sorted_boxes, float, (size_t)PRE_CAP * 7);
     TCB_CUDA(ctx, cudaMemsetAsync(cand_count, 0, sizeof(int), st));
-    pp_candidates_kernel<<<tcb_div_up(n_anchors, 256), 256, 0, st>>>(cls_dev, (int)n_anchors, num_class, score_thresh, cand, cand_count);
+    TCB_KLAUNCH(ctx, pp_candidates_kernel, tcb_div_up(n_anchors, 256), 256, 0, st, cls_dev, (int)n_anchors, num_class, score_thresh, cand, cand_count);
     TCB_LAUNCHED(ctx);
     WideBufs wb;
     const int m_max = (int)(n_anchors < pre_max ? n_anchors : pre_max);
     if (m_max > WIDE_MIN && wide_bufs(ctx, m_max, wb)) {
         TCB_CUDA(ctx, cudaFuncSetAttribute(pp_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ORDER_CACHE * 8));
-        pp_order_kernel<<<1, T, ORDER_CACHE * 8, st>>>(p, cand, cand_count, (int)n_anchors, wb.skeys, wb.m);
+        TCB_KLAUNCH(ctx, pp_order_kernel, 1, T, ORDER_CACHE * 8, st, p, cand, cand_count, (int)n_anchors, wb.skeys, wb.m);
         TCB_LAUNCHED(ctx);
-        pp_decode_kernel<<<tcb_div_up(m_max, 256), 256, 0, st>>>(p, box_dev, dir_dev, wb.skeys, wb.m, sorted_boxes, wb.R);
+        TCB_KLAUNCH(ctx, pp_decode_kernel, tcb_div_up(m_max, 256), 256, 0, st, p, box_dev, dir_dev, wb.skeys, wb.m, sorted_boxes, wb.R);
         TCB_LAUNCHED(ctx);
         const int nb = tcb_div_up(m_max, 64);
-        rot_mask_kernel<<<dim3(nb, nb), MASK_T, 0, st>>>(wb.R, wb.m, nms_thresh, wb.mask, wb.pairs, wb.pair_cap);
+        TCB_KLAUNCH(ctx, rot_mask_kernel, dim3(nb, nb), MASK_T, 0, st, wb.R, wb.m, nms_thresh, wb.mask, wb.pairs, wb.pair_cap);
         TCB_LAUNCHED(ctx);
-        rot_pairs_kernel<<<ctx->num_sms * 8, 256, 0, st>>>(wb.R, wb.m, nms_thresh, wb.pairs, wb.pair_cap, wb.mask);
+        TCB_KLAUNCH(ctx, rot_pairs_kernel, ctx->num_sms * 8, 256, 0, st, wb.R, wb.m, nms_thresh, wb.pairs, wb.pair_cap, wb.mask);
         TCB_LAUNCHED(ctx);
         TCB_CUDA(ctx, cudaFuncSetAttribute(pp_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SweepShared)));
-        pp_finish_kernel<<<1, SWEEP_T, sizeof(SweepShared), st>>>(p, cls_dev, wb.mask, wb.skeys, wb.m, sorted_boxes, out_boxes_dev, out_scores_dev,
+        TCB_KLAUNCH(ctx, pp_finish_kernel, 1, SWEEP_T, sizeof(SweepShared), st, p, cls_dev, wb.mask, wb.skeys, wb.m, sorted_boxes, out_boxes_dev, out_scores_dev,
                                                              out_labels_dev, out_count_dev);
         TCB_LAUNCHED(ctx);
         return TCB_OK;
     }
     if ((rc = opt_in_smem(ctx, pp_post_kernel))) return rc;
-    pp_post_kernel<<<1, T, sizeof(FrameShared), st>>>(p, cls_dev, box_dev, dir_dev, cand, cand_count, (int)n_anchors, sorted_boxes,
+    TCB_KLAUNCH(ctx, pp_post_kernel, 1, T, sizeof(FrameShared), st, p, cls_dev, box_dev, dir_dev, cand, cand_count, (int)n_anchors, sorted_boxes,
                                                        out_boxes_dev, out_scores_dev, out_labels_dev, out_count_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
@@ -714,9 +729,9 @@ extern "C" int tcb_centerpoint_post(tcb_ctx* ctx, int num_heads, const float* co
     TCB_WS(ctx, head_scores, float, rows);
     TCB_WS(ctx, head_labels, int, rows);
     if ((rc = opt_in_smem(ctx, cp_head_kernel))) return rc;
-    cp_head_kernel<<<num_heads, T, sizeof(FrameShared), st>>>(p, head_boxes, head_scores, head_labels, head_count);
+    TCB_KLAUNCH(ctx, cp_head_kernel, num_heads, T, sizeof(FrameShared), st, p, head_boxes, head_scores, head_labels, head_count);
     TCB_LAUNCHED(ctx);
-    cp_concat_kernel<<<1, 256, 0, st>>>(num_heads, post_max, head_boxes, head_scores, head_labels, head_count, out_boxes_dev,
+    TCB_KLAUNCH(ctx, cp_concat_kernel, 1, 256, 0, st, num_heads, post_max, head_boxes, head_scores, head_labels, head_count, out_boxes_dev,
                                         out_scores_dev, out_labels_dev, out_count_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
@@ -736,7 +751,7 @@ extern "C" int tcb_class_score_filter(tcb_ctx* ctx, const long long* labels_dev,
         TCB_CUDA(ctx, cudaMemcpyAsync(gcls, group_class_host, sizeof(int) * n_groups, cudaMemcpyHostToDevice, st));
         TCB_CUDA(ctx, cudaMemcpyAsync(gthr, group_thresh_host, sizeof(float) * n_groups, cudaMemcpyHostToDevice, st));
     }
-    class_filter_kernel<<<1, 1024, 0, st>>>(labels_dev, scores_dev, n, n_groups, gcls, gthr, out_idx_dev, out_count_dev);
+    TCB_KLAUNCH(ctx, class_filter_kernel, 1, 1024, 0, st, labels_dev, scores_dev, n, n_groups, gcls, gthr, out_idx_dev, out_count_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }

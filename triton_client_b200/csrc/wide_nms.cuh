@@ -16,6 +16,7 @@ constexpr int MW = PRE_CAP / 64;      // mask words per row
 template <typename Box, typename Pred>
 __global__ void __launch_bounds__(64) tile_mask_kernel(const Box* __restrict__ R_all, const int* __restrict__ m_all, int m_stride, Pred pred,
                                                        unsigned long long* __restrict__ mask_all) {
+    pdl_wait();
     const int bi = blockIdx.y, bj = blockIdx.x, set = blockIdx.z;
     const int m = m_all[(size_t)set * m_stride];
     if (bj < bi || bj * 64 >= m) return;          // lower triangle / past the last candidate: never read

@@ -37,6 +37,7 @@ struct DecodeParams {
 // 85 dependent round trips: 50 us even for a 16x16 head.)
 constexpr int HD_CELLS = 32, HD_THREADS = 256;
 __global__ void __launch_bounds__(HD_THREADS) yolo_head_decode_kernel(const DecodeParams p) {
+    pdl_wait();
     extern __shared__ float hd_tile[];              // [HD_CELLS][no + 1]
     const int HW = p.H * p.W;
     const int no = 5 + p.nc, pitch = no + 1;
@@ -132,6 +133,7 @@ __device__ __forceinline__ ABox make_abox(const float* b4, int cls) {
 // c3: nms_cpu(boxes, confs, thresh, min_mode) -> keep indices (score descending, ties lower index first)
 __global__ void __launch_bounds__(T, 1) aa_nms_kernel(const float* __restrict__ boxes, const float* __restrict__ scores, int n, float thresh,
                                                       int min_mode, int post_max, int* __restrict__ keep, int* __restrict__ count) {
+    pdl_wait();
     extern __shared__ __align__(16) unsigned char smem_raw[];
     AFrameShared& S = *reinterpret_cast<AFrameShared*>(smem_raw);
     auto key_of = [&](int i) { return sel::make_key(__ldg(scores + i), (unsigned)i); };
@@ -148,6 +150,7 @@ __global__ void __launch_bounds__(T, 1) aa_nms_kernel(const float* __restrict__ 
 // descending, row ascending — the order in which extract_boxes_onnx emits its rows.
 __global__ void __launch_bounds__(256) yolo4_candidates_kernel(const float* __restrict__ confs, int B, int N, int nc, float conf_thresh,
                                                                unsigned long long* __restrict__ cand, int* __restrict__ cand_count) {
+    pdl_wait();
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const int b = blockIdx.y;
     bool ok = false;
@@ -173,6 +176,7 @@ __global__ void __launch_bounds__(256) yolo4_candidates_kernel(const float* __re
 __global__ void __launch_bounds__(T, 1) yolo4_nms_kernel(const float* __restrict__ boxes, int N, const unsigned long long* __restrict__ cand,
                                                          const int* __restrict__ cand_count, float nms_thresh, int post_max,
                                                          float* __restrict__ out, int* __restrict__ out_count) {
+    pdl_wait();
     extern __shared__ __align__(16) unsigned char smem_raw[];
     AFrameShared& S = *reinterpret_cast<AFrameShared*>(smem_raw);
     const int b = blockIdx.x, tid = threadIdx.x;
@@ -215,6 +219,7 @@ struct OrderShared {
 __global__ void __launch_bounds__(T, 1) aa_order_kernel(int mode, const float* __restrict__ boxes, const float* __restrict__ scores, int N,
                                                         const unsigned long long* __restrict__ cand, const int* __restrict__ cand_count,
                                                         unsigned long long* __restrict__ skeys_out, ABox* __restrict__ R_out, int* __restrict__ m_out) {
+    pdl_wait();
     __shared__ OrderShared S;
     extern __shared__ __align__(16) unsigned long long key_cache[];
     const int b = blockIdx.x, tid = threadIdx.x;
@@ -243,6 +248,7 @@ __global__ void __launch_bounds__(wide::SWEEP_T, 1) aa_sweep_kernel(int mode, co
                                                                    const unsigned long long* __restrict__ skeys_all, const ABox* __restrict__ R_all,
                                                                    const int* __restrict__ m_all, int n_rows, int post_max,
                                                                    int* __restrict__ keep, float* __restrict__ out, int* __restrict__ count) {
+    pdl_wait();
     extern __shared__ __align__(128) unsigned char sweep_raw[];
     wide::SweepShared& S = *reinterpret_cast<wide::SweepShared*>(sweep_raw);
     __shared__ int nk_s;
@@ -274,6 +280,7 @@ __global__ void __launch_bounds__(wide::SWEEP_T, 1) aa_sweep_kernel(int mode, co
 
 // c5: pairwise IoU (base_postprocess.py:48-70), float32
 __global__ void __launch_bounds__(256) box_iou_kernel(const float* __restrict__ a, int n, const float* __restrict__ b, int m, float* __restrict__ out) {
+    pdl_wait();
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (long long)n * m) return;
     const int ia = (int)(i / m), ib = (int)(i - (long long)ia * m);
@@ -310,7 +317,7 @@ extern "C" int tcb_yolo_head_decode(tcb_ctx* ctx, const float* head_dev, int b, 
     const size_t tile_bytes = (size_t)HD_CELLS * (5 + num_classes + 1) * sizeof(float);
     if (tile_bytes > 200 * 1024) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_yolo_head_decode: %d classes exceed the shared-memory tile", num_classes);
     if (tile_bytes > 48 * 1024) TCB_CUDA(ctx, cudaFuncSetAttribute(yolo_head_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_bytes));
-    yolo_head_decode_kernel<<<(unsigned)ctas, HD_THREADS, tile_bytes, (cudaStream_t)stream>>>(p);
+    TCB_KLAUNCH(ctx, yolo_head_decode_kernel, (unsigned)ctas, HD_THREADS, tile_bytes, (cudaStream_t)stream, p);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }
@@ -331,13 +338,13 @@ static int aa_wide_run(tcb_ctx* ctx, int mode, int sets, int n_rows, const float
                        const int* cand_count, const AAWide& wb, NumpyNmsPred pred, int post_max, int* keep, float* out, int* count,
                        cudaStream_t st) {
     TCB_CUDA(ctx, cudaFuncSetAttribute(aa_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ORDER_CACHE * 8));
-    aa_order_kernel<<<sets, T, ORDER_CACHE * 8, st>>>(mode, boxes, scores, n_rows, cand, cand_count, wb.skeys, wb.R, wb.m);
+    TCB_KLAUNCH(ctx, aa_order_kernel, sets, T, ORDER_CACHE * 8, st, mode, boxes, scores, n_rows, cand, cand_count, wb.skeys, wb.R, wb.m);
     TCB_LAUNCHED(ctx);
     const int nb = tcb_div_up(n_rows < PRE_CAP ? n_rows : PRE_CAP, 64);
-    wide::tile_mask_kernel<ABox, NumpyNmsPred><<<dim3(nb, nb, sets), 64, 0, st>>>(wb.R, wb.m, 1, pred, wb.mask);
+    TCB_KLAUNCH(ctx, (wide::tile_mask_kernel<ABox, NumpyNmsPred>), dim3(nb, nb, sets), 64, 0, st, wb.R, wb.m, 1, pred, wb.mask);
     TCB_LAUNCHED(ctx);
     TCB_CUDA(ctx, cudaFuncSetAttribute(aa_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(wide::SweepShared)));
-    aa_sweep_kernel<<<sets, wide::SWEEP_T, sizeof(wide::SweepShared), st>>>(mode, wb.mask, wb.skeys, wb.R, wb.m, n_rows, post_max, keep, out, count);
+    TCB_KLAUNCH(ctx, aa_sweep_kernel, sets, wide::SWEEP_T, sizeof(wide::SweepShared), st, mode, wb.mask, wb.skeys, wb.R, wb.m, n_rows, post_max, keep, out, count);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }
@@ -353,7 +360,7 @@ extern "C" int tcb_nms_axis_aligned(tcb_ctx* ctx, const float* boxes_dev, const 
         return aa_wide_run(ctx, 0, 1, n, boxes_dev, scores_dev, nullptr, nullptr, wb, NumpyNmsPred{thresh, min_mode ? 1 : 0}, post_max, keep_dev, nullptr,
                            count_dev, (cudaStream_t)stream);
     TCB_CUDA(ctx, cudaFuncSetAttribute(aa_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AFrameShared)));
-    aa_nms_kernel<<<1, T, sizeof(AFrameShared), (cudaStream_t)stream>>>(boxes_dev, scores_dev, n, thresh, min_mode ? 1 : 0, post_max, keep_dev, count_dev);
+    TCB_KLAUNCH(ctx, aa_nms_kernel, 1, T, sizeof(AFrameShared), (cudaStream_t)stream, boxes_dev, scores_dev, n, thresh, min_mode ? 1 : 0, post_max, keep_dev, count_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }
@@ -379,14 +386,14 @@ extern "C" int tcb_yolo4_post(tcb_ctx* ctx, const float* boxes_dev, const float*
     TCB_WS(ctx, cand, unsigned long long, (size_t)b * (n > 0 ? n : 1));
     TCB_CUDA(ctx, cudaMemsetAsync(cand_count, 0, sizeof(int) * b, st));
     if (n > 0) {
-        yolo4_candidates_kernel<<<dim3(tcb_div_up(n, 256), b), 256, 0, st>>>(confs_dev, b, n, nc, conf_thresh, cand, cand_count);
+        TCB_KLAUNCH(ctx, yolo4_candidates_kernel, dim3(tcb_div_up(n, 256), b), 256, 0, st, confs_dev, b, n, nc, conf_thresh, cand, cand_count);
         TCB_LAUNCHED(ctx);
     }
     AAWide wb;
     if (n > WIDE_MIN && aa_wide_bufs(ctx, b, wb))
         return aa_wide_run(ctx, 1, b, n, boxes_dev, nullptr, cand, cand_count, wb, NumpyNmsPred{nms_thresh, 0}, post_max, nullptr, out_dev, count_dev, st);
     TCB_CUDA(ctx, cudaFuncSetAttribute(yolo4_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AFrameShared)));
-    yolo4_nms_kernel<<<b, T, sizeof(AFrameShared), st>>>(boxes_dev, n > 0 ? n : 1, cand, cand_count, nms_thresh, post_max, out_dev, count_dev);
+    TCB_KLAUNCH(ctx, yolo4_nms_kernel, b, T, sizeof(AFrameShared), st, boxes_dev, n > 0 ? n : 1, cand, cand_count, nms_thresh, post_max, out_dev, count_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }
@@ -397,7 +404,7 @@ extern "C" int tcb_box_iou(tcb_ctx* ctx, const float* boxes_a_dev, int n, const 
     if (n == 0 || m == 0) return TCB_OK;
     TCB_REQUIRE(ctx, boxes_a_dev && boxes_b_dev && out_dev, "tcb_box_iou: null buffer");
     TCB_REQUIRE(ctx, (((uintptr_t)boxes_a_dev | (uintptr_t)boxes_b_dev) & 15) == 0, "tcb_box_iou: box arrays must be 16-byte aligned");
-    box_iou_kernel<<<tcb_div_up((long long)n * m, 256), 256, 0, (cudaStream_t)stream>>>(boxes_a_dev, n, boxes_b_dev, m, out_dev);
+    TCB_KLAUNCH(ctx, box_iou_kernel, tcb_div_up((long long)n * m, 256), 256, 0, (cudaStream_t)stream, boxes_a_dev, n, boxes_b_dev, m, out_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }
