@@ -93,7 +93,9 @@ __device__ __forceinline__ unsigned lane_id() { return threadIdx.x & 31; }
 // successor be scheduled early in turn, then waits until the predecessor has completed and its writes are visible.
 // Without the launch attribute both instructions do nothing.
 __device__ __forceinline__ void pdl_enter() {
+#ifndef TCB_PDL_WAIT_ONLY   // (A/B builds: -DTCB_PDL_WAIT_ONLY turns every early trigger off)
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+#endif
     asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 // What kernels launched with the attribute use where they would otherwise write __ldg(p): a plain, coherent load.
