@@ -63,7 +63,7 @@ static inline void tcb_ws_reset(tcb_ctx* ctx) { ctx->ws_used = 0; }
             return tcb_fail((ctx), TCB_ERR_CUDA, "%s: launch failed: %s", __func__, cudaGetErrorString(e__)); \
     } while (0)
 
-// Launch `kernel` (which must begin with pdl_enter()) with programmatic stream serialization when the context allows it.
+// Launch `kernel` (which must begin with pdl_wait() / pdl_enter()) with programmatic stream serialization when the context allows it.
 #define TCB_KLAUNCH(ctx, kernel, grid, block, smem, st, ...)                                             \
     TCB_CUDA((ctx), tcb_launch((ctx)->pdl != 0, kernel, dim3(grid), dim3(block), (size_t)(smem), (st), __VA_ARGS__))
 
@@ -88,23 +88,19 @@ __device__ __forceinline__ void st_stream_f4(float* p, float4 v) {
 }
 __device__ __forceinline__ unsigned lane_id() { return threadIdx.x & 31; }
 
-// Programmatic dependent launch. A kernel launched through tcb_launch(pdl = true) may become resident while the kernel
-// before it on the stream is still draining; it must call pdl_enter() before it touches global memory: that lets ITS
-// successor be scheduled early in turn, then waits until the predecessor has completed and its writes are visible.
-// Without the launch attribute both instructions do nothing.
-__device__ __forceinline__ void pdl_enter() {
-#ifndef TCB_PDL_WAIT_ONLY   // (A/B builds: -DTCB_PDL_WAIT_ONLY turns every early trigger off)
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-#endif
-    asm volatile("griddepcontrol.wait;" ::: "memory");
-}
-// What kernels launched with the attribute use where they would otherwise write __ldg(p): a plain, coherent load.
+// Programmatic dependent launch. A kernel launched through tcb_launch(pdl = true) is scheduled as soon as every CTA of
+// the kernel before it on the stream has exited, without waiting for that kernel's memory flush and the launch latency
+// behind it; it must call pdl_wait() before it touches global memory (a no-op without the launch attribute).
+// No kernel here triggers its successor early (griddepcontrol.launch_dependents): measured on the bench step and the
+// voxelisation chain, the early trigger gained nothing over this form (131.2 vs 131.6 us per configs[1] step), and a
+// successor that is resident while its producer still runs must not read the producer's output through the
+// non-coherent path (ld.global.nc — what `const T* __restrict__` and __ldg compile to), which cost a stale pair
+// count in the wide rotated-NMS path when it was tried.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_enter() { pdl_wait(); }
+// A plain (coherent) load where one would write __ldg(p).
 template <typename T>
 __device__ __forceinline__ T ld_coherent(const T* p) { return *p; }
-// The cautious form: no early trigger, so this kernel's successor is scheduled only when every CTA here has exited (the
-// implicit trigger) — nothing of this kernel can still be loading when the successor becomes resident, and kernels that
-// read their inputs through the non-coherent path stay correct. What is saved is the successor's launch latency.
-__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 template <typename... KA, typename... A>
 static inline cudaError_t tcb_launch(bool pdl, void (*kernel)(KA...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, A... args) {
     cudaLaunchConfig_t cfg = {};

@@ -17,11 +17,10 @@
 //                   the zero-padded (P, F) block and the count
 //   decorate      : PillarVFE.forward decoration (OPCD/pcdet/models/backbones_3d/vfe/pillar_vfe.py:94-118)
 #include "common.cuh"
-// Kernels here are launched with programmatic stream serialization (TCB_KLAUNCH): a kernel can be resident before the
-// one that produces its inputs has finished, so inputs must not be read through the non-coherent path (ld.global.nc
-// is only valid for data that is read-only for the kernel's whole lifetime). That is why the const pointer
-// parameters carry no __restrict__ and nothing is read with __ldg: the compiler then emits coherent loads, which
-// griddepcontrol.wait orders. (The point rows themselves can come from tcb_pointcloud2_unpack on the same stream.)
+// Kernels here are launched with programmatic stream serialization (TCB_KLAUNCH) and begin with pdl_enter(). Their const
+// pointer parameters carry no __restrict__ and nothing is read with __ldg, so every input is read with coherent loads
+// (see common.cuh: that matters once a kernel may be resident while its producer still runs; the point rows themselves can
+// come from tcb_pointcloud2_unpack on the same stream).
 #include <limits.h>
 
 namespace {
