@@ -88,3 +88,20 @@ def test_limits_are_errors(engine):
     big = np.zeros((2049, 6))
     with pytest.raises(TcbError):
         engine.calculate_metrics(torch.from_numpy(big).cuda(), [2049], torch.from_numpy(big).cuda(), [2049])
+
+
+def test_ap_per_class_edge_frames(engine):
+    """No predictions, no targets, a class without predictions, fewer than ten thresholds: same numbers as the oracle."""
+    ev = EvaluationMetrics(engine)
+    rng = np.random.default_rng(5)
+    cases = [(np.zeros((0, 10), bool), np.zeros(0), np.zeros(0), np.array([0.0, 1.0, 1.0])),          # nothing predicted
+             (rng.uniform(0, 1, (7, 10)) < 0.5, rng.uniform(0.3, 1, 7), np.zeros(7), np.array([0.0] * 8 + [2.0, 2.0, 5.0])),   # classes 2, 5 unpredicted
+             (rng.uniform(0, 1, (40, 3)) < 0.2, rng.uniform(0.3, 1, 40), rng.integers(0, 3, 40).astype(float), rng.integers(0, 3, 60).astype(float)),
+             (rng.uniform(0, 1, (1, 10)) < 2.0, np.array([0.9]), np.array([1.0]), np.array([1.0]))]
+    for k, (tp, conf, pcls, tcls) in enumerate(cases):
+        p, r, ap, f1, cls = ev.ap_per_class(tp, conf, pcls, tcls)
+        wp, wr, wap, wf1, wcls = em.ap_per_class(tp, conf, pcls, tcls)
+        _check(dict(p=p, r=r, ap=ap, f1=f1, ap_class=cls), dict(p=wp, r=wr, ap=wap, f1=wf1, ap_class=wcls), k)
+    out = engine.ap_per_class(torch.zeros((3, 10), dtype=torch.uint8).cuda(), torch.rand(3, dtype=torch.float64).cuda(),
+                              torch.zeros(3, dtype=torch.float64).cuda(), [3], torch.zeros(0, dtype=torch.float64).cuda(), [0], max_classes=4)
+    assert int(out["num_classes"][0]) == 0                                                              # no targets: no classes

@@ -59,7 +59,7 @@ class EvaluationMetrics:
     def ap_per_class(self, tp, conf, pred_cls, target_cls, plot=False, save_dir='.', names=()):
         eng = self.engine
         tp = np.asarray(tp)
-        tp = tp.reshape(len(tp), -1)
+        tp = tp.reshape(len(tp), tp.shape[1] if tp.ndim > 1 else 1)
         target_cls = np.asarray(target_cls, np.float64)
         dev = lambda a, dt: torch.from_numpy(np.ascontiguousarray(np.asarray(a).astype(dt))).to(eng.device)
         nc = max(1, len(np.unique(target_cls)))
