@@ -109,6 +109,7 @@ def main():
 
     pre_row("a1-a3 stretch+adjust", "C2 64x1280x720->640x640", 64, 720, 1280, 640, 640, "stretch")
     pre_row("a7 letterbox+adjust", "C2 64x1280x720->640x640", 64, 720, 1280, 640, 640, "letterbox")
+    pre_row("a1 stretch, general scales", "32x1920x1080->640x640 (two-pass kernel: 3:1 and 1.69:1)", 32, 1080, 1920, 640, 640, "stretch")
     pre_row("a3 adjust only", "C1 1x640x640", 1, 640, 640, 640, 640, "stretch")
     pre_row("a3 adjust only (batch 64)", "C1-shape 64x640x640", 64, 640, 640, 640, 640, "stretch")
     pre_row("a4 FCOS adjust", "C3 1x800x1333", 1, 800, 1333, 800, 1333, "stretch", 1.0)
