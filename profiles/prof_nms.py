@@ -3,7 +3,7 @@ sys.path.insert(0,'.')
 from triton_client_b200 import synth, _lib
 from triton_client_b200.gpu import Engine
 import os
-_lib.LIB_PATH=os.path.join('profiles','probes','libtcb200_prof.so')   # built by profiles/probes/build_prof_lib.sh (yolo_post.cu with -DTCB_NMS_PROFILE)
+_lib.LIB_PATH=os.environ.get('TCB_PROF_LIB') or os.path.join('profiles','probes','libtcb200_prof.so')   # built by profiles/probes/build_prof_lib.sh (yolo_post.cu with -DTCB_NMS_PROFILE)
 eng=Engine(0)
 pred=torch.from_numpy(synth.yolo_output(64,25200,2,2002)).cuda()
 l=_lib.lib()
