@@ -209,3 +209,41 @@ def test_two_batches_in_flight(engine):
             assert np.array_equal(x, np.concatenate([pre2d.preprocess_frame(f.numpy(), 160, 160, mode="letterbox") for f in frames]))
         for got, w in ((da, want[0]), (db, want[1])):
             assert all(torch.equal(a, b) for a, b in zip(got, w))
+
+
+def test_cuda_graph_replay_matches_eager(engine):
+    """The preprocess + YOLO post entry points captured once in a CUDA graph (their launches carry the programmatic
+    serialization attribute) and replayed on new inputs give what the eager calls give."""
+    dev = engine.device
+    frames = torch.zeros((4, 180, 320, 3), dtype=torch.uint8, device=dev)
+    pred = torch.zeros((4, 3000, 7), dtype=torch.float32, device=dev)
+    x = torch.empty((4, 3, 160, 160), dtype=torch.float32, device=dev)
+    det = torch.zeros((4, 300, 6), dtype=torch.float64, device=dev)
+    cnt = torch.zeros((2, 4), dtype=torch.int32, device=dev)
+
+    def both():
+        engine.preprocess_images(frames, 160, 160, mode="letterbox", div=255.0, out=x)
+        engine.yolo_nms(pred, conf_thres=0.3, iou_thres=0.45, max_det=300, out=det, counts=cnt)
+
+    data = [(torch.from_numpy(np.stack([synth.image_noise(180, 320, 300 + 10 * k + i) for i in range(4)])).to(dev),
+             torch.from_numpy(synth.yolo_output(4, 3000, 2, 70 + k)).to(dev)) for k in range(3)]
+    frames.copy_(data[0][0]); pred.copy_(data[0][1])
+    s = torch.cuda.Stream(dev)
+    s.wait_stream(torch.cuda.current_stream(dev))
+    with torch.cuda.stream(s):
+        both()
+    torch.cuda.current_stream(dev).wait_stream(s)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=s):
+        both()
+    for f, p in data[1:] + data[:1]:
+        frames.copy_(f); pred.copy_(p)
+        g.replay()
+        torch.cuda.synchronize()
+        got = (x.clone(), det.clone(), cnt.clone())
+        both()
+        torch.cuda.synchronize()
+        assert torch.equal(got[0], x) and torch.equal(got[2], cnt)
+        for b in range(4):
+            n = int(cnt[0, b])
+            assert n > 0 and torch.equal(got[1][b, :n], det[b, :n])
