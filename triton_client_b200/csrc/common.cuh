@@ -92,12 +92,18 @@ __device__ __forceinline__ unsigned lane_id() { return threadIdx.x & 31; }
 // the kernel before it on the stream has exited, without waiting for that kernel's memory flush and the launch latency
 // behind it; it must call pdl_wait() before it touches global memory (a no-op without the launch attribute).
 // No kernel here triggers its successor early (griddepcontrol.launch_dependents): measured on the bench step and the
-// voxelisation chain, the early trigger gained nothing over this form (131.2 vs 131.6 us per configs[1] step), and a
+// voxelisation chain, the early trigger gained nothing over this form (configs[1] step with every launch edge intact:
+// 121.2 us wait-only, 122.6 us with the trigger — the waiting CTAs take room from the producer's tail), and a
 // successor that is resident while its producer still runs must not read the producer's output through the
 // non-coherent path (ld.global.nc — what `const T* __restrict__` and __ldg compile to), which cost a stale pair
 // count in the wide rotated-NMS path when it was tried.
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
-__device__ __forceinline__ void pdl_enter() { pdl_wait(); }
+__device__ __forceinline__ void pdl_enter() {
+#ifdef TCB_PDL_EARLY   // A/B builds only: trigger the successor before waiting (see above for why this is not the default)
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+#endif
+    pdl_wait();
+}
 // A plain (coherent) load where one would write __ldg(p).
 template <typename T>
 __device__ __forceinline__ T ld_coherent(const T* p) { return *p; }
