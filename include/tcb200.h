@@ -135,8 +135,11 @@ int tcb_nms_axis_aligned(tcb_ctx* ctx, const float* boxes_dev, const float* scor
  * YOLOv4 two-tensor postprocess: extract_boxes_onnx (utils/postprocess.py:265-322) / post_processing
  * (tools/utils.py:166-233): max and first arg-max over classes, keep max > conf_thresh, per-class nms_cpu(nms_thresh),
  * rows [x1,y1,x2,y2,conf,conf,cls] grouped by class ascending, score descending inside a class.
- * boxes_dev [b,n,4] (the reference's [b,n,1,4]), confs_dev [b,n,nc]; out_dev [b,post_max,7] f32, count_dev [b].
- * At most 4096 candidates per image pass the confidence cut into NMS; post_max <= 1024.
+ * boxes_dev [b,n,4] (the reference's [b,n,1,4]), confs_dev [b,n,nc]; out_dev [b,post_max,7] f32, count_dev [2*b]:
+ * count_dev[i] = rows kept for image i, count_dev[b+i] = 1 when more than 4096 rows of image i passed the confidence
+ * cut (the reference is unbounded; only the first 4096 in output order reach the NMS, so the result is then NOT the
+ * reference's and the caller must treat it as an error — the Python drop-ins raise). A count equal to post_max means
+ * the output may be truncated. post_max <= 1024.
  */
 size_t tcb_yolo4_post_workspace(int b, int n);
 int tcb_yolo4_post(tcb_ctx* ctx, const float* boxes_dev, const float* confs_dev, int b, int n, int nc, float conf_thresh,

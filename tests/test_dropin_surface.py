@@ -58,3 +58,23 @@ def test_signatures_match_live_reference():
     for cls in ("Yolov5client", "FCOS_client"):
         for m in ("register_client", "get_preprocess", "get_postprocess", "parse_model"):
             assert hasattr(getattr(mine, cls), m)
+
+
+def test_det3d_preprocess_reads_the_config_it_is_given(tmp_path):
+    """The reference builds its voxel generator from Config.fromfile(cfg) (clients/preprocess/voxelize.py:13-24): a cfg
+    path must change the voxelisation parameters, and one that cannot be honoured must be refused."""
+    from triton_client_b200.clients.preprocess.voxelize import det3DPreprocess
+    good = tmp_path / "cfg.py"
+    good.write_text("import itertools\nvoxel_generator = dict(\n    range=[-10.0, -10.0, -2.0, 10.0, 10.0, 2.0],\n    voxel_size=[0.1, 0.1, 4],\n"
+                    "    max_points_in_voxel=7,\n    max_voxel_num=[111, 222],\n)\n")
+    p = det3DPreprocess(str(good))
+    assert p.range == [-10.0, -10.0, -2.0, 10.0, 10.0, 2.0] and p.voxel_size == [0.1, 0.1, 4]
+    assert p.max_points_in_voxel == 7 and p.max_voxel_num == [111, 222]
+    assert det3DPreprocess().max_points_in_voxel == 20
+    bad = tmp_path / "bad.py"
+    bad.write_text("voxel_generator = dict(range=[0, 0, 0, 1, 1, 1])\n")
+    with pytest.raises(ValueError):
+        det3DPreprocess(str(bad))
+    with pytest.raises(ValueError):
+        (tmp_path / "none.py").write_text("x = 1\n")
+        det3DPreprocess(str(tmp_path / "none.py"))

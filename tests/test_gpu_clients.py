@@ -211,6 +211,19 @@ def test_two_batches_in_flight(engine):
             assert all(torch.equal(a, b) for a, b in zip(got, w))
 
 
+def test_two_pageable_batches_in_flight(engine):
+    """Deferred calls with ordinary (pageable) numpy frames: each call stages its frames in pinned memory, and the second
+    call's staging must not overwrite what the first call's uploads are still reading."""
+    pre = Yolov5client(engine=engine).get_preprocess()
+    fa = np.stack([synth.image_noise(360, 640, 1800 + i) for i in range(24)])
+    fb = np.stack([synth.image_noise(360, 640, 1850 + i) for i in range(24)])
+    wa, wb = (np.concatenate([pre2d.preprocess_frame(f, 320, 320, mode="letterbox") for f in fr]) for fr in (fa, fb))
+    for _ in range(4):
+        h1 = pre.image_adjust_batch_async(fa, (320, 320), mode="letterbox", chunks=6)
+        h2 = pre.image_adjust_batch_async(fb, (320, 320), mode="letterbox", chunks=6)
+        assert np.array_equal(h1.result(), wa) and np.array_equal(h2.result(), wb)
+
+
 def test_cuda_graph_replay_matches_eager(engine):
     """The preprocess + YOLO post entry points captured once in a CUDA graph (their launches carry the programmatic
     serialization attribute) and replayed on new inputs give what the eager calls give."""

@@ -66,7 +66,8 @@ def test_yolo4_post_golden(engine):
     confs = np.concatenate([g[f"confs{i}"] for i in range(3)], 1)
     out, cnt = engine.yolo4_post(torch.from_numpy(boxes).cuda(), torch.from_numpy(confs).cuda(), 0.2, 0.4)
     for i in range(boxes.shape[0]):
-        assert np.array_equal(out[i, :int(cnt[i])].cpu().numpy(), g[f"post{i}"])
+        assert np.array_equal(out[i, :int(cnt[0, i])].cpu().numpy(), g[f"post{i}"])
+    assert int(cnt[1].sum()) == 0
 
 
 def test_yolo4_post_full_size_vs_oracle(engine):
@@ -87,7 +88,29 @@ def test_yolo4_post_full_size_vs_oracle(engine):
     for i in range(2):
         w = np.array(want[i], np.float32).reshape(-1, 7)
         assert w.shape[0] > 50 and w.shape[0] <= 1024
-        assert np.array_equal(out[i, :int(cnt[i])].cpu().numpy(), w)
+        assert np.array_equal(out[i, :int(cnt[0, i])].cpu().numpy(), w)
+    assert int(cnt[1].sum()) == 0
+
+
+@pytest.mark.parametrize("n", [400, 6000])     # single-CTA path and the wide path
+def test_yolo4_post_reports_what_it_cuts(engine, n):
+    """The reference is unbounded; the kernel takes 4096 candidates per image into the NMS. When more pass the confidence
+    cut it must say so (count[b + i]) and the drop-ins must refuse to return an incomplete result."""
+    from triton_client_b200.utils import postprocess as up
+    rng = np.random.default_rng(5)
+    xy = rng.uniform(0, 0.9, (2, n, 2))
+    boxes = np.concatenate([xy, xy + 0.01], -1).astype(np.float32).reshape(2, n, 1, 4)
+    confs = rng.uniform(0, 0.05, (2, n, 3)).astype(np.float32)
+    confs[1, :, 2] = 0.9                              # image 1: every row passes
+    out, cnt = engine.yolo4_post(torch.from_numpy(boxes).cuda(), torch.from_numpy(confs).cuda(), 0.4, 0.6)
+    cnt = cnt.cpu().numpy()
+    assert cnt[1].tolist() == [0, 1 if n > 4096 else 0] and cnt[0, 0] == 0
+    if n > 4096:
+        with pytest.raises(OverflowError):
+            up.extract_boxes_onnx(0.4, 0.6, [boxes, confs])
+    many = np.tile(boxes[0, :, 0], (5000 // n + 1, 1))[:5000]
+    with pytest.raises(OverflowError):                # > 4096 boxes into nms_cpu
+        up.nms_cpu(many, np.ones(5000, np.float32), 0.5)
 
 
 @pytest.mark.parametrize("min_mode", [False, True])

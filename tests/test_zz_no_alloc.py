@@ -8,8 +8,9 @@ failure has then already run every other test. It passes alone in a fresh proces
 device performs the one-time set-up) and after the other tests.
 
 Checked here, through the C ABI: two calls in a row give exactly what tcb_yolo_nms gives (bit-exact,
-the standard of tests/test_gpu_yolo.py) — the second call is smaller than the first, so it runs over
-the first call's left-overs in the shared array; sizes beyond the compiled-in maximum are refused.
+the standard of tests/test_gpu_yolo.py) — each later call is smaller than the first, so it runs over
+the earlier calls' left-overs in the shared array (one of them has more than 4096 candidates in a frame,
+which is what reaches the array's sort area); sizes beyond the compiled-in maximum are refused.
 """
 import numpy as np
 import pytest
@@ -26,8 +27,15 @@ def _rows(out, cnt):
 
 
 def test_static_entry_matches_context_entry_on_two_calls_in_a_row(engine):
+    rng = np.random.default_rng(8)
+    dense = np.zeros((1, 9000, 7), np.float32)      # every row a candidate: more than 4096 per frame, so the ordering
+    dense[0, :, 0:2] = rng.uniform(100, 400, (9000, 2))   # leaves shared memory and sorts in the static array's sort area
+    dense[0, :, 2:4] = rng.uniform(20, 90, (9000, 2))
+    dense[0, :, 4] = rng.uniform(0.5, 1, 9000)
+    dense[0, :, 5:] = rng.uniform(0.6, 1, (9000, 2))
     calls = [
-        (synth.yolo_output(4, 25200, 2, 4242), dict(conf_thres=0.3)),                                   # large: sorts in the static sort area
+        (synth.yolo_output(4, 25200, 2, 4242), dict(conf_thres=0.3)),                                   # largest footprint in the array
+        (dense, dict(conf_thres=0.25)),
         (synth.yolo_output(2, 3000, 5, 4243, objects=25, rows_per_object=20, tie_frac=0.5), dict(conf_thres=0.25, iou_thres=0.6, classes=[0, 2, 4], max_det=50)),
     ]
     for pred, kw in calls:  # back to back, no reset in between

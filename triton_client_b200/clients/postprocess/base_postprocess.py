@@ -55,7 +55,11 @@ class Postprocess(ABC):
         b = torch.as_tensor(np.asarray(boxes, dtype=np.float32)).to(dev)
         s = torch.as_tensor(np.asarray(confs, dtype=np.float32)).to(dev)
         keep, cnt = self.engine.nms_axis_aligned(b, s, nms_thresh, min_mode)
-        return keep[:int(cnt[0].item())].cpu().numpy().astype(np.int64)
+        kept, cut = (int(v) for v in cnt.cpu())
+        if cut or (kept >= keep.shape[0] and b.shape[0] > kept):
+            # the reference has no bound; the kernel considers the 4096 best boxes and keeps at most 1024
+            raise OverflowError("nms_cpu: %d boxes (limit 4096) / %d kept (limit %d)" % (b.shape[0], kept, keep.shape[0]))
+        return keep[:kept].cpu().numpy().astype(np.int64)
 
     @abstractmethod
     def postprocess(self):

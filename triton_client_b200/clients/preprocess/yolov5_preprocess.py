@@ -83,13 +83,19 @@ class _ImagePreprocess(Preprocess):
             src = torch.from_numpy(np.ascontiguousarray(frames))
         else:
             src = frames.contiguous()
-        if not src.is_pinned():   # pageable source: stage it once (a pinned caller buffer avoids this memcpy)
-            pin = st.pinned("pre_in_host", src.numel()).view(n, h, w, 3)
+        # deferred calls alternate between two sets of host buffers, so that the next batch can be queued while the
+        # previous one's uploads are still reading their staging buffer and the caller still reads the previous result
+        # (copy=False views stay valid until the next call but one)
+        self._out_turn = (getattr(self, "_out_turn", 0) + 1) & 1 if defer else 0
+        staged = not src.is_pinned()
+        if staged:   # pageable source: stage it once (a pinned caller buffer avoids this memcpy)
+            if getattr(self, "_in_done", None) is None:
+                self._in_done = [None, None]
+            if self._in_done[self._out_turn] is not None:
+                self._in_done[self._out_turn].synchronize()    # the uploads that last read this staging buffer have ended
+            pin = st.pinned("pre_in_host" if self._out_turn == 0 else "pre_in_host_b", src.numel()).view(n, h, w, 3)
             pin.copy_(src)
             src = pin
-        # deferred calls alternate between two host buffers, so that the next batch can be queued while the caller still
-        # reads the previous result (copy=False views stay valid until the next call but one)
-        self._out_turn = (getattr(self, "_out_turn", 0) + 1) & 1 if defer else 0
         host_out = st.pinned("pre_out" if self._out_turn == 0 else "pre_out_b", n * 3 * oh * ow * 4).view(torch.float32).view(n, 3, oh, ow)
         if getattr(self, "_streams", None) is None:
             self._streams = (torch.cuda.Stream(dev), torch.cuda.Stream(dev), torch.cuda.Stream(dev))
@@ -134,6 +140,8 @@ class _ImagePreprocess(Preprocess):
                 e_o.record(s_out)
                 ev_out.append(e_o)
         done = ev_out[-1]
+        if staged:
+            self._in_done[self._out_turn] = e_in
 
         def finish():
             done.synchronize()             # this call's last download (a later call's work may already be queued behind it)

@@ -200,7 +200,7 @@ __global__ void __launch_bounds__(T, 1) yolo4_nms_kernel(const float* __restrict
         float* r = o + k * 7;  // [x1, y1, x2, y2, conf, conf, cls] (utils/postprocess.py:314-318)
         r[0] = bx.x1; r[1] = bx.y1; r[2] = bx.x2; r[3] = bx.y2; r[4] = conf; r[5] = conf; r[6] = (float)bx.cls;
     }
-    if (tid == 0) { out_count[b] = nk; }
+    if (tid == 0) { out_count[b] = nk; out_count[gridDim.x + b] = cand_count[b] > PRE_CAP ? 1 : 0; }
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -218,7 +218,8 @@ struct OrderShared {
 // mode 0: nms_cpu (scores + boxes, one set); mode 1: YOLOv4 candidates of image blockIdx.x
 __global__ void __launch_bounds__(T, 1) aa_order_kernel(int mode, const float* __restrict__ boxes, const float* __restrict__ scores, int N,
                                                         const unsigned long long* __restrict__ cand, const int* __restrict__ cand_count,
-                                                        unsigned long long* __restrict__ skeys_out, ABox* __restrict__ R_out, int* __restrict__ m_out) {
+                                                        unsigned long long* __restrict__ skeys_out, ABox* __restrict__ R_out, int* __restrict__ m_out,
+                                                        int* __restrict__ cut_out) {
     pdl_wait();
     __shared__ OrderShared S;
     extern __shared__ __align__(16) unsigned long long key_cache[];
@@ -241,7 +242,10 @@ __global__ void __launch_bounds__(T, 1) aa_order_kernel(int mode, const float* _
             R_out[(long long)b * PRE_CAP + c] = make_abox(boxes + ((long long)b * N + row) * 4, cls);
         }
     }
-    if (tid == 0) m_out[b] = m;
+    if (tid == 0) {
+        m_out[b] = m;
+        if (mode == 1) cut_out[gridDim.x + b] = cand_count[b] > PRE_CAP ? 1 : 0;   // candidates beyond the 4096 best were dropped
+    }
 }
 
 __global__ void __launch_bounds__(wide::SWEEP_T, 1) aa_sweep_kernel(int mode, const unsigned long long* __restrict__ mask_all,
@@ -338,7 +342,7 @@ static int aa_wide_run(tcb_ctx* ctx, int mode, int sets, int n_rows, const float
                        const int* cand_count, const AAWide& wb, NumpyNmsPred pred, int post_max, int* keep, float* out, int* count,
                        cudaStream_t st) {
     TCB_CUDA(ctx, cudaFuncSetAttribute(aa_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ORDER_CACHE * 8));
-    TCB_KLAUNCH(ctx, aa_order_kernel, sets, T, ORDER_CACHE * 8, st, mode, boxes, scores, n_rows, cand, cand_count, wb.skeys, wb.R, wb.m);
+    TCB_KLAUNCH(ctx, aa_order_kernel, sets, T, ORDER_CACHE * 8, st, mode, boxes, scores, n_rows, cand, cand_count, wb.skeys, wb.R, wb.m, count);
     TCB_LAUNCHED(ctx);
     const int nb = tcb_div_up(n_rows < PRE_CAP ? n_rows : PRE_CAP, 64);
     TCB_KLAUNCH(ctx, (wide::tile_mask_kernel<ABox, NumpyNmsPred>), dim3(nb, nb, sets), 64, 0, st, wb.R, wb.m, 1, pred, wb.mask);

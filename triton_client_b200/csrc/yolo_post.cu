@@ -215,6 +215,8 @@ __global__ void __launch_bounds__(32 * FS_WARPS) yolo_filter_stream_kernel(
         advance(ahead);
     }
     const int lane_off = lane * stride + 4, group_off = 32 * stride;
+    unsigned phases = 0;   // bit k = parity of buffer k's next completion; flipped only by a real bulk wait, because a
+                           // chunk the lanes copy themselves (unaligned frame start, ragged tail) never arrives on the barrier
     for (int it = 0; ch < total; ch += nwarps, it++, advance(cur), advance(ahead)) {
         const int slot = it % FS_NBUF;
         // refill the buffer filtered in the previous iteration (released by the __syncwarp at the end of it)
@@ -224,7 +226,8 @@ __global__ void __launch_bounds__(32 * FS_WARPS) yolo_filter_stream_kernel(
         const float* src = chunk_src(cur, row0, nrow);
         float* rows = bufs + slot * buf_floats;
         if (bulk_ok(src, nrow)) {
-            yf_bar_wait(bar + slot, (unsigned)(it / FS_NBUF) & 1u);   // buffer `slot` completes once every FS_NBUF iterations
+            yf_bar_wait(bar + slot, (phases >> slot) & 1u);
+            phases ^= 1u << slot;
         } else {
             for (int i = lane; i < nrow * stride; i += 32) rows[i] = __ldg(src + i);
             __syncwarp();

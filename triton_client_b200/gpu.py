@@ -131,12 +131,13 @@ class Engine:
         return keep, cnt
 
     def yolo4_post(self, boxes, confs, conf_thresh=0.4, nms_thresh=0.6, post_max=1024):
-        """extract_boxes_onnx: boxes [B,N,1,4] (or [B,N,4]), confs [B,N,nc] -> (rows [B,post_max,7], counts [B])."""
+        """extract_boxes_onnx: boxes [B,N,1,4] (or [B,N,4]), confs [B,N,nc] -> (rows [B,post_max,7], counts [2,B]:
+        kept rows per image, and 1 where more than 4096 rows passed the confidence cut (result incomplete))."""
         _need_cuda(boxes, confs)
         b, n, nc = confs.shape
         bx = boxes.reshape(b, n, 4).contiguous().float()
         out = torch.zeros((b, post_max, 7), dtype=torch.float32, device=bx.device)
-        cnt = torch.zeros((b,), dtype=torch.int32, device=bx.device)
+        cnt = torch.zeros((2, b), dtype=torch.int32, device=bx.device)
         self.ctx.call("tcb_yolo4_post", _ptr(bx), _ptr(confs.contiguous().float()), b, n, nc, float(conf_thresh), float(nms_thresh),
                       int(post_max), _ptr(out), _ptr(cnt), _lib.stream_ptr())
         return out, cnt

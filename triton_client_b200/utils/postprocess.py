@@ -54,6 +54,11 @@ def extract_boxes_onnx(conf_thresh, nms_thresh, output):
     c = torch.as_tensor(np.asarray(confs) if not isinstance(confs, torch.Tensor) else confs, dtype=torch.float32).to(eng.device)
     rows, cnt = eng.yolo4_post(b, c, conf_thresh, nms_thresh)
     rows, cnt = rows.cpu().numpy(), cnt.cpu().numpy()
+    if cnt[1].any() or (cnt[0] >= rows.shape[1]).any():
+        # the reference has no bound; the kernel keeps 4096 candidates / 1024 rows per image and says when that cut anything
+        raise OverflowError("extract_boxes_onnx: more than 4096 rows above conf_thresh or 1024 kept rows in an image "
+                            "(images %s): raise conf_thresh" % np.nonzero(cnt[1] | (cnt[0] >= rows.shape[1]))[0].tolist())
+    cnt = cnt[0]
     out = []
     for i in range(rows.shape[0]):
         r = rows[i, :cnt[i]]
