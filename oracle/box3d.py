@@ -47,8 +47,37 @@ def nms_gpu(boxes, scores, thresh, pre_maxsize=None):
     return order[torch.from_numpy(keep[:nk].astype(np.int64))]
 
 
+def iou_normal(b):
+    """iou_normal (iou3d_nms_kernel.cu:314-325): axis-aligned BEV overlap of (x, y, dx, dy), heading ignored; float32."""
+    b = np.ascontiguousarray(b, np.float32)
+    f = np.float32
+    x1, y1 = b[:, 0] - b[:, 3] / f(2), b[:, 1] - b[:, 4] / f(2)
+    x2, y2 = b[:, 0] + b[:, 3] / f(2), b[:, 1] + b[:, 4] / f(2)
+    w = np.maximum(np.minimum(x2[:, None], x2[None]) - np.maximum(x1[:, None], x1[None]), f(0))
+    h = np.maximum(np.minimum(y2[:, None], y2[None]) - np.maximum(y1[:, None], y1[None]), f(0))
+    inter = w * h
+    area = b[:, 3] * b[:, 4]
+    return inter / np.maximum(area[:, None] + area[None] - inter, f(1e-8))
+
+
+def nms_normal_gpu(boxes, scores, thresh):
+    """iou3d_nms_utils.nms_normal_gpu (iou3d_nms_utils.py:102-116): sort descending, greedy sweep with iou_normal."""
+    boxes = torch.as_tensor(boxes, dtype=torch.float32)
+    scores = torch.as_tensor(scores, dtype=torch.float32)
+    order = torch.sort(scores, descending=True, stable=True)[1]
+    over = iou_normal(boxes[order][:, :7].numpy()) > np.float32(thresh)
+    n = over.shape[0]
+    removed = np.zeros(n, bool)
+    keep = []
+    for i in range(n):
+        if not removed[i]:
+            keep.append(i)
+            removed[i + 1:] |= over[i, i + 1:]
+    return order[torch.tensor(keep, dtype=torch.int64)]
+
+
 # --- reference: OPCD/pcdet/models/model_utils/model_nms_utils.py:6-25 ---------------------------------
-def class_agnostic_nms(box_scores, box_preds, nms_thresh, pre_max, post_max, score_thresh=None):
+def class_agnostic_nms(box_scores, box_preds, nms_thresh, pre_max, post_max, score_thresh=None, nms_type="nms_gpu"):
     src_box_scores = box_scores
     if score_thresh is not None:
         scores_mask = (box_scores >= score_thresh)
@@ -58,7 +87,7 @@ def class_agnostic_nms(box_scores, box_preds, nms_thresh, pre_max, post_max, sco
     if box_scores.shape[0] > 0:
         box_scores_nms, indices = stable_topk(box_scores, min(pre_max, box_scores.shape[0]))
         boxes_for_nms = box_preds[indices]
-        keep_idx = nms_gpu(boxes_for_nms[:, 0:7], box_scores_nms, nms_thresh)
+        keep_idx = (nms_gpu if nms_type == "nms_gpu" else nms_normal_gpu)(boxes_for_nms[:, 0:7], box_scores_nms, nms_thresh)
         selected = indices[keep_idx[:post_max]]
     if score_thresh is not None:
         original_idxs = scores_mask.nonzero().view(-1)
@@ -135,12 +164,12 @@ def generate_predicted_boxes(cls_preds, box_preds, dir_cls_preds, anchors, dir_o
 
 
 # --- reference: OPCD/pcdet/models/detectors/detector3d_template.py:178-284 (MULTI_CLASSES_NMS False) --
-def post_processing(batch_cls_preds, batch_box_preds, score_thresh=0.1, nms_thresh=0.01, pre_max=4096, post_max=500):
-    box_preds = batch_box_preds[0]
-    cls_preds = torch.sigmoid(batch_cls_preds[0])
+def post_processing(batch_cls_preds, batch_box_preds, score_thresh=0.1, nms_thresh=0.01, pre_max=4096, post_max=500, index=0, nms_type="nms_gpu"):
+    box_preds = batch_box_preds[index]
+    cls_preds = torch.sigmoid(batch_cls_preds[index])
     cls_preds, label_preds = torch.max(cls_preds, dim=-1)
     label_preds = label_preds + 1
-    selected, selected_scores = class_agnostic_nms(cls_preds, box_preds, nms_thresh, pre_max, post_max, score_thresh)
+    selected, selected_scores = class_agnostic_nms(cls_preds, box_preds, nms_thresh, pre_max, post_max, score_thresh, nms_type)
     return {"pred_boxes": box_preds[selected], "pred_scores": selected_scores, "pred_labels": label_preds[selected]}
 
 
@@ -151,6 +180,12 @@ def pp_anchor_post(cls_preds, box_preds, dir_preds, anchor_range, anchor_sizes, 
     post = {k: kw.pop(k) for k in ("score_thresh", "nms_thresh", "pre_max", "post_max") if k in kw}
     c, b = generate_predicted_boxes(cls_preds, box_preds, dir_preds, anchors, **kw)
     return post_processing(c, b, **post)
+
+
+def pp_anchor_post_batch(cls_preds, box_preds, dir_preds, *a, **kw):
+    """A batch [B,H,W,*]: the per-sample loop of Detector3DTemplate.post_processing (detector3d_template.py:196-199) —
+    every sample is the single-frame chain on its own slice."""
+    return [pp_anchor_post(cls_preds[b], box_preds[b], None if dir_preds is None else dir_preds[b], *a, **dict(kw)) for b in range(cls_preds.shape[0])]
 
 
 # --- reference: OPCD/pcdet/models/model_utils/centernet_utils.py:118-151 ------------------------------
@@ -235,6 +270,13 @@ def centerhead_generate_predicted_boxes(heads, class_id_mapping_each_head, point
         scores.append(selected_scores)
         labels.append(final["pred_labels"][selected])
     return {"pred_boxes": torch.cat(boxes, 0), "pred_scores": torch.cat(scores, 0), "pred_labels": torch.cat(labels, 0) + 1}
+
+
+def centerhead_generate_predicted_boxes_batch(heads, *a, **kw):
+    """heads: per head a dict of [B,c,H,W] arrays; CenterHead.generate_predicted_boxes(batch_size, ...) keeps the samples
+    apart (ret_dict[k], center_head.py:257-300), so sample b is the single-frame chain on slice b."""
+    B = next(iter(heads[0].values())).shape[0]
+    return [centerhead_generate_predicted_boxes([{k: v[b] for k, v in h.items()} for h in heads], *a, **dict(kw)) for b in range(B)]
 
 
 # --- reference: clients/postprocess/detector_3d_postprocess.py:55-64, 98-133 --------------------------

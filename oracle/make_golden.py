@@ -293,6 +293,206 @@ def golden_eval():
     save("eval", **out)
 
 
+def spread_scores(logits, rng, thresh=0.1, rel_gap=4e-6, fresh=lambda rng, n: rng.normal(-5.0, 1.2, n)):
+    """Re-draws logits until the sigmoid scores >= thresh (as torch computes them) are pairwise more than rel_gap apart,
+    so that neither torch.topk's unspecified tie order nor the ulps between two exp() implementations can change an
+    order the golden depends on."""
+    x = logits.reshape(-1).astype(np.float32)
+    for _ in range(200):
+        s = torch.sigmoid(torch.from_numpy(x)).numpy()
+        cand = np.nonzero(s >= thresh * 0.98)[0]
+        o = cand[np.argsort(s[cand], kind="stable")]
+        close = np.nonzero(np.diff(s[o]) <= rel_gap * s[o][1:])[0]
+        if close.size == 0:
+            return x.reshape(logits.shape)
+        x[o[close]] = fresh(rng, close.size).astype(np.float32)
+    raise RuntimeError("could not separate the scores")
+
+
+def golden_utils_preprocess():
+    """utils/preprocess.py::image_adjust (:127-175) run unmodified. cv2 path (pil=False, the reachable one): a PNG on
+    disk -> imread -> resize(w,h) -> BGR2RGB -> CHW -> /255, for every `scaling` value (the cv2 path ignores it).
+    PIL path (:133-167): unreachable as shipped, because `Image` is rebound to sensor_msgs.msg.Image (:7 vs :10); it is
+    run here with that one global bound back to PIL.Image — the module's own first import — on frames already at
+    (w,h), so that Pillow's resize is the identity and what is pinned is the scaling arithmetic of :147-159 and the
+    NCHW/NHWC choice of :161-165."""
+    import tempfile
+    import types
+    import cv2
+    import PIL.Image
+    ref_harness.communicator()                       # installs the rospy / sensor_msgs / cv_bridge / tritonclient placeholders
+    up = ref_harness.load_file("ref_utils_preprocess", "utils/preprocess.py")
+    up.mc.ModelInput = types.SimpleNamespace(FORMAT_NCHW=2, FORMAT_NHWC=1, FORMAT_NONE=0)
+    out = {}
+    cases = [(synth.image_smooth(180, 320, synth.seed_for(1, 50)), 160, 96), (synth.image_noise(97, 131, synth.seed_for(1, 51)), 64, 48),
+             (synth.image_noise(120, 200, synth.seed_for(1, 52)), 100, 60)]
+    with tempfile.TemporaryDirectory() as d:
+        for k, (bgr, w, h) in enumerate(cases):
+            path = os.path.join(d, f"f{k}.png")
+            cv2.imwrite(path, bgr)
+            res = [up.image_adjust(path, None, "FP32", 3, h, w, sc, pil=False) for sc in ("NONE", "INCEPTION", "VGG", "COCO")]
+            assert all(np.array_equal(res[0], r) for r in res)
+            out[f"cv_bgr{k}"], out[f"cv_wh{k}"], out[f"cv_out{k}"] = bgr, np.array([w, h]), res[0]
+    saved = up.Image
+    up.Image = PIL.Image
+    try:
+        rgb = synth.image_noise(48, 64, synth.seed_for(1, 53))
+        out["pil_rgb"] = rgb
+        for sc in ("NONE", "INCEPTION", "VGG", "COCO"):
+            for fmt, tag in ((2, "nchw"), (1, "nhwc")):
+                r = up.image_adjust(PIL.Image.fromarray(rgb), fmt, "FP32", 3, 48, 64, sc, pil=True)
+                assert r.dtype == np.float32
+                out[f"pil_{sc}_{tag}"] = r
+    finally:
+        up.Image = saved
+    save("utils_preprocess", **out)
+
+
+def golden_dynamic_vfe():
+    """DynamicPillarVFE.forward (OPCD/pcdet/models/backbones_3d/vfe/dynamic_pillar_vfe.py:90-142) run unmodified up to the
+    PFN layers (pfn_layers emptied, as golden_pillar_vfe does) on a batch of two small nuScenes-like clouds; torch_scatter
+    is the stand-in of ref_harness.install_torch_scatter, `.cuda()` is a no-op, and torch.unique is wrapped only to record
+    the inverse index the function keeps local."""
+    ref_harness.install_torch_scatter()
+    mod = ref_harness.pcdet("models.backbones_3d.vfe.dynamic_pillar_vfe")
+    rng_, vs = [-51.2, -51.2, -5.0, 51.2, 51.2, 3.0], [0.2, 0.2, 8.0]
+    a = synth.lidar_multisweep(synth.seed_for(5, 60), sweeps=2, beams=8, azimuths=300)
+    b = synth.lidar_multisweep(synth.seed_for(5, 61), sweeps=3, beams=6, azimuths=250)
+    pts = np.concatenate([np.concatenate([np.zeros((len(a), 1), np.float32), a], 1), np.concatenate([np.ones((len(b), 1), np.float32), b], 1)])
+    pts[5, 1] = 1e3                                   # out of range rows
+    pts[77, 2] = -51.3
+    cfg = ref_harness._Cfg(USE_NORM=True, WITH_DISTANCE=False, USE_ABSLOTE_XYZ=True, NUM_FILTERS=[64])
+    with ref_harness.no_cuda():
+        vfe = mod.DynamicPillarVFE(cfg, 5, vs, [512, 512, 1], rng_)
+        vfe.pfn_layers = torch.nn.ModuleList([])
+        seen = {}
+        real_unique = torch.unique
+
+        def spy(*a, **k):
+            r = real_unique(*a, **k)
+            seen["inv"] = r[1]
+            return r
+        torch.unique = spy
+        try:
+            bd = vfe.forward({"points": torch.from_numpy(pts)})
+        finally:
+            torch.unique = real_unique
+    feats = bd["pillar_features"].numpy()
+    assert feats.shape[1] == 11 and feats.shape[0] < len(pts)
+    save("dynamic_vfe", points=pts, range=np.array(rng_, np.float64), vsize=np.array(vs, np.float64), grid=np.array([512, 512, 1]),
+         feats=feats, unq_inv=seen["inv"].numpy(), voxel_coords=bd["voxel_coords"].numpy())
+
+
+def golden_pcdet_post():
+    """The pcdet glue that runs server-side behind the 3D clients, unmodified, on batches of two frames:
+    (pp)  AnchorHeadTemplate.generate_anchors + generate_predicted_boxes (anchor_head_template.py:37-52, 225-272) ->
+          Detector3DTemplate.post_processing (detector3d_template.py:178-284) -> model_nms_utils.class_agnostic_nms (:6-25)
+          -> iou3d_nms_utils.nms_gpu (:84-99), with the compiled extension replaced by ref_harness.install_iou3d_nms_cuda
+          (the reference's own iou_bev + its host sweep); the pointpillar.yaml head on a 48x48 map;
+    (cp)  CenterHead.generate_predicted_boxes (center_head.py:253-304): two heads (1 + 2 classes) on a 32x32 map;
+    (nms) class_agnostic_nms alone, NMS_TYPE nms_gpu and nms_normal_gpu, with and without score_thresh."""
+    C = ref_harness._Cfg
+    ref_harness.install_iou3d_nms_cuda()
+    rng = np.random.default_rng(4040)
+    out = {}
+    with ref_harness.no_cuda():
+        aht = ref_harness.pcdet("models.dense_heads.anchor_head_template")
+        det = ref_harness.pcdet("models.detectors.detector3d_template")
+        ch = ref_harness.pcdet("models.dense_heads.center_head")
+        nmsu = ref_harness.pcdet("models.model_utils.model_nms_utils")
+        bcu = ref_harness.pcdet("utils.box_coder_utils")
+        # ---- (pp)
+        B, H, W = 2, 48, 48
+        pc_range = np.array([0, -7.68, -3, 15.36, 7.68, 1], np.float32)
+        gen_cfg = [C(class_name=n, anchor_sizes=[s], anchor_rotations=[0, 1.57], anchor_bottom_heights=[b], align_center=False, feature_map_stride=2,
+                     matched_threshold=0.6, unmatched_threshold=0.45)
+                   for n, s, b in (("Car", [3.9, 1.6, 1.56], -1.78), ("Pedestrian", [0.8, 0.6, 1.73], -0.6), ("Cyclist", [1.76, 0.6, 1.73], -0.6))]
+        head = aht.AnchorHeadTemplate.__new__(aht.AnchorHeadTemplate)
+        torch.nn.Module.__init__(head)
+        head.model_cfg = C(DIR_OFFSET=0.78539, DIR_LIMIT_OFFSET=0.0, NUM_DIR_BINS=2)
+        head.use_multihead = False
+        head.box_coder = bcu.ResidualCoder()
+        anchors, head.num_anchors_per_location = aht.AnchorHeadTemplate.generate_anchors(gen_cfg, grid_size=np.array([96, 96, 1]),
+                                                                                         point_cloud_range=pc_range, anchor_ndim=7)
+        head.anchors = [x.cuda() for x in anchors]
+        cls = rng.normal(-5.0, 1.2, (B, H, W, 6, 3))
+        for b in range(B):
+            for _ in range(30):
+                y, x, k, c = rng.integers(2, H - 2), rng.integers(2, W - 2), rng.integers(0, 6), rng.integers(0, 3)
+                cls[b, y - 1:y + 2, x - 1:x + 2, k, c] += rng.uniform(4, 8)
+        cls = spread_scores(np.clip(cls, -8.9, 6.0), rng).reshape(B, H, W, 18)
+        box = rng.normal(0, 0.3, (B, H, W, 42)).astype(np.float32)
+        dirp = synth._quantise(rng.normal(0, 1, (B, H, W, 12)))
+        bc, bb = head.generate_predicted_boxes(B, torch.from_numpy(cls), torch.from_numpy(box), torch.from_numpy(dirp))
+        d = det.Detector3DTemplate.__new__(det.Detector3DTemplate)
+        torch.nn.Module.__init__(d)
+        d.num_class = 3
+        d.model_cfg = C(POST_PROCESSING=C(RECALL_THRESH_LIST=[0.3, 0.5, 0.7], SCORE_THRESH=0.1, OUTPUT_RAW_SCORE=False, EVAL_METRIC="kitti",
+                                          NMS_CONFIG=C(MULTI_CLASSES_NMS=False, NMS_TYPE="nms_gpu", NMS_THRESH=0.01, NMS_PRE_MAXSIZE=4096, NMS_POST_MAXSIZE=500)))
+        preds, _ = d.post_processing({"batch_size": B, "batch_cls_preds": bc, "batch_box_preds": bb, "cls_preds_normalized": False})
+        out["pp_range"], out["pp_cls"], out["pp_box"], out["pp_dir"] = pc_range, cls, box, dirp
+        for b in range(B):
+            assert 20 < preds[b]["pred_boxes"].shape[0] <= 500
+            out[f"pp_boxes{b}"], out[f"pp_scores{b}"], out[f"pp_labels{b}"] = (preds[b][k].numpy() for k in ("pred_boxes", "pred_scores", "pred_labels"))
+        # ---- (cp)
+        hd = ch.CenterHead.__new__(ch.CenterHead)
+        torch.nn.Module.__init__(hd)
+        hd.model_cfg = C(POST_PROCESSING=C(SCORE_THRESH=0.1, POST_CENTER_LIMIT_RANGE=[-61.2, -61.2, -10.0, 61.2, 61.2, 10.0], MAX_OBJ_PER_SAMPLE=60,
+                                           NMS_CONFIG=C(NMS_TYPE="nms_gpu", NMS_THRESH=0.2, NMS_PRE_MAXSIZE=1000, NMS_POST_MAXSIZE=30)))
+        hd.separate_head_cfg = C(HEAD_ORDER=["center", "center_z", "dim", "rot", "vel"])
+        hd.point_cloud_range, hd.voxel_size, hd.feature_map_stride = [-51.2, -51.2, -5.0, 51.2, 51.2, 3.0], [0.2, 0.2, 8.0], 4
+        hd.class_id_mapping_each_head = [torch.tensor([0]), torch.tensor([1, 2])]
+        h = w = 32
+        yy, xx = np.mgrid[0:h, 0:w]
+        pred_dicts = []
+        for hi, c in enumerate((1, 2)):
+            hm = rng.normal(-6, 1, (B, c, h, w))
+            for b in range(B):
+                for _ in range(14):
+                    k, py, px = rng.integers(0, c), rng.uniform(0, h), rng.uniform(0, w)
+                    hm[b, k] += 8.0 * np.exp(-((yy - py) ** 2 + (xx - px) ** 2) / (2 * 1.5 ** 2))
+            hm = spread_scores(np.clip(hm, -8.9, 6.0), rng, thresh=0.02, fresh=lambda r, n: r.normal(-6, 1, n))
+            ang = rng.uniform(-np.pi, np.pi, (B, h, w))
+            pd = {"hm": hm, "center": rng.uniform(0, 1, (B, 2, h, w)), "center_z": rng.normal(-1, 0.5, (B, 1, h, w)),
+                  "dim": rng.normal(0.7, 0.3, (B, 3, h, w)), "rot": np.stack([np.cos(ang), np.sin(ang)], 1), "vel": rng.normal(0, 2, (B, 2, h, w))}
+            pd = {k: torch.from_numpy(np.ascontiguousarray(v, np.float32)) for k, v in pd.items()}
+            pred_dicts.append(pd)
+            for k, v in pd.items():
+                out[f"cp{hi}_{k}"] = v.numpy()
+        ret = hd.generate_predicted_boxes(B, pred_dicts)
+        for b in range(B):
+            assert ret[b]["pred_boxes"].shape[0] > 8
+            out[f"cp_boxes{b}"], out[f"cp_scores{b}"], out[f"cp_labels{b}"] = (ret[b][k].numpy() for k in ("pred_boxes", "pred_scores", "pred_labels"))
+        # ---- (nms)
+        boxes = synth.random_boxes7(1500, 909, extent=25.0)
+        scores = torch.sigmoid(torch.from_numpy(spread_scores(rng.normal(-1, 2, 1500), rng, thresh=0.0, fresh=lambda r, n: r.normal(-1, 2, n)))).numpy()
+        out["nms_boxes"], out["nms_scores"] = boxes, scores
+        for tag, typ, thr, st in (("rot", "nms_gpu", 0.1, 0.2), ("rot_all", "nms_gpu", 0.3, None), ("normal", "nms_normal_gpu", 0.1, 0.2)):
+            cfgn = C(NMS_TYPE=typ, NMS_THRESH=thr, NMS_PRE_MAXSIZE=1000, NMS_POST_MAXSIZE=200)
+            sel, ssc = nmsu.class_agnostic_nms(torch.from_numpy(scores), torch.from_numpy(boxes), cfgn, score_thresh=st)
+            assert 30 < sel.numel() <= 200
+            out[f"nms_{tag}_cfg"] = np.array([thr, -1.0 if st is None else st, 1000, 200], np.float64)
+            out[f"nms_{tag}_sel"], out[f"nms_{tag}_scores"] = sel.numpy(), ssc.numpy()
+    save("pcdet_post", **out)
+
+
+def golden_low_score_nu():
+    """PointPillarPostprocess.remove_low_score_nu / get_annotations_indices (clients/postprocess/detector_3d_postprocess.py
+    :55-64, :98-133) run unmodified (jsk_recognition_msgs is a placeholder: its classes are only named in an import)."""
+    c = ref_harness.clients()
+    post = c.PointPillarPostprocess()
+    rng = np.random.default_rng(31)
+    n = 400
+    labels = rng.integers(0, 10, n).astype(np.int64)
+    scores = (np.round(rng.uniform(0, 1, n) * 20) / 20).astype(np.float32)      # many values exactly on a threshold (>=)
+    boxes = rng.normal(0, 10, (n, 9)).astype(np.float32)
+    res = post.remove_low_score_nu({"box3d_lidar": boxes, "scores": scores, "labels": labels, "metadata": {"token": "x"}}, 0.45)
+    assert "metadata" not in res and 50 < len(res["scores"]) < n
+    idx = post.get_annotations_indices(6, 0.15, labels, scores)
+    save("low_score_nu", boxes=boxes, scores=scores, labels=labels, out_boxes=res["box3d_lidar"], out_scores=res["scores"], out_labels=res["labels"],
+         motorcycle_idx=np.array(idx, np.int64))
+
+
 golden_overlay.__doc__ = golden_overlay.__doc__ % np.__version__
 
 

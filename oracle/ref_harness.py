@@ -37,6 +37,9 @@ def clients():
         for n in ["tritonclient", "tritonclient.grpc", "tritonclient.grpc.model_config_pb2",
                   "tritonclient.grpc.service_pb2", "tritonclient.grpc.service_pb2_grpc"]:
             _stub(n)
+        for n in ["jsk_recognition_msgs", "jsk_recognition_msgs.msg"]:      # ROS message classes: named, never instantiated here
+            if n not in sys.modules:
+                sys.modules[n] = _AnyModule(n)
         saved_path, saved_cwd = list(sys.path), os.getcwd()
         saved_mods = {k: v for k, v in sys.modules.items() if k == "clients" or k.startswith("clients.")}
         for k in saved_mods:
@@ -165,3 +168,150 @@ def communicator():
             os.chdir(saved_cwd)
             sys.path[:] = saved_path
     return _communicator
+
+
+# ---- the vendored pcdet tree as an importable package --------------------------------------------------------------
+# `import pcdet` fails here (its __init__ wants a generated version.py and every sub-package __init__ imports compiled
+# ops), so the tree is mounted under the name `ref_pcdet` by a finder with three rules: a name that is a .py file of
+# the tree is executed UNMODIFIED; a name that is a directory becomes an empty package (its __init__.py is not run);
+# any other name below ref_pcdet (compiled extensions such as iou3d_nms_cuda, generated files) is a placeholder module.
+# Third-party packages the tree imports and this image lacks (spconv, torch_scatter, SharedArray, ...) are placeholders
+# too, except where a golden script installs a working stand-in first (torch_scatter, iou3d_nms_cuda below).
+import importlib.abc
+import importlib.machinery
+
+PCDET = "ref_pcdet"
+
+
+class _PcdetFinder(importlib.abc.MetaPathFinder, importlib.abc.Loader):
+    def find_spec(self, fullname, path=None, target=None):
+        if fullname != PCDET and not fullname.startswith(PCDET + "."):
+            return None
+        rel = fullname.split(".")[1:]
+        base = os.path.join(OPCD, "pcdet", *rel)
+        if os.path.isfile(base + ".py"):
+            return importlib.util.spec_from_file_location(fullname, base + ".py")
+        if os.path.isdir(base):
+            spec = importlib.machinery.ModuleSpec(fullname, self, is_package=True)
+            spec.submodule_search_locations = [base]
+            return spec
+        return importlib.machinery.ModuleSpec(fullname, self)
+
+    def create_module(self, spec):
+        if spec.submodule_search_locations is None:
+            return _AnyModule(spec.name)
+        return None
+
+    def exec_module(self, module):
+        pass
+
+
+def pcdet(module):
+    """Import `pcdet.<module>` of the vendored OpenPCDet tree, e.g. pcdet("models.model_utils.model_nms_utils")."""
+    if not any(isinstance(f, _PcdetFinder) for f in sys.meta_path):
+        sys.meta_path.insert(0, _PcdetFinder())
+        for n in ["SharedArray", "spconv", "spconv.pytorch", "cumm", "easydict", "tensorboardX", "numba", "kornia"]:
+            try:
+                importlib.import_module(n)
+            except Exception:
+                if n not in sys.modules:
+                    sys.modules[n] = _AnyModule(n)
+    return importlib.import_module(PCDET + "." + module)
+
+
+class no_cuda:
+    """Tensor.cuda() / Module.cuda() as no-ops while reference code that hard-codes `.cuda()` runs (no GPU here)."""
+
+    def __enter__(self):
+        import torch
+        self._t, self._m = torch.Tensor.cuda, torch.nn.Module.cuda
+        torch.Tensor.cuda = lambda s, *a, **k: s
+        torch.nn.Module.cuda = lambda s, *a, **k: s
+
+    def __exit__(self, *exc):
+        import torch
+        torch.Tensor.cuda, torch.nn.Module.cuda = self._t, self._m
+
+
+def install_torch_scatter():
+    """torch_scatter is not in this image. Stand-in with its published semantics for the two calls the tree makes
+    (dynamic_pillar_vfe.py:40,105): scatter_mean = scatter_add in input order / count (count clamped to 1),
+    scatter_max = per-group maximum and arg-max."""
+    import torch
+    if "torch_scatter" in sys.modules and hasattr(sys.modules["torch_scatter"], "_tcb_standin"):
+        return
+    m = types.ModuleType("torch_scatter")
+    m._tcb_standin = True
+
+    def scatter_mean(src, index, dim=0):
+        assert dim == 0
+        n = int(index.max()) + 1 if index.numel() else 0
+        out = torch.zeros((n,) + tuple(src.shape[1:]), dtype=src.dtype).index_add_(0, index, src)
+        cnt = torch.zeros((n,), dtype=src.dtype).index_add_(0, index, torch.ones_like(index, dtype=src.dtype)).clamp_(min=1)
+        return out / cnt.view((n,) + (1,) * (src.dim() - 1))
+
+    def scatter_max(src, index, dim=0):
+        assert dim == 0
+        n = int(index.max()) + 1 if index.numel() else 0
+        idx = index.view((-1,) + (1,) * (src.dim() - 1)).expand_as(src)
+        out = torch.full((n,) + tuple(src.shape[1:]), float("-inf"), dtype=src.dtype).scatter_reduce_(0, idx, src, "amax", include_self=True)
+        return out, None
+
+    m.scatter_mean, m.scatter_max = scatter_mean, scatter_max
+    sys.modules["torch_scatter"] = m
+
+
+def install_iou3d_nms_cuda():
+    """The compiled extension behind pcdet.ops.iou3d_nms.iou3d_nms_utils, rebuilt for the CPU from the reference's own
+    parts: the pairwise test is the reference's iou_bev as compiled from its iou3d_cpu.cpp (oracle/_ref/libiou3d_ref.so;
+    same arithmetic as the device function, iou3d_nms_kernel.cu:227-234), the mask layout and the host sweep are
+    iou3d_nms.cpp:90-136 (box i suppresses a later box j when iou_bev(i, j) > thresh). nms_normal_gpu uses the
+    axis-aligned overlap of iou3d_nms_kernel.cu:314-325."""
+    import ctypes
+    import numpy as np
+    import torch
+    name = PCDET + ".ops.iou3d_nms.iou3d_nms_cuda"
+    if name in sys.modules and hasattr(sys.modules[name], "_tcb_standin"):
+        return
+    pcdet("ops.iou3d_nms")    # the package first
+    so = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "libiou3d_ref.so")
+    ref = ctypes.CDLL(so)
+    m = types.ModuleType(name)
+    m._tcb_standin = True
+
+    def sweep(over, keep):
+        n = over.shape[0]
+        removed = np.zeros(n, bool)
+        k = 0
+        for i in range(n):
+            if not removed[i]:
+                keep[k] = i
+                k += 1
+                removed[i + 1:] |= over[i, i + 1:]
+        return k
+
+    def nms_gpu(boxes, keep, thresh):
+        b = np.ascontiguousarray(boxes.detach().numpy(), np.float32)
+        n = b.shape[0]
+        iou = np.zeros((n, n), np.float32)
+        P = ctypes.c_void_p
+        if n:
+            ref.ref_boxes_iou_bev_cpu(P(b.ctypes.data), n, P(b.ctypes.data), n, P(iou.ctypes.data))
+        return sweep(iou > np.float32(thresh), keep)
+
+    def nms_normal_gpu(boxes, keep, thresh):
+        b = np.ascontiguousarray(boxes.detach().numpy(), np.float32)
+        f = np.float32
+        x1, y1 = b[:, 0] - b[:, 3] / f(2), b[:, 1] - b[:, 4] / f(2)
+        x2, y2 = b[:, 0] + b[:, 3] / f(2), b[:, 1] + b[:, 4] / f(2)
+        lx, rx = np.maximum(x1[:, None], x1[None]), np.minimum(x2[:, None], x2[None])
+        ty, by = np.maximum(y1[:, None], y1[None]), np.minimum(y2[:, None], y2[None])
+        w, h = np.maximum(rx - lx, f(0)), np.maximum(by - ty, f(0))
+        inter = w * h
+        area = b[:, 3] * b[:, 4]
+        iou = inter / np.maximum(area[:, None] + area[None] - inter, f(1e-8))
+        return sweep(iou > f(thresh), keep)
+
+    m.nms_gpu, m.nms_normal_gpu = nms_gpu, nms_normal_gpu
+    sys.modules[name] = m
+    setattr(sys.modules[PCDET + ".ops.iou3d_nms"], "iou3d_nms_cuda", m)

@@ -145,3 +145,55 @@ def test_class_score_filter(engine):
     want = box3d.remove_low_score_nu({"labels": labels, "scores": scores, "i": np.arange(400)})["i"]
     idx, cnt = engine.class_score_filter(torch.from_numpy(labels).cuda(), torch.from_numpy(scores).cuda(), box3d.NUSC_GROUPS)
     assert idx[:int(cnt.item())].cpu().tolist() == want.tolist()
+
+
+PP_SMALL = dict(anchor_sizes=KITTI_ANCHORS["anchor_sizes"], anchor_bottoms=KITTI_ANCHORS["anchor_bottoms"],
+                anchor_rotations=KITTI_ANCHORS["anchor_rotations"])
+
+
+def _same_as_reference(gb, gs, gl, g, tag, b):
+    """Against outputs of the unmodified pcdet code: rows, order and labels identical, floats within 1e-5."""
+    assert gb.shape == g[f"{tag}_boxes{b}"].shape
+    assert np.array_equal(gl, g[f"{tag}_labels{b}"])
+    _close(gs, g[f"{tag}_scores{b}"])
+    _close(gb, g[f"{tag}_boxes{b}"], rtol=1e-5, atol=1e-5)
+
+
+def test_pp_reference_glue_golden(engine):
+    """The whole PointPillars chain as pcdet runs it (AnchorHeadTemplate.generate_predicted_boxes -> post_processing ->
+    class_agnostic_nms -> nms_gpu, unmodified: oracle/make_golden.py golden_pcdet_post), batch of two."""
+    g = golden("pcdet_post")
+    for b in range(2):
+        gb, gs, gl = _pp_gpu(engine, g["pp_cls"][b], g["pp_box"][b], g["pp_dir"][b], anchor_range=g["pp_range"].tolist(), **PP_SMALL)
+        _same_as_reference(gb, gs, gl, g, "pp", b)
+
+
+def test_centerpoint_reference_glue_golden(engine):
+    """CenterHead.generate_predicted_boxes run unmodified on a batch of two, two heads (1 + 2 classes), K=60, post 30."""
+    g = golden("pcdet_post")
+    for b in range(2):
+        heads = [{k: np.ascontiguousarray(g[f"cp{h}_{k}"][b]) for k in ("hm", "center", "center_z", "dim", "rot", "vel")} for h in range(2)]
+        gb, gs, gl = _cp_gpu(engine, heads, class_map=[[0], [1, 2]], k=60, score_thresh=0.1, nms_thresh=0.2, pre_max=1000, post_max=30)
+        _same_as_reference(gb, gs, gl, g, "cp", b)
+
+
+@pytest.mark.parametrize("tag", ["rot", "rot_all"])
+def test_class_agnostic_nms_reference_golden(engine, tag):
+    """model_nms_utils.class_agnostic_nms run unmodified (score mask -> topk -> nms_gpu -> post cut -> index map)."""
+    g = golden("pcdet_post")
+    thr, st, pre, post = g[f"nms_{tag}_cfg"]
+    boxes, scores = g["nms_boxes"], g["nms_scores"]
+    idx = np.nonzero(scores >= np.float32(st))[0] if st >= 0 else np.arange(len(scores))
+    keep, cnt = engine.rotated_nms(torch.from_numpy(boxes[idx]).cuda(), torch.from_numpy(scores[idx]).cuda(), float(thr), int(pre), int(post))
+    sel = idx[keep[:int(cnt.item())].cpu().numpy()]
+    assert np.array_equal(sel, g[f"nms_{tag}_sel"])
+
+
+def test_remove_low_score_nu_reference_golden(engine):
+    from triton_client_b200.clients import PointPillarPostprocess
+    g = golden("low_score_nu")
+    post = PointPillarPostprocess(engine=engine)
+    res = post.remove_low_score_nu({"box3d_lidar": g["boxes"], "scores": g["scores"], "labels": g["labels"], "metadata": {}}, 0.45)
+    assert "metadata" not in res
+    assert np.array_equal(res["box3d_lidar"], g["out_boxes"]) and np.array_equal(res["scores"], g["out_scores"]) and np.array_equal(res["labels"], g["out_labels"])
+    assert post.get_annotations_indices(6, 0.15, g["labels"], g["scores"]) == g["motorcycle_idx"].tolist()

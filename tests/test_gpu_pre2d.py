@@ -114,6 +114,26 @@ def test_scaling_modes_swap_and_pad(engine):
     assert np.array_equal(got, pre2d.image_adjust_ros(img))
 
 
+def test_utils_image_adjust_reference_golden(engine):
+    """utils/preprocess.py::image_adjust run unmodified (golden_utils_preprocess): the cv2 path through the drop-in twin
+    (file path in, like the reference), and the scaling modes of its PIL path as kernel parameters."""
+    import cv2
+    import tempfile, os
+    from triton_client_b200.utils import preprocess as up
+    g = golden("utils_preprocess")
+    with tempfile.TemporaryDirectory() as d:
+        for k in range(3):
+            w, h = (int(v) for v in g[f"cv_wh{k}"])
+            path = os.path.join(d, f"f{k}.png")
+            cv2.imwrite(path, g[f"cv_bgr{k}"])
+            assert np.array_equal(up.image_adjust(path, w, h, "COCO", engine=engine), g[f"cv_out{k}"])
+            assert np.array_equal(up.image_adjust(g[f"cv_bgr{k}"], w, h, engine=engine), g[f"cv_out{k}"])
+    rgb = g["pil_rgb"]
+    for sc in ("NONE", "INCEPTION", "VGG", "COCO"):
+        got = up.image_adjust(np.ascontiguousarray(rgb[:, :, ::-1]), rgb.shape[1], rgb.shape[0], sc, engine=engine)
+        assert np.array_equal(got[0], g[f"pil_{sc}_nchw"]), sc
+
+
 def test_strided_source_and_input_not_mutated(engine):
     big = torch.from_numpy(synth.image_noise(200, 300, 6)).cuda()
     view = big[10:150, 20:221]                      # row stride 900 B, offset not 16-B aligned

@@ -127,3 +127,16 @@ def test_dynamic_pillar_vfe_c5(engine):
 def test_dynamic_pillar_empty(engine):
     f, inv, c, counts = engine.dynamic_pillar(torch.full((10, 6), 1e4).cuda(), NUSC[0], NUSC[1])
     assert counts.cpu().tolist() == [0, 0]
+
+
+def test_dynamic_pillar_vfe_reference_golden(engine):
+    """DynamicPillarVFE.forward run unmodified (golden_dynamic_vfe): inverse index and voxel coords identical, raw features
+    and centre offsets identical, cluster offsets within 1e-5 (the mean is a float32 running sum there)."""
+    g = golden("dynamic_vfe")
+    f, inv, c, counts = engine.dynamic_pillar(torch.from_numpy(g["points"]).cuda(), g["range"].tolist(), g["vsize"].tolist(), batch_size=2)
+    nv, nu = (int(v) for v in counts.cpu())
+    assert nv == g["feats"].shape[0] and nu == g["voxel_coords"].shape[0]
+    assert np.array_equal(inv[:nv].cpu().numpy(), g["unq_inv"]) and np.array_equal(c[:nu].cpu().numpy(), g["voxel_coords"])
+    got = f[:nv].cpu().numpy()
+    assert np.array_equal(got[:, :5], g["feats"][:, :5]) and np.array_equal(got[:, 8:], g["feats"][:, 8:])
+    np.testing.assert_allclose(got[:, 5:8], g["feats"][:, 5:8], rtol=1e-5, atol=2e-5)

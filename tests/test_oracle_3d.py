@@ -88,3 +88,53 @@ def test_full_chain_runs_and_is_deterministic():
     r2 = box3d.pp_anchor_post(cls, box, dirp, **KITTI_ANCHORS)
     assert r1["pred_boxes"].shape[0] > 0 and torch.equal(r1["pred_boxes"], r2["pred_boxes"])
     assert r1["pred_labels"].min() >= 1 and r1["pred_labels"].max() <= 3
+
+
+PP_SMALL = dict(anchor_sizes=KITTI_ANCHORS["anchor_sizes"], anchor_bottoms=KITTI_ANCHORS["anchor_bottoms"],
+                anchor_rotations=KITTI_ANCHORS["anchor_rotations"])
+
+
+def _same_dets(got, g, tag, b, exact_cols=None):
+    """labels and row order exact; float columns exact where the restatement repeats torch's CPU arithmetic."""
+    assert np.array_equal(got["pred_labels"].numpy(), g[f"{tag}_labels{b}"])
+    assert np.array_equal(got["pred_scores"].numpy(), g[f"{tag}_scores{b}"])
+    bx, want = got["pred_boxes"].numpy(), g[f"{tag}_boxes{b}"]
+    cols = [c for c in range(want.shape[1]) if c != 6]
+    assert bx.shape == want.shape and np.array_equal(bx[:, cols], want[:, cols])
+    np.testing.assert_allclose(bx[:, 6], want[:, 6], rtol=2e-7, atol=1e-7)     # torch's vectorised atan2 depends on the tensor's position in the batch (1 ulp)
+
+
+def test_golden_pointpillars_glue_batch():
+    """generate_predicted_boxes -> post_processing -> class_agnostic_nms -> nms_gpu run unmodified on a batch of two
+    (oracle/make_golden.py: golden_pcdet_post) vs the restated chain, sample by sample."""
+    g = golden("pcdet_post")
+    res = box3d.pp_anchor_post_batch(g["pp_cls"], g["pp_box"], g["pp_dir"], g["pp_range"], **PP_SMALL)
+    for b in range(2):
+        _same_dets(res[b], g, "pp", b)
+
+
+def test_golden_centerhead_glue_batch():
+    g = golden("pcdet_post")
+    heads = [{k: g[f"cp{h}_{k}"] for k in ("hm", "center", "center_z", "dim", "rot", "vel")} for h in range(2)]
+    res = box3d.centerhead_generate_predicted_boxes_batch(heads, [[0], [1, 2]], [-51.2, -51.2, -5.0, 51.2, 51.2, 3.0], [0.2, 0.2, 8.0], 4,
+                                                          [-61.2, -61.2, -10.0, 61.2, 61.2, 10.0], K=60, score_thresh=0.1, nms_thresh=0.2,
+                                                          pre_max=1000, post_max=30)
+    for b in range(2):
+        _same_dets(res[b], g, "cp", b)
+
+
+@pytest.mark.parametrize("tag,nms_type", [("rot", "nms_gpu"), ("rot_all", "nms_gpu"), ("normal", "nms_normal_gpu")])
+def test_golden_class_agnostic_nms(tag, nms_type):
+    g = golden("pcdet_post")
+    thr, st, pre, post = g[f"nms_{tag}_cfg"]
+    sel, sc = box3d.class_agnostic_nms(torch.from_numpy(g["nms_scores"]), torch.from_numpy(g["nms_boxes"]), float(thr), int(pre), int(post),
+                                       None if st < 0 else float(st), nms_type)
+    assert np.array_equal(sel.numpy(), g[f"nms_{tag}_sel"]) and np.array_equal(sc.numpy(), g[f"nms_{tag}_scores"])
+
+
+def test_golden_remove_low_score_nu():
+    g = golden("low_score_nu")
+    res = box3d.remove_low_score_nu({"box3d_lidar": g["boxes"], "scores": g["scores"], "labels": g["labels"], "metadata": {}})
+    assert np.array_equal(res["box3d_lidar"], g["out_boxes"]) and np.array_equal(res["scores"], g["out_scores"])
+    assert np.array_equal(res["labels"], g["out_labels"])
+    assert box3d.get_annotations_indices(6, 0.15, g["labels"], g["scores"]) == g["motorcycle_idx"].tolist()

@@ -61,3 +61,17 @@ def test_against_live_reference():
     img = np.random.default_rng(11).integers(0, 256, (90, 160, 3), dtype=np.uint8)
     ref = pre.image_adjust(cv2.resize(img, (64, 64)))
     assert np.array_equal(pre2d.preprocess_frame(img, 64, 64), ref)
+
+
+def test_golden_utils_image_adjust():
+    """utils/preprocess.py::image_adjust run unmodified (oracle/make_golden.py: golden_utils_preprocess): the cv2 path
+    (which ignores `scaling` and always divides by 255) and the scaling arithmetic of the PIL path."""
+    g = golden("utils_preprocess")
+    for k in range(3):
+        w, h = (int(v) for v in g[f"cv_wh{k}"])
+        assert np.array_equal(pre2d.image_adjust_utils(g[f"cv_bgr{k}"], w, h, "COCO"), g[f"cv_out{k}"])
+    rgb = g["pil_rgb"]
+    for sc in ("NONE", "INCEPTION", "VGG", "COCO"):
+        got = pre2d.image_adjust_utils(rgb[:, :, ::-1], rgb.shape[1], rgb.shape[0], sc)[0]      # the oracle flips BGR -> RGB
+        assert np.array_equal(got, g[f"pil_{sc}_nchw"]), sc
+        assert np.array_equal(np.transpose(got, (1, 2, 0)), g[f"pil_{sc}_nhwc"]), sc

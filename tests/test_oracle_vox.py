@@ -52,3 +52,11 @@ def test_mask_against_live_reference():
     pts = synth.lidar_sweep(42, beams=8, azimuths=100)
     rng = np.array(KITTI[0], np.float32)
     assert np.array_equal(cu.mask_points_by_range(pts, rng), ov.mask_points_by_range(pts, rng))
+
+
+def test_golden_dynamic_pillar_vfe():
+    """DynamicPillarVFE.forward run unmodified (oracle/make_golden.py: golden_dynamic_vfe) vs the restatement."""
+    g = golden("dynamic_vfe")
+    f, inv, c = ov.dynamic_pillar_vfe(g["points"], g["vsize"].tolist(), g["range"].tolist(), g["grid"].tolist())
+    assert np.array_equal(inv, g["unq_inv"]) and np.array_equal(c, g["voxel_coords"])
+    assert np.array_equal(f, g["feats"])
