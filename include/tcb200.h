@@ -173,28 +173,32 @@ int tcb_detectron_post(tcb_ctx* ctx, int num_levels, const float* const* logits_
 enum { TCB_VOX_CONTINUE = 0, TCB_VOX_BREAK = 1 };
 
 /*
- * Hard voxelisation of one sweep, bit-identical to the sequential first-seen scan of the voxel
- * generators the reference calls: spconv's VoxelGenerator via
+ * Hard voxelisation of a batch of b sweeps, every sweep bit-identical to the sequential first-seen scan of the
+ * voxel generators the reference calls: spconv's VoxelGenerator via
  * OPCD/pcdet/datasets/processor/data_processor.py:15-60,115-143 (PointpillarPreprocess.filter_pc,
  * clients/preprocess/preprocess_3d.py:33-51) and det3d's VoxelGenerator via
- * clients/preprocess/voxelize.py:19-24,38-42.
- * pts_dev: [n, pt_stride] f32 rows, the first nfeat (>= 3: x,y,z,...) columns are kept as features.
+ * clients/preprocess/voxelize.py:19-24,38-42. The batch is what the reference's layouts
+ * carry — the leading column of voxel_coords [b,z,y,x] (preprocess_3d.py:50, voxelize.py:46-47) is the sweep's
+ * index in the batch — and a sweep's result does not depend on what else is in the call.
+ * pts_dev: [n, pt_stride] f32 rows of all sweeps back to back, the first nfeat (>= 3: x,y,z,...) columns are
+ * kept as features; sweep_offsets_host: b+1 ascending row offsets (host ints, [0] = 0, [b] = n; ragged and
+ * empty sweeps allowed; NULL when b == 1). b <= 64.
  * range = {x0,y0,z0,x1,y1,z1}, vsize = {sx,sy,sz}; grid = round((max-min)/size).
- * overflow_mode: what happens at the (max_vox+1)-th new cell — TCB_VOX_CONTINUE drops that point and goes
- *   on (spconv), TCB_VOX_BREAK stops the scan (SECOND / det3d lineage).
+ * overflow_mode: what happens at the (max_vox+1)-th new cell of a sweep — TCB_VOX_CONTINUE drops that point and
+ *   goes on (spconv), TCB_VOX_BREAK stops the scan of that sweep (SECOND / det3d lineage).
  * f64_math: 0 = cell index computed in float32 from float32 range/size (KITTI .bin, Triton FP32),
  *   1 = in double (the det3d path as the reference client runs it on float64 arrays).
  * range_mask_xy: 1 applies mask_points_by_range first (OPCD/pcdet/utils/common_utils.py:60-63: x,y inclusive,
  *   z not tested). z_offset / intensity_col fuse the caller-side conditioning of
  *   communicator/ros_inference3d.py:127-128 (z += offset; column intensity_col /= its per-sweep max;
  *   0.f and -1 switch them off).
- * Outputs (caller-allocated for max_vox voxels): voxels [max_vox, max_pts, nfeat] f32 (rows < M written,
- * zero padded), coords [max_vox, 4] i32 as [batch=0, z, y, x] (preprocess_3d.py:50, voxelize.py:46-47),
- * num_pts [max_vox] i32, m_out_dev [1] i32 = M. Needs tcb_voxelize_workspace(n, max_vox) bytes.
+ * Outputs (caller-allocated): voxels [b, max_vox, max_pts, nfeat] f32 (rows < M_s of sweep s written, zero
+ * padded), coords [b, max_vox, 4] i32 as [s, z, y, x], num_pts [b, max_vox] i32, m_out_dev [b] i32 = M_s.
+ * Needs tcb_voxelize_workspace(n, b, max_vox, grid cells) bytes.
  */
-size_t tcb_voxelize_workspace(int n, int max_vox);
-int tcb_voxelize(tcb_ctx* ctx, const float* pts_dev, int n, int pt_stride, int nfeat, const double range[6],
-                 const double vsize[3], int max_pts, int max_vox, int overflow_mode, int f64_math,
+size_t tcb_voxelize_workspace(int n, int b, int max_vox, long long cells);
+int tcb_voxelize(tcb_ctx* ctx, const float* pts_dev, int n, const int* sweep_offsets_host, int b, int pt_stride, int nfeat,
+                 const double range[6], const double vsize[3], int max_pts, int max_vox, int overflow_mode, int f64_math,
                  int range_mask_xy, float z_offset, int intensity_col, float* voxels_dev, int* coords_dev,
                  int* num_pts_dev, int* m_out_dev, void* stream);
 
@@ -202,11 +206,12 @@ int tcb_voxelize(tcb_ctx* ctx, const float* pts_dev, int n, int pt_stride, int n
  * Pillar feature decoration, PillarVFE.forward up to the PFN layers
  * (OPCD/pcdet/models/backbones_3d/vfe/pillar_vfe.py:76-81,86-92,94-118): per voxel mean of xyz, offsets to
  * the mean and to the pillar centre, concatenated after the raw features, padded slots zeroed:
- * [M, max_pts, nfeat] -> [M, max_pts, nfeat+6]. M is read from m_dev when non-NULL (device-resident count
- * straight from tcb_voxelize, no host sync), else m_max is used; m_max bounds the launch.
+ * [b, m_max, max_pts, nfeat] -> [b, m_max, max_pts, nfeat+6] — the layout tcb_voxelize leaves (m_max = its
+ * max_vox). The voxel count of sweep s is read from m_dev[s] when m_dev is non-NULL (device-resident, straight
+ * from tcb_voxelize, no host sync), else all m_max rows of every sweep are decorated.
  */
 int tcb_pillar_decorate(tcb_ctx* ctx, const float* voxels_dev, const int* coords_dev, const int* num_pts_dev,
-                        const int* m_dev, int m_max, int max_pts, int nfeat, const double vsize[3],
+                        const int* m_dev, int b, int m_max, int max_pts, int nfeat, const double vsize[3],
                         const double range_min[3], float* out_dev, void* stream);
 
 /*

@@ -140,3 +140,70 @@ def test_dynamic_pillar_vfe_reference_golden(engine):
     got = f[:nv].cpu().numpy()
     assert np.array_equal(got[:, :5], g["feats"][:, :5]) and np.array_equal(got[:, 8:], g["feats"][:, 8:])
     np.testing.assert_allclose(got[:, 5:8], g["feats"][:, 5:8], rtol=1e-5, atol=2e-5)
+
+
+def _batch_of(sweeps):
+    offs = np.concatenate([[0], np.cumsum([len(s) for s in sweeps])]).astype(int).tolist()
+    return np.concatenate(sweeps).astype(np.float32), offs
+
+
+@pytest.mark.parametrize("cfg,p,mv,overflow,f", [
+    (KITTI, 32, 12000, "continue", 4), (KITTI, 32, 2000, "break", 4), (SHIPPED, 5, 40000, "continue", 4),
+    (NUSC, 20, 60000, "break", 5), (NUSC, 20, 3000, "break", 5), (NUSC, 20, 3000, "continue", 5),
+])
+def test_batched_sweeps_equal_their_single_calls_and_the_oracle(engine, cfg, p, mv, overflow, f):
+    """b sweeps in one call (ragged lengths, an empty sweep, one sweep entirely outside the range): every sweep's voxels,
+    coords, counts and order are those of the sequential scan of that sweep alone, the batch column is its index —
+    the layout of voxel_coords [b,z,y,x] (clients/preprocess/preprocess_3d.py:50)."""
+    mk = (lambda seed, **kw: synth.lidar_sweep(seed, **kw)) if f == 4 else \
+         (lambda seed, **kw: synth.lidar_multisweep(seed, sweeps=3, beams=kw.get("beams", 32), azimuths=kw.get("azimuths", 940)))
+    sweeps = [mk(8101), mk(8102, beams=16, azimuths=700), np.zeros((0, f), np.float32), mk(8103, beams=40, azimuths=1000)[:1025],
+              np.full((300, f), 1e4, np.float32), mk(8104, beams=8, azimuths=333)]
+    pts, offs = _batch_of(sweeps)
+    v, c, n, m = engine.voxelize(torch.from_numpy(pts).cuda(), cfg[0], cfg[1], p, mv, overflow=overflow, offsets=offs)
+    torch.cuda.synchronize()
+    assert v.shape == (len(sweeps), mv, p, f) and m.shape == (len(sweeps),)
+    for s, sw in enumerate(sweeps):
+        ms = int(m[s])
+        want = ov.points_to_voxel(sw, cfg[0], cfg[1], p, mv, overflow)
+        got = (v[s, :ms].cpu().numpy(), c[s, :ms].cpu().numpy(), n[s, :ms].cpu().numpy())
+        assert (got[1][:, 0] == s).all()
+        assert got[0].shape == want[0].shape and np.array_equal(got[1][:, 1:], want[1]) and np.array_equal(got[2], want[2])
+        assert np.array_equal(got[0], want[0])
+        one = _gpu_vox(engine, sw, cfg[0], cfg[1], p, mv, overflow=overflow)
+        assert np.array_equal(one[0], got[0]) and np.array_equal(one[1][:, 1:], got[1][:, 1:]) and np.array_equal(one[2], got[2])
+    assert int(m[2]) == 0 and int(m[4]) == 0
+
+
+def test_batched_conditioning_uses_each_sweeps_own_maximum(engine):
+    a, b = synth.lidar_sweep(8201, beams=16, azimuths=500), synth.lidar_sweep(8202, beams=16, azimuths=400)
+    a[:, 3] *= 37.0
+    b[:, 3] *= 5.0
+    pts, offs = _batch_of([a, b])
+    v, c, n, m = engine.voxelize(torch.from_numpy(pts).cuda(), KITTI[0], KITTI[1], 32, 40000, range_mask=True, z_offset=1.5,
+                                 intensity_col=3, offsets=offs)
+    for s, sw in enumerate((a, b)):
+        d = ov.filter_pc_pointpillar(ov.condition_points(sw, 1.5), *KITTI, 32, 40000)
+        ms = int(m[s])
+        assert np.array_equal(c[s, :ms, 1:].cpu().numpy(), d["voxel_coords"][:, 1:]) and np.array_equal(v[s, :ms].cpu().numpy(), d["voxels"])
+
+
+def test_batched_decoration(engine):
+    sweeps = [synth.lidar_sweep(8301), synth.lidar_sweep(8302, beams=32, azimuths=900), synth.lidar_sweep(8303, beams=8, azimuths=100)]
+    pts, offs = _batch_of(sweeps)
+    v, c, n, m = engine.voxelize(torch.from_numpy(pts).cuda(), *KITTI, 32, 12000, offsets=offs)
+    feats = engine.pillar_decorate(v, c, n, KITTI[1], KITTI[0], m=m)
+    assert feats.shape == (3, 12000, 32, 10)
+    for s in range(3):
+        ms = int(m[s])
+        want = ov.pillar_decorate(v[s, :ms].cpu().numpy(), c[s, :ms].cpu().numpy(), n[s, :ms].cpu().numpy(), KITTI[1], np.array(KITTI[0], np.float32))
+        np.testing.assert_allclose(feats[s, :ms].cpu().numpy(), want, rtol=1e-5, atol=2e-5)
+        one = engine.pillar_decorate(v[s].contiguous(), c[s].contiguous(), n[s].contiguous(), KITTI[1], KITTI[0], m=m[s:s + 1].contiguous())
+        assert torch.equal(one[:ms], feats[s, :ms])
+    # five features / 20 slots (the nuScenes pillars): rows of 20 and 44 bytes
+    cloud = synth.lidar_multisweep(8304, sweeps=2)
+    v, c, n, m = engine.voxelize(torch.from_numpy(cloud).cuda(), *NUSC, 20, 30000)
+    feats = engine.pillar_decorate(v, c, n, NUSC[1], NUSC[0], m=m)
+    ms = int(m[0])
+    want = ov.pillar_decorate(v[:ms].cpu().numpy(), c[:ms].cpu().numpy(), n[:ms].cpu().numpy(), NUSC[1], NUSC[0])
+    np.testing.assert_allclose(feats[:ms].cpu().numpy(), want, rtol=1e-5, atol=2e-5)

@@ -50,10 +50,10 @@ SIGNATURES = {
     "tcb_detectron_post": (c_int, [c_void_p, c_int, P(c_void_p), P(c_void_p), P(c_void_p), P(c_int), P(c_int), P(c_int), c_int, c_int,
                                    P(c_float), c_int, c_float, c_int, c_float, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                    c_void_p, c_void_p]),
-    "tcb_voxelize_workspace": (c_size_t, [c_int, c_int]),
-    "tcb_voxelize": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, P(c_double), P(c_double), c_int, c_int, c_int, c_int,
+    "tcb_voxelize_workspace": (c_size_t, [c_int, c_int, c_int, c_ll]),
+    "tcb_voxelize": (c_int, [c_void_p, c_void_p, c_int, P(c_int), c_int, c_int, c_int, P(c_double), P(c_double), c_int, c_int, c_int, c_int,
                              c_int, c_float, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
-    "tcb_pillar_decorate": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, P(c_double),
+    "tcb_pillar_decorate": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, P(c_double),
                                     P(c_double), c_void_p, c_void_p]),
     "tcb_dynamic_pillar_workspace": (c_size_t, [c_int, c_int, c_int, c_int]),
     "tcb_dynamic_pillar": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, P(c_double), P(c_double), c_void_p, c_void_p, c_void_p,

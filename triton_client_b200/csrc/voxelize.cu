@@ -6,15 +6,17 @@
 // point indices: voxel id = rank of the cell's FIRST point among all first points, slot inside the voxel
 // = rank of the point among the cell's points — bit-identical to the sequential scan.
 //
-//   K1 cells+hash : per point, x/y range mask (common_utils.py:60-63, inclusive, no z test), cell =
-//                   floor((p - min)/size) per axis in f32 (or f64), atomicCAS open-addressing insert of
-//                   the linear cell id, atomicMin(first point index), atomicAdd(point count)
-//   K2 count      : per 1024-point block, how many points are the first of their cell
+//   K1 cells      : per point, x/y range mask (common_utils.py:60-63, inclusive, no z test), cell =
+//                   floor((p - min)/size) per axis in f32 (or f64); table slot = the cell id itself (pillar
+//                   grids) or an atomicCAS open-addressing insert of it; atomicMin(first point index),
+//                   atomicAdd(point count) -> arrival position
+//   K2 mark       : per table slot, the cell's first point gets a record and its 1024-point block counts it
 //   K3 scan       : exclusive scan of the block counts (one CTA)
 //   K4 assign     : voxel id = block offset + in-block rank; coords; CSR segment; overflow break point
-//   K5 scatter    : point index -> its voxel's CSR segment (unordered, atomicAdd cursor)
-//   K6 gather     : one warp per voxel orders the segment by point index, keeps the first P, writes
-//                   the zero-padded (P, F) block and the count
+//   K5 scatter    : point index -> its arrival position in its voxel's CSR segment (unordered); zero-fills the voxels
+//   K6 place      : per point, slot = number of smaller indices in the segment; slots < P store their row
+//   (break mode: K7 counts each voxel's points before the sweep's break point)
+// A call takes a batch of sweeps (ragged, back to back in one array); tables, numbering and outputs are per sweep.
 //   decorate      : PillarVFE.forward decoration (OPCD/pcdet/models/backbones_3d/vfe/pillar_vfe.py:94-118)
 #include "common.cuh"
 // Kernels here are launched with programmatic stream serialization (TCB_KLAUNCH) and begin with pdl_enter(). Their const
@@ -25,30 +27,60 @@
 
 namespace {
 
-constexpr int VB = 1024;  // points per block in the ordered passes
+constexpr int VB = 1024;            // points per block; a block never straddles two sweeps
+constexpr int VOX_MAX_BATCH = 64;   // sweeps per call (the sweep table travels in the kernel parameters)
+
+// Sweeps of a batch lie back to back in one [n, pt_stride] array. Every kernel that walks the points uses blocks of VB
+// points cut per sweep, so a block's sweep is one lookup and the ordered passes (first-seen numbering) restart per sweep.
+struct VoxBatch {
+    int b;
+    int pt_off[VOX_MAX_BATCH + 1];    // first point row of sweep s; pt_off[b] = n
+    int blk_off[VOX_MAX_BATCH + 1];   // first block of sweep s;     blk_off[b] = number of blocks
+};
 
 struct VoxParams {
     const float* pts; int n; int pt_stride; int nfeat;
-    double rmin[3], rmax_x, rmax_y, rmin_x, rmin_y;  // range
-    double vs[3];
+    double rmin[3], vs[3];
     float rminf[3], vsf[3], mx0, mx1, my0, my1;  // f32 copies (f32 mode and range mask)
     int grid[3];
     int max_pts, max_vox, break_mode, f64_math, range_mask;
-    float z_offset; int intensity_col; const float* intensity_max;  // b1 conditioning (optional)
-    int H;  // hash size (power of two)
+    float z_offset; int intensity_col; const float* intensity_max;  // b1 conditioning (optional); one maximum per sweep
+    int dense;   // 1: slot = cell id (pillar grids: the whole grid fits a table); 0: open-addressing hash of the cell id
+    int TS;      // table slots per sweep (dense: cells; hash: a power of two >= 2 * the largest sweep)
 };
 
-__device__ __forceinline__ float cond_feature(const VoxParams& p, const float* row, int j) {
-    float v = ld_coherent(row + j);
-    if (j == 2) v = v + p.z_offset;
-    if (j == p.intensity_col) v = v / ld_coherent(p.intensity_max);
-    return v;
+__device__ __forceinline__ int vox_sweep_of_block(const VoxBatch& B, int blk) {
+    int lo = 0, hi = B.b - 1;   // the last sweep whose first block is <= blk (empty sweeps share their successor's offset)
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (B.blk_off[mid] <= blk) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+// sweep and point row handled by this thread (block of VB threads); false for the ragged tail of a sweep's last block
+__device__ __forceinline__ bool vox_locate(const VoxBatch& B, int& s, int& i) {
+    s = vox_sweep_of_block(B, (int)blockIdx.x);
+    i = B.pt_off[s] + ((int)blockIdx.x - B.blk_off[s]) * VB + (int)threadIdx.x;
+    return i < B.pt_off[s + 1];
 }
 
-// cell id of point i, or -1 when masked / outside the grid
-__device__ __forceinline__ int point_cell(const VoxParams& p, int i, int& cx, int& cy, int& cz) {
-    const float* row = p.pts + (long long)i * p.pt_stride;
-    const float x = cond_feature(p, row, 0), y = cond_feature(p, row, 1), z = cond_feature(p, row, 2);
+__device__ __forceinline__ float cond_value(const VoxParams& p, int s, float v, int j) {
+    if (j == 2) v = v + p.z_offset;
+    if (j == p.intensity_col) v = v / ld_coherent(p.intensity_max + s);
+    return v;
+}
+__device__ __forceinline__ float cond_feature(const VoxParams& p, int s, const float* row, int j) {
+    return cond_value(p, s, ld_coherent(row + j), j);
+}
+// a whole 16-byte row (x, y, z, feature) in one load
+__device__ __forceinline__ float4 cond_row4(const VoxParams& p, int s, long long i) {
+    float4 r = *reinterpret_cast<const float4*>(p.pts + i * 4);
+    r.x = cond_value(p, s, r.x, 0); r.y = cond_value(p, s, r.y, 1); r.z = cond_value(p, s, r.z, 2); r.w = cond_value(p, s, r.w, 3);
+    return r;
+}
+
+// cell id of a point, or -1 when masked / outside the grid
+__device__ __forceinline__ int point_cell(const VoxParams& p, float x, float y, float z, int& cx, int& cy, int& cz) {
     if (p.range_mask && !(x >= p.mx0 && x <= p.mx1 && y >= p.my0 && y <= p.my1)) return -1;
     int c[3];
     const float q[3] = {x, y, z};
@@ -67,61 +99,105 @@ __device__ __forceinline__ int point_cell(const VoxParams& p, int i, int& cx, in
     cx = c[0]; cy = c[1]; cz = c[2];
     return (cz * p.grid[1] + cy) * p.grid[0] + cx;
 }
+// How a kernel reads point rows: ROW_ANY scalar loads at any stride (the lanes of a warp read neighbouring rows, so the
+// loads of one row's columns hit the same lines); ROW_VEC4 one 16-byte load per row (stride 4, aligned: KITTI x, y, z, i).
+enum { ROW_ANY = 0, ROW_VEC4 = 1 };
 
 __device__ __forceinline__ unsigned hash_cell(int cell, int H) {
     return ((unsigned)cell * 2654435761u) >> 7 & (unsigned)(H - 1);
 }
 
-__global__ void __launch_bounds__(256) vox_hash_kernel(const VoxParams p, int* __restrict__ pslot,
-                                                       int* __restrict__ hkey, int* __restrict__ hmin, int* __restrict__ hcnt) {
+// Table record of a cell: x = smallest point index seen (atomicMin), y = points seen (atomicAdd).
+constexpr long long VOX_EMPTY = 0x000000007fffffffLL;   // {x = INT_MAX, y = 0}
+
+// one pass that prepares everything the call needs: cell records, hash keys (hash mode), first-point records + block
+// counts (`zero16` 16-byte units), per-sweep maxima
+__global__ void __launch_bounds__(256) vox_init_kernel(long long* __restrict__ recs, long long n_recs, int* __restrict__ hkey, long long n_keys,
+                                                       void* __restrict__ flags, long long n_flags16, float* __restrict__ imax, int b) {
     pdl_enter();
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= p.n) return;
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x, step = (long long)gridDim.x * blockDim.x;
+    longlong2* r2 = reinterpret_cast<longlong2*>(recs);   // workspace blocks are 256-byte aligned
+    for (long long k = t; k < (n_recs >> 1); k += step) r2[k] = make_longlong2(VOX_EMPTY, VOX_EMPTY);
+    if (t == 0 && (n_recs & 1)) recs[n_recs - 1] = VOX_EMPTY;
+    int4* k4 = reinterpret_cast<int4*>(hkey);
+    for (long long k = t; k < (n_keys >> 2); k += step) k4[k] = make_int4(-1, -1, -1, -1);
+    if (t < (n_keys & 3)) hkey[n_keys - 1 - t] = -1;
+    int4* f4 = reinterpret_cast<int4*>(flags);
+    for (long long k = t; k < n_flags16; k += step) f4[k] = make_int4(0, 0, 0, 0);
+    if (imax && t < b) imax[t] = -INFINITY;
+}
+
+template <int ROWS>
+__global__ void __launch_bounds__(VB) vox_cell_kernel(const VoxParams p, const VoxBatch B, int2* __restrict__ pslot,
+                                                      int* __restrict__ hkey, int2* __restrict__ recs) {
+    pdl_enter();
+    int s, i;
+    const bool valid = vox_locate(B, s, i);
+    float x, y, z;
+    if (ROWS == ROW_VEC4) {
+        if (!valid) return;
+        const float4 r = *reinterpret_cast<const float4*>(p.pts + (long long)i * 4);
+        x = cond_value(p, s, r.x, 0); y = cond_value(p, s, r.y, 1); z = cond_value(p, s, r.z, 2);
+    } else {
+        if (!valid) return;
+        const float* row = p.pts + (long long)i * p.pt_stride;
+        x = cond_feature(p, s, row, 0); y = cond_feature(p, s, row, 1); z = cond_feature(p, s, row, 2);
+    }
     int cx, cy, cz;
-    const int cell = point_cell(p, i, cx, cy, cz);
-    if (cell < 0) { pslot[i] = -1; return; }
-    unsigned h = hash_cell(cell, p.H);
-    while (true) {
-        const int prev = atomicCAS(&hkey[h], -1, cell);
-        if (prev == -1 || prev == cell) break;
-        h = (h + 1) & (unsigned)(p.H - 1);
+    const int cell = point_cell(p, x, y, z, cx, cy, cz);
+    if (cell < 0) { pslot[i] = make_int2(-1, 0); return; }
+    int slot;
+    if (p.dense) {
+        slot = s * p.TS + cell;
+    } else {
+        int* keys = hkey + (long long)s * p.TS;
+        unsigned h = hash_cell(cell, p.TS);
+        while (true) {
+            const int prev = atomicCAS(&keys[h], -1, cell);
+            if (prev == -1 || prev == cell) break;
+            h = (h + 1) & (unsigned)(p.TS - 1);
+        }
+        slot = s * p.TS + (int)h;
     }
-    atomicMin(&hmin[h], i);
-    atomicAdd(&hcnt[h], 1);
-    pslot[i] = (int)h;
+    // Neighbouring points of a scan line mostly share their pillar: the lanes of a warp that hit the same slot send one
+    // atomicMin (their lowest index: the group's first lane) and one atomicAdd (their number) between them. The value the
+    // add returns numbers the cell's points in arrival order — the point's place in the cell's CSR segment later on.
+    const unsigned act = __activemask();
+    const unsigned peers = __match_any_sync(act, slot);
+    const int leader = __ffs(peers) - 1, lane = threadIdx.x & 31;
+    int base = 0;
+    if (lane == leader) {
+        atomicMin(&recs[slot].x, i);
+        base = atomicAdd(&recs[slot].y, __popc(peers));
+    }
+    base = __shfl_sync(peers, base, leader);
+    pslot[i] = make_int2(slot, base + __popc(peers & ((1u << lane) - 1)));
 }
 
-__device__ __forceinline__ int block_sum(int v, int* sh) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll
-    for (int s = 16; s > 0; s >>= 1) v += __shfl_xor_sync(0xffffffffu, v, s);
-    if (lane == 0) sh[warp] = v;
-    __syncthreads();
-    int t = (threadIdx.x < (blockDim.x >> 5)) ? sh[threadIdx.x] : 0;
-    if (warp == 0) {
-#pragma unroll
-        for (int s = 16; s > 0; s >>= 1) t += __shfl_xor_sync(0xffffffffu, t, s);
-        if (lane == 0) sh[0] = t;
-    }
-    __syncthreads();
-    const int r = sh[0];
-    __syncthreads();
-    return r;
-}
-
-__global__ void __launch_bounds__(VB) vox_count_kernel(int n, const int* pslot, const int* hmin,
-                                                       int* __restrict__ blocksum) {
+// Per table slot: the cell's first point gets a record {slot, points in the cell} (the ordered passes then read these in
+// point order instead of chasing every point's table slot) and its bit in a bitmap over the points, from which the scan
+// kernel counts the first points of every 1024-point block (32 words each: blocks start at multiples of 1024 bits
+// because every sweep's bits start at its first block).
+__global__ void __launch_bounds__(256) vox_mark_kernel(const VoxBatch B, const int2* recs, long long n_recs, int TS,
+                                                       int2* __restrict__ finfo, unsigned* __restrict__ bitmap) {
     pdl_enter();
-    __shared__ int sh[32];
-    const int i = blockIdx.x * VB + threadIdx.x;
-    int first = 0;
-    if (i < n) { const int s = pslot[i]; first = (s >= 0 && hmin[s] == i); }
-    const int tot = block_sum(first, sh);
-    if (threadIdx.x == 0) blocksum[blockIdx.x] = tot;
+    const long long step = (long long)gridDim.x * blockDim.x;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n_recs; k += step) {
+        const int2 r = recs[k];
+        if (r.x == INT_MAX) continue;
+        const int s = (int)(k / TS);
+        finfo[r.x] = make_int2((int)k, r.y);
+        const int bit = B.blk_off[s] * VB + (r.x - B.pt_off[s]);
+        atomicOr(&bitmap[bit >> 5], 1u << (bit & 31));
+    }
 }
 
-// exclusive scan of up to 1024*1024 points' block sums by one CTA (nblk <= 4096)
-__global__ void __launch_bounds__(1024) vox_scan_kernel(int nblk, int* __restrict__ blocksum, int max_vox,
+// scalars: [0] CSR cursor, [2 + s] index of the point at which the scan of sweep s breaks
+constexpr int SC_CURSOR = 0, SC_BREAK = 2;
+
+// exclusive scan of the block sums of the whole batch by one CTA (blocksum[nblk] = total), then per sweep: occupied
+// cells = difference of the prefix at its block range, M = min(cells, max_vox); also resets the per-call scalars.
+__global__ void __launch_bounds__(1024) vox_scan_kernel(const VoxBatch B, int nblk, const unsigned* bitmap, int* __restrict__ blocksum, int max_vox,
                                                         int* __restrict__ scalars, int* __restrict__ m_out) {
     pdl_enter();
     __shared__ int sh[32];
@@ -130,7 +206,12 @@ __global__ void __launch_bounds__(1024) vox_scan_kernel(int nblk, int* __restric
     __syncthreads();
     for (int base = 0; base < nblk; base += 1024) {
         const int i = base + threadIdx.x;
-        const int v = (i < nblk) ? blocksum[i] : 0;
+        int v = 0;
+        if (i < nblk) {   // first points of block i = set bits of its 32 bitmap words
+            const uint4* w4 = reinterpret_cast<const uint4*>(bitmap + 32ll * i);
+#pragma unroll
+            for (int q = 0; q < 8; q++) { const uint4 w = w4[q]; v += __popc(w.x) + __popc(w.y) + __popc(w.z) + __popc(w.w); }
+        }
         const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
         int inc = v;
 #pragma unroll
@@ -150,25 +231,28 @@ __global__ void __launch_bounds__(1024) vox_scan_kernel(int nblk, int* __restric
         if (threadIdx.x == 1023) carry = prefix + v;
         __syncthreads();
     }
-    if (threadIdx.x == 0) {
-        const int total = carry;
-        scalars[0] = total;                              // occupied cells
-        scalars[1] = INT_MAX;                            // break point index (break mode)
-        scalars[2] = 0;                                  // CSR cursor
-        *m_out = total < max_vox ? total : max_vox;
+    if (threadIdx.x == 0) { blocksum[nblk] = carry; scalars[SC_CURSOR] = 0; }
+    __syncthreads();
+    if ((int)threadIdx.x < B.b) {
+        const int s = threadIdx.x;
+        const int cells = blocksum[B.blk_off[s + 1]] - blocksum[B.blk_off[s]];
+        m_out[s] = cells < max_vox ? cells : max_vox;
+        scalars[SC_BREAK + s] = INT_MAX;
     }
 }
 
-__global__ void __launch_bounds__(VB) vox_assign_kernel(const VoxParams p, const int* pslot, const int* hmin,
-                                                        const int* hcnt, const int* blockoff,
-                                                        int* __restrict__ hvid, int* __restrict__ hseg, int* __restrict__ vslot,
-                                                        int* __restrict__ scalars, int* __restrict__ coords) {
+// vrec[slot] = {voxel id, CSR segment start (-1: cell beyond max_voxels), points in the cell, -}
+__global__ void __launch_bounds__(VB) vox_assign_kernel(const VoxParams p, const VoxBatch B, const int2* finfo,
+                                                        const int* hkey, const int* blockoff, int4* __restrict__ vrec,
+                                                        int2* __restrict__ vinfo, int* __restrict__ scalars,
+                                                        int* __restrict__ coords, int* __restrict__ num_pts) {
     pdl_enter();
-    __shared__ int sh[32];
-    const int i = blockIdx.x * VB + threadIdx.x;
+    __shared__ int sh[32], sh2[32];
+    __shared__ int seg_base;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    int s = -1, first = 0;
-    if (i < p.n) { s = pslot[i]; first = (s >= 0 && hmin[s] == i); }
+    int s, i, sl = -1, cnt = 0;
+    if (vox_locate(B, s, i)) { const int2 f = finfo[i]; sl = f.x; cnt = f.y; }
+    const int first = cnt > 0;
     // in-block exclusive rank of `first`
     const unsigned bal = __ballot_sync(0xffffffffu, first);
     if (lane == 0) sh[warp] = __popc(bal);
@@ -180,139 +264,225 @@ __global__ void __launch_bounds__(VB) vox_assign_kernel(const VoxParams p, const
         sh[lane] = w;
     }
     __syncthreads();
+    const int vid = first ? blockoff[blockIdx.x] - blockoff[B.blk_off[s]] + (warp ? sh[warp - 1] : 0) + __popc(bal & ((1u << lane) - 1)) : 0;
+    const bool kept = first && vid < p.max_vox;
+    // CSR segments: the block's kept cells take one stretch of the cursor (one atomic per block)
+    const int mine = kept ? cnt : 0;
+    int inc = mine;
+#pragma unroll
+    for (int k = 1; k < 32; k <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, k); if (lane >= k) inc += t; }
+    if (lane == 31) sh2[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        int w = sh2[lane];
+#pragma unroll
+        for (int k = 1; k < 32; k <<= 1) { const int t = __shfl_up_sync(0xffffffffu, w, k); if (lane >= k) w += t; }
+        sh2[lane] = w;
+        if (lane == 31) seg_base = w > 0 ? atomicAdd(&scalars[SC_CURSOR], w) : 0;
+    }
+    __syncthreads();
     if (!first) return;
-    const int vid = blockoff[blockIdx.x] + (warp ? sh[warp - 1] : 0) + __popc(bal & ((1u << lane) - 1));
-    hvid[s] = vid;
-    if (vid < p.max_vox) {
-        int cx, cy, cz;
-        point_cell(p, i, cx, cy, cz);
-        reinterpret_cast<int4*>(coords)[vid] = make_int4(0, cz, cy, cx);  // [batch, z, y, x] (preprocess_3d.py:50)
-        vslot[vid] = s;
-        hseg[s] = atomicAdd(&scalars[2], hcnt[s]);
-    } else if (vid == p.max_vox) {
-        scalars[1] = i;  // the point at which the SECOND/det3d scan breaks
-    }
-}
-
-__global__ void __launch_bounds__(256) vox_scatter_kernel(const VoxParams p, const int* pslot, const int* hvid,
-                                                          const int* hseg, int* __restrict__ hfill,
-                                                          const int* scalars, int* __restrict__ csr) {
-    pdl_enter();
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= p.n) return;
-    const int s = pslot[i];
-    if (s < 0) return;
-    if (hvid[s] >= p.max_vox) return;                 // "continue": the voxel was never created
-    if (p.break_mode && i >= scalars[1]) return;      // "break": the scan stopped before this point
-    csr[hseg[s] + atomicAdd(&hfill[s], 1)] = i;
-}
-
-// One warp per voxel: keep the max_pts smallest point indices of the segment, in ascending order.
-__global__ void __launch_bounds__(256) vox_gather_kernel(const VoxParams p, const int* m_dev, const int* vslot,
-                                                         const int* hseg, const int* hfill,
-                                                         const int* csr, float* __restrict__ voxels, int* __restrict__ num_pts) {
-    pdl_enter();
-    const int lane = threadIdx.x & 31;
-    const int v = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (v >= *m_dev) return;
-    const int s = vslot[v];
-    const int L = hfill[s];
-    const int* seg = csr + hseg[s];
-    const int P = p.max_pts, F = p.nfeat;
-    const int keep = L < P ? L : P;
-    float* vout = voxels + (long long)v * P * F;
-    if (lane == 0) num_pts[v] = keep;
-    if (L <= 32) {
-        const int mine = lane < L ? seg[lane] : INT_MAX;
-        int rank = 0;
-        for (int t = 0; t < L; t++) rank += (__shfl_sync(0xffffffffu, mine, t) < mine);
-        if (lane < L && rank < P) {
-            const float* row = p.pts + (long long)mine * p.pt_stride;
-            for (int j = 0; j < F; j++) vout[rank * F + j] = cond_feature(p, row, j);
-        }
-    } else if (L <= 32 * 8) {
-        // up to 256 points: the segment is read once into registers (8 per lane), then P rounds of "smallest index
-        // greater than the last one" run on registers and shuffles only
-        int q[8];
-#pragma unroll
-        for (int u = 0; u < 8; u++) q[u] = lane + 32 * u < L ? seg[lane + 32 * u] : INT_MAX;
-        int last = -1;
-        for (int r = 0; r < keep; r++) {
-            int best = INT_MAX;
-#pragma unroll
-            for (int u = 0; u < 8; u++) if (q[u] > last && q[u] < best) best = q[u];
-#pragma unroll
-            for (int k = 16; k > 0; k >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, k));
-            last = best;
-            const float* row = p.pts + (long long)best * p.pt_stride;
-            for (int j = lane; j < F; j += 32) vout[r * F + j] = cond_feature(p, row, j);
-        }
+    if (kept) {
+        const int cell = p.dense ? sl - s * p.TS : hkey[sl];
+        const int cx = cell % p.grid[0], t = cell / p.grid[0], cy = t % p.grid[1], cz = t / p.grid[1];
+        const long long v = (long long)s * p.max_vox + vid;
+        const int seg = seg_base + (warp ? sh2[warp - 1] : 0) + inc - mine;
+        reinterpret_cast<int4*>(coords)[v] = make_int4(s, cz, cy, cx);  // [batch, z, y, x] (preprocess_3d.py:50)
+        vinfo[v] = make_int2(seg, cnt);
+        vrec[sl] = make_int4(vid, seg, cnt, 0);
+        if (!p.break_mode) num_pts[v] = cnt < p.max_pts ? cnt : p.max_pts;   // "break": counted once the break point is known
     } else {
-        int last = -1;
-        for (int r = 0; r < keep; r++) {  // selection: next smallest index greater than `last`
-            int best = INT_MAX;
-            for (int t = lane; t < L; t += 32) { const int q = seg[t]; if (q > last && q < best) best = q; }
-#pragma unroll
-            for (int k = 16; k > 0; k >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, k));
-            last = best;
-            const float* row = p.pts + (long long)best * p.pt_stride;
-            for (int j = lane; j < F; j += 32) vout[r * F + j] = cond_feature(p, row, j);
-        }
+        vrec[sl] = make_int4(vid, -1, cnt, 0);
+        if (vid == p.max_vox) scalars[SC_BREAK + s] = i;   // the point at which the SECOND/det3d scan breaks
     }
-    for (int e = keep * F + lane; e < P * F; e += 32) vout[e] = 0.f;  // zero padding
 }
 
-// per-frame max of one feature column (b1: intensity /= max(intensity)); values assumed finite
-__global__ void __launch_bounds__(256) vox_colmax_kernel(const float* pts, int n, int stride, int col, float* __restrict__ out) {
+// Every point of a kept cell goes to its arrival position in the cell's segment (unordered; ranked afterwards). The
+// blocks of a sweep also clear the sweep's M voxels between them (the zero padding of the voxel generators), so that
+// the placement that follows only writes the rows that exist.
+__global__ void __launch_bounds__(VB) vox_scatter_kernel(const VoxParams p, const VoxBatch B, const int* m_dev, const int2* pslot,
+                                                         const int4* vrec, int* __restrict__ csr, float* __restrict__ voxels) {
     pdl_enter();
-    float m = -INFINITY;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) m = fmaxf(m, ld_coherent(pts + (long long)i * stride + col));
+    int s, i;
+    const bool valid = vox_locate(B, s, i);
+    if (valid) {
+        const int2 ps = pslot[i];
+        if (ps.x >= 0) {
+            const int4 vr = vrec[ps.x];
+            if (vr.y >= 0) csr[vr.y + ps.y] = i;          // vr.y < 0, "continue": the voxel was never created
+        }
+    }
+    const int nb = B.blk_off[s + 1] - B.blk_off[s], r = (int)blockIdx.x - B.blk_off[s];
+    const long long per_vox = (long long)p.max_pts * p.nfeat;
+    const long long total = (long long)m_dev[s] * per_vox;                       // floats of this sweep to clear
+    float* base = voxels + (long long)s * p.max_vox * per_vox;
+    if ((per_vox & 3) == 0 && (((uintptr_t)voxels) & 15) == 0) {
+        const long long q4 = total >> 2, chunk = (q4 + nb - 1) / nb;
+        const long long lo = (long long)r * chunk, hi = min(q4, lo + chunk);
+        for (long long q = lo + threadIdx.x; q < hi; q += VB) st_stream_f4(base + 4 * q, make_float4(0.f, 0.f, 0.f, 0.f));
+    } else {
+        const long long chunk = (total + nb - 1) / nb;
+        const long long lo = (long long)r * chunk, hi = min(total, lo + chunk);
+        for (long long q = lo + threadIdx.x; q < hi; q += VB) base[q] = 0.f;
+    }
+}
+
+// Point-centric placement: a point's slot in its voxel is the number of points of the same cell with a smaller index
+// (what the sequential scan's per-voxel counter gives it). The cell's segment is a handful of indices that the lanes
+// of a warp mostly share, so every point counts for itself and, when its rank is below max_points, stores its own row
+// — read in order — straight into the voxel. The count stops (checked every 8 entries) once max_points smaller indices
+// are seen, so a crowded cell costs its late points little; only its first max_points points walk the whole segment.
+template <int ROWS>
+__global__ void __launch_bounds__(VB) vox_place_kernel(const VoxParams p, const VoxBatch B, const int2* pslot, const int4* vrec,
+                                                       const int* scalars, const int* csr, float* __restrict__ voxels) {
+    pdl_enter();
+    int s, i;
+    if (!vox_locate(B, s, i)) return;
+    const int sl = pslot[i].x;
+    if (sl < 0) return;
+    const int4 vr = vrec[sl];
+    if (vr.y < 0) return;
+    if (p.break_mode && i >= scalars[SC_BREAK + s]) return;   // "break": the scan stopped before this point
+    const int* seg = csr + vr.y;
+    const int P = p.max_pts, F = p.nfeat, L = vr.z;
+    int rank = 0, t = 0;
+    for (; t + 8 <= L && rank < P; t += 8) {
+        int c = 0;
 #pragma unroll
-    for (int s = 16; s > 0; s >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, s));
+        for (int u = 0; u < 8; u++) c += (seg[t + u] < i);
+        rank += c;
+    }
+    if (rank < P) for (; t < L; t++) rank += (seg[t] < i);
+    if (rank >= P) return;
+    float* vout = voxels + ((long long)s * p.max_vox + vr.x) * P * F;
+    if (ROWS == ROW_VEC4) {
+        reinterpret_cast<float4*>(vout)[rank] = cond_row4(p, s, i);
+    } else {
+        const float* row = p.pts + (long long)i * p.pt_stride;
+        for (int j = 0; j < F; j++) vout[rank * F + j] = cond_feature(p, s, row, j);
+    }
+}
+
+// "break" mode: a voxel holds the points of its cell that come before the sweep's break point, at most max_points
+__global__ void __launch_bounds__(256) vox_breakcount_kernel(const VoxParams p, int b, const int* m_dev, const int2* vinfo, const int* scalars,
+                                                             const int* csr, int* __restrict__ num_pts) {
+    pdl_enter();
+    const long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int s = (int)(v / p.max_vox);
+    if (s >= b || (int)(v - (long long)s * p.max_vox) >= m_dev[s]) return;
+    const int2 vi = vinfo[v];
+    const int brk = scalars[SC_BREAK + s];
+    int lb = vi.y;
+    if (brk != INT_MAX) {
+        lb = 0;
+        for (int t = 0; t < vi.y; t++) lb += (csr[vi.x + t] < brk);
+    }
+    num_pts[v] = lb < p.max_pts ? lb : p.max_pts;
+}
+
+// per-sweep max of one feature column (b1: intensity /= max(intensity)); values assumed finite. grid (x, sweep)
+__global__ void __launch_bounds__(256) vox_colmax_kernel(const float* pts, const VoxBatch B, int stride, int col, float* __restrict__ out) {
+    pdl_enter();
+    const int s = blockIdx.y;
+    float m = -INFINITY;
+    for (int i = B.pt_off[s] + blockIdx.x * blockDim.x + threadIdx.x; i < B.pt_off[s + 1]; i += gridDim.x * blockDim.x)
+        m = fmaxf(m, ld_coherent(pts + (long long)i * stride + col));
+#pragma unroll
+    for (int k = 16; k > 0; k >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, k));
     if ((threadIdx.x & 31) == 0) {
         // float atomic max through the ordered-int trick
-        if (m >= 0.f) atomicMax(reinterpret_cast<int*>(out), __float_as_int(m));
-        else atomicMin(reinterpret_cast<unsigned*>(out), __float_as_uint(m));
+        if (m >= 0.f) atomicMax(reinterpret_cast<int*>(out + s), __float_as_int(m));
+        else atomicMin(reinterpret_cast<unsigned*>(out + s), __float_as_uint(m));
     }
-}
-
-__global__ void vox_init_max_kernel(float* out) {
-    pdl_enter();
-    *out = -INFINITY;
 }
 
 // ---- pillar decoration ---------------------------------------------------------------------------
 // out[v, s, :] = mask * [feat(F), xyz - mean(3), xyz - pillar centre(3)]      (pillar_vfe.py:94-118)
-__global__ void __launch_bounds__(256) pillar_decorate_kernel(const float* voxels, const int* coords,
-                                                              const int* num_pts, const int* m_dev, int m_host,
-                                                              int P, int F, float vx, float vy, float vz, float xo, float yo, float zo,
-                                                              float* __restrict__ out) {
+// One warp per voxel. The voxel's P x F block comes in with coalesced 16-byte loads into the warp's slice of shared
+// memory, the P x (F+6) result is assembled there and leaves with coalesced 16-byte stores (an output row is 40-44
+// bytes: written from registers each lane would store 10 scattered words).
+constexpr int DEC_WARPS = 8;
+// TP, TF: compile-time max_points / features of the two served configurations (32 x 4 KITTI, 20 x 5 nuScenes), 0 = run time
+template <bool VEC4, int TP, int TF>
+__global__ void __launch_bounds__(32 * DEC_WARPS, 6) pillar_decorate_kernel(const float* voxels, const int* coords, const int* num_pts,
+                                                                            const int* m_dev, int b, int vox_stride,
+                                                                            int P_rt, int F_rt, float vx, float vy, float vz, float xo, float yo, float zo,
+                                                                            float* __restrict__ out) {
+    extern __shared__ __align__(16) float dec_smem[];
+    const int P = TP ? TP : P_rt, F = TF ? TF : F_rt;
+    __shared__ int pre[VOX_MAX_BATCH + 1];
     pdl_enter();
-    const int lane = threadIdx.x & 31;
-    const int v = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int M = m_dev ? *m_dev : m_host;
-    if (v >= M) return;
-    const float* vin = voxels + (long long)v * P * F;
-    const int n = num_pts[v];
-    const int4 c = reinterpret_cast<const int4*>(coords)[v];  // b, z, y, x
-    float sx = 0.f, sy = 0.f, sz = 0.f;
-    for (int s = lane; s < P; s += 32) { sx += vin[s * F]; sy += vin[s * F + 1]; sz += vin[s * F + 2]; }
+    if ((int)threadIdx.x < b) pre[threadIdx.x + 1] = m_dev ? m_dev[threadIdx.x] : vox_stride;
+    __syncthreads();
+    if (threadIdx.x == 0) { int a = 0; for (int s = 0; s < b; s++) { const int m = pre[s + 1]; pre[s] = a; a += m; } pre[b] = a; }
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int FO = F + 6, nin = P * F, nout = P * FO;
+    float* sin_ = dec_smem + (size_t)warp * (((nin + 3) & ~3) + ((nout + 3) & ~3));
+    float* sout = sin_ + ((nin + 3) & ~3);
+    const int total = pre[b], nw = gridDim.x * DEC_WARPS;
+    for (int k = blockIdx.x * DEC_WARPS + warp; k < total; k += nw) {     // warps stride over the voxels of the whole batch
+        int lo = 0, hi = b - 1;
+        while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (pre[mid] <= k) lo = mid; else hi = mid - 1; }
+        const long long v = (long long)lo * vox_stride + (k - pre[lo]);
+        const float* vin = voxels + v * nin;
+        const int n = num_pts[v];
+        const int4 c = reinterpret_cast<const int4*>(coords)[v];  // b, z, y, x
+        const float px = (float)c.w * vx + xo, py = (float)c.z * vy + yo, pz = (float)c.y * vz + zo;
+        if (TF == 4 && VEC4) {
+            // a 16-byte row per slot: lane = slot, the slot's row stays in registers from the load to the outputs
+            constexpr int RF = TF > 0 ? TF : 1;
+            auto load_row = [&](int q, float (&r)[RF]) {
+                if (RF == 4 && VEC4) { const float4 t = reinterpret_cast<const float4*>(vin)[q]; r[0] = t.x; r[1] = t.y; r[2] = t.z; r[RF - 1] = t.w; }
+                else {
 #pragma unroll
-    for (int k = 16; k > 0; k >>= 1) {
-        sx += __shfl_xor_sync(0xffffffffu, sx, k); sy += __shfl_xor_sync(0xffffffffu, sy, k); sz += __shfl_xor_sync(0xffffffffu, sz, k);
-    }
-    const float fn = (float)n;
-    const float mx = sx / fn, my = sy / fn, mz = sz / fn;
-    const float px = (float)c.w * vx + xo, py = (float)c.z * vy + yo, pz = (float)c.y * vz + zo;
-    const int FO = F + 6;
-    float* vo = out + (long long)v * P * FO;
-    for (int s = lane; s < P; s += 32) {
-        const float mask = (n > s) ? 1.f : 0.f;
-        const float x = vin[s * F], y = vin[s * F + 1], z = vin[s * F + 2];
-        float* o = vo + s * FO;
-        for (int j = 0; j < F; j++) o[j] = vin[s * F + j] * mask;
-        o[F + 0] = (x - mx) * mask; o[F + 1] = (y - my) * mask; o[F + 2] = (z - mz) * mask;
-        o[F + 3] = (x - px) * mask; o[F + 4] = (y - py) * mask; o[F + 5] = (z - pz) * mask;
+                    for (int j = 0; j < RF; j++) r[j] = vin[q * RF + j];
+                }
+            };
+            float sx = 0.f, sy = 0.f, sz = 0.f;
+            for (int q = lane; q < P; q += 32) { float r[RF]; load_row(q, r); sx += r[0]; sy += r[1]; sz += r[2]; }
+#pragma unroll
+            for (int q = 16; q > 0; q >>= 1) {
+                sx += __shfl_xor_sync(0xffffffffu, sx, q); sy += __shfl_xor_sync(0xffffffffu, sy, q); sz += __shfl_xor_sync(0xffffffffu, sz, q);
+            }
+            const float fn = (float)n;
+            const float mx = sx / fn, my = sy / fn, mz = sz / fn;
+            for (int q = lane; q < P; q += 32) {
+                float r[RF];
+                load_row(q, r);                                               // P > 32: the second read hits L1
+                const float mask = (n > q) ? 1.f : 0.f;
+                float* o = sout + q * (RF + 6);
+#pragma unroll
+                for (int j = 0; j < RF; j++) o[j] = r[j] * mask;
+                o[RF + 0] = (r[0] - mx) * mask; o[RF + 1] = (r[1] - my) * mask; o[RF + 2] = (r[2] - mz) * mask;
+                o[RF + 3] = (r[0] - px) * mask; o[RF + 4] = (r[1] - py) * mask; o[RF + 5] = (r[2] - pz) * mask;
+            }
+        } else {
+            if (VEC4) { for (int e = lane; e < (nin >> 2); e += 32) reinterpret_cast<float4*>(sin_)[e] = reinterpret_cast<const float4*>(vin)[e]; }
+            else      { for (int e = lane; e < nin; e += 32) sin_[e] = vin[e]; }
+            __syncwarp();
+            float sx = 0.f, sy = 0.f, sz = 0.f;
+            for (int q = lane; q < P; q += 32) { sx += sin_[q * F]; sy += sin_[q * F + 1]; sz += sin_[q * F + 2]; }
+#pragma unroll
+            for (int q = 16; q > 0; q >>= 1) {
+                sx += __shfl_xor_sync(0xffffffffu, sx, q); sy += __shfl_xor_sync(0xffffffffu, sy, q); sz += __shfl_xor_sync(0xffffffffu, sz, q);
+            }
+            const float fn = (float)n;
+            const float mx = sx / fn, my = sy / fn, mz = sz / fn;
+            for (int q = lane; q < P; q += 32) {
+                const float mask = (n > q) ? 1.f : 0.f;
+                const float x = sin_[q * F], y = sin_[q * F + 1], z = sin_[q * F + 2];
+                float* o = sout + q * FO;
+                for (int j = 0; j < F; j++) o[j] = sin_[q * F + j] * mask;
+                o[F + 0] = (x - mx) * mask; o[F + 1] = (y - my) * mask; o[F + 2] = (z - mz) * mask;
+                o[F + 3] = (x - px) * mask; o[F + 4] = (y - py) * mask; o[F + 5] = (z - pz) * mask;
+            }
+        }
+        __syncwarp();
+        float* vo = out + v * nout;
+        if (VEC4) { for (int e = lane; e < (nout >> 2); e += 32) st_stream_f4(vo + 4 * e, reinterpret_cast<const float4*>(sout)[e]); }
+        else      { for (int e = lane; e < nout; e += 32) vo[e] = sout[e]; }
+        __syncwarp();   // the next voxel overwrites both slices
     }
 }
 
@@ -547,31 +717,60 @@ __global__ void __launch_bounds__(1024) jsk_boxes_kernel(const float* boxes, con
 
 }  // namespace
 
-extern "C" size_t tcb_voxelize_workspace(int n, int max_vox) {
+// table geometry shared by the workspace query and the entry point
+static void vox_table(long long cells, int n_max, int& dense, int& TS) {
+    // pillar grids (a few hundred thousand cells) index the table by cell id: no keys, no probing; sparse 3-D grids
+    // (C4': 90 M cells) hash the cell id into 2 * n slots
+    dense = (cells <= (1ll << 20) || cells <= 4ll * (n_max > 0 ? n_max : 1)) ? 1 : 0;
+    TS = dense ? (int)cells : next_pow2(2LL * (n_max > 0 ? n_max : 1));
+}
+
+extern "C" size_t tcb_voxelize_workspace(int n, int b, int max_vox, long long cells) {
     if (n < 0) n = 0;
+    if (b < 1) b = 1;
     if (max_vox < 0) max_vox = 0;
-    const size_t H = (size_t)next_pow2(2LL * (n > 0 ? n : 1));
-    size_t bytes = 4096;
-    bytes += 2 * ((size_t)n * 4 + 256);          // pslot, csr
-    bytes += 6 * (H * 4 + 256);                  // hkey, hmin, hcnt, hvid, hseg, hfill
-    bytes += ((size_t)n / VB + 2) * 4 + 256;     // block sums
-    bytes += (size_t)max_vox * 4 + 256;          // vslot
+    int dense, TS;
+    vox_table(cells > 0 ? cells : 1, n, dense, TS);   // n as the bound of the largest sweep
+    size_t bytes = 8192;
+    bytes += (size_t)n * 12 + 512;                            // pslot (slot, arrival position), csr
+    bytes += (size_t)b * TS * (8 + 16 + (dense ? 0 : 4)) + 768; // cell records, voxel records, hash keys
+    bytes += (size_t)b * max_vox * 8 + 256;                   // vinfo (segment, points)
+    bytes += (size_t)n * 8 + ((size_t)n / VB + b + 4) * (4 + 128) + 1024; // first-point records, block sums, first-point bitmap
     return bytes;
 }
 
-extern "C" int tcb_voxelize(tcb_ctx* ctx, const float* pts_dev, int n, int pt_stride, int nfeat, const double range[6],
-                            const double vsize[3], int max_pts, int max_vox, int overflow_mode, int f64_math,
+extern "C" int tcb_voxelize(tcb_ctx* ctx, const float* pts_dev, int n, const int* sweep_offsets_host, int b, int pt_stride, int nfeat,
+                            const double range[6], const double vsize[3], int max_pts, int max_vox, int overflow_mode, int f64_math,
                             int range_mask_xy, float z_offset, int intensity_col, float* voxels_dev, int* coords_dev,
                             int* num_pts_dev, int* m_out_dev, void* stream) {
     TCB_CHECK_CTX(ctx);
     TCB_REQUIRE(ctx, range && vsize && voxels_dev && coords_dev && num_pts_dev && m_out_dev, "tcb_voxelize: null argument");
     TCB_REQUIRE(ctx, n >= 0 && (n == 0 || pts_dev), "tcb_voxelize: bad points");
+    TCB_REQUIRE(ctx, b >= 1 && (b == 1 || sweep_offsets_host), "tcb_voxelize: b sweeps need b+1 row offsets");
+    if (b > VOX_MAX_BATCH) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_voxelize: %d sweeps per call (limit %d)", b, VOX_MAX_BATCH);
     TCB_REQUIRE(ctx, nfeat >= 3 && pt_stride >= nfeat, "tcb_voxelize: need nfeat >= 3 and pt_stride >= nfeat (got %d, %d)", nfeat, pt_stride);
     TCB_REQUIRE(ctx, max_pts >= 1 && max_vox >= 1, "tcb_voxelize: max_pts and max_vox must be >= 1");
     TCB_REQUIRE(ctx, overflow_mode == 0 || overflow_mode == 1, "tcb_voxelize: overflow_mode must be 0 (continue) or 1 (break)");
     TCB_REQUIRE(ctx, intensity_col < nfeat, "tcb_voxelize: intensity_col out of range");
     if (n > (1 << 26)) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_voxelize: more than 2^26 points");
     cudaStream_t st = (cudaStream_t)stream;
+
+    VoxBatch B;
+    memset(&B, 0, sizeof(B));
+    B.b = b;
+    int n_max = 0;
+    for (int s = 0; s <= b; s++) {
+        const int off = sweep_offsets_host ? sweep_offsets_host[s] : (s == 0 ? 0 : n);
+        TCB_REQUIRE(ctx, off >= 0 && off <= n && (s == 0 ? off == 0 : off >= B.pt_off[s - 1]), "tcb_voxelize: sweep offsets must ascend from 0 to n");
+        B.pt_off[s] = off;
+        if (s > 0) {
+            const int ns = off - B.pt_off[s - 1];
+            n_max = ns > n_max ? ns : n_max;
+            B.blk_off[s] = B.blk_off[s - 1] + tcb_div_up(ns, VB);
+        }
+    }
+    TCB_REQUIRE(ctx, B.pt_off[b] == n, "tcb_voxelize: the last sweep offset must be n");
+    const int nblk = B.blk_off[b];
 
     VoxParams p;
     memset(&p, 0, sizeof(p));
@@ -592,66 +791,94 @@ extern "C" int tcb_voxelize(tcb_ctx* ctx, const float* pts_dev, int n, int pt_st
     p.mx0 = (float)range[0]; p.mx1 = (float)range[3]; p.my0 = (float)range[1]; p.my1 = (float)range[4];
     p.max_pts = max_pts; p.max_vox = max_vox; p.break_mode = overflow_mode; p.f64_math = f64_math ? 1 : 0;
     p.range_mask = range_mask_xy ? 1 : 0; p.z_offset = z_offset; p.intensity_col = intensity_col;
-    p.H = next_pow2(2LL * (n > 0 ? n : 1));
+    vox_table(cells, n_max, p.dense, p.TS);
+    const long long slots = (long long)b * p.TS;
+    if (slots >= INT_MAX || (long long)b * max_vox >= INT_MAX) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_voxelize: batch too large for 32-bit slot ids");
 
-    const int nblk = tcb_div_up(n > 0 ? n : 1, VB);
-    if (nblk > 65536) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_voxelize: too many points");
-    TCB_WS(ctx, scalars, int, 64);
-    TCB_WS(ctx, pslot, int, n > 0 ? n : 1);
+    TCB_WS(ctx, scalars, int, 2 * VOX_MAX_BATCH + 64);
+    TCB_WS(ctx, pslot, int2, n > 0 ? n : 1);
     TCB_WS(ctx, csr, int, n > 0 ? n : 1);
-    TCB_WS(ctx, htab, int, (size_t)p.H * 6);
-    TCB_WS(ctx, blocksum, int, nblk + 1);
-    TCB_WS(ctx, vslot, int, max_vox);
-    int *hkey = htab, *hmin = htab + p.H, *hcnt = htab + 2 * (size_t)p.H, *hfill = htab + 3 * (size_t)p.H,
-        *hvid = htab + 4 * (size_t)p.H, *hseg = htab + 5 * (size_t)p.H;
-    float* imax = reinterpret_cast<float*>(scalars + 8);
+    TCB_WS(ctx, recs, int2, slots);
+    TCB_WS(ctx, vrec, int4, slots);
+    TCB_WS(ctx, hkey, int, p.dense ? 1 : slots);
+    TCB_WS(ctx, vinfo, int2, (size_t)b * max_vox);
+    // zeroed per call, in one stretch: first-point records (8 B per point), then the first-point bitmap (1024 bits a block)
+    const long long zero16 = ((long long)n * 8 + 15) / 16 + (long long)nblk * 8;
+    TCB_WS(ctx, zeroed, char, zero16 * 16 + 16);
+    TCB_WS(ctx, blocksum, int, nblk + 2);
+    int2* finfo = reinterpret_cast<int2*>(zeroed);
+    unsigned* bitmap = reinterpret_cast<unsigned*>(zeroed + (((size_t)n * 8 + 15) / 16) * 16);
+    float* imax = reinterpret_cast<float*>(scalars + SC_BREAK + VOX_MAX_BATCH);
     p.intensity_max = imax;
+    const bool use_max = intensity_col >= 0 && n > 0;
+    // 16-byte rows read and written whole: KITTI-style (x, y, z, intensity) clouds
+    const bool vec4 = pt_stride == 4 && nfeat == 4 && (((uintptr_t)pts_dev | (uintptr_t)voxels_dev) & 15) == 0;
 
-    // hkey = -1, hmin = INT_MAX (0x7f7f7f7f is large enough: indices < 2^26), hcnt = hfill = 0
-    TCB_CUDA(ctx, cudaMemsetAsync(hkey, 0xff, (size_t)p.H * 4, st));
-    TCB_CUDA(ctx, cudaMemsetAsync(hmin, 0x7f, (size_t)p.H * 4, st));
-    TCB_CUDA(ctx, cudaMemsetAsync(hcnt, 0, (size_t)p.H * 8, st));
-    if (intensity_col >= 0 && n > 0) {
-        TCB_KLAUNCH(ctx, vox_init_max_kernel, 1, 1, 0, st, imax);
-        TCB_LAUNCHED(ctx);
-        TCB_KLAUNCH(ctx, vox_colmax_kernel, ctx->num_sms * 2, 256, 0, st, pts_dev, n, pt_stride, intensity_col, imax);
-        TCB_LAUNCHED(ctx);
-    }
-    if (n > 0) {
-        TCB_KLAUNCH(ctx, vox_hash_kernel, tcb_div_up(n, 256), 256, 0, st, p, pslot, hkey, hmin, hcnt);
-        TCB_LAUNCHED(ctx);
-        TCB_KLAUNCH(ctx, vox_count_kernel, nblk, VB, 0, st, n, pslot, hmin, blocksum);
-        TCB_LAUNCHED(ctx);
-    } else {
-        TCB_CUDA(ctx, cudaMemsetAsync(blocksum, 0, sizeof(int) * (nblk + 1), st));
-    }
-    TCB_KLAUNCH(ctx, vox_scan_kernel, 1, 1024, 0, st, nblk, blocksum, max_vox, scalars, m_out_dev);
+    const long long init_units = (slots >> 1) + (p.dense ? 0 : (slots >> 2)) + zero16 + 1;
+    const int init_ctas = (int)(init_units < (long long)ctx->num_sms * 8 * 256 ? tcb_div_up(init_units, 256) : ctx->num_sms * 8);
+    TCB_KLAUNCH(ctx, vox_init_kernel, init_ctas, 256, 0, st, reinterpret_cast<long long*>(recs), slots, hkey, p.dense ? 0ll : slots,
+                (void*)zeroed, zero16, use_max ? imax : (float*)nullptr, b);
     TCB_LAUNCHED(ctx);
-    if (n > 0) {
-        TCB_KLAUNCH(ctx, vox_assign_kernel, nblk, VB, 0, st, p, pslot, hmin, hcnt, blocksum, hvid, hseg, vslot, scalars, coords_dev);
+    if (use_max) {
+        TCB_KLAUNCH(ctx, vox_colmax_kernel, dim3(tcb_div_up(ctx->num_sms * 2, b), b), 256, 0, st, pts_dev, B, pt_stride, intensity_col, imax);
         TCB_LAUNCHED(ctx);
-        TCB_KLAUNCH(ctx, vox_scatter_kernel, tcb_div_up(n, 256), 256, 0, st, p, pslot, hvid, hseg, hfill, scalars, csr);
+    }
+    if (nblk > 0) {
+        if (vec4) TCB_KLAUNCH(ctx, vox_cell_kernel<ROW_VEC4>, nblk, VB, 0, st, p, B, pslot, hkey, recs);
+        else      TCB_KLAUNCH(ctx, vox_cell_kernel<ROW_ANY>, nblk, VB, 0, st, p, B, pslot, hkey, recs);
         TCB_LAUNCHED(ctx);
-        TCB_KLAUNCH(ctx, vox_gather_kernel, tcb_div_up((long long)max_vox * 32, 256), 256, 0, st, p, m_out_dev, vslot, hseg, hfill, csr, voxels_dev, num_pts_dev);
+        const int mark_ctas = (int)(slots < (long long)ctx->num_sms * 8 * 256 ? tcb_div_up(slots, 256) : ctx->num_sms * 8);
+        TCB_KLAUNCH(ctx, vox_mark_kernel, mark_ctas, 256, 0, st, B, recs, slots, p.TS, finfo, bitmap);
         TCB_LAUNCHED(ctx);
+    }
+    TCB_KLAUNCH(ctx, vox_scan_kernel, 1, 1024, 0, st, B, nblk, bitmap, blocksum, max_vox, scalars, m_out_dev);
+    TCB_LAUNCHED(ctx);
+    if (nblk > 0) {
+        TCB_KLAUNCH(ctx, vox_assign_kernel, nblk, VB, 0, st, p, B, finfo, hkey, blocksum, vrec, vinfo, scalars, coords_dev, num_pts_dev);
+        TCB_LAUNCHED(ctx);
+        TCB_KLAUNCH(ctx, vox_scatter_kernel, nblk, VB, 0, st, p, B, m_out_dev, pslot, vrec, csr, voxels_dev);
+        TCB_LAUNCHED(ctx);
+        if (vec4) TCB_KLAUNCH(ctx, vox_place_kernel<ROW_VEC4>, nblk, VB, 0, st, p, B, pslot, vrec, scalars, csr, voxels_dev);
+        else      TCB_KLAUNCH(ctx, vox_place_kernel<ROW_ANY>, nblk, VB, 0, st, p, B, pslot, vrec, scalars, csr, voxels_dev);
+        TCB_LAUNCHED(ctx);
+        if (overflow_mode) {
+            TCB_KLAUNCH(ctx, vox_breakcount_kernel, tcb_div_up((long long)b * max_vox, 256), 256, 0, st, p, b, m_out_dev, vinfo, scalars, csr, num_pts_dev);
+            TCB_LAUNCHED(ctx);
+        }
     }
     return TCB_OK;
 }
 
 extern "C" int tcb_pillar_decorate(tcb_ctx* ctx, const float* voxels_dev, const int* coords_dev, const int* num_pts_dev,
-                                   const int* m_dev, int m_max, int max_pts, int nfeat, const double vsize[3],
+                                   const int* m_dev, int b, int m_max, int max_pts, int nfeat, const double vsize[3],
                                    const double range_min[3], float* out_dev, void* stream) {
     TCB_CHECK_CTX(ctx);
     TCB_REQUIRE(ctx, voxels_dev && coords_dev && num_pts_dev && out_dev && vsize && range_min, "tcb_pillar_decorate: null argument");
-    TCB_REQUIRE(ctx, m_max >= 0 && max_pts >= 1 && nfeat >= 3, "tcb_pillar_decorate: bad shape");
+    TCB_REQUIRE(ctx, b >= 1 && m_max >= 0 && max_pts >= 1 && nfeat >= 3, "tcb_pillar_decorate: bad shape");
     if (m_max == 0) return TCB_OK;
     // offsets exactly as PillarVFE.__init__ computes them (pillar_vfe.py:76-81): Python doubles, used as f32 scalars
     const float vx = (float)vsize[0], vy = (float)vsize[1], vz = (float)vsize[2];
     const float xo = (float)(vsize[0] / 2 + range_min[0]), yo = (float)(vsize[1] / 2 + range_min[1]), zo = (float)(vsize[2] / 2 + range_min[2]);
-    TCB_KLAUNCH(ctx, pillar_decorate_kernel, tcb_div_up((long long)m_max * 32, 256), 256, 0, (cudaStream_t)stream, 
-        voxels_dev, coords_dev, num_pts_dev, m_dev, m_max, max_pts, nfeat, vx, vy, vz, xo, yo, zo, out_dev);
-    TCB_LAUNCHED(ctx);
-    return TCB_OK;
+    const int nin = max_pts * nfeat, nout = max_pts * (nfeat + 6);
+    const size_t smem = (size_t)DEC_WARPS * (((nin + 3) & ~3) + ((nout + 3) & ~3)) * sizeof(float);
+    if (smem > 200 * 1024) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_pillar_decorate: %d points x %d features per voxel exceed the shared-memory tile", max_pts, nfeat);
+    if (b > VOX_MAX_BATCH) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_pillar_decorate: %d sweeps per call (limit %d)", b, VOX_MAX_BATCH);
+    const long long vmax = (long long)b * m_max;
+    const int per_sm = (int)((size_t)200 * 1024 / (smem + 1024)) < 8 ? (int)((size_t)200 * 1024 / (smem + 1024)) : 8;
+    const int ctas = (int)(vmax < (long long)ctx->num_sms * per_sm * DEC_WARPS ? tcb_div_up(vmax, DEC_WARPS) : ctx->num_sms * (per_sm > 0 ? per_sm : 1));
+    auto ctas_of = [&]() { return ctas; };
+    const bool vec4 = (nin % 4 == 0) && (nout % 4 == 0) && (((uintptr_t)voxels_dev | (uintptr_t)out_dev) & 15) == 0;
+    auto launch = [&](auto kernel) -> int {
+        if (smem > 48 * 1024) TCB_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        TCB_KLAUNCH(ctx, kernel, ctas_of(), 32 * DEC_WARPS, smem, (cudaStream_t)stream, voxels_dev, coords_dev, num_pts_dev, m_dev, b, m_max,
+                    max_pts, nfeat, vx, vy, vz, xo, yo, zo, out_dev);
+        TCB_LAUNCHED(ctx);
+        return TCB_OK;
+    };
+    if (vec4 && max_pts == 32 && nfeat == 4) return launch(pillar_decorate_kernel<true, 32, 4>);
+    if (vec4 && max_pts == 20 && nfeat == 5) return launch(pillar_decorate_kernel<true, 20, 5>);
+    if (vec4) return launch(pillar_decorate_kernel<true, 0, 0>);
+    return launch(pillar_decorate_kernel<false, 0, 0>);
 }
 
 extern "C" size_t tcb_dynamic_pillar_workspace(int n, int batch, int gx, int gy) {

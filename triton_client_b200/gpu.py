@@ -181,35 +181,42 @@ class Engine:
 
     # ---- LiDAR voxelisation + pillar decoration ------------------------------------------------------
     def voxelize(self, points, point_range, voxel_size, max_pts, max_vox, overflow="continue", f64_math=False,
-                 range_mask=False, z_offset=0.0, intensity_col=-1, nfeat=None):
-        """points: f32 CUDA [n, C]. Returns device tensors (voxels [max_vox,P,F], coords [max_vox,4] b,z,y,x,
-        num_points [max_vox], m [1]); rows >= m are not meaningful. No host sync."""
+                 range_mask=False, z_offset=0.0, intensity_col=-1, nfeat=None, offsets=None):
+        """points: f32 CUDA [n, C]. One sweep: returns device tensors (voxels [max_vox,P,F], coords [max_vox,4] b,z,y,x,
+        num_points [max_vox], m [1]); rows >= m are not meaningful. A batch: `offsets` = b+1 ascending row offsets of the
+        sweeps inside `points` (host ints) and every result gains a leading batch dimension ([b,max_vox,...], m [b]; the
+        batch column of coords is the sweep's index). No host sync."""
         _need_cuda(points)
         if points.dtype != torch.float32 or points.dim() != 2 or (points.shape[0] > 0 and points.stride(1) != 1):
             raise TypeError("voxelize: points must be a float32 [n, C] tensor with contiguous rows")
         n, c = points.shape
         f = int(nfeat) if nfeat is not None else c
         dev = points.device
-        voxels = torch.empty((max_vox, max_pts, f), dtype=torch.float32, device=dev)
-        coords = torch.empty((max_vox, 4), dtype=torch.int32, device=dev)
-        num = torch.empty((max_vox,), dtype=torch.int32, device=dev)
-        m = torch.empty((1,), dtype=torch.int32, device=dev)
+        b = 1 if offsets is None else len(offsets) - 1
+        lead = () if offsets is None else (b,)
+        voxels = torch.empty(lead + (max_vox, max_pts, f), dtype=torch.float32, device=dev)
+        coords = torch.empty(lead + (max_vox, 4), dtype=torch.int32, device=dev)
+        num = torch.empty(lead + (max_vox,), dtype=torch.int32, device=dev)
+        m = torch.empty((b,), dtype=torch.int32, device=dev)
         rng = (ctypes.c_double * 6)(*[float(v) for v in point_range])
         vs = (ctypes.c_double * 3)(*[float(v) for v in voxel_size])
-        self.ctx.call("tcb_voxelize", _ptr(points), n, points.stride(0) if n > 0 else c, f, rng, vs, int(max_pts), int(max_vox),
+        offs = None if offsets is None else (c_int * (b + 1))(*[int(v) for v in offsets])
+        self.ctx.call("tcb_voxelize", _ptr(points), n, offs, b, points.stride(0) if n > 0 else c, f, rng, vs, int(max_pts), int(max_vox),
                       1 if overflow == "break" else 0, 1 if f64_math else 0, 1 if range_mask else 0, float(z_offset),
                       int(intensity_col), _ptr(voxels), _ptr(coords), _ptr(num), _ptr(m), _lib.stream_ptr())
         return voxels, coords, num, m
 
     def pillar_decorate(self, voxels, coords, num_points, voxel_size, point_range, m=None):
-        """(M,P,F) voxels -> (M,P,F+6) decorated features; `m` may be the device count from voxelize()."""
+        """(M,P,F) voxels -> (M,P,F+6) decorated features, or a batch (b,M,P,F) -> (b,M,P,F+6); `m` may be the device
+        count(s) from voxelize()."""
         _need_cuda(voxels, coords, num_points)
-        mm, p, f = voxels.shape
-        out = torch.empty((mm, p, f + 6), dtype=torch.float32, device=voxels.device)
+        b = voxels.shape[0] if voxels.dim() == 4 else 1
+        mm, p, f = voxels.shape[-3:]
+        out = torch.empty(tuple(voxels.shape[:-1]) + (f + 6,), dtype=torch.float32, device=voxels.device)
         vs = (ctypes.c_double * 3)(*[float(v) for v in voxel_size])
         r0 = (ctypes.c_double * 3)(*[float(v) for v in point_range[:3]])
         self.ctx.call("tcb_pillar_decorate", _ptr(voxels), _ptr(coords), _ptr(num_points), _ptr(m) if m is not None else None,
-                      mm, p, f, vs, r0, _ptr(out), _lib.stream_ptr())
+                      b, mm, p, f, vs, r0, _ptr(out), _lib.stream_ptr())
         return out
 
     def dynamic_pillar(self, points, point_range, voxel_size, batch_size=1):
