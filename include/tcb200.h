@@ -149,20 +149,21 @@ int tcb_yolo4_post(tcb_ctx* ctx, const float* boxes_dev, const float* confs_dev,
 int tcb_box_iou(tcb_ctx* ctx, const float* boxes_a_dev, int n, const float* boxes_b_dev, int m, float* out_dev, void* stream);
 
 /*
- * detectron2 dense-detector inference for one image (RetinaNet variant 0, FCOS variant 1) — the part of the served
+ * detectron2 dense-detector inference for a batch of b images (RetinaNet variant 0, FCOS variant 1) — the part of the served
  * model that produces what FCOSpostprocess.extract_boxes unpacks (clients/postprocess/detectron_postprocess.py:26-37,
  * utils/postprocess.py:368-468; tensors per examples/RetinaNet_detectron/config.pbtxt:13-33). detectron2 is not
  * vendored by the reference: restated from its published algorithm, parity unpinned.
- * Per level l: logits [A*K, h_l, w_l], deltas [A*4, h_l, w_l] (FCOS: + centerness [1,h_l,w_l], score =
+ * Per level l: logits [b, A*K, h_l, w_l], deltas [b, A*4, h_l, w_l] (FCOS: + centerness [b,1,h_l,w_l], score =
  * sqrt(sigmoid(cls)*sigmoid(ctr))); keep score > score_thresh, top-k by score, decode against the anchors
  * (location*stride + cell anchor; Box2BoxTransform with dw,dh clamped at log(1000/16), or linear ltrb*size for
  * FCOS); concatenate levels, clip to (img_h,img_w), torchvision batched_nms(nms_thresh), keep max_det.
  * The `*_dev` level arguments are HOST arrays of device pointers; h, w, strides host int arrays; cell_anchors_host
- * [num_levels*A*4] (x0,y0,x1,y1). Outputs: boxes [max_det,4], scores [max_det], classes int64 [max_det], count [1].
+ * [num_levels*A*4] (x0,y0,x1,y1). Outputs: boxes [b,max_det,4], scores [b,max_det], classes int64 [b,max_det], count [b];
+ * every image is processed on its own (detectron2 loops over the images of a batch).
  * topk <= 4096; if more than 4096 boxes reach the NMS the lowest-scoring ones are dropped; max_det <= 1024.
  */
-size_t tcb_detectron_post_workspace(int num_levels, const int* h, const int* w, int num_anchors, int num_classes, int topk);
-int tcb_detectron_post(tcb_ctx* ctx, int num_levels, const float* const* logits_dev, const float* const* deltas_dev,
+size_t tcb_detectron_post_workspace(int b, int num_levels, const int* h, const int* w, int num_anchors, int num_classes, int topk);
+int tcb_detectron_post(tcb_ctx* ctx, int b, int num_levels, const float* const* logits_dev, const float* const* deltas_dev,
                        const float* const* ctrness_dev, const int* h, const int* w, const int* strides, int num_anchors,
                        int num_classes, const float* cell_anchors_host, int variant, float score_thresh, int topk,
                        float nms_thresh, int max_det, int img_h, int img_w, float* out_boxes_dev, float* out_scores_dev,
@@ -239,26 +240,28 @@ int tcb_rotated_iou(tcb_ctx* ctx, const float* boxes_a_dev, int n, const float* 
 
 /* class_agnostic_nms without the score cut (OPCD/pcdet/models/model_utils/model_nms_utils.py:13-19) =
  * topk(min(pre_max, n)) by score + nms_gpu (iou3d_nms_utils.py:84-99, src/iou3d_nms.cpp:90-136,
- * nms_kernel src/iou3d_nms_kernel.cu:267-311) + [:post_max]. Order: score descending, ties by lower
- * index. keep_dev[post_max]: indices into the input, in kept order; count_dev[1].
- * pre_max <= 4096, post_max <= 1024. */
-int tcb_rotated_nms(tcb_ctx* ctx, const float* boxes_dev, const float* scores_dev, int n, float thresh,
+ * nms_kernel src/iou3d_nms_kernel.cu:267-311) + [:post_max], for b independent box sets (the per-sample loop of
+ * OPCD/pcdet/models/detectors/detector3d_template.py:196-199): boxes_dev [b,n,7], scores_dev [b,n].
+ * Order: score descending, ties by lower index. keep_dev [b,post_max]: indices into the set, in kept order;
+ * count_dev [b]. pre_max <= 4096, post_max <= 1024. */
+int tcb_rotated_nms(tcb_ctx* ctx, const float* boxes_dev, const float* scores_dev, int b, int n, float thresh,
                     int pre_max, int post_max, int* keep_dev, int* count_dev, void* stream);
 
 /*
- * PointPillars anchor head post for one frame: analytic anchors (AnchorGenerator.generate_anchors,
+ * PointPillars anchor head post for a batch of b frames: analytic anchors (AnchorGenerator.generate_anchors,
  * OPCD/pcdet/models/dense_heads/target_assigner/anchor_generator.py:17-60, align_center False, one size per
  * class) + ResidualCoder.decode_torch (OPCD/pcdet/utils/box_coder_utils.py:45-77) + direction bins
- * (generate_predicted_boxes, OPCD/pcdet/models/dense_heads/anchor_head_template.py:225-272, limit_period
- * OPCD/pcdet/utils/common_utils.py:21-24) + post_processing (OPCD/pcdet/models/detectors/detector3d_template.py:
- * 178-284: sigmoid, max over classes, label+1) + class_agnostic_nms(score_thresh, pre_max, nms_thresh, post_max).
- * cls_dev [h,w,A*num_class], box_dev [h,w,A*7], dir_dev [h,w,A*num_dir_bins] (NULL = no direction classifier),
- * A = num_class*num_rot anchors per location ordered (class, rotation); anchor_sizes [num_class*3] (dx,dy,dz),
- * anchor_bottoms [num_class], anchor_rotations [num_class*num_rot] are host arrays.
- * Outputs: boxes [post_max,7], scores [post_max], labels [post_max] int64 (1-based), count [1].
+ * (generate_predicted_boxes(batch_size, ...), OPCD/pcdet/models/dense_heads/anchor_head_template.py:225-272,
+ * limit_period OPCD/pcdet/utils/common_utils.py:21-24) + post_processing (OPCD/pcdet/models/detectors/
+ * detector3d_template.py:178-284: per sample :196-199 sigmoid, max over classes, label+1) +
+ * class_agnostic_nms(score_thresh, pre_max, nms_thresh, post_max). A frame's result does not depend on the batch.
+ * cls_dev [b,h,w,A*num_class], box_dev [b,h,w,A*7], dir_dev [b,h,w,A*num_dir_bins] (NULL = no direction
+ * classifier), A = num_class*num_rot anchors per location ordered (class, rotation); anchor_sizes [num_class*3]
+ * (dx,dy,dz), anchor_bottoms [num_class], anchor_rotations [num_class*num_rot] are host arrays.
+ * Outputs: boxes [b,post_max,7], scores [b,post_max], labels [b,post_max] int64 (1-based), count [b].
  */
-size_t tcb_pp_anchor_post_workspace(int h, int w, int num_class, int num_rot);
-int tcb_pp_anchor_post(tcb_ctx* ctx, const float* cls_dev, const float* box_dev, const float* dir_dev, int h, int w,
+size_t tcb_pp_anchor_post_workspace(int b, int h, int w, int num_class, int num_rot);
+int tcb_pp_anchor_post(tcb_ctx* ctx, const float* cls_dev, const float* box_dev, const float* dir_dev, int b, int h, int w,
                        int num_class, int num_rot, const float anchor_range[6], const float* anchor_sizes,
                        const float* anchor_bottoms, const float* anchor_rotations, float dir_offset,
                        float dir_limit_offset, int num_dir_bins, float score_thresh, float nms_thresh, int pre_max,
@@ -266,18 +269,18 @@ int tcb_pp_anchor_post(tcb_ctx* ctx, const float* cls_dev, const float* box_dev,
                        int* out_count_dev, void* stream);
 
 /*
- * CenterPoint head post for one frame: CenterHead.generate_predicted_boxes
+ * CenterPoint head post for a batch of b frames: CenterHead.generate_predicted_boxes(batch_size, pred_dicts)
  * (OPCD/pcdet/models/dense_heads/center_head.py:253-304) = per head sigmoid + exp, _topk and
  * decode_bbox_from_heatmap (OPCD/pcdet/models/model_utils/centernet_utils.py:136-216), centre-range and
- * score > thresh mask, class id mapping, class_agnostic_nms(pre_max, nms_thresh, post_max); heads concatenated,
- * labels + 1. Per-head tensors are NCHW planes of one frame: hm [c,h,w], center [2,h,w], center_z [1,h,w],
- * dim [3,h,w] (log), rot [2,h,w] (cos, sin), vel [2,h,w] (vel_dev or its entries may be NULL).
+ * score > thresh mask, class id mapping, class_agnostic_nms(pre_max, nms_thresh, post_max); per frame the heads
+ * concatenated, labels + 1. Per-head tensors are NCHW: hm [b,c,h,w], center [b,2,h,w], center_z [b,1,h,w],
+ * dim [b,3,h,w] (log), rot [b,2,h,w] (cos, sin), vel [b,2,h,w] (vel_dev or its entries may be NULL).
  * The `*_dev` arguments are HOST arrays of num_heads device pointers; head_num_class [num_heads] and
- * class_id_map (concatenated per head, 0-based) are host arrays. Outputs: boxes [heads*post_max, 9],
- * scores, labels int64 (1-based), count [1]. K <= 4096.
+ * class_id_map (concatenated per head, 0-based) are host arrays. Outputs: boxes [b, heads*post_max, 9],
+ * scores [b, heads*post_max], labels int64 (1-based), count [b]. K <= 4096.
  */
-size_t tcb_centerpoint_post_workspace(int num_heads, int pre_max, int post_max);
-int tcb_centerpoint_post(tcb_ctx* ctx, int num_heads, const float* const* hm_dev, const float* const* center_dev,
+size_t tcb_centerpoint_post_workspace(int b, int num_heads, int pre_max, int post_max);
+int tcb_centerpoint_post(tcb_ctx* ctx, int b, int num_heads, const float* const* hm_dev, const float* const* center_dev,
                          const float* const* center_z_dev, const float* const* dim_dev, const float* const* rot_dev,
                          const float* const* vel_dev, const int* head_num_class, const int* class_id_map, int h, int w,
                          int feature_map_stride, const float voxel_size_xy[2], const float range_min_xy[2],

@@ -166,6 +166,13 @@ def test_pp_reference_glue_golden(engine):
     for b in range(2):
         gb, gs, gl = _pp_gpu(engine, g["pp_cls"][b], g["pp_box"][b], g["pp_dir"][b], anchor_range=g["pp_range"].tolist(), **PP_SMALL)
         _same_as_reference(gb, gs, gl, g, "pp", b)
+    # the batch in one call, as generate_predicted_boxes(batch_size, ...) / post_processing take it
+    ob, osc, ol, cnt = engine.pp_anchor_post(*(torch.from_numpy(g[k]).cuda() for k in ("pp_cls", "pp_box", "pp_dir")),
+                                             anchor_range=g["pp_range"].tolist(), **PP_SMALL)
+    assert ob.shape == (2, 500, 7) and cnt.shape == (2,)
+    for b in range(2):
+        k = int(cnt[b])
+        _same_as_reference(ob[b, :k].cpu().numpy(), osc[b, :k].cpu().numpy(), ol[b, :k].cpu().numpy(), g, "pp", b)
 
 
 def test_centerpoint_reference_glue_golden(engine):
@@ -175,6 +182,13 @@ def test_centerpoint_reference_glue_golden(engine):
         heads = [{k: np.ascontiguousarray(g[f"cp{h}_{k}"][b]) for k in ("hm", "center", "center_z", "dim", "rot", "vel")} for h in range(2)]
         gb, gs, gl = _cp_gpu(engine, heads, class_map=[[0], [1, 2]], k=60, score_thresh=0.1, nms_thresh=0.2, pre_max=1000, post_max=30)
         _same_as_reference(gb, gs, gl, g, "cp", b)
+    heads = [{k: torch.from_numpy(g[f"cp{h}_{k}"]).cuda() for k in ("hm", "center", "center_z", "dim", "rot", "vel")} for h in range(2)]
+    ob, osc, ol, cnt = engine.centerpoint_post(heads, [[0], [1, 2]], NUSC["feature_map_stride"], NUSC["voxel_size"], NUSC["point_cloud_range"],
+                                               NUSC["post_center_limit_range"], k=60, score_thresh=0.1, nms_thresh=0.2, pre_max=1000, post_max=30)
+    assert ob.shape == (2, 60, 9) and cnt.shape == (2,)
+    for b in range(2):
+        k = int(cnt[b])
+        _same_as_reference(ob[b, :k].cpu().numpy(), osc[b, :k].cpu().numpy(), ol[b, :k].cpu().numpy(), g, "cp", b)
 
 
 @pytest.mark.parametrize("tag", ["rot", "rot_all"])
@@ -197,3 +211,36 @@ def test_remove_low_score_nu_reference_golden(engine):
     assert "metadata" not in res
     assert np.array_equal(res["box3d_lidar"], g["out_boxes"]) and np.array_equal(res["scores"], g["out_scores"]) and np.array_equal(res["labels"], g["out_labels"])
     assert post.get_annotations_indices(6, 0.15, g["labels"], g["scores"]) == g["motorcycle_idx"].tolist()
+
+
+def test_batched_frames_equal_their_single_calls(engine):
+    """Full-size C4 / C5 frames in one call (wide NMS path, several frames): every frame's rows are those of its own call."""
+    frames = [synth.pp_head_outputs(4100 + i) for i in range(3)]
+    cls, box, dirp = (torch.from_numpy(np.stack([f[j] for f in frames])).cuda() for j in range(3))
+    ob, osc, ol, cnt = engine.pp_anchor_post(cls, box, dirp, **KITTI_ANCHORS)
+    for i, f in enumerate(frames):
+        gb, gs, gl = _pp_gpu(engine, *f, **KITTI_ANCHORS)
+        k = int(cnt[i])
+        assert k == len(gs) and k > 20
+        assert np.array_equal(ob[i, :k].cpu().numpy(), gb) and np.array_equal(osc[i, :k].cpu().numpy(), gs) and np.array_equal(ol[i, :k].cpu().numpy(), gl)
+    want = box3d.pp_anchor_post(*frames[2], **KITTI_ANCHORS)
+    k = int(cnt[2])
+    assert np.array_equal(ol[2, :k].cpu().numpy(), want["pred_labels"].numpy())
+    _close(ob[2, :k].cpu().numpy(), want["pred_boxes"].numpy(), rtol=1e-5, atol=1e-5)
+    cps = [synth.centerpoint_head_outputs(5100 + i) for i in range(3)]
+    heads = [{k: torch.from_numpy(np.stack([c[h][k] for c in cps])).cuda() for k in cps[0][h]} for h in range(6)]
+    ob, osc, ol, cnt = engine.centerpoint_post(heads, CLASS_MAP, NUSC["feature_map_stride"], NUSC["voxel_size"], NUSC["point_cloud_range"],
+                                               NUSC["post_center_limit_range"])
+    for i, c in enumerate(cps):
+        gb, gs, gl = _cp_gpu(engine, c)
+        k = int(cnt[i])
+        assert k == len(gs) and k > 20
+        assert np.array_equal(ob[i, :k].cpu().numpy(), gb) and np.array_equal(osc[i, :k].cpu().numpy(), gs) and np.array_equal(ol[i, :k].cpu().numpy(), gl)
+    # rotated NMS of several box sets at once (single-CTA path and wide path)
+    for n in (300, 3000):
+        boxes = np.stack([synth.random_boxes7(n, 600 + i, extent=30.0) for i in range(4)])
+        scores = np.stack([np.random.default_rng(700 + i).permutation(n).astype(np.float32) / n for i in range(4)])
+        keep, cnt = engine.rotated_nms(torch.from_numpy(boxes).cuda(), torch.from_numpy(scores).cuda(), 0.1, 4096, 500)
+        for i in range(4):
+            want = box3d.nms_gpu(boxes[i], scores[i], 0.1, pre_maxsize=4096)[:500].tolist()
+            assert keep[i, :int(cnt[i])].cpu().tolist() == want

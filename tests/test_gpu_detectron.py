@@ -48,3 +48,27 @@ def test_many_candidates_and_nothing(engine):
     _check(_run(engine, logits, deltas, cells, topk=300, max_det=200), dp.dense_inference(logits, deltas, STRIDES, cells, HW, topk=300, max_det=200))
     empty = [np.full_like(l, -8.0) for l in logits]
     assert _run(engine, empty, deltas, cells)[0].shape[0] == 0
+
+
+def test_batched_images_equal_their_single_calls(engine):
+    """Three images in one call ([B,A*K,H,W] levels): each image's detections are those of its own call and of the oracle."""
+    cells = dp.retinanet_cell_anchors()
+    imgs = [synth.detectron_head_outputs(3100 + i, num_classes=8) for i in range(3)]
+    logits = [torch.from_numpy(np.stack([im[0][l] for im in imgs])).cuda() for l in range(5)]
+    deltas = [torch.from_numpy(np.stack([im[1][l] for im in imgs])).cuda() for l in range(5)]
+    ob, osc, oc, cnt = engine.detectron_post(logits, deltas, STRIDES, cells, HW)
+    assert ob.shape == (3, 100, 4) and cnt.shape == (3,)
+    for i, im in enumerate(imgs):
+        one = _run(engine, im[0], im[1], cells)
+        k = int(cnt[i])
+        assert np.array_equal(ob[i, :k].cpu().numpy(), one[0]) and np.array_equal(osc[i, :k].cpu().numpy(), one[1]) and np.array_equal(oc[i, :k].cpu().numpy(), one[2])
+    _check((ob[2, :int(cnt[2])].cpu().numpy(), osc[2, :int(cnt[2])].cpu().numpy(), oc[2, :int(cnt[2])].cpu().numpy()),
+           dp.dense_inference(imgs[2][0], imgs[2][1], STRIDES, cells, HW))
+    fc = [synth.detectron_head_outputs(3110 + i, anchors_per_loc=1, fcos=True, planted=300) for i in range(2)]
+    fcells = dp.fcos_cell_anchors(STRIDES)
+    stack = lambda j: [torch.from_numpy(np.stack([im[j][l] for im in fc])).cuda() for l in range(5)]
+    ob, osc, oc, cnt = engine.detectron_post(stack(0), stack(1), STRIDES, fcells, HW, ctrness=stack(2), score_thresh=0.2, nms_thresh=0.6)
+    for i, im in enumerate(fc):
+        one = _run(engine, im[0], im[1], fcells, im[2], score_thresh=0.2, nms_thresh=0.6)
+        k = int(cnt[i])
+        assert k == len(one[1]) and np.array_equal(ob[i, :k].cpu().numpy(), one[0]) and np.array_equal(oc[i, :k].cpu().numpy(), one[2])

@@ -46,8 +46,8 @@ SIGNATURES = {
     "tcb_yolo4_post_workspace": (c_size_t, [c_int, c_int]),
     "tcb_yolo4_post": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_float, c_int, c_void_p, c_void_p, c_void_p]),
     "tcb_box_iou": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p]),
-    "tcb_detectron_post_workspace": (c_size_t, [c_int, P(c_int), P(c_int), c_int, c_int, c_int]),
-    "tcb_detectron_post": (c_int, [c_void_p, c_int, P(c_void_p), P(c_void_p), P(c_void_p), P(c_int), P(c_int), P(c_int), c_int, c_int,
+    "tcb_detectron_post_workspace": (c_size_t, [c_int, c_int, P(c_int), P(c_int), c_int, c_int, c_int]),
+    "tcb_detectron_post": (c_int, [c_void_p, c_int, c_int, P(c_void_p), P(c_void_p), P(c_void_p), P(c_int), P(c_int), P(c_int), c_int, c_int,
                                    P(c_float), c_int, c_float, c_int, c_float, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                    c_void_p, c_void_p]),
     "tcb_voxelize_workspace": (c_size_t, [c_int, c_int, c_int, c_ll]),
@@ -59,13 +59,13 @@ SIGNATURES = {
     "tcb_dynamic_pillar": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, P(c_double), P(c_double), c_void_p, c_void_p, c_void_p,
                                    c_void_p, c_void_p]),
     "tcb_rotated_iou": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p]),
-    "tcb_rotated_nms": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_float, c_int, c_int, c_void_p, c_void_p, c_void_p]),
-    "tcb_pp_anchor_post_workspace": (c_size_t, [c_int, c_int, c_int, c_int]),
-    "tcb_pp_anchor_post": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, P(c_float), P(c_float),
+    "tcb_rotated_nms": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "tcb_pp_anchor_post_workspace": (c_size_t, [c_int, c_int, c_int, c_int, c_int]),
+    "tcb_pp_anchor_post": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, P(c_float), P(c_float),
                                    P(c_float), P(c_float), c_float, c_float, c_int, c_float, c_float, c_int, c_int,
                                    c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
-    "tcb_centerpoint_post_workspace": (c_size_t, [c_int, c_int, c_int]),
-    "tcb_centerpoint_post": (c_int, [c_void_p, c_int, P(c_void_p), P(c_void_p), P(c_void_p), P(c_void_p), P(c_void_p), P(c_void_p),
+    "tcb_centerpoint_post_workspace": (c_size_t, [c_int, c_int, c_int, c_int]),
+    "tcb_centerpoint_post": (c_int, [c_void_p, c_int, c_int, P(c_void_p), P(c_void_p), P(c_void_p), P(c_void_p), P(c_void_p), P(c_void_p),
                                      P(c_int), P(c_int), c_int, c_int, c_int, P(c_float), P(c_float), P(c_float), c_int,
                                      c_float, c_float, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "tcb_class_score_filter": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, P(c_int), P(c_float), c_void_p, c_void_p, c_void_p]),

@@ -1,4 +1,4 @@
-// detectron2 dense-detector inference (RetinaNet / FCOS) for one image.
+// detectron2 dense-detector inference (RetinaNet / FCOS) for a batch of images.
 // In the reference this runs inside the served TorchScript model (examples/RetinaNet_detectron/config.pbtxt:1-34);
 // the client only unpacks its three output tensors (clients/postprocess/detectron_postprocess.py:26-37,
 // utils/postprocess.py:368-468). detectron2 is neither vendored nor pinned: PARITY UNPINNED, restated from its
@@ -19,16 +19,27 @@ constexpr int DET_CACHE = 16384;   // candidate keys a level kernel keeps in sha
 __device__ __forceinline__ float sigmoidf_ref(float x) { return 1.f / (1.f + expf(-x)); }
 
 struct Level {
-    const float *logits, *deltas, *ctrness;   // [A*K,H,W], [A*4,H,W], FCOS: [1,H,W]
+    const float *logits, *deltas, *ctrness;   // [b,A*K,H,W], [b,A*4,H,W], FCOS: [b,1,H,W]
     int H, W, stride;
     float cell[MAX_ANCHORS][4];               // cell anchors (x0,y0,x1,y1) around the location
-    unsigned long long* cand; int* cand_count; // this level's candidates (score, flat index in (y,x,a,k) order)
+    unsigned long long* cand;                  // this level's candidates (score, flat index in (y,x,a,k) order): [b][A*K*H*W]
 };
 struct DetParams {
     Level lv[MAX_LEVELS];
     int num_levels, A, K, variant, topk, max_det, img_h, img_w;
     float score_thresh, nms_thresh;
+    int* counts;                               // [b][MAX_LEVELS] candidates per image and level
 };
+// level l of image `img`: the level with its pointers moved to that image
+__device__ __forceinline__ Level level_of(const DetParams& p, int l, int img, int*& count) {
+    Level L = p.lv[l];
+    const long long HW = (long long)L.H * L.W;
+    L.logits += img * (long long)p.A * p.K * HW; L.deltas += img * (long long)p.A * 4 * HW;
+    if (L.ctrness) L.ctrness += img * HW;
+    L.cand += img * (long long)p.A * p.K * HW;
+    count = p.counts + img * MAX_LEVELS + l;
+    return L;
+}
 
 // Candidates of every level in one launch: grid = (spatial chunks of 4096, channels A*K, levels), four 16-byte loads
 // per thread when the plane allows. HBM-bound: a logit below logit_floor cannot pass the
@@ -38,7 +49,8 @@ constexpr int DC_Q = 4;                                   // 16-byte loads per t
 constexpr int DC_SPAN = 256 * 4 * DC_Q;                   // logits per CTA
 __global__ void __launch_bounds__(256) det_candidates_kernel(const DetParams p, float logit_floor) {
     pdl_wait();
-    const Level& L = p.lv[blockIdx.z];
+    int* cand_count;
+    const Level L = level_of(p, blockIdx.z % p.num_levels, blockIdx.z / p.num_levels, cand_count);   // z = (image, level)
     const int HW = L.H * L.W;
     if ((int)blockIdx.x * DC_SPAN >= HW) return;  // (whole CTA)
     __shared__ int s_count, s_base;
@@ -90,7 +102,7 @@ __global__ void __launch_bounds__(256) det_candidates_kernel(const DetParams p, 
         }
     }
     __syncthreads();
-    if (threadIdx.x == 0) s_base = s_count ? atomicAdd(L.cand_count, s_count) : 0;
+    if (threadIdx.x == 0) s_base = s_count ? atomicAdd(cand_count, s_count) : 0;
     __syncthreads();
     const int gbase = s_base;
 #pragma unroll
@@ -132,15 +144,20 @@ __global__ void __launch_bounds__(T, 1) det_level_kernel(const DetParams p, floa
     pdl_wait();
     __shared__ DLevelShared S;
     extern __shared__ __align__(16) unsigned long long key_cache[];
-    const int tid = threadIdx.x, l = blockIdx.x;
+    const int tid = threadIdx.x, l = blockIdx.x, img = blockIdx.y;
     const float scale_clamp = logf(1000.f / 16.f);
-    int M = 0;
-    for (int q = 0; q < l; q++) M += min(min(*p.lv[q].cand_count, p.A * p.K * p.lv[q].H * p.lv[q].W), p.topk);
     {
-        const Level& L = p.lv[l];
+        const size_t mo = (size_t)img * p.num_levels * p.topk;   // this image's rows of the merged arrays
+        mbox += mo; mscore += mo; mcls += mo; mkeys += mo;
+    }
+    int M = 0;
+    for (int q = 0; q < l; q++) M += min(min(p.counts[img * MAX_LEVELS + q], p.A * p.K * p.lv[q].H * p.lv[q].W), p.topk);
+    {
+        int* cand_count;
+        const Level L = level_of(p, l, img, cand_count);
 
         const int cap = p.A * p.K * L.H * L.W;
-        const int n = min(*L.cand_count, cap);
+        const int n = min(*cand_count, cap);
         const unsigned long long* ck = L.cand;
         auto key_of = [&](int i) { return ck[i]; };
         const int m = sel::cta_topk_sorted(key_of, n, p.topk, S.skeys, S.sel, key_cache, DET_CACHE);
@@ -182,9 +199,14 @@ __global__ void __launch_bounds__(T, 1) det_post_kernel(const DetParams p, float
     pdl_wait();
     extern __shared__ __align__(16) unsigned char smem_raw[];
     DFrameShared& S = *reinterpret_cast<DFrameShared*>(smem_raw);
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, img = blockIdx.x;
+    {
+        const size_t mo = (size_t)img * p.num_levels * p.topk;
+        mbox += mo; mscore += mo; mcls += mo; mkeys += mo;
+        out_boxes += (size_t)img * p.max_det * 4; out_scores += (size_t)img * p.max_det; out_classes += (size_t)img * p.max_det; out_count += img;
+    }
     int M = 0;
-    for (int l = 0; l < p.num_levels; l++) M += min(min(*p.lv[l].cand_count, p.A * p.K * p.lv[l].H * p.lv[l].W), p.topk);
+    for (int l = 0; l < p.num_levels; l++) M += min(min(p.counts[img * MAX_LEVELS + l], p.A * p.K * p.lv[l].H * p.lv[l].W), p.topk);
     // torchvision.ops.batched_nms as the served (CUDA) model runs it: coordinate trick unless boxes.numel() > 20000
     auto mkey_of = [&](int i) { return mkeys[i]; };
     const int m = sel::cta_topk_sorted(mkey_of, M, PRE_CAP, S.skeys, S.sel);
@@ -228,14 +250,15 @@ __global__ void __launch_bounds__(T, 1) det_post_kernel(const DetParams p, float
 
 }  // namespace
 
-extern "C" size_t tcb_detectron_post_workspace(int num_levels, const int* h, const int* w, int num_anchors, int num_classes, int topk) {
-    size_t bytes = 8192;
-    for (int l = 0; l < num_levels; l++) bytes += (size_t)h[l] * w[l] * num_anchors * num_classes * 8 + 512;
-    bytes += (size_t)num_levels * (size_t)topk * (16 + 4 + 4 + 8) + 2048;
+extern "C" size_t tcb_detectron_post_workspace(int b, int num_levels, const int* h, const int* w, int num_anchors, int num_classes, int topk) {
+    const size_t bb = (size_t)(b > 0 ? b : 1);
+    size_t bytes = 8192 + bb * MAX_LEVELS * 4;
+    for (int l = 0; l < num_levels; l++) bytes += bb * (size_t)h[l] * w[l] * num_anchors * num_classes * 8 + 512;
+    bytes += bb * (size_t)num_levels * (size_t)topk * (16 + 4 + 4 + 8) + 2048;
     return bytes;
 }
 
-extern "C" int tcb_detectron_post(tcb_ctx* ctx, int num_levels, const float* const* logits_dev, const float* const* deltas_dev,
+extern "C" int tcb_detectron_post(tcb_ctx* ctx, int b, int num_levels, const float* const* logits_dev, const float* const* deltas_dev,
                                   const float* const* ctrness_dev, const int* h, const int* w, const int* strides, int num_anchors,
                                   int num_classes, const float* cell_anchors_host, int variant, float score_thresh, int topk,
                                   float nms_thresh, int max_det, int img_h, int img_w, float* out_boxes_dev, float* out_scores_dev,
@@ -246,7 +269,8 @@ extern "C" int tcb_detectron_post(tcb_ctx* ctx, int num_levels, const float* con
     if (num_levels < 1 || num_levels > MAX_LEVELS || num_anchors < 1 || num_anchors > MAX_ANCHORS)
         return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_detectron_post: levels %d (<= %d), anchors %d (<= %d)", num_levels, MAX_LEVELS, num_anchors, MAX_ANCHORS);
     TCB_REQUIRE(ctx, variant == 0 || (variant == 1 && ctrness_dev), "tcb_detectron_post: variant 0 (RetinaNet) or 1 (FCOS, needs centerness)");
-    TCB_REQUIRE(ctx, num_classes >= 1 && topk >= 1 && max_det >= 1 && nms_thresh >= 0.f, "tcb_detectron_post: bad parameters");
+    TCB_REQUIRE(ctx, b >= 1 && num_classes >= 1 && topk >= 1 && max_det >= 1 && nms_thresh >= 0.f, "tcb_detectron_post: bad parameters");
+    if ((long long)b * num_levels > 65535) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_detectron_post: images x levels > 65535");
     if (topk > PRE_CAP || (long long)topk * num_levels > 16384) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_detectron_post: topk %d too large", topk);
     if (max_det > POST_CAP) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_detectron_post: max_det %d > %d", max_det, POST_CAP);
     cudaStream_t st = (cudaStream_t)stream;
@@ -254,8 +278,9 @@ extern "C" int tcb_detectron_post(tcb_ctx* ctx, int num_levels, const float* con
     memset(&p, 0, sizeof(p));
     p.num_levels = num_levels; p.A = num_anchors; p.K = num_classes; p.variant = variant; p.topk = topk; p.max_det = max_det;
     p.img_h = img_h; p.img_w = img_w; p.score_thresh = score_thresh; p.nms_thresh = nms_thresh;
-    TCB_WS(ctx, counts, int, 64);
-    TCB_CUDA(ctx, cudaMemsetAsync(counts, 0, sizeof(int) * 64, st));
+    TCB_WS(ctx, counts, int, (size_t)b * MAX_LEVELS);
+    TCB_CUDA(ctx, cudaMemsetAsync(counts, 0, sizeof(int) * (size_t)b * MAX_LEVELS, st));
+    p.counts = counts;
     for (int l = 0; l < num_levels; l++) {
         Level& L = p.lv[l];
         L.logits = logits_dev[l]; L.deltas = deltas_dev[l]; L.ctrness = ctrness_dev ? ctrness_dev[l] : nullptr;
@@ -265,10 +290,10 @@ extern "C" int tcb_detectron_post(tcb_ctx* ctx, int num_levels, const float* con
         if (n > (1ll << 30)) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_detectron_post: level %d too large", l);
         for (int a = 0; a < num_anchors; a++)
             for (int j = 0; j < 4; j++) L.cell[a][j] = cell_anchors_host[((size_t)l * num_anchors + a) * 4 + j];
-        TCB_WS(ctx, cand, unsigned long long, n);
-        L.cand = cand; L.cand_count = counts + l;
+        TCB_WS(ctx, cand, unsigned long long, (size_t)b * n);
+        L.cand = cand;
     }
-    const size_t mcap = (size_t)num_levels * topk;
+    const size_t mcap = (size_t)b * num_levels * topk;
     TCB_WS(ctx, mbox, float4, mcap);
     TCB_WS(ctx, mscore, float, mcap);
     TCB_WS(ctx, mcls, int, mcap);
@@ -280,14 +305,14 @@ extern "C" int tcb_detectron_post(tcb_ctx* ctx, int num_levels, const float* con
         int hw_max = 1;
         for (int l = 0; l < num_levels; l++) hw_max = hw_max > p.lv[l].H * p.lv[l].W ? hw_max : p.lv[l].H * p.lv[l].W;
         TCB_REQUIRE(ctx, num_anchors * num_classes <= 65535, "tcb_detectron_post: more than 65535 channels");
-        TCB_KLAUNCH(ctx, det_candidates_kernel, dim3(tcb_div_up(hw_max, DC_SPAN), num_anchors * num_classes, num_levels), 256, 0, st, p, logit_floor);
+        TCB_KLAUNCH(ctx, det_candidates_kernel, dim3(tcb_div_up(hw_max, DC_SPAN), num_anchors * num_classes, num_levels * b), 256, 0, st, p, logit_floor);
         TCB_LAUNCHED(ctx);
     }
     TCB_CUDA(ctx, cudaFuncSetAttribute(det_level_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DET_CACHE * 8));
-    TCB_KLAUNCH(ctx, det_level_kernel, num_levels, T, DET_CACHE * 8, st, p, mbox, mscore, mcls, mkeys);
+    TCB_KLAUNCH(ctx, det_level_kernel, dim3(num_levels, b), T, DET_CACHE * 8, st, p, mbox, mscore, mcls, mkeys);
     TCB_LAUNCHED(ctx);
     TCB_CUDA(ctx, cudaFuncSetAttribute(det_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DFrameShared)));
-    TCB_KLAUNCH(ctx, det_post_kernel, 1, T, sizeof(DFrameShared), st, p, mbox, mscore, mcls, mkeys, out_boxes_dev, out_scores_dev, out_classes_dev, out_count_dev);
+    TCB_KLAUNCH(ctx, det_post_kernel, b, T, sizeof(DFrameShared), st, p, mbox, mscore, mcls, mkeys, out_boxes_dev, out_scores_dev, out_classes_dev, out_count_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }

@@ -64,12 +64,14 @@ static_assert(sizeof(FrameShared) <= 227 * 1024, "FrameShared exceeds the 227 KB
 // ---------------------------------------------------------------------------------------------------------
 // tcb_rotated_nms: scores + boxes in any order -> top pre_max by score -> greedy NMS -> keep indices
 // ---------------------------------------------------------------------------------------------------------
+// blockIdx.x = box set of the batch (boxes [b,n,7], scores [b,n], keep [b,post_max], count [b])
 __global__ void __launch_bounds__(T, 1) rotated_nms_kernel(const float* __restrict__ boxes, const float* __restrict__ scores, int n,
                                                            float thresh, int pre_max, int post_max,
                                                            int* __restrict__ keep, int* __restrict__ count) {
     pdl_wait();
     extern __shared__ __align__(16) unsigned char smem_raw[];
     FrameShared& S = *reinterpret_cast<FrameShared*>(smem_raw);
+    boxes += 7ll * n * blockIdx.x; scores += (long long)n * blockIdx.x; keep += (long long)post_max * blockIdx.x; count += blockIdx.x;
     auto key_of = [&](int i) { return sel::make_key(__ldg(scores + i), (unsigned)i); };
     const int m = sel::cta_topk_sorted(key_of, n, pre_max, S.skeys, S.sel);
     for (int c = threadIdx.x; c < m; c += T) S.R[c] = rot::make_rbox(boxes + 7ll * sel::key_index(S.skeys[c]));
@@ -106,9 +108,12 @@ struct OrderShared {
 // list (one slot reservation per tile) for rot_pairs_kernel; the tile's mask words are written as zeros. Should the
 // list be full, the tile evaluates its pairs itself.
 // m_dev[0] = number of candidates, m_dev[1] = pairs listed so far (zeroed by the order kernel).
+// blockIdx.z = candidate set of the batch; per-set strides: PRE_CAP boxes, WIDE_M ints, mask_stride words, pair_cap pairs
+constexpr int WIDE_M = 64;   // ints per set in the m array ([0] candidates, [1] pairs listed)
 __global__ void __launch_bounds__(MASK_T) rot_mask_kernel(const rot::RBox* __restrict__ R, int* __restrict__ m_dev, float thresh,
-                                                          unsigned long long* __restrict__ mask, unsigned* __restrict__ pairs, int pair_cap) {
+                                                          unsigned long long* __restrict__ mask, size_t mask_stride, unsigned* __restrict__ pairs, int pair_cap) {
     pdl_wait();
+    R += (size_t)blockIdx.z * PRE_CAP; m_dev += blockIdx.z * WIDE_M; mask += blockIdx.z * mask_stride; pairs += (size_t)blockIdx.z * pair_cap;
     const int bi = blockIdx.y, bj = blockIdx.x;   // row tile, column tile
     const int m = m_dev[0];
     if (bj < bi || bj * 64 >= m) return;          // lower triangle / past the last candidate: never read
@@ -164,8 +169,9 @@ __global__ void __launch_bounds__(MASK_T) rot_mask_kernel(const rot::RBox* __res
 // Mask, step 2: the exact rotated IoU of every listed pair, one pair per thread with all lanes busy (inside the tiles
 // the few pairs that survive the distance test would each run with most of their warp idle).
 __global__ void __launch_bounds__(256) rot_pairs_kernel(const rot::RBox* __restrict__ R, const int* __restrict__ m_dev, float thresh,
-                                                        const unsigned* __restrict__ pairs, int pair_cap, unsigned long long* __restrict__ mask) {
+                                                        const unsigned* __restrict__ pairs, int pair_cap, unsigned long long* __restrict__ mask, size_t mask_stride) {
     pdl_wait();
+    R += (size_t)blockIdx.y * PRE_CAP; m_dev += blockIdx.y * WIDE_M; mask += blockIdx.y * mask_stride; pairs += (size_t)blockIdx.y * pair_cap;
     const int total = min(m_dev[1], pair_cap);
     for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < total; q += gridDim.x * blockDim.x) {
         const unsigned e = pairs[q];
@@ -184,6 +190,7 @@ __global__ void __launch_bounds__(T, 1) rot_order_kernel(const float* __restrict
     pdl_wait();
     __shared__ OrderShared S;
     extern __shared__ __align__(16) unsigned long long key_cache[];
+    scores += (long long)n * blockIdx.x; skeys_out += (size_t)blockIdx.x * PRE_CAP; m_out += blockIdx.x * WIDE_M;
     auto key_of = [&](int i) { return sel::make_key(__ldg(scores + i), (unsigned)i); };
     const int m = sel::cta_topk_sorted(key_of, n, pre_max, S.skeys, S.sel, key_cache, ORDER_CACHE);
     for (int c = threadIdx.x; c < m; c += T) skeys_out[c] = S.skeys[c];
@@ -192,17 +199,19 @@ __global__ void __launch_bounds__(T, 1) rot_order_kernel(const float* __restrict
 
 // the ordered candidates' boxes, one thread each over the whole grid (inside the one-CTA order kernel the four
 // dependent rounds of scattered loads per thread cost more than the selection itself)
-__global__ void __launch_bounds__(256) rot_rbox_kernel(const float* __restrict__ boxes, const unsigned long long* __restrict__ skeys,
+__global__ void __launch_bounds__(256) rot_rbox_kernel(const float* __restrict__ boxes, int n, const unsigned long long* __restrict__ skeys,
                                                        const int* __restrict__ m_dev, rot::RBox* __restrict__ R_out) {
     pdl_wait();
+    boxes += 7ll * n * blockIdx.y; skeys += (size_t)blockIdx.y * PRE_CAP; m_dev += blockIdx.y * WIDE_M; R_out += (size_t)blockIdx.y * PRE_CAP;
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c < m_dev[0]) R_out[c] = rot::make_rbox(boxes + 7ll * sel::key_index(skeys[c]));
 }
 
-__global__ void __launch_bounds__(SWEEP_T, 1) rot_sweep_kernel(const unsigned long long* __restrict__ mask, const unsigned long long* __restrict__ skeys,
+__global__ void __launch_bounds__(SWEEP_T, 1) rot_sweep_kernel(const unsigned long long* __restrict__ mask, size_t mask_stride, const unsigned long long* __restrict__ skeys,
                                                           const int* __restrict__ m_dev, int post_max, int* __restrict__ keep,
                                                           int* __restrict__ count) {
     pdl_wait();
+    mask += blockIdx.x * mask_stride; skeys += (size_t)blockIdx.x * PRE_CAP; m_dev += blockIdx.x * WIDE_M; keep += (long long)post_max * blockIdx.x; count += blockIdx.x;
     extern __shared__ __align__(128) unsigned char sweep_raw[];
     SweepShared& S = *reinterpret_cast<SweepShared*>(sweep_raw);
     __shared__ int nk_s;
@@ -227,30 +236,48 @@ struct PPParams {
     float dir_offset, dir_limit_offset, period;
     float score_thresh, nms_thresh;
     int pre_max, post_max;
+    int n_anchors;                               // H * W * num_class * num_rot: rows per frame of the batch
 };
 
 __device__ __forceinline__ float sigmoidf_ref(float x) { return 1.f / (1.f + expf(-x)); }  // torch.sigmoid
 
-// per anchor: sigmoid of every class logit, max / first arg-max (detector3d_template.py:217,251), keep score >= thresh
+// per anchor: sigmoid of every class logit, max (detector3d_template.py:217,251), keep score >= thresh.
+// grid (tiles of PPC_TILE anchors, frame). The tile's logits come in with 16-byte loads into shared memory (an anchor's
+// row is num_class floats: 12 bytes for KITTI), then a thread takes every 256th anchor of the tile.
+constexpr int PPC_TILE = 1024;
+template <bool VEC4>
 __global__ void __launch_bounds__(256) pp_candidates_kernel(const float* __restrict__ cls, int n_anchors, int num_class, float thresh,
                                                             unsigned long long* __restrict__ cand, int* __restrict__ cand_count) {
+    extern __shared__ __align__(16) float ppc_tile[];
     pdl_wait();
-    const int a = blockIdx.x * blockDim.x + threadIdx.x;
-    bool ok = false;
-    float best = 0.f;
-    if (a < n_anchors) {
-        const float* p = cls + (long long)a * num_class;
-        best = sigmoidf_ref(__ldg(p));
-        for (int c = 1; c < num_class; c++) best = fmaxf(best, sigmoidf_ref(__ldg(p + c)));
-        ok = best >= thresh;
+    const int f = blockIdx.y, a0 = blockIdx.x * PPC_TILE;
+    const int rows = min(PPC_TILE, n_anchors - a0);
+    const float* src = cls + ((long long)f * n_anchors + a0) * num_class;
+    const int nfl = rows * num_class;
+    if (VEC4) {
+        for (int e = threadIdx.x; e < (nfl >> 2); e += 256) reinterpret_cast<float4*>(ppc_tile)[e] = __ldg(reinterpret_cast<const float4*>(src) + e);
+        for (int e = (nfl & ~3) + threadIdx.x; e < nfl; e += 256) ppc_tile[e] = __ldg(src + e);
+    } else {
+        for (int e = threadIdx.x; e < nfl; e += 256) ppc_tile[e] = __ldg(src + e);
     }
-    const unsigned em = __ballot_sync(0xffffffffu, ok);
-    if (em) {
-        const int lane = threadIdx.x & 31;
-        int base = 0;
-        if (lane == 0) base = atomicAdd(cand_count, __popc(em));
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (ok) cand[base + __popc(em & ((1u << lane) - 1))] = sel::make_key(best, (unsigned)a);
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    for (int r = threadIdx.x; r < PPC_TILE; r += 256) {     // whole warps leave together: rows is checked per lane below
+        bool ok = false;
+        float best = 0.f;
+        if (r < rows) {
+            const float* p = ppc_tile + r * num_class;
+            best = sigmoidf_ref(p[0]);
+            for (int c = 1; c < num_class; c++) best = fmaxf(best, sigmoidf_ref(p[c]));
+            ok = best >= thresh;
+        }
+        const unsigned em = __ballot_sync(0xffffffffu, ok);
+        if (em) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(&cand_count[f], __popc(em));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (ok) cand[(long long)f * n_anchors + base + __popc(em & ((1u << lane) - 1))] = sel::make_key(best, (unsigned)(a0 + r));
+        }
     }
 }
 
@@ -295,7 +322,11 @@ __global__ void __launch_bounds__(T, 1) pp_post_kernel(const PPParams p, const f
     pdl_wait();
     extern __shared__ __align__(16) unsigned char smem_raw[];
     FrameShared& S = *reinterpret_cast<FrameShared*>(smem_raw);
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, f = blockIdx.x;    // one CTA per frame of the batch
+    cls += (long long)f * p.n_anchors * p.num_class; box_preds += (long long)f * p.n_anchors * 7;
+    if (dir_preds) dir_preds += (long long)f * p.n_anchors * p.num_dir_bins;
+    cand += (long long)f * cand_cap; cand_count += f; sorted_boxes += (size_t)f * PRE_CAP * 7;
+    out_boxes += (long long)f * p.post_max * 7; out_scores += (long long)f * p.post_max; out_labels += (long long)f * p.post_max; out_count += f;
     const int nc = min(*cand_count, cand_cap);
     auto key_of = [&](int i) { return cand[i]; };
     const int m = sel::cta_topk_sorted(key_of, nc, p.pre_max, S.skeys, S.sel);   // class_agnostic_nms topk (model_nms_utils.py:15)
@@ -330,7 +361,8 @@ __global__ void __launch_bounds__(T, 1) pp_order_kernel(const PPParams p, const 
     pdl_wait();
     __shared__ OrderShared S;
     extern __shared__ __align__(16) unsigned long long key_cache[];
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, f = blockIdx.x;
+    cand += (long long)f * cand_cap; cand_count += f; skeys_out += (size_t)f * PRE_CAP; m_out += f * WIDE_M;
     const int nc = min(*cand_count, cand_cap);
     auto key_of = [&](int i) { return cand[i]; };
     const int m = sel::cta_topk_sorted(key_of, nc, p.pre_max, S.skeys, S.sel, key_cache, ORDER_CACHE);
@@ -343,6 +375,10 @@ __global__ void __launch_bounds__(256) pp_decode_kernel(const PPParams p, const 
                                                         const unsigned long long* __restrict__ skeys, const int* __restrict__ m_dev,
                                                         float* __restrict__ sorted_boxes, rot::RBox* __restrict__ R_out) {
     pdl_wait();
+    const int f = blockIdx.y;
+    box_preds += (long long)f * p.n_anchors * 7;
+    if (dir_preds) dir_preds += (long long)f * p.n_anchors * p.num_dir_bins;
+    skeys += (size_t)f * PRE_CAP; m_dev += f * WIDE_M; sorted_boxes += (size_t)f * PRE_CAP * 7; R_out += (size_t)f * PRE_CAP;
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= m_dev[0]) return;
     float b7[7];
@@ -353,14 +389,17 @@ __global__ void __launch_bounds__(256) pp_decode_kernel(const PPParams p, const 
 }
 
 __global__ void __launch_bounds__(SWEEP_T, 1) pp_finish_kernel(const PPParams p, const float* __restrict__ cls, const unsigned long long* __restrict__ mask,
-                                                          const unsigned long long* __restrict__ skeys, const int* __restrict__ m_dev,
+                                                          size_t mask_stride, const unsigned long long* __restrict__ skeys, const int* __restrict__ m_dev,
                                                           const float* __restrict__ sorted_boxes, float* __restrict__ out_boxes,
                                                           float* __restrict__ out_scores, long long* __restrict__ out_labels,
                                                           int* __restrict__ out_count) {
     pdl_wait();
     extern __shared__ __align__(128) unsigned char sweep_raw[];
     SweepShared& S = *reinterpret_cast<SweepShared*>(sweep_raw);
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, f = blockIdx.x;
+    cls += (long long)f * p.n_anchors * p.num_class; mask += f * mask_stride; skeys += (size_t)f * PRE_CAP; m_dev += f * WIDE_M;
+    sorted_boxes += (size_t)f * PRE_CAP * 7;
+    out_boxes += (long long)f * p.post_max * 7; out_scores += (long long)f * p.post_max; out_labels += (long long)f * p.post_max; out_count += f;
     __shared__ int nk_s;
     if (tid < 32) { const int v = warp_mask_sweep(mask, *m_dev, p.post_max, S); if (tid == 0) nk_s = v; }
     __syncthreads();
@@ -404,9 +443,16 @@ __global__ void __launch_bounds__(T, 1) cp_head_kernel(const CPParams p, float* 
     pdl_wait();
     extern __shared__ __align__(16) unsigned char smem_raw[];
     FrameShared& S = *reinterpret_cast<FrameShared*>(smem_raw);
-    const int tid = threadIdx.x, h = blockIdx.x;
-    const CPHead& hd = p.head[h];
+    const int tid = threadIdx.x, h = blockIdx.x, f = blockIdx.y;   // head, frame of the batch ([b,c,H,W] tensors)
+    CPHead hd = p.head[h];
     const int HW = p.H * p.W, n = hd.num_class * HW;
+    hd.hm += (long long)f * n; hd.center += (long long)f * 2 * HW; hd.center_z += (long long)f * HW; hd.dim += (long long)f * 3 * HW;
+    hd.rot += (long long)f * 2 * HW;
+    if (hd.vel) hd.vel += (long long)f * 2 * HW;
+    {
+        const long long rows = (long long)p.num_heads * (p.pre_max + p.post_max);
+        head_boxes += f * rows * 9; head_scores += f * rows; head_labels += f * rows; head_count += f * CP_MAX_HEADS;
+    }
     // _topk (centernet_utils.py:136-151): per-class top-K then top-K across classes == global top-K of the sigmoids
     // The selection makes seven passes over the scores: compute each sigmoid once into shared memory (as ordered
     // 32-bit patterns) — with K <= 1024 only the first 1024 slots of skeys are used, so the rest of skeys and all of
@@ -484,8 +530,14 @@ __global__ void __launch_bounds__(T, 1) cp_head_kernel(const CPParams p, float* 
 __global__ void __launch_bounds__(256) cp_concat_kernel(int num_heads, int post_max, const float* __restrict__ head_boxes,
                                                         const float* __restrict__ head_scores, const int* __restrict__ head_labels,
                                                         const int* __restrict__ head_count, float* __restrict__ out_boxes,
-                                                        float* __restrict__ out_scores, long long* __restrict__ out_labels, int* __restrict__ out_count) {
+                                                        float* __restrict__ out_scores, long long* __restrict__ out_labels, int* __restrict__ out_count,
+                                                        int pre_max) {
     pdl_wait();
+    {
+        const long long f = blockIdx.x, rows = (long long)num_heads * (pre_max + post_max), orows = (long long)num_heads * post_max;
+        head_boxes += f * rows * 9; head_scores += f * rows; head_labels += f * rows; head_count += f * CP_MAX_HEADS;
+        out_boxes += f * orows * 9; out_scores += f * orows; out_labels += f * orows; out_count += f;
+    }
     int off = 0;
     for (int h = 0; h < num_heads; h++) {
         const int n = head_count[h];
@@ -553,70 +605,79 @@ static int opt_in_smem(tcb_ctx* ctx, K kernel) {
     return TCB_OK;
 }
 
-// workspace of the wide path; false (nothing taken) when the context's workspace has no room for it
+// workspace of the wide path for `sets` candidate sets; false (nothing taken) when the context's workspace has no room for it
 struct WideBufs {
-    unsigned long long* skeys;
-    rot::RBox* R;
-    unsigned long long* mask;
-    int* m;
-    unsigned* pairs;
+    unsigned long long* skeys;     // [sets][PRE_CAP]
+    rot::RBox* R;                  // [sets][PRE_CAP]
+    unsigned long long* mask;      // [sets][mask_stride]
+    size_t mask_stride;
+    int* m;                        // [sets][WIDE_M]
+    unsigned* pairs;               // [sets][pair_cap]
     int pair_cap;
 };
-static int wide_pair_cap(int m_max) {   // every pair of a small set; 2 M pairs (8 MB) beyond that, the tiles take the overflow
-    const long long all = (long long)m_max * (m_max - 1) / 2;
-    return (int)(all < (2ll << 20) ? (all > 0 ? all : 1) : (2ll << 20));
+static int wide_pair_cap(int m_max, int sets) {   // every pair of a small set; 2 M pairs (8 MB) beyond that (512 K per set in a batch), the tiles take the overflow
+    const long long all = (long long)m_max * (m_max - 1) / 2, cap = sets > 1 ? (512ll << 10) : (2ll << 20);
+    return (int)(all < cap ? (all > 0 ? all : 1) : cap);
 }
-static size_t wide_bytes(int m_max) {
-    return (size_t)PRE_CAP * (8 + sizeof(rot::RBox)) + (size_t)m_max * MW * 8 + (size_t)wide_pair_cap(m_max) * 4 + 5 * 256 + 256;
+static size_t wide_bytes(int m_max, int sets) {
+    return (size_t)sets * ((size_t)PRE_CAP * (8 + sizeof(rot::RBox)) + (size_t)m_max * MW * 8 + (size_t)wide_pair_cap(m_max, sets) * 4 + WIDE_M * 4) + 6 * 256;
 }
-static bool wide_bufs(tcb_ctx* ctx, int m_max, WideBufs& wb) {
-    if (((ctx->ws_used + 255) & ~(size_t)255) + wide_bytes(m_max) > ctx->ws_bytes) return false;
-    wb.skeys = (unsigned long long*)tcb_ws_alloc(ctx, (size_t)PRE_CAP * 8);
-    wb.R = (rot::RBox*)tcb_ws_alloc(ctx, (size_t)PRE_CAP * sizeof(rot::RBox));
-    wb.mask = (unsigned long long*)tcb_ws_alloc(ctx, (size_t)m_max * MW * 8);
-    wb.m = (int*)tcb_ws_alloc(ctx, 256);
-    wb.pair_cap = wide_pair_cap(m_max);
-    wb.pairs = (unsigned*)tcb_ws_alloc(ctx, (size_t)wb.pair_cap * 4);
+static bool wide_bufs(tcb_ctx* ctx, int m_max, int sets, WideBufs& wb) {
+    if (((ctx->ws_used + 255) & ~(size_t)255) + wide_bytes(m_max, sets) > ctx->ws_bytes) return false;
+    wb.skeys = (unsigned long long*)tcb_ws_alloc(ctx, (size_t)sets * PRE_CAP * 8);
+    wb.R = (rot::RBox*)tcb_ws_alloc(ctx, (size_t)sets * PRE_CAP * sizeof(rot::RBox));
+    wb.mask_stride = (size_t)m_max * MW;
+    wb.mask = (unsigned long long*)tcb_ws_alloc(ctx, (size_t)sets * wb.mask_stride * 8);
+    wb.m = (int*)tcb_ws_alloc(ctx, (size_t)sets * WIDE_M * 4);
+    wb.pair_cap = wide_pair_cap(m_max, sets);
+    wb.pairs = (unsigned*)tcb_ws_alloc(ctx, (size_t)sets * wb.pair_cap * 4);
     return wb.skeys && wb.R && wb.mask && wb.m && wb.pairs;
 }
+// mask (tiles + listed pairs) of `sets` ordered candidate sets already in wb.R / wb.m
+static int wide_mask(tcb_ctx* ctx, const WideBufs& wb, int m_max, int sets, float thresh, cudaStream_t st) {
+    const int nb = tcb_div_up(m_max, 64);
+    TCB_KLAUNCH(ctx, rot_mask_kernel, dim3(nb, nb, sets), MASK_T, 0, st, wb.R, wb.m, thresh, wb.mask, wb.mask_stride, wb.pairs, wb.pair_cap);
+    TCB_LAUNCHED(ctx);
+    const int per = sets > 1 ? tcb_div_up(ctx->num_sms * 8, sets) : ctx->num_sms * 8;
+    TCB_KLAUNCH(ctx, rot_pairs_kernel, dim3(per, sets), 256, 0, st, wb.R, wb.m, thresh, wb.pairs, wb.pair_cap, wb.mask, wb.mask_stride);
+    TCB_LAUNCHED(ctx);
+    return TCB_OK;
+}
 
-extern "C" int tcb_rotated_nms(tcb_ctx* ctx, const float* boxes_dev, const float* scores_dev, int n, float thresh, int pre_max,
+extern "C" int tcb_rotated_nms(tcb_ctx* ctx, const float* boxes_dev, const float* scores_dev, int b, int n, float thresh, int pre_max,
                                int post_max, int* keep_dev, int* count_dev, void* stream) {
     TCB_CHECK_CTX(ctx);
-    TCB_REQUIRE(ctx, n >= 0 && keep_dev && count_dev && (n == 0 || (boxes_dev && scores_dev)), "tcb_rotated_nms: bad arguments");
+    TCB_REQUIRE(ctx, b >= 1 && n >= 0 && keep_dev && count_dev && (n == 0 || (boxes_dev && scores_dev)), "tcb_rotated_nms: bad arguments");
+    if (b > 65535) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_rotated_nms: more than 65535 box sets");
     int rc = check_nms_limits(ctx, "tcb_rotated_nms", thresh, pre_max, post_max);
     if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     WideBufs wb;
     const int m_max = n < pre_max ? n : pre_max;
-    if (m_max > WIDE_MIN && wide_bufs(ctx, m_max, wb)) {
+    if (m_max > WIDE_MIN && wide_bufs(ctx, m_max, b, wb)) {
         TCB_CUDA(ctx, cudaFuncSetAttribute(rot_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ORDER_CACHE * 8));
-        TCB_KLAUNCH(ctx, rot_order_kernel, 1, T, ORDER_CACHE * 8, st, scores_dev, n, pre_max, wb.skeys, wb.m);
+        TCB_KLAUNCH(ctx, rot_order_kernel, b, T, ORDER_CACHE * 8, st, scores_dev, n, pre_max, wb.skeys, wb.m);
         TCB_LAUNCHED(ctx);
-        TCB_KLAUNCH(ctx, rot_rbox_kernel, tcb_div_up(m_max, 256), 256, 0, st, boxes_dev, wb.skeys, wb.m, wb.R);
+        TCB_KLAUNCH(ctx, rot_rbox_kernel, dim3(tcb_div_up(m_max, 256), b), 256, 0, st, boxes_dev, n, wb.skeys, wb.m, wb.R);
         TCB_LAUNCHED(ctx);
-        const int nb = tcb_div_up(m_max, 64);
-        TCB_KLAUNCH(ctx, rot_mask_kernel, dim3(nb, nb), MASK_T, 0, st, wb.R, wb.m, thresh, wb.mask, wb.pairs, wb.pair_cap);
-        TCB_LAUNCHED(ctx);
-        TCB_KLAUNCH(ctx, rot_pairs_kernel, ctx->num_sms * 8, 256, 0, st, wb.R, wb.m, thresh, wb.pairs, wb.pair_cap, wb.mask);
-        TCB_LAUNCHED(ctx);
+        if ((rc = wide_mask(ctx, wb, m_max, b, thresh, st))) return rc;
         TCB_CUDA(ctx, cudaFuncSetAttribute(rot_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SweepShared)));
-        TCB_KLAUNCH(ctx, rot_sweep_kernel, 1, SWEEP_T, sizeof(SweepShared), st, wb.mask, wb.skeys, wb.m, post_max, keep_dev, count_dev);
+        TCB_KLAUNCH(ctx, rot_sweep_kernel, b, SWEEP_T, sizeof(SweepShared), st, wb.mask, wb.mask_stride, wb.skeys, wb.m, post_max, keep_dev, count_dev);
         TCB_LAUNCHED(ctx);
         return TCB_OK;
     }
     if ((rc = opt_in_smem(ctx, rotated_nms_kernel))) return rc;
-    TCB_KLAUNCH(ctx, rotated_nms_kernel, 1, T, sizeof(FrameShared), st, boxes_dev, scores_dev, n, thresh, pre_max, post_max, keep_dev, count_dev);
+    TCB_KLAUNCH(ctx, rotated_nms_kernel, b, T, sizeof(FrameShared), st, boxes_dev, scores_dev, n, thresh, pre_max, post_max, keep_dev, count_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }
 
-extern "C" size_t tcb_pp_anchor_post_workspace(int h, int w, int num_class, int num_rot) {
-    const size_t n = (size_t)h * w * num_class * num_rot;
-    return n * 8 + (size_t)PRE_CAP * 7 * 4 + 4096 + wide_bytes(PRE_CAP);
+extern "C" size_t tcb_pp_anchor_post_workspace(int b, int h, int w, int num_class, int num_rot) {
+    const size_t n = (size_t)h * w * num_class * num_rot, bb = (size_t)(b > 0 ? b : 1);
+    return bb * (n * 8 + (size_t)PRE_CAP * 7 * 4 + 512) + 4096 + wide_bytes(PRE_CAP, (int)bb);
 }
 
-extern "C" int tcb_pp_anchor_post(tcb_ctx* ctx, const float* cls_dev, const float* box_dev, const float* dir_dev, int h, int w,
+extern "C" int tcb_pp_anchor_post(tcb_ctx* ctx, const float* cls_dev, const float* box_dev, const float* dir_dev, int b, int h, int w,
                                   int num_class, int num_rot, const float anchor_range[6], const float* anchor_sizes,
                                   const float* anchor_bottoms, const float* anchor_rotations, float dir_offset,
                                   float dir_limit_offset, int num_dir_bins, float score_thresh, float nms_thresh, int pre_max,
@@ -625,7 +686,8 @@ extern "C" int tcb_pp_anchor_post(tcb_ctx* ctx, const float* cls_dev, const floa
     TCB_CHECK_CTX(ctx);
     TCB_REQUIRE(ctx, cls_dev && box_dev && anchor_range && anchor_sizes && anchor_bottoms && anchor_rotations &&
                      out_boxes_dev && out_scores_dev && out_labels_dev && out_count_dev, "tcb_pp_anchor_post: null argument");
-    TCB_REQUIRE(ctx, h >= 2 && w >= 2, "tcb_pp_anchor_post: feature map must be at least 2x2");
+    TCB_REQUIRE(ctx, b >= 1 && h >= 2 && w >= 2, "tcb_pp_anchor_post: need b >= 1 and a feature map of at least 2x2");
+    if (b > 65535) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_pp_anchor_post: more than 65535 frames");
     if (num_class < 1 || num_class > PP_MAX_CLASSES || num_rot < 1 || num_rot > PP_MAX_ROT)
         return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_pp_anchor_post: num_class %d (<= %d) / num_rot %d (<= %d)", num_class, PP_MAX_CLASSES, num_rot, PP_MAX_ROT);
     TCB_REQUIRE(ctx, dir_dev == nullptr || num_dir_bins >= 1, "tcb_pp_anchor_post: num_dir_bins must be >= 1");
@@ -637,7 +699,7 @@ extern "C" int tcb_pp_anchor_post(tcb_ctx* ctx, const float* cls_dev, const floa
 
     PPParams p;
     memset(&p, 0, sizeof(p));
-    p.H = h; p.W = w; p.num_class = num_class; p.num_rot = num_rot; p.num_dir_bins = num_dir_bins;
+    p.H = h; p.W = w; p.num_class = num_class; p.num_rot = num_rot; p.num_dir_bins = num_dir_bins; p.n_anchors = (int)n_anchors;
     // anchor_generator.py:28-31: float32 range difference divided by a numpy int64 grid size -> float64 stride
     p.x0 = anchor_range[0]; p.y0 = anchor_range[1];
     p.x_stride = (double)(anchor_range[3] - anchor_range[0]) / (double)(w - 1);
@@ -651,43 +713,42 @@ extern "C" int tcb_pp_anchor_post(tcb_ctx* ctx, const float* cls_dev, const floa
     p.period = (float)(2.0 * 3.141592653589793 / (double)(num_dir_bins > 0 ? num_dir_bins : 1));
     p.score_thresh = score_thresh; p.nms_thresh = nms_thresh; p.pre_max = pre_max; p.post_max = post_max;
 
-    TCB_WS(ctx, cand_count, int, 64);
-    TCB_WS(ctx, cand, unsigned long long, n_anchors);
-    TCB_WS(ctx, sorted_boxes, float, (size_t)PRE_CAP * 7);
-    TCB_CUDA(ctx, cudaMemsetAsync(cand_count, 0, sizeof(int), st));
-    TCB_KLAUNCH(ctx, pp_candidates_kernel, tcb_div_up(n_anchors, 256), 256, 0, st, cls_dev, (int)n_anchors, num_class, score_thresh, cand, cand_count);
+    TCB_WS(ctx, cand_count, int, b + 64);
+    TCB_WS(ctx, cand, unsigned long long, (size_t)b * n_anchors);
+    TCB_WS(ctx, sorted_boxes, float, (size_t)b * PRE_CAP * 7);
+    TCB_CUDA(ctx, cudaMemsetAsync(cand_count, 0, sizeof(int) * b, st));
+    const size_t tile_bytes = (size_t)PPC_TILE * num_class * sizeof(float);
+    const bool vec4 = (((uintptr_t)cls_dev) & 15) == 0 && ((n_anchors * num_class) & 3) == 0;   // every frame and tile starts on a 16-byte boundary
+    if (vec4) TCB_KLAUNCH(ctx, pp_candidates_kernel<true>, dim3(tcb_div_up(n_anchors, PPC_TILE), b), 256, tile_bytes, st, cls_dev, (int)n_anchors, num_class, score_thresh, cand, cand_count);
+    else      TCB_KLAUNCH(ctx, pp_candidates_kernel<false>, dim3(tcb_div_up(n_anchors, PPC_TILE), b), 256, tile_bytes, st, cls_dev, (int)n_anchors, num_class, score_thresh, cand, cand_count);
     TCB_LAUNCHED(ctx);
     WideBufs wb;
     const int m_max = (int)(n_anchors < pre_max ? n_anchors : pre_max);
-    if (m_max > WIDE_MIN && wide_bufs(ctx, m_max, wb)) {
+    if (m_max > WIDE_MIN && wide_bufs(ctx, m_max, b, wb)) {
         TCB_CUDA(ctx, cudaFuncSetAttribute(pp_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ORDER_CACHE * 8));
-        TCB_KLAUNCH(ctx, pp_order_kernel, 1, T, ORDER_CACHE * 8, st, p, cand, cand_count, (int)n_anchors, wb.skeys, wb.m);
+        TCB_KLAUNCH(ctx, pp_order_kernel, b, T, ORDER_CACHE * 8, st, p, cand, cand_count, (int)n_anchors, wb.skeys, wb.m);
         TCB_LAUNCHED(ctx);
-        TCB_KLAUNCH(ctx, pp_decode_kernel, tcb_div_up(m_max, 256), 256, 0, st, p, box_dev, dir_dev, wb.skeys, wb.m, sorted_boxes, wb.R);
+        TCB_KLAUNCH(ctx, pp_decode_kernel, dim3(tcb_div_up(m_max, 256), b), 256, 0, st, p, box_dev, dir_dev, wb.skeys, wb.m, sorted_boxes, wb.R);
         TCB_LAUNCHED(ctx);
-        const int nb = tcb_div_up(m_max, 64);
-        TCB_KLAUNCH(ctx, rot_mask_kernel, dim3(nb, nb), MASK_T, 0, st, wb.R, wb.m, nms_thresh, wb.mask, wb.pairs, wb.pair_cap);
-        TCB_LAUNCHED(ctx);
-        TCB_KLAUNCH(ctx, rot_pairs_kernel, ctx->num_sms * 8, 256, 0, st, wb.R, wb.m, nms_thresh, wb.pairs, wb.pair_cap, wb.mask);
-        TCB_LAUNCHED(ctx);
+        if ((rc = wide_mask(ctx, wb, m_max, b, nms_thresh, st))) return rc;
         TCB_CUDA(ctx, cudaFuncSetAttribute(pp_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SweepShared)));
-        TCB_KLAUNCH(ctx, pp_finish_kernel, 1, SWEEP_T, sizeof(SweepShared), st, p, cls_dev, wb.mask, wb.skeys, wb.m, sorted_boxes, out_boxes_dev, out_scores_dev,
+        TCB_KLAUNCH(ctx, pp_finish_kernel, b, SWEEP_T, sizeof(SweepShared), st, p, cls_dev, wb.mask, wb.mask_stride, wb.skeys, wb.m, sorted_boxes, out_boxes_dev, out_scores_dev,
                                                              out_labels_dev, out_count_dev);
         TCB_LAUNCHED(ctx);
         return TCB_OK;
     }
     if ((rc = opt_in_smem(ctx, pp_post_kernel))) return rc;
-    TCB_KLAUNCH(ctx, pp_post_kernel, 1, T, sizeof(FrameShared), st, p, cls_dev, box_dev, dir_dev, cand, cand_count, (int)n_anchors, sorted_boxes,
+    TCB_KLAUNCH(ctx, pp_post_kernel, b, T, sizeof(FrameShared), st, p, cls_dev, box_dev, dir_dev, cand, cand_count, (int)n_anchors, sorted_boxes,
                                                        out_boxes_dev, out_scores_dev, out_labels_dev, out_count_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }
 
-extern "C" size_t tcb_centerpoint_post_workspace(int num_heads, int pre_max, int post_max) {
-    return (size_t)num_heads * (size_t)(pre_max + post_max) * (9 * 4 + 4 + 4) + 4096;
+extern "C" size_t tcb_centerpoint_post_workspace(int b, int num_heads, int pre_max, int post_max) {
+    return (size_t)(b > 0 ? b : 1) * ((size_t)num_heads * (size_t)(pre_max + post_max) * (9 * 4 + 4 + 4) + 256) + 4096;
 }
 
-extern "C" int tcb_centerpoint_post(tcb_ctx* ctx, int num_heads, const float* const* hm_dev, const float* const* center_dev,
+extern "C" int tcb_centerpoint_post(tcb_ctx* ctx, int b, int num_heads, const float* const* hm_dev, const float* const* center_dev,
                                     const float* const* center_z_dev, const float* const* dim_dev, const float* const* rot_dev,
                                     const float* const* vel_dev, const int* head_num_class, const int* class_id_map, int h, int w,
                                     int feature_map_stride, const float voxel_size_xy[2], const float range_min_xy[2],
@@ -699,7 +760,7 @@ extern "C" int tcb_centerpoint_post(tcb_ctx* ctx, int num_heads, const float* co
                      range_min_xy && limit_range && out_boxes_dev && out_scores_dev && out_labels_dev && out_count_dev,
                 "tcb_centerpoint_post: null argument");
     if (num_heads < 1 || num_heads > CP_MAX_HEADS) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_centerpoint_post: %d heads (limit %d)", num_heads, CP_MAX_HEADS);
-    TCB_REQUIRE(ctx, h >= 1 && w >= 1 && k >= 1, "tcb_centerpoint_post: bad shape");
+    TCB_REQUIRE(ctx, b >= 1 && b <= 65535 && h >= 1 && w >= 1 && k >= 1, "tcb_centerpoint_post: bad shape");
     if (k > PRE_CAP) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_centerpoint_post: K %d > %d", k, PRE_CAP);
     int rc = check_nms_limits(ctx, "tcb_centerpoint_post", nms_thresh, pre_max, post_max);
     if (rc) return rc;
@@ -723,16 +784,16 @@ extern "C" int tcb_centerpoint_post(tcb_ctx* ctx, int num_heads, const float* co
     for (int j = 0; j < 6; j++) p.limit[j] = limit_range[j];
     p.score_thresh = score_thresh; p.nms_thresh = nms_thresh; p.pre_max = pre_max; p.post_max = post_max;
 
-    const size_t rows = (size_t)num_heads * (size_t)(pre_max + post_max);
-    TCB_WS(ctx, head_count, int, 64);
+    const size_t rows = (size_t)b * num_heads * (size_t)(pre_max + post_max);
+    TCB_WS(ctx, head_count, int, (size_t)b * CP_MAX_HEADS + 64);
     TCB_WS(ctx, head_boxes, float, rows * 9);
     TCB_WS(ctx, head_scores, float, rows);
     TCB_WS(ctx, head_labels, int, rows);
     if ((rc = opt_in_smem(ctx, cp_head_kernel))) return rc;
-    TCB_KLAUNCH(ctx, cp_head_kernel, num_heads, T, sizeof(FrameShared), st, p, head_boxes, head_scores, head_labels, head_count);
+    TCB_KLAUNCH(ctx, cp_head_kernel, dim3(num_heads, b), T, sizeof(FrameShared), st, p, head_boxes, head_scores, head_labels, head_count);
     TCB_LAUNCHED(ctx);
-    TCB_KLAUNCH(ctx, cp_concat_kernel, 1, 256, 0, st, num_heads, post_max, head_boxes, head_scores, head_labels, head_count, out_boxes_dev,
-                                        out_scores_dev, out_labels_dev, out_count_dev);
+    TCB_KLAUNCH(ctx, cp_concat_kernel, b, 256, 0, st, num_heads, post_max, head_boxes, head_scores, head_labels, head_count, out_boxes_dev,
+                                        out_scores_dev, out_labels_dev, out_count_dev, pre_max);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }

@@ -151,11 +151,15 @@ class Engine:
 
     def detectron_post(self, logits, deltas, strides, cell_anchors, image_hw, ctrness=None, score_thresh=0.05, topk=1000,
                        nms_thresh=0.5, max_det=100):
-        """RetinaNet (ctrness None) / FCOS dense-detector inference for one image. logits[l]: CUDA f32 [A*K,H,W],
-        deltas[l]: [A*4,H,W], cell_anchors[l]: A rows (x0,y0,x1,y1). Returns (boxes [max_det,4], scores, classes, count)."""
+        """RetinaNet (ctrness None) / FCOS dense-detector inference. logits[l]: CUDA f32 [A*K,H,W], deltas[l]: [A*4,H,W]
+        (one image) or [B,A*K,H,W] / [B,A*4,H,W] (a batch), cell_anchors[l]: A rows (x0,y0,x1,y1).
+        Returns (boxes [max_det,4], scores, classes, count [1]), with a leading B on each for a batch (count [B])."""
         nl = len(logits)
         a = len(cell_anchors[0])
-        k = logits[0].shape[0] // a
+        batched = logits[0].dim() == 4
+        b = logits[0].shape[0] if batched else 1
+        lead = (b,) if batched else ()
+        k = logits[0].shape[-3] // a
         keep = [t.contiguous() for t in list(logits) + list(deltas) + (list(ctrness) if ctrness is not None else [])]
 
         def arr(ts):
@@ -170,11 +174,11 @@ class Engine:
         ss = (c_int * nl)(*[int(v) for v in strides])
         flat = [float(v) for lv in cell_anchors for row in lv for v in row]
         ca = (c_float * len(flat))(*flat)
-        ob = torch.zeros((max_det, 4), dtype=torch.float32, device=dev)
-        osc = torch.zeros((max_det,), dtype=torch.float32, device=dev)
-        oc = torch.zeros((max_det,), dtype=torch.int64, device=dev)
-        cnt = torch.zeros((1,), dtype=torch.int32, device=dev)
-        self.ctx.call("tcb_detectron_post", nl, arr(keep[:nl]), arr(keep[nl:2 * nl]), arr(keep[2 * nl:]) if ctrness is not None else None,
+        ob = torch.zeros(lead + (max_det, 4), dtype=torch.float32, device=dev)
+        osc = torch.zeros(lead + (max_det,), dtype=torch.float32, device=dev)
+        oc = torch.zeros(lead + (max_det,), dtype=torch.int64, device=dev)
+        cnt = torch.zeros((b,), dtype=torch.int32, device=dev)
+        self.ctx.call("tcb_detectron_post", b, nl, arr(keep[:nl]), arr(keep[nl:2 * nl]), arr(keep[2 * nl:]) if ctrness is not None else None,
                       hs, ws, ss, a, k, ca, 0 if ctrness is None else 1, float(score_thresh), int(topk), float(nms_thresh), int(max_det),
                       int(image_hw[0]), int(image_hw[1]), _ptr(ob), _ptr(osc), _ptr(oc), _ptr(cnt), _lib.stream_ptr())
         return ob, osc, oc, cnt
@@ -246,35 +250,42 @@ class Engine:
         return out
 
     def rotated_nms(self, boxes, scores, thresh, pre_max=4096, post_max=500):
-        """topk(pre_max) + nms_gpu + [:post_max]. Returns (keep int32 [post_max] indices into the input, count [1])."""
+        """topk(pre_max) + nms_gpu + [:post_max]. boxes (n,7) + scores (n,) -> (keep int32 [post_max] indices into the
+        input, count [1]); a batch boxes (b,n,7) + scores (b,n) -> (keep [b,post_max], count [b])."""
         _need_cuda(boxes, scores)
-        b, s = boxes.contiguous().float(), scores.contiguous().float()
-        keep = torch.empty((post_max,), dtype=torch.int32, device=b.device)
-        cnt = torch.zeros((1,), dtype=torch.int32, device=b.device)
-        self.ctx.call("tcb_rotated_nms", _ptr(b), _ptr(s), b.shape[0], float(thresh), int(pre_max), int(post_max), _ptr(keep), _ptr(cnt),
+        bx, s = boxes.contiguous().float(), scores.contiguous().float()
+        batched = bx.dim() == 3
+        b, n = (bx.shape[0], bx.shape[1]) if batched else (1, bx.shape[0])
+        keep = torch.empty((b, post_max) if batched else (post_max,), dtype=torch.int32, device=bx.device)
+        cnt = torch.zeros((b,), dtype=torch.int32, device=bx.device)
+        self.ctx.call("tcb_rotated_nms", _ptr(bx), _ptr(s), b, n, float(thresh), int(pre_max), int(post_max), _ptr(keep), _ptr(cnt),
                       _lib.stream_ptr())
         return keep, cnt
 
     def pp_anchor_post(self, cls_preds, box_preds, dir_preds, anchor_range, anchor_sizes, anchor_bottoms, anchor_rotations,
                        dir_offset=0.78539, dir_limit_offset=0.0, num_dir_bins=2, score_thresh=0.1, nms_thresh=0.01,
                        pre_max=4096, post_max=500):
-        """One frame of PointPillars head outputs: cls (H,W,A*nc), box (H,W,A*7), dir (H,W,A*bins) or None.
-        Returns device tensors (boxes [post_max,7], scores [post_max], labels int64 [post_max], count [1])."""
+        """PointPillars head outputs of one frame — cls (H,W,A*nc), box (H,W,A*7), dir (H,W,A*bins) or None — or of a
+        batch (B,H,W,...). Returns device tensors (boxes [post_max,7], scores [post_max], labels int64 [post_max],
+        count [1]), with a leading B on each for a batch (count [B])."""
         _need_cuda(cls_preds, box_preds)
+        batched = cls_preds.dim() == 4
+        b = cls_preds.shape[0] if batched else 1
+        lead = (b,) if batched else ()
         h, w = cls_preds.shape[-3], cls_preds.shape[-2]
         nc = len(anchor_sizes)
         nrot = len(anchor_rotations[0])
         dev = cls_preds.device
-        ob = torch.zeros((post_max, 7), dtype=torch.float32, device=dev)
-        osc = torch.zeros((post_max,), dtype=torch.float32, device=dev)
-        ol = torch.zeros((post_max,), dtype=torch.int64, device=dev)
-        cnt = torch.zeros((1,), dtype=torch.int32, device=dev)
+        ob = torch.zeros(lead + (post_max, 7), dtype=torch.float32, device=dev)
+        osc = torch.zeros(lead + (post_max,), dtype=torch.float32, device=dev)
+        ol = torch.zeros(lead + (post_max,), dtype=torch.int64, device=dev)
+        cnt = torch.zeros((b,), dtype=torch.int32, device=dev)
         rng = (c_float * 6)(*[float(np.float32(v)) for v in anchor_range])
         sizes = (c_float * (nc * 3))(*[float(v) for s in anchor_sizes for v in s])
         bots = (c_float * nc)(*[float(v) for v in anchor_bottoms])
         rots = (c_float * (nc * nrot))(*[float(v) for r in anchor_rotations for v in r])
         self.ctx.call("tcb_pp_anchor_post", _ptr(cls_preds.contiguous()), _ptr(box_preds.contiguous()),
-                      _ptr(dir_preds.contiguous()) if dir_preds is not None else None, h, w, nc, nrot, rng, sizes, bots, rots,
+                      _ptr(dir_preds.contiguous()) if dir_preds is not None else None, b, h, w, nc, nrot, rng, sizes, bots, rots,
                       float(dir_offset), float(dir_limit_offset), int(num_dir_bins), float(score_thresh), float(nms_thresh),
                       int(pre_max), int(post_max), _ptr(ob), _ptr(osc), _ptr(ol), _ptr(cnt), _lib.stream_ptr())
         return ob, osc, ol, cnt
@@ -282,8 +293,9 @@ class Engine:
     def centerpoint_post(self, heads, class_id_map, feature_map_stride, voxel_size, point_range, limit_range, k=500,
                          score_thresh=0.1, nms_thresh=0.2, pre_max=1000, post_max=83):
         """heads: list of dicts with CUDA f32 tensors hm [c,H,W], center [2,H,W], center_z [1,H,W], dim [3,H,W],
-        rot [2,H,W], optional vel [2,H,W]; class_id_map: list (per head) of global 0-based class ids.
-        Returns (boxes [heads*post_max,9], scores, labels int64 1-based, count [1])."""
+        rot [2,H,W], optional vel [2,H,W] — or each with a leading batch dimension [B,...]; class_id_map: list (per head)
+        of global 0-based class ids. Returns (boxes [heads*post_max,9], scores, labels int64 1-based, count [1]), with a
+        leading B on each for a batch (count [B])."""
         nh = len(heads)
         keep_alive = []
 
@@ -303,17 +315,20 @@ class Engine:
 
         hm = heads[0]["hm"]
         _need_cuda(hm)
+        batched = hm.dim() == 4
+        b = hm.shape[0] if batched else 1
+        lead = (b,) if batched else ()
         h, w = hm.shape[-2], hm.shape[-1]
         dev = hm.device
         ncls = (c_int * nh)(*[int(hd["hm"].shape[-3]) for hd in heads])
         cmap = [int(v) for m in class_id_map for v in m]
         cmap_arr = (c_int * len(cmap))(*cmap)
-        ob = torch.zeros((nh * post_max, 9), dtype=torch.float32, device=dev)
-        osc = torch.zeros((nh * post_max,), dtype=torch.float32, device=dev)
-        ol = torch.zeros((nh * post_max,), dtype=torch.int64, device=dev)
-        cnt = torch.zeros((1,), dtype=torch.int32, device=dev)
+        ob = torch.zeros(lead + (nh * post_max, 9), dtype=torch.float32, device=dev)
+        osc = torch.zeros(lead + (nh * post_max,), dtype=torch.float32, device=dev)
+        ol = torch.zeros(lead + (nh * post_max,), dtype=torch.int64, device=dev)
+        cnt = torch.zeros((b,), dtype=torch.int32, device=dev)
         has_vel = all(hd.get("vel") is not None for hd in heads)
-        self.ctx.call("tcb_centerpoint_post", nh, ptrs("hm"), ptrs("center"), ptrs("center_z"), ptrs("dim"), ptrs("rot"),
+        self.ctx.call("tcb_centerpoint_post", b, nh, ptrs("hm"), ptrs("center"), ptrs("center_z"), ptrs("dim"), ptrs("rot"),
                       ptrs("vel", True) if has_vel else None, ncls, cmap_arr, h, w, int(feature_map_stride),
                       (c_float * 2)(float(voxel_size[0]), float(voxel_size[1])), (c_float * 2)(float(point_range[0]), float(point_range[1])),
                       (c_float * 6)(*[float(v) for v in limit_range]), int(k), float(score_thresh), float(nms_thresh),
