@@ -41,73 +41,151 @@ __device__ __forceinline__ Level level_of(const DetParams& p, int l, int img, in
     return L;
 }
 
-// Candidates of every level in one launch: grid = (spatial chunks of 4096, channels A*K, levels), four 16-byte loads
-// per thread when the plane allows. HBM-bound: a logit below logit_floor cannot pass the
-// score threshold (logit_floor sits 0.01 below the threshold's logit, far more than expf's error), so the sigmoid is
-// only evaluated for the few that might; those are kept iff sigmoid > thresh exactly as before.
-constexpr int DC_Q = 4;                                   // 16-byte loads per thread
-constexpr int DC_SPAN = 256 * 4 * DC_Q;                   // logits per CTA
-__global__ void __launch_bounds__(256) det_candidates_kernel(const DetParams p, float logit_floor) {
+// Candidates of every level in one launch. A level's logits of one image are A*K*H*W contiguous floats; they are cut into
+// spans of DC_SPAN floats (planes are not respected: channel and location are recovered per candidate) and the spans of
+// all images and levels form one work list that the warps of a persistent grid walk, every warp on its own: it keeps the
+// 16-byte asynchronous copies (cp.async) of its NEXT span in flight while it works on the current one, every lane reading
+// back only what it copied itself, so nothing in the stream waits for a barrier. HBM-bound: a logit below logit_floor
+// cannot pass the score threshold (logit_floor sits 0.01 below the threshold's logit, far more than expf's error), so the
+// stream is only compared against it; the few per cent that might pass are listed in the warp's shared memory (one scan
+// of per-lane counts, no per-element vote) and the sigmoid, the exact `> thresh` test and the key are then computed over
+// the list with the lanes packed. Keys collect in a per-warp pending list that is flushed with ONE reservation on the
+// (image, level) counter when it fills or the warp moves on to another image or level.
+constexpr int DC_Q = 4;                                   // 16-byte copies per lane and span
+constexpr int DC_SPAN = 32 * 4 * DC_Q;                    // logits per span (one warp)
+constexpr int DC_WARPS = 8;
+constexpr int DC_PEND = 128;                              // pending keys per warp
+constexpr int DC_NBUF = 2;                                // span buffers per warp: one copy in flight behind the span being filtered (three buffers and
+                                                          // fewer resident warps measured slower: 362 vs 311 us for 16 RetinaNet images)
+struct DetSpans { int first[MAX_LEVELS + 1]; int per_image[MAX_LEVELS]; };   // span list: level-major, then image, then span
+struct DcWarp {                                           // a warp's slice of shared memory
+    float buf[DC_NBUF][DC_SPAN];
+    unsigned long long pend[DC_PEND];
+    unsigned short l_pos[DC_SPAN];
+};
+
+__device__ __forceinline__ void dc_copy16(float* dst_smem, const float* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
+}
+
+__global__ void __launch_bounds__(32 * DC_WARPS) det_candidates_kernel(const DetParams p, const DetSpans W, float logit_floor) {
+    extern __shared__ __align__(16) unsigned char dc_raw[];
     pdl_wait();
-    int* cand_count;
-    const Level L = level_of(p, blockIdx.z % p.num_levels, blockIdx.z / p.num_levels, cand_count);   // z = (image, level)
-    const int HW = L.H * L.W;
-    if ((int)blockIdx.x * DC_SPAN >= HW) return;  // (whole CTA)
-    __shared__ int s_count, s_base;
-    if (threadIdx.x == 0) s_count = 0;
-    __syncthreads();
-    const int ch = blockIdx.y;
-    const int a = ch / p.K, k = ch - a * p.K;
-    const float* plane = L.logits + (long long)ch * HW;
-    float x[DC_Q][4];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    DcWarp& S = reinterpret_cast<DcWarp*>(dc_raw)[warp];
+    const int total_items = W.first[p.num_levels];
+    const int nworkers = gridDim.x * DC_WARPS;
+    const unsigned lt = (1u << lane) - 1u;
+
+    struct Item { const float* src; int n; int level, img; int flat0; };
+    auto item_of = [&](int it) {
+        int l = 0;
+        while (it >= W.first[l + 1]) l++;
+        const int r = it - W.first[l], img = r / W.per_image[l], sp = r - img * W.per_image[l];
+        const int n_img = p.A * p.K * p.lv[l].H * p.lv[l].W;     // < 2^30 (checked on the host)
+        Item q;
+        q.level = l; q.img = img; q.flat0 = sp * DC_SPAN;
+        q.src = p.lv[l].logits + (long long)img * n_img + q.flat0;
+        q.n = min(DC_SPAN, n_img - q.flat0);
+        return q;
+    };
+    // lane t copies the DC_Q groups of 4 floats at (g * 32 + t) * 4: whole 16-byte groups inside the span asynchronously, a
+    // ragged or unaligned group with plain loads
+    auto issue = [&](const Item& q, float* dst) {
 #pragma unroll
-    for (int q = 0; q < DC_Q; q++) {              // all loads first
-        const int sp0 = blockIdx.x * DC_SPAN + (q * 256 + threadIdx.x) * 4;
-        const float* src = plane + sp0;
-        if (sp0 + 3 < HW && (((uintptr_t)src) & 15) == 0) {
-            const float4 v = __ldg(reinterpret_cast<const float4*>(src));
-            x[q][0] = v.x; x[q][1] = v.y; x[q][2] = v.z; x[q][3] = v.w;
+        for (int g = 0; g < DC_Q; g++) {
+            const int e = (g * 32 + lane) * 4;
+            if (e + 3 < q.n && ((((uintptr_t)(q.src + e)) & 15) == 0)) dc_copy16(dst + e, q.src + e);
+            else {
+#pragma unroll
+                for (int j = 0; j < 4; j++) dst[e + j] = e + j < q.n ? __ldg(q.src + e + j) : -INFINITY;
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    int pend_n = 0, pend_img = -1, pend_level = -1;
+    auto flush = [&]() {                                   // whole warp
+        if (pend_n == 0) return;
+        const Level& L = p.lv[pend_level];
+        int base = 0;
+        if (lane == 0) base = atomicAdd(p.counts + pend_img * MAX_LEVELS + pend_level, pend_n);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        unsigned long long* dst = L.cand + (long long)pend_img * p.A * p.K * L.H * L.W + base;
+        for (int i = lane; i < pend_n; i += 32) dst[i] = S.pend[i];
+        __syncwarp();
+        pend_n = 0;
+    };
+
+    int it = blockIdx.x * DC_WARPS + warp, stage = 0;
+    if (it >= total_items) return;
+    Item cur = item_of(it);
+    issue(cur, S.buf[0]);
+    for (; it < total_items; it += nworkers, stage ^= 1) {
+        const int nxt = it + nworkers;
+        Item next = cur;
+        if (nxt < total_items) {
+            next = item_of(nxt);
+            issue(next, S.buf[stage ^ 1]);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");     // this span's copies: all but the group just committed
         } else {
-#pragma unroll
-            for (int j = 0; j < 4; j++) x[q][j] = sp0 + j < HW ? __ldg(src + j) : -INFINITY;
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
-    }
-    // slots: one shared-memory reservation per warp and element column, one global reservation per CTA (a dense head
-    // would otherwise serialise hundreds of thousands of atomics on the level's counter)
-    const int lane = threadIdx.x & 31;
-    unsigned long long key[DC_Q * 4];
-    int slot[DC_Q * 4];
+        float x[DC_Q][4];
 #pragma unroll
-    for (int q = 0; q < DC_Q; q++) {
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            const int e = q * 4 + j;
-            bool ok = false;
-            key[e] = 0ull;
-            if (x[q][j] > logit_floor) {
-                const int sp = blockIdx.x * DC_SPAN + (q * 256 + threadIdx.x) * 4 + j;
-                float s = sigmoidf_ref(x[q][j]);
-                if (p.variant == 1) s = sqrtf(s * sigmoidf_ref(__ldg(L.ctrness + sp)));   // FCOS: sqrt(cls * centerness)
-                ok = s > p.score_thresh;
-                key[e] = sel::make_key(s, (unsigned)(((long long)sp * p.A + a) * p.K + k));
-            }
-            slot[e] = -1;
-            const unsigned em = __ballot_sync(0xffffffffu, ok);
-            if (em) {
-                int base = 0;
-                if (lane == 0) base = atomicAdd(&s_count, __popc(em));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (ok) slot[e] = base + __popc(em & ((1u << lane) - 1));
-            }
+        for (int g = 0; g < DC_Q; g++) {
+            const float4 v = *reinterpret_cast<const float4*>(&S.buf[stage][(g * 32 + lane) * 4]);   // what this lane copied itself
+            x[g][0] = v.x; x[g][1] = v.y; x[g][2] = v.z; x[g][3] = v.w;
         }
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) s_base = s_count ? atomicAdd(cand_count, s_count) : 0;
-    __syncthreads();
-    const int gbase = s_base;
+        int mine = 0;
 #pragma unroll
-    for (int e = 0; e < DC_Q * 4; e++)
-        if (slot[e] >= 0) L.cand[gbase + slot[e]] = key[e];
+        for (int g = 0; g < DC_Q; g++)
+#pragma unroll
+            for (int j = 0; j < 4; j++) mine += (x[g][j] > logit_floor);
+        int inc = mine;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += t; }
+        const int total = __shfl_sync(0xffffffffu, inc, 31);
+        if (total > 0) {                                   // uniform over the warp
+            if (pend_n && (pend_img != cur.img || pend_level != cur.level)) flush();
+            pend_img = cur.img; pend_level = cur.level;
+            float* l_val = S.buf[stage];                   // every lane holds its part of the span in registers by now
+            __syncwarp();
+            int o = inc - mine;
+            if (mine) {
+#pragma unroll
+                for (int g = 0; g < DC_Q; g++)
+#pragma unroll
+                    for (int j = 0; j < 4; j++)
+                        if (x[g][j] > logit_floor) { l_val[o] = x[g][j]; S.l_pos[o] = (unsigned short)((g * 32 + lane) * 4 + j); o++; }
+            }
+            __syncwarp();
+            const Level& L = p.lv[cur.level];
+            const int HW = L.H * L.W;
+            for (int r0 = 0; r0 < total; r0 += 32) {       // the list, lanes packed: score, exact threshold, key
+                const int e = r0 + lane;
+                bool ok = false;
+                unsigned long long key = 0ull;
+                if (e < total) {
+                    const int flat = cur.flat0 + S.l_pos[e];               // (channel, location) inside the image's tensor
+                    const int ch = flat / HW, sp = flat - ch * HW;
+                    const int a = ch / p.K, k = ch - a * p.K;
+                    float sc = sigmoidf_ref(l_val[e]);
+                    if (p.variant == 1) sc = sqrtf(sc * sigmoidf_ref(__ldg(L.ctrness + (long long)cur.img * HW + sp)));   // FCOS: sqrt(cls * centerness)
+                    ok = sc > p.score_thresh;
+                    key = sel::make_key(sc, (unsigned)(((long long)sp * p.A + a) * p.K + k));
+                }
+                const unsigned em = __ballot_sync(0xffffffffu, ok);
+                if (em) {
+                    if (pend_n + __popc(em) > DC_PEND) flush();
+                    if (ok) S.pend[pend_n + __popc(em & lt)] = key;
+                    pend_n += __popc(em);
+                }
+            }
+            __syncwarp();                                  // the list (in buf[stage]) is rewritten by the copy issued in the next iteration
+        }
+        cur = next;
+    }
+    flush();
 }
 
 struct ABox { float x1, y1, x2, y2, area; int cls; };
@@ -302,10 +380,21 @@ extern "C" int tcb_detectron_post(tcb_ctx* ctx, int b, int num_levels, const flo
         // sigmoid(x) > t needs x > logit(t); FCOS scores sqrt(cls * ctr) > t need cls > t*t. 0.01 below that: never a false reject
         const double t = variant == 1 ? (double)score_thresh * (double)score_thresh : (double)score_thresh;
         const float logit_floor = t <= 0.0 ? -INFINITY : (t >= 1.0 ? INFINITY : (float)(log(t / (1.0 - t)) - 0.01));
-        int hw_max = 1;
-        for (int l = 0; l < num_levels; l++) hw_max = hw_max > p.lv[l].H * p.lv[l].W ? hw_max : p.lv[l].H * p.lv[l].W;
-        TCB_REQUIRE(ctx, num_anchors * num_classes <= 65535, "tcb_detectron_post: more than 65535 channels");
-        TCB_KLAUNCH(ctx, det_candidates_kernel, dim3(tcb_div_up(hw_max, DC_SPAN), num_anchors * num_classes, num_levels * b), 256, 0, st, p, logit_floor);
+        DetSpans W;
+        memset(&W, 0, sizeof(W));
+            long long items = 0;
+        for (int l = 0; l < num_levels; l++) {
+            W.first[l] = (int)items;
+            W.per_image[l] = tcb_div_up((long long)num_anchors * num_classes * p.lv[l].H * p.lv[l].W, DC_SPAN);
+            items += (long long)W.per_image[l] * b;
+            if (items > (1ll << 30)) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_detectron_post: batch too large");
+        }
+        W.first[num_levels] = (int)items;
+        const size_t dc_smem = sizeof(DcWarp) * DC_WARPS;      // 48 KB: four CTAs per SM
+        const long long want = tcb_div_up(items, DC_WARPS);
+        const int ctas = (int)(want < (long long)ctx->num_sms * 4 ? want : (long long)ctx->num_sms * 4);
+        TCB_CUDA(ctx, cudaFuncSetAttribute(det_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dc_smem));
+        TCB_KLAUNCH(ctx, det_candidates_kernel, ctas, 32 * DC_WARPS, dc_smem, st, p, W, logit_floor);
         TCB_LAUNCHED(ctx);
     }
     TCB_CUDA(ctx, cudaFuncSetAttribute(det_level_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DET_CACHE * 8));

@@ -246,7 +246,7 @@ __device__ __forceinline__ float sigmoidf_ref(float x) { return 1.f / (1.f + exp
 // row is num_class floats: 12 bytes for KITTI), then a thread takes every 256th anchor of the tile.
 constexpr int PPC_TILE = 1024;
 template <bool VEC4>
-__global__ void __launch_bounds__(256) pp_candidates_kernel(const float* __restrict__ cls, int n_anchors, int num_class, float thresh,
+__global__ void __launch_bounds__(256) pp_candidates_kernel(const float* __restrict__ cls, int n_anchors, int num_class, float thresh, float logit_floor,
                                                             unsigned long long* __restrict__ cand, int* __restrict__ cand_count) {
     extern __shared__ __align__(16) float ppc_tile[];
     pdl_wait();
@@ -261,24 +261,48 @@ __global__ void __launch_bounds__(256) pp_candidates_kernel(const float* __restr
         for (int e = threadIdx.x; e < nfl; e += 256) ppc_tile[e] = __ldg(src + e);
     }
     __syncthreads();
+    // slots: one shared-memory reservation per warp and round, one global reservation per CTA (a frame's counter would
+    // otherwise serialise thousands of atomics from all over the grid)
+    __shared__ int s_count, s_base;
+    if (threadIdx.x == 0) s_count = 0;
+    __syncthreads();
     const int lane = threadIdx.x & 31;
-    for (int r = threadIdx.x; r < PPC_TILE; r += 256) {     // whole warps leave together: rows is checked per lane below
+    unsigned long long key[PPC_TILE / 256];
+    int slot[PPC_TILE / 256];
+#pragma unroll
+    for (int q = 0; q < PPC_TILE / 256; q++) {
+        const int r = q * 256 + threadIdx.x;
         bool ok = false;
         float best = 0.f;
         if (r < rows) {
             const float* p = ppc_tile + r * num_class;
-            best = sigmoidf_ref(p[0]);
-            for (int c = 1; c < num_class; c++) best = fmaxf(best, sigmoidf_ref(p[c]));
-            ok = best >= thresh;
+            float top = p[0];
+            for (int c = 1; c < num_class; c++) top = fmaxf(top, p[c]);
+            // an anchor whose largest logit lies below logit_floor (0.01 under the threshold's logit: far more than expf's
+            // error) cannot reach the threshold; the few that might get the sigmoid of every class, as the reference computes it
+            if (top > logit_floor) {
+                best = sigmoidf_ref(p[0]);
+                for (int c = 1; c < num_class; c++) best = fmaxf(best, sigmoidf_ref(p[c]));
+                ok = best >= thresh;
+            }
         }
+        key[q] = sel::make_key(best, (unsigned)(a0 + r));
+        slot[q] = -1;
         const unsigned em = __ballot_sync(0xffffffffu, ok);
         if (em) {
             int base = 0;
-            if (lane == 0) base = atomicAdd(&cand_count[f], __popc(em));
+            if (lane == 0) base = atomicAdd(&s_count, __popc(em));
             base = __shfl_sync(0xffffffffu, base, 0);
-            if (ok) cand[(long long)f * n_anchors + base + __popc(em & ((1u << lane) - 1))] = sel::make_key(best, (unsigned)(a0 + r));
+            if (ok) slot[q] = base + __popc(em & ((1u << lane) - 1));
         }
     }
+    __syncthreads();
+    if (threadIdx.x == 0) s_base = s_count ? atomicAdd(&cand_count[f], s_count) : 0;
+    __syncthreads();
+    unsigned long long* dst = cand + (long long)f * n_anchors + s_base;
+#pragma unroll
+    for (int q = 0; q < PPC_TILE / 256; q++)
+        if (slot[q] >= 0) dst[slot[q]] = key[q];
 }
 
 // anchor a -> decoded box (anchor_generator.py:17-60 analytically, box_coder_utils.py:45-77, anchor_head_template.py:253-263)
@@ -719,8 +743,10 @@ extern "C" int tcb_pp_anchor_post(tcb_ctx* ctx, const float* cls_dev, const floa
     TCB_CUDA(ctx, cudaMemsetAsync(cand_count, 0, sizeof(int) * b, st));
     const size_t tile_bytes = (size_t)PPC_TILE * num_class * sizeof(float);
     const bool vec4 = (((uintptr_t)cls_dev) & 15) == 0 && ((n_anchors * num_class) & 3) == 0;   // every frame and tile starts on a 16-byte boundary
-    if (vec4) TCB_KLAUNCH(ctx, pp_candidates_kernel<true>, dim3(tcb_div_up(n_anchors, PPC_TILE), b), 256, tile_bytes, st, cls_dev, (int)n_anchors, num_class, score_thresh, cand, cand_count);
-    else      TCB_KLAUNCH(ctx, pp_candidates_kernel<false>, dim3(tcb_div_up(n_anchors, PPC_TILE), b), 256, tile_bytes, st, cls_dev, (int)n_anchors, num_class, score_thresh, cand, cand_count);
+    const double st_d = (double)score_thresh;
+    const float logit_floor = st_d <= 0.0 ? -INFINITY : (st_d >= 1.0 ? INFINITY : (float)(log(st_d / (1.0 - st_d)) - 0.01));
+    if (vec4) TCB_KLAUNCH(ctx, pp_candidates_kernel<true>, dim3(tcb_div_up(n_anchors, PPC_TILE), b), 256, tile_bytes, st, cls_dev, (int)n_anchors, num_class, score_thresh, logit_floor, cand, cand_count);
+    else      TCB_KLAUNCH(ctx, pp_candidates_kernel<false>, dim3(tcb_div_up(n_anchors, PPC_TILE), b), 256, tile_bytes, st, cls_dev, (int)n_anchors, num_class, score_thresh, logit_floor, cand, cand_count);
     TCB_LAUNCHED(ctx);
     WideBufs wb;
     const int m_max = (int)(n_anchors < pre_max ? n_anchors : pre_max);
