@@ -83,6 +83,21 @@ int tcb_preprocess_image(tcb_ctx* ctx, const uint8_t* src_dev, int n, int h, int
                          int mode, int out_h, int out_w, float div, const float sub[3],
                          int pad_value, float* dst_dev, float* inv_affine_host, void* stream);
 
+/*
+ * Host boundary of the preprocess result: the reference's image_adjust returns a host float32
+ * array that goes into raw_input_contents (clients/preprocess/yolov5_preprocess.py:12-24, communicator/
+ * ros_inference.py:143-146), so the model input has to come back over PCIe — but its padding is a constant.
+ * tcb_content_rect: where tcb_preprocess_image puts the resampled frame for (mode, h, w, out_h, out_w):
+ *   rect = {left, top, width, height} in output pixels; everything outside it holds the pad value. Host only.
+ * tcb_copy_rect_d2h: asynchronous device -> (pinned) host copy of that rectangle of every plane of a
+ *   [planes, plane_h, plane_w] array, both sides in the same layout; the rest of the host array is not touched,
+ *   so a host buffer that already holds the pad value receives the same bytes as a full download
+ *   (configs[1] letterbox: 360 of 640 rows per plane).
+ */
+int tcb_content_rect(int mode, int h, int w, int out_h, int out_w, int rect[4]);
+int tcb_copy_rect_d2h(tcb_ctx* ctx, const void* src_dev, void* dst_host, int planes, int plane_h, int plane_w, int elem_bytes,
+                      int left, int top, int rect_w, int rect_h, void* stream);
+
 /* ---- YOLOv5 postprocess ---------------------------------------------------- */
 
 /*

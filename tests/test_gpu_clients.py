@@ -168,6 +168,36 @@ def test_pipelined_batch_equals_single_shot(engine):
     assert np.array_equal(a2, want[::-1])
 
 
+@pytest.mark.parametrize("hw", [(180, 320), (320, 180), (200, 200)])     # bands above/below, bands left/right, no bands
+def test_repeated_batches_download_only_the_frame_rows(engine, hw):
+    """From the second batch of a geometry on, only the rectangle that carries the frame comes back over PCIe (the padding
+    already sits in the pinned result buffer): results stay those of a full download, also when the geometry changes in
+    between and when deferred calls alternate between the two result buffers."""
+    pre = Yolov5client(engine=engine).get_preprocess()
+    h, w = hw
+    mk = lambda seed, hh=h, ww=w, n=12: np.stack([synth.image_noise(hh, ww, seed + i) for i in range(n)])
+    want = lambda fr: np.concatenate([pre2d.preprocess_frame(f, 160, 160, mode="letterbox") for f in fr])
+    sizes = []
+    for k in range(4):
+        fr = mk(3000 + 20 * k)
+        got = pre.image_adjust_batch(fr, (160, 160), mode="letterbox", chunks=3, copy=(k % 2 == 0))
+        assert np.array_equal(got, want(fr)), k
+        sizes.append(pre.last_d2h_bytes)
+    full = 12 * 3 * 160 * 160 * 4
+    assert sizes[0] == full and (sizes[1] < full if h != w else sizes[1] == full)
+    other = mk(3100, 90, 160)                                   # another geometry through the same buffers, then back
+    assert np.array_equal(pre.image_adjust_batch(other, (160, 160), mode="letterbox", chunks=3), want(other))
+    fr = mk(3200)
+    assert np.array_equal(pre.image_adjust_batch(fr, (160, 160), mode="letterbox", chunks=3), want(fr)) and pre.last_d2h_bytes == full
+    fa, fb = mk(3300), mk(3400)
+    for _ in range(3):
+        ha = pre.image_adjust_batch_async(fa, (160, 160), mode="letterbox", chunks=3, copy=False)
+        hb = pre.image_adjust_batch_async(fb, (160, 160), mode="letterbox", chunks=3, copy=False)
+        assert np.array_equal(ha.result(), want(fa)) and np.array_equal(hb.result(), want(fb))
+    assert pre.last_d2h_bytes < full or h == w
+    assert not ha.result().flags.writeable
+
+
 def test_extract_boxes_async_equals_extract_boxes(engine):
     """The pipelined variant: queued on its own stream while a batch preprocess runs on the others; same results, same
     return-the-exception convention."""

@@ -671,6 +671,64 @@ int iround_half_even(double v) { return (int)nearbyint(v); }  // python round() 
 
 }  // namespace
 
+// where the resampled frame lands in the (out_h, out_w) output and the gains of the mapping, per mode
+static void content_geometry(int mode, int h, int w, int out_h, int out_w, int& left, int& top, int& new_w, int& new_h, double& gain_x, double& gain_y) {
+    if (mode == TCB_RESIZE_STRETCH) {
+        left = 0; top = 0; new_w = out_w; new_h = out_h;
+        gain_x = (double)out_w / w; gain_y = (double)out_h / h;
+    } else if (mode == TCB_RESIZE_LETTERBOX) {
+        // ultralytics letterbox (SURVEY A2): r=min(S/h,S/w); new=round(w r),round(h r); pads split with round(+-0.1)
+        double r = fmin((double)out_h / h, (double)out_w / w);
+        new_w = iround_half_even(w * r); new_h = iround_half_even(h * r);
+        if (new_w < 1) new_w = 1;
+        if (new_h < 1) new_h = 1;
+        if (new_w > out_w) new_w = out_w;
+        if (new_h > out_h) new_h = out_h;
+        double dw = (out_w - new_w) / 2.0, dh = (out_h - new_h) / 2.0;
+        left = iround_half_even(dw - 0.1); top = iround_half_even(dh - 0.1);
+        gain_x = r; gain_y = r;
+    } else {
+        left = 0; top = 0; new_w = w; new_h = h;
+        gain_x = 1.0; gain_y = 1.0;
+    }
+}
+
+extern "C" int tcb_content_rect(int mode, int h, int w, int out_h, int out_w, int rect[4]) {
+    if (!rect || h < 1 || w < 1 || out_h < 1 || out_w < 1) return tcb_fail(nullptr, TCB_ERR_ARG, "tcb_content_rect: bad arguments");
+    if (mode != TCB_RESIZE_STRETCH && mode != TCB_RESIZE_LETTERBOX && mode != TCB_RESIZE_PAD) return tcb_fail(nullptr, TCB_ERR_ARG, "tcb_content_rect: unknown mode %d", mode);
+    if (mode == TCB_RESIZE_PAD && (h > out_h || w > out_w)) return tcb_fail(nullptr, TCB_ERR_ARG, "tcb_content_rect: PAD mode needs src <= out");
+    double gx, gy;
+    content_geometry(mode, h, w, out_h, out_w, rect[0], rect[1], rect[2], rect[3], gx, gy);
+    return TCB_OK;
+}
+
+extern "C" int tcb_copy_rect_d2h(tcb_ctx* ctx, const void* src_dev, void* dst_host, int planes, int plane_h, int plane_w, int elem_bytes,
+                                 int left, int top, int rect_w, int rect_h, void* stream) {
+    TCB_CHECK_CTX(ctx);
+    TCB_REQUIRE(ctx, planes >= 0 && plane_h >= 1 && plane_w >= 1 && elem_bytes >= 1, "tcb_copy_rect_d2h: bad plane shape");
+    TCB_REQUIRE(ctx, left >= 0 && top >= 0 && rect_w >= 0 && rect_h >= 0 && left + rect_w <= plane_w && top + rect_h <= plane_h, "tcb_copy_rect_d2h: rectangle outside the plane");
+    if (planes == 0 || rect_w == 0 || rect_h == 0) return TCB_OK;
+    TCB_REQUIRE(ctx, src_dev && dst_host, "tcb_copy_rect_d2h: null buffer");
+    const size_t pitch = (size_t)plane_w * elem_bytes;
+    if (rect_w == plane_w) {
+        // whole rows: one run of rect_h rows per plane -> a pitched 2-D copy (long contiguous runs for the copy engine)
+        const size_t off = (size_t)top * pitch, run = (size_t)rect_h * pitch, ppitch = (size_t)plane_h * pitch;
+        TCB_CUDA(ctx, cudaMemcpy2DAsync((char*)dst_host + off, ppitch, (const char*)src_dev + off, ppitch, run, (size_t)planes, cudaMemcpyDeviceToHost,
+                                        (cudaStream_t)stream));
+        return TCB_OK;
+    }
+    cudaMemcpy3DParms q;
+    memset(&q, 0, sizeof(q));
+    q.srcPtr = make_cudaPitchedPtr(const_cast<void*>(src_dev), pitch, (size_t)plane_w * elem_bytes, (size_t)plane_h);
+    q.dstPtr = make_cudaPitchedPtr(dst_host, pitch, (size_t)plane_w * elem_bytes, (size_t)plane_h);
+    q.srcPos = make_cudaPos((size_t)left * elem_bytes, (size_t)top, 0);
+    q.dstPos = q.srcPos;
+    q.extent = make_cudaExtent((size_t)rect_w * elem_bytes, (size_t)rect_h, (size_t)planes);
+    q.kind = cudaMemcpyDeviceToHost;
+    TCB_CUDA(ctx, cudaMemcpy3DAsync(&q, (cudaStream_t)stream));
+    return TCB_OK;
+}
+
 extern "C" int tcb_preprocess_image(tcb_ctx* ctx, const uint8_t* src_dev, int n, int h, int w,
                                     long long src_row_stride, long long src_img_stride, int channel_swap,
                                     int mode, int out_h, int out_w, float div, const float sub[3],
@@ -694,25 +752,8 @@ extern "C" int tcb_preprocess_image(tcb_ctx* ctx, const uint8_t* src_dev, int n,
     p.swap = channel_swap ? 1 : 0;
 
     double gain_x, gain_y;
-    if (mode == TCB_RESIZE_STRETCH) {
-        p.left = 0; p.top = 0; p.new_w = out_w; p.new_h = out_h;
-        gain_x = (double)out_w / w; gain_y = (double)out_h / h;
-    } else if (mode == TCB_RESIZE_LETTERBOX) {
-        // ultralytics letterbox (SURVEY A2): r=min(S/h,S/w); new=round(w r),round(h r); pads split with round(+-0.1)
-        double r = fmin((double)out_h / h, (double)out_w / w);
-        p.new_w = iround_half_even(w * r); p.new_h = iround_half_even(h * r);
-        if (p.new_w < 1) p.new_w = 1;
-        if (p.new_h < 1) p.new_h = 1;
-        if (p.new_w > out_w) p.new_w = out_w;
-        if (p.new_h > out_h) p.new_h = out_h;
-        double dw = (out_w - p.new_w) / 2.0, dh = (out_h - p.new_h) / 2.0;
-        p.left = iround_half_even(dw - 0.1); p.top = iround_half_even(dh - 0.1);
-        gain_x = r; gain_y = r;
-    } else {
-        TCB_REQUIRE(ctx, h <= out_h && w <= out_w, "tcb_preprocess_image: PAD mode needs src (%dx%d) <= out (%dx%d)", h, w, out_h, out_w);
-        p.left = 0; p.top = 0; p.new_w = w; p.new_h = h;
-        gain_x = 1.0; gain_y = 1.0;
-    }
+    if (mode == TCB_RESIZE_PAD) TCB_REQUIRE(ctx, h <= out_h && w <= out_w, "tcb_preprocess_image: PAD mode needs src (%dx%d) <= out (%dx%d)", h, w, out_h, out_w);
+    content_geometry(mode, h, w, out_h, out_w, p.left, p.top, p.new_w, p.new_h, gain_x, gain_y);
     if (inv_affine_host) {
         inv_affine_host[0] = (float)gain_x; inv_affine_host[1] = (float)gain_y;
         inv_affine_host[2] = (float)p.left; inv_affine_host[3] = (float)p.top;

@@ -64,6 +64,29 @@ class Engine:
         return out, np.array(list(aff), dtype=np.float32)
 
     # ---- YOLOv5 postprocess ----------------------------------------------------------------------
+    MODES = {"stretch": 0, "letterbox": 1, "pad": 2}
+
+    def content_rect(self, mode, h, w, out_h, out_w):
+        """(left, top, width, height) of the resampled frame inside the (out_h, out_w) output of preprocess_images."""
+        rect = (c_int * 4)()
+        rc = self.lib.tcb_content_rect(self.MODES[mode], int(h), int(w), int(out_h), int(out_w), rect)
+        if rc != 0:
+            raise _lib.TcbError(rc, (self.lib.tcb_last_error(None) or b"").decode())
+        return tuple(int(v) for v in rect)
+
+    def copy_rect_d2h(self, src, dst_host, rect):
+        """Asynchronous download (current stream) of rectangle `rect` of every [H,W] plane of CUDA tensor `src` [..., H, W]
+        into the pinned host tensor `dst_host` of the same shape; the rest of `dst_host` is left as it is."""
+        _need_cuda(src)
+        if not (src.is_contiguous() and dst_host.is_contiguous() and dst_host.is_pinned() and tuple(src.shape) == tuple(dst_host.shape)
+                and src.dtype == dst_host.dtype):
+            raise TypeError("copy_rect_d2h: need a contiguous CUDA source and a pinned, contiguous host destination of the same shape and dtype")
+        h, w = src.shape[-2], src.shape[-1]
+        planes = src.numel() // (h * w) if h * w else 0
+        left, top, rw, rh = rect
+        self.ctx.call("tcb_copy_rect_d2h", _ptr(src), c_void_p(dst_host.data_ptr()), planes, h, w, src.element_size(), left, top, rw, rh,
+                      _lib.stream_ptr())
+
     def yolo_nms_workspace(self, b, n):
         return int(self.lib.tcb_yolo_nms_workspace(int(b), int(n)))
 
@@ -185,11 +208,12 @@ class Engine:
 
     # ---- LiDAR voxelisation + pillar decoration ------------------------------------------------------
     def voxelize(self, points, point_range, voxel_size, max_pts, max_vox, overflow="continue", f64_math=False,
-                 range_mask=False, z_offset=0.0, intensity_col=-1, nfeat=None, offsets=None):
+                 range_mask=False, z_offset=0.0, intensity_col=-1, nfeat=None, offsets=None, out=None):
         """points: f32 CUDA [n, C]. One sweep: returns device tensors (voxels [max_vox,P,F], coords [max_vox,4] b,z,y,x,
         num_points [max_vox], m [1]); rows >= m are not meaningful. A batch: `offsets` = b+1 ascending row offsets of the
         sweeps inside `points` (host ints) and every result gains a leading batch dimension ([b,max_vox,...], m [b]; the
-        batch column of coords is the sweep's index). No host sync."""
+        batch column of coords is the sweep's index). `out` = a previous call's result tuple to write into (same shapes): a
+        steady-state caller then allocates nothing per call. No host sync."""
         _need_cuda(points)
         if points.dtype != torch.float32 or points.dim() != 2 or (points.shape[0] > 0 and points.stride(1) != 1):
             raise TypeError("voxelize: points must be a float32 [n, C] tensor with contiguous rows")
@@ -198,10 +222,15 @@ class Engine:
         dev = points.device
         b = 1 if offsets is None else len(offsets) - 1
         lead = () if offsets is None else (b,)
-        voxels = torch.empty(lead + (max_vox, max_pts, f), dtype=torch.float32, device=dev)
-        coords = torch.empty(lead + (max_vox, 4), dtype=torch.int32, device=dev)
-        num = torch.empty(lead + (max_vox,), dtype=torch.int32, device=dev)
-        m = torch.empty((b,), dtype=torch.int32, device=dev)
+        if out is not None:
+            voxels, coords, num, m = out
+            if tuple(voxels.shape) != lead + (max_vox, max_pts, f) or m.shape[0] != b:
+                raise ValueError("voxelize: `out` does not match this call's shapes")
+        else:
+            voxels = torch.empty(lead + (max_vox, max_pts, f), dtype=torch.float32, device=dev)
+            coords = torch.empty(lead + (max_vox, 4), dtype=torch.int32, device=dev)
+            num = torch.empty(lead + (max_vox,), dtype=torch.int32, device=dev)
+            m = torch.empty((b,), dtype=torch.int32, device=dev)
         rng = (ctypes.c_double * 6)(*[float(v) for v in point_range])
         vs = (ctypes.c_double * 3)(*[float(v) for v in voxel_size])
         offs = None if offsets is None else (c_int * (b + 1))(*[int(v) for v in offsets])
@@ -210,13 +239,14 @@ class Engine:
                       int(intensity_col), _ptr(voxels), _ptr(coords), _ptr(num), _ptr(m), _lib.stream_ptr())
         return voxels, coords, num, m
 
-    def pillar_decorate(self, voxels, coords, num_points, voxel_size, point_range, m=None):
+    def pillar_decorate(self, voxels, coords, num_points, voxel_size, point_range, m=None, out=None):
         """(M,P,F) voxels -> (M,P,F+6) decorated features, or a batch (b,M,P,F) -> (b,M,P,F+6); `m` may be the device
         count(s) from voxelize()."""
         _need_cuda(voxels, coords, num_points)
         b = voxels.shape[0] if voxels.dim() == 4 else 1
         mm, p, f = voxels.shape[-3:]
-        out = torch.empty(tuple(voxels.shape[:-1]) + (f + 6,), dtype=torch.float32, device=voxels.device)
+        if out is None:
+            out = torch.empty(tuple(voxels.shape[:-1]) + (f + 6,), dtype=torch.float32, device=voxels.device)
         vs = (ctypes.c_double * 3)(*[float(v) for v in voxel_size])
         r0 = (ctypes.c_double * 3)(*[float(v) for v in point_range[:3]])
         self.ctx.call("tcb_pillar_decorate", _ptr(voxels), _ptr(coords), _ptr(num_points), _ptr(m) if m is not None else None,
@@ -264,7 +294,7 @@ class Engine:
 
     def pp_anchor_post(self, cls_preds, box_preds, dir_preds, anchor_range, anchor_sizes, anchor_bottoms, anchor_rotations,
                        dir_offset=0.78539, dir_limit_offset=0.0, num_dir_bins=2, score_thresh=0.1, nms_thresh=0.01,
-                       pre_max=4096, post_max=500):
+                       pre_max=4096, post_max=500, out=None):
         """PointPillars head outputs of one frame — cls (H,W,A*nc), box (H,W,A*7), dir (H,W,A*bins) or None — or of a
         batch (B,H,W,...). Returns device tensors (boxes [post_max,7], scores [post_max], labels int64 [post_max],
         count [1]), with a leading B on each for a batch (count [B])."""
@@ -276,10 +306,13 @@ class Engine:
         nc = len(anchor_sizes)
         nrot = len(anchor_rotations[0])
         dev = cls_preds.device
-        ob = torch.zeros(lead + (post_max, 7), dtype=torch.float32, device=dev)
-        osc = torch.zeros(lead + (post_max,), dtype=torch.float32, device=dev)
-        ol = torch.zeros(lead + (post_max,), dtype=torch.int64, device=dev)
-        cnt = torch.zeros((b,), dtype=torch.int32, device=dev)
+        if out is not None:
+            ob, osc, ol, cnt = out            # a previous call's result tuple (same shapes): rows beyond count keep older values
+        else:
+            ob = torch.zeros(lead + (post_max, 7), dtype=torch.float32, device=dev)
+            osc = torch.zeros(lead + (post_max,), dtype=torch.float32, device=dev)
+            ol = torch.zeros(lead + (post_max,), dtype=torch.int64, device=dev)
+            cnt = torch.zeros((b,), dtype=torch.int32, device=dev)
         rng = (c_float * 6)(*[float(np.float32(v)) for v in anchor_range])
         sizes = (c_float * (nc * 3))(*[float(v) for s in anchor_sizes for v in s])
         bots = (c_float * nc)(*[float(v) for v in anchor_bottoms])
@@ -291,7 +324,7 @@ class Engine:
         return ob, osc, ol, cnt
 
     def centerpoint_post(self, heads, class_id_map, feature_map_stride, voxel_size, point_range, limit_range, k=500,
-                         score_thresh=0.1, nms_thresh=0.2, pre_max=1000, post_max=83):
+                         score_thresh=0.1, nms_thresh=0.2, pre_max=1000, post_max=83, out=None):
         """heads: list of dicts with CUDA f32 tensors hm [c,H,W], center [2,H,W], center_z [1,H,W], dim [3,H,W],
         rot [2,H,W], optional vel [2,H,W] — or each with a leading batch dimension [B,...]; class_id_map: list (per head)
         of global 0-based class ids. Returns (boxes [heads*post_max,9], scores, labels int64 1-based, count [1]), with a
@@ -323,10 +356,13 @@ class Engine:
         ncls = (c_int * nh)(*[int(hd["hm"].shape[-3]) for hd in heads])
         cmap = [int(v) for m in class_id_map for v in m]
         cmap_arr = (c_int * len(cmap))(*cmap)
-        ob = torch.zeros(lead + (nh * post_max, 9), dtype=torch.float32, device=dev)
-        osc = torch.zeros(lead + (nh * post_max,), dtype=torch.float32, device=dev)
-        ol = torch.zeros(lead + (nh * post_max,), dtype=torch.int64, device=dev)
-        cnt = torch.zeros((b,), dtype=torch.int32, device=dev)
+        if out is not None:
+            ob, osc, ol, cnt = out            # a previous call's result tuple (same shapes): rows beyond count keep older values
+        else:
+            ob = torch.zeros(lead + (nh * post_max, 9), dtype=torch.float32, device=dev)
+            osc = torch.zeros(lead + (nh * post_max,), dtype=torch.float32, device=dev)
+            ol = torch.zeros(lead + (nh * post_max,), dtype=torch.int64, device=dev)
+            cnt = torch.zeros((b,), dtype=torch.int32, device=dev)
         has_vel = all(hd.get("vel") is not None for hd in heads)
         self.ctx.call("tcb_centerpoint_post", b, nh, ptrs("hm"), ptrs("center"), ptrs("center_z"), ptrs("dim"), ptrs("rot"),
                       ptrs("vel", True) if has_vel else None, ncls, cmap_arr, h, w, int(feature_map_stride),
