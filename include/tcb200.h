@@ -98,6 +98,31 @@ int tcb_content_rect(int mode, int h, int w, int out_h, int out_w, int rect[4]);
 int tcb_copy_rect_d2h(tcb_ctx* ctx, const void* src_dev, void* dst_host, int planes, int plane_h, int plane_w, int elem_bytes,
                       int left, int top, int rect_w, int rect_h, void* stream);
 
+/* ---- compressed camera frames ------------------------------------------------- */
+
+/*
+ * Baseline JPEG decode on the device, bit-identical to what the reference's compressed-image branch computes:
+ *   cv_image = cv2.imdecode(buf, cv2.IMREAD_ANYCOLOR)   # BGR8      (communicator/ros_inference.py:123-130)
+ *   cv_image = cv_image[..., ::-1]                                  (:131; here: bgr = 0 writes RGB directly)
+ * i.e. libjpeg-turbo's default decode path (Huffman, dequantisation + islow integer IDCT, fancy chroma
+ * upsampling, fixed-point YCbCr -> RGB). Scope: 8-bit baseline / extended-sequential Huffman streams with one
+ * interleaved scan, 3 components (4:4:4, 4:2:2, 4:4:0, 4:2:0) or 1 (grey), with or without restart intervals;
+ * anything else (progressive, arithmetic, 12-bit, CMYK, RGB-coded) is refused with TCB_ERR_ARG and a message —
+ * there is no CPU fallback.
+ * tcb_jpeg_info: frame size and component count of one stream (host only).
+ * tcb_jpeg_decode: n streams of the SAME size and component count -> out_dev [n, out_h, out_w, out_channels] u8
+ *   (channels 3: RGB, or BGR when bgr != 0; channels 1: grey). jpeg_host / jpeg_len: n host pointers and
+ *   lengths. The marker parse runs on the calling thread; the entropy-coded bytes go through staging_host
+ *   (PINNED host memory of at least tcb_jpeg_staging_bytes(sum of lengths, n) bytes, in use until `stream`
+ *   has passed this call) to the device in one copy; everything else is kernels on `stream`, no host sync.
+ *   Needs tcb_jpeg_workspace(sum of lengths, n, out_h, out_w) bytes of context workspace.
+ */
+int tcb_jpeg_info(const unsigned char* jpeg_host, size_t len, int* height, int* width, int* channels);
+size_t tcb_jpeg_staging_bytes(size_t total_jpeg_bytes, int n);
+size_t tcb_jpeg_workspace(size_t total_jpeg_bytes, int n, int height, int width);
+int tcb_jpeg_decode(tcb_ctx* ctx, const unsigned char* const* jpeg_host, const size_t* jpeg_len, int n, void* staging_host,
+                    size_t staging_bytes, int bgr, unsigned char* out_dev, int out_h, int out_w, int out_channels, void* stream);
+
 /* ---- YOLOv5 postprocess ---------------------------------------------------- */
 
 /*

@@ -37,6 +37,10 @@ SIGNATURES = {
     "tcb_launch_count": (c_ll, [c_void_p]),
     "tcb_preprocess_image": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_ll, c_ll, c_int, c_int, c_int, c_int,
                                      c_float, P(c_float), c_int, c_void_p, P(c_float), c_void_p]),
+    "tcb_jpeg_info": (c_int, [c_void_p, c_size_t, P(c_int), P(c_int), P(c_int)]),
+    "tcb_jpeg_staging_bytes": (c_size_t, [c_size_t, c_int]),
+    "tcb_jpeg_workspace": (c_size_t, [c_size_t, c_int, c_int, c_int]),
+    "tcb_jpeg_decode": (c_int, [c_void_p, P(c_void_p), P(c_size_t), c_int, c_void_p, c_size_t, c_int, c_void_p, c_int, c_int, c_int, c_void_p]),
     "tcb_content_rect": (c_int, [c_int, c_int, c_int, c_int, c_int, P(c_int)]),
     "tcb_copy_rect_d2h": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "tcb_yolo_nms_workspace": (c_size_t, [c_int, c_int]),

@@ -95,3 +95,17 @@ class Stager:
         view.copy_(t, non_blocking=True)
         torch.cuda.current_stream().synchronize()
         return view.numpy().copy() if copy else view.numpy()
+
+
+def decode_compressed_image(data, engine=None, device=False):
+    """The compressed-image branch of the reference's 2D callback (communicator/ros_inference.py:123-131):
+        cv_image = cv2.imdecode(np.ndarray(shape=(1, len(msg.data)), dtype=np.uint8, buffer=msg.data), cv2.IMREAD_ANYCOLOR)[..., ::-1]
+    `data` = msg.data (bytes-like, a baseline JPEG). Returns the RGB frame (H, W, 3) uint8 — a host ndarray like the
+    reference's, or with device=True the CUDA tensor, ready for Yolov5preprocess.image_adjust_device / resize_adjust
+    without the pixels ever visiting the host. Decoded by tcb_jpeg_decode, bit-identical to OpenCV. A list of streams
+    of one size gives (n, H, W, 3)."""
+    eng = engine or default_engine()
+    single = isinstance(data, (bytes, bytearray, memoryview, np.ndarray))
+    frames = eng.jpeg_decode([data] if single else list(data), bgr=False)
+    frames = frames[0] if single else frames
+    return frames if device else frames.cpu().numpy()

@@ -64,6 +64,41 @@ class Engine:
         return out, np.array(list(aff), dtype=np.float32)
 
     # ---- YOLOv5 postprocess ----------------------------------------------------------------------
+    # ---- compressed camera frames ---------------------------------------------------------------------
+    def jpeg_info(self, data):
+        """(height, width, channels) of a baseline JPEG stream (bytes-like)."""
+        buf = np.frombuffer(data, np.uint8)
+        h, w, c = c_int(), c_int(), c_int()
+        rc = self.lib.tcb_jpeg_info(c_void_p(buf.ctypes.data), buf.size, ctypes.byref(h), ctypes.byref(w), ctypes.byref(c))
+        if rc != 0:
+            raise _lib.TcbError(rc, (self.lib.tcb_last_error(None) or b"").decode())
+        return h.value, w.value, c.value
+
+    def jpeg_decode(self, streams, bgr=False, out=None):
+        """cv2.imdecode(..., IMREAD_ANYCOLOR) of a list of same-sized baseline JPEG streams (bytes-like), on the device:
+        uint8 CUDA tensor [n, H, W, 3] in RGB order (the reference flips cv2's BGR to RGB right away; bgr=True keeps
+        cv2's order) or [n, H, W] for grey streams. Bit-identical to OpenCV / libjpeg-turbo."""
+        bufs = [np.frombuffer(s, np.uint8) for s in streams]
+        n = len(bufs)
+        if n == 0:
+            return torch.empty((0, 0, 0, 3), dtype=torch.uint8, device=self.device)
+        h, w, c = self.jpeg_info(bufs[0])
+        total = sum(b.size for b in bufs)
+        need = int(self.lib.tcb_jpeg_staging_bytes(total, n))
+        if getattr(self, "_jpeg_event", None) is not None:
+            self._jpeg_event.synchronize()                # the previous call's upload has left the staging buffer
+        if getattr(self, "_jpeg_stage", None) is None or self._jpeg_stage.numel() < need:
+            self._jpeg_stage = torch.empty(max(need, 1 << 20), dtype=torch.uint8).pin_memory()
+        if out is None:
+            out = torch.empty((n, h, w, 3) if c == 3 else (n, h, w), dtype=torch.uint8, device=self.device)
+        ptrs = (c_void_p * n)(*[b.ctypes.data for b in bufs])
+        lens = (ctypes.c_size_t * n)(*[b.size for b in bufs])
+        self.ctx.call("tcb_jpeg_decode", ptrs, lens, n, c_void_p(self._jpeg_stage.data_ptr()), self._jpeg_stage.numel(), 1 if bgr else 0,
+                      _ptr(out), h, w, c, _lib.stream_ptr())
+        self._jpeg_event = torch.cuda.Event()
+        self._jpeg_event.record()
+        return out
+
     MODES = {"stretch": 0, "letterbox": 1, "pad": 2}
 
     def content_rect(self, mode, h, w, out_h, out_w):
