@@ -348,24 +348,26 @@ int tcb_class_score_filter(tcb_ctx* ctx, const long long* labels_dev, const floa
 int tcb_scale_boxes(tcb_ctx* ctx, const double* det_dev, int n, int orig_h, int orig_w, int input_size0, int input_size1,
                     int normalized, int math_mode, double* out_dev, void* stream);
 
-/* The per-detection drawing loop of RosInference._callback (communicator/ros_inference.py:148-169), in place on b
- * device frames (h x w x 3 uint8, row_stride / frame_stride in bytes): each of the first count_dev[f] (NULL:
- * max_det) rows of det_dev[f] (max_det x 6 float64, model-input pixels) is scaled like _scale_boxes (math_mode 1
- * or 2; orig size = h, w), truncated like Python's int(), and drawn as cv2.rectangle(thickness 1 or 2) plus, when
- * labels != 0, cv2.putText('{:.2f} {}'.format(conf, name), (x1, int(y1 - 10)), FONT_HERSHEY_SIMPLEX, 0.5, thickness
- * 2). Detections are painted in order (a later one overwrites an earlier one). class_names: host memory,
- * num_classes strings back to back, each '\0'-terminated (<= 128 classes, <= 2560 bytes; labels longer than 64
- * characters are cut). colors: host memory, 3 bytes in frame channel order, or num_classes x 3 when
- * per_class_color != 0 (Yolov5postprocess.plot_boxes_cv2's per-class colours,
- * clients/postprocess/yolov5_postprocess.py:127-169; its 1.2-scale labels are not available). Rectangles are
- * identical to OpenCV's everywhere; labels are identical when they lie inside the frame — a label cut by the
- * frame edge can differ in a few pixels (OpenCV clips stroke outlines before rasterising them). */
+/* The per-detection drawing loop of RosInference._callback (communicator/ros_inference.py:148-169) and of
+ * Yolov5postprocess.plot_boxes_cv2 (clients/postprocess/yolov5_postprocess.py:127-169), in place on b device
+ * frames (h x w x 3 uint8, row_stride / frame_stride in bytes): each of the first count_dev[f] (NULL: max_det) rows of
+ * det_dev[f] (max_det x 6 float64: x1, y1, x2, y2, conf, class) is scaled like _scale_boxes (math_mode 1 or 2; orig
+ * size = h, w; normalized != 0: x * w, y * h as plot_boxes_cv2 does), truncated like Python's int(), and drawn as
+ * cv2.rectangle(thickness 1 or 2) plus, when labels != 0, cv2.putText(text, (x1, int(y1 + text_dy)),
+ * FONT_HERSHEY_SIMPLEX, font_scale, color, text_thickness) with text = '{:.2f} {}'.format(conf, name) (labels 1:
+ * ros_inference.py:163-169, font_scale 0.5, text_thickness 2, text_dy -10) or the class name alone (labels 2:
+ * plot_boxes_cv2, font_scale 1.2, text_thickness 1, text_dy 0). Detections are painted in order (a later one
+ * overwrites an earlier one). class_names: host memory, num_classes strings back to back, each '\0'-terminated
+ * (<= 128 classes, <= 2560 bytes; labels longer than 64 characters are cut). colors: host memory, 3 bytes in frame
+ * channel order, or num_classes x 3 when per_class_color != 0 (plot_boxes_cv2's get_color table). Pixels are
+ * identical to OpenCV's for every scale and thickness, labels cut by the frame edge included: the strokes of the
+ * Hershey font are rasterised with OpenCV's own rules (clipLine, LineIterator, FillConvexPoly, Circle). */
 size_t tcb_draw_detections_workspace(int b, int max_det);
 int tcb_draw_detections(tcb_ctx* ctx, unsigned char* frames_dev, int b, int h, int w, long long row_stride,
                         long long frame_stride, const double* det_dev, const int* count_dev, int max_det,
                         int input_size0, int input_size1, int normalized, int math_mode, const char* class_names,
                         int num_classes, const unsigned char* colors, int per_class_color, int thickness, int labels,
-                        void* stream);
+                        double font_scale, int text_thickness, int text_dy, void* stream);
 
 /* ---- ROS message decode/encode around the 3D path ----------------------------- */
 

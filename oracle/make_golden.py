@@ -248,6 +248,34 @@ def golden_overlay():
     save("overlay", **out)
 
 
+def golden_plot_boxes():
+    """Yolov5postprocess.plot_boxes_cv2 (clients/postprocess/yolov5_postprocess.py:127-169) run unmodified: normalised
+    boxes (rows [x1, y1, x2, y2, conf, conf, class] as extract_boxes_onnx builds them: np.float32 values, np.int64 class),
+    per-class colours from get_color, putText(class name, scale 1.2, thickness 1), rectangle thickness 1. Boxes reach
+    over every frame edge, so labels and rectangles are clipped. numpy here is %s (np.float32 * int stays float32)."""
+    import contextlib
+    import io
+    c = ref_harness.clients()
+    post = c.Yolov5client().get_postprocess()
+    names = ["crop", "weed", "person", "traffic light", "Qjg|y_{"]
+    out = {"names": np.array(names), "numpy_version": np.array(np.__version__)}
+    for k, (h, w, n) in enumerate([(180, 320, 9), (97, 131, 14)]):
+        rng = np.random.default_rng(600 + k)
+        img = synth.image_noise(h, w, synth.seed_for(9, k))
+        xy = rng.uniform(-0.15, 0.95, (n, 2))
+        wh = rng.uniform(0.05, 0.5, (n, 2))
+        boxes = np.concatenate([xy, xy + wh, rng.uniform(0.3, 1, (n, 2))], 1).astype(np.float32)
+        cls = rng.integers(0, len(names), n)
+        rows = [[b[0], b[1], b[2], b[3], b[4], b[5], np.int64(ci)] for b, ci in zip(boxes, cls)]
+        with contextlib.redirect_stdout(io.StringIO()):
+            res = post.plot_boxes_cv2(img, rows, class_names=names)
+        assert res.shape == img.shape and (res != img).any()
+        out[f"img{k}"], out[f"boxes{k}"], out[f"cls{k}"], out[f"out{k}"] = img, boxes, cls.astype(np.int64), res
+    save("plot_boxes", **out)
+
+
+golden_plot_boxes.__doc__ = golden_plot_boxes.__doc__ % np.__version__
+
 EVAL_CASES = [dict(n_gt=24, nc=2), dict(n_gt=40, nc=2, miss=0.3, false_pos=20), dict(n_gt=6, nc=3, dup=0.6),
               dict(n_gt=12, nc=2, miss=1.0, false_pos=5),              # nothing matches: the frame is skipped
               dict(n_gt=60, nc=5, dup=0.5, swap=0.2, false_pos=30), dict(n_gt=1, nc=1, miss=0.0, false_pos=0, dup=0.0, swap=0.0),

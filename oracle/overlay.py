@@ -8,27 +8,21 @@ communicator/ros_inference.py:148-169:
                 cv2.FONT_HERSHEY_SIMPLEX, fontScale=0.5, thickness=2, color)
 and communicator/evaluate_inference.py:237-256 (_scale_box_array, float64 array arithmetic).
 
-Pinned: tests/golden/overlay.npz holds frames annotated by the unmodified RosInference._callback run in the build
-container (oracle/make_golden.py::golden_overlay), and tests/test_oracle_overlay.py checks rect_mask / text_mask
-against cv2 itself when cv2 is importable. OpenCV is a dependency of the reference, not part of its tree: the
-rectangle rule below is the observed raster of cv2.rectangle (thickness 1: the outline; thickness 2: the outline
-grown by its 4-neighbourhood), the glyph rasters are measured from cv2.putText (csrc/gen_font_atlas.py).
-Known difference: a label cut by the frame edge can differ from OpenCV in a few pixels (OpenCV clips each stroke
-outline before walking it).
+and, per box, Yolov5postprocess.plot_boxes_cv2 (clients/postprocess/yolov5_postprocess.py:127-169: normalised boxes,
+per-class colours, putText of the class name at scale 1.2 thickness 1, rectangle thickness 1).
+
+Pinned: tests/golden/overlay.npz holds frames annotated by the unmodified RosInference._callback and plot_boxes_cv2 run
+in the build container (oracle/make_golden.py::golden_overlay), and tests/test_oracle_overlay.py checks rect_mask /
+text_mask against cv2 itself. OpenCV is a dependency of the reference, not part of its tree: the rectangle rule below is
+the observed raster of cv2.rectangle (thickness 1: the outline; thickness 2: the outline grown by its 4-neighbourhood),
+the text is oracle/cvdraw.py's restatement of putText (Hershey strokes + OpenCV's line / polygon / disc rasterisers),
+identical to cv2.putText for every scale, thickness and position, labels cut by the frame edge included.
 """
 import os
 
 import numpy as np
 
-_ATLAS = None
-
-
-def atlas():
-    global _ATLAS
-    if _ATLAS is None:
-        z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "hershey_s05_t2.npz"))
-        _ATLAS = (z["adv2"].astype(np.int64), z["rows"].astype(np.int64), [int(v) for v in z["cell"]])
-    return _ATLAS
+from . import cvdraw
 
 
 def scale_box(box4, orig_size, input_size, normalized=False, f64=True):
@@ -79,24 +73,10 @@ def rect_mask(h, w, x1, y1, x2, y2, thickness):
     return m
 
 
-def text_mask(h, w, text, ox, oy):
-    """Pixels cv2.putText(img, text, (ox,oy), FONT_HERSHEY_SIMPLEX, 0.5, color, 2) writes (in-frame labels exactly)."""
-    adv2, rows, (cw, ch, y0) = atlas()
+def text_mask(h, w, text, ox, oy, font_scale=0.5, thickness=2):
+    """Pixels cv2.putText(img, text, (ox,oy), FONT_HERSHEY_SIMPLEX, font_scale, color, thickness) writes."""
     out = np.zeros((h, w), bool)
-    pen2 = 0
-    for c in text:
-        g = ord(c) - 32
-        if not 0 <= g < 95:
-            g = ord("?") - 32
-        px = ox + (pen2 >> 1)
-        for r in range(ch):
-            bits = int(rows[g, pen2 & 1, r])
-            y = oy + y0 + r
-            if bits and 0 <= y < h:
-                for b in range(cw):
-                    if (bits >> b) & 1 and 0 <= px + b < w:
-                        out[y, px + b] = True
-        pen2 += int(adv2[g])
+    cvdraw.put_text(out, "".join(c if 32 <= ord(c) < 127 else "?" for c in text), (int(ox), int(oy)), font_scale, thickness)
     return out
 
 
@@ -105,10 +85,11 @@ def label_text(conf, name):
 
 
 def draw_detections(frame, det, class_names, color, input_size, thickness=2, labels=True, f64=True, normalized=False,
-                    per_class_color=False):
+                    per_class_color=False, font_scale=0.5, text_thickness=2, text_dy=-10):
     """The loop body of RosInference._callback over one frame. frame (H,W,3) u8 is modified in place and returned;
     det (n,6) float64 rows [x1,y1,x2,y2,conf,cls] in model-input pixels. per_class_color: `color` is a table indexed
-    by class (plot_boxes_cv2's colouring, yolov5_postprocess.py:127-169); later detections paint over earlier ones."""
+    by class (plot_boxes_cv2's colouring, yolov5_postprocess.py:127-169); later detections paint over earlier ones.
+    labels: False, True ('{:.2f} {name}') or "name" (the class name alone, plot_boxes_cv2)."""
     h, w = frame.shape[:2]
     for row in np.asarray(det, np.float64).reshape(-1, 6):
         col = np.asarray(color[int(row[5])] if per_class_color else color, np.uint8)
@@ -116,6 +97,24 @@ def draw_detections(frame, det, class_names, color, input_size, thickness=2, lab
         x1, y1, x2, y2 = (int(v) for v in b)
         frame[rect_mask(h, w, x1, y1, x2, y2, thickness)] = col
         if labels:
-            ten = np.float64(10) if f64 else np.float32(10)
-            frame[text_mask(h, w, label_text(row[4], class_names[int(row[5])]), x1, int(b[1] - ten))] = col
+            text = class_names[int(row[5])] if labels == "name" else label_text(row[4], class_names[int(row[5])])
+            oy = y1 if text_dy == 0 else int(b[1] + (np.float64(text_dy) if f64 else np.float32(text_dy)))
+            frame[text_mask(h, w, text, x1, oy, font_scale, text_thickness)] = col
     return frame
+
+
+def plot_colors(num_classes):
+    """The per-class colour table of plot_boxes_cv2's get_color (yolov5_postprocess.py:130-161): (red, green, blue) per class id."""
+    import math
+    colors = np.array([[1, 0, 1], [0, 0, 1], [0, 1, 1], [0, 1, 0], [1, 1, 0], [1, 0, 0]], dtype=np.float32)
+
+    def get_color(c, x, max_val):
+        ratio = float(x) / max_val * 5
+        i, j = int(math.floor(ratio)), int(math.ceil(ratio))
+        ratio = ratio - i
+        return int(((1 - ratio) * colors[i][c] + ratio * colors[j][c]) * 255)
+    out = []
+    for cls_id in range(num_classes):
+        offset = cls_id * 123457 % num_classes
+        out.append((get_color(2, offset, num_classes), get_color(1, offset, num_classes), get_color(0, offset, num_classes)))
+    return out

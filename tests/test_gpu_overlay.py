@@ -153,3 +153,48 @@ def test_argument_errors(engine):
         engine.draw_detections(f, d, None, ["n%d" % i for i in range(200)], GREEN, [8, 8])
     with pytest.raises(TypeError):
         engine.draw_detections(f.float(), d, None, NAMES, GREEN, [8, 8])
+
+
+def test_plot_boxes_cv2_reference_golden(engine):
+    """Frames annotated by the unmodified Yolov5postprocess.plot_boxes_cv2 (golden_plot_boxes): per-class colours, class
+    names at scale 1.2 / thickness 1, rectangles thickness 1, boxes and labels cut by every frame edge — through the
+    drop-in method and its two free-function twins."""
+    from triton_client_b200.clients import Yolov5client
+    from triton_client_b200.clients import wire
+    g = golden("plot_boxes")
+    names = [str(v) for v in g["names"]]
+    mode = 1 if int(str(g["numpy_version"]).split(".")[0]) < 2 else 2
+    post = Yolov5client(engine=engine).get_postprocess()
+    for k in range(2):
+        img, boxes, cls = g[f"img{k}"], g[f"boxes{k}"], g[f"cls{k}"]
+        det = np.concatenate([boxes[:, :4], boxes[:, 5:6], cls[:, None].astype(np.float32)], 1).astype(np.float64)
+        got = _gpu_draw(engine, img[None], [det], names, overlay.plot_colors(len(names)), (1, 1), thickness=1, labels="name", math_mode=mode,
+                        normalized=True, per_class_color=True, font_scale=1.2, text_thickness=1, text_dy=0)[0]
+        assert np.array_equal(got, g[f"out{k}"]), int((got != g[f"out{k}"]).any(-1).sum())
+        if (int(np.__version__.split(".")[0]) < 2) == (mode == 1):     # the drop-in follows the running numpy like the reference does
+            rows = [[b[0], b[1], b[2], b[3], b[4], b[5], np.int64(ci)] for b, ci in zip(boxes, cls)]
+            before = img.copy()
+            out = post.plot_boxes_cv2(img, rows, class_names=names)
+            assert np.array_equal(out, g[f"out{k}"]) and np.array_equal(img, before)
+            wire._engine = engine
+            from triton_client_b200.tools import utils as tu
+            from triton_client_b200.utils import postprocess as up
+            assert np.array_equal(up.plot_boxes_cv2(img, rows, class_names=names), out) and np.array_equal(tu.plot_boxes_cv2(img, rows, class_names=names), out)
+            plain = post.plot_boxes_cv2(img, [r[:4] for r in rows])            # no class names: red rectangles only
+            want = overlay.draw_detections(img.copy(), det, names, (255, 0, 0), None, thickness=1, labels=False, f64=(mode == 1), normalized=True)
+            assert np.array_equal(plain, want)
+
+
+@pytest.mark.parametrize("scale,thick,dy", [(0.5, 2, -10), (1.2, 1, 0), (0.8, 3, 5), (2.0, 1, -3), (0.35, 1, 0), (1.0, 2, -20)])
+def test_text_at_any_scale_and_thickness_matches_oracle(engine, scale, thick, dy):
+    """Stroke-level labels: any font scale / thickness, many of them cut by the frame edge."""
+    rng = np.random.default_rng(int(scale * 100) + thick)
+    h, w, size = 120, 200, 100
+    frames = np.stack([synth.image_noise(h, w, 70 + i) for i in range(2)])
+    names = ["crop", "weed", "traffic light", "Quxz@gp|", "~{}[]#%&"]
+    dets = [_random_det(rng, n, size, len(names), spill=40.0) for n in (14, 9)]
+    kw = dict(font_scale=scale, text_thickness=thick, text_dy=dy)
+    got = _gpu_draw(engine, frames, dets, names, (9, 200, 77), [size, size], thickness=1, labels=True, math_mode=2, **kw)
+    for i in range(2):
+        want = overlay.draw_detections(frames[i].copy(), dets[i], names, (9, 200, 77), [size, size], 1, True, f64=False, **kw)
+        assert np.array_equal(got[i], want), f"frame {i}: {(got[i] != want).any(-1).sum()} pixels differ"

@@ -78,7 +78,8 @@ SIGNATURES = {
     "tcb_scale_boxes": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "tcb_draw_detections_workspace": (c_size_t, [c_int, c_int]),
     "tcb_draw_detections": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_ll, c_ll, c_void_p, c_void_p, c_int,
-                                    c_int, c_int, c_int, c_int, ctypes.c_char_p, c_int, ctypes.c_char_p, c_int, c_int, c_int, c_void_p]),
+                                    c_int, c_int, c_int, c_int, ctypes.c_char_p, c_int, ctypes.c_char_p, c_int, c_int, c_int, c_double, c_int,
+                                    c_int, c_void_p]),
     "tcb_pointcloud2_unpack_workspace": (c_size_t, [c_int, c_int]),
     "tcb_pointcloud2_unpack": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_ll, c_int, P(c_int), P(c_int), c_int, c_int,
                                        c_void_p, c_void_p, c_void_p]),

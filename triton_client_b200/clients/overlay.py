@@ -76,3 +76,55 @@ class Overlay:
         frame = torch.from_numpy(img).to(dev)
         self.annotate_device(frame, det.to(dev).unsqueeze(0), None)
         return frame.cpu().numpy()
+
+
+def _plot_colors(num_classes):
+    """plot_boxes_cv2's get_color table (clients/postprocess/yolov5_postprocess.py:130-161): (red, green, blue) per class id."""
+    import math
+    colors = np.array([[1, 0, 1], [0, 0, 1], [0, 1, 1], [0, 1, 0], [1, 1, 0], [1, 0, 0]], dtype=np.float32)
+
+    def get_color(c, x, max_val):
+        ratio = float(x) / max_val * 5
+        i, j = int(math.floor(ratio)), int(math.ceil(ratio))
+        ratio = ratio - i
+        return int(((1 - ratio) * colors[i][c] + ratio * colors[j][c]) * 255)
+    table = []
+    for cls_id in range(num_classes):
+        offset = cls_id * 123457 % num_classes
+        table.append((get_color(2, offset, num_classes), get_color(1, offset, num_classes), get_color(0, offset, num_classes)))
+    return table
+
+
+def plot_boxes_cv2(img, boxes, savename=None, class_names=None, color=None, engine=None):
+    """Yolov5postprocess.plot_boxes_cv2 (clients/postprocess/yolov5_postprocess.py:127-169; twins tools/utils.py:99 and
+    utils/postprocess.py:324) on the GPU: `boxes` rows hold normalised x1, y1, x2, y2 and, when they have 7 entries and
+    class_names is given, cls_conf at [5] and cls_id at [6]; every box is drawn with cv2.rectangle(thickness 1) in its
+    class's get_color colour (or `color`, or red), labelled with cv2.putText(class name, (x1, y1), FONT_HERSHEY_SIMPLEX,
+    1.2, rgb, 1). Returns the annotated copy (the input is not modified); `savename` writes it with cv2.imwrite like the
+    reference. Pixels are those OpenCV paints."""
+    eng = engine or wire.default_engine()
+    img = np.ascontiguousarray(img)
+    out = torch.from_numpy(img.copy()).to(eng.device)
+    rows = [list(b) for b in boxes]
+    if rows:
+        labelled = bool(class_names) and all(len(b) >= 7 for b in rows)
+        det = np.zeros((len(rows), 6), np.float64)
+        for k, b in enumerate(rows):
+            det[k, :4] = [float(np.float32(v)) for v in b[:4]]
+            if labelled:
+                det[k, 4], det[k, 5] = float(b[5]), int(b[6])
+                print('%s: %f' % (class_names[int(b[6])], b[5]))      # the reference prints every labelled box (:155)
+        if labelled:
+            names = list(class_names)
+            table = [tuple(int(v) for v in color)] * len(names) if color else _plot_colors(len(names))
+            eng.draw_detections(out, torch.from_numpy(det).to(eng.device).unsqueeze(0), None, names, table, (1, 1), thickness=1, labels="name",
+                                math_mode=2 if _numpy2() else 1, normalized=True, per_class_color=True, font_scale=1.2, text_thickness=1, text_dy=0)
+        else:
+            eng.draw_detections(out, torch.from_numpy(det).to(eng.device).unsqueeze(0), None, [""], tuple(int(v) for v in color) if color else (255, 0, 0),
+                                (1, 1), thickness=1, labels=False, math_mode=2 if _numpy2() else 1, normalized=True)
+    res = out.cpu().numpy()
+    if savename:
+        import cv2
+        print("save plot results to %s" % savename)
+        cv2.imwrite(savename, res)
+    return res

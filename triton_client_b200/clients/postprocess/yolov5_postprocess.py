@@ -129,3 +129,9 @@ class Yolov5postprocess(Postprocess):
         if labels and any(len(l) for l in labels):  # :64-71 builds torch tensors from a numpy array's .device
             raise AttributeError("'numpy.ndarray' object has no attribute 'device'")
         return out, both[0]
+
+    def plot_boxes_cv2(self, img, boxes, savename=None, class_names=None, color=None):
+        """clients/postprocess/yolov5_postprocess.py:127-169, drawn on the GPU with OpenCV's own raster rules
+        (clients/overlay.py::plot_boxes_cv2): normalised boxes, per-class colours, 1.2-scale class-name labels."""
+        from ..overlay import plot_boxes_cv2
+        return plot_boxes_cv2(img, boxes, savename, class_names, color, engine=self.engine)

@@ -7,34 +7,36 @@
 // and _scale_box_array (communicator/evaluate_inference.py:237-256) — so the detections never leave the device
 // between NMS and the annotated frame.
 //
-// Two kernels: (1) one thread per detection scales the box, truncates to pixel coordinates like Python's int(),
-// formats the label text and lays out its glyphs; (2) one CTA per 128x16 pixel tile lists the detections that touch
-// the tile (in order) and paints them in order, last writer wins like successive cv2 calls. A tile nothing touches
-// reads the item boxes and exits without touching the frame.
+// Two kernels: (1) one thread per detection scales the box, truncates to pixel coordinates like Python's int() and
+// formats the label text; (2) one CTA per frame walks the frame's detections in order — like the reference's successive
+// cv2 calls, the last writer wins — and for each one all threads draw its rectangle, then its label, stroke by stroke,
+// straight into the frame. Frames nothing is detected in are not touched.
 //
-// Raster rules (OpenCV is the reference's dependency, not in its tree; rules measured from it, see oracle/overlay.py):
-// thickness 1 = the rectangle outline; thickness 2 = the outline grown by its 4-neighbourhood; glyphs from the
-// atlas generated by gen_font_atlas.py (exact for labels inside the frame).
+// Raster rules: OpenCV's own (it is the reference's dependency, not in its tree), restated in oracle/cvdraw.py and pinned
+// there against cv2 itself: cv2.rectangle thickness 1 = the outline, thickness 2 = the outline grown by its
+// 4-neighbourhood; cv2.putText = FONT_HERSHEY_SIMPLEX strokes (font_strokes.inc, measured against cv2.putText glyph by
+// glyph by oracle/gen_font_strokes.py) placed with putText's 16.16 pen arithmetic and drawn by ThickLine: thin strokes round
+// their endpoints to pixels, clip them to the frame (clipLine, in double) and walk LineIterator's Bresenham; thick
+// strokes fill a quad (FillConvexPoly: Line2 outline + edge-stepped spans) and a disc at the polyline's vertices.
+// Any scale, any thickness, labels cut by the frame edge included.
 #include "common.cuh"
 
 namespace {
 
-#define TCB_ATLAS_DECL static __device__ const
-#include "font_atlas.inc"
+#include "font_strokes.inc"
 
 constexpr int MAXC = 64;              // label characters kept (the rest is dropped)
 constexpr int NAME_BYTES = 2560, MAX_CLASSES = 128;
-constexpr int TILE_W = 128, TILE_H = 16, DRAW_T = 256;
-constexpr int ROWS_PER_THREAD = TILE_W * TILE_H / DRAW_T;   // 8
+constexpr int DRAW_T = 256;
+constexpr int XY_SHIFT = 16;
+constexpr long long XY_ONE = 1ll << XY_SHIFT, XY_HALF = XY_ONE >> 1;
 
 struct __align__(16) DrawItem {
     int xa, ya, xb, yb;               // rectangle corners, ordered
     int ox, oy;                       // text origin
-    int text_w;                       // glyph cells end at ox + text_w
-    int nchar;
+    int nchar, pad;
     unsigned char rgb[4];
-    unsigned char glyph[MAXC];        // atlas index (ASCII - 32)
-    unsigned short pen2[MAXC];        // pen position of each glyph in half pixels from ox
+    unsigned char text[MAXC];         // printable ASCII - 32
 };
 
 struct DrawParams {
@@ -42,6 +44,7 @@ struct DrawParams {
     long long row_stride, frame_stride;
     int orig_h, orig_w, in0, in1;     // _scale_boxes: x *= orig_w / input_size[0], y = y * orig_h / input_size[1]
     int normalized, math_mode, thickness, labels, per_class_color, num_classes;
+    int text_thickness, text_dy, hscale;   // putText: thickness, origin = (x1, y1 + text_dy), hscale = cvRound(fontScale * 65536)
     unsigned char color[4];
     unsigned char class_color[MAX_CLASSES * 3];
     unsigned short name_off[MAX_CLASSES + 1];
@@ -131,137 +134,304 @@ __global__ void __launch_bounds__(128) draw_items_kernel(const DrawParams p, con
     const int x1 = py_int(o[0]), y1 = py_int(o[1]), x2 = py_int(o[2]), y2 = py_int(o[3]);
     it.xa = min(x1, x2); it.xb = max(x1, x2); it.ya = min(y1, y2); it.yb = max(y1, y2);
     it.ox = x1;
-    it.oy = p.math_mode == 2 ? py_int((double)((float)o[1] - 10.0f)) : py_int(o[1] - 10.0);
+    // ros_inference.py:165 int(box[1] - 10): the subtraction happens before the truncation, in the box's arithmetic
+    it.oy = p.text_dy == 0 ? y1 : (p.math_mode == 2 ? py_int((double)((float)o[1] + (float)p.text_dy)) : py_int(o[1] + (double)p.text_dy));
     const int cls = py_int(d[5]);
     const bool cls_ok = cls >= 0 && cls < p.num_classes;
     const unsigned char* col = (p.per_class_color && cls_ok) ? p.class_color + 3 * cls : p.color;
     it.rgb[0] = col[0]; it.rgb[1] = col[1]; it.rgb[2] = col[2]; it.rgb[3] = 0;
-    it.nchar = 0; it.text_w = 0;
+    it.nchar = 0; it.pad = 0;
     if (p.labels) {
         char text[MAXC];
-        int len = format_2f(d[4], text, MAXC);
-        if (len < MAXC) text[len++] = ' ';
-        if (cls_ok)
+        int len = 0;
+        if (p.labels == 1) {                       // '{:.2f} {}'.format(conf, name)  (ros_inference.py:164)
+            len = format_2f(d[4], text, MAXC);
+            if (len < MAXC) text[len++] = ' ';
+        }
+        if (cls_ok)                                // labels == 2: the class name alone (plot_boxes_cv2, yolov5_postprocess.py:164)
             for (int k = p.name_off[cls]; k < p.name_off[cls + 1] && len < MAXC; k++) text[len++] = p.names[k];
-        int pen2 = 0;
         for (int k = 0; k < len; k++) {
             int g = (int)(unsigned char)text[k] - 32;
             if (g < 0 || g >= 95) g = '?' - 32;
-            it.glyph[k] = (unsigned char)g;
-            it.pen2[k] = (unsigned short)pen2;
-            pen2 += kGlyphAdvance2[g];
+            it.text[k] = (unsigned char)g;
         }
         it.nchar = len;
-        it.text_w = len ? (it.pen2[len - 1] >> 1) + TCB_GLYPH_W : 0;
     }
     items[(long long)f * p.max_det + i] = it;
 }
 
-// Outline coverage (same set as cv2.rectangle, see oracle/overlay.py): thickness 1 = the outline; thickness 2 = the
-// band one pixel either side of it without its four outermost corners. draw_tiles_kernel evaluates it per column as
-// row intervals.
-struct TileItem { int xa, ya, xb, yb, ox, oy, text_w, idx; unsigned rgb; };
+// ---------------------------------------------------------------------------------------------------------------------
+// OpenCV's rasterisation rules (drawing.cpp), as restated and pinned in oracle/cvdraw.py
+// ---------------------------------------------------------------------------------------------------------------------
+struct Canvas { unsigned char* px; long long row_stride; int w, h; unsigned char r, g, b; };
+__device__ __forceinline__ void put_px(const Canvas& c, int x, int y) {
+    if (x >= 0 && x < c.w && y >= 0 && y < c.h) { unsigned char* q = c.px + (long long)y * c.row_stride + 3ll * x; q[0] = c.r; q[1] = c.g; q[2] = c.b; }
+}
+__device__ __forceinline__ void hline(const Canvas& c, int y, int xa, int xb) {
+    if (y < 0 || y >= c.h) return;
+    xa = max(xa, 0); xb = min(xb, c.w - 1);
+    for (int x = xa; x <= xb; x++) { unsigned char* q = c.px + (long long)y * c.row_stride + 3ll * x; q[0] = c.r; q[1] = c.g; q[2] = c.b; }
+}
 
-__global__ void __launch_bounds__(DRAW_T) draw_tiles_kernel(const DrawParams p, const int* __restrict__ count, const DrawItem* __restrict__ items,
-                                                            unsigned char* __restrict__ frames) {
-    pdl_wait();
-    __shared__ TileItem list[DRAW_T];
-    __shared__ int warp_cnt[DRAW_T / 32];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int f = blockIdx.z;
-    const int tx0 = blockIdx.x * TILE_W, ty0 = blockIdx.y * TILE_H;
-    const int tx1 = min(tx0 + TILE_W, p.w) - 1, ty1 = min(ty0 + TILE_H, p.h) - 1;
-    const int n = min(count ? count[f] : p.max_det, p.max_det);
-    const DrawItem* fi = items + (long long)f * p.max_det;
-    const int grow = p.thickness == 2 ? 1 : 0;
-    const int px = tx0 + (tid & (TILE_W - 1)), py0 = ty0 + (tid >> 7);   // rows py0, py0+2, ...
-    unsigned hit[ROWS_PER_THREAD];
-#pragma unroll
-    for (int j = 0; j < ROWS_PER_THREAD; j++) hit[j] = 0xffffffffu;
-    bool any = false;
-    for (int base = 0; base < n; base += DRAW_T) {
-        const int i = base + tid;
-        bool touch = false;
-        TileItem t;
-        if (i < n) {
-            const int4 r = *reinterpret_cast<const int4*>(&fi[i].xa);
-            const int4 q = *reinterpret_cast<const int4*>(&fi[i].ox);   // ox, oy, text_w, nchar
-            t.xa = r.x; t.ya = r.y; t.xb = r.z; t.yb = r.w; t.ox = q.x; t.oy = q.y; t.text_w = q.z; t.idx = i;
-            t.rgb = *reinterpret_cast<const unsigned*>(fi[i].rgb);
-            const bool in_outer = !(tx1 < t.xa - grow || tx0 > t.xb + grow || ty1 < t.ya - grow || ty0 > t.yb + grow);
-            const int hole = grow + 1;   // tile strictly inside the outline's hole: nothing to paint
-            const bool in_hole = tx0 >= t.xa + hole && tx1 <= t.xb - hole && ty0 >= t.ya + hole && ty1 <= t.yb - hole;
-            const bool in_text = q.w > 0 && !(tx1 < t.ox || tx0 >= t.ox + t.text_w || ty1 < t.oy + TCB_GLYPH_Y0 || ty0 >= t.oy + TCB_GLYPH_Y0 + TCB_GLYPH_H);
-            if (!in_text) t.text_w = 0;
-            touch = (in_outer && !in_hole) || in_text;
+// clipLine(Size2l, Point2l&, Point2l&): integer endpoints, the cuts in double, truncated
+__device__ bool clip_line(long long width, long long height, long long& x1, long long& y1, long long& x2, long long& y2) {
+    const long long right = width - 1, bottom = height - 1;
+    if (width <= 0 || height <= 0) return false;
+    int c1 = (x1 < 0) + (x1 > right) * 2 + (y1 < 0) * 4 + (y1 > bottom) * 8;
+    int c2 = (x2 < 0) + (x2 > right) * 2 + (y2 < 0) * 4 + (y2 > bottom) * 8;
+    if ((c1 & c2) == 0 && (c1 | c2) != 0) {
+        long long a;
+        if (c1 & 12) {
+            a = c1 < 8 ? 0 : bottom;
+            x1 += (long long)((double)(a - y1) * (double)(x2 - x1) / (double)(y2 - y1));
+            y1 = a;
+            c1 = (x1 < 0) + (x1 > right) * 2;
         }
-        const unsigned bal = __ballot_sync(0xffffffffu, touch);
-        if (lane == 0) warp_cnt[warp] = __popc(bal);
-        __syncthreads();
-        int before = 0, total = 0;
-#pragma unroll
-        for (int k = 0; k < DRAW_T / 32; k++) { const int c = warp_cnt[k]; if (k < warp) before += c; total += c; }
-        if (touch) list[before + __popc(bal & ((1u << lane) - 1))] = t;
-        __syncthreads();
-        if (total && px <= tx1) {
-            any = true;
-            for (int k = 0; k < total; k++) {
-                const TileItem t2 = list[k];
-                // The rows of this thread's column that the outline covers are at most two intervals [r0,r1], [r2,r3]
-                // (same set as rect_covers, worked out once per item instead of once per pixel):
-                //   outside the grown box: none; its outermost columns (thickness 2): [ya, yb] (no corners);
-                //   the columns of the vertical edges: [ya-g, yb+g]; columns in between: the two horizontal bands.
-                int r0 = 1, r1 = 0, r2 = 1, r3 = 0;
-                if (px >= t2.xa - grow && px <= t2.xb + grow) {
-                    if (grow && (px == t2.xa - 1 || px == t2.xb + 1)) { r0 = t2.ya; r1 = t2.yb; }
-                    else if (px >= t2.xa + grow + 1 && px <= t2.xb - grow - 1 && t2.ya + grow + 1 <= t2.yb - grow - 1) {
-                        r0 = t2.ya - grow; r1 = t2.ya + grow; r2 = t2.yb - grow; r3 = t2.yb + grow;
-                    } else { r0 = t2.ya - grow; r1 = t2.yb + grow; }
-                }
-                const int ylast = py0 + 2 * (ROWS_PER_THREAD - 1);
-                const bool rect_here = (r0 <= ylast && r1 >= py0) || (r2 <= ylast && r3 >= py0);
-                const int gx = px - t2.ox;
-                const bool text_here = t2.text_w && gx >= 0 && gx < t2.text_w;
-                if (!rect_here && !text_here) continue;
-                // glyph cells over this column (the same for all of the thread's rows): the pen advances at least 4 pixels
-                // per character, so at most four 16-wide cells overlap; each is kept as (first atlas row << 5 | bit)
-                unsigned cell[4];
-                int ncell = 0;
-                if (text_here) {
-                    const DrawItem& it = fi[t2.idx];
-                    const int nchar = it.nchar;
-                    for (int ch = 0; ch < nchar; ch++) {
-                        const int pen2 = it.pen2[ch];
-                        const int dx = gx - (pen2 >> 1);
-                        if (dx < 0) break;                           // pens only move right
-                        if (dx < TCB_GLYPH_W && ncell < 4) cell[ncell++] = ((unsigned)(((int)it.glyph[ch] * 2 + (pen2 & 1)) * TCB_GLYPH_H) << 5) | (unsigned)dx;
+        if (c2 & 12) {
+            a = c2 < 8 ? 0 : bottom;
+            x2 += (long long)((double)(a - y2) * (double)(x2 - x1) / (double)(y2 - y1));
+            y2 = a;
+            c2 = (x2 < 0) + (x2 > right) * 2;
+        }
+        if ((c1 & c2) == 0 && (c1 | c2) != 0) {
+            if (c1) {
+                a = c1 == 1 ? 0 : right;
+                y1 += (long long)((double)(a - x1) * (double)(y2 - y1) / (double)(x2 - x1));
+                x1 = a;
+                c1 = 0;
+            }
+            if (c2) {
+                a = c2 == 1 ? 0 : right;
+                y2 += (long long)((double)(a - x2) * (double)(y2 - y1) / (double)(x2 - x1));
+                x2 = a;
+                c2 = 0;
+            }
+        }
+    }
+    return (c1 | c2) == 0;
+}
+
+// Line2: endpoints in 16.16 fixed point (the outline FillConvexPoly draws around its spans)
+__device__ void line2(const Canvas& c, long long x1, long long y1, long long x2, long long y2) {
+    if (!clip_line((long long)c.w << XY_SHIFT, (long long)c.h << XY_SHIFT, x1, y1, x2, y2)) return;
+    long long dx = x2 - x1, dy = y2 - y1;
+    const long long ax = dx < 0 ? -dx : dx, ay = dy < 0 ? -dy : dy;
+    if (ax > ay) {
+        if (dx < 0) { dy = -dy; long long t = x1; x1 = x2; x2 = t; t = y1; y1 = y2; y2 = t; }
+        const long long y_step = (dy << XY_SHIFT) / (ax | 1);       // C division: towards zero
+        int ecount = (int)((x2 - x1) >> XY_SHIFT);
+        x1 += XY_HALF; y1 += XY_HALF;
+        put_px(c, (int)((x2 + XY_HALF) >> XY_SHIFT), (int)((y2 + XY_HALF) >> XY_SHIFT));
+        int x = (int)(x1 >> XY_SHIFT);
+        while (ecount >= 0) { put_px(c, x, (int)(y1 >> XY_SHIFT)); x++; y1 += y_step; ecount--; }
+    } else {
+        if (dy < 0) { dx = -dx; long long t = x1; x1 = x2; x2 = t; t = y1; y1 = y2; y2 = t; }
+        const long long x_step = (dx << XY_SHIFT) / (ay | 1);
+        int ecount = (int)((y2 - y1) >> XY_SHIFT);
+        x1 += XY_HALF; y1 += XY_HALF;
+        put_px(c, (int)((x2 + XY_HALF) >> XY_SHIFT), (int)((y2 + XY_HALF) >> XY_SHIFT));
+        int y = (int)(y1 >> XY_SHIFT);
+        while (ecount >= 0) { put_px(c, (int)(x1 >> XY_SHIFT), y); x1 += x_step; y++; ecount--; }
+    }
+}
+
+// Line(img, pt1, pt2, color, 8): integer endpoints, clipped to the frame, LineIterator's 8-connected Bresenham from the left end
+__device__ void line_int(const Canvas& c, long long x1, long long y1, long long x2, long long y2) {
+    if (!clip_line(c.w, c.h, x1, y1, x2, y2)) return;
+    int dx = (int)(x2 - x1), dy = (int)(y2 - y1);
+    if (dx < 0) { dx = -dx; dy = -dy; x1 = x2; y1 = y2; }
+    const int sy = dy < 0 ? -1 : 1;
+    dy = dy < 0 ? -dy : dy;
+    const bool steep = dy > dx;
+    if (steep) { const int t = dx; dx = dy; dy = t; }
+    int err = dx - (dy + dy);
+    const int plus = dx + dx, minus = -(dy + dy);
+    int x = (int)x1, y = (int)y1;
+    for (int k = 0; k <= dx; k++) {
+        put_px(c, x, y);
+        const bool m = err < 0;
+        err += minus + (m ? plus : 0);
+        if (steep) { y += sy; if (m) x++; }
+        else { x++; if (m) y += sy; }
+    }
+}
+
+// FillConvexPoly(img, v, 4, color, LINE_8, XY_SHIFT)
+__device__ void fill_quad(const Canvas& c, const long long (&vx)[4], const long long (&vy)[4]) {
+    const int n = 4;
+    long long xmin = vx[0], xmax = vx[0], ymin = vy[0], ymax = vy[0];
+    int imin = 0;
+    {
+        long long px = vx[n - 1], py = vy[n - 1];
+        for (int i = 0; i < n; i++) {
+            if (vy[i] < ymin) { ymin = vy[i]; imin = i; }
+            ymax = max(ymax, vy[i]); xmax = max(xmax, vx[i]); xmin = min(xmin, vx[i]);
+            line2(c, px, py, vx[i], vy[i]);
+            px = vx[i]; py = vy[i];
+        }
+    }
+    xmin = (xmin + XY_HALF) >> XY_SHIFT; xmax = (xmax + XY_HALF) >> XY_SHIFT;
+    ymin = (ymin + XY_HALF) >> XY_SHIFT; ymax = (ymax + XY_HALF) >> XY_SHIFT;
+    if ((int)xmax < 0 || (int)ymax < 0 || (int)xmin >= c.w || (int)ymin >= c.h) return;
+    ymax = min(ymax, (long long)c.h - 1);
+    int edges = n;
+    int e_idx[2] = {imin, imin}, e_di[2] = {1, n - 1}, e_ye[2] = {(int)ymin, (int)ymin};
+    long long e_x[2] = {-XY_ONE, -XY_ONE}, e_dx[2] = {0, 0};
+    int y = (int)ymin;
+    do {
+        for (int i = 0; i < 2; i++) {
+            if (y >= e_ye[i]) {
+                int idx0 = e_idx[i];
+                const int di = e_di[i];
+                int idx = idx0 + di;
+                if (idx >= n) idx -= n;
+                for (; edges-- > 0;) {
+                    const int ty = (int)((vy[idx] + XY_HALF) >> XY_SHIFT);
+                    if (ty > y) {
+                        const long long xs = vx[idx0], xe = vx[idx];
+                        e_ye[i] = ty;
+                        e_dx[i] = ((xe - xs) * 2 + (ty - y)) / (2 * (ty - y));
+                        e_x[i] = xs;
+                        e_idx[i] = idx;
+                        break;
                     }
-                }
-#pragma unroll
-                for (int j = 0; j < ROWS_PER_THREAD; j++) {
-                    const int y = py0 + 2 * j;
-                    bool c = (y >= r0 && y <= r1) || (y >= r2 && y <= r3);
-                    const int gy = y - (t2.oy + TCB_GLYPH_Y0);
-                    if (!c && ncell && gy >= 0 && gy < TCB_GLYPH_H) {
-#pragma unroll
-                        for (int q = 0; q < 4; q++)
-                            if (q < ncell && ((kGlyphRows[(cell[q] >> 5) + gy] >> (cell[q] & 31u)) & 1)) c = true;
-                    }
-                    if (c) hit[j] = t2.rgb;
+                    idx0 = idx;
+                    idx += di;
+                    if (idx >= n) idx -= n;
                 }
             }
         }
-        __syncthreads();
-    }
-    if (!any) return;
-    unsigned char* fp = frames + (long long)f * p.frame_stride;
-#pragma unroll
-    for (int j = 0; j < ROWS_PER_THREAD; j++) {
-        const int y = py0 + 2 * j;
-        if (hit[j] != 0xffffffffu && y <= ty1) {
-            unsigned char* q = fp + (long long)y * p.row_stride + 3ll * px;
-            q[0] = (unsigned char)(hit[j] & 255u); q[1] = (unsigned char)((hit[j] >> 8) & 255u); q[2] = (unsigned char)((hit[j] >> 16) & 255u);
+        if (edges < 0) break;
+        if (y >= 0) {
+            const int left = e_x[0] > e_x[1] ? 1 : 0, right = 1 - left;
+            const int xx1 = (int)((e_x[left] + XY_HALF) >> XY_SHIFT), xx2 = (int)((e_x[right] + XY_HALF) >> XY_SHIFT);
+            if (xx2 >= 0 && xx1 < c.w) hline(c, y, xx1, xx2);
         }
+        e_x[0] += e_dx[0];
+        e_x[1] += e_dx[1];
+    } while (++y <= (int)ymax);
+}
+
+// Circle(img, center, radius, color, fill = 1)
+__device__ void disc(const Canvas& c, int cx, int cy, int radius) {
+    int err = 0, dx = radius, dy = 0, plus = 1, minus = (radius << 1) - 1;
+    while (dx >= dy) {
+        hline(c, cy - dy, cx - dx, cx + dx);
+        hline(c, cy + dy, cx - dx, cx + dx);
+        hline(c, cy - dx, cx - dy, cx + dy);
+        hline(c, cy + dx, cx - dy, cx + dy);
+        dy++;
+        err += plus;
+        plus += 2;
+        const int mask = (err <= 0) - 1;
+        err -= minus & mask;
+        dx += mask;
+        minus -= mask & 2;
+    }
+}
+
+// ThickLine(img, p0, p1, color, thickness, LINE_8, flags, XY_SHIFT): flags bit 0 / 1 = a disc at p0 / p1
+__device__ void thick_line(const Canvas& c, long long x0, long long y0, long long x1, long long y1, int thickness, int flags) {
+    if (thickness <= 1) {
+        line_int(c, (x0 + XY_HALF) >> XY_SHIFT, (y0 + XY_HALF) >> XY_SHIFT, (x1 + XY_HALF) >> XY_SHIFT, (y1 + XY_HALF) >> XY_SHIFT);
+        return;
+    }
+    const double inv = 1.0 / (double)XY_ONE;
+    const double dx = (double)(x0 - x1) * inv, dy = (double)(y1 - y0) * inv;
+    double r = dx * dx + dy * dy;
+    const int odd = thickness & 1;
+    const long long t = (long long)thickness << (XY_SHIFT - 1);
+    if (fabs(r) > 2.220446049250313e-16) {
+        r = ((double)t + (double)odd * (double)XY_ONE * 0.5) / sqrt(r);
+        const long long dpx = (long long)rint(dy * r), dpy = (long long)rint(dx * r);      // cvRound
+        const long long vx[4] = {x0 + dpx, x0 - dpx, x1 - dpx, x1 + dpx}, vy[4] = {y0 + dpy, y0 - dpy, y1 - dpy, y1 + dpy};
+        fill_quad(c, vx, vy);
+    }
+    const int radius = (int)((t + XY_HALF) >> XY_SHIFT);
+    if (flags & 1) disc(c, (int)((x0 + XY_HALF) >> XY_SHIFT), (int)((y0 + XY_HALF) >> XY_SHIFT), radius);
+    if (flags & 2) disc(c, (int)((x1 + XY_HALF) >> XY_SHIFT), (int)((y1 + XY_HALF) >> XY_SHIFT), radius);
+}
+
+// segments of glyph g (ASCII - 32): number, and the k-th one (endpoints in Hershey units, is it the first of its polyline)
+__device__ __forceinline__ int glyph_segments(int g) {
+    int n = 0;
+    for (int k = c_hf_off[g] + 2; k < c_hf_off[g + 1];) { const int m = c_hf_data[k]; n += m > 1 ? m - 1 : 0; k += 1 + 2 * m; }
+    return n;
+}
+__device__ __forceinline__ void glyph_segment(int g, int j, int& xa, int& ya, int& xb, int& yb, bool& first) {
+    for (int k = c_hf_off[g] + 2; k < c_hf_off[g + 1];) {
+        const int m = c_hf_data[k], ns = m > 1 ? m - 1 : 0;
+        if (j < ns) {
+            const signed char* q = c_hf_data + k + 1 + 2 * j;
+            xa = q[0]; ya = q[1]; xb = q[2]; yb = q[3]; first = j == 0;
+            return;
+        }
+        j -= ns;
+        k += 1 + 2 * m;
+    }
+}
+
+// One CTA per frame. Detections are drawn in order (later ones paint over earlier ones, as the reference's loop does);
+// inside a detection the rectangle comes first, then the label; all pixels of a detection have one colour, so the
+// threads that draw it need no order among themselves.
+__global__ void __launch_bounds__(DRAW_T) draw_frames_kernel(const DrawParams p, const int* __restrict__ count, const DrawItem* __restrict__ items,
+                                                             unsigned char* __restrict__ frames) {
+    pdl_wait();
+    __shared__ long long pen[MAXC];        // view_x of every character of the current label (16.16)
+    __shared__ int seg0[MAXC + 1];         // first segment of every character
+    const int tid = threadIdx.x, f = blockIdx.x;
+    const int n = min(count ? count[f] : p.max_det, p.max_det);
+    Canvas c;
+    c.px = frames + (long long)f * p.frame_stride; c.row_stride = p.row_stride; c.w = p.w; c.h = p.h;
+    for (int i = 0; i < n; i++) {
+        const DrawItem& it = items[(long long)f * p.max_det + i];
+        c.r = it.rgb[0]; c.g = it.rgb[1]; c.b = it.rgb[2];
+        // ---- cv2.rectangle: the outline (thickness 1), grown by its 4-neighbourhood (thickness 2) ----
+        {
+            const int xa = it.xa, xb = it.xb, ya = it.ya, yb = it.yb, grow = p.thickness == 2 ? 1 : 0;
+            // outline pixels inside the frame grown by one: top / bottom rows, then the left / right columns between them
+            const int cx0 = max(xa, -1), cx1 = min(xb, p.w), cy0 = max(ya + 1, -1), cy1 = min(yb - 1, p.h);
+            const int nrow = max(cx1 - cx0 + 1, 0), ncol = max(cy1 - cy0 + 1, 0);
+            const int total = 2 * nrow + 2 * ncol;
+            for (int k = tid; k < total; k += DRAW_T) {
+                int x, y;
+                if (k < 2 * nrow) { x = cx0 + (k >> 1); y = (k & 1) ? yb : ya; }
+                else { const int q = k - 2 * nrow; y = cy0 + (q >> 1); x = (q & 1) ? xb : xa; }
+                put_px(c, x, y);
+                if (grow) { put_px(c, x - 1, y); put_px(c, x + 1, y); put_px(c, x, y - 1); put_px(c, x, y + 1); }
+            }
+        }
+        __syncthreads();
+        // ---- cv2.putText ----
+        const int nchar = it.nchar;
+        if (nchar > 0) {
+            if (tid == 0) {                                    // putText's pen: view_x -= left * hscale; draw; view_x += right * hscale
+                long long view_x = (long long)it.ox << XY_SHIFT;
+                int s0 = 0;
+                for (int k = 0; k < nchar; k++) {
+                    const int g = it.text[k];
+                    view_x -= (long long)c_hf_data[c_hf_off[g]] * p.hscale;
+                    pen[k] = view_x;
+                    seg0[k] = s0;
+                    s0 += glyph_segments(g);
+                    view_x += (long long)c_hf_data[c_hf_off[g] + 1] * p.hscale;
+                }
+                seg0[nchar] = s0;
+            }
+            __syncthreads();
+            const long long view_y = ((long long)it.oy << XY_SHIFT) + (long long)HF_BASE_LINE * p.hscale;
+            const int total = seg0[nchar];
+            for (int sidx = tid; sidx < total; sidx += DRAW_T) {
+                int lo = 0, hi = nchar - 1;                    // the character that owns segment sidx
+                while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (seg0[mid] <= sidx) lo = mid; else hi = mid - 1; }
+                int xa, ya, xb, yb;
+                bool first;
+                glyph_segment(it.text[lo], sidx - seg0[lo], xa, ya, xb, yb, first);
+                thick_line(c, (long long)xa * p.hscale + pen[lo], (long long)ya * p.hscale + view_y, (long long)xb * p.hscale + pen[lo],
+                           (long long)yb * p.hscale + view_y, p.text_thickness, first ? 3 : 2);
+            }
+        }
+        __syncthreads();
     }
 }
 
@@ -290,13 +460,16 @@ extern "C" size_t tcb_draw_detections_workspace(int b, int max_det) {
 extern "C" int tcb_draw_detections(tcb_ctx* ctx, unsigned char* frames_dev, int b, int h, int w, long long row_stride, long long frame_stride,
                                    const double* det_dev, const int* count_dev, int max_det, int input_size0, int input_size1,
                                    int normalized, int math_mode, const char* class_names, int num_classes,
-                                   const unsigned char* colors, int per_class_color, int thickness, int labels, void* stream) {
+                                   const unsigned char* colors, int per_class_color, int thickness, int labels, double font_scale,
+                                   int text_thickness, int text_dy, void* stream) {
     TCB_CHECK_CTX(ctx);
     TCB_REQUIRE(ctx, b >= 0 && h > 0 && w > 0 && max_det >= 0, "tcb_draw_detections: bad sizes");
     TCB_REQUIRE(ctx, row_stride >= 3ll * w && (b <= 1 || frame_stride >= row_stride * h), "tcb_draw_detections: strides smaller than the frame");
     TCB_REQUIRE(ctx, input_size0 > 0 && input_size1 > 0, "tcb_draw_detections: bad model input size");
     TCB_REQUIRE(ctx, math_mode >= 0 && math_mode <= 2, "tcb_draw_detections: math_mode must be 0, 1 or 2");
     TCB_REQUIRE(ctx, thickness == 1 || thickness == 2, "tcb_draw_detections: thickness must be 1 or 2");
+    TCB_REQUIRE(ctx, labels >= 0 && labels <= 2, "tcb_draw_detections: labels must be 0 (none), 1 ('conf name') or 2 (name)");
+    TCB_REQUIRE(ctx, !labels || (font_scale > 0.0 && font_scale <= 64.0 && text_thickness >= 1 && text_thickness <= 32), "tcb_draw_detections: font scale in (0, 64], text thickness in [1, 32]");
     TCB_REQUIRE(ctx, colors != nullptr, "tcb_draw_detections: colors is null");
     TCB_REQUIRE(ctx, num_classes >= 0 && (num_classes == 0 || class_names || (!labels && !per_class_color)), "tcb_draw_detections: class names missing");
     if (num_classes > MAX_CLASSES) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_draw_detections: %d classes > compiled limit %d", num_classes, MAX_CLASSES);
@@ -307,7 +480,8 @@ extern "C" int tcb_draw_detections(tcb_ctx* ctx, unsigned char* frames_dev, int 
     memset(&p, 0, sizeof(p));
     p.h = h; p.w = w; p.max_det = max_det; p.row_stride = row_stride; p.frame_stride = frame_stride;
     p.orig_h = h; p.orig_w = w; p.in0 = input_size0; p.in1 = input_size1;
-    p.normalized = normalized ? 1 : 0; p.math_mode = math_mode; p.thickness = thickness; p.labels = labels ? 1 : 0;
+    p.normalized = normalized ? 1 : 0; p.math_mode = math_mode; p.thickness = thickness; p.labels = labels;
+    p.text_thickness = text_thickness; p.text_dy = text_dy; p.hscale = (int)nearbyint(font_scale * 65536.0);   // cvRound(fontScale * XY_ONE)
     p.per_class_color = per_class_color ? 1 : 0; p.num_classes = num_classes;
     if (per_class_color) memcpy(p.class_color, colors, (size_t)num_classes * 3);
     else memcpy(p.color, colors, 3);
@@ -328,7 +502,7 @@ extern "C" int tcb_draw_detections(tcb_ctx* ctx, unsigned char* frames_dev, int 
     cudaStream_t st = (cudaStream_t)stream;
     TCB_KLAUNCH(ctx, draw_items_kernel, dim3(tcb_div_up(max_det, 128), b), 128, 0, st, p, det_dev, count_dev, items);
     TCB_LAUNCHED(ctx);
-    TCB_KLAUNCH(ctx, draw_tiles_kernel, dim3(tcb_div_up(w, TILE_W), tcb_div_up(h, TILE_H), b), DRAW_T, 0, st, p, count_dev, items, frames_dev);
+    TCB_KLAUNCH(ctx, draw_frames_kernel, b, DRAW_T, 0, st, p, count_dev, items, frames_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }

@@ -430,9 +430,11 @@ class Engine:
         return out
 
     def draw_detections(self, frames, det, counts, class_names, color, input_size, thickness=2, labels=True, math_mode=1,
-                        normalized=False, per_class_color=False):
+                        normalized=False, per_class_color=False, font_scale=0.5, text_thickness=2, text_dy=-10):
         """The drawing loop of RosInference._callback (ros_inference.py:148-169) in place on CUDA frames
-        [b,h,w,3] (or [h,w,3]) uint8; det [b,max_det,6] float64 + counts [b] int32 as extract_boxes_device returns."""
+        [b,h,w,3] (or [h,w,3]) uint8; det [b,max_det,6] float64 + counts [b] int32 as extract_boxes_device returns.
+        labels: False / True ('{:.2f} {name}') / "name" (the class name alone, as plot_boxes_cv2 writes it); the text is
+        cv2.putText(text, (x1, int(y1 + text_dy)), FONT_HERSHEY_SIMPLEX, font_scale, color, text_thickness)."""
         _need_cuda(frames, det)
         if frames.dtype != torch.uint8 or frames.shape[-1] != 3 or frames.dim() not in (3, 4):
             raise TypeError("draw_detections: frames must be uint8 [b,h,w,3] or [h,w,3]")
@@ -446,7 +448,8 @@ class Engine:
         cols = bytes(int(v) & 255 for c in (color if per_class_color else [color]) for v in c)
         self.ctx.call("tcb_draw_detections", _ptr(f4), b, h, w, f4.stride(1), f4.stride(0) if b > 1 else h * f4.stride(1), _ptr(d),
                       _ptr(cnt) if cnt is not None else None, d.shape[1], int(input_size[0]), int(input_size[1]), int(bool(normalized)),
-                      int(math_mode), names, len(class_names), cols, int(bool(per_class_color)), int(thickness), int(bool(labels)),
+                      int(math_mode), names, len(class_names), cols, int(bool(per_class_color)), int(thickness),
+                      2 if labels == "name" else int(bool(labels)), ctypes.c_double(float(font_scale)), int(text_thickness), int(text_dy),
                       _lib.stream_ptr())
         return frames
 

@@ -76,3 +76,8 @@ def extract_boxes_triton(response):
 
 def extract_boxes_detectron(prediction):          # utils/postprocess.py:368-468
     return FCOSpostprocess().extract_boxes(prediction)
+
+
+def plot_boxes_cv2(img, boxes, savename=None, class_names=None, color=None):      # utils/postprocess.py:324-366 (= tools/utils.py:99-141)
+    from ..clients.overlay import plot_boxes_cv2 as _plot
+    return _plot(img, boxes, savename, class_names, color)
