@@ -371,67 +371,76 @@ __device__ __forceinline__ void glyph_segment(int g, int j, int& xa, int& ya, in
     }
 }
 
-// One CTA per frame. Detections are drawn in order (later ones paint over earlier ones, as the reference's loop does);
-// inside a detection the rectangle comes first, then the label; all pixels of a detection have one colour, so the
-// threads that draw it need no order among themselves.
+// One detection: the rectangle first, then the label; all its pixels have one colour, so the threads that draw it need
+// no order among themselves. pen / seg0: MAXC(+1) entries of shared memory; ends with a __syncthreads().
+__device__ void draw_one(const DrawParams& p, Canvas& c, const DrawItem& it, long long* pen, int* seg0) {
+    const int tid = threadIdx.x;
+    c.r = it.rgb[0]; c.g = it.rgb[1]; c.b = it.rgb[2];
+    // ---- cv2.rectangle: the outline (thickness 1), grown by its 4-neighbourhood (thickness 2) ----
+    {
+        const int xa = it.xa, xb = it.xb, ya = it.ya, yb = it.yb, grow = p.thickness == 2 ? 1 : 0;
+        // outline pixels inside the frame grown by one: top / bottom rows, then the left / right columns between them
+        const int cx0 = max(xa, -1), cx1 = min(xb, p.w), cy0 = max(ya + 1, -1), cy1 = min(yb - 1, p.h);
+        const int nrow = max(cx1 - cx0 + 1, 0), ncol = max(cy1 - cy0 + 1, 0);
+        const int total = 2 * nrow + 2 * ncol;
+        for (int k = tid; k < total; k += DRAW_T) {
+            int x, y;
+            if (k < 2 * nrow) { x = cx0 + (k >> 1); y = (k & 1) ? yb : ya; }
+            else { const int q = k - 2 * nrow; y = cy0 + (q >> 1); x = (q & 1) ? xb : xa; }
+            put_px(c, x, y);
+            if (grow) { put_px(c, x - 1, y); put_px(c, x + 1, y); put_px(c, x, y - 1); put_px(c, x, y + 1); }
+        }
+    }
+    __syncthreads();
+    // ---- cv2.putText ----
+    const int nchar = it.nchar;
+    if (nchar > 0) {
+        if (tid == 0) {                                    // putText's pen: view_x -= left * hscale; draw; view_x += right * hscale
+            long long view_x = (long long)it.ox << XY_SHIFT;
+            int s0 = 0;
+            for (int k = 0; k < nchar; k++) {
+                const int g = it.text[k];
+                view_x -= (long long)c_hf_data[c_hf_off[g]] * p.hscale;
+                pen[k] = view_x;
+                seg0[k] = s0;
+                s0 += glyph_segments(g);
+                view_x += (long long)c_hf_data[c_hf_off[g] + 1] * p.hscale;
+            }
+            seg0[nchar] = s0;
+        }
+        __syncthreads();
+        const long long view_y = ((long long)it.oy << XY_SHIFT) + (long long)HF_BASE_LINE * p.hscale;
+        const int total = seg0[nchar];
+        for (int sidx = tid; sidx < total; sidx += DRAW_T) {
+            int lo = 0, hi = nchar - 1;                    // the character that owns segment sidx
+            while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (seg0[mid] <= sidx) lo = mid; else hi = mid - 1; }
+            int xa, ya, xb, yb;
+            bool first;
+            glyph_segment(it.text[lo], sidx - seg0[lo], xa, ya, xb, yb, first);
+            thick_line(c, (long long)xa * p.hscale + pen[lo], (long long)ya * p.hscale + view_y, (long long)xb * p.hscale + pen[lo],
+                       (long long)yb * p.hscale + view_y, p.text_thickness, first ? 3 : 2);
+        }
+    }
+    __syncthreads();
+}
+
+// ORDERED: one CTA per frame draws its detections one after the other (later ones paint over earlier ones, as the
+// reference's loop does) — needed when detections have different colours. Otherwise every pixel any detection touches
+// ends up with the one colour whatever the order, and each detection gets a CTA of its own (grid max_det x frames).
+template <bool ORDERED>
 __global__ void __launch_bounds__(DRAW_T) draw_frames_kernel(const DrawParams p, const int* __restrict__ count, const DrawItem* __restrict__ items,
                                                              unsigned char* __restrict__ frames) {
     pdl_wait();
     __shared__ long long pen[MAXC];        // view_x of every character of the current label (16.16)
     __shared__ int seg0[MAXC + 1];         // first segment of every character
-    const int tid = threadIdx.x, f = blockIdx.x;
+    const int f = ORDERED ? blockIdx.x : blockIdx.y;
     const int n = min(count ? count[f] : p.max_det, p.max_det);
     Canvas c;
     c.px = frames + (long long)f * p.frame_stride; c.row_stride = p.row_stride; c.w = p.w; c.h = p.h;
-    for (int i = 0; i < n; i++) {
-        const DrawItem& it = items[(long long)f * p.max_det + i];
-        c.r = it.rgb[0]; c.g = it.rgb[1]; c.b = it.rgb[2];
-        // ---- cv2.rectangle: the outline (thickness 1), grown by its 4-neighbourhood (thickness 2) ----
-        {
-            const int xa = it.xa, xb = it.xb, ya = it.ya, yb = it.yb, grow = p.thickness == 2 ? 1 : 0;
-            // outline pixels inside the frame grown by one: top / bottom rows, then the left / right columns between them
-            const int cx0 = max(xa, -1), cx1 = min(xb, p.w), cy0 = max(ya + 1, -1), cy1 = min(yb - 1, p.h);
-            const int nrow = max(cx1 - cx0 + 1, 0), ncol = max(cy1 - cy0 + 1, 0);
-            const int total = 2 * nrow + 2 * ncol;
-            for (int k = tid; k < total; k += DRAW_T) {
-                int x, y;
-                if (k < 2 * nrow) { x = cx0 + (k >> 1); y = (k & 1) ? yb : ya; }
-                else { const int q = k - 2 * nrow; y = cy0 + (q >> 1); x = (q & 1) ? xb : xa; }
-                put_px(c, x, y);
-                if (grow) { put_px(c, x - 1, y); put_px(c, x + 1, y); put_px(c, x, y - 1); put_px(c, x, y + 1); }
-            }
-        }
-        __syncthreads();
-        // ---- cv2.putText ----
-        const int nchar = it.nchar;
-        if (nchar > 0) {
-            if (tid == 0) {                                    // putText's pen: view_x -= left * hscale; draw; view_x += right * hscale
-                long long view_x = (long long)it.ox << XY_SHIFT;
-                int s0 = 0;
-                for (int k = 0; k < nchar; k++) {
-                    const int g = it.text[k];
-                    view_x -= (long long)c_hf_data[c_hf_off[g]] * p.hscale;
-                    pen[k] = view_x;
-                    seg0[k] = s0;
-                    s0 += glyph_segments(g);
-                    view_x += (long long)c_hf_data[c_hf_off[g] + 1] * p.hscale;
-                }
-                seg0[nchar] = s0;
-            }
-            __syncthreads();
-            const long long view_y = ((long long)it.oy << XY_SHIFT) + (long long)HF_BASE_LINE * p.hscale;
-            const int total = seg0[nchar];
-            for (int sidx = tid; sidx < total; sidx += DRAW_T) {
-                int lo = 0, hi = nchar - 1;                    // the character that owns segment sidx
-                while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (seg0[mid] <= sidx) lo = mid; else hi = mid - 1; }
-                int xa, ya, xb, yb;
-                bool first;
-                glyph_segment(it.text[lo], sidx - seg0[lo], xa, ya, xb, yb, first);
-                thick_line(c, (long long)xa * p.hscale + pen[lo], (long long)ya * p.hscale + view_y, (long long)xb * p.hscale + pen[lo],
-                           (long long)yb * p.hscale + view_y, p.text_thickness, first ? 3 : 2);
-            }
-        }
-        __syncthreads();
+    if (ORDERED) {
+        for (int i = 0; i < n; i++) draw_one(p, c, items[(long long)f * p.max_det + i], pen, seg0);
+    } else if ((int)blockIdx.x < n) {
+        draw_one(p, c, items[(long long)f * p.max_det + blockIdx.x], pen, seg0);
     }
 }
 
@@ -502,7 +511,8 @@ extern "C" int tcb_draw_detections(tcb_ctx* ctx, unsigned char* frames_dev, int 
     cudaStream_t st = (cudaStream_t)stream;
     TCB_KLAUNCH(ctx, draw_items_kernel, dim3(tcb_div_up(max_det, 128), b), 128, 0, st, p, det_dev, count_dev, items);
     TCB_LAUNCHED(ctx);
-    TCB_KLAUNCH(ctx, draw_frames_kernel, b, DRAW_T, 0, st, p, count_dev, items, frames_dev);
+    if (per_class_color) { TCB_KLAUNCH(ctx, draw_frames_kernel<true>, b, DRAW_T, 0, st, p, count_dev, items, frames_dev); }
+    else { TCB_KLAUNCH(ctx, draw_frames_kernel<false>, dim3(max_det, b), DRAW_T, 0, st, p, count_dev, items, frames_dev); }
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }
