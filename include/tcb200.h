@@ -278,14 +278,21 @@ int tcb_dynamic_pillar(tcb_ctx* ctx, const float* pts_dev, int n, int ncol, int 
 int tcb_rotated_iou(tcb_ctx* ctx, const float* boxes_a_dev, int n, const float* boxes_b_dev, int m,
                     float* out_dev, void* stream);
 
+/* NMS_CONFIG.NMS_TYPE of the pcdet configs, looked up by name in iou3d_nms_utils (model_nms_utils.py:15):
+ * nms_gpu = rotated BEV IoU (iou3d_nms_utils.py:84-99, nms_kernel src/iou3d_nms_kernel.cu:267-311);
+ * nms_normal_gpu = axis-aligned BEV IoU, heading ignored (iou3d_nms_utils.py:102-116, iou_normal +
+ * nms_normal_kernel src/iou3d_nms_kernel.cu:314-367). Both: sort descending, bit mask, host sweep
+ * (src/iou3d_nms.cpp:90-136 / :139-187). */
+#define TCB_NMS_GPU 0
+#define TCB_NMS_NORMAL 1
+
 /* class_agnostic_nms without the score cut (OPCD/pcdet/models/model_utils/model_nms_utils.py:13-19) =
- * topk(min(pre_max, n)) by score + nms_gpu (iou3d_nms_utils.py:84-99, src/iou3d_nms.cpp:90-136,
- * nms_kernel src/iou3d_nms_kernel.cu:267-311) + [:post_max], for b independent box sets (the per-sample loop of
+ * topk(min(pre_max, n)) by score + the NMS nms_type names + [:post_max], for b independent box sets (the per-sample loop of
  * OPCD/pcdet/models/detectors/detector3d_template.py:196-199): boxes_dev [b,n,7], scores_dev [b,n].
  * Order: score descending, ties by lower index. keep_dev [b,post_max]: indices into the set, in kept order;
  * count_dev [b]. pre_max <= 4096, post_max <= 1024. */
 int tcb_rotated_nms(tcb_ctx* ctx, const float* boxes_dev, const float* scores_dev, int b, int n, float thresh,
-                    int pre_max, int post_max, int* keep_dev, int* count_dev, void* stream);
+                    int nms_type, int pre_max, int post_max, int* keep_dev, int* count_dev, void* stream);
 
 /*
  * PointPillars anchor head post for a batch of b frames: analytic anchors (AnchorGenerator.generate_anchors,
@@ -304,8 +311,8 @@ size_t tcb_pp_anchor_post_workspace(int b, int h, int w, int num_class, int num_
 int tcb_pp_anchor_post(tcb_ctx* ctx, const float* cls_dev, const float* box_dev, const float* dir_dev, int b, int h, int w,
                        int num_class, int num_rot, const float anchor_range[6], const float* anchor_sizes,
                        const float* anchor_bottoms, const float* anchor_rotations, float dir_offset,
-                       float dir_limit_offset, int num_dir_bins, float score_thresh, float nms_thresh, int pre_max,
-                       int post_max, float* out_boxes_dev, float* out_scores_dev, long long* out_labels_dev,
+                       float dir_limit_offset, int num_dir_bins, float score_thresh, float nms_thresh, int nms_type,
+                       int pre_max, int post_max, float* out_boxes_dev, float* out_scores_dev, long long* out_labels_dev,
                        int* out_count_dev, void* stream);
 
 /*
@@ -324,8 +331,8 @@ int tcb_centerpoint_post(tcb_ctx* ctx, int b, int num_heads, const float* const*
                          const float* const* center_z_dev, const float* const* dim_dev, const float* const* rot_dev,
                          const float* const* vel_dev, const int* head_num_class, const int* class_id_map, int h, int w,
                          int feature_map_stride, const float voxel_size_xy[2], const float range_min_xy[2],
-                         const float limit_range[6], int k, float score_thresh, float nms_thresh, int pre_max, int post_max,
-                         float* out_boxes_dev, float* out_scores_dev, long long* out_labels_dev, int* out_count_dev,
+                         const float limit_range[6], int k, float score_thresh, float nms_thresh, int nms_type, int pre_max,
+                         int post_max, float* out_boxes_dev, float* out_scores_dev, long long* out_labels_dev, int* out_count_dev,
                          void* stream);
 
 /* Per-class score cut of PointPillarPostprocess.remove_low_score_nu / get_annotations_indices

@@ -47,8 +47,27 @@ def nms_gpu(boxes, scores, thresh, pre_maxsize=None):
     return order[torch.from_numpy(keep[:nk].astype(np.int64))]
 
 
+def fma32(a, b, c):
+    """float32 fma(a, b, c), exactly: the product is exact in float64, the sum is rounded to odd there (TwoSum gives the
+    sign of what float64 dropped), and 53 bits >= 24 + 2 make the final rounding to float32 the correctly rounded one."""
+    p = np.asarray(a, np.float32).astype(np.float64) * np.asarray(b, np.float32).astype(np.float64)
+    c = np.asarray(c, np.float32).astype(np.float64)
+    p, c = np.broadcast_arrays(p, c)
+    s = p + c
+    bb = s - p
+    err = (p - (s - bb)) + (c - bb)
+    odd = (s.view(np.int64) & 1).astype(bool)
+    nxt = np.nextafter(s, np.where(err > 0, np.inf, -np.inf))
+    with np.errstate(over="ignore"):
+        return np.where((err != 0) & ~odd, nxt, s).astype(np.float32)
+
+
 def iou_normal(b):
-    """iou_normal (iou3d_nms_kernel.cu:314-325): axis-aligned BEV overlap of (x, y, dx, dy), heading ignored; float32."""
+    """iou_normal (iou3d_nms_kernel.cu:314-325): axis-aligned BEV overlap of (x, y, dx, dy), heading ignored; float32.
+    Element [i, j]: a = box i (the mask row), b = box j. This function exists only as CUDA in the reference; its nvcc
+    build (12.9, sm_100a, SASS read back) contracts `Sa + Sb` into fma(b.dx, b.dy, Sa) with Sa = a.dx * a.dy rounded
+    first and fuses nothing else that changes a value (x -+ dx / 2 as an fma by 0.5 is exact), so that is what is
+    restated here."""
     b = np.ascontiguousarray(b, np.float32)
     f = np.float32
     x1, y1 = b[:, 0] - b[:, 3] / f(2), b[:, 1] - b[:, 4] / f(2)
@@ -57,7 +76,8 @@ def iou_normal(b):
     h = np.maximum(np.minimum(y2[:, None], y2[None]) - np.maximum(y1[:, None], y1[None]), f(0))
     inter = w * h
     area = b[:, 3] * b[:, 4]
-    return inter / np.maximum(area[:, None] + area[None] - inter, f(1e-8))
+    both = fma32(b[None, :, 3], b[None, :, 4], area[:, None])
+    return inter / np.maximum(both - inter, f(1e-8))
 
 
 def nms_normal_gpu(boxes, scores, thresh):
@@ -177,7 +197,7 @@ def pp_anchor_post(cls_preds, box_preds, dir_preds, anchor_range, anchor_sizes, 
     """Whole d2-d4 chain for one frame, composed from the pieces above."""
     h, w = cls_preds.shape[0], cls_preds.shape[1]
     anchors = generate_anchors((w, h), anchor_range, anchor_sizes, anchor_rotations, anchor_bottoms)
-    post = {k: kw.pop(k) for k in ("score_thresh", "nms_thresh", "pre_max", "post_max") if k in kw}
+    post = {k: kw.pop(k) for k in ("score_thresh", "nms_thresh", "pre_max", "post_max", "nms_type") if k in kw}
     c, b = generate_predicted_boxes(cls_preds, box_preds, dir_preds, anchors, **kw)
     return post_processing(c, b, **post)
 
@@ -253,7 +273,8 @@ def decode_bbox_from_heatmap(heatmap, rot_cos, rot_sin, center, center_z, dim, p
 
 # --- reference: OPCD/pcdet/models/dense_heads/center_head.py:253-304 ----------------------------------
 def centerhead_generate_predicted_boxes(heads, class_id_mapping_each_head, point_cloud_range, voxel_size, feature_map_stride,
-                                        post_center_limit_range, K=500, score_thresh=0.1, nms_thresh=0.2, pre_max=1000, post_max=83):
+                                        post_center_limit_range, K=500, score_thresh=0.1, nms_thresh=0.2, pre_max=1000, post_max=83,
+                                        nms_type="nms_gpu"):
     limit = torch.tensor(post_center_limit_range).float()
     boxes, scores, labels = [], [], []
     for idx, pd in enumerate(heads):
@@ -265,7 +286,7 @@ def centerhead_generate_predicted_boxes(heads, class_id_mapping_each_head, point
             center_z=t["center_z"], dim=batch_dim, vel=t.get("vel"), point_cloud_range=point_cloud_range, voxel_size=voxel_size,
             feature_map_stride=feature_map_stride, K=K, score_thresh=score_thresh, post_center_limit_range=limit)[0]
         final["pred_labels"] = torch.as_tensor(class_id_mapping_each_head[idx])[final["pred_labels"].long()]
-        selected, selected_scores = class_agnostic_nms(final["pred_scores"], final["pred_boxes"], nms_thresh, pre_max, post_max, None)
+        selected, selected_scores = class_agnostic_nms(final["pred_scores"], final["pred_boxes"], nms_thresh, pre_max, post_max, None, nms_type)
         boxes.append(final["pred_boxes"][selected])
         scores.append(selected_scores)
         labels.append(final["pred_labels"][selected])

@@ -266,7 +266,8 @@ def install_iou3d_nms_cuda():
     parts: the pairwise test is the reference's iou_bev as compiled from its iou3d_cpu.cpp (oracle/_ref/libiou3d_ref.so;
     same arithmetic as the device function, iou3d_nms_kernel.cu:227-234), the mask layout and the host sweep are
     iou3d_nms.cpp:90-136 (box i suppresses a later box j when iou_bev(i, j) > thresh). nms_normal_gpu uses the
-    axis-aligned overlap of iou3d_nms_kernel.cu:314-325."""
+    axis-aligned overlap of iou3d_nms_kernel.cu:314-325, which has no CPU twin in the reference: box3d.iou_normal restates
+    it with the one contraction the reference's own nvcc build makes."""
     import ctypes
     import numpy as np
     import torch
@@ -300,17 +301,9 @@ def install_iou3d_nms_cuda():
         return sweep(iou > np.float32(thresh), keep)
 
     def nms_normal_gpu(boxes, keep, thresh):
+        from oracle import box3d
         b = np.ascontiguousarray(boxes.detach().numpy(), np.float32)
-        f = np.float32
-        x1, y1 = b[:, 0] - b[:, 3] / f(2), b[:, 1] - b[:, 4] / f(2)
-        x2, y2 = b[:, 0] + b[:, 3] / f(2), b[:, 1] + b[:, 4] / f(2)
-        lx, rx = np.maximum(x1[:, None], x1[None]), np.minimum(x2[:, None], x2[None])
-        ty, by = np.maximum(y1[:, None], y1[None]), np.minimum(y2[:, None], y2[None])
-        w, h = np.maximum(rx - lx, f(0)), np.maximum(by - ty, f(0))
-        inter = w * h
-        area = b[:, 3] * b[:, 4]
-        iou = inter / np.maximum(area[:, None] + area[None] - inter, f(1e-8))
-        return sweep(iou > f(thresh), keep)
+        return sweep(box3d.iou_normal(b) > np.float32(thresh), keep)
 
     m.nms_gpu, m.nms_normal_gpu = nms_gpu, nms_normal_gpu
     sys.modules[name] = m

@@ -48,6 +48,38 @@ def test_rotated_nms_keep_lists(engine, n, thresh, pre, post, extent):
     assert keep[:k].cpu().tolist() == sel.tolist()
 
 
+@pytest.mark.parametrize("n,thresh,pre,post,extent", [(300, 0.1, 4096, 500, 12), (1000, 0.05, 777, 1000, 30), (4096, 0.5, 4096, 1024, 40),
+                                                     (4096, 0.0, 4096, 500, 12), (5000, 0.3, 641, 640, 25)])
+def test_nms_normal_keep_lists(engine, n, thresh, pre, post, extent):
+    """NMS_TYPE nms_normal_gpu (axis-aligned BEV IoU, heading ignored): the CTA path (<= 512 candidates) and the wide one."""
+    boxes = synth.random_boxes7(n, 77 + n, extent=extent)
+    scores = (np.round(np.random.default_rng(n + 1).uniform(0, 1, n) * 4096) / 4096).astype(np.float32)
+    sel, _ = box3d.class_agnostic_nms(torch.from_numpy(scores), torch.from_numpy(boxes), thresh, pre, post, None, "nms_normal_gpu")
+    keep, cnt = engine.rotated_nms(torch.from_numpy(boxes).cuda(), torch.from_numpy(scores).cuda(), thresh, pre, post, nms_type="nms_normal_gpu")
+    assert keep[:int(cnt.item())].cpu().tolist() == sel.tolist()
+    rot, _ = box3d.class_agnostic_nms(torch.from_numpy(scores), torch.from_numpy(boxes), thresh, pre, post)
+    assert n < 1000 or rot.tolist() != sel.tolist()        # the two NMS types do differ on these boxes
+    with pytest.raises(AttributeError):
+        engine.rotated_nms(torch.from_numpy(boxes).cuda(), torch.from_numpy(scores).cuda(), thresh, pre, post, nms_type="nms_cpu")
+
+
+def test_pp_and_centerpoint_posts_with_nms_normal(engine):
+    """NMS_CONFIG.NMS_TYPE = nms_normal_gpu through both head posts (full-size frames)."""
+    cls, box, dirp = synth.pp_head_outputs(5201)
+    want = box3d.pp_anchor_post(cls, box, dirp, nms_type="nms_normal_gpu", **KITTI_ANCHORS)
+    gb, gs, gl = _pp_gpu(engine, cls, box, dirp, nms_type="nms_normal_gpu", **KITTI_ANCHORS)
+    assert np.array_equal(gl, want["pred_labels"].numpy()) and len(gl) > 20
+    _close(gs, want["pred_scores"].numpy())
+    _close(gb, want["pred_boxes"].numpy(), rtol=1e-5, atol=1e-5)
+    rot = box3d.pp_anchor_post(cls, box, dirp, **KITTI_ANCHORS)
+    assert len(rot["pred_labels"]) != len(gl) or not np.array_equal(rot["pred_scores"].numpy(), want["pred_scores"].numpy())
+    heads = synth.centerpoint_head_outputs(5202)
+    want = box3d.centerhead_generate_predicted_boxes(heads, CLASS_MAP, nms_type="nms_normal_gpu", **NUSC)
+    gb, gs, gl = _cp_gpu(engine, heads, nms_type="nms_normal_gpu")
+    assert np.array_equal(gl, want["pred_labels"].numpy()) and len(gl) > 20
+    _close(gs, want["pred_scores"].numpy())
+
+
 def test_rotated_nms_empty(engine):
     keep, cnt = engine.rotated_nms(torch.zeros((0, 7)).cuda(), torch.zeros((0,)).cuda(), 0.1)
     assert int(cnt.item()) == 0
@@ -191,14 +223,15 @@ def test_centerpoint_reference_glue_golden(engine):
         _same_as_reference(ob[b, :k].cpu().numpy(), osc[b, :k].cpu().numpy(), ol[b, :k].cpu().numpy(), g, "cp", b)
 
 
-@pytest.mark.parametrize("tag", ["rot", "rot_all"])
-def test_class_agnostic_nms_reference_golden(engine, tag):
-    """model_nms_utils.class_agnostic_nms run unmodified (score mask -> topk -> nms_gpu -> post cut -> index map)."""
+@pytest.mark.parametrize("tag,nms_type", [("rot", "nms_gpu"), ("rot_all", "nms_gpu"), ("normal", "nms_normal_gpu")])
+def test_class_agnostic_nms_reference_golden(engine, tag, nms_type):
+    """model_nms_utils.class_agnostic_nms run unmodified (score mask -> topk -> NMS_TYPE -> post cut -> index map)."""
     g = golden("pcdet_post")
     thr, st, pre, post = g[f"nms_{tag}_cfg"]
     boxes, scores = g["nms_boxes"], g["nms_scores"]
     idx = np.nonzero(scores >= np.float32(st))[0] if st >= 0 else np.arange(len(scores))
-    keep, cnt = engine.rotated_nms(torch.from_numpy(boxes[idx]).cuda(), torch.from_numpy(scores[idx]).cuda(), float(thr), int(pre), int(post))
+    keep, cnt = engine.rotated_nms(torch.from_numpy(boxes[idx]).cuda(), torch.from_numpy(scores[idx]).cuda(), float(thr), int(pre), int(post),
+                                   nms_type=nms_type)
     sel = idx[keep[:int(cnt.item())].cpu().numpy()]
     assert np.array_equal(sel, g[f"nms_{tag}_sel"])
 

@@ -65,15 +65,15 @@ SIGNATURES = {
     "tcb_dynamic_pillar": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, P(c_double), P(c_double), c_void_p, c_void_p, c_void_p,
                                    c_void_p, c_void_p]),
     "tcb_rotated_iou": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p]),
-    "tcb_rotated_nms": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "tcb_rotated_nms": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "tcb_pp_anchor_post_workspace": (c_size_t, [c_int, c_int, c_int, c_int, c_int]),
     "tcb_pp_anchor_post": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, P(c_float), P(c_float),
-                                   P(c_float), P(c_float), c_float, c_float, c_int, c_float, c_float, c_int, c_int,
+                                   P(c_float), P(c_float), c_float, c_float, c_int, c_float, c_float, c_int, c_int, c_int,
                                    c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "tcb_centerpoint_post_workspace": (c_size_t, [c_int, c_int, c_int, c_int]),
     "tcb_centerpoint_post": (c_int, [c_void_p, c_int, c_int, P(c_void_p), P(c_void_p), P(c_void_p), P(c_void_p), P(c_void_p), P(c_void_p),
                                      P(c_int), P(c_int), c_int, c_int, c_int, P(c_float), P(c_float), P(c_float), c_int,
-                                     c_float, c_float, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+                                     c_float, c_float, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "tcb_class_score_filter": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, P(c_int), P(c_float), c_void_p, c_void_p, c_void_p]),
     "tcb_scale_boxes": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "tcb_draw_detections_workspace": (c_size_t, [c_int, c_int]),

@@ -79,8 +79,8 @@ class PointPillarPostprocess(Postprocess):
         n = int(cnt.item())
         return {'pred_boxes': ob[:n].cpu(), 'pred_scores': osc[:n].cpu(), 'pred_labels': ol[:n].cpu()}
 
-    def rotated_nms(self, boxes, scores, thresh, pre_max=4096, post_max=500):
+    def rotated_nms(self, boxes, scores, thresh, pre_max=4096, post_max=500, nms_type="nms_gpu"):
         dev = self.engine.device
         keep, cnt = self.engine.rotated_nms(torch.as_tensor(boxes, dtype=torch.float32).to(dev), torch.as_tensor(scores, dtype=torch.float32).to(dev),
-                                            thresh, pre_max, post_max)
+                                            thresh, pre_max, post_max, nms_type)
         return keep[:int(cnt.item())].cpu().long()

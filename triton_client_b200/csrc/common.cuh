@@ -19,9 +19,26 @@ struct tcb_ctx {
     int pdl;           // launch the hot kernels with programmatic stream serialization (TCB_PDL, default on)
     int* tickets;      // TCB_TICKETS ints behind the workspace, zero between calls: "last CTA of a group" counters that
                        // the kernel using them resets itself, so no per-call memset is needed
+    char* stage;       // TCB_STAGE_SLOTS pinned slots of TCB_STAGE_BYTES for small host tables (tcb_stage_h2d)
+    cudaEvent_t stage_done[8];
+    int stage_next;
     char err[TCB_ERRLEN];
 };
 #define TCB_TICKETS 65536
+#define TCB_STAGE_SLOTS 8
+#define TCB_STAGE_BYTES 16384
+
+// Copy a small host table to the device without blocking the caller: through a pinned slot of the context (a slot is
+// reused only after the copy that read it has finished); tables larger than a slot go straight from the caller's memory.
+int tcb_stage_h2d(tcb_ctx* ctx, void* dev, const void* host, size_t bytes, cudaStream_t st);
+
+// Per-file set-up run once by tcb_create on the context's device (opt-ins to > 48 KB of dynamic shared memory), so the
+// entry points themselves make no driver calls besides their launches.
+typedef int (*tcb_init_fn)(tcb_ctx*);
+struct TcbInitReg { explicit TcbInitReg(tcb_init_fn fn); };
+#define TCB_SMEM_OPT_IN(ctx, kernel, bytes) \
+    TCB_CUDA((ctx), cudaFuncSetAttribute((const void*)(kernel), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes)))
+#define TCB_SMEM_LIMIT (227 * 1024)
 
 int tcb_fail(tcb_ctx* ctx, int code, const char* fmt, ...);
 void tcb_clear_error(tcb_ctx* ctx);

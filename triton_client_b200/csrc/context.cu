@@ -17,6 +17,28 @@ int tcb_fail(tcb_ctx* ctx, int code, const char* fmt, ...) {
 
 void tcb_clear_error(tcb_ctx* ctx) { if (ctx) ctx->err[0] = 0; }
 
+// Filled by the static TcbInitReg objects of the other translation units while the library loads (plain zero-initialised
+// storage, so the order of those constructors does not matter).
+static tcb_init_fn g_init[32];
+static int g_num_init;
+TcbInitReg::TcbInitReg(tcb_init_fn fn) { if (g_num_init < 32) g_init[g_num_init++] = fn; }
+
+int tcb_stage_h2d(tcb_ctx* ctx, void* dev, const void* host, size_t bytes, cudaStream_t st) {
+    if (bytes == 0) return TCB_OK;
+    if (bytes > TCB_STAGE_BYTES) {
+        TCB_CUDA(ctx, cudaMemcpyAsync(dev, host, bytes, cudaMemcpyHostToDevice, st));
+        return TCB_OK;
+    }
+    const int slot = ctx->stage_next;
+    ctx->stage_next = (slot + 1) % TCB_STAGE_SLOTS;
+    TCB_CUDA(ctx, cudaEventSynchronize(ctx->stage_done[slot]));   // the copy that last read this slot (long finished, normally)
+    char* pin = ctx->stage + (size_t)slot * TCB_STAGE_BYTES;
+    memcpy(pin, host, bytes);
+    TCB_CUDA(ctx, cudaMemcpyAsync(dev, pin, bytes, cudaMemcpyHostToDevice, st));
+    TCB_CUDA(ctx, cudaEventRecord(ctx->stage_done[slot], st));
+    return TCB_OK;
+}
+
 extern "C" {
 
 const char* tcb_version(void) { return "tcb200 0.1 (sm_100a)"; }
@@ -48,6 +70,20 @@ int tcb_create(int device, size_t workspace_bytes, tcb_ctx** out) {
     }
     c->tickets = reinterpret_cast<int*>(c->ws + ws_round);
     c->ws_bytes = workspace_bytes;
+    e = cudaMallocHost((void**)&c->stage, (size_t)TCB_STAGE_SLOTS * TCB_STAGE_BYTES);
+    for (int i = 0; i < TCB_STAGE_SLOTS && e == cudaSuccess; i++) e = cudaEventCreateWithFlags(&c->stage_done[i], cudaEventDisableTiming);
+    if (e != cudaSuccess) {
+        tcb_destroy(c);
+        return tcb_fail(nullptr, TCB_ERR_ALLOC, "tcb_create: pinned staging -> %s", cudaGetErrorString(e));
+    }
+    for (int i = 0; i < g_num_init; i++) {
+        const int rc = g_init[i](c);
+        if (rc != TCB_OK) {
+            tcb_fail(nullptr, rc, "tcb_create: %s", c->err);
+            tcb_destroy(c);
+            return rc;
+        }
+    }
     *out = c;
     return TCB_OK;
 }
@@ -55,6 +91,8 @@ int tcb_create(int device, size_t workspace_bytes, tcb_ctx** out) {
 int tcb_destroy(tcb_ctx* ctx) {
     if (!ctx) return TCB_OK;
     if (ctx->ws) cudaFree(ctx->ws);
+    for (int i = 0; i < TCB_STAGE_SLOTS; i++) if (ctx->stage_done[i]) cudaEventDestroy(ctx->stage_done[i]);
+    if (ctx->stage) cudaFreeHost(ctx->stage);
     delete ctx;
     return TCB_OK;
 }

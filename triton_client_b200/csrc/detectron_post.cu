@@ -328,6 +328,14 @@ __global__ void __launch_bounds__(T, 1) det_post_kernel(const DetParams p, float
 
 }  // namespace
 
+static int init_detectron(tcb_ctx* ctx) {   // run by tcb_create
+    TCB_SMEM_OPT_IN(ctx, det_candidates_kernel, sizeof(DcWarp) * DC_WARPS);
+    TCB_SMEM_OPT_IN(ctx, det_level_kernel, DET_CACHE * 8);
+    TCB_SMEM_OPT_IN(ctx, det_post_kernel, sizeof(DFrameShared));
+    return TCB_OK;
+}
+static TcbInitReg reg_detectron(&init_detectron);
+
 extern "C" size_t tcb_detectron_post_workspace(int b, int num_levels, const int* h, const int* w, int num_anchors, int num_classes, int topk) {
     const size_t bb = (size_t)(b > 0 ? b : 1);
     size_t bytes = 8192 + bb * MAX_LEVELS * 4;
@@ -393,14 +401,11 @@ extern "C" int tcb_detectron_post(tcb_ctx* ctx, int b, int num_levels, const flo
         const size_t dc_smem = sizeof(DcWarp) * DC_WARPS;      // 48 KB: four CTAs per SM
         const long long want = tcb_div_up(items, DC_WARPS);
         const int ctas = (int)(want < (long long)ctx->num_sms * 4 ? want : (long long)ctx->num_sms * 4);
-        TCB_CUDA(ctx, cudaFuncSetAttribute(det_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dc_smem));
         TCB_KLAUNCH(ctx, det_candidates_kernel, ctas, 32 * DC_WARPS, dc_smem, st, p, W, logit_floor);
         TCB_LAUNCHED(ctx);
     }
-    TCB_CUDA(ctx, cudaFuncSetAttribute(det_level_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DET_CACHE * 8));
     TCB_KLAUNCH(ctx, det_level_kernel, dim3(num_levels, b), T, DET_CACHE * 8, st, p, mbox, mscore, mcls, mkeys);
     TCB_LAUNCHED(ctx);
-    TCB_CUDA(ctx, cudaFuncSetAttribute(det_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DFrameShared)));
     TCB_KLAUNCH(ctx, det_post_kernel, b, T, sizeof(DFrameShared), st, p, mbox, mscore, mcls, mkeys, out_boxes_dev, out_scores_dev, out_classes_dev, out_count_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;

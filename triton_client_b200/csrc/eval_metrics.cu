@@ -465,20 +465,20 @@ static int launch_match(tcb_ctx* ctx, const double* gts, const int* goff_dev, co
     return TCB_OK;
 }
 
+static int init_eval(tcb_ctx* ctx) {
+    TCB_SMEM_OPT_IN(ctx, eval_ap_kernel, sizeof(ApShared));
+    return TCB_OK;
+}
+static TcbInitReg reg_eval(&init_eval);
+
 static int launch_ap(tcb_ctx* ctx, ApArgs& a, int frames, cudaStream_t st) {
-    static bool opted[64] = {false};
-    if (!opted[ctx->device & 63]) {
-        TCB_CUDA(ctx, cudaFuncSetAttribute(eval_ap_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ApShared)));
-        opted[ctx->device & 63] = true;
-    }
     TCB_KLAUNCH(ctx, eval_ap_kernel, frames, EV_T, sizeof(ApShared), st, a);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }
 
 static int upload_offsets(tcb_ctx* ctx, const int* host, int frames, int* dev, cudaStream_t st) {
-    TCB_CUDA(ctx, cudaMemcpyAsync(dev, host, sizeof(int) * (size_t)(frames + 1), cudaMemcpyHostToDevice, st));
-    return TCB_OK;
+    return tcb_stage_h2d(ctx, dev, host, sizeof(int) * (size_t)(frames + 1), st);
 }
 
 extern "C" size_t tcb_eval_workspace(int frames, int max_classes) {

@@ -528,6 +528,12 @@ size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 }  // namespace
 
+static int init_jpeg(tcb_ctx* ctx) {   // run by tcb_create
+    TCB_SMEM_OPT_IN(ctx, jpeg_huffman_kernel, sizeof(HuffShared));
+    return TCB_OK;
+}
+static TcbInitReg reg_jpeg(&init_jpeg);
+
 extern "C" int tcb_jpeg_info(const unsigned char* jpeg_host, size_t len, int* height, int* width, int* channels) {
     if (!jpeg_host || !height || !width || !channels) return tcb_fail(nullptr, TCB_ERR_ARG, "tcb_jpeg_info: null argument");
     size_t i = 2;
@@ -618,7 +624,6 @@ extern "C" int tcb_jpeg_decode(tcb_ctx* ctx, const unsigned char* const* jpeg_ho
     const JpegHdr* d_hdrs = (const JpegHdr*)dev_stage;
     const unsigned char* d_scan = (const unsigned char*)(dev_stage + scan_at);
     const JSeg* d_segs = (const JSeg*)(dev_stage + seg_at);
-    TCB_CUDA(ctx, cudaFuncSetAttribute(jpeg_huffman_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(HuffShared)));
     TCB_KLAUNCH(ctx, jpeg_huffman_kernel, n, HUFF_T, sizeof(HuffShared), st, d_hdrs, d_scan, d_segs, exit_st, used_in, adv, gpos, coef);
     TCB_LAUNCHED(ctx);
     long long max_blocks = 0;

@@ -41,15 +41,16 @@ constexpr int QCAP = 8192;   // pending exact IoU tests per greedy round
 struct RotPred {
     static constexpr bool kQueue = true;
     float thresh;
-    // far apart: the reference's polygon is empty, IoU 0, never > thresh (>= 0)
+    int normal;    // 0: nms_gpu (rotated BEV IoU), 1: nms_normal_gpu (axis-aligned BEV IoU)
+    // far apart: the reference's polygon (or axis-aligned intersection) is empty, IoU 0, never > thresh (>= 0)
     __device__ __forceinline__ bool maybe(const rot::RBox& a, const rot::RBox& b) const { return !rot::far_apart(a, b); }
-    __device__ __forceinline__ bool exact(const rot::RBox& a, const rot::RBox& b) const { return rot::iou_bev(a, b) > thresh; }
+    __device__ __forceinline__ bool exact(const rot::RBox& a, const rot::RBox& b) const { return rot::overlaps(a, b, thresh, normal); }
     __device__ __forceinline__ bool operator()(const rot::RBox& a, const rot::RBox& b) const { return maybe(a, b) && exact(a, b); }
 };
 typedef nms::Shared<rot::RBox, POST_CAP, PRE_CAP, QCAP> NmsShared;
 
-__device__ __forceinline__ int cta_rotated_nms(const rot::RBox* __restrict__ R, int m, float thresh, int post_max, NmsShared& S) {
-    return nms::cta_greedy_nms(R, m, RotPred{thresh}, post_max, S);
+__device__ __forceinline__ int cta_rotated_nms(const rot::RBox* __restrict__ R, int m, float thresh, int normal, int post_max, NmsShared& S) {
+    return nms::cta_greedy_nms(R, m, RotPred{thresh, normal}, post_max, S);
 }
 
 // shared memory of the one-CTA-per-frame kernels
@@ -66,7 +67,7 @@ static_assert(sizeof(FrameShared) <= 227 * 1024, "FrameShared exceeds the 227 KB
 // ---------------------------------------------------------------------------------------------------------
 // blockIdx.x = box set of the batch (boxes [b,n,7], scores [b,n], keep [b,post_max], count [b])
 __global__ void __launch_bounds__(T, 1) rotated_nms_kernel(const float* __restrict__ boxes, const float* __restrict__ scores, int n,
-                                                           float thresh, int pre_max, int post_max,
+                                                           float thresh, int normal, int pre_max, int post_max,
                                                            int* __restrict__ keep, int* __restrict__ count) {
     pdl_wait();
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -76,7 +77,7 @@ __global__ void __launch_bounds__(T, 1) rotated_nms_kernel(const float* __restri
     const int m = sel::cta_topk_sorted(key_of, n, pre_max, S.skeys, S.sel);
     for (int c = threadIdx.x; c < m; c += T) S.R[c] = rot::make_rbox(boxes + 7ll * sel::key_index(S.skeys[c]));
     __syncthreads();
-    const int nk = cta_rotated_nms(S.R, m, thresh, post_max, S.nms);
+    const int nk = cta_rotated_nms(S.R, m, thresh, normal, post_max, S.nms);
     for (int k = threadIdx.x; k < nk; k += T) keep[k] = (int)sel::key_index(S.skeys[S.nms.kpos[k]]);
     if (threadIdx.x == 0) *count = nk;
 }
@@ -110,7 +111,7 @@ struct OrderShared {
 // m_dev[0] = number of candidates, m_dev[1] = pairs listed so far (zeroed by the order kernel).
 // blockIdx.z = candidate set of the batch; per-set strides: PRE_CAP boxes, WIDE_M ints, mask_stride words, pair_cap pairs
 constexpr int WIDE_M = 64;   // ints per set in the m array ([0] candidates, [1] pairs listed)
-__global__ void __launch_bounds__(MASK_T) rot_mask_kernel(const rot::RBox* __restrict__ R, int* __restrict__ m_dev, float thresh,
+__global__ void __launch_bounds__(MASK_T) rot_mask_kernel(const rot::RBox* __restrict__ R, int* __restrict__ m_dev, float thresh, int normal,
                                                           unsigned long long* __restrict__ mask, size_t mask_stride, unsigned* __restrict__ pairs, int pair_cap) {
     pdl_wait();
     R += (size_t)blockIdx.z * PRE_CAP; m_dev += blockIdx.z * WIDE_M; mask += blockIdx.z * mask_stride; pairs += (size_t)blockIdx.z * pair_cap;
@@ -159,7 +160,7 @@ __global__ void __launch_bounds__(MASK_T) rot_mask_kernel(const rot::RBox* __res
             if (base + q < pair_cap) pairs[base + q] = 0xffffffffu;
             const int e = queue[q];
             const int i = e >> 6, j = e & 63;
-            if (rot::iou_bev(rows[i], cols[j]) > thresh) atomicOr(&tmask[i], 1ull << j);
+            if (rot::overlaps(rows[i], cols[j], thresh, normal)) atomicOr(&tmask[i], 1ull << j);
         }
         __syncthreads();
     }
@@ -168,7 +169,7 @@ __global__ void __launch_bounds__(MASK_T) rot_mask_kernel(const rot::RBox* __res
 
 // Mask, step 2: the exact rotated IoU of every listed pair, one pair per thread with all lanes busy (inside the tiles
 // the few pairs that survive the distance test would each run with most of their warp idle).
-__global__ void __launch_bounds__(256) rot_pairs_kernel(const rot::RBox* __restrict__ R, const int* __restrict__ m_dev, float thresh,
+__global__ void __launch_bounds__(256) rot_pairs_kernel(const rot::RBox* __restrict__ R, const int* __restrict__ m_dev, float thresh, int normal,
                                                         const unsigned* __restrict__ pairs, int pair_cap, unsigned long long* __restrict__ mask, size_t mask_stride) {
     pdl_wait();
     R += (size_t)blockIdx.y * PRE_CAP; m_dev += blockIdx.y * WIDE_M; mask += blockIdx.y * mask_stride; pairs += (size_t)blockIdx.y * pair_cap;
@@ -177,7 +178,7 @@ __global__ void __launch_bounds__(256) rot_pairs_kernel(const rot::RBox* __restr
         const unsigned e = pairs[q];
         if (e == 0xffffffffu) continue;
         const int gi = (int)(e >> 16), gj = (int)(e & 0xffffu);
-        if (rot::iou_bev(R[gi], R[gj]) > thresh) atomicOr(&mask[(size_t)gi * MW + (gj >> 6)], 1ull << (gj & 63));
+        if (rot::overlaps(R[gi], R[gj], thresh, normal)) atomicOr(&mask[(size_t)gi * MW + (gj >> 6)], 1ull << (gj & 63));
     }
 }
 
@@ -235,6 +236,7 @@ struct PPParams {
     float rot[PP_MAX_CLASSES][PP_MAX_ROT];
     float dir_offset, dir_limit_offset, period;
     float score_thresh, nms_thresh;
+    int nms_normal;
     int pre_max, post_max;
     int n_anchors;                               // H * W * num_class * num_rot: rows per frame of the batch
 };
@@ -362,7 +364,7 @@ __global__ void __launch_bounds__(T, 1) pp_post_kernel(const PPParams p, const f
         S.R[c] = rot::make_rbox(b7);
     }
     __syncthreads();
-    const int nk = cta_rotated_nms(S.R, m, p.nms_thresh, p.post_max, S.nms);
+    const int nk = cta_rotated_nms(S.R, m, p.nms_thresh, p.nms_normal, p.post_max, S.nms);
     for (int k = tid; k < nk; k += T) {
         const int c = S.nms.kpos[k];
         const unsigned long long key = S.skeys[c];
@@ -459,6 +461,7 @@ struct CPParams {
     float stride, vx, vy, rx, ry;        // feature_map_stride, voxel size, range min
     float limit[6];                      // POST_CENTER_LIMIT_RANGE
     float score_thresh, nms_thresh;
+    int nms_normal;
     int pre_max, post_max;
 };
 
@@ -538,7 +541,7 @@ __global__ void __launch_bounds__(T, 1) cp_head_kernel(const CPParams p, float* 
     }
     const int mv = min(base, p.pre_max);
     __syncthreads();
-    const int nk = cta_rotated_nms(S.R, mv, p.nms_thresh, p.post_max, S.nms);
+    const int nk = cta_rotated_nms(S.R, mv, p.nms_thresh, p.nms_normal, p.post_max, S.nms);
     for (int k = tid; k < nk; k += T) {
         const int c = S.nms.kpos[k];
         const long long src = (long long)p.num_heads * p.post_max + (long long)h * p.pre_max + c;
@@ -615,19 +618,26 @@ extern "C" int tcb_rotated_iou(tcb_ctx* ctx, const float* boxes_a_dev, int n, co
     return TCB_OK;
 }
 
-static int check_nms_limits(tcb_ctx* ctx, const char* who, float thresh, int pre_max, int post_max) {
+static int check_nms_limits(tcb_ctx* ctx, const char* who, float thresh, int nms_type, int pre_max, int post_max) {
     if (!(thresh >= 0.f)) return tcb_fail(ctx, TCB_ERR_ARG, "%s: nms threshold must be >= 0", who);
+    if (nms_type != TCB_NMS_GPU && nms_type != TCB_NMS_NORMAL) return tcb_fail(ctx, TCB_ERR_ARG, "%s: nms_type must be TCB_NMS_GPU or TCB_NMS_NORMAL", who);
     if (pre_max < 1 || post_max < 1) return tcb_fail(ctx, TCB_ERR_ARG, "%s: pre/post max size must be >= 1", who);
     if (pre_max > PRE_CAP) return tcb_fail(ctx, TCB_ERR_LIMIT, "%s: NMS_PRE_MAXSIZE %d > compiled limit %d", who, pre_max, PRE_CAP);
     if (post_max > POST_CAP) return tcb_fail(ctx, TCB_ERR_LIMIT, "%s: NMS_POST_MAXSIZE %d > compiled limit %d", who, post_max, POST_CAP);
     return TCB_OK;
 }
 
-template <typename K>
-static int opt_in_smem(tcb_ctx* ctx, K kernel) {
-    TCB_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FrameShared)));
+static int init_post3d(tcb_ctx* ctx) {   // run by tcb_create
+    TCB_SMEM_OPT_IN(ctx, rotated_nms_kernel, sizeof(FrameShared));
+    TCB_SMEM_OPT_IN(ctx, pp_post_kernel, sizeof(FrameShared));
+    TCB_SMEM_OPT_IN(ctx, cp_head_kernel, sizeof(FrameShared));
+    TCB_SMEM_OPT_IN(ctx, rot_order_kernel, ORDER_CACHE * 8);
+    TCB_SMEM_OPT_IN(ctx, pp_order_kernel, ORDER_CACHE * 8);
+    TCB_SMEM_OPT_IN(ctx, rot_sweep_kernel, sizeof(SweepShared));
+    TCB_SMEM_OPT_IN(ctx, pp_finish_kernel, sizeof(SweepShared));
     return TCB_OK;
 }
+static TcbInitReg reg_post3d(&init_post3d);
 
 // workspace of the wide path for `sets` candidate sets; false (nothing taken) when the context's workspace has no room for it
 struct WideBufs {
@@ -658,40 +668,37 @@ static bool wide_bufs(tcb_ctx* ctx, int m_max, int sets, WideBufs& wb) {
     return wb.skeys && wb.R && wb.mask && wb.m && wb.pairs;
 }
 // mask (tiles + listed pairs) of `sets` ordered candidate sets already in wb.R / wb.m
-static int wide_mask(tcb_ctx* ctx, const WideBufs& wb, int m_max, int sets, float thresh, cudaStream_t st) {
+static int wide_mask(tcb_ctx* ctx, const WideBufs& wb, int m_max, int sets, float thresh, int normal, cudaStream_t st) {
     const int nb = tcb_div_up(m_max, 64);
-    TCB_KLAUNCH(ctx, rot_mask_kernel, dim3(nb, nb, sets), MASK_T, 0, st, wb.R, wb.m, thresh, wb.mask, wb.mask_stride, wb.pairs, wb.pair_cap);
+    TCB_KLAUNCH(ctx, rot_mask_kernel, dim3(nb, nb, sets), MASK_T, 0, st, wb.R, wb.m, thresh, normal, wb.mask, wb.mask_stride, wb.pairs, wb.pair_cap);
     TCB_LAUNCHED(ctx);
     const int per = sets > 1 ? tcb_div_up(ctx->num_sms * 8, sets) : ctx->num_sms * 8;
-    TCB_KLAUNCH(ctx, rot_pairs_kernel, dim3(per, sets), 256, 0, st, wb.R, wb.m, thresh, wb.pairs, wb.pair_cap, wb.mask, wb.mask_stride);
+    TCB_KLAUNCH(ctx, rot_pairs_kernel, dim3(per, sets), 256, 0, st, wb.R, wb.m, thresh, normal, wb.pairs, wb.pair_cap, wb.mask, wb.mask_stride);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }
 
-extern "C" int tcb_rotated_nms(tcb_ctx* ctx, const float* boxes_dev, const float* scores_dev, int b, int n, float thresh, int pre_max,
+extern "C" int tcb_rotated_nms(tcb_ctx* ctx, const float* boxes_dev, const float* scores_dev, int b, int n, float thresh, int nms_type, int pre_max,
                                int post_max, int* keep_dev, int* count_dev, void* stream) {
     TCB_CHECK_CTX(ctx);
     TCB_REQUIRE(ctx, b >= 1 && n >= 0 && keep_dev && count_dev && (n == 0 || (boxes_dev && scores_dev)), "tcb_rotated_nms: bad arguments");
     if (b > 65535) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_rotated_nms: more than 65535 box sets");
-    int rc = check_nms_limits(ctx, "tcb_rotated_nms", thresh, pre_max, post_max);
+    int rc = check_nms_limits(ctx, "tcb_rotated_nms", thresh, nms_type, pre_max, post_max);
     if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     WideBufs wb;
     const int m_max = n < pre_max ? n : pre_max;
     if (m_max > WIDE_MIN && wide_bufs(ctx, m_max, b, wb)) {
-        TCB_CUDA(ctx, cudaFuncSetAttribute(rot_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ORDER_CACHE * 8));
         TCB_KLAUNCH(ctx, rot_order_kernel, b, T, ORDER_CACHE * 8, st, scores_dev, n, pre_max, wb.skeys, wb.m);
         TCB_LAUNCHED(ctx);
         TCB_KLAUNCH(ctx, rot_rbox_kernel, dim3(tcb_div_up(m_max, 256), b), 256, 0, st, boxes_dev, n, wb.skeys, wb.m, wb.R);
         TCB_LAUNCHED(ctx);
-        if ((rc = wide_mask(ctx, wb, m_max, b, thresh, st))) return rc;
-        TCB_CUDA(ctx, cudaFuncSetAttribute(rot_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SweepShared)));
+        if ((rc = wide_mask(ctx, wb, m_max, b, thresh, nms_type, st))) return rc;
         TCB_KLAUNCH(ctx, rot_sweep_kernel, b, SWEEP_T, sizeof(SweepShared), st, wb.mask, wb.mask_stride, wb.skeys, wb.m, post_max, keep_dev, count_dev);
         TCB_LAUNCHED(ctx);
         return TCB_OK;
     }
-    if ((rc = opt_in_smem(ctx, rotated_nms_kernel))) return rc;
-    TCB_KLAUNCH(ctx, rotated_nms_kernel, b, T, sizeof(FrameShared), st, boxes_dev, scores_dev, n, thresh, pre_max, post_max, keep_dev, count_dev);
+    TCB_KLAUNCH(ctx, rotated_nms_kernel, b, T, sizeof(FrameShared), st, boxes_dev, scores_dev, n, thresh, nms_type, pre_max, post_max, keep_dev, count_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
 }
@@ -704,8 +711,8 @@ extern "C" size_t tcb_pp_anchor_post_workspace(int b, int h, int w, int num_clas
 extern "C" int tcb_pp_anchor_post(tcb_ctx* ctx, const float* cls_dev, const float* box_dev, const float* dir_dev, int b, int h, int w,
                                   int num_class, int num_rot, const float anchor_range[6], const float* anchor_sizes,
                                   const float* anchor_bottoms, const float* anchor_rotations, float dir_offset,
-                                  float dir_limit_offset, int num_dir_bins, float score_thresh, float nms_thresh, int pre_max,
-                                  int post_max, float* out_boxes_dev, float* out_scores_dev, long long* out_labels_dev,
+                                  float dir_limit_offset, int num_dir_bins, float score_thresh, float nms_thresh, int nms_type,
+                                  int pre_max, int post_max, float* out_boxes_dev, float* out_scores_dev, long long* out_labels_dev,
                                   int* out_count_dev, void* stream) {
     TCB_CHECK_CTX(ctx);
     TCB_REQUIRE(ctx, cls_dev && box_dev && anchor_range && anchor_sizes && anchor_bottoms && anchor_rotations &&
@@ -715,7 +722,7 @@ extern "C" int tcb_pp_anchor_post(tcb_ctx* ctx, const float* cls_dev, const floa
     if (num_class < 1 || num_class > PP_MAX_CLASSES || num_rot < 1 || num_rot > PP_MAX_ROT)
         return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_pp_anchor_post: num_class %d (<= %d) / num_rot %d (<= %d)", num_class, PP_MAX_CLASSES, num_rot, PP_MAX_ROT);
     TCB_REQUIRE(ctx, dir_dev == nullptr || num_dir_bins >= 1, "tcb_pp_anchor_post: num_dir_bins must be >= 1");
-    int rc = check_nms_limits(ctx, "tcb_pp_anchor_post", nms_thresh, pre_max, post_max);
+    int rc = check_nms_limits(ctx, "tcb_pp_anchor_post", nms_thresh, nms_type, pre_max, post_max);
     if (rc) return rc;
     const long long n_anchors = (long long)h * w * num_class * num_rot;
     if (n_anchors > (1ll << 30)) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_pp_anchor_post: too many anchors");
@@ -735,7 +742,7 @@ extern "C" int tcb_pp_anchor_post(tcb_ctx* ctx, const float* cls_dev, const floa
     }
     p.dir_offset = dir_offset; p.dir_limit_offset = dir_limit_offset;
     p.period = (float)(2.0 * 3.141592653589793 / (double)(num_dir_bins > 0 ? num_dir_bins : 1));
-    p.score_thresh = score_thresh; p.nms_thresh = nms_thresh; p.pre_max = pre_max; p.post_max = post_max;
+    p.score_thresh = score_thresh; p.nms_thresh = nms_thresh; p.nms_normal = nms_type; p.pre_max = pre_max; p.post_max = post_max;
 
     TCB_WS(ctx, cand_count, int, b + 64);
     TCB_WS(ctx, cand, unsigned long long, (size_t)b * n_anchors);
@@ -751,19 +758,16 @@ extern "C" int tcb_pp_anchor_post(tcb_ctx* ctx, const float* cls_dev, const floa
     WideBufs wb;
     const int m_max = (int)(n_anchors < pre_max ? n_anchors : pre_max);
     if (m_max > WIDE_MIN && wide_bufs(ctx, m_max, b, wb)) {
-        TCB_CUDA(ctx, cudaFuncSetAttribute(pp_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ORDER_CACHE * 8));
         TCB_KLAUNCH(ctx, pp_order_kernel, b, T, ORDER_CACHE * 8, st, p, cand, cand_count, (int)n_anchors, wb.skeys, wb.m);
         TCB_LAUNCHED(ctx);
         TCB_KLAUNCH(ctx, pp_decode_kernel, dim3(tcb_div_up(m_max, 256), b), 256, 0, st, p, box_dev, dir_dev, wb.skeys, wb.m, sorted_boxes, wb.R);
         TCB_LAUNCHED(ctx);
-        if ((rc = wide_mask(ctx, wb, m_max, b, nms_thresh, st))) return rc;
-        TCB_CUDA(ctx, cudaFuncSetAttribute(pp_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SweepShared)));
+        if ((rc = wide_mask(ctx, wb, m_max, b, nms_thresh, nms_type, st))) return rc;
         TCB_KLAUNCH(ctx, pp_finish_kernel, b, SWEEP_T, sizeof(SweepShared), st, p, cls_dev, wb.mask, wb.mask_stride, wb.skeys, wb.m, sorted_boxes, out_boxes_dev, out_scores_dev,
                                                              out_labels_dev, out_count_dev);
         TCB_LAUNCHED(ctx);
         return TCB_OK;
     }
-    if ((rc = opt_in_smem(ctx, pp_post_kernel))) return rc;
     TCB_KLAUNCH(ctx, pp_post_kernel, b, T, sizeof(FrameShared), st, p, cls_dev, box_dev, dir_dev, cand, cand_count, (int)n_anchors, sorted_boxes,
                                                        out_boxes_dev, out_scores_dev, out_labels_dev, out_count_dev);
     TCB_LAUNCHED(ctx);
@@ -778,7 +782,7 @@ extern "C" int tcb_centerpoint_post(tcb_ctx* ctx, int b, int num_heads, const fl
                                     const float* const* center_z_dev, const float* const* dim_dev, const float* const* rot_dev,
                                     const float* const* vel_dev, const int* head_num_class, const int* class_id_map, int h, int w,
                                     int feature_map_stride, const float voxel_size_xy[2], const float range_min_xy[2],
-                                    const float limit_range[6], int k, float score_thresh, float nms_thresh, int pre_max, int post_max,
+                                    const float limit_range[6], int k, float score_thresh, float nms_thresh, int nms_type, int pre_max, int post_max,
                                     float* out_boxes_dev, float* out_scores_dev, long long* out_labels_dev, int* out_count_dev,
                                     void* stream) {
     TCB_CHECK_CTX(ctx);
@@ -788,7 +792,7 @@ extern "C" int tcb_centerpoint_post(tcb_ctx* ctx, int b, int num_heads, const fl
     if (num_heads < 1 || num_heads > CP_MAX_HEADS) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_centerpoint_post: %d heads (limit %d)", num_heads, CP_MAX_HEADS);
     TCB_REQUIRE(ctx, b >= 1 && b <= 65535 && h >= 1 && w >= 1 && k >= 1, "tcb_centerpoint_post: bad shape");
     if (k > PRE_CAP) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_centerpoint_post: K %d > %d", k, PRE_CAP);
-    int rc = check_nms_limits(ctx, "tcb_centerpoint_post", nms_thresh, pre_max, post_max);
+    int rc = check_nms_limits(ctx, "tcb_centerpoint_post", nms_thresh, nms_type, pre_max, post_max);
     if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
 
@@ -808,14 +812,13 @@ extern "C" int tcb_centerpoint_post(tcb_ctx* ctx, int b, int num_heads, const fl
     }
     p.stride = (float)feature_map_stride; p.vx = voxel_size_xy[0]; p.vy = voxel_size_xy[1]; p.rx = range_min_xy[0]; p.ry = range_min_xy[1];
     for (int j = 0; j < 6; j++) p.limit[j] = limit_range[j];
-    p.score_thresh = score_thresh; p.nms_thresh = nms_thresh; p.pre_max = pre_max; p.post_max = post_max;
+    p.score_thresh = score_thresh; p.nms_thresh = nms_thresh; p.nms_normal = nms_type; p.pre_max = pre_max; p.post_max = post_max;
 
     const size_t rows = (size_t)b * num_heads * (size_t)(pre_max + post_max);
     TCB_WS(ctx, head_count, int, (size_t)b * CP_MAX_HEADS + 64);
     TCB_WS(ctx, head_boxes, float, rows * 9);
     TCB_WS(ctx, head_scores, float, rows);
     TCB_WS(ctx, head_labels, int, rows);
-    if ((rc = opt_in_smem(ctx, cp_head_kernel))) return rc;
     TCB_KLAUNCH(ctx, cp_head_kernel, dim3(num_heads, b), T, sizeof(FrameShared), st, p, head_boxes, head_scores, head_labels, head_count);
     TCB_LAUNCHED(ctx);
     TCB_KLAUNCH(ctx, cp_concat_kernel, b, 256, 0, st, num_heads, post_max, head_boxes, head_scores, head_labels, head_count, out_boxes_dev,
@@ -835,8 +838,9 @@ extern "C" int tcb_class_score_filter(tcb_ctx* ctx, const long long* labels_dev,
     TCB_WS(ctx, gcls, int, 64);
     TCB_WS(ctx, gthr, float, 64);
     if (n_groups) {
-        TCB_CUDA(ctx, cudaMemcpyAsync(gcls, group_class_host, sizeof(int) * n_groups, cudaMemcpyHostToDevice, st));
-        TCB_CUDA(ctx, cudaMemcpyAsync(gthr, group_thresh_host, sizeof(float) * n_groups, cudaMemcpyHostToDevice, st));
+        int rc;
+        if ((rc = tcb_stage_h2d(ctx, gcls, group_class_host, sizeof(int) * n_groups, st))) return rc;
+        if ((rc = tcb_stage_h2d(ctx, gthr, group_thresh_host, sizeof(float) * n_groups, st))) return rc;
     }
     TCB_KLAUNCH(ctx, class_filter_kernel, 1, 1024, 0, st, labels_dev, scores_dev, n, n_groups, gcls, gthr, out_idx_dev, out_count_dev);
     TCB_LAUNCHED(ctx);

@@ -729,6 +729,23 @@ extern "C" int tcb_copy_rect_d2h(tcb_ctx* ctx, const void* src_dev, void* dst_ho
     return TCB_OK;
 }
 
+static const size_t SMEM_MAX = 100 * 1024, SMEM_GOOD = 36 * 1024;   // tile budgets of tcb_preprocess_image
+typedef void (*kern1_t)(const PreParams);
+typedef void (*kern2_t)(const PreParams, const TileGeo);
+static const kern1_t one_pass[2][2] = {{preprocess_kernel<false, false, false>, preprocess_kernel<false, false, true>},
+                                       {preprocess_kernel<true, false, false>, preprocess_kernel<true, false, true>}};
+static const kern2_t two_pass[2][2][2] = {
+    {{preprocess2_kernel<false, false, false>, preprocess2_kernel<false, false, true>},
+     {preprocess2_kernel<false, true, false>, preprocess2_kernel<false, true, true>}},
+    {{preprocess2_kernel<true, false, false>, preprocess2_kernel<true, false, true>},
+     {preprocess2_kernel<true, true, false>, preprocess2_kernel<true, true, true>}}};
+
+static int init_preprocess(tcb_ctx* ctx) {   // run by tcb_create
+    for (int i = 0; i < 8; i++) TCB_SMEM_OPT_IN(ctx, two_pass[i >> 2][(i >> 1) & 1][i & 1], SMEM_MAX);
+    return TCB_OK;
+}
+static TcbInitReg reg_preprocess(&init_preprocess);
+
 extern "C" int tcb_preprocess_image(tcb_ctx* ctx, const uint8_t* src_dev, int n, int h, int w,
                                     long long src_row_stride, long long src_img_stride, int channel_swap,
                                     int mode, int out_h, int out_w, float div, const float sub[3],
@@ -792,7 +809,6 @@ extern "C" int tcb_preprocess_image(tcb_ctx* ctx, const uint8_t* src_dev, int n,
     p.fast_area = (area || half_x || same_x) && p.vec_store && (((uintptr_t)src_dev & 15) == 0) && (src_row_stride % 16 == 0) &&
                   (n == 1 || src_img_stride % 16 == 0) && (p.left % 4 == 0) && (p.new_w % 4 == 0);
     if (p.fast_area && same_x && !area && !half_x) p.fast_area = 2;
-    const size_t SMEM_MAX = 100 * 1024, SMEM_GOOD = 36 * 1024;
     bool staged = false;
     size_t smem = 0;
     const double sx = area ? 2.0 : p.scale_x, sy = area ? 2.0 : p.scale_y;
@@ -823,15 +839,6 @@ extern "C" int tcb_preprocess_image(tcb_ctx* ctx, const uint8_t* src_dev, int n,
         grid = dim3(tcb_div_up(out_w, TW), tcb_div_up(out_h, p.th), n);
         TCB_REQUIRE(ctx, grid.y <= 65535, "tcb_preprocess_image: output too tall (%d rows)", out_h);
     }
-    typedef void (*kern1_t)(const PreParams);
-    typedef void (*kern2_t)(const PreParams, const TileGeo);
-    static const kern1_t one_pass[2][2] = {{preprocess_kernel<false, false, false>, preprocess_kernel<false, false, true>},
-                                           {preprocess_kernel<true, false, false>, preprocess_kernel<true, false, true>}};
-    static const kern2_t two_pass[2][2][2] = {
-        {{preprocess2_kernel<false, false, false>, preprocess2_kernel<false, false, true>},
-         {preprocess2_kernel<false, true, false>, preprocess2_kernel<false, true, true>}},
-        {{preprocess2_kernel<true, false, false>, preprocess2_kernel<true, false, true>},
-         {preprocess2_kernel<true, true, false>, preprocess2_kernel<true, true, true>}}};
     const bool has_sub = p.sub[0] != 0.f || p.sub[1] != 0.f || p.sub[2] != 0.f;
     if (staged) {
         // source footprint of every tile column / row, with the kernel's own tap arithmetic
@@ -871,8 +878,6 @@ extern "C" int tcb_preprocess_image(tcb_ctx* ctx, const uint8_t* src_dev, int n,
             }
         }
         kern2_t kern = two_pass[area ? 1 : 0][p.exact2 ? 1 : 0][has_sub ? 1 : 0];
-        if (smem > 48 * 1024)  // opt in to > 48 KB dynamic shared memory
-            TCB_CUDA(ctx, cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX));
         TCB_CUDA(ctx, tcb_launch(ctx->pdl != 0, kern, grid, dim3(NTHREADS), smem, st, p, geo));
     } else {
         kern1_t kern = one_pass[area ? 1 : 0][p.exact_recip ? 1 : 0];

@@ -121,4 +121,22 @@ __device__ __forceinline__ float iou_bev(const RBox& a, const RBox& b) {
     return ov / fmaxf(sa + sb - ov, 1e-8f);
 }
 
+// iou_normal (iou3d_nms_kernel.cu:314-325), the predicate of nms_normal_gpu: axis-aligned BEV overlap of (x, y, dx, dy),
+// heading ignored. a is the box of the mask row (the earlier, higher-scoring one), b the later one. The reference has no
+// CPU twin of this function; its CUDA build (nvcc 12.9, sm_100a SASS read back) contracts `Sa + Sb` into one
+// fma(b.dx, b.dy, Sa) with Sa = a.dx * a.dy rounded first, and nothing else — restated with explicit intrinsics.
+__device__ __forceinline__ float iou_normal(const RBox& a, const RBox& b) {
+    const float left = fmaxf(a.x - a.dx / 2, b.x - b.dx / 2), right = fminf(a.x + a.dx / 2, b.x + b.dx / 2);
+    const float top = fmaxf(a.y - a.dy / 2, b.y - b.dy / 2), bottom = fminf(a.y + a.dy / 2, b.y + b.dy / 2);
+    const float width = fmaxf(right - left, 0.f), height = fmaxf(bottom - top, 0.f);
+    const float inter = width * height;
+    const float sa = a.dx * a.dy;
+    return inter / fmaxf(__fmaf_rn(b.dx, b.dy, sa) - inter, 1e-8f);
+}
+
+// the suppression test of nms_gpu (normal == 0) / nms_normal_gpu (normal != 0)
+__device__ __forceinline__ bool overlaps(const RBox& a, const RBox& b, float thresh, int normal) {
+    return (normal ? iou_normal(a, b) : iou_bev(a, b)) > thresh;
+}
+
 }  // namespace rot

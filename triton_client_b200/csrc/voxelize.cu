@@ -849,6 +849,15 @@ extern "C" int tcb_voxelize(tcb_ctx* ctx, const float* pts_dev, int n, const int
     return TCB_OK;
 }
 
+static int init_voxelize(tcb_ctx* ctx) {   // run by tcb_create
+    TCB_SMEM_OPT_IN(ctx, (pillar_decorate_kernel<true, 32, 4>), 200 * 1024);
+    TCB_SMEM_OPT_IN(ctx, (pillar_decorate_kernel<true, 20, 5>), 200 * 1024);
+    TCB_SMEM_OPT_IN(ctx, (pillar_decorate_kernel<true, 0, 0>), 200 * 1024);
+    TCB_SMEM_OPT_IN(ctx, (pillar_decorate_kernel<false, 0, 0>), 200 * 1024);
+    return TCB_OK;
+}
+static TcbInitReg reg_voxelize(&init_voxelize);
+
 extern "C" int tcb_pillar_decorate(tcb_ctx* ctx, const float* voxels_dev, const int* coords_dev, const int* num_pts_dev,
                                    const int* m_dev, int b, int m_max, int max_pts, int nfeat, const double vsize[3],
                                    const double range_min[3], float* out_dev, void* stream) {
@@ -869,7 +878,6 @@ extern "C" int tcb_pillar_decorate(tcb_ctx* ctx, const float* voxels_dev, const 
     auto ctas_of = [&]() { return ctas; };
     const bool vec4 = (nin % 4 == 0) && (nout % 4 == 0) && (((uintptr_t)voxels_dev | (uintptr_t)out_dev) & 15) == 0;
     auto launch = [&](auto kernel) -> int {
-        if (smem > 48 * 1024) TCB_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         TCB_KLAUNCH(ctx, kernel, ctas_of(), 32 * DEC_WARPS, smem, (cudaStream_t)stream, voxels_dev, coords_dev, num_pts_dev, m_dev, b, m_max,
                     max_pts, nfeat, vx, vy, vz, xo, yo, zo, out_dev);
         TCB_LAUNCHED(ctx);

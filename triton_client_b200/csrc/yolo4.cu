@@ -297,6 +297,16 @@ __global__ void __launch_bounds__(256) box_iou_kernel(const float* __restrict__ 
 
 }  // namespace
 
+static int init_yolo4(tcb_ctx* ctx) {   // run by tcb_create
+    TCB_SMEM_OPT_IN(ctx, yolo_head_decode_kernel, 200 * 1024);
+    TCB_SMEM_OPT_IN(ctx, aa_order_kernel, ORDER_CACHE * 8);
+    TCB_SMEM_OPT_IN(ctx, aa_sweep_kernel, sizeof(wide::SweepShared));
+    TCB_SMEM_OPT_IN(ctx, aa_nms_kernel, sizeof(AFrameShared));
+    TCB_SMEM_OPT_IN(ctx, yolo4_nms_kernel, sizeof(AFrameShared));
+    return TCB_OK;
+}
+static TcbInitReg reg_yolo4(&init_yolo4);
+
 extern "C" int tcb_yolo_head_decode(tcb_ctx* ctx, const float* head_dev, int b, int h, int w, int num_anchors, int num_classes,
                                     const float* anchors_host, int variant, double scale_x_y, float stride, int row_offset,
                                     int total_rows, float* boxes_dev, float* confs_dev, float* pred_dev, void* stream) {
@@ -320,7 +330,6 @@ extern "C" int tcb_yolo_head_decode(tcb_ctx* ctx, const float* head_dev, int b, 
     TCB_REQUIRE(ctx, ctas < (1ll << 31), "tcb_yolo_head_decode: head too large");
     const size_t tile_bytes = (size_t)HD_CELLS * (5 + num_classes + 1) * sizeof(float);
     if (tile_bytes > 200 * 1024) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_yolo_head_decode: %d classes exceed the shared-memory tile", num_classes);
-    if (tile_bytes > 48 * 1024) TCB_CUDA(ctx, cudaFuncSetAttribute(yolo_head_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_bytes));
     TCB_KLAUNCH(ctx, yolo_head_decode_kernel, (unsigned)ctas, HD_THREADS, tile_bytes, (cudaStream_t)stream, p);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
@@ -341,13 +350,11 @@ static bool aa_wide_bufs(tcb_ctx* ctx, int sets, AAWide& wb) {
 static int aa_wide_run(tcb_ctx* ctx, int mode, int sets, int n_rows, const float* boxes, const float* scores, const unsigned long long* cand,
                        const int* cand_count, const AAWide& wb, NumpyNmsPred pred, int post_max, int* keep, float* out, int* count,
                        cudaStream_t st) {
-    TCB_CUDA(ctx, cudaFuncSetAttribute(aa_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ORDER_CACHE * 8));
     TCB_KLAUNCH(ctx, aa_order_kernel, sets, T, ORDER_CACHE * 8, st, mode, boxes, scores, n_rows, cand, cand_count, wb.skeys, wb.R, wb.m, count);
     TCB_LAUNCHED(ctx);
     const int nb = tcb_div_up(n_rows < PRE_CAP ? n_rows : PRE_CAP, 64);
     TCB_KLAUNCH(ctx, (wide::tile_mask_kernel<ABox, NumpyNmsPred>), dim3(nb, nb, sets), 64, 0, st, wb.R, wb.m, 1, pred, wb.mask);
     TCB_LAUNCHED(ctx);
-    TCB_CUDA(ctx, cudaFuncSetAttribute(aa_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(wide::SweepShared)));
     TCB_KLAUNCH(ctx, aa_sweep_kernel, sets, wide::SWEEP_T, sizeof(wide::SweepShared), st, mode, wb.mask, wb.skeys, wb.R, wb.m, n_rows, post_max, keep, out, count);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
@@ -363,7 +370,6 @@ extern "C" int tcb_nms_axis_aligned(tcb_ctx* ctx, const float* boxes_dev, const 
     if (n > WIDE_MIN && aa_wide_bufs(ctx, 1, wb))
         return aa_wide_run(ctx, 0, 1, n, boxes_dev, scores_dev, nullptr, nullptr, wb, NumpyNmsPred{thresh, min_mode ? 1 : 0}, post_max, keep_dev, nullptr,
                            count_dev, (cudaStream_t)stream);
-    TCB_CUDA(ctx, cudaFuncSetAttribute(aa_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AFrameShared)));
     TCB_KLAUNCH(ctx, aa_nms_kernel, 1, T, sizeof(AFrameShared), (cudaStream_t)stream, boxes_dev, scores_dev, n, thresh, min_mode ? 1 : 0, post_max, keep_dev, count_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;
@@ -396,7 +402,6 @@ extern "C" int tcb_yolo4_post(tcb_ctx* ctx, const float* boxes_dev, const float*
     AAWide wb;
     if (n > WIDE_MIN && aa_wide_bufs(ctx, b, wb))
         return aa_wide_run(ctx, 1, b, n, boxes_dev, nullptr, cand, cand_count, wb, NumpyNmsPred{nms_thresh, 0}, post_max, nullptr, out_dev, count_dev, st);
-    TCB_CUDA(ctx, cudaFuncSetAttribute(yolo4_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AFrameShared)));
     TCB_KLAUNCH(ctx, yolo4_nms_kernel, b, T, sizeof(AFrameShared), st, boxes_dev, n > 0 ? n : 1, cand, cand_count, nms_thresh, post_max, out_dev, count_dev);
     TCB_LAUNCHED(ctx);
     return TCB_OK;

@@ -993,6 +993,14 @@ size_t yolo_ws_bytes(int b, int n) {
 
 extern "C" size_t tcb_yolo_nms_workspace(int b, int n) { return (b > 0 && n > 0) ? yolo_ws_bytes(b, n) : 0; }
 
+static int init_yolo_post(tcb_ctx* ctx) {   // run by tcb_create
+    TCB_SMEM_OPT_IN(ctx, yolo_filter_stream_kernel<128>, TCB_SMEM_LIMIT);
+    TCB_SMEM_OPT_IN(ctx, yolo_filter_stream_kernel<32>, TCB_SMEM_LIMIT);
+    TCB_SMEM_OPT_IN(ctx, yolo_nms_kernel, NMS_SMEM_BYTES);
+    return TCB_OK;
+}
+static TcbInitReg reg_yolo_post(&init_yolo_post);
+
 extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, int nc, double conf_thres,
                             double iou_thres, const int* classes_host, int n_classes, int agnostic, int max_det,
                             int max_nms, double* out_dev, int* count_dev, int* xc_count_dev, void* stream) {
@@ -1078,7 +1086,7 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
             // FS_NBUF row buffers per warp; as many CTAs as fit, each warp streaming its share of the b * chunks chunks
             const size_t fsm = 8 * FS_WARPS * FS_NBUF + (size_t)FS_WARPS * chunk_rows + (size_t)FS_WARPS * FS_NBUF * chunk_rows * (5 + nc) * sizeof(float);
             auto kernel = chunk_rows == 128 ? yolo_filter_stream_kernel<128> : yolo_filter_stream_kernel<32>;
-            TCB_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsm));
+            if (fsm > (size_t)TCB_SMEM_LIMIT) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_yolo_nms: %d classes exceed the filter's shared-memory rows", nc);
             const int per_sm = (int)((220 * 1024) / (fsm + 1024)) < 4 ? (int)((220 * 1024) / (fsm + 1024)) : 4;
             const long long chunks_total = (long long)b * chunks;
             if (chunks_total >= (1ll << 30)) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_yolo_nms: b*n too large (%d x %d)", b, n);
@@ -1095,7 +1103,6 @@ extern "C" int tcb_yolo_nms(tcb_ctx* ctx, const float* pred_dev, int b, int n, i
         TCB_LAUNCHED(ctx);
     }
     const size_t smem = NMS_SMEM_BYTES;
-    TCB_CUDA(ctx, cudaFuncSetAttribute(yolo_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     TCB_CUDA(ctx, tcb_launch(ctx->pdl != 0, yolo_nms_kernel, dim3(b, G), dim3(NMS_THREADS), smem, st, n > 0 ? n : 1, c_score, c_box, c_meta,
                              c_count, gsort, npad, iou_thres, agnostic ? 0.0 : 4096.0, max_det, max_nms, out_dev, count_dev, go, xc_count,
                              xc_count_dev, chunk_info, chunks, chunk_rows));

@@ -23,6 +23,15 @@ def _need_cuda(*tensors):
             raise TypeError("triton_client_b200.gpu ops take CUDA tensors only (there is no CPU path)")
 
 
+def _nms_type(name):
+    """NMS_CONFIG.NMS_TYPE -> TCB_NMS_GPU / TCB_NMS_NORMAL; the reference resolves the name with
+    getattr(iou3d_nms_utils, NMS_TYPE) (model_nms_utils.py:15), so any other name is an AttributeError there too."""
+    try:
+        return {"nms_gpu": 0, "nms_normal_gpu": 1}[name]
+    except KeyError:
+        raise AttributeError(f"module 'iou3d_nms_utils' has no attribute {name!r}") from None
+
+
 class Engine:
     """A tcb_ctx plus the torch plumbing around it. One per pre/post object (one frame in flight)."""
 
@@ -314,8 +323,8 @@ class Engine:
         self.ctx.call("tcb_rotated_iou", _ptr(a), a.shape[0], _ptr(b), b.shape[0], _ptr(out), _lib.stream_ptr())
         return out
 
-    def rotated_nms(self, boxes, scores, thresh, pre_max=4096, post_max=500):
-        """topk(pre_max) + nms_gpu + [:post_max]. boxes (n,7) + scores (n,) -> (keep int32 [post_max] indices into the
+    def rotated_nms(self, boxes, scores, thresh, pre_max=4096, post_max=500, nms_type="nms_gpu"):
+        """topk(pre_max) + getattr(iou3d_nms_utils, nms_type) + [:post_max] (nms_gpu: rotated, nms_normal_gpu: axis-aligned). boxes (n,7) + scores (n,) -> (keep int32 [post_max] indices into the
         input, count [1]); a batch boxes (b,n,7) + scores (b,n) -> (keep [b,post_max], count [b])."""
         _need_cuda(boxes, scores)
         bx, s = boxes.contiguous().float(), scores.contiguous().float()
@@ -323,13 +332,13 @@ class Engine:
         b, n = (bx.shape[0], bx.shape[1]) if batched else (1, bx.shape[0])
         keep = torch.empty((b, post_max) if batched else (post_max,), dtype=torch.int32, device=bx.device)
         cnt = torch.zeros((b,), dtype=torch.int32, device=bx.device)
-        self.ctx.call("tcb_rotated_nms", _ptr(bx), _ptr(s), b, n, float(thresh), int(pre_max), int(post_max), _ptr(keep), _ptr(cnt),
+        self.ctx.call("tcb_rotated_nms", _ptr(bx), _ptr(s), b, n, float(thresh), _nms_type(nms_type), int(pre_max), int(post_max), _ptr(keep), _ptr(cnt),
                       _lib.stream_ptr())
         return keep, cnt
 
     def pp_anchor_post(self, cls_preds, box_preds, dir_preds, anchor_range, anchor_sizes, anchor_bottoms, anchor_rotations,
                        dir_offset=0.78539, dir_limit_offset=0.0, num_dir_bins=2, score_thresh=0.1, nms_thresh=0.01,
-                       pre_max=4096, post_max=500, out=None):
+                       pre_max=4096, post_max=500, out=None, nms_type="nms_gpu"):
         """PointPillars head outputs of one frame — cls (H,W,A*nc), box (H,W,A*7), dir (H,W,A*bins) or None — or of a
         batch (B,H,W,...). Returns device tensors (boxes [post_max,7], scores [post_max], labels int64 [post_max],
         count [1]), with a leading B on each for a batch (count [B])."""
@@ -355,11 +364,11 @@ class Engine:
         self.ctx.call("tcb_pp_anchor_post", _ptr(cls_preds.contiguous()), _ptr(box_preds.contiguous()),
                       _ptr(dir_preds.contiguous()) if dir_preds is not None else None, b, h, w, nc, nrot, rng, sizes, bots, rots,
                       float(dir_offset), float(dir_limit_offset), int(num_dir_bins), float(score_thresh), float(nms_thresh),
-                      int(pre_max), int(post_max), _ptr(ob), _ptr(osc), _ptr(ol), _ptr(cnt), _lib.stream_ptr())
+                      _nms_type(nms_type), int(pre_max), int(post_max), _ptr(ob), _ptr(osc), _ptr(ol), _ptr(cnt), _lib.stream_ptr())
         return ob, osc, ol, cnt
 
     def centerpoint_post(self, heads, class_id_map, feature_map_stride, voxel_size, point_range, limit_range, k=500,
-                         score_thresh=0.1, nms_thresh=0.2, pre_max=1000, post_max=83, out=None):
+                         score_thresh=0.1, nms_thresh=0.2, pre_max=1000, post_max=83, out=None, nms_type="nms_gpu"):
         """heads: list of dicts with CUDA f32 tensors hm [c,H,W], center [2,H,W], center_z [1,H,W], dim [3,H,W],
         rot [2,H,W], optional vel [2,H,W] — or each with a leading batch dimension [B,...]; class_id_map: list (per head)
         of global 0-based class ids. Returns (boxes [heads*post_max,9], scores, labels int64 1-based, count [1]), with a
@@ -403,7 +412,7 @@ class Engine:
                       ptrs("vel", True) if has_vel else None, ncls, cmap_arr, h, w, int(feature_map_stride),
                       (c_float * 2)(float(voxel_size[0]), float(voxel_size[1])), (c_float * 2)(float(point_range[0]), float(point_range[1])),
                       (c_float * 6)(*[float(v) for v in limit_range]), int(k), float(score_thresh), float(nms_thresh),
-                      int(pre_max), int(post_max), _ptr(ob), _ptr(osc), _ptr(ol), _ptr(cnt), _lib.stream_ptr())
+                      _nms_type(nms_type), int(pre_max), int(post_max), _ptr(ob), _ptr(osc), _ptr(ol), _ptr(cnt), _lib.stream_ptr())
         return ob, osc, ol, cnt
 
     def class_score_filter(self, labels, scores, groups):
