@@ -29,7 +29,15 @@ struct DetParams {
     int num_levels, A, K, variant, topk, max_det, img_h, img_w;
     float score_thresh, nms_thresh;
     int* counts;                               // [b][MAX_LEVELS] candidates per image and level
+    int* hist;                                 // [b][MAX_LEVELS][DET_NB] candidates per score bin (det_bin), det_hist_kernel
+    unsigned hist_base;                        // det_bin: (ordered score bits >> 16) - hist_base, clamped to [0, DET_NB)
 };
+static_assert(sel::THREADS == 1024, "det_level_kernel scans one histogram bin per thread");
+constexpr int DET_NB = 1024;                   // 7 mantissa bits per binade: scores in (0.05, 1] spread over ~560 bins
+__device__ __forceinline__ int det_bin(unsigned long long key, unsigned base) {
+    const int d = (int)((unsigned)(key >> 48)) - (int)base;
+    return d < 0 ? 0 : (d > DET_NB - 1 ? DET_NB - 1 : d);
+}
 // level l of image `img`: the level with its pointers moved to that image
 __device__ __forceinline__ Level level_of(const DetParams& p, int l, int img, int*& count) {
     Level L = p.lv[l];
@@ -51,13 +59,29 @@ __device__ __forceinline__ Level level_of(const DetParams& p, int l, int img, in
 // of per-lane counts, no per-element vote) and the sigmoid, the exact `> thresh` test and the key are then computed over
 // the list with the lanes packed. Keys collect in a per-warp pending list that is flushed with ONE reservation on the
 // (image, level) counter when it fills or the warp moves on to another image or level.
-constexpr int DC_Q = 4;                                   // 16-byte copies per lane and span
+#ifndef TCB_DC_Q
+#define TCB_DC_Q 8
+#endif
+#ifndef TCB_DC_WARPS
+#define TCB_DC_WARPS 8
+#endif
+constexpr int DC_Q = TCB_DC_Q;                            // 16-byte copies per lane and span
 constexpr int DC_SPAN = 32 * 4 * DC_Q;                    // logits per span (one warp)
-constexpr int DC_WARPS = 8;
+constexpr int DC_WARPS = TCB_DC_WARPS;
 constexpr int DC_PEND = 128;                              // pending keys per warp
 constexpr int DC_NBUF = 2;                                // span buffers per warp: one copy in flight behind the span being filtered (three buffers and
                                                           // fewer resident warps measured slower: 362 vs 311 us for 16 RetinaNet images)
-struct DetSpans { int first[MAX_LEVELS + 1]; int per_image[MAX_LEVELS]; };   // span list: level-major, then image, then span
+struct DetSpans {                                         // span list: level-major, then image, then span
+    int first[MAX_LEVELS + 1]; int per_image[MAX_LEVELS];
+    float inv_per_image[MAX_LEVELS], inv_hw[MAX_LEVELS], inv_k;   // reciprocals for divmod_small
+};
+// n / d for 0 <= n < 2^30 and a quotient below 2^16: the float product is off by at most one, which the remainder shows
+__device__ __forceinline__ int divmod_small(int n, int d, float inv_d, int& rem) {
+    int q = (int)((float)n * inv_d);
+    rem = n - q * d;
+    if (rem < 0) { q--; rem += d; } else if (rem >= d) { q++; rem -= d; }
+    return q;
+}
 struct DcWarp {                                           // a warp's slice of shared memory
     float buf[DC_NBUF][DC_SPAN];
     unsigned long long pend[DC_PEND];
@@ -81,7 +105,8 @@ __global__ void __launch_bounds__(32 * DC_WARPS) det_candidates_kernel(const Det
     auto item_of = [&](int it) {
         int l = 0;
         while (it >= W.first[l + 1]) l++;
-        const int r = it - W.first[l], img = r / W.per_image[l], sp = r - img * W.per_image[l];
+        int sp;
+        const int img = divmod_small(it - W.first[l], W.per_image[l], W.inv_per_image[l], sp);
         const int n_img = p.A * p.K * p.lv[l].H * p.lv[l].W;     // < 2^30 (checked on the host)
         Item q;
         q.level = l; q.img = img; q.flat0 = sp * DC_SPAN;
@@ -92,13 +117,18 @@ __global__ void __launch_bounds__(32 * DC_WARPS) det_candidates_kernel(const Det
     // lane t copies the DC_Q groups of 4 floats at (g * 32 + t) * 4: whole 16-byte groups inside the span asynchronously, a
     // ragged or unaligned group with plain loads
     auto issue = [&](const Item& q, float* dst) {
+        if (q.n == DC_SPAN && (((uintptr_t)q.src) & 15) == 0) {      // a whole aligned span (all but the last of an image): uniform over the warp
 #pragma unroll
-        for (int g = 0; g < DC_Q; g++) {
-            const int e = (g * 32 + lane) * 4;
-            if (e + 3 < q.n && ((((uintptr_t)(q.src + e)) & 15) == 0)) dc_copy16(dst + e, q.src + e);
-            else {
+            for (int g = 0; g < DC_Q; g++) dc_copy16(dst + (g * 32 + lane) * 4, q.src + (g * 32 + lane) * 4);
+        } else {
 #pragma unroll
-                for (int j = 0; j < 4; j++) dst[e + j] = e + j < q.n ? __ldg(q.src + e + j) : -INFINITY;
+            for (int g = 0; g < DC_Q; g++) {
+                const int e = (g * 32 + lane) * 4;
+                if (e + 3 < q.n && ((((uintptr_t)(q.src + e)) & 15) == 0)) dc_copy16(dst + e, q.src + e);
+                else {
+#pragma unroll
+                    for (int j = 0; j < 4; j++) dst[e + j] = e + j < q.n ? __ldg(q.src + e + j) : -INFINITY;
+                }
             }
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
@@ -130,17 +160,21 @@ __global__ void __launch_bounds__(32 * DC_WARPS) det_candidates_kernel(const Det
         } else {
             asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
-        float x[DC_Q][4];
-#pragma unroll
-        for (int g = 0; g < DC_Q; g++) {
-            const float4 v = *reinterpret_cast<const float4*>(&S.buf[stage][(g * 32 + lane) * 4]);   // what this lane copied itself
-            x[g][0] = v.x; x[g][1] = v.y; x[g][2] = v.z; x[g][3] = v.w;
-        }
+        // bit (g & 7) * 4 + j of word g >> 3: the lane's element j of copy group g lies above the floor
+        unsigned above[(DC_Q + 7) / 8];
         int mine = 0;
 #pragma unroll
-        for (int g = 0; g < DC_Q; g++)
+        for (int w8 = 0; w8 < (DC_Q + 7) / 8; w8++) {
+            unsigned m = 0u;
 #pragma unroll
-            for (int j = 0; j < 4; j++) mine += (x[g][j] > logit_floor);
+            for (int g = w8 * 8; g < DC_Q && g < w8 * 8 + 8; g++) {
+                const float4 v = *reinterpret_cast<const float4*>(&S.buf[stage][(g * 32 + lane) * 4]);   // what this lane copied itself
+                m |= (v.x > logit_floor ? 1u : 0u) << ((g & 7) * 4) | (v.y > logit_floor ? 2u : 0u) << ((g & 7) * 4) |
+                     (v.z > logit_floor ? 4u : 0u) << ((g & 7) * 4) | (v.w > logit_floor ? 8u : 0u) << ((g & 7) * 4);
+            }
+            above[w8] = m;
+            mine += __popc(m);
+        }
         int inc = mine;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += t; }
@@ -148,17 +182,18 @@ __global__ void __launch_bounds__(32 * DC_WARPS) det_candidates_kernel(const Det
         if (total > 0) {                                   // uniform over the warp
             if (pend_n && (pend_img != cur.img || pend_level != cur.level)) flush();
             pend_img = cur.img; pend_level = cur.level;
-            float* l_val = S.buf[stage];                   // every lane holds its part of the span in registers by now
-            __syncwarp();
-            int o = inc - mine;
-            if (mine) {
+            int o = inc - mine;                            // the list holds positions only; values are read back from the span buffer
 #pragma unroll
-                for (int g = 0; g < DC_Q; g++)
-#pragma unroll
-                    for (int j = 0; j < 4; j++)
-                        if (x[g][j] > logit_floor) { l_val[o] = x[g][j]; S.l_pos[o] = (unsigned short)((g * 32 + lane) * 4 + j); o++; }
+            for (int w8 = 0; w8 < (DC_Q + 7) / 8; w8++) {
+                unsigned m = above[w8];
+                while (m) {
+                    const int bit = __ffs(m) - 1;
+                    m &= m - 1u;
+                    S.l_pos[o++] = (unsigned short)((((w8 * 8 + (bit >> 2)) * 32 + lane) << 2) + (bit & 3));
+                }
             }
             __syncwarp();
+            const float* l_buf = S.buf[stage];
             const Level& L = p.lv[cur.level];
             const int HW = L.H * L.W;
             for (int r0 = 0; r0 < total; r0 += 32) {       // the list, lanes packed: score, exact threshold, key
@@ -166,10 +201,12 @@ __global__ void __launch_bounds__(32 * DC_WARPS) det_candidates_kernel(const Det
                 bool ok = false;
                 unsigned long long key = 0ull;
                 if (e < total) {
-                    const int flat = cur.flat0 + S.l_pos[e];               // (channel, location) inside the image's tensor
-                    const int ch = flat / HW, sp = flat - ch * HW;
-                    const int a = ch / p.K, k = ch - a * p.K;
-                    float sc = sigmoidf_ref(l_val[e]);
+                    const int pos = S.l_pos[e];
+                    const int flat = cur.flat0 + pos;                      // (channel, location) inside the image's tensor
+                    int sp, k;
+                    const int ch = divmod_small(flat, HW, W.inv_hw[cur.level], sp);
+                    const int a = divmod_small(ch, p.K, W.inv_k, k);
+                    float sc = sigmoidf_ref(l_buf[pos]);
                     if (p.variant == 1) sc = sqrtf(sc * sigmoidf_ref(__ldg(L.ctrness + (long long)cur.img * HW + sp)));   // FCOS: sqrt(cls * centerness)
                     ok = sc > p.score_thresh;
                     key = sel::make_key(sc, (unsigned)(((long long)sp * p.A + a) * p.K + k));
@@ -181,11 +218,33 @@ __global__ void __launch_bounds__(32 * DC_WARPS) det_candidates_kernel(const Det
                     pend_n += __popc(em);
                 }
             }
-            __syncwarp();                                  // the list (in buf[stage]) is rewritten by the copy issued in the next iteration
+            __syncwarp();                                  // buf[stage] is rewritten by the copy issued in the next iteration
         }
         cur = next;
     }
     flush();
+}
+
+// Score histogram of every (image, level) candidate list (det_bin bins), DH_SPLIT CTAs per list: shared-memory counts,
+// then one global add per non-empty bin. The lists are a few tens of MB and still in L2.
+constexpr int DH_SPLIT = 16, DH_T = 256;
+__global__ void __launch_bounds__(DH_T) det_hist_kernel(const DetParams p) {
+    pdl_wait();
+    __shared__ int h[DET_NB];
+    const int l = blockIdx.y, img = blockIdx.z, tid = threadIdx.x;
+    int* cand_count;
+    const Level L = level_of(p, l, img, cand_count);
+    const int n = min(*cand_count, p.A * p.K * L.H * L.W);
+    if (n <= p.topk) return;                                  // det_level_kernel sorts such a list as it is
+    for (int i = tid; i < DET_NB; i += DH_T) h[i] = 0;
+    __syncthreads();
+    const int per = (n + DH_SPLIT - 1) / DH_SPLIT, lo = blockIdx.x * per, hi = min(n, lo + per);
+#pragma unroll 4
+    for (int i = lo + tid; i < hi; i += DH_T) atomicAdd(&h[det_bin(L.cand[i], p.hist_base)], 1);
+    __syncthreads();
+    int* hist = p.hist + (img * MAX_LEVELS + l) * DET_NB;
+    for (int i = tid; i < DET_NB; i += DH_T)
+        if (h[i]) atomicAdd(hist + i, h[i]);
 }
 
 struct ABox { float x1, y1, x2, y2, area; int cls; };
@@ -237,8 +296,36 @@ __global__ void __launch_bounds__(T, 1) det_level_kernel(const DetParams p, floa
         const int cap = p.A * p.K * L.H * L.W;
         const int n = min(*cand_count, cap);
         const unsigned long long* ck = L.cand;
+        // The score histogram the candidate pass left behind names the bin of the topk-th score at once: one pass over the
+        // candidates keeps the keys of that bin and above (topk + one bin's worth) in shared memory, and the selection runs
+        // over those instead of sweeping all n keys once per radix digit.
+        int n_sel = n, use_cache = 0;
+        if (n > p.topk) {
+            const int* hist = p.hist + (img * MAX_LEVELS + l) * DET_NB;
+            const int bin = DET_NB - 1 - tid;                         // thread t owns bin DET_NB-1-t: scan from the top bin downwards
+            const int hcount = hist[bin];
+            int total;
+            const int above = sel::cta_exclusive_scan(hcount, S.sel.warp_tot, total);
+            if (above < p.topk && p.topk <= above + hcount) { S.sel.digit = bin; S.sel.above = above + hcount; }
+            if (tid == 0) S.sel.count = 0;
+            __syncthreads();
+            const int cut = S.sel.digit, want = S.sel.above;         // keys in bins >= cut: want of them, topk <= want
+            if (total == n && want <= DET_CACHE) {
+#pragma unroll 8
+                for (int i = tid; i < n; i += T) {
+                    const unsigned long long k = ck[i];
+                    if (det_bin(k, p.hist_base) >= cut) key_cache[atomicAdd(&S.sel.count, 1)] = k;
+                }
+                __syncthreads();
+                n_sel = S.sel.count;                                 // == want
+                use_cache = 1;
+            }
+            __syncthreads();
+        }
         auto key_of = [&](int i) { return ck[i]; };
-        const int m = sel::cta_topk_sorted(key_of, n, p.topk, S.skeys, S.sel, key_cache, DET_CACHE);
+        auto key_of_cache = [&](int i) { return key_cache[i]; };
+        const int m = use_cache ? sel::cta_topk_sorted(key_of_cache, n_sel, p.topk, S.skeys, S.sel)
+                                : sel::cta_topk_sorted(key_of, n, p.topk, S.skeys, S.sel, key_cache, DET_CACHE);
         const int HW = L.H * L.W;
         for (int c = tid; c < m; c += T) {
             const unsigned long long key = S.skeys[c];
@@ -338,7 +425,7 @@ static TcbInitReg reg_detectron(&init_detectron);
 
 extern "C" size_t tcb_detectron_post_workspace(int b, int num_levels, const int* h, const int* w, int num_anchors, int num_classes, int topk) {
     const size_t bb = (size_t)(b > 0 ? b : 1);
-    size_t bytes = 8192 + bb * MAX_LEVELS * 4;
+    size_t bytes = 8192 + bb * MAX_LEVELS * 4 * (1 + DET_NB);
     for (int l = 0; l < num_levels; l++) bytes += bb * (size_t)h[l] * w[l] * num_anchors * num_classes * 8 + 512;
     bytes += bb * (size_t)num_levels * (size_t)topk * (16 + 4 + 4 + 8) + 2048;
     return bytes;
@@ -359,14 +446,22 @@ extern "C" int tcb_detectron_post(tcb_ctx* ctx, int b, int num_levels, const flo
     if ((long long)b * num_levels > 65535) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_detectron_post: images x levels > 65535");
     if (topk > PRE_CAP || (long long)topk * num_levels > 16384) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_detectron_post: topk %d too large", topk);
     if (max_det > POST_CAP) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_detectron_post: max_det %d > %d", max_det, POST_CAP);
+    if ((long long)num_anchors * num_classes > 65535) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_detectron_post: anchors x classes > 65535");
     cudaStream_t st = (cudaStream_t)stream;
     DetParams p;
     memset(&p, 0, sizeof(p));
     p.num_levels = num_levels; p.A = num_anchors; p.K = num_classes; p.variant = variant; p.topk = topk; p.max_det = max_det;
     p.img_h = img_h; p.img_w = img_w; p.score_thresh = score_thresh; p.nms_thresh = nms_thresh;
-    TCB_WS(ctx, counts, int, (size_t)b * MAX_LEVELS);
-    TCB_CUDA(ctx, cudaMemsetAsync(counts, 0, sizeof(int) * (size_t)b * MAX_LEVELS, st));
+    TCB_WS(ctx, counts, int, (size_t)b * MAX_LEVELS * (1 + DET_NB));           // counts, then the score histograms
+    TCB_CUDA(ctx, cudaMemsetAsync(counts, 0, sizeof(int) * (size_t)b * MAX_LEVELS * (1 + DET_NB), st));
     p.counts = counts;
+    p.hist = counts + (size_t)b * MAX_LEVELS;
+    {
+        float t = score_thresh;                                                  // FCOS scores are sqrt(cls * ctr) > thresh too
+        unsigned u;
+        memcpy(&u, &t, 4);
+        p.hist_base = ((u & 0x80000000u) ? ~u : (u | 0x80000000u)) >> 16;
+    }
     for (int l = 0; l < num_levels; l++) {
         Level& L = p.lv[l];
         L.logits = logits_dev[l]; L.deltas = deltas_dev[l]; L.ctrness = ctrness_dev ? ctrness_dev[l] : nullptr;
@@ -394,16 +489,24 @@ extern "C" int tcb_detectron_post(tcb_ctx* ctx, int b, int num_levels, const flo
         for (int l = 0; l < num_levels; l++) {
             W.first[l] = (int)items;
             W.per_image[l] = tcb_div_up((long long)num_anchors * num_classes * p.lv[l].H * p.lv[l].W, DC_SPAN);
+            W.inv_per_image[l] = 1.0f / (float)W.per_image[l];
+            W.inv_hw[l] = 1.0f / (float)(p.lv[l].H * p.lv[l].W);
             items += (long long)W.per_image[l] * b;
             if (items > (1ll << 30)) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_detectron_post: batch too large");
         }
         W.first[num_levels] = (int)items;
+        W.inv_k = 1.0f / (float)num_classes;
         const size_t dc_smem = sizeof(DcWarp) * DC_WARPS;      // 48 KB: four CTAs per SM
         const long long want = tcb_div_up(items, DC_WARPS);
-        const int ctas = (int)(want < (long long)ctx->num_sms * 4 ? want : (long long)ctx->num_sms * 4);
+        int per_sm = (int)((220 * 1024) / (dc_smem + 1024));   // resident CTAs per SM (shared memory; 64 registers x 256 threads allow 4)
+        per_sm = per_sm < 1 ? 1 : (per_sm > 2048 / (32 * DC_WARPS) ? 2048 / (32 * DC_WARPS) : per_sm);
+        if (per_sm * DC_WARPS > 32) per_sm = 32 / DC_WARPS;
+        const int ctas = (int)(want < (long long)ctx->num_sms * per_sm ? want : (long long)ctx->num_sms * per_sm);
         TCB_KLAUNCH(ctx, det_candidates_kernel, ctas, 32 * DC_WARPS, dc_smem, st, p, W, logit_floor);
         TCB_LAUNCHED(ctx);
     }
+    TCB_KLAUNCH(ctx, det_hist_kernel, dim3(DH_SPLIT, num_levels, b), DH_T, 0, st, p);
+    TCB_LAUNCHED(ctx);
     TCB_KLAUNCH(ctx, det_level_kernel, dim3(num_levels, b), T, DET_CACHE * 8, st, p, mbox, mscore, mcls, mkeys);
     TCB_LAUNCHED(ctx);
     TCB_KLAUNCH(ctx, det_post_kernel, b, T, sizeof(DFrameShared), st, p, mbox, mscore, mcls, mkeys, out_boxes_dev, out_scores_dev, out_classes_dev, out_count_dev);
