@@ -105,66 +105,81 @@ struct OrderShared {
     sel::Scratch sel;
 };
 
-// Mask, step 1: per 64x64 tile of the upper triangle, the cheap distance test. Pairs it cannot rule out go to a global
-// list (one slot reservation per tile) for rot_pairs_kernel; the tile's mask words are written as zeros. Should the
-// list be full, the tile evaluates its pairs itself.
+// Mask, step 1: the cheap distance test of every pair of the upper triangle. A CTA takes 64 rows x 256 columns: thread =
+// (row, 64-column block) keeps its row in registers, walks the block's columns (x, y, radius + margin as one float4
+// each, broadcast from shared memory) and collects the pairs it cannot rule out as a 64-bit word — no votes, no atomics
+// in the loop. Those pairs go to a global list (one slot reservation per CTA) for rot_pairs_kernel; the mask words are
+// written as zeros. Should the list be full, the thread evaluates its pairs itself.
 // m_dev[0] = number of candidates, m_dev[1] = pairs listed so far (zeroed by the order kernel).
 // blockIdx.z = candidate set of the batch; per-set strides: PRE_CAP boxes, WIDE_M ints, mask_stride words, pair_cap pairs
 constexpr int WIDE_M = 64;   // ints per set in the m array ([0] candidates, [1] pairs listed)
+constexpr int MASK_COLS = MASK_T;   // columns per CTA: MASK_T / 64 blocks of 64
 __global__ void __launch_bounds__(MASK_T) rot_mask_kernel(const rot::RBox* __restrict__ R, int* __restrict__ m_dev, float thresh, int normal,
                                                           unsigned long long* __restrict__ mask, size_t mask_stride, unsigned* __restrict__ pairs, int pair_cap) {
     pdl_wait();
     R += (size_t)blockIdx.z * PRE_CAP; m_dev += blockIdx.z * WIDE_M; mask += blockIdx.z * mask_stride; pairs += (size_t)blockIdx.z * pair_cap;
-    const int bi = blockIdx.y, bj = blockIdx.x;   // row tile, column tile
+    const int bi = blockIdx.y, c0 = blockIdx.x * MASK_COLS;   // row block, first column
     const int m = m_dev[0];
-    if (bj < bi || bj * 64 >= m) return;          // lower triangle / past the last candidate: never read
-    __shared__ rot::RBox rows[64], cols[64];
-    __shared__ unsigned long long tmask[64];
-    __shared__ unsigned short queue[64 * 64];
-    __shared__ int qn, qbase;
-    const int tid = threadIdx.x, lane = tid & 31;
-    if (tid < 64) {
-        const int g = bi * 64 + tid;
-        if (g < m) rows[tid] = R[g];
-        tmask[tid] = 0ull;
-    } else if (tid < 128) {
-        const int g = bj * 64 + tid - 64;
-        if (g < m) cols[tid - 64] = R[g];
-    }
-    if (tid == 0) qn = 0;
-    __syncthreads();
-    for (int e = tid; e < 64 * 64; e += MASK_T) {
-        const int i = e >> 6, j = e & 63;
-        const int gi = bi * 64 + i, gj = bj * 64 + j;
-        const bool near = gj > gi && gj < m && !rot::far_apart(rows[i], cols[j]);
-        const unsigned bal = __ballot_sync(0xffffffffu, near);
-        if (bal) {
-            int base = 0;
-            if (lane == 0) base = atomicAdd(&qn, __popc(bal));
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if (near) queue[base + __popc(bal & ((1u << lane) - 1))] = (unsigned short)e;
-        }
+    if (c0 + MASK_COLS <= bi * 64 || c0 >= m || bi * 64 >= m) return;   // wholly below the diagonal / past the last candidate: never read
+    __shared__ float4 cols[MASK_COLS];
+    __shared__ int warp_tot[MASK_T / 32];
+    __shared__ int qbase;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    {
+        const int g = c0 + tid;
+        float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (g < m) { const rot::RBox b = R[g]; c = make_float4(b.x, b.y, b.r + 0.05f, 0.f); }
+        cols[tid] = c;
     }
     __syncthreads();
-    const int nq = qn;
-    if (tid == 0) qbase = nq ? atomicAdd(&m_dev[1], nq) : 0;
-    __syncthreads();
-    const int base = qbase;
-    if (base + nq <= pair_cap) {
-        for (int q = tid; q < nq; q += MASK_T) {
-            const int e = queue[q];
-            pairs[base + q] = ((unsigned)(bi * 64 + (e >> 6)) << 16) | (unsigned)(bj * 64 + (e & 63));
+    const int r = tid & 63, q = tid >> 6;
+    const int gi = bi * 64 + r, bj = (c0 >> 6) + q;           // this thread's row and column block
+    unsigned lo = 0u, hi = 0u;
+    const bool live = gi < m && bj >= bi && bj * 64 < m;
+    if (live) {
+        const float ax = R[gi].x, ay = R[gi].y, ar = R[gi].r;
+        const float4* cb = cols + q * 64;
+#pragma unroll
+        for (int j = 0; j < 32; j++) {                        // far apart (rot::far_apart): squared distance > (ra + rb + 0.05)^2
+            const float4 c = cb[j], d = cb[j + 32];
+            const float x0 = ax - c.x, y0 = ay - c.y, l0 = ar + c.z, x1 = ax - d.x, y1 = ay - d.y, l1 = ar + d.z;
+            if (!(x0 * x0 + y0 * y0 > l0 * l0)) lo |= 1u << j;
+            if (!(x1 * x1 + y1 * y1 > l1 * l1)) hi |= 1u << j;
         }
-    } else {   // list full: blank whatever part of the reservation lies inside it, evaluate here
-        for (int q = tid; q < nq; q += MASK_T) {
-            if (base + q < pair_cap) pairs[base + q] = 0xffffffffu;
-            const int e = queue[q];
-            const int i = e >> 6, j = e & 63;
-            if (rot::overlaps(rows[i], cols[j], thresh, normal)) atomicOr(&tmask[i], 1ull << j);
+        const int left = m - bj * 64;                         // columns of this block that exist
+        if (left < 64) { if (left <= 32) { hi = 0u; lo &= (left == 32 ? 0xffffffffu : ((1u << left) - 1u)); } else hi &= (1u << (left - 32)) - 1u; }
+        if (bj == bi) {                                       // diagonal block: columns after the row only
+            if (r < 32) lo &= (r == 31 ? 0u : ~((2u << r) - 1u));
+            else { lo = 0u; hi &= (r == 63 ? 0u : ~((2u << (r - 32)) - 1u)); }
         }
-        __syncthreads();
     }
-    if (tid < 64 && bi * 64 + tid < m) mask[(size_t)(bi * 64 + tid) * MW + bj] = tmask[tid];
+    // slots for the CTA's pairs: exclusive scan of the per-thread counts, one reservation on the set's counter
+    const int nq = __popc(lo) + __popc(hi);
+    int inc = nq;
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, s); if (lane >= s) inc += t; }
+    if (lane == 31) warp_tot[warp] = inc;
+    __syncthreads();
+    if (tid == 0) {
+        int tot = 0;
+#pragma unroll
+        for (int w = 0; w < MASK_T / 32; w++) { const int t = warp_tot[w]; warp_tot[w] = tot; tot += t; }
+        qbase = tot ? atomicAdd(&m_dev[1], tot) : 0;
+    }
+    __syncthreads();
+    if (!live) return;
+    int at = qbase + warp_tot[warp] + inc - nq;
+    unsigned long long word = 0ull;
+    unsigned long long near = ((unsigned long long)hi << 32) | lo;
+    while (near) {
+        const int j = __ffsll((long long)near) - 1;
+        near &= near - 1ull;
+        const int gj = bj * 64 + j;
+        if (at < pair_cap) pairs[at] = ((unsigned)gi << 16) | (unsigned)gj;
+        else if (rot::overlaps(R[gi], R[gj], thresh, normal)) word |= 1ull << j;   // list full: evaluated here
+        at++;
+    }
+    mask[(size_t)gi * MW + bj] = word;
 }
 
 // Mask, step 2: the exact rotated IoU of every listed pair, one pair per thread with all lanes busy (inside the tiles
@@ -670,7 +685,7 @@ static bool wide_bufs(tcb_ctx* ctx, int m_max, int sets, WideBufs& wb) {
 // mask (tiles + listed pairs) of `sets` ordered candidate sets already in wb.R / wb.m
 static int wide_mask(tcb_ctx* ctx, const WideBufs& wb, int m_max, int sets, float thresh, int normal, cudaStream_t st) {
     const int nb = tcb_div_up(m_max, 64);
-    TCB_KLAUNCH(ctx, rot_mask_kernel, dim3(nb, nb, sets), MASK_T, 0, st, wb.R, wb.m, thresh, normal, wb.mask, wb.mask_stride, wb.pairs, wb.pair_cap);
+    TCB_KLAUNCH(ctx, rot_mask_kernel, dim3(tcb_div_up(nb * 64, MASK_COLS), nb, sets), MASK_T, 0, st, wb.R, wb.m, thresh, normal, wb.mask, wb.mask_stride, wb.pairs, wb.pair_cap);
     TCB_LAUNCHED(ctx);
     const int per = sets > 1 ? tcb_div_up(ctx->num_sms * 8, sets) : ctx->num_sms * 8;
     TCB_KLAUNCH(ctx, rot_pairs_kernel, dim3(per, sets), 256, 0, st, wb.R, wb.m, thresh, normal, wb.pairs, wb.pair_cap, wb.mask, wb.mask_stride);
