@@ -173,3 +173,18 @@ def test_errors_are_returned_not_fatal(engine):
         engine.preprocess_images(src, 2, 2, mode="pad")
     out, _ = engine.preprocess_images(src, 8, 8)  # context still usable afterwards
     assert out.shape == (1, 3, 8, 8)
+
+
+@pytest.mark.parametrize("h,w", [(800, 1333), (36, 53), (37, 53), (64, 64), (3, 4)])
+def test_same_size_frames_flat_path(engine, h, w):
+    """Output the size of the source (FCOS / RetinaNet image_adjust on model-sized frames): a flat u8 HWC -> f32 CHW stream
+    when the pixel count is a multiple of 4, the tiled kernel otherwise; every normalisation, channel swap, several frames."""
+    imgs = [synth.image_noise(h, w, 300 + i) for i in range(3)]
+    for div, sub, swap in [(1.0, None, False), (255.0, None, False), (127.5, (1, 1, 1), True), (1.0, (123, 117, 104), True), (3.1, (0.5, 0, 2), False)]:
+        got, _ = _run(engine, imgs, h, w, mode="stretch", div=div, sub=sub, swap=swap)
+        for i, img in enumerate(imgs):
+            want = pre2d.preprocess_frame(img, h, w, mode="stretch", swap=swap, div=div, sub=sub or (0.0, 0.0, 0.0))
+            assert np.array_equal(got[i:i + 1], want), (h, w, div, sub, swap, i)
+    for mode in ("letterbox", "pad"):     # the other modes at the same size are the identity too
+        got, _ = _run(engine, imgs[:1], h, w, mode=mode, div=255.0, pad_value=114)
+        assert np.array_equal(got, pre2d.preprocess_frame(imgs[0], h, w, mode=mode, div=255.0, pad_value=114))

@@ -510,6 +510,43 @@ __device__ __forceinline__ void pass_ident(const PreParams& p, const uint8_t* __
     }
 }
 
+// Output the size of the source, nothing padded, packed rows: cv2.resize is then the identity (x and y taps (2048, 0)) and
+// image_adjust is u8 HWC -> normalised f32 CHW of one flat pixel array per frame, whatever the row length (FCOS /
+// RetinaNet frames are 1333 wide: their rows are not 16-byte aligned, the planes are). Thread = 4 consecutive pixels =
+// three aligned 4-byte loads (12 B stride across the lanes), one 16-byte store per plane (512 B contiguous per warp).
+#ifndef TCB_FLAT_UNROLL
+#define TCB_FLAT_UNROLL 4
+#endif
+constexpr int FLAT_UNROLL = TCB_FLAT_UNROLL;
+template <bool EXACT, bool HAS_SUB>
+__global__ void __launch_bounds__(256) preprocess_flat_kernel(const PreParams p) {
+    pdl_enter();
+    const long long plane = (long long)p.out_h * p.out_w, groups = plane >> 2;     // groups of 4 pixels (plane % 4 == 0)
+    const unsigned* src = reinterpret_cast<const unsigned*>(p.src + (long long)blockIdx.y * p.img_stride);
+    float* dst = p.dst + (long long)blockIdx.y * 3 * plane;
+    const long long g0 = ((long long)blockIdx.x * FLAT_UNROLL) * 256 + threadIdx.x;
+    unsigned w[FLAT_UNROLL][3];
+#pragma unroll
+    for (int u = 0; u < FLAT_UNROLL; u++) {
+        const long long g = g0 + u * 256;
+        if (g < groups) { w[u][0] = __ldg(src + 3 * g); w[u][1] = __ldg(src + 3 * g + 1); w[u][2] = __ldg(src + 3 * g + 2); }   // the three loads of a warp share their lines: through L1
+    }
+#pragma unroll
+    for (int u = 0; u < FLAT_UNROLL; u++) {
+        const long long g = g0 + u * 256;
+        if (g >= groups) break;
+        float o[3][4];
+#pragma unroll
+        for (int e = 0; e < 12; e++) {                                // byte e = pixel e/3, channel e%3
+            const unsigned v = __byte_perm(w[u][e >> 2], 0u, 0x4440u | (unsigned)(e & 3));
+            const int c = e % 3, k = e / 3;
+            o[c][k] = norm2<EXACT, HAS_SUB>((int)v, p.div, p.rdiv, p.rlo, p.sub[p.swap ? 2 - c : c]);
+        }
+#pragma unroll
+        for (int c = 0; c < 3; c++) st_stream_f4(dst + (p.swap ? 2 - c : c) * plane + 4 * g, make_float4(o[c][0], o[c][1], o[c][2], o[c][3]));
+    }
+}
+
 template <bool AREA, bool EXACT, bool HAS_SUB>
 __global__ void __launch_bounds__(NTHREADS) preprocess2_kernel(const PreParams p, const TileGeo geo) {
     extern __shared__ __align__(16) uint8_t smem[];
@@ -800,6 +837,20 @@ extern "C" int tcb_preprocess_image(tcb_ctx* ctx, const uint8_t* src_dev, int n,
         p.padv[c] = (float)pad_value / div - p.sub[c];
     }
     p.vec_store = (out_w % 4 == 0) && (((uintptr_t)dst_dev & 15) == 0);
+
+    const bool has_sub_any = p.sub[0] != 0.f || p.sub[1] != 0.f || p.sub[2] != 0.f;
+    if (h == out_h && w == out_w && p.new_h == h && p.new_w == w && p.left == 0 && p.top == 0 && src_row_stride == (long long)w * 3 &&
+        ((long long)h * w) % 4 == 0 && (((uintptr_t)src_dev) & 3) == 0 && (n == 1 || src_img_stride % 4 == 0) && (((uintptr_t)dst_dev) & 15) == 0) {
+        // same size, packed rows: a flat stream per frame (preprocess_flat_kernel)
+        typedef void (*kernf_t)(const PreParams);
+        static const kernf_t flat[2][2] = {{preprocess_flat_kernel<false, false>, preprocess_flat_kernel<false, true>},
+                                           {preprocess_flat_kernel<true, false>, preprocess_flat_kernel<true, true>}};
+        const long long groups = ((long long)h * w) >> 2;
+        TCB_CUDA(ctx, tcb_launch(ctx->pdl != 0, flat[p.exact2 ? 1 : 0][has_sub_any ? 1 : 0], dim3(tcb_div_up(groups, 256 * FLAT_UNROLL), n), dim3(256), 0,
+                                 (cudaStream_t)stream, p));
+        TCB_LAUNCHED(ctx);
+        return TCB_OK;
+    }
 
     // Tile height: the largest of 32/16/8 output rows whose shared-memory need (staged source bytes + 16-bit row
     // buffer + tap tables) stays <= 36 KB, so that six CTAs fit an SM; failing that the largest that fits 100 KB;
