@@ -259,67 +259,146 @@ struct PPParams {
 __device__ __forceinline__ float sigmoidf_ref(float x) { return 1.f / (1.f + expf(-x)); }  // torch.sigmoid
 
 // per anchor: sigmoid of every class logit, max (detector3d_template.py:217,251), keep score >= thresh.
-// grid (tiles of PPC_TILE anchors, frame). The tile's logits come in with 16-byte loads into shared memory (an anchor's
-// row is num_class floats: 12 bytes for KITTI), then a thread takes every 256th anchor of the tile.
-constexpr int PPC_TILE = 1024;
-template <bool VEC4>
-__global__ void __launch_bounds__(256) pp_candidates_kernel(const float* __restrict__ cls, int n_anchors, int num_class, float thresh, float logit_floor,
-                                                            unsigned long long* __restrict__ cand, int* __restrict__ cand_count) {
-    extern __shared__ __align__(16) float ppc_tile[];
+// The logits of all frames are cut into spans of PC_ANCHORS anchors (PC_ANCHORS * num_class floats, a whole number of
+// 16-byte groups per lane) that the warps of a persistent grid walk, each on its own: the 16-byte asynchronous copies of
+// a warp's NEXT span are in flight while it works on the current one, every lane reading back only what it copied itself.
+// A logit below logit_floor cannot reach the threshold (the floor sits 0.01 below the threshold's logit, far more than
+// expf's error), so the stream is only compared against it: a bit per logit in a register word, the positions of the few
+// that pass listed in shared memory, and the sigmoids / exact test / key computed over the list with the lanes packed (an
+// anchor listed through several classes is taken at its first). Keys collect in a per-warp pending list that is flushed
+// with one reservation on the frame's counter.
+#ifndef TCB_PC_NBUF
+#define TCB_PC_NBUF 1
+#endif
+constexpr int PC_ANCHORS = 256, PC_WARPS = 8, PC_PEND = 128, PC_NBUF = TCB_PC_NBUF;
+__device__ __forceinline__ void pc_copy16(float* dst_smem, const float* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
+}
+// shared memory of one warp: two span buffers, the position list, the pending keys
+__host__ __device__ inline size_t pc_warp_bytes(int num_class) { return (size_t)PC_ANCHORS * num_class * (PC_NBUF * 4 + 2) + PC_PEND * 8; }
+
+__global__ void __launch_bounds__(32 * PC_WARPS) pp_candidates_kernel(const float* cls, int b, int n_anchors, int num_class, float inv_nc, float thresh,
+                                                                      float logit_floor, unsigned long long* __restrict__ cand, int* __restrict__ cand_count) {
+    extern __shared__ __align__(16) unsigned char pc_raw[];
     pdl_wait();
-    const int f = blockIdx.y, a0 = blockIdx.x * PPC_TILE;
-    const int rows = min(PPC_TILE, n_anchors - a0);
-    const float* src = cls + ((long long)f * n_anchors + a0) * num_class;
-    const int nfl = rows * num_class;
-    if (VEC4) {
-        for (int e = threadIdx.x; e < (nfl >> 2); e += 256) reinterpret_cast<float4*>(ppc_tile)[e] = __ldg(reinterpret_cast<const float4*>(src) + e);
-        for (int e = (nfl & ~3) + threadIdx.x; e < nfl; e += 256) ppc_tile[e] = __ldg(src + e);
-    } else {
-        for (int e = threadIdx.x; e < nfl; e += 256) ppc_tile[e] = __ldg(src + e);
-    }
-    __syncthreads();
-    // slots: one shared-memory reservation per warp and round, one global reservation per CTA (a frame's counter would
-    // otherwise serialise thousands of atomics from all over the grid)
-    __shared__ int s_count, s_base;
-    if (threadIdx.x == 0) s_count = 0;
-    __syncthreads();
-    const int lane = threadIdx.x & 31;
-    unsigned long long key[PPC_TILE / 256];
-    int slot[PPC_TILE / 256];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int span = PC_ANCHORS * num_class, Q = span >> 7;           // floats per span; 16-byte groups per lane (2 * num_class)
+    unsigned char* mine_raw = pc_raw + (size_t)warp * pc_warp_bytes(num_class);
+    unsigned long long* pend = reinterpret_cast<unsigned long long*>(mine_raw);
+    float* buf0 = reinterpret_cast<float*>(mine_raw + PC_PEND * 8);
+    unsigned short* l_pos = reinterpret_cast<unsigned short*>(buf0 + PC_NBUF * span);
+    const int per_frame = (n_anchors + PC_ANCHORS - 1) / PC_ANCHORS;
+    const int total_items = per_frame * b, nworkers = gridDim.x * PC_WARPS;
+    const unsigned lt = (1u << lane) - 1u;
+    const long long frame_floats = (long long)n_anchors * num_class;
+
+    struct Item { const float* src; int n, f, a0; };
+    auto item_of = [&](int it) {
+        Item q;
+        int sp;
+        q.f = it / per_frame; sp = it - q.f * per_frame;
+        q.a0 = sp * PC_ANCHORS;
+        q.src = cls + q.f * frame_floats + (long long)q.a0 * num_class;
+        q.n = min(PC_ANCHORS, n_anchors - q.a0) * num_class;
+        return q;
+    };
+    auto issue = [&](const Item& q, float* dst) {
+        if (q.n == span && (((uintptr_t)q.src) & 15) == 0) {
+            for (int g = 0; g < Q; g++) pc_copy16(dst + (g * 32 + lane) * 4, q.src + (g * 32 + lane) * 4);
+        } else {
+            for (int g = 0; g < Q; g++) {
+                const int e = (g * 32 + lane) * 4;
+                if (e + 3 < q.n && ((((uintptr_t)(q.src + e)) & 15) == 0)) pc_copy16(dst + e, q.src + e);
+                else {
 #pragma unroll
-    for (int q = 0; q < PPC_TILE / 256; q++) {
-        const int r = q * 256 + threadIdx.x;
-        bool ok = false;
-        float best = 0.f;
-        if (r < rows) {
-            const float* p = ppc_tile + r * num_class;
-            float top = p[0];
-            for (int c = 1; c < num_class; c++) top = fmaxf(top, p[c]);
-            // an anchor whose largest logit lies below logit_floor (0.01 under the threshold's logit: far more than expf's
-            // error) cannot reach the threshold; the few that might get the sigmoid of every class, as the reference computes it
-            if (top > logit_floor) {
-                best = sigmoidf_ref(p[0]);
-                for (int c = 1; c < num_class; c++) best = fmaxf(best, sigmoidf_ref(p[c]));
-                ok = best >= thresh;
+                    for (int j = 0; j < 4; j++) dst[e + j] = e + j < q.n ? ld_coherent(q.src + e + j) : -INFINITY;
+                }
             }
         }
-        key[q] = sel::make_key(best, (unsigned)(a0 + r));
-        slot[q] = -1;
-        const unsigned em = __ballot_sync(0xffffffffu, ok);
-        if (em) {
-            int base = 0;
-            if (lane == 0) base = atomicAdd(&s_count, __popc(em));
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if (ok) slot[q] = base + __popc(em & ((1u << lane) - 1));
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    int pend_n = 0, pend_f = -1;
+    auto flush = [&]() {                                   // whole warp
+        if (pend_n == 0) return;
+        int base = 0;
+        if (lane == 0) base = atomicAdd(cand_count + pend_f, pend_n);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        unsigned long long* dst = cand + (long long)pend_f * n_anchors + base;
+        for (int i = lane; i < pend_n; i += 32) dst[i] = pend[i];
+        __syncwarp();
+        pend_n = 0;
+    };
+
+    int it = blockIdx.x * PC_WARPS + warp, stage = 0;
+    if (it >= total_items) return;
+    Item cur = item_of(it);
+    issue(cur, buf0);
+    for (; it < total_items; it += nworkers, stage ^= (PC_NBUF - 1)) {
+        const int nxt = it + nworkers;
+        Item next = cur;
+        if (PC_NBUF == 2 && nxt < total_items) {
+            next = item_of(nxt);
+            issue(next, buf0 + (stage ^ 1) * span);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");     // this span's copies: all but the group just committed
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) s_base = s_count ? atomicAdd(&cand_count[f], s_count) : 0;
-    __syncthreads();
-    unsigned long long* dst = cand + (long long)f * n_anchors + s_base;
+        const float* x = buf0 + stage * span;
+        unsigned long long above = 0ull;                   // bit g * 4 + j: the lane's element j of copy group g lies above the floor
+        for (int g = 0; g < Q; g++) {
+            const float4 v = *reinterpret_cast<const float4*>(x + (g * 32 + lane) * 4);   // what this lane copied itself
+            const unsigned m = (v.x > logit_floor ? 1u : 0u) | (v.y > logit_floor ? 2u : 0u) | (v.z > logit_floor ? 4u : 0u) | (v.w > logit_floor ? 8u : 0u);
+            above |= (unsigned long long)m << (4 * g);
+        }
+        const int mine = __popcll(above);
+        int inc = mine;
 #pragma unroll
-    for (int q = 0; q < PPC_TILE / 256; q++)
-        if (slot[q] >= 0) dst[slot[q]] = key[q];
+        for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += t; }
+        const int total = __shfl_sync(0xffffffffu, inc, 31);
+        if (total > 0) {                                   // uniform over the warp
+            if (pend_n && pend_f != cur.f) flush();
+            pend_f = cur.f;
+            int o = inc - mine;
+            while (above) {
+                const int bit = __ffsll((long long)above) - 1;
+                above &= above - 1ull;
+                l_pos[o++] = (unsigned short)((((bit >> 2) * 32 + lane) << 2) + (bit & 3));
+            }
+            __syncwarp();
+            for (int r0 = 0; r0 < total; r0 += 32) {       // the list, lanes packed
+                const int e = r0 + lane;
+                bool ok = false;
+                unsigned long long key = 0ull;
+                if (e < total) {
+                    const int pos = l_pos[e];
+                    int a = (int)((float)pos * inv_nc), c = pos - a * num_class;
+                    if (c < 0) { a--; c += num_class; } else if (c >= num_class) { a++; c -= num_class; }
+                    const float* pa = x + a * num_class;
+                    bool first = true;                     // an anchor is evaluated through the first of its classes on the list
+                    for (int k = 0; k < c; k++) first = first && !(pa[k] > logit_floor);
+                    if (first) {
+                        float best = sigmoidf_ref(pa[0]);
+                        for (int k = 1; k < num_class; k++) best = fmaxf(best, sigmoidf_ref(pa[k]));
+                        ok = best >= thresh;
+                        key = sel::make_key(best, (unsigned)(cur.a0 + a));
+                    }
+                }
+                const unsigned em = __ballot_sync(0xffffffffu, ok);
+                if (em) {
+                    if (pend_n + __popc(em) > PC_PEND) flush();
+                    if (ok) pend[pend_n + __popc(em & lt)] = key;
+                    pend_n += __popc(em);
+                }
+            }
+            __syncwarp();                                  // the span buffer is rewritten by the copy issued in the next iteration
+        }
+        if (PC_NBUF == 1 && nxt < total_items) {           // one buffer per warp: more warps per SM hold the bytes in flight instead
+            next = item_of(nxt);
+            issue(next, buf0);
+        }
+        cur = next;
+    }
+    flush();
 }
 
 // anchor a -> decoded box (anchor_generator.py:17-60 analytically, box_coder_utils.py:45-77, anchor_head_template.py:253-263)
@@ -643,6 +722,7 @@ static int check_nms_limits(tcb_ctx* ctx, const char* who, float thresh, int nms
 }
 
 static int init_post3d(tcb_ctx* ctx) {   // run by tcb_create
+    TCB_SMEM_OPT_IN(ctx, pp_candidates_kernel, pc_warp_bytes(PP_MAX_CLASSES) * PC_WARPS);
     TCB_SMEM_OPT_IN(ctx, rotated_nms_kernel, sizeof(FrameShared));
     TCB_SMEM_OPT_IN(ctx, pp_post_kernel, sizeof(FrameShared));
     TCB_SMEM_OPT_IN(ctx, cp_head_kernel, sizeof(FrameShared));
@@ -763,13 +843,20 @@ extern "C" int tcb_pp_anchor_post(tcb_ctx* ctx, const float* cls_dev, const floa
     TCB_WS(ctx, cand, unsigned long long, (size_t)b * n_anchors);
     TCB_WS(ctx, sorted_boxes, float, (size_t)b * PRE_CAP * 7);
     TCB_CUDA(ctx, cudaMemsetAsync(cand_count, 0, sizeof(int) * b, st));
-    const size_t tile_bytes = (size_t)PPC_TILE * num_class * sizeof(float);
-    const bool vec4 = (((uintptr_t)cls_dev) & 15) == 0 && ((n_anchors * num_class) & 3) == 0;   // every frame and tile starts on a 16-byte boundary
     const double st_d = (double)score_thresh;
     const float logit_floor = st_d <= 0.0 ? -INFINITY : (st_d >= 1.0 ? INFINITY : (float)(log(st_d / (1.0 - st_d)) - 0.01));
-    if (vec4) TCB_KLAUNCH(ctx, pp_candidates_kernel<true>, dim3(tcb_div_up(n_anchors, PPC_TILE), b), 256, tile_bytes, st, cls_dev, (int)n_anchors, num_class, score_thresh, logit_floor, cand, cand_count);
-    else      TCB_KLAUNCH(ctx, pp_candidates_kernel<false>, dim3(tcb_div_up(n_anchors, PPC_TILE), b), 256, tile_bytes, st, cls_dev, (int)n_anchors, num_class, score_thresh, logit_floor, cand, cand_count);
-    TCB_LAUNCHED(ctx);
+    {
+        const size_t pc_smem = pc_warp_bytes(num_class) * PC_WARPS;
+        int per_sm = (int)((220 * 1024) / (pc_smem + 1024));
+        per_sm = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
+        const long long items = (long long)tcb_div_up(n_anchors, PC_ANCHORS) * b;
+        if (items >= (1ll << 31)) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_pp_anchor_post: batch too large");
+        const long long want = tcb_div_up(items, PC_WARPS);
+        const int ctas = (int)(want < (long long)ctx->num_sms * per_sm ? want : (long long)ctx->num_sms * per_sm);
+        TCB_KLAUNCH(ctx, pp_candidates_kernel, ctas, 32 * PC_WARPS, pc_smem, st, cls_dev, b, (int)n_anchors, num_class, 1.0f / (float)num_class, score_thresh,
+                    logit_floor, cand, cand_count);
+        TCB_LAUNCHED(ctx);
+    }
     WideBufs wb;
     const int m_max = (int)(n_anchors < pre_max ? n_anchors : pre_max);
     if (m_max > WIDE_MIN && wide_bufs(ctx, m_max, b, wb)) {
