@@ -395,7 +395,45 @@ class CenterPoint(Workload):
         return "inputs cycle through 2 distinct sets of ~170 MB each (clouds + head outputs) and a step writes ~140 MB of voxels; no flush needed"
 
 
-WORKLOADS = {c.key: c for c in (Yolo1, Yolo64, Detectron, PointPillars, CenterPoint)}
+class JpegDecode(Workload):
+    """the CompressedImage branch of the 2D callback (communicator/ros_inference.py:123-131):
+    cv2.imdecode(buf, IMREAD_ANYCOLOR)[..., ::-1] of every frame -> tcb_jpeg_decode of the batch. The entry point takes HOST
+    streams, so a step holds the host marker parse, the upload of the scan bytes and the three kernels."""
+    key, survey = "jpeg", "f3"
+    name = "next row f3: 64 CompressedImage frames (1280x720 baseline JPEG, quality 90, 4:2:0) -> RGB u8 frames on the device (host marker parse + scan upload + Huffman / IDCT / colour kernels)"
+    batch, ring = 64, 2
+    stage_names = ("jpeg_decode",)
+    cpu_kind, cpu_what = "reference", "cv2.imdecode + channel flip, the reference's own call"
+
+    def __init__(self, eng, dev, frame_ids):
+        import cv2
+        import torch
+        from triton_client_b200 import synth
+        super().__init__(eng, dev, frame_ids)
+        base = [cv2.imencode(".jpg", synth.image_smooth(720, 1280, synth.seed_for(2, 40 + k)), [cv2.IMWRITE_JPEG_QUALITY, 90])[1].tobytes() for k in range(6)]
+        self.sets = [[base[(i + 3 * r) % 6] for i in range(self.batch)] for r in range(self.ring)]
+        self.out = torch.empty((self.batch, 720, 1280, 3), dtype=torch.uint8, device=dev)
+
+    def stage_bytes(self):
+        return {"jpeg_decode": sum(len(s) for s in self.sets[0]) + self.batch * 720 * 1280 * 3}
+
+    def step(self, i, ev=None):
+        _rec(ev, 0)
+        self.eng.jpeg_decode(self.sets[i % self.ring], out=self.out)
+        _rec(ev, 1)
+
+    def cpu_frames(self, idxs, as_written=True):
+        import cv2
+        n = 0
+        for i in idxs:
+            n += int(cv2.imdecode(np.frombuffer(self.sets[0][i % self.batch], np.uint8), cv2.IMREAD_ANYCOLOR)[..., ::-1].shape[0] > 0)
+        return n
+
+    def l2_note(self):
+        return "a step writes 177 MB of frames (> 126 MB L2) from ~16 MB of compressed bytes that arrive from the host inside the step"
+
+
+WORKLOADS = {c.key: c for c in (Yolo1, Yolo64, Detectron, PointPillars, CenterPoint, JpegDecode)}
 
 
 def make_workload(key, eng, dev, rank, world):
@@ -489,7 +527,8 @@ def cpu_port(wl, budget_s=6.0, max_frames=8):
     t0 = time.perf_counter()
     wl.cpu_frames(range(n), True)
     dt = time.perf_counter() - t0
-    return {"value": n / dt, "unit": "frames/s", "cores": 1, "kind": "port", "sample": f"{n} frame(s) of the workload, oracle port as the reference writes the path"}, n
+    return {"value": n / dt, "unit": "frames/s", "cores": 1, "kind": getattr(wl, "cpu_kind", "port"),
+            "sample": f"{n} frame(s) of the workload, {getattr(wl, 'cpu_what', 'oracle port as the reference writes the path')}"}, n
 
 
 def latency_c1(wl, frames=1000):
@@ -537,7 +576,7 @@ def latency_c1(wl, frames=1000):
 def measure_config(torch, key, dev, peak, steps, min_seconds, with_cpu):
     """One BASELINE config, single GPU: the same timed region as the main line, with its own clock samples."""
     from triton_client_b200.gpu import Engine
-    eng = Engine(dev.index or 0, workspace_bytes=(3 << 30) if key == "detectron" else (1 << 30))   # detectron: room for every logit of 16 images as a candidate
+    eng = Engine(dev.index or 0, workspace_bytes=(3 << 30) if key == "detectron" else ((2 << 30) if key == "jpeg" else (1 << 30)))   # detectron: room for every logit of 16 images as a candidate
     wl = make_workload(key, eng, dev, 0, 1)
     t = timed_region(torch, None, 1, dev, wl, steps, 3, min_seconds)
     out = {"workload": wl.name, "survey_config": wl.survey, "batch": wl.batch, "frames_per_s": wl.batch * 1e3 / t["ms_per_step"],
@@ -860,6 +899,10 @@ def run_gpu(args):
                     cfgs[f"c{k}"] = measure_config(torch, ck, dev, peak, 4 if ck != "yolo1" else 50, args.config_seconds, not args.no_cpu_baseline)
                 except Exception as ex:       # a config that cannot run must not cost the headline line
                     cfgs[f"c{k}"] = {"workload": WORKLOADS[ck].name, "error": str(ex)[:300]}
+            try:      # SURVEY 8(f) rank 3, beside the five BASELINE configs
+                cfgs["f3_jpeg"] = measure_config(torch, "jpeg", dev, peak, 4, args.config_seconds, not args.no_cpu_baseline)
+            except Exception as ex:
+                cfgs["f3_jpeg"] = {"workload": WORKLOADS["jpeg"].name, "error": str(ex)[:300]}
             line["configs"] = cfgs
             if "p50_latency" in cfgs.get("c0", {}):
                 line["p50_latency"] = dict(cfgs["c0"]["p50_latency"], config=WORKLOADS["yolo1"].name)
@@ -875,7 +918,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="yolo64", choices=sorted(set(WORKLOADS) | set(ALIASES)))
+    ap.add_argument("--workload", default="yolo64", choices=sorted((set(WORKLOADS) - {"jpeg"}) | set(ALIASES)))
     ap.add_argument("--min-seconds", type=float, default=0.5, help="the K steps are repeated until the timed region lasts this long")
     ap.add_argument("--config-seconds", type=float, default=0.25, help="timed region of each entry of `configs`")
     ap.add_argument("--no-cpu-baseline", action="store_true")

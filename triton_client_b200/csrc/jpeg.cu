@@ -18,6 +18,9 @@
 //   idct    : one thread per 8x8 block: dequantise, two 8-point passes, clamp, store into the component's plane
 //   colour  : four pixels per thread: upsample the chroma on the fly, convert, store RGB or BGR bytes
 #include "common.cuh"
+#include <stdlib.h>
+#include <thread>
+#include <vector>
 
 namespace {
 
@@ -557,7 +560,7 @@ extern "C" int tcb_jpeg_info(const unsigned char* jpeg_host, size_t len, int* he
 
 extern "C" size_t tcb_jpeg_staging_bytes(size_t total_jpeg_bytes, int n) {
     const size_t nn = (size_t)(n > 0 ? n : 0);
-    return align_up(nn * sizeof(JpegHdr), 256) + align_up(total_jpeg_bytes + nn * 64 + 256, 256) + align_up((total_jpeg_bytes / 16 + nn * 16 + 64) * sizeof(JSeg), 256) + 1024;
+    return align_up(nn * sizeof(JpegHdr), 256) + align_up(total_jpeg_bytes + total_jpeg_bytes / 8 + nn * 80 + 256, 256) + align_up((total_jpeg_bytes / 16 + nn * 16 + 64) * sizeof(JSeg), 256) + 1024;
 }
 
 extern "C" size_t tcb_jpeg_workspace(size_t total_jpeg_bytes, int n, int height, int width) {
@@ -583,32 +586,69 @@ extern "C" int tcb_jpeg_decode(tcb_ctx* ctx, const unsigned char* const* jpeg_ho
     // staging layout: headers | scan bytes | segments
     char* sbase = (char*)staging_host;
     JpegHdr* hdrs = (JpegHdr*)sbase;
-    const size_t scan_at = align_up((size_t)n * sizeof(JpegHdr), 256), scan_cap = align_up(total + (size_t)n * 64 + 256, 256);
+    const size_t scan_at = align_up((size_t)n * sizeof(JpegHdr), 256), scan_cap = align_up(total + total / 8 + (size_t)n * 80 + 256, 256);
     unsigned char* scan = (unsigned char*)(sbase + scan_at);
     const size_t seg_at = scan_at + scan_cap;
     JSeg* segs = (JSeg*)(sbase + seg_at);
     const int seg_cap = (int)((staging_bytes - seg_at) / sizeof(JSeg));
-    size_t scan_used = 0;
+    // Every stream is parsed into its own stretch of the scan area (its raw length bounds the unstuffed bytes), so the
+    // streams of a batch are parsed by a few host threads side by side; the segment lists are joined afterwards.
+    std::vector<size_t> scan_off(n + 1, 0);
+    for (int k = 0; k < n; k++) scan_off[k + 1] = align_up(scan_off[k] + jpeg_len[k] + jpeg_len[k] / 8 + 48, 16);   // unstuffing shrinks a stream, the 4-byte alignment of
+                                                                                                      // restart segments can grow it a little; + readable slack behind it
+    if (scan_off[n] > scan_cap) return tcb_fail(ctx, TCB_ERR_WORKSPACE, "tcb_jpeg_decode: staging buffer too small for the scan bytes");
+    std::vector<std::vector<JSeg>> seg_of(n);
+    std::vector<const char*> err_of(n, nullptr);
+    auto parse_range = [&](int k0, int k1) {
+        for (int k = k0; k < k1; k++) {
+            size_t sl = 0;
+            int ns = 0;
+            std::vector<JSeg>& sv = seg_of[k];
+            sv.resize(64);
+            const char* err = parse_jpeg(jpeg_host[k], jpeg_len[k], hdrs[k], scan + scan_off[k], scan_off[k + 1] - scan_off[k], sl, sv.data(), (int)sv.size(), ns);
+            if (err && !strcmp(err, "too many restart intervals for the staging buffer")) {   // a stream with many restart intervals: room for one per MCU row pair at least
+                sv.resize(jpeg_len[k] / 2 + 64);
+                err = parse_jpeg(jpeg_host[k], jpeg_len[k], hdrs[k], scan + scan_off[k], scan_off[k + 1] - scan_off[k], sl, sv.data(), (int)sv.size(), ns);
+            }
+            err_of[k] = err;
+            sv.resize(err ? 0 : ns);
+        }
+    };
+    {
+        int nthreads = (int)(total >> 24);                    // one thread per 16 MB of streams: a 64-frame batch of 720p frames is parsed in ~3 ms by
+                                                              // one thread, less than its kernels take, and extra threads only disturbed the launching thread
+        const int hw = (int)std::thread::hardware_concurrency();
+        nthreads = nthreads > 8 ? 8 : nthreads;
+        if (hw > 0 && nthreads > hw) nthreads = hw;
+        { const char* e = getenv("TCB_JPEG_THREADS"); if (e && atoi(e) > 0) nthreads = atoi(e); }   // override (measurement)
+        if (nthreads > n) nthreads = n;
+        if (nthreads <= 1) parse_range(0, n);
+        else {
+            std::vector<std::thread> pool;
+            for (int t = 1; t < nthreads; t++) pool.emplace_back(parse_range, (int)((long long)n * t / nthreads), (int)((long long)n * (t + 1) / nthreads));
+            parse_range(0, n / nthreads);
+            for (auto& th : pool) th.join();
+        }
+    }
     int seg_used = 0, sub_used = 0;
     long long coef_used = 0, plane_used = 0;
     for (int k = 0; k < n; k++) {
-        size_t sl = 0;
-        int ns = 0;
-        const char* err = parse_jpeg(jpeg_host[k], jpeg_len[k], hdrs[k], scan + scan_used, scan_cap - scan_used, sl, segs + seg_used, seg_cap - seg_used, ns);
-        if (err) return tcb_fail(ctx, TCB_ERR_ARG, "tcb_jpeg_decode: stream %d: %s", k, err);
+        if (err_of[k]) return tcb_fail(ctx, TCB_ERR_ARG, "tcb_jpeg_decode: stream %d: %s", k, err_of[k]);
         JpegHdr& h = hdrs[k];
         if (h.width != out_w || h.height != out_h || h.ncomp != out_channels)
             return tcb_fail(ctx, TCB_ERR_ARG, "tcb_jpeg_decode: stream %d is %dx%dx%d, the output is %dx%dx%d", k, h.height, h.width, h.ncomp, out_h, out_w, out_channels);
-        h.scan_off = (long long)scan_used; h.seg_first = seg_used; h.sub_first = sub_used;
+        const int ns = (int)seg_of[k].size();
+        if (seg_used + ns > seg_cap) return tcb_fail(ctx, TCB_ERR_WORKSPACE, "tcb_jpeg_decode: staging buffer too small for %d restart intervals", seg_used + ns);
+        memcpy(segs + seg_used, seg_of[k].data(), sizeof(JSeg) * (size_t)ns);
+        h.scan_off = (long long)scan_off[k]; h.seg_first = seg_used; h.sub_first = sub_used;
         h.nsub = 0;
-        for (int s = 0; s < ns; s++) {
-            segs[seg_used + s].sub_first = h.nsub;
-            h.nsub += segs[seg_used + s].byte_len > 0 ? tcb_div_up(segs[seg_used + s].byte_len, SUB_BYTES) : 1;
+        for (int s2 = 0; s2 < ns; s2++) {
+            segs[seg_used + s2].sub_first = h.nsub;
+            h.nsub += segs[seg_used + s2].byte_len > 0 ? tcb_div_up(segs[seg_used + s2].byte_len, SUB_BYTES) : 1;
         }
         h.coef_off = coef_used;
         coef_used += h.blocks * 64;
         for (int c = 0; c < h.ncomp; c++) { h.plane_off[c] = plane_used; plane_used += (long long)h.comp_bw[c] * h.comp_bh[c] * 64; }
-        scan_used = align_up(scan_used + sl + 16, 16);      // readable slack behind every image's stream
         seg_used += ns; sub_used += h.nsub;
     }
     const size_t copy_bytes = seg_at + (size_t)seg_used * sizeof(JSeg);

@@ -94,18 +94,24 @@ class Engine:
         h, w, c = self.jpeg_info(bufs[0])
         total = sum(b.size for b in bufs)
         need = int(self.lib.tcb_jpeg_staging_bytes(total, n))
-        if getattr(self, "_jpeg_event", None) is not None:
-            self._jpeg_event.synchronize()                # the previous call's upload has left the staging buffer
-        if getattr(self, "_jpeg_stage", None) is None or self._jpeg_stage.numel() < need:
-            self._jpeg_stage = torch.empty(max(need, 1 << 20), dtype=torch.uint8).pin_memory()
+        # two pinned staging buffers taken in turn: the host parse of this call overlaps the kernels of the previous one,
+        # and a buffer is rewritten only after the upload that read it (two calls ago) has finished
+        if getattr(self, "_jpeg_slots", None) is None:
+            self._jpeg_slots, self._jpeg_turn = [[None, None], [None, None]], 0
+        slot = self._jpeg_slots[self._jpeg_turn]
+        self._jpeg_turn ^= 1
+        if slot[1] is not None:
+            slot[1].synchronize()
+        if slot[0] is None or slot[0].numel() < need:
+            slot[0] = torch.empty(max(need, 1 << 20), dtype=torch.uint8).pin_memory()
         if out is None:
             out = torch.empty((n, h, w, 3) if c == 3 else (n, h, w), dtype=torch.uint8, device=self.device)
         ptrs = (c_void_p * n)(*[b.ctypes.data for b in bufs])
         lens = (ctypes.c_size_t * n)(*[b.size for b in bufs])
-        self.ctx.call("tcb_jpeg_decode", ptrs, lens, n, c_void_p(self._jpeg_stage.data_ptr()), self._jpeg_stage.numel(), 1 if bgr else 0,
+        self.ctx.call("tcb_jpeg_decode", ptrs, lens, n, c_void_p(slot[0].data_ptr()), slot[0].numel(), 1 if bgr else 0,
                       _ptr(out), h, w, c, _lib.stream_ptr())
-        self._jpeg_event = torch.cuda.Event()
-        self._jpeg_event.record()
+        slot[1] = torch.cuda.Event()
+        slot[1].record()
         return out
 
     MODES = {"stretch": 0, "letterbox": 1, "pad": 2}
