@@ -115,6 +115,31 @@ def class_agnostic_nms(box_scores, box_preds, nms_thresh, pre_max, post_max, sco
     return selected, src_box_scores[selected]
 
 
+# --- reference: OPCD/pcdet/models/model_utils/model_nms_utils.py:28-66 ---------------------------------
+def multi_classes_nms(cls_scores, box_preds, nms_thresh, pre_max, post_max, score_thresh=None, nms_type="nms_gpu"):
+    """Per class: score cut, top pre_max, NMS, first post_max; the classes' rows concatenated in class order."""
+    cls_scores, box_preds = torch.as_tensor(cls_scores), torch.as_tensor(box_preds)
+    pred_scores, pred_labels, pred_boxes = [], [], []
+    for k in range(cls_scores.shape[1]):
+        if score_thresh is not None:
+            scores_mask = (cls_scores[:, k] >= score_thresh)
+            box_scores = cls_scores[scores_mask, k]
+            cur_box_preds = box_preds[scores_mask]
+        else:
+            box_scores = cls_scores[:, k]
+            cur_box_preds = box_preds
+        selected = torch.zeros((0,), dtype=torch.int64)
+        if box_scores.shape[0] > 0:
+            box_scores_nms, indices = stable_topk(box_scores, min(pre_max, box_scores.shape[0]))
+            boxes_for_nms = cur_box_preds[indices]
+            keep_idx = (nms_gpu if nms_type == "nms_gpu" else nms_normal_gpu)(boxes_for_nms[:, 0:7], box_scores_nms, nms_thresh)
+            selected = indices[keep_idx[:post_max]]
+        pred_scores.append(box_scores[selected])
+        pred_labels.append(box_scores.new_ones(len(selected)).long() * k)
+        pred_boxes.append(cur_box_preds[selected])
+    return torch.cat(pred_scores, dim=0), torch.cat(pred_labels, dim=0), torch.cat(pred_boxes, dim=0)
+
+
 # --- reference: OPCD/pcdet/models/dense_heads/target_assigner/anchor_generator.py:17-60 (CPU tensors) --
 def generate_anchors(grid_size_xy, anchor_range, anchor_sizes, anchor_rotations, anchor_bottoms):
     """One entry per class; returns the concatenated [1, ny, nx, n_class, n_rot, 7] tensor of

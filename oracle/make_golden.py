@@ -501,6 +501,17 @@ def golden_pcdet_post():
             assert 30 < sel.numel() <= 200
             out[f"nms_{tag}_cfg"] = np.array([thr, -1.0 if st is None else st, 1000, 200], np.float64)
             out[f"nms_{tag}_sel"], out[f"nms_{tag}_scores"] = sel.numpy(), ssc.numpy()
+        # ---- (multi) multi_classes_nms (model_nms_utils.py:28-66): per-class score cut / top-k / NMS / post cut, three classes
+        mc_scores = torch.sigmoid(torch.from_numpy(np.stack([spread_scores(rng.normal(-1.5, 2, 1500), rng, thresh=0.0, fresh=lambda r, n: r.normal(-1.5, 2, n))
+                                                             for _ in range(3)], 1))).numpy().astype(np.float32)
+        mc_boxes = np.concatenate([boxes, rng.normal(0, 1, (1500, 2)).astype(np.float32)], 1)          # 7 + 2 extra columns (velocities) ride along
+        out["mc_scores"], out["mc_boxes"] = mc_scores, mc_boxes
+        for tag, typ, thr, st in (("rot", "nms_gpu", 0.2, 0.3), ("normal", "nms_normal_gpu", 0.1, None)):
+            cfgn = C(NMS_TYPE=typ, NMS_THRESH=thr, NMS_PRE_MAXSIZE=400, NMS_POST_MAXSIZE=60)
+            ps, pl, pb = nmsu.multi_classes_nms(torch.from_numpy(mc_scores), torch.from_numpy(mc_boxes), cfgn, score_thresh=st)
+            assert 40 < ps.numel() <= 180 and pl.unique().numel() == 3
+            out[f"mc_{tag}_cfg"] = np.array([thr, -1.0 if st is None else st, 400, 60], np.float64)
+            out[f"mc_{tag}_scores"], out[f"mc_{tag}_labels"], out[f"mc_{tag}_boxes"] = ps.numpy(), pl.numpy(), pb.numpy()
     save("pcdet_post", **out)
 
 

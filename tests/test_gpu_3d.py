@@ -236,6 +236,24 @@ def test_class_agnostic_nms_reference_golden(engine, tag, nms_type):
     assert np.array_equal(sel, g[f"nms_{tag}_sel"])
 
 
+@pytest.mark.parametrize("tag,nms_type", [("rot", "nms_gpu"), ("normal", "nms_normal_gpu")])
+def test_multi_classes_nms_reference_golden(engine, tag, nms_type):
+    """model_nms_utils.multi_classes_nms run unmodified: three classes, rows with two extra columns riding along."""
+    from triton_client_b200.clients import PointPillarPostprocess
+    g = golden("pcdet_post")
+    thr, st, pre, post = g[f"mc_{tag}_cfg"]
+    ps, pl, pb = engine.multi_classes_nms(torch.from_numpy(g["mc_scores"]).cuda(), torch.from_numpy(g["mc_boxes"]).cuda(), float(thr), int(pre), int(post),
+                                          None if st < 0 else float(st), nms_type)
+    assert np.array_equal(ps.cpu().numpy(), g[f"mc_{tag}_scores"]) and np.array_equal(pl.cpu().numpy(), g[f"mc_{tag}_labels"])
+    assert np.array_equal(pb.cpu().numpy(), g[f"mc_{tag}_boxes"])
+    qs, ql, qb = PointPillarPostprocess(engine=engine).multi_classes_nms(g["mc_scores"], g["mc_boxes"], float(thr), int(pre), int(post),
+                                                                        None if st < 0 else float(st), nms_type)
+    assert np.array_equal(qs.numpy(), g[f"mc_{tag}_scores"]) and np.array_equal(ql.numpy(), g[f"mc_{tag}_labels"]) and np.array_equal(qb.numpy(), g[f"mc_{tag}_boxes"])
+    # a cut nobody passes, and a class nobody passes
+    es, el, eb = engine.multi_classes_nms(torch.from_numpy(g["mc_scores"]).cuda(), torch.from_numpy(g["mc_boxes"]).cuda(), 0.1, 100, 10, 2.0, nms_type)
+    assert es.numel() == 0 and el.numel() == 0 and eb.shape == (0, 9)
+
+
 def test_remove_low_score_nu_reference_golden(engine):
     from triton_client_b200.clients import PointPillarPostprocess
     g = golden("low_score_nu")

@@ -132,6 +132,15 @@ def test_golden_class_agnostic_nms(tag, nms_type):
     assert np.array_equal(sel.numpy(), g[f"nms_{tag}_sel"]) and np.array_equal(sc.numpy(), g[f"nms_{tag}_scores"])
 
 
+@pytest.mark.parametrize("tag,nms_type", [("rot", "nms_gpu"), ("normal", "nms_normal_gpu")])
+def test_golden_multi_classes_nms(tag, nms_type):
+    g = golden("pcdet_post")
+    thr, st, pre, post = g[f"mc_{tag}_cfg"]
+    ps, pl, pb = box3d.multi_classes_nms(g["mc_scores"], g["mc_boxes"], float(thr), int(pre), int(post), None if st < 0 else float(st), nms_type)
+    assert np.array_equal(ps.numpy(), g[f"mc_{tag}_scores"]) and np.array_equal(pl.numpy(), g[f"mc_{tag}_labels"])
+    assert np.array_equal(pb.numpy(), g[f"mc_{tag}_boxes"])
+
+
 def test_golden_remove_low_score_nu():
     g = golden("low_score_nu")
     res = box3d.remove_low_score_nu({"box3d_lidar": g["boxes"], "scores": g["scores"], "labels": g["labels"], "metadata": {}})

@@ -79,6 +79,13 @@ class PointPillarPostprocess(Postprocess):
         n = int(cnt.item())
         return {'pred_boxes': ob[:n].cpu(), 'pred_scores': osc[:n].cpu(), 'pred_labels': ol[:n].cpu()}
 
+    def multi_classes_nms(self, cls_scores, box_preds, nms_thresh, pre_max=4096, post_max=500, score_thresh=None, nms_type="nms_gpu"):
+        """model_nms_utils.multi_classes_nms (the MULTI_CLASSES_NMS branch of post_processing) -> CPU tensors."""
+        dev = self.engine.device
+        ps, pl, pb = self.engine.multi_classes_nms(torch.as_tensor(cls_scores, dtype=torch.float32).to(dev), torch.as_tensor(box_preds, dtype=torch.float32).to(dev),
+                                                   nms_thresh, pre_max, post_max, score_thresh, nms_type)
+        return ps.cpu(), pl.cpu(), pb.cpu()
+
     def rotated_nms(self, boxes, scores, thresh, pre_max=4096, post_max=500, nms_type="nms_gpu"):
         dev = self.engine.device
         keep, cnt = self.engine.rotated_nms(torch.as_tensor(boxes, dtype=torch.float32).to(dev), torch.as_tensor(scores, dtype=torch.float32).to(dev),

@@ -342,6 +342,27 @@ class Engine:
                       _lib.stream_ptr())
         return keep, cnt
 
+    def multi_classes_nms(self, cls_scores, box_preds, nms_thresh, pre_max=4096, post_max=500, score_thresh=None, nms_type="nms_gpu"):
+        """model_nms_utils.multi_classes_nms (OPCD/pcdet/models/model_utils/model_nms_utils.py:28-66): per class the score cut,
+        top pre_max, NMS of NMS_TYPE and the first post_max — the classes are the batch of one tcb_rotated_nms call (scores
+        under the cut enter as -inf: they order last, cannot suppress a row that counts, and are dropped from the kept lists).
+        cls_scores (N, C), box_preds (N, 7 + extra) CUDA -> (pred_scores, pred_labels int64, pred_boxes), classes in order."""
+        _need_cuda(cls_scores, box_preds)
+        sc = cls_scores.float().t().contiguous()                                  # [C, N]
+        c, n = sc.shape
+        bp = box_preds.float().contiguous()
+        if n == 0 or c == 0:
+            return sc.new_zeros((0,)), torch.zeros((0,), dtype=torch.int64, device=sc.device), bp[:0]
+        if score_thresh is not None:
+            sc = torch.where(sc >= float(score_thresh), sc, torch.full_like(sc, float("-inf")))
+        boxes7 = bp[:, :7].unsqueeze(0).expand(c, n, 7).contiguous()
+        keep, cnt = self.rotated_nms(boxes7, sc, nms_thresh, pre_max, post_max, nms_type=nms_type)
+        kept_scores = torch.gather(sc, 1, keep.long().clamp_(0, n - 1))          # [C, post_max]
+        valid = (torch.arange(keep.shape[1], device=sc.device)[None, :] < cnt[:, None]) & (kept_scores > float("-inf"))
+        labels = torch.arange(c, device=sc.device, dtype=torch.int64)[:, None].expand_as(keep)
+        rows = keep.long()[valid]                                                 # class-major, kept order inside a class
+        return kept_scores[valid], labels[valid], bp[rows]
+
     def pp_anchor_post(self, cls_preds, box_preds, dir_preds, anchor_range, anchor_sizes, anchor_bottoms, anchor_rotations,
                        dir_offset=0.78539, dir_limit_offset=0.0, num_dir_bins=2, score_thresh=0.1, nms_thresh=0.01,
                        pre_max=4096, post_max=500, out=None, nms_type="nms_gpu"):
