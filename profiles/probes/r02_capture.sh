@@ -7,9 +7,10 @@ python bench.py --steps 20 --warmup 5 > $O/bench.json 2> $O/bench.err || { tail 
 NCU="ncu --clock-control none"
 $NCU --metrics gpu__time_duration.sum -c 800 --csv --log-file $O/launches_bench.csv \
     python bench.py --steps 4 --warmup 3 --min-seconds 0 --no-configs --no-cpu-baseline > $O/ncu_bench.log 2>&1
-for w in detectron pointpillars centerpoint; do
-    $NCU --metrics gpu__time_duration.sum -c 400 --csv --log-file $O/launches_$w.csv python profiles/probes/prof_posts.py $w > $O/ncu_$w.log 2>&1
+for w in detectron pointpillars centerpoint; do   # our kernels only: the workload set-up launches hundreds of torch kernels first
+    $NCU --metrics gpu__time_duration.sum -k "regex:preprocess|det_|pp_|rot_|cp_|vox_|pillar_" -c 120 --csv --log-file $O/launches_$w.csv python profiles/probes/prof_posts.py $w > $O/ncu_$w.log 2>&1
 done
+$NCU --metrics gpu__time_duration.sum -k regex:jpeg -c 12 --csv --log-file $O/launches_jpeg.csv python profiles/probes/prof_jpeg.py 2 > $O/ncu_jpeg.log 2>&1
 full() {  # name, kernel regex, launch-skip, target...
     local name=$1 k=$2 s=$3; shift 3
     $NCU --set full --import-source on -k "regex:$k" -s $s -c 1 -f -o $O/full_$name "$@" > $O/full_$name.log 2>&1
@@ -24,5 +25,11 @@ full decorate   'pillar_decorate'      2  python profiles/probes/prof_posts.py p
 full voxcell    'vox_cell'             2  python profiles/probes/prof_posts.py pointpillars
 full voxplace   'vox_place'            2  python profiles/probes/prof_posts.py pointpillars
 full voxscatter 'vox_scatter'          2  python profiles/probes/prof_posts.py pointpillars
+full rotmask    'rot_mask'             2  python profiles/probes/prof_posts.py pointpillars
+full rotpairs   'rot_pairs'            2  python profiles/probes/prof_posts.py pointpillars
+full dethist    'det_hist'             2  python profiles/probes/prof_posts.py detectron
+full detpost    'det_post'             2  python profiles/probes/prof_posts.py detectron
+full flat       'preprocess_flat'      2  python profiles/probes/prof_posts.py detectron
+full huff       'jpeg_huffman'         1  python profiles/probes/prof_jpeg.py 1
 full cphead     'cp_head'              2  python profiles/probes/prof_posts.py centerpoint
 ls -la $O

@@ -68,6 +68,7 @@ ALGO = {
     "nms": ("`yolo_nms_kernel` (bench, 128 CTAs)", None),
     "detcand": ("`det_candidates_kernel` (16 RetinaNet images, 201 600 anchors x 80 classes)", 16 * 201600 * 80 * 4 // 1 * 1 // 1),
     "detlevel": ("`det_level_kernel` (80 lists, top-1000 each)", None),
+    "detpost": ("`det_post_kernel` (16 images: top-4096 of <= 5000 rows, class-aware NMS, 100 kept)", None),
     "ppcand": ("`pp_candidates_kernel` (16 frames x 321 408 anchors x 3 classes)", 16 * 321408 * 3 * 4),
     "decorate": ("`pillar_decorate_kernel<1,32,4>` (16 x 12 000 pillars, 32 x 4 -> 32 x 10)", 16 * 12000 * 32 * 14 * 4),
     "voxcell": ("`vox_cell_kernel<1>` (16 sweeps, 1.73 M points)", None),
@@ -96,7 +97,8 @@ def main():
     for tag, title in (("bench", "`python bench.py --steps 4 --warmup 3 --min-seconds 0 --no-configs --no-cpu-baseline` (configs[1], the line's workload)"),
                        ("detectron", "`python profiles/probes/prof_posts.py detectron` (bench.py's configs[2] workload, 3 steps of 16 images)"),
                        ("pointpillars", "`python profiles/probes/prof_posts.py pointpillars` (configs[3], 3 steps of 16 sweeps)"),
-                       ("centerpoint", "`python profiles/probes/prof_posts.py centerpoint` (configs[4], 3 steps of 16 clouds)")):
+                       ("centerpoint", "`python profiles/probes/prof_posts.py centerpoint` (configs[4], 3 steps of 16 clouds)"),
+                       ("jpeg", "`python profiles/probes/prof_jpeg.py 2` (64 frames 1280x720, quality 90, no restart intervals)")):
         path = os.path.join(CAP, f"launches_{tag}.csv")
         if not os.path.exists(path):
             continue
@@ -149,7 +151,7 @@ def main():
         if tag == "pre":
             json.dump({"kernel": "preprocess2_kernel<1,1,0>", "command": "ncu --set full --clock-control none --import-source on -k regex:preprocess -s 6 -c 1 python bench.py "
                        "--steps 4 --warmup 3 --min-seconds 0 --no-configs --no-cpu-baseline", "duration_us": us, "dram_bytes_read": rd, "dram_bytes_write": wr,
-                       "traffic_bytes_per_launch": rd + wr, "algorithmic_bytes_per_launch": alg, "round": 2},
+                       "dram_traffic_bytes_per_launch": int(rd + wr), "algorithmic_bytes_per_launch": alg, "round": 2},
                       open(os.path.join(ROOT, "profiles", "r02_pre_kernel.json"), "w"), indent=1)
     open(os.path.join(ROOT, "profiles", "r02_kernels.md"), "w").write("\n".join(km) + "\n")
     print("wrote profiles/r02_launches.md, profiles/r02_kernels.md")

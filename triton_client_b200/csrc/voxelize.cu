@@ -202,16 +202,27 @@ __global__ void __launch_bounds__(1024) vox_scan_kernel(const VoxBatch B, int nb
     pdl_enter();
     __shared__ int sh[32];
     __shared__ int carry;
+    __shared__ int cnt[1024];
     if (threadIdx.x == 0) carry = 0;
     __syncthreads();
     for (int base = 0; base < nblk; base += 1024) {
-        const int i = base + threadIdx.x;
-        int v = 0;
-        if (i < nblk) {   // first points of block i = set bits of its 32 bitmap words
-            const uint4* w4 = reinterpret_cast<const uint4*>(bitmap + 32ll * i);
+        // first points of block i = set bits of its 32 bitmap words = 8 16-byte units: the CTA reads the units of 1024
+        // blocks with coalesced loads (thread t takes unit j * 1024 + t), eight neighbouring lanes add up one block
+        const uint4* w4 = reinterpret_cast<const uint4*>(bitmap + 32ll * base);
+        const long long units = 8ll * min(1024, nblk - base);
 #pragma unroll
-            for (int q = 0; q < 8; q++) { const uint4 w = w4[q]; v += __popc(w.x) + __popc(w.y) + __popc(w.z) + __popc(w.w); }
+        for (int j = 0; j < 8; j++) {
+            const int u = j * 1024 + threadIdx.x;
+            int c = 0;
+            if (u < units) { const uint4 w = w4[u]; c = __popc(w.x) + __popc(w.y) + __popc(w.z) + __popc(w.w); }
+            c += __shfl_xor_sync(0xffffffffu, c, 1);
+            c += __shfl_xor_sync(0xffffffffu, c, 2);
+            c += __shfl_xor_sync(0xffffffffu, c, 4);
+            if ((threadIdx.x & 7) == 0) cnt[u >> 3] = c;
         }
+        __syncthreads();
+        const int i = base + threadIdx.x;
+        const int v = i < nblk ? cnt[threadIdx.x] : 0;
         const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
         int inc = v;
 #pragma unroll
