@@ -259,7 +259,7 @@ struct PPParams {
 __device__ __forceinline__ float sigmoidf_ref(float x) { return 1.f / (1.f + expf(-x)); }  // torch.sigmoid
 
 // per anchor: sigmoid of every class logit, max (detector3d_template.py:217,251), keep score >= thresh.
-// The logits of all frames are cut into spans of PC_ANCHORS anchors (PC_ANCHORS * num_class floats, a whole number of
+// The logits of all frames are cut into spans of `pa` anchors (pa * num_class floats, a whole number of
 // 16-byte groups per lane) that the warps of a persistent grid walk, each on its own: the 16-byte asynchronous copies of
 // a warp's NEXT span are in flight while it works on the current one, every lane reading back only what it copied itself.
 // A logit below logit_floor cannot reach the threshold (the floor sits 0.01 below the threshold's logit, far more than
@@ -270,24 +270,26 @@ __device__ __forceinline__ float sigmoidf_ref(float x) { return 1.f / (1.f + exp
 #ifndef TCB_PC_NBUF
 #define TCB_PC_NBUF 1
 #endif
-constexpr int PC_ANCHORS = 256, PC_WARPS = 8, PC_PEND = 128, PC_NBUF = TCB_PC_NBUF;
+constexpr int PC_WARPS = 8, PC_PEND = 128, PC_NBUF = TCB_PC_NBUF;
+// anchors per span: a multiple of 128 with at most 16 16-byte groups per lane (the lane's bit word has 64 bits)
+static inline int pc_anchors(int num_class) { return num_class <= 2 ? 1024 : (num_class <= 4 ? 512 : 256); }
 __device__ __forceinline__ void pc_copy16(float* dst_smem, const float* src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
 }
 // shared memory of one warp: two span buffers, the position list, the pending keys
-__host__ __device__ inline size_t pc_warp_bytes(int num_class) { return (size_t)PC_ANCHORS * num_class * (PC_NBUF * 4 + 2) + PC_PEND * 8; }
+__host__ __device__ inline size_t pc_warp_bytes(int num_class, int pa) { return (size_t)pa * num_class * (PC_NBUF * 4 + 2) + PC_PEND * 8; }
 
-__global__ void __launch_bounds__(32 * PC_WARPS) pp_candidates_kernel(const float* cls, int b, int n_anchors, int num_class, float inv_nc, float thresh,
+__global__ void __launch_bounds__(32 * PC_WARPS) pp_candidates_kernel(const float* cls, int b, int n_anchors, int num_class, int pa, float inv_nc, float thresh,
                                                                       float logit_floor, unsigned long long* __restrict__ cand, int* __restrict__ cand_count) {
     extern __shared__ __align__(16) unsigned char pc_raw[];
     pdl_wait();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int span = PC_ANCHORS * num_class, Q = span >> 7;           // floats per span; 16-byte groups per lane (2 * num_class)
-    unsigned char* mine_raw = pc_raw + (size_t)warp * pc_warp_bytes(num_class);
+    const int span = pa * num_class, Q = span >> 7;                    // floats per span; 16-byte groups per lane
+    unsigned char* mine_raw = pc_raw + (size_t)warp * pc_warp_bytes(num_class, pa);
     unsigned long long* pend = reinterpret_cast<unsigned long long*>(mine_raw);
     float* buf0 = reinterpret_cast<float*>(mine_raw + PC_PEND * 8);
     unsigned short* l_pos = reinterpret_cast<unsigned short*>(buf0 + PC_NBUF * span);
-    const int per_frame = (n_anchors + PC_ANCHORS - 1) / PC_ANCHORS;
+    const int per_frame = (n_anchors + pa - 1) / pa;
     const int total_items = per_frame * b, nworkers = gridDim.x * PC_WARPS;
     const unsigned lt = (1u << lane) - 1u;
     const long long frame_floats = (long long)n_anchors * num_class;
@@ -297,9 +299,9 @@ __global__ void __launch_bounds__(32 * PC_WARPS) pp_candidates_kernel(const floa
         Item q;
         int sp;
         q.f = it / per_frame; sp = it - q.f * per_frame;
-        q.a0 = sp * PC_ANCHORS;
+        q.a0 = sp * pa;
         q.src = cls + q.f * frame_floats + (long long)q.a0 * num_class;
-        q.n = min(PC_ANCHORS, n_anchors - q.a0) * num_class;
+        q.n = min(pa, n_anchors - q.a0) * num_class;
         return q;
     };
     auto issue = [&](const Item& q, float* dst) {
@@ -373,12 +375,17 @@ __global__ void __launch_bounds__(32 * PC_WARPS) pp_candidates_kernel(const floa
                     const int pos = l_pos[e];
                     int a = (int)((float)pos * inv_nc), c = pos - a * num_class;
                     if (c < 0) { a--; c += num_class; } else if (c >= num_class) { a++; c -= num_class; }
-                    const float* pa = x + a * num_class;
+                    const float* row = x + a * num_class;
                     bool first = true;                     // an anchor is evaluated through the first of its classes on the list
-                    for (int k = 0; k < c; k++) first = first && !(pa[k] > logit_floor);
+                    for (int k = 0; k < c; k++) first = first && !(row[k] > logit_floor);
                     if (first) {
-                        float best = sigmoidf_ref(pa[0]);
-                        for (int k = 1; k < num_class; k++) best = fmaxf(best, sigmoidf_ref(pa[k]));
+                        // max over the classes of sigmoid(logit): the sigmoid of the largest logit — and of any other within
+                        // 1e-5 of it (expf's 2 ulp could reorder only logits that close)
+                        float top = row[0];
+                        for (int k = 1; k < num_class; k++) top = fmaxf(top, row[k]);
+                        float best = sigmoidf_ref(top);
+                        for (int k = 0; k < num_class; k++)
+                            if (row[k] != top && row[k] > top - 1e-5f) best = fmaxf(best, sigmoidf_ref(row[k]));
                         ok = best >= thresh;
                         key = sel::make_key(best, (unsigned)(cur.a0 + a));
                     }
@@ -722,7 +729,7 @@ static int check_nms_limits(tcb_ctx* ctx, const char* who, float thresh, int nms
 }
 
 static int init_post3d(tcb_ctx* ctx) {   // run by tcb_create
-    TCB_SMEM_OPT_IN(ctx, pp_candidates_kernel, pc_warp_bytes(PP_MAX_CLASSES) * PC_WARPS);
+    TCB_SMEM_OPT_IN(ctx, pp_candidates_kernel, 200 * 1024);
     TCB_SMEM_OPT_IN(ctx, rotated_nms_kernel, sizeof(FrameShared));
     TCB_SMEM_OPT_IN(ctx, pp_post_kernel, sizeof(FrameShared));
     TCB_SMEM_OPT_IN(ctx, cp_head_kernel, sizeof(FrameShared));
@@ -846,14 +853,15 @@ extern "C" int tcb_pp_anchor_post(tcb_ctx* ctx, const float* cls_dev, const floa
     const double st_d = (double)score_thresh;
     const float logit_floor = st_d <= 0.0 ? -INFINITY : (st_d >= 1.0 ? INFINITY : (float)(log(st_d / (1.0 - st_d)) - 0.01));
     {
-        const size_t pc_smem = pc_warp_bytes(num_class) * PC_WARPS;
+        const size_t pc_smem = pc_warp_bytes(num_class, pc_anchors(num_class)) * PC_WARPS;
         int per_sm = (int)((220 * 1024) / (pc_smem + 1024));
         per_sm = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
-        const long long items = (long long)tcb_div_up(n_anchors, PC_ANCHORS) * b;
+        const int pa = pc_anchors(num_class);
+        const long long items = (long long)tcb_div_up(n_anchors, pa) * b;
         if (items >= (1ll << 31)) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_pp_anchor_post: batch too large");
         const long long want = tcb_div_up(items, PC_WARPS);
         const int ctas = (int)(want < (long long)ctx->num_sms * per_sm ? want : (long long)ctx->num_sms * per_sm);
-        TCB_KLAUNCH(ctx, pp_candidates_kernel, ctas, 32 * PC_WARPS, pc_smem, st, cls_dev, b, (int)n_anchors, num_class, 1.0f / (float)num_class, score_thresh,
+        TCB_KLAUNCH(ctx, pp_candidates_kernel, ctas, 32 * PC_WARPS, pc_smem, st, cls_dev, b, (int)n_anchors, num_class, pa, 1.0f / (float)num_class, score_thresh,
                     logit_floor, cand, cand_count);
         TCB_LAUNCHED(ctx);
     }
