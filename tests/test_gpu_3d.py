@@ -179,6 +179,22 @@ def test_class_score_filter(engine):
     assert idx[:int(cnt.item())].cpu().tolist() == want.tolist()
 
 
+def test_class_score_filter_tables_queued_back_to_back(engine):
+    """The group tables travel through the context's pinned slots (eight of them, reused in turn): twenty calls with
+    twenty different tables queued without a sync in between must each see their own table."""
+    rng = np.random.default_rng(2)
+    labels = torch.from_numpy(rng.integers(0, 10, 300).astype(np.int64)).cuda()
+    scores_h = (np.round(rng.uniform(0, 1, 300) * 50) / 50).astype(np.float32)
+    scores = torch.from_numpy(scores_h).cuda()
+    tables = [[(int(c), float(np.float32(0.02 * (k + c)))) for c in rng.permutation(10)[:1 + k % 7]] for k in range(20)]
+    res = [engine.class_score_filter(labels, scores, t) for t in tables]
+    torch.cuda.synchronize()
+    lab = labels.cpu().numpy()
+    for t, (idx, cnt) in zip(tables, res):
+        want = [i for c, th in t for i in np.nonzero((lab == c) & (scores_h >= np.float32(th)))[0].tolist()]
+        assert idx[:int(cnt.item())].cpu().tolist() == want
+
+
 PP_SMALL = dict(anchor_sizes=KITTI_ANCHORS["anchor_sizes"], anchor_bottoms=KITTI_ANCHORS["anchor_bottoms"],
                 anchor_rotations=KITTI_ANCHORS["anchor_rotations"])
 

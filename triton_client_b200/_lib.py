@@ -163,7 +163,14 @@ class Context:
             pass
 
 
+_raw_stream = None
+
+
 def stream_ptr():
-    """cudaStream_t of torch's current stream as an integer for the C ABI."""
+    """cudaStream_t of torch's current stream (current device) as an integer for the C ABI."""
+    global _raw_stream
     import torch
-    return c_void_p(torch.cuda.current_stream().cuda_stream)
+    if _raw_stream is None:      # torch's own fast path to the raw handle (what its extensions use); the public objects otherwise
+        fast = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+        _raw_stream = (lambda: fast(torch.cuda.current_device())) if fast is not None else (lambda: torch.cuda.current_stream().cuda_stream)
+    return c_void_p(_raw_stream())

@@ -19,6 +19,7 @@ struct tcb_ctx {
     int pdl;           // launch the hot kernels with programmatic stream serialization (TCB_PDL, default on)
     int* tickets;      // TCB_TICKETS ints behind the workspace, zero between calls: "last CTA of a group" counters that
                        // the kernel using them resets itself, so no per-call memset is needed
+    float pre_div; int pre_div_known, pre_exact_recip, pre_exact2;   // tcb_preprocess_image: exact-division checks of the last divisor
     char* stage;       // TCB_STAGE_SLOTS pinned slots of TCB_STAGE_BYTES for small host tables (tcb_stage_h2d)
     cudaEvent_t stage_done[8];
     int stage_next;

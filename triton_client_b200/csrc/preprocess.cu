@@ -820,18 +820,21 @@ extern "C" int tcb_preprocess_image(tcb_ctx* ctx, const uint8_t* src_dev, int n,
     const bool area = (w == 2 * p.new_w) && (h == 2 * p.new_h);
 
     p.div = div; p.rdiv = 1.0f / div;
-    p.exact_recip = 1;
-    for (int v = 0; v < 256; v++) {
-        float f = (float)v, q0 = f * p.rdiv;
-        float q = fmaf(fmaf(-q0, div, f), p.rdiv, q0);
-        if (q != f / div) { p.exact_recip = 0; break; }
-    }
     p.rlo = (float)(1.0 / (double)div - (double)p.rdiv);
-    p.exact2 = 1;
-    for (int v = 0; v < 256; v++) {
-        const float f = (float)v;
-        if (fmaf(f, p.rdiv, f * p.rlo) != f / div) { p.exact2 = 0; break; }
+    if (!ctx->pre_div_known || ctx->pre_div != div) {      // 2 x 256 checks: once per divisor, not once per frame
+        int e1 = 1, e2 = 1;
+        for (int v = 0; v < 256; v++) {
+            float f = (float)v, q0 = f * p.rdiv;
+            float q = fmaf(fmaf(-q0, div, f), p.rdiv, q0);
+            if (q != f / div) { e1 = 0; break; }
+        }
+        for (int v = 0; v < 256; v++) {
+            const float f = (float)v;
+            if (fmaf(f, p.rdiv, f * p.rlo) != f / div) { e2 = 0; break; }
+        }
+        ctx->pre_div = div; ctx->pre_exact_recip = e1; ctx->pre_exact2 = e2; ctx->pre_div_known = 1;
     }
+    p.exact_recip = ctx->pre_exact_recip; p.exact2 = ctx->pre_exact2;
     for (int c = 0; c < 3; c++) {
         p.sub[c] = sub ? sub[c] : 0.f;
         p.padv[c] = (float)pad_value / div - p.sub[c];

@@ -65,12 +65,12 @@ class Engine:
             out = torch.empty((n, 3, out_h, out_w), dtype=torch.float32, device=src.device)
         elif tuple(out.shape) != (n, 3, out_h, out_w) or out.dtype != torch.float32 or not out.is_contiguous():
             raise ValueError("preprocess_images: bad `out` tensor")
-        sub_arr = (c_float * 3)(*(sub if sub is not None else (0.0, 0.0, 0.0)))
+        sub_arr = (c_float * 3)(*sub) if sub is not None else None       # NULL = no subtraction
         aff = (c_float * 4)()
         self.ctx.call("tcb_preprocess_image", _ptr(src), n, h, w, src.stride(1), src.stride(0) if n > 1 else h * src.stride(1),
                       1 if swap else 0, _MODES[mode] if isinstance(mode, str) else int(mode), out_h, out_w,
                       float(div), sub_arr, int(pad_value), _ptr(out), aff, _lib.stream_ptr())
-        return out, np.array(list(aff), dtype=np.float32)
+        return out, np.frombuffer(aff, dtype=np.float32)     # the array keeps `aff` alive
 
     # ---- YOLOv5 postprocess ----------------------------------------------------------------------
     # ---- compressed camera frames ---------------------------------------------------------------------
@@ -155,8 +155,9 @@ class Engine:
         if classes is not None:
             ncls = len(classes)
             cls_arr = (c_int * max(ncls, 1))(*[int(v) for v in classes])
+        cp = counts.data_ptr()                         # rows of the [2, b] int32 tensor, without building views for the call
         self.ctx.call("tcb_yolo_nms", _ptr(pred), b, n, c - 5, float(conf_thres), float(iou_thres), cls_arr, ncls,
-                      1 if agnostic else 0, int(max_det), int(max_nms), _ptr(out), _ptr(counts[0]), _ptr(counts[1]),
+                      1 if agnostic else 0, int(max_det), int(max_nms), _ptr(out), c_void_p(cp), c_void_p(cp + 4 * counts.stride(0)),
                       _lib.stream_ptr())
         return out, counts[0], counts[1]
 
