@@ -19,6 +19,7 @@
 //   colour  : four pixels per thread: upsample the chroma on the fly, convert, store RGB or BGR bytes
 #include "common.cuh"
 #include <stdlib.h>
+#include <new>
 #include <thread>
 #include <vector>
 
@@ -571,8 +572,22 @@ extern "C" size_t tcb_jpeg_workspace(size_t total_jpeg_bytes, int n, int height,
     return tcb_jpeg_staging_bytes(total_jpeg_bytes, n) + subs * (8 + 8 + 16 + 16) + nn * blocks * (128 + 64) + 16 * 256 + 4096;
 }
 
+static int tcb_jpeg_decode_(tcb_ctx* ctx, const unsigned char* const* jpeg_host, const size_t* jpeg_len, int n, void* staging_host,
+                            size_t staging_bytes, int bgr, unsigned char* out_dev, int out_h, int out_w, int out_channels, void* stream);
+
 extern "C" int tcb_jpeg_decode(tcb_ctx* ctx, const unsigned char* const* jpeg_host, const size_t* jpeg_len, int n, void* staging_host,
                                size_t staging_bytes, int bgr, unsigned char* out_dev, int out_h, int out_w, int out_channels, void* stream) {
+    try {       // the host parse uses std::vector / std::thread: nothing may leave a C entry point as an exception
+        return tcb_jpeg_decode_(ctx, jpeg_host, jpeg_len, n, staging_host, staging_bytes, bgr, out_dev, out_h, out_w, out_channels, stream);
+    } catch (const std::bad_alloc&) {
+        return tcb_fail(ctx, TCB_ERR_ALLOC, "tcb_jpeg_decode: host allocation failed");
+    } catch (...) {
+        return tcb_fail(ctx, TCB_ERR_ARG, "tcb_jpeg_decode: unexpected host error");
+    }
+}
+
+static int tcb_jpeg_decode_(tcb_ctx* ctx, const unsigned char* const* jpeg_host, const size_t* jpeg_len, int n, void* staging_host,
+                            size_t staging_bytes, int bgr, unsigned char* out_dev, int out_h, int out_w, int out_channels, void* stream) {
     TCB_CHECK_CTX(ctx);
     TCB_REQUIRE(ctx, n >= 0 && (n == 0 || (jpeg_host && jpeg_len && staging_host && out_dev)), "tcb_jpeg_decode: null argument");
     TCB_REQUIRE(ctx, out_h >= 1 && out_w >= 1 && (out_channels == 1 || out_channels == 3), "tcb_jpeg_decode: bad output shape");
@@ -625,8 +640,13 @@ extern "C" int tcb_jpeg_decode(tcb_ctx* ctx, const unsigned char* const* jpeg_ho
         if (nthreads <= 1) parse_range(0, n);
         else {
             std::vector<std::thread> pool;
-            for (int t = 1; t < nthreads; t++) pool.emplace_back(parse_range, (int)((long long)n * t / nthreads), (int)((long long)n * (t + 1) / nthreads));
+            int started = 1;                                  // ranges [n*t/nthreads, n*(t+1)/nthreads); the calling thread takes what no thread got
+            try {
+                for (; started < nthreads; started++)
+                    pool.emplace_back(parse_range, (int)((long long)n * started / nthreads), (int)((long long)n * (started + 1) / nthreads));
+            } catch (...) {}                                  // no more threads to be had: nothing may escape a C entry point
             parse_range(0, n / nthreads);
+            if (started < nthreads) parse_range((int)((long long)n * started / nthreads), n);
             for (auto& th : pool) th.join();
         }
     }
