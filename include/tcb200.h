@@ -112,7 +112,8 @@ int tcb_copy_rect_d2h(tcb_ctx* ctx, const void* src_dev, void* dst_host, int pla
  * tcb_jpeg_info: frame size and component count of one stream (host only).
  * tcb_jpeg_decode: n streams of the SAME size and component count -> out_dev [n, out_h, out_w, out_channels] u8
  *   (channels 3: RGB, or BGR when bgr != 0; channels 1: grey). jpeg_host / jpeg_len: n host pointers and
- *   lengths. The marker parse runs on the calling thread; the entropy-coded bytes go through staging_host
+ *   lengths. The marker parse runs on the calling thread (batches above 32 MB of streams: on a few host threads
+ *   that end with the call); the entropy-coded bytes go through staging_host
  *   (PINNED host memory of at least tcb_jpeg_staging_bytes(sum of lengths, n) bytes, in use until `stream`
  *   has passed this call) to the device in one copy; everything else is kernels on `stream`, no host sync.
  *   Needs tcb_jpeg_workspace(sum of lengths, n, out_h, out_w) bytes of context workspace.
@@ -338,7 +339,8 @@ int tcb_centerpoint_post(tcb_ctx* ctx, int b, int num_heads, const float* const*
 /* Per-class score cut of PointPillarPostprocess.remove_low_score_nu / get_annotations_indices
  * (clients/postprocess/detector_3d_postprocess.py:55-64,98-133): for each (class, threshold) group in the
  * given order, the ascending indices i with labels[i] == class and scores[i] >= threshold, concatenated.
- * labels int64, group tables are host arrays (<= 64 groups); out_idx_dev holds up to n_groups*n indices. */
+ * labels int64, group tables are host arrays (<= 64 groups; copied through pinned slots of the context, the call does
+ * not wait for the device); out_idx_dev holds up to n_groups*n indices. */
 int tcb_class_score_filter(tcb_ctx* ctx, const long long* labels_dev, const float* scores_dev, int n, int n_groups,
                            const int* group_class_host, const float* group_thresh_host, int* out_idx_dev,
                            int* out_count_dev, void* stream);
