@@ -182,19 +182,43 @@ __global__ void __launch_bounds__(MASK_T) rot_mask_kernel(const rot::RBox* __res
     mask[(size_t)gi * MW + bj] = word;
 }
 
-// Mask, step 2: the exact rotated IoU of every listed pair, one pair per thread with all lanes busy (inside the tiles
-// the few pairs that survive the distance test would each run with most of their warp idle).
-__global__ void __launch_bounds__(256) rot_pairs_kernel(const rot::RBox* __restrict__ R, const int* __restrict__ m_dev, float thresh, int normal,
-                                                        const unsigned* __restrict__ pairs, int pair_cap, unsigned long long* __restrict__ mask, size_t mask_stride) {
+// Mask, step 2: the exact IoU of the listed pairs. A warp takes 64 pairs at a time, drops those a separating axis rules
+// out (rot::separated: about half of what the circle test lets through) and packs the rest into its slice of shared
+// memory, so that the expensive exact test (polygon clip, ~2000 instructions) always runs with the lanes full.
+constexpr int PAIR_WARPS = 8;
+__global__ void __launch_bounds__(32 * PAIR_WARPS) rot_pairs_kernel(const rot::RBox* __restrict__ R, const int* __restrict__ m_dev, float thresh, int normal,
+                                                                    const unsigned* __restrict__ pairs, int pair_cap, unsigned long long* __restrict__ mask, size_t mask_stride) {
     pdl_wait();
+    __shared__ unsigned list[PAIR_WARPS][96];
     R += (size_t)blockIdx.y * PRE_CAP; m_dev += blockIdx.y * WIDE_M; mask += blockIdx.y * mask_stride; pairs += (size_t)blockIdx.y * pair_cap;
     const int total = min(m_dev[1], pair_cap);
-    for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < total; q += gridDim.x * blockDim.x) {
-        const unsigned e = pairs[q];
-        if (e == 0xffffffffu) continue;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned lt = (1u << lane) - 1u;
+    unsigned* mine = list[warp];
+    auto exact = [&](unsigned e) {
         const int gi = (int)(e >> 16), gj = (int)(e & 0xffffu);
-        if (rot::overlaps(R[gi], R[gj], thresh, normal)) atomicOr(&mask[(size_t)gi * MW + (gj >> 6)], 1ull << (gj & 63));
+        const bool hit = normal ? rot::iou_normal(R[gi], R[gj]) > thresh : rot::iou_bev(R[gi], R[gj]) > thresh;
+        if (hit) atomicOr(&mask[(size_t)gi * MW + (gj >> 6)], 1ull << (gj & 63));
+    };
+    int have = 0;
+    for (int q0 = (blockIdx.x * PAIR_WARPS + warp) * 64; q0 < total; q0 += gridDim.x * PAIR_WARPS * 64) {
+#pragma unroll
+        for (int half = 0; half < 2; half++) {
+            const int q = q0 + half * 32 + lane;
+            const unsigned e = q < total ? pairs[q] : 0xffffffffu;
+            const bool ok = e != 0xffffffffu && !rot::separated(R[e >> 16], R[e & 0xffffu], normal);
+            const unsigned bal = __ballot_sync(0xffffffffu, ok);
+            if (ok) mine[have + __popc(bal & lt)] = e;
+            have += __popc(bal);
+        }
+        __syncwarp();
+        while (have >= 32) {
+            have -= 32;
+            exact(mine[have + lane]);
+        }
+        __syncwarp();
     }
+    if (lane < have) exact(mine[lane]);
 }
 
 using wide::SweepShared;

@@ -134,6 +134,23 @@ __device__ __forceinline__ float iou_normal(const RBox& a, const RBox& b) {
     return inter / fmaxf(__fmaf_rn(b.dx, b.dy, sa) - inter, 1e-8f);
 }
 
+// Second conservative pre-test, for the pairs the circle test lets through: a separating axis between the two rectangles
+// (the four edge directions) with a 3 cm margin. The reference counts a corner as inside a box up to 1 cm outside its edge
+// and finds edge crossings only where edges cross, so with a gap above that margin its point list is empty and its IoU
+// exactly 0; for nms_normal_gpu the boxes are axis-aligned and a gap along x or y makes the intersection exactly 0.
+// Any NaN makes every comparison false: such a pair is left to the exact test.
+__device__ __forceinline__ bool separated(const RBox& a, const RBox& b, int normal) {
+    const float m = 0.03f;
+    const float ox = b.x - a.x, oy = b.y - a.y;
+    if (normal) return fabsf(ox) > (a.dx + b.dx) * 0.5f + m || fabsf(oy) > (a.dy + b.dy) * 0.5f + m;
+    const float ahx = fabsf(a.dx) * 0.5f, ahy = fabsf(a.dy) * 0.5f, bhx = fabsf(b.dx) * 0.5f, bhy = fabsf(b.dy) * 0.5f;
+    const float cd = fabsf(a.c * b.c + a.s * b.s), sd = fabsf(b.s * a.c - b.c * a.s);   // |cos|, |sin| of the heading difference
+    float rx = ox * a.c + oy * a.s, ry = oy * a.c - ox * a.s;                             // b's centre in a's frame
+    if (fabsf(rx) > ahx + bhx * cd + bhy * sd + m || fabsf(ry) > ahy + bhx * sd + bhy * cd + m) return true;
+    rx = ox * b.c + oy * b.s; ry = oy * b.c - ox * b.s;                                   // a's centre in b's frame (sign dropped)
+    return fabsf(rx) > bhx + ahx * cd + ahy * sd + m || fabsf(ry) > bhy + ahx * sd + ahy * cd + m;
+}
+
 // the suppression test of nms_gpu (normal == 0) / nms_normal_gpu (normal != 0)
 __device__ __forceinline__ bool overlaps(const RBox& a, const RBox& b, float thresh, int normal) {
     return (normal ? iou_normal(a, b) : iou_bev(a, b)) > thresh;
