@@ -8,6 +8,7 @@
 // below). Either way nothing leaves the device: no D2H of the mask, no serial host sweep (iou3d_nms.cpp:105-134).
 #include <cstddef>
 #include "common.cuh"
+#include <stdlib.h>
 #include "cta_select.cuh"
 #include "rotated.cuh"
 #include "cta_nms.cuh"
