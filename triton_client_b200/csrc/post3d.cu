@@ -304,11 +304,21 @@ __device__ __forceinline__ void pc_copy16(float* dst_smem, const float* src) {
 // shared memory of one warp: two span buffers, the position list, the pending keys
 __host__ __device__ inline size_t pc_warp_bytes(int num_class, int pa) { return (size_t)pa * num_class * (PC_NBUF * 4 + 2) + PC_PEND * 8; }
 
-__global__ void __launch_bounds__(32 * PC_WARPS) pp_candidates_kernel(const float* cls, int b, int n_anchors, int num_class, int pa, float inv_nc, float thresh,
+__device__ __noinline__ float pc_best_of_all(const float* row, int num_class) {
+    float best = sigmoidf_ref(row[0]);
+    for (int k = 1; k < num_class; k++) best = fmaxf(best, sigmoidf_ref(row[k]));
+    return best;
+}
+
+// NC: the class count as a compile-time constant (1..4: the bit-word loops unroll with constant shifts), 0 = any
+template <int NC>
+__global__ void __launch_bounds__(32 * PC_WARPS) pp_candidates_kernel(const float* cls, int b, int n_anchors, int num_class_rt, int pa_rt, float inv_nc, float thresh,
                                                                       float logit_floor, unsigned long long* __restrict__ cand, int* __restrict__ cand_count) {
     extern __shared__ __align__(16) unsigned char pc_raw[];
     pdl_wait();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int num_class = NC ? NC : num_class_rt;
+    const int pa = NC ? (NC <= 2 ? 1024 : 512) : pa_rt;                 // = pc_anchors(num_class)
     const int span = pa * num_class, Q = span >> 7;                    // floats per span; 16-byte groups per lane
     unsigned char* mine_raw = pc_raw + (size_t)warp * pc_warp_bytes(num_class, pa);
     unsigned long long* pend = reinterpret_cast<unsigned long long*>(mine_raw);
@@ -331,7 +341,12 @@ __global__ void __launch_bounds__(32 * PC_WARPS) pp_candidates_kernel(const floa
     };
     auto issue = [&](const Item& q, float* dst) {
         if (q.n == span && (((uintptr_t)q.src) & 15) == 0) {
-            for (int g = 0; g < Q; g++) pc_copy16(dst + (g * 32 + lane) * 4, q.src + (g * 32 + lane) * 4);
+            if (NC) {
+#pragma unroll
+                for (int g = 0; g < (NC ? (NC <= 2 ? 1024 : 512) * NC / 128 : 1); g++) pc_copy16(dst + (g * 32 + lane) * 4, q.src + (g * 32 + lane) * 4);
+            } else {
+                for (int g = 0; g < Q; g++) pc_copy16(dst + (g * 32 + lane) * 4, q.src + (g * 32 + lane) * 4);
+            }
         } else {
             for (int g = 0; g < Q; g++) {
                 const int e = (g * 32 + lane) * 4;
@@ -372,10 +387,23 @@ __global__ void __launch_bounds__(32 * PC_WARPS) pp_candidates_kernel(const floa
         }
         const float* x = buf0 + stage * span;
         unsigned long long above = 0ull;                   // bit g * 4 + j: the lane's element j of copy group g lies above the floor
-        for (int g = 0; g < Q; g++) {
-            const float4 v = *reinterpret_cast<const float4*>(x + (g * 32 + lane) * 4);   // what this lane copied itself
-            const unsigned m = (v.x > logit_floor ? 1u : 0u) | (v.y > logit_floor ? 2u : 0u) | (v.z > logit_floor ? 4u : 0u) | (v.w > logit_floor ? 8u : 0u);
-            above |= (unsigned long long)m << (4 * g);
+        if (NC) {
+            unsigned w[2] = {0u, 0u};
+#pragma unroll
+            for (int g = 0; g < (NC ? (NC <= 2 ? 1024 : 512) * NC / 128 : 1); g++) {
+                const float4 v = *reinterpret_cast<const float4*>(x + (g * 32 + lane) * 4);   // what this lane copied itself
+                if (v.x > logit_floor) w[g >> 3] |= 1u << ((g & 7) * 4);
+                if (v.y > logit_floor) w[g >> 3] |= 2u << ((g & 7) * 4);
+                if (v.z > logit_floor) w[g >> 3] |= 4u << ((g & 7) * 4);
+                if (v.w > logit_floor) w[g >> 3] |= 8u << ((g & 7) * 4);
+            }
+            above = ((unsigned long long)w[1] << 32) | w[0];
+        } else {
+            for (int g = 0; g < Q; g++) {
+                const float4 v = *reinterpret_cast<const float4*>(x + (g * 32 + lane) * 4);
+                const unsigned m = (v.x > logit_floor ? 1u : 0u) | (v.y > logit_floor ? 2u : 0u) | (v.z > logit_floor ? 4u : 0u) | (v.w > logit_floor ? 8u : 0u);
+                above |= (unsigned long long)m << (4 * g);
+            }
         }
         const int mine = __popcll(above);
         int inc = mine;
@@ -409,8 +437,9 @@ __global__ void __launch_bounds__(32 * PC_WARPS) pp_candidates_kernel(const floa
                         float top = row[0];
                         for (int k = 1; k < num_class; k++) top = fmaxf(top, row[k]);
                         float best = sigmoidf_ref(top);
-                        for (int k = 0; k < num_class; k++)
-                            if (row[k] != top && row[k] > top - 1e-5f) best = fmaxf(best, sigmoidf_ref(row[k]));
+                        bool close = false;
+                        for (int k = 0; k < num_class; k++) close = close || (row[k] != top && row[k] > top - 1e-5f);
+                        if (close) best = pc_best_of_all(row, num_class);          // (out of line: keeps the sigmoids out of the common path)
                         ok = best >= thresh;
                         key = sel::make_key(best, (unsigned)(cur.a0 + a));
                     }
@@ -754,7 +783,11 @@ static int check_nms_limits(tcb_ctx* ctx, const char* who, float thresh, int nms
 }
 
 static int init_post3d(tcb_ctx* ctx) {   // run by tcb_create
-    TCB_SMEM_OPT_IN(ctx, pp_candidates_kernel, 200 * 1024);
+    TCB_SMEM_OPT_IN(ctx, pp_candidates_kernel<0>, 200 * 1024);
+    TCB_SMEM_OPT_IN(ctx, pp_candidates_kernel<1>, 200 * 1024);
+    TCB_SMEM_OPT_IN(ctx, pp_candidates_kernel<2>, 200 * 1024);
+    TCB_SMEM_OPT_IN(ctx, pp_candidates_kernel<3>, 200 * 1024);
+    TCB_SMEM_OPT_IN(ctx, pp_candidates_kernel<4>, 200 * 1024);
     TCB_SMEM_OPT_IN(ctx, rotated_nms_kernel, sizeof(FrameShared));
     TCB_SMEM_OPT_IN(ctx, pp_post_kernel, sizeof(FrameShared));
     TCB_SMEM_OPT_IN(ctx, cp_head_kernel, sizeof(FrameShared));
@@ -886,9 +919,14 @@ extern "C" int tcb_pp_anchor_post(tcb_ctx* ctx, const float* cls_dev, const floa
         if (items >= (1ll << 31)) return tcb_fail(ctx, TCB_ERR_LIMIT, "tcb_pp_anchor_post: batch too large");
         const long long want = tcb_div_up(items, PC_WARPS);
         const int ctas = (int)(want < (long long)ctx->num_sms * per_sm ? want : (long long)ctx->num_sms * per_sm);
-        TCB_KLAUNCH(ctx, pp_candidates_kernel, ctas, 32 * PC_WARPS, pc_smem, st, cls_dev, b, (int)n_anchors, num_class, pa, 1.0f / (float)num_class, score_thresh,
-                    logit_floor, cand, cand_count);
-        TCB_LAUNCHED(ctx);
+        auto launch = [&](auto kernel) -> int {
+            TCB_KLAUNCH(ctx, kernel, ctas, 32 * PC_WARPS, pc_smem, st, cls_dev, b, (int)n_anchors, num_class, pa, 1.0f / (float)num_class, score_thresh,
+                        logit_floor, cand, cand_count);
+            TCB_LAUNCHED(ctx);
+            return TCB_OK;
+        };
+        if ((rc = num_class == 1 ? launch(pp_candidates_kernel<1>) : num_class == 2 ? launch(pp_candidates_kernel<2>) : num_class == 3 ? launch(pp_candidates_kernel<3>)
+                : num_class == 4 ? launch(pp_candidates_kernel<4>) : launch(pp_candidates_kernel<0>))) return rc;
     }
     WideBufs wb;
     const int m_max = (int)(n_anchors < pre_max ? n_anchors : pre_max);
