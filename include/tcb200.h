@@ -201,7 +201,7 @@ int tcb_box_iou(tcb_ctx* ctx, const float* boxes_a_dev, int n, const float* boxe
  * The `*_dev` level arguments are HOST arrays of device pointers; h, w, strides host int arrays; cell_anchors_host
  * [num_levels*A*4] (x0,y0,x1,y1). Outputs: boxes [b,max_det,4], scores [b,max_det], classes int64 [b,max_det], count [b];
  * every image is processed on its own (detectron2 loops over the images of a batch).
- * topk <= 4096; if more than 4096 boxes reach the NMS the lowest-scoring ones are dropped; max_det <= 1024.
+ * topk <= 4096, num_levels*topk <= 16384 (every one of those rows can reach the NMS, as in detectron2); max_det <= 1024.
  */
 size_t tcb_detectron_post_workspace(int b, int num_levels, const int* h, const int* w, int num_anchors, int num_classes, int topk);
 int tcb_detectron_post(tcb_ctx* ctx, int b, int num_levels, const float* const* logits_dev, const float* const* deltas_dev,

@@ -68,7 +68,7 @@ ALGO = {
     "nms": ("`yolo_nms_kernel` (bench, 128 CTAs)", None),
     "detcand": ("`det_candidates_kernel` (16 RetinaNet images, 201 600 anchors x 80 classes)", 16 * 201600 * 80 * 4 // 1 * 1 // 1),
     "detlevel": ("`det_level_kernel` (80 lists, top-1000 each)", None),
-    "detpost": ("`det_post_kernel` (16 images: top-4096 of <= 5000 rows, class-aware NMS, 100 kept)", None),
+    "detpost": ("`det_post_kernel` (16 images: class-aware NMS of <= 5000 rows in rounds, 100 kept)", None),
     "ppcand": ("`pp_candidates_kernel` (16 frames x 321 408 anchors x 3 classes)", 16 * 321408 * 3 * 4),
     "decorate": ("`pillar_decorate_kernel<1,32,4>` (16 x 12 000 pillars, 32 x 4 -> 32 x 10)", 16 * 12000 * 32 * 14 * 4),
     "voxcell": ("`vox_cell_kernel<1>` (16 sweeps, 1.73 M points)", None),

@@ -42,6 +42,17 @@ def test_fcos_c3(engine):
     _check(_run(engine, logits, deltas, cells, ctr, **kw), dp.dense_inference(logits, deltas, STRIDES, cells, HW, ctrness=ctr, **kw))
 
 
+def test_more_kept_rows_wanted_than_the_best_1024_give(engine):
+    """One or two classes and a tiny IoU threshold: of ~5000 merged rows a few hundred survive, fewer than max_det, so the NMS
+    over the best 1024 rows cannot settle the result and the full width must (kept < max_det is only reachable that way)."""
+    cells = dp.retinanet_cell_anchors()
+    for nc, kw in ((1, dict(max_det=1000, nms_thresh=0.0)), (1, dict(max_det=1000, nms_thresh=0.01)), (2, dict(max_det=600, nms_thresh=0.0))):
+        logits, deltas = synth.detectron_head_outputs(3005, num_classes=nc, planted=3000)
+        got, want = _run(engine, logits, deltas, cells, **kw), dp.dense_inference(logits, deltas, STRIDES, cells, HW, **kw)
+        _check(got, want)
+        assert 100 < got[0].shape[0] < kw["max_det"]
+
+
 def test_many_candidates_and_nothing(engine):
     logits, deltas = synth.detectron_head_outputs(3004, num_classes=4, planted=3000)
     cells = dp.retinanet_cell_anchors()

@@ -267,6 +267,7 @@ struct DFrameShared {
     sel::Scratch sel;
     DNmsShared nms;
     float red[32];
+    int keptg[POST_CAP];       // merged-row ids of the rows kept so far, in order
     int total;
 };
 
@@ -373,8 +374,6 @@ __global__ void __launch_bounds__(T, 1) det_post_kernel(const DetParams p, float
     int M = 0;
     for (int l = 0; l < p.num_levels; l++) M += min(min(p.counts[img * MAX_LEVELS + l], p.A * p.K * p.lv[l].H * p.lv[l].W), p.topk);
     // torchvision.ops.batched_nms as the served (CUDA) model runs it: coordinate trick unless boxes.numel() > 20000
-    auto mkey_of = [&](int i) { return mkeys[i]; };
-    const int m = sel::cta_topk_sorted(mkey_of, M, PRE_CAP, S.skeys, S.sel);
     const int vanilla = (long long)M * 4 > 20000 ? 1 : 0;
     float mx = -INFINITY;
     for (int c = tid; c < M; c += T) { const float4 b = mbox[c]; mx = fmaxf(mx, fmaxf(fmaxf(b.x, b.y), fmaxf(b.z, b.w))); }
@@ -390,8 +389,14 @@ __global__ void __launch_bounds__(T, 1) det_post_kernel(const DetParams p, float
     }
     __syncthreads();
     const float max_coord = S.red[0];
-    for (int c = tid; c < m; c += T) {
-        const int g = (int)sel::key_index(S.skeys[c]);
+    // The greedy pass walks the rows in score order and stops at max_det kept ones. It runs in rounds over the next-best
+    // rows — 1024 first, which nearly always settles the result with a quarter of the select + sort work, then as many as
+    // fit beside the rows kept so far — each round over [rows kept so far | new rows]: the kept rows do not suppress one
+    // another, so they are kept again, in order, and the new rows are tested against all of them. Every merged row
+    // (num_levels * topk of them, more than one sort's worth) can be reached this way, as in detectron2, whose
+    // batched_nms sees them all.
+    const int post_max = min(p.max_det, POST_CAP);
+    auto load_row = [&](int g) {
         const float4 b = mbox[g];
         const int cls = mcls[g];
         const float off = vanilla ? 0.f : (float)cls * (max_coord + 1.f);   // offsets = idxs.to(boxes) * (max_coordinate + 1)
@@ -399,12 +404,41 @@ __global__ void __launch_bounds__(T, 1) det_post_kernel(const DetParams p, float
         r.x1 = b.x + off; r.y1 = b.y + off; r.x2 = b.z + off; r.y2 = b.w + off;
         r.area = (r.x2 - r.x1) * (r.y2 - r.y1);
         r.cls = cls;
-        S.R[c] = r;
+        return r;
+    };
+    int nk = 0;
+    unsigned long long below = ~0ull;                          // rows with a key under this one have not been looked at yet
+    for (int width = 1024; ; width = PRE_CAP) {
+        auto key_rest = [&](int i) { const unsigned long long k = mkeys[i]; return k < below ? k : 0ull; };   // (keys are >= 2^31: never 0)
+        const int cap = width - nk;
+        // rows not looked at yet (the others read as key 0, below every real key; the select must never be asked for more
+        // rows than there are, or zeros would count among its k largest)
+        if (tid == 0) S.total = 0;
+        __syncthreads();
+        {
+            int mine = 0;
+            for (int c = tid; c < M; c += T) mine += (mkeys[c] < below);
+            if (mine) atomicAdd(&S.total, mine);
+        }
+        __syncthreads();
+        const int left = S.total;
+        const int m = left ? sel::cta_topk_sorted(key_rest, M, min(cap, left), S.skeys, S.sel) : 0;
+        for (int c = tid; c < nk; c += T) S.R[c] = load_row(S.keptg[c]);
+        for (int c = tid; c < m; c += T) S.R[nk + c] = load_row((int)sel::key_index(S.skeys[c]));
+        __syncthreads();
+        const int nk2 = nms::cta_greedy_nms(S.R, nk + m, TvPred{p.nms_thresh, vanilla}, post_max, S.nms);
+        int gnew = -1;
+        if (tid >= nk && tid < nk2) gnew = (int)sel::key_index(S.skeys[S.nms.kpos[tid] - nk]);   // kpos[0..nk) = 0..nk-1: the rows kept before
+        const unsigned long long last = m ? S.skeys[m - 1] : 0ull;
+        __syncthreads();
+        if (gnew >= 0) S.keptg[tid] = gnew;
+        nk = nk2;
+        below = last;
+        __syncthreads();
+        if (nk == post_max || left <= cap) break;              // settled, or no row left (uniform over the CTA)
     }
-    __syncthreads();
-    const int nk = nms::cta_greedy_nms(S.R, m, TvPred{p.nms_thresh, vanilla}, min(p.max_det, POST_CAP), S.nms);
     for (int k = tid; k < nk; k += T) {
-        const int g = (int)sel::key_index(S.skeys[S.nms.kpos[k]]);
+        const int g = S.keptg[k];
         const float4 b = mbox[g];
         out_boxes[k * 4] = b.x; out_boxes[k * 4 + 1] = b.y; out_boxes[k * 4 + 2] = b.z; out_boxes[k * 4 + 3] = b.w;
         out_scores[k] = mscore[g];
