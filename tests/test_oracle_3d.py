@@ -147,3 +147,27 @@ def test_golden_remove_low_score_nu():
     assert np.array_equal(res["box3d_lidar"], g["out_boxes"]) and np.array_equal(res["scores"], g["out_scores"])
     assert np.array_equal(res["labels"], g["out_labels"])
     assert box3d.get_annotations_indices(6, 0.15, g["labels"], g["scores"]) == g["motorcycle_idx"].tolist()
+
+
+def test_fma32_is_the_correctly_rounded_fused_multiply_add():
+    """box3d.fma32 (what iou_normal's `Sa + Sb` contraction needs) against exact rational arithmetic, including sums that cancel."""
+    from fractions import Fraction
+    rng = np.random.default_rng(0)
+    a = rng.normal(0, 3, 3000).astype(np.float32)
+    b = rng.normal(0, 3, 3000).astype(np.float32)
+    c = (-(a * b) + rng.normal(0, 1e-6, 3000)).astype(np.float32)
+    c[::3] = rng.normal(0, 1e4, len(c[::3])).astype(np.float32)
+    got = box3d.fma32(a, b, c)
+    for i in range(0, 3000, 3):
+        ex = Fraction(float(a[i])) * Fraction(float(b[i])) + Fraction(float(c[i]))
+        v = np.float32(float(ex))
+        cands = [np.nextafter(v, np.float32(-np.inf)), v, np.nextafter(v, np.float32(np.inf))]
+        best = min(cands, key=lambda t: (abs(Fraction(float(t)) - ex), int(np.float32(t).view(np.uint32)) & 1))
+        assert best == got[i], (i, a[i], b[i], c[i])
+
+
+def test_nms_type_names_resolve_like_getattr_on_iou3d_nms_utils():
+    from triton_client_b200.gpu import _nms_type
+    assert _nms_type("nms_gpu") == 0 and _nms_type("nms_normal_gpu") == 1
+    with pytest.raises(AttributeError):
+        _nms_type("nms_cpu")
