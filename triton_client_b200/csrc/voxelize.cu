@@ -63,6 +63,16 @@ __device__ __forceinline__ bool vox_locate(const VoxBatch& B, int& s, int& i) {
     i = B.pt_off[s] + ((int)blockIdx.x - B.blk_off[s]) * VB + (int)threadIdx.x;
     return i < B.pt_off[s + 1];
 }
+// the same for kernels whose threads do not cooperate: CTAs of VB / SUB threads, SUB of them per block of VB points (a CTA
+// retires as soon as its own warps are done instead of waiting for the slowest of 32)
+template <int SUB>
+__device__ __forceinline__ bool vox_locate_sub(const VoxBatch& B, int& s, int& i) {
+    const int blk = (int)blockIdx.x / SUB;
+    s = vox_sweep_of_block(B, blk);
+    i = B.pt_off[s] + (blk - B.blk_off[s]) * VB + ((int)blockIdx.x % SUB) * (VB / SUB) + (int)threadIdx.x;
+    return i < B.pt_off[s + 1];
+}
+constexpr int PLACE_SUB = 4;
 
 __device__ __forceinline__ float cond_value(const VoxParams& p, int s, float v, int j) {
     if (j == 2) v = v + p.z_offset;
@@ -128,11 +138,11 @@ __global__ void __launch_bounds__(256) vox_init_kernel(long long* __restrict__ r
 }
 
 template <int ROWS>
-__global__ void __launch_bounds__(VB) vox_cell_kernel(const VoxParams p, const VoxBatch B, int2* __restrict__ pslot,
-                                                      int* __restrict__ hkey, int2* __restrict__ recs) {
+__global__ void __launch_bounds__(VB / PLACE_SUB) vox_cell_kernel(const VoxParams p, const VoxBatch B, int2* __restrict__ pslot,
+                                                                  int* __restrict__ hkey, int2* __restrict__ recs) {
     pdl_enter();
     int s, i;
-    const bool valid = vox_locate(B, s, i);
+    const bool valid = vox_locate_sub<PLACE_SUB>(B, s, i);
     float x, y, z;
     if (ROWS == ROW_VEC4) {
         if (!valid) return;
@@ -311,11 +321,11 @@ __global__ void __launch_bounds__(VB) vox_assign_kernel(const VoxParams p, const
 // Every point of a kept cell goes to its arrival position in the cell's segment (unordered; ranked afterwards). The
 // blocks of a sweep also clear the sweep's M voxels between them (the zero padding of the voxel generators), so that
 // the placement that follows only writes the rows that exist.
-__global__ void __launch_bounds__(VB) vox_scatter_kernel(const VoxParams p, const VoxBatch B, const int* m_dev, const int2* pslot,
-                                                         const int4* vrec, int* __restrict__ csr, float* __restrict__ voxels) {
+__global__ void __launch_bounds__(VB / PLACE_SUB) vox_scatter_kernel(const VoxParams p, const VoxBatch B, const int* m_dev, const int2* pslot,
+                                                                     const int4* vrec, int* __restrict__ csr, float* __restrict__ voxels) {
     pdl_enter();
     int s, i;
-    const bool valid = vox_locate(B, s, i);
+    const bool valid = vox_locate_sub<PLACE_SUB>(B, s, i);
     if (valid) {
         const int2 ps = pslot[i];
         if (ps.x >= 0) {
@@ -323,18 +333,18 @@ __global__ void __launch_bounds__(VB) vox_scatter_kernel(const VoxParams p, cons
             if (vr.y >= 0) csr[vr.y + ps.y] = i;          // vr.y < 0, "continue": the voxel was never created
         }
     }
-    const int nb = B.blk_off[s + 1] - B.blk_off[s], r = (int)blockIdx.x - B.blk_off[s];
+    const int nb = (B.blk_off[s + 1] - B.blk_off[s]) * PLACE_SUB, r = (int)blockIdx.x - B.blk_off[s] * PLACE_SUB;   // CTAs of this sweep, this one's rank
     const long long per_vox = (long long)p.max_pts * p.nfeat;
     const long long total = (long long)m_dev[s] * per_vox;                       // floats of this sweep to clear
     float* base = voxels + (long long)s * p.max_vox * per_vox;
     if ((per_vox & 3) == 0 && (((uintptr_t)voxels) & 15) == 0) {
         const long long q4 = total >> 2, chunk = (q4 + nb - 1) / nb;
         const long long lo = (long long)r * chunk, hi = min(q4, lo + chunk);
-        for (long long q = lo + threadIdx.x; q < hi; q += VB) st_stream_f4(base + 4 * q, make_float4(0.f, 0.f, 0.f, 0.f));
+        for (long long q = lo + threadIdx.x; q < hi; q += VB / PLACE_SUB) st_stream_f4(base + 4 * q, make_float4(0.f, 0.f, 0.f, 0.f));
     } else {
         const long long chunk = (total + nb - 1) / nb;
         const long long lo = (long long)r * chunk, hi = min(total, lo + chunk);
-        for (long long q = lo + threadIdx.x; q < hi; q += VB) base[q] = 0.f;
+        for (long long q = lo + threadIdx.x; q < hi; q += VB / PLACE_SUB) base[q] = 0.f;
     }
 }
 
@@ -344,11 +354,11 @@ __global__ void __launch_bounds__(VB) vox_scatter_kernel(const VoxParams p, cons
 // — read in order — straight into the voxel. The count stops (checked every 8 entries) once max_points smaller indices
 // are seen, so a crowded cell costs its late points little; only its first max_points points walk the whole segment.
 template <int ROWS>
-__global__ void __launch_bounds__(VB) vox_place_kernel(const VoxParams p, const VoxBatch B, const int2* pslot, const int4* vrec,
-                                                       const int* scalars, const int* csr, float* __restrict__ voxels) {
+__global__ void __launch_bounds__(VB / PLACE_SUB) vox_place_kernel(const VoxParams p, const VoxBatch B, const int2* pslot, const int4* vrec,
+                                                                   const int* scalars, const int* csr, float* __restrict__ voxels) {
     pdl_enter();
     int s, i;
-    if (!vox_locate(B, s, i)) return;
+    if (!vox_locate_sub<PLACE_SUB>(B, s, i)) return;
     const int sl = pslot[i].x;
     if (sl < 0) return;
     const int4 vr = vrec[sl];
@@ -835,8 +845,8 @@ extern "C" int tcb_voxelize(tcb_ctx* ctx, const float* pts_dev, int n, const int
         TCB_LAUNCHED(ctx);
     }
     if (nblk > 0) {
-        if (vec4) TCB_KLAUNCH(ctx, vox_cell_kernel<ROW_VEC4>, nblk, VB, 0, st, p, B, pslot, hkey, recs);
-        else      TCB_KLAUNCH(ctx, vox_cell_kernel<ROW_ANY>, nblk, VB, 0, st, p, B, pslot, hkey, recs);
+        if (vec4) TCB_KLAUNCH(ctx, vox_cell_kernel<ROW_VEC4>, nblk * PLACE_SUB, VB / PLACE_SUB, 0, st, p, B, pslot, hkey, recs);
+        else      TCB_KLAUNCH(ctx, vox_cell_kernel<ROW_ANY>, nblk * PLACE_SUB, VB / PLACE_SUB, 0, st, p, B, pslot, hkey, recs);
         TCB_LAUNCHED(ctx);
         const int mark_ctas = (int)(slots < (long long)ctx->num_sms * 8 * 256 ? tcb_div_up(slots, 256) : ctx->num_sms * 8);
         TCB_KLAUNCH(ctx, vox_mark_kernel, mark_ctas, 256, 0, st, B, recs, slots, p.TS, finfo, bitmap);
@@ -847,10 +857,10 @@ extern "C" int tcb_voxelize(tcb_ctx* ctx, const float* pts_dev, int n, const int
     if (nblk > 0) {
         TCB_KLAUNCH(ctx, vox_assign_kernel, nblk, VB, 0, st, p, B, finfo, hkey, blocksum, vrec, vinfo, scalars, coords_dev, num_pts_dev);
         TCB_LAUNCHED(ctx);
-        TCB_KLAUNCH(ctx, vox_scatter_kernel, nblk, VB, 0, st, p, B, m_out_dev, pslot, vrec, csr, voxels_dev);
+        TCB_KLAUNCH(ctx, vox_scatter_kernel, nblk * PLACE_SUB, VB / PLACE_SUB, 0, st, p, B, m_out_dev, pslot, vrec, csr, voxels_dev);
         TCB_LAUNCHED(ctx);
-        if (vec4) TCB_KLAUNCH(ctx, vox_place_kernel<ROW_VEC4>, nblk, VB, 0, st, p, B, pslot, vrec, scalars, csr, voxels_dev);
-        else      TCB_KLAUNCH(ctx, vox_place_kernel<ROW_ANY>, nblk, VB, 0, st, p, B, pslot, vrec, scalars, csr, voxels_dev);
+        if (vec4) TCB_KLAUNCH(ctx, vox_place_kernel<ROW_VEC4>, nblk * PLACE_SUB, VB / PLACE_SUB, 0, st, p, B, pslot, vrec, scalars, csr, voxels_dev);
+        else      TCB_KLAUNCH(ctx, vox_place_kernel<ROW_ANY>, nblk * PLACE_SUB, VB / PLACE_SUB, 0, st, p, B, pslot, vrec, scalars, csr, voxels_dev);
         TCB_LAUNCHED(ctx);
         if (overflow_mode) {
             TCB_KLAUNCH(ctx, vox_breakcount_kernel, tcb_div_up((long long)b * max_vox, 256), 256, 0, st, p, b, m_out_dev, vinfo, scalars, csr, num_pts_dev);
