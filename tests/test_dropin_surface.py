@@ -49,7 +49,8 @@ def test_signatures_match_live_reference():
              (mine.FCOSpostprocess.extract_boxes, ref.FCOSpostprocess.extract_boxes),
              (mine.Yolov5postprocess.load_class_names, ref.Yolov5postprocess.load_class_names),
              (mine.Postprocess.nms_cpu, ref.Postprocess.nms_cpu), (mine.Postprocess.box_iou, ref.Postprocess.box_iou),
-             (mine.Postprocess.xywh2xyxy, ref.Postprocess.xywh2xyxy)]
+             (mine.Postprocess.xywh2xyxy, ref.Postprocess.xywh2xyxy),
+             (mine.Yolov5postprocess.plot_boxes_cv2, ref.Yolov5postprocess.plot_boxes_cv2)]
     for a, b in pairs:
         pa, pb = inspect.signature(a).parameters, inspect.signature(b).parameters
         assert list(pa) == list(pb), (a, list(pa), list(pb))
