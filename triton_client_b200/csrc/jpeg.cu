@@ -38,6 +38,7 @@ struct JSeg { int byte_off, byte_len, mcu_first, sub_first; };   // a restart in
 struct JpegHdr {
     int width, height, ncomp, hmax, vmax, mcux, mcuy, ri, bpm;
     int comp_h[3], comp_v[3], comp_tq[3], comp_td[3], comp_ta[3], comp_bw[3], comp_bh[3], comp_first_j[3];
+    int up_hf[3], up_vf[3], up_dw[3], up_dh[3];   // upsampling factors and downsampled size of every component (colour kernel)
     int mcu_comp[MAX_BPM], mcu_bx[MAX_BPM], mcu_by[MAX_BPM];
     long long scan_off;            // bytes, inside the batch's scan buffer (16-byte aligned)
     int scan_len, seg_first, nseg, sub_first, nsub;
@@ -359,19 +360,35 @@ __global__ void __launch_bounds__(256) jpeg_colour_kernel(const JpegHdr* __restr
         for (int i = 0; i < npx; i++) px[i] = (unsigned char)(yw >> (8 * i));
         return;
     }
-    int hf[2], vf[2], dw[2], dh[2];
+    const int hf[2] = {H.up_hf[1], H.up_hf[2]}, vf[2] = {H.up_vf[1], H.up_vf[2]}, dw[2] = {H.up_dw[1], H.up_dw[2]}, dh[2] = {H.up_dh[1], H.up_dh[2]};
+    // 4:2:0 away from the left / right edge (nearly every thread of a camera frame): the four pixels share two chroma columns
+    // and their two neighbours — eight bytes per component instead of a look-up per pixel. v(c) = 3 * near row + far row;
+    // even x: (3 v(c) + v(c - 1) + 8) >> 4, odd x: (3 v(c) + v(c + 1) + 7) >> 4 (chroma_at, h2v2).
+    int cbv[4], crv[4];
+    const int c0 = x0 >> 1;
+    const bool fast = npx == 4 && hf[0] == 2 && vf[0] == 2 && hf[1] == 2 && vf[1] == 2 && c0 >= 1 && c0 + 2 < min(dw[0], dw[1]);
+    if (fast) {
 #pragma unroll
-    for (int c = 1; c < 3; c++) {
-        hf[c - 1] = H.hmax / H.comp_h[c]; vf[c - 1] = H.vmax / H.comp_v[c];
-        dw[c - 1] = (H.width * H.comp_h[c] + H.hmax - 1) / H.hmax; dh[c - 1] = (H.height * H.comp_v[c] + H.vmax - 1) / H.vmax;
+        for (int c = 0; c < 2; c++) {
+            const unsigned char* pl = planes + H.plane_off[1 + c];
+            const int pitch = H.comp_bw[1 + c] * 8, cy = y >> 1, yn = (y & 1) ? min(cy + 1, dh[c] - 1) : max(cy - 1, 0);
+            const unsigned char* r0 = pl + (long long)cy * pitch + c0 - 1;
+            const unsigned char* r1 = pl + (long long)yn * pitch + c0 - 1;
+            int v[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) v[k] = r0[k] * 3 + r1[k];
+            int* o4 = c == 0 ? cbv : crv;
+            o4[0] = (3 * v[1] + v[0] + 8) >> 4; o4[1] = (3 * v[1] + v[2] + 7) >> 4;
+            o4[2] = (3 * v[2] + v[1] + 8) >> 4; o4[3] = (3 * v[2] + v[3] + 7) >> 4;
+        }
     }
     unsigned char rgb[12];
 #pragma unroll
     for (int i = 0; i < 4; i++) {
         const int x = min(x0 + i, H.width - 1);
         const int Y = (int)((yw >> (8 * i)) & 255u);
-        const int cb = chroma_at(planes + H.plane_off[1], H.comp_bw[1] * 8, dw[0], dh[0], hf[0], vf[0], x, y) - 128;
-        const int cr = chroma_at(planes + H.plane_off[2], H.comp_bw[2] * 8, dw[1], dh[1], hf[1], vf[1], x, y) - 128;
+        const int cb = (fast ? cbv[i] : chroma_at(planes + H.plane_off[1], H.comp_bw[1] * 8, dw[0], dh[0], hf[0], vf[0], x, y)) - 128;
+        const int cr = (fast ? crv[i] : chroma_at(planes + H.plane_off[2], H.comp_bw[2] * 8, dw[1], dh[1], hf[1], vf[1], x, y)) - 128;
         const int r = min(max(Y + ((91881 * cr + 32768) >> 16), 0), 255);
         const int g = min(max(Y + ((-22554 * cb + 32768 - 46802 * cr) >> 16), 0), 255);
         const int b = min(max(Y + ((116130 * cb + 32768) >> 16), 0), 255);
@@ -484,6 +501,8 @@ const char* parse_jpeg(const unsigned char* d, size_t len, JpegHdr& h, unsigned 
         for (int v = 0; v < h.comp_v[c]; v++)
             for (int hh = 0; hh < h.comp_h[c]; hh++) { h.mcu_comp[h.bpm] = c; h.mcu_bx[h.bpm] = hh; h.mcu_by[h.bpm] = v; h.bpm++; }
         h.comp_bw[c] = h.mcux * h.comp_h[c]; h.comp_bh[c] = h.mcuy * h.comp_v[c];
+        h.up_hf[c] = h.hmax / h.comp_h[c]; h.up_vf[c] = h.vmax / h.comp_v[c];
+        h.up_dw[c] = (h.width * h.comp_h[c] + h.hmax - 1) / h.hmax; h.up_dh[c] = (h.height * h.comp_v[c] + h.vmax - 1) / h.vmax;
     }
     h.blocks = (long long)h.mcux * h.mcuy * h.bpm;
     // entropy-coded data: unstuff, cut at RSTn, stop at any other marker (EOI)
